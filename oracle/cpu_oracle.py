@@ -1,0 +1,252 @@
+"""ctypes view of oracle/liboracle.so (and oracle/_ref/libref_kdtree.so).
+
+TEST INFRASTRUCTURE ONLY -- the checker, never the product.  Importers allowed: tests/,
+__graft_entry__.smoke(), bench.py's cpu_baseline / --impl reference legs.  The product package
+(racing-slam_b200/) never imports this module.
+
+Reference restated: see the header of oracle/slam_oracle.cpp (file:line citations there).
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+from dataclasses import dataclass
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB = None
+_REF = None
+
+
+def build(verbose: bool = False) -> None:
+    """Compile liboracle.so (and oracle/_ref when /root/reference exists) via oracle/Makefile."""
+    r = subprocess.run(["make", "-C", _HERE], capture_output=True, text=True)
+    if verbose or r.returncode != 0:
+        print(r.stdout, r.stderr)
+    if r.returncode != 0:
+        raise RuntimeError("oracle build failed")
+
+
+def _ptr(a, ctype):
+    if a is None:
+        return None
+    return a.ctypes.data_as(C.POINTER(ctype))
+
+
+class ProjParams(C.Structure):
+    """Mirror of OrcProjParams; constants of src/MapMatcher.cpp:12-18 as runtime values."""
+    _fields_ = [("fx", C.c_float), ("fy", C.c_float), ("cx", C.c_float), ("cy", C.c_float),
+                ("width", C.c_int32), ("height", C.c_int32), ("radius", C.c_float), ("max_dist", C.c_float),
+                ("min_cos", C.c_float), ("nearer", C.c_float), ("further", C.c_float), ("replace", C.c_int32)]
+
+
+def lib():
+    global _LIB
+    if _LIB is None:
+        path = os.path.join(_HERE, "liboracle.so")
+        if not os.path.exists(path):
+            build()
+        L = C.CDLL(path)
+        u8p, i32p, f32p, u32p = (C.POINTER(C.c_uint8), C.POINTER(C.c_int32), C.POINTER(C.c_float),
+                                 C.POINTER(C.c_uint32))
+        L.orc_hamming256.argtypes = [u8p, u8p]
+        L.orc_hamming256.restype = C.c_int
+        L.orc_knn2.argtypes = [u8p, C.c_int, u8p, C.c_int, i32p, i32p]
+        L.orc_crosscheck.argtypes = [u8p, C.c_int, u8p, C.c_int, i32p, i32p]
+        L.orc_match_descriptors.argtypes = [u8p, C.c_int, u8p, C.c_int, C.c_float, C.c_float, i32p, i32p]
+        L.orc_match_descriptors.restype = C.c_int
+        L.orc_match_features.argtypes = [u8p, C.c_int, u8p, C.c_int, C.c_float, i32p, i32p]
+        L.orc_match_features.restype = C.c_int
+        L.orc_kd_build.argtypes = [f32p, C.c_int, u32p]
+        L.orc_kd_radius_search.argtypes = [f32p, u32p, C.c_int, C.c_float, C.c_float, C.c_float, i32p, C.c_int]
+        L.orc_kd_radius_search.restype = C.c_int
+        L.orc_camera_center.argtypes = [f32p, f32p]
+        L.orc_projection_matrix.argtypes = [f32p, C.c_float, C.c_float, C.c_float, C.c_float, f32p]
+        L.orc_project.argtypes = [f32p, C.c_float, C.c_float, C.c_float, C.c_float, f32p, C.c_int, f32p]
+        L.orc_point_stats.argtypes = [f32p, C.c_int, i32p, f32p, f32p, f32p]
+        L.orc_match_projection.argtypes = [C.c_int, f32p, u8p, u32p, u8p, C.c_int, f32p, f32p, f32p, i32p, u8p, u8p,
+                                           i32p, C.c_int, f32p, C.POINTER(ProjParams), i32p, i32p, f32p, i32p, i32p,
+                                           C.POINTER(C.c_int64)]
+        _LIB = L
+    return _LIB
+
+
+def ref_kdtree():
+    """The reference's own KDTree2D (oracle/_ref/libref_kdtree.so) or None when not built."""
+    global _REF
+    if _REF is None:
+        path = os.path.join(_HERE, "_ref", "libref_kdtree.so")
+        if not os.path.exists(path):
+            return None
+        R = C.CDLL(path)
+        R.ref_kd_create.argtypes = [C.POINTER(C.c_float), C.c_int]
+        R.ref_kd_create.restype = C.c_void_p
+        R.ref_kd_radius_search.argtypes = [C.c_void_p, C.c_float, C.c_float, C.c_float, C.POINTER(C.c_int32), C.c_int]
+        R.ref_kd_radius_search.restype = C.c_int
+        R.ref_kd_destroy.argtypes = [C.c_void_p]
+        _REF = R
+    return _REF
+
+
+def _u8(a):
+    a = np.ascontiguousarray(a, dtype=np.uint8)
+    return a.reshape(-1, 32) if a.size else a.reshape(0, 32)
+
+
+def hamming(a, b) -> int:
+    a, b = np.ascontiguousarray(a, np.uint8), np.ascontiguousarray(b, np.uint8)
+    return lib().orc_hamming256(_ptr(a, C.c_uint8), _ptr(b, C.c_uint8))
+
+
+def knn2(q, t):
+    q, t = _u8(q), _u8(t)
+    idx = np.full((len(q), 2), -1, np.int32)
+    dist = np.full((len(q), 2), -1, np.int32)
+    if len(q):
+        lib().orc_knn2(_ptr(q, C.c_uint8), len(q), _ptr(t, C.c_uint8), len(t), _ptr(idx, C.c_int32),
+                       _ptr(dist, C.c_int32))
+    return idx, dist
+
+
+def crosscheck(q, t):
+    q, t = _u8(q), _u8(t)
+    idx = np.full(len(q), -1, np.int32)
+    dist = np.full(len(q), -1, np.int32)
+    if len(q):
+        lib().orc_crosscheck(_ptr(q, C.c_uint8), len(q), _ptr(t, C.c_uint8), len(t), _ptr(idx, C.c_int32),
+                             _ptr(dist, C.c_int32))
+    return idx, dist
+
+
+def match_descriptors(q, t, max_dist=64.0, ratio=0.75):
+    """(query_idx, train_idx) arrays; src/MapMatcher.cpp:129-163 with train = matched key-frame rows."""
+    q, t = _u8(q), _u8(t)
+    oq = np.zeros(max(len(q), 1), np.int32)
+    ot = np.zeros(max(len(q), 1), np.int32)
+    n = lib().orc_match_descriptors(_ptr(q, C.c_uint8), len(q), _ptr(t, C.c_uint8), len(t), max_dist, ratio,
+                                    _ptr(oq, C.c_int32), _ptr(ot, C.c_int32))
+    return oq[:n].copy(), ot[:n].copy()
+
+
+def match_features(prev, cur, max_dist=64.0):
+    """(train_idx, query_idx) arrays; src/features/FeatureExtractor.cpp:15-30."""
+    prev, cur = _u8(prev), _u8(cur)
+    ot = np.zeros(max(len(cur), 1), np.int32)
+    oq = np.zeros(max(len(cur), 1), np.int32)
+    n = lib().orc_match_features(_ptr(prev, C.c_uint8), len(prev), _ptr(cur, C.c_uint8), len(cur), max_dist,
+                                 _ptr(ot, C.c_int32), _ptr(oq, C.c_int32))
+    return ot[:n].copy(), oq[:n].copy()
+
+
+def kd_build(xy):
+    xy = np.ascontiguousarray(xy, np.float32).reshape(-1, 2)
+    perm = np.zeros(len(xy), np.uint32)
+    lib().orc_kd_build(_ptr(xy, C.c_float), len(xy), _ptr(perm, C.c_uint32))
+    return perm
+
+
+def kd_radius_search(xy, perm, target, radius, cap=4096):
+    xy = np.ascontiguousarray(xy, np.float32).reshape(-1, 2)
+    perm = np.ascontiguousarray(perm, np.uint32)
+    out = np.zeros(cap, np.int32)
+    n = lib().orc_kd_radius_search(_ptr(xy, C.c_float), _ptr(perm, C.c_uint32), len(xy), float(target[0]),
+                                   float(target[1]), float(radius), _ptr(out, C.c_int32), cap)
+    assert n <= cap
+    return out[:n].copy()
+
+
+def ref_kd_radius_search_all(xy, targets, radius, cap=4096):
+    """Run the REFERENCE KDTree2D on every target; list of index arrays in push_back order."""
+    R = ref_kdtree()
+    assert R is not None
+    xy = np.ascontiguousarray(xy, np.float32).reshape(-1, 2)
+    h = R.ref_kd_create(_ptr(xy, C.c_float), len(xy))
+    out = np.zeros(cap, np.int32)
+    res = []
+    try:
+        for t in np.asarray(targets, np.float32).reshape(-1, 2):
+            n = R.ref_kd_radius_search(h, float(t[0]), float(t[1]), float(radius), _ptr(out, C.c_int32), cap)
+            assert n <= cap
+            res.append(out[:n].copy())
+    finally:
+        R.ref_kd_destroy(h)
+    return res
+
+
+def camera_center(pose_colmajor):
+    p = np.ascontiguousarray(pose_colmajor, np.float32).reshape(16)
+    c = np.zeros(3, np.float32)
+    lib().orc_camera_center(_ptr(p, C.c_float), _ptr(c, C.c_float))
+    return c
+
+
+def projection_matrix(pose_colmajor, fx, fy, cx, cy):
+    p = np.ascontiguousarray(pose_colmajor, np.float32).reshape(16)
+    m = np.zeros(12, np.float32)
+    lib().orc_projection_matrix(_ptr(p, C.c_float), fx, fy, cx, cy, _ptr(m, C.c_float))
+    return m.reshape(3, 4)
+
+
+def project(pose_colmajor, fx, fy, cx, cy, pos):
+    p = np.ascontiguousarray(pose_colmajor, np.float32).reshape(16)
+    pos = np.ascontiguousarray(pos, np.float32).reshape(-1, 3)
+    uv = np.zeros((len(pos), 2), np.float32)
+    lib().orc_project(_ptr(p, C.c_float), fx, fy, cx, cy, _ptr(pos, C.c_float), len(pos), _ptr(uv, C.c_float))
+    return uv
+
+
+def point_stats(pos, obs_offset, obs_center):
+    """avg_viewing_normal / observed_distance_range (src/MapPoint.cpp:24-45) per point."""
+    pos = np.ascontiguousarray(pos, np.float32).reshape(-1, 3)
+    obs_offset = np.ascontiguousarray(obs_offset, np.int32)
+    obs_center = np.ascontiguousarray(obs_center, np.float32).reshape(-1, 3)
+    normal = np.zeros((len(pos), 3), np.float32)
+    rng = np.zeros((len(pos), 2), np.float32)
+    lib().orc_point_stats(_ptr(pos, C.c_float), len(pos), _ptr(obs_offset, C.c_int32), _ptr(obs_center, C.c_float),
+                          _ptr(normal, C.c_float), _ptr(rng, C.c_float))
+    return normal, rng
+
+
+@dataclass
+class ProjResult:
+    point: np.ndarray      # [nkp] point-set index or -1
+    dist: np.ndarray       # [nkp] Hamming distance or -1
+    uv: np.ndarray         # [n_visit, 2] projections (NaN where the point was skipped up front)
+    kp: np.ndarray         # [n_visit] keypoint each visited point chose, -1 = none
+    d: np.ndarray          # [n_visit]
+    near_border: int
+    near_radius: int
+
+
+def match_projection(kp_xy, kp_desc, kd_perm, kp_matched, pos, normal, rng, obs_offset, obs_desc, skip, order, pose,
+                     params: ProjParams, want_stats=True) -> ProjResult:
+    kp_xy = np.ascontiguousarray(kp_xy, np.float32).reshape(-1, 2)
+    kp_desc = _u8(kp_desc)
+    nkp = len(kp_xy)
+    kd_perm = np.ascontiguousarray(kd_perm, np.uint32)
+    kp_matched = None if kp_matched is None else np.ascontiguousarray(kp_matched, np.uint8)
+    pos = np.ascontiguousarray(pos, np.float32).reshape(-1, 3)
+    normal = np.ascontiguousarray(normal, np.float32).reshape(-1, 3)
+    rng = np.ascontiguousarray(rng, np.float32).reshape(-1, 2)
+    obs_offset = np.ascontiguousarray(obs_offset, np.int32)
+    obs_desc = _u8(obs_desc)
+    skip = None if skip is None else np.ascontiguousarray(skip, np.uint8)
+    order = None if order is None else np.ascontiguousarray(order, np.int32)
+    n_visit = len(order) if order is not None else len(pos)
+    pose = np.ascontiguousarray(pose, np.float32).reshape(16)
+    out_point = np.full(nkp, -1, np.int32)
+    out_dist = np.full(nkp, -1, np.int32)
+    uv = np.zeros((n_visit, 2), np.float32)
+    kp = np.zeros(n_visit, np.int32)
+    d = np.zeros(n_visit, np.int32)
+    stats = (C.c_int64 * 2)(0, 0)
+    lib().orc_match_projection(nkp, _ptr(kp_xy, C.c_float), _ptr(kp_desc, C.c_uint8), _ptr(kd_perm, C.c_uint32),
+                               _ptr(kp_matched, C.c_uint8), len(pos), _ptr(pos, C.c_float), _ptr(normal, C.c_float),
+                               _ptr(rng, C.c_float), _ptr(obs_offset, C.c_int32), _ptr(obs_desc, C.c_uint8),
+                               _ptr(skip, C.c_uint8), _ptr(order, C.c_int32), n_visit, _ptr(pose, C.c_float),
+                               C.byref(params), _ptr(out_point, C.c_int32), _ptr(out_dist, C.c_int32),
+                               _ptr(uv, C.c_float), _ptr(kp, C.c_int32), _ptr(d, C.c_int32),
+                               stats if want_stats else None)
+    return ProjResult(out_point, out_dist, uv, kp, d, int(stats[0]), int(stats[1]))

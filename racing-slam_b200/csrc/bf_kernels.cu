@@ -1,0 +1,543 @@
+// bf_kernels.cu -- brute-force Hamming kNN-2 / cross-check kernels for sm_100a.
+//
+// Replaces the arithmetic of cv::BFMatcher::knnMatch as the reference calls it
+// (src/MapMatcher.cpp:147-148, src/features/FeatureExtractor.cpp:20-21):
+//   K1  bf_scan_kernel     XOR + POPC distances, per-thread packed-key top-2 over a train range that
+//                          is streamed through shared memory with cp.async.bulk (TMA) + mbarrier
+//   K3  bf_finish_*        merge of the train-split partials + the reference's filters
+//   K2  bf_mutual_kernel   cross-check mutuality from row and column partials
+//
+// Roofline: the integer POPC pipe (8 POPC32 per 256-bit comparison), not HBM: a descriptor
+// byte is reused by every query row of the tile.
+#include "slamgpu_internal.cuh"
+
+namespace slamgpu {
+
+namespace {
+
+constexpr int kThreads = 256;
+constexpr int kChunk = 128;                 // train descriptors per shared-memory stage (4 KB)
+constexpr int kStages = 4;                  // ring depth -> 16 KB of shared memory per CTA
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p)
+{
+    return static_cast<uint32_t>(__cvta_generic_to_shared(p));
+}
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity)
+{
+    uint32_t ok;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok)
+        : "r"(smem_u32(bar)), "r"(parity)
+        : "memory");
+    return ok != 0;
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity)
+{
+    while (!mbar_try_wait(bar, parity)) {
+    }
+}
+// 1-D bulk async copy global -> shared (TMA engine, SASS UBLKCP); completion is counted in
+// bytes on the mbarrier.  src/dst 16-byte aligned, size a multiple of 16.
+__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar)
+{
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                     smem_u32(dst)),
+                 "l"(src), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
+
+struct ScanArgs {
+    const uint8_t* q_base;
+    const uint8_t* t_base;
+    const int32_t* frame_offset;  // batched: row offsets of every frame; null = single pair
+    const int32_t* pairs;         // batched: [n_pairs x 2] (query_frame, train_frame)
+    int nq, nt;                   // single pair sizes
+    int tiles, splits, t_per_split;
+    int max_rows;                 // row stride of the key array per (pair, split)
+    int swap_roles;               // batched only: scan pair as (train_frame, query_frame)
+    uint2* keys;
+};
+
+// 256-bit Hamming distance: 8 x (LOP3 xor + POPC) + adds.
+__device__ __forceinline__ uint32_t hamming256(const uint32_t (&q)[8], const uint4& a, const uint4& b)
+{
+    return __popc(q[0] ^ a.x) + __popc(q[1] ^ a.y) + __popc(q[2] ^ a.z) + __popc(q[3] ^ a.w) +
+           __popc(q[4] ^ b.x) + __popc(q[5] ^ b.y) + __popc(q[6] ^ b.z) + __popc(q[7] ^ b.w);
+}
+
+template <int R>
+__device__ __forceinline__ void scan_one(const uint4* __restrict__ sm, int j, uint32_t tkey,
+                                         const uint32_t (&q)[R][8], uint32_t (&b0)[R], uint32_t (&b1)[R])
+{
+    const uint4 a = sm[2 * j];      // warp-uniform address -> shared-memory broadcast
+    const uint4 b = sm[2 * j + 1];
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+        const uint32_t d = hamming256(q[r], a, b);
+        const uint32_t key = (d << kIdxBits) | tkey;
+        const uint32_t hi = max(key, b0[r]);
+        b0[r] = min(key, b0[r]);
+        b1[r] = min(b1[r], hi);
+    }
+}
+
+template <int R>
+__global__ void __launch_bounds__(kThreads) bf_scan_kernel(const ScanArgs a)
+{
+    __shared__ __align__(128) uint4 s_train[kStages][kChunk * 2];
+    __shared__ __align__(8) uint64_t s_full[kStages];
+
+    const int tid = threadIdx.x;
+    int bid = blockIdx.x;
+    const int tile = bid % a.tiles;
+    bid /= a.tiles;
+    const int split = bid % a.splits;
+    const int pair = bid / a.splits;
+
+    const uint8_t* qp = a.q_base;
+    const uint8_t* tp = a.t_base;
+    int nq = a.nq, nt = a.nt;
+    if (a.pairs != nullptr) {
+        int fq = a.pairs[2 * pair], ft = a.pairs[2 * pair + 1];
+        if (a.swap_roles) {
+            const int tmp = fq; fq = ft; ft = tmp;
+        }
+        const int q0 = a.frame_offset[fq], t0 = a.frame_offset[ft];
+        nq = a.frame_offset[fq + 1] - q0;
+        nt = a.frame_offset[ft + 1] - t0;
+        qp += static_cast<size_t>(q0) * 32;
+        tp += static_cast<size_t>(t0) * 32;
+    }
+    const int row0 = tile * (kThreads * R);
+    if (row0 >= nq) return;   // ragged batch: this pair has fewer query tiles (finish never reads them)
+
+    const int t_begin = min(split * a.t_per_split, nt);
+    const int t_end = min(t_begin + a.t_per_split, nt);
+    const int n_chunks = (t_end - t_begin + kChunk - 1) / kChunk;
+
+    if (tid == 0) {
+#pragma unroll
+        for (int s = 0; s < kStages; ++s) mbar_init(&s_full[s], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+
+    auto issue = [&](int c) {
+        const int s = c % kStages;
+        const int t0 = t_begin + c * kChunk;
+        const uint32_t bytes = static_cast<uint32_t>(min(kChunk, t_end - t0)) * 32u;
+        mbar_expect_tx(&s_full[s], bytes);
+        bulk_g2s(&s_train[s][0], tp + static_cast<size_t>(t0) * 32, bytes, &s_full[s]);
+    };
+    if (tid == 0) {
+        for (int c = 0; c < min(kStages - 1, n_chunks); ++c) issue(c);
+    }
+
+    // query rows live in registers: R x 8 words per thread, rows tile-strided so loads coalesce
+    uint32_t q[R][8];
+    uint32_t b0[R], b1[R];
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+        const int row = min(row0 + r * kThreads + tid, nq - 1);
+        const uint4* src = reinterpret_cast<const uint4*>(qp + static_cast<size_t>(row) * 32);
+        const uint4 lo = __ldg(src), hi = __ldg(src + 1);
+        q[r][0] = lo.x; q[r][1] = lo.y; q[r][2] = lo.z; q[r][3] = lo.w;
+        q[r][4] = hi.x; q[r][5] = hi.y; q[r][6] = hi.z; q[r][7] = hi.w;
+        b0[r] = kKeyNone;
+        b1[r] = kKeyNone;
+    }
+
+    for (int c = 0; c < n_chunks; ++c) {
+        // the stage refilled here was consumed in iteration c-1 (the __syncthreads below orders it)
+        if (tid == 0 && c + kStages - 1 < n_chunks) issue(c + kStages - 1);
+        const int s = c % kStages;
+        mbar_wait(&s_full[s], static_cast<uint32_t>((c / kStages) & 1));
+        const int t0 = t_begin + c * kChunk;
+        const int cnt = min(kChunk, t_end - t0);
+        const uint4* sm = &s_train[s][0];
+        if (cnt == kChunk) {
+#pragma unroll 4
+            for (int j = 0; j < kChunk; ++j) scan_one<R>(sm, j, static_cast<uint32_t>(t0 + j), q, b0, b1);
+        } else {
+            for (int j = 0; j < cnt; ++j) scan_one<R>(sm, j, static_cast<uint32_t>(t0 + j), q, b0, b1);
+        }
+        __syncthreads();
+    }
+
+    uint2* out = a.keys + (static_cast<size_t>(pair) * a.splits + split) * a.max_rows;
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+        const int row = row0 + r * kThreads + tid;
+        if (row < nq) out[row] = make_uint2(b0[r], b1[r]);
+    }
+}
+
+// merge the split partials of one query row
+__device__ __forceinline__ uint2 merge_partials(const uint2* keys, int splits, size_t stride)
+{
+    uint32_t m0 = kKeyNone, m1 = kKeyNone;
+    for (int s = 0; s < splits; ++s) {
+        const uint2 p = keys[s * stride];
+        uint32_t hi = max(p.x, m0);
+        m0 = min(p.x, m0);
+        m1 = min(m1, hi);
+        m1 = min(m1, p.y);   // p.y >= p.x, so it can only compete for second place
+    }
+    return make_uint2(m0, m1);
+}
+
+__global__ void bf_finish_raw_kernel(const uint2* keys, int splits, int max_rows, int nq, int32_t* idx, int32_t* dist)
+{
+    const int q = blockIdx.x * blockDim.x + threadIdx.x;
+    if (q >= nq) return;
+    const uint2 m = merge_partials(keys + q, splits, max_rows);
+    int2 i, d;
+    i.x = m.x == kKeyNone ? -1 : static_cast<int>(m.x & kIdxMask);
+    d.x = m.x == kKeyNone ? -1 : static_cast<int>(m.x >> kIdxBits);
+    i.y = m.y == kKeyNone ? -1 : static_cast<int>(m.y & kIdxMask);
+    d.y = m.y == kKeyNone ? -1 : static_cast<int>(m.y >> kIdxBits);
+    reinterpret_cast<int2*>(idx)[q] = i;
+    reinterpret_cast<int2*>(dist)[q] = d;
+}
+
+struct FilterArgs {
+    const uint2* keys;
+    int splits, max_rows;
+    int nq, nt;                    // single pair
+    const int32_t* frame_offset;   // batched
+    const int32_t* pairs;
+    float max_dist, ratio;
+    int32_t* out_train;            // [pair][max_rows]
+    int32_t* out_count;            // [pair]
+};
+
+// src/MapMatcher.cpp:151-161: drop if d0 > max_dist (float, non-strict) or, with k = 2,
+// d0 > ratio * d1 (float multiply, no contraction possible: the product feeds a compare).
+__global__ void bf_finish_filter_kernel(const FilterArgs a)
+{
+    const int pair = blockIdx.y;
+    int nq = a.nq, nt = a.nt;
+    if (a.pairs != nullptr) {
+        const int fq = a.pairs[2 * pair], ft = a.pairs[2 * pair + 1];
+        nq = a.frame_offset[fq + 1] - a.frame_offset[fq];
+        nt = a.frame_offset[ft + 1] - a.frame_offset[ft];
+    }
+    const int q = blockIdx.x * blockDim.x + threadIdx.x;
+    bool keep = false;
+    int train = -1;
+    if (q < nq) {
+        const uint2 m = merge_partials(a.keys + static_cast<size_t>(pair) * a.splits * a.max_rows + q, a.splits,
+                                       a.max_rows);
+        if (m.x != kKeyNone) {
+            const float d0 = static_cast<float>(m.x >> kIdxBits);
+            keep = !(d0 > a.max_dist);
+            if (keep && nt >= 2 && m.y != kKeyNone) {
+                const float d1 = static_cast<float>(m.y >> kIdxBits);
+                keep = !(d0 > __fmul_rn(a.ratio, d1));
+            }
+            if (keep) train = static_cast<int>(m.x & kIdxMask);
+        }
+        a.out_train[static_cast<size_t>(pair) * a.max_rows + q] = train;
+    } else if (q < a.max_rows) {
+        a.out_train[static_cast<size_t>(pair) * a.max_rows + q] = -1;   // ragged batch padding
+    }
+    const unsigned ballot = __ballot_sync(0xFFFFFFFFu, keep);
+    if ((threadIdx.x & 31) == 0 && ballot != 0) atomicAdd(&a.out_count[pair], __popc(ballot));
+}
+
+// cross-check: (q,t) survives iff t = argmin row q and q = argmin column t (lowest index on ties).
+// strict_max_dist < 0: raw cross-check.  >= 0: also require distance < strict_max_dist
+// (src/features/FeatureExtractor.cpp:25).
+__global__ void bf_mutual_kernel(const uint2* row_keys, int row_splits, int row_stride, const uint2* col_keys,
+                                 int col_splits, int col_stride, int nq, float strict_max_dist, int32_t* idx,
+                                 int32_t* dist)
+{
+    const int q = blockIdx.x * blockDim.x + threadIdx.x;
+    if (q >= nq) return;
+    const uint2 m = merge_partials(row_keys + q, row_splits, row_stride);
+    int oi = -1, od = -1;
+    if (m.x != kKeyNone) {
+        const int t = static_cast<int>(m.x & kIdxMask);
+        const uint2 c = merge_partials(col_keys + t, col_splits, col_stride);
+        if (c.x != kKeyNone && static_cast<int>(c.x & kIdxMask) == q) {
+            const int d = static_cast<int>(m.x >> kIdxBits);
+            if (strict_max_dist < 0.0f || static_cast<float>(d) < strict_max_dist) {
+                oi = t;
+                od = d;
+            }
+        }
+    }
+    idx[q] = oi;
+    dist[q] = od;
+}
+
+// exclusive scan of per-pair counts (single CTA; n is at most a few hundred thousand)
+__global__ void bf_scan_counts_kernel(const int32_t* count, int n, int32_t* offset)
+{
+    __shared__ int s_warp[32];
+    __shared__ int s_carry;
+    if (threadIdx.x == 0) s_carry = 0;
+    __syncthreads();
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (int base = 0; base < n; base += blockDim.x) {
+        const int i = base + threadIdx.x;
+        const int v = i < n ? count[i] : 0;
+        int x = v;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int y = __shfl_up_sync(0xFFFFFFFFu, x, o);
+            if (lane >= o) x += y;
+        }
+        if (lane == 31) s_warp[warp] = x;
+        __syncthreads();
+        if (warp == 0) {
+            int w = lane < (blockDim.x >> 5) ? s_warp[lane] : 0;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const int y = __shfl_up_sync(0xFFFFFFFFu, w, o);
+                if (lane >= o) w += y;
+            }
+            s_warp[lane] = w;   // inclusive scan of warp totals
+        }
+        __syncthreads();
+        const int warp_off = warp == 0 ? 0 : s_warp[warp - 1];
+        const int carry = s_carry;
+        if (i < n) offset[i] = carry + warp_off + x - v;
+        __syncthreads();
+        if (threadIdx.x == blockDim.x - 1) s_carry = carry + warp_off + x;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) offset[n] = s_carry;
+}
+
+// ordered compaction: one warp per pair walks its rows 32 at a time
+__global__ void bf_compact_kernel(const int32_t* out_train, const int32_t* frame_offset, const int32_t* pairs,
+                                  int nq_single, int n_pairs, int max_rows, const int32_t* offset,
+                                  int32_t* query_list, int32_t* train_list)
+{
+    const int pair = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    if (pair >= n_pairs) return;
+    int nq = nq_single;
+    if (pairs != nullptr) {
+        const int fq = pairs[2 * pair];
+        nq = frame_offset[fq + 1] - frame_offset[fq];
+    }
+    int pos = offset[pair];
+    const int32_t* src = out_train + static_cast<size_t>(pair) * max_rows;
+    for (int base = 0; base < nq; base += 32) {
+        const int q = base + lane;
+        const int t = q < nq ? src[q] : -1;
+        const unsigned ballot = __ballot_sync(0xFFFFFFFFu, t >= 0);
+        if (t >= 0) {
+            const int p = pos + __popc(ballot & ((1u << lane) - 1u));
+            query_list[p] = q;
+            train_list[p] = t;
+        }
+        pos += __popc(ballot);
+    }
+}
+
+} // namespace
+
+BfPlan bf_make_plan(int n_sm, int nq_max, int nt_max, int64_t n_pairs)
+{
+    BfPlan p;
+    const int64_t target = static_cast<int64_t>(n_sm) * 4;   // ~32 resident warps per SM
+    const int64_t work_r2 = ((nq_max + 511) / 512) * static_cast<int64_t>((nt_max + kChunk - 1) / kChunk) * n_pairs;
+    p.r = work_r2 >= target ? 2 : 1;
+    p.tile = kThreads * p.r;
+    p.tiles = max(1, (nq_max + p.tile - 1) / p.tile);
+    const int64_t ctas_no_split = static_cast<int64_t>(p.tiles) * n_pairs;
+    int64_t splits = (target + ctas_no_split - 1) / ctas_no_split;
+    const int64_t max_splits = max(1, (nt_max + 31) / 32);
+    splits = min(max(splits, int64_t(1)), max_splits);
+    int tps = static_cast<int>((nt_max + splits - 1) / splits);
+    tps = max(8, (tps + 7) & ~7);
+    p.t_per_split = tps;
+    p.splits = max(1, (nt_max + tps - 1) / tps);
+    return p;
+}
+
+size_t bf_partial_elems(const BfPlan& p, int64_t n_pairs, int max_rows)
+{
+    return static_cast<size_t>(n_pairs) * p.splits * max_rows;
+}
+
+int bf_launch_scan(slamgpu_ctx* ctx, const BfPlan& plan, const uint8_t* d_query, int nq, const uint8_t* d_train,
+                   int nt, const int32_t* d_frame_offset, const int32_t* d_pairs, int n_pairs, int max_rows,
+                   bool swap_roles, uint2* d_keys)
+{
+    ScanArgs a;
+    a.q_base = d_query;
+    a.t_base = d_train;
+    a.frame_offset = d_frame_offset;
+    a.pairs = d_pairs;
+    a.nq = nq;
+    a.nt = nt;
+    a.tiles = plan.tiles;
+    a.splits = plan.splits;
+    a.t_per_split = plan.t_per_split;
+    a.max_rows = max_rows;
+    a.swap_roles = swap_roles ? 1 : 0;
+    a.keys = d_keys;
+    const int64_t n_ctas = static_cast<int64_t>(plan.tiles) * plan.splits * n_pairs;
+    if (n_ctas <= 0) return SLAMGPU_OK;
+    SG_CHECK(n_ctas < (int64_t(1) << 31), "brute-force grid too large; split the pair list");
+    const dim3 grid(static_cast<unsigned>(n_ctas));
+    if (plan.r == 2) {
+        bf_scan_kernel<2><<<grid, kThreads, 0, ctx->stream>>>(a);
+    } else {
+        bf_scan_kernel<1><<<grid, kThreads, 0, ctx->stream>>>(a);
+    }
+    ctx->launches++;
+    SG_CUDA(cudaGetLastError());
+    return SLAMGPU_OK;
+}
+
+int bf_launch_finish_raw(slamgpu_ctx* ctx, const BfPlan& plan, const uint2* d_keys, int nq, int nt, int max_rows,
+                         int32_t* d_idx, int32_t* d_dist)
+{
+    (void)nt;
+    if (nq <= 0) return SLAMGPU_OK;
+    bf_finish_raw_kernel<<<(nq + 255) / 256, 256, 0, ctx->stream>>>(d_keys, plan.splits, max_rows, nq, d_idx, d_dist);
+    ctx->launches++;
+    SG_CUDA(cudaGetLastError());
+    return SLAMGPU_OK;
+}
+
+int bf_launch_finish_filter(slamgpu_ctx* ctx, const BfPlan& plan, const uint2* d_keys, int nq, int nt,
+                            const int32_t* d_frame_offset, const int32_t* d_pairs, int n_pairs, int max_rows,
+                            float max_dist, float ratio, int32_t* d_out_train, int32_t* d_out_count)
+{
+    if (n_pairs <= 0 || max_rows <= 0) return SLAMGPU_OK;
+    SG_CUDA(cudaMemsetAsync(d_out_count, 0, sizeof(int32_t) * n_pairs, ctx->stream));
+    FilterArgs a;
+    a.keys = d_keys;
+    a.splits = plan.splits;
+    a.max_rows = max_rows;
+    a.nq = nq;
+    a.nt = nt;
+    a.frame_offset = d_frame_offset;
+    a.pairs = d_pairs;
+    a.max_dist = max_dist;
+    a.ratio = ratio;
+    a.out_train = d_out_train;
+    a.out_count = d_out_count;
+    const int rows = d_pairs ? max_rows : nq;
+    for (int p0 = 0; p0 < n_pairs; p0 += 65535) {   // gridDim.y limit
+        const int np = min(65535, n_pairs - p0);
+        FilterArgs b = a;
+        b.keys = a.keys + static_cast<size_t>(p0) * plan.splits * max_rows;
+        b.pairs = d_pairs ? d_pairs + 2 * static_cast<size_t>(p0) : nullptr;
+        b.out_train = d_out_train + static_cast<size_t>(p0) * max_rows;
+        b.out_count = d_out_count + p0;
+        bf_finish_filter_kernel<<<dim3((rows + 255) / 256, np), 256, 0, ctx->stream>>>(b);
+        ctx->launches++;
+    }
+    SG_CUDA(cudaGetLastError());
+    return SLAMGPU_OK;
+}
+
+int bf_launch_mutual(slamgpu_ctx* ctx, const BfPlan& row_plan, const uint2* d_row_keys, int row_stride,
+                     const BfPlan& col_plan, const uint2* d_col_keys, int col_stride, int nq, int nt,
+                     float strict_max_dist, int32_t* d_idx, int32_t* d_dist)
+{
+    (void)nt;
+    if (nq <= 0) return SLAMGPU_OK;
+    bf_mutual_kernel<<<(nq + 255) / 256, 256, 0, ctx->stream>>>(d_row_keys, row_plan.splits, row_stride, d_col_keys,
+                                                                 col_plan.splits, col_stride, nq, strict_max_dist,
+                                                                 d_idx, d_dist);
+    ctx->launches++;
+    SG_CUDA(cudaGetLastError());
+    return SLAMGPU_OK;
+}
+
+int bf_launch_scan_counts(slamgpu_ctx* ctx, const int32_t* d_count, int n, int32_t* d_offset)
+{
+    bf_scan_counts_kernel<<<1, 1024, 0, ctx->stream>>>(d_count, n, d_offset);
+    ctx->launches++;
+    SG_CUDA(cudaGetLastError());
+    return SLAMGPU_OK;
+}
+
+int bf_launch_compact(slamgpu_ctx* ctx, const int32_t* d_out_train, const int32_t* d_frame_offset,
+                      const int32_t* d_pairs, int nq_single, int n_pairs, int max_rows, const int32_t* d_offset,
+                      int32_t* d_query_list, int32_t* d_train_list)
+{
+    if (n_pairs <= 0) return SLAMGPU_OK;
+    const int warps_per_cta = 8;
+    bf_compact_kernel<<<(n_pairs + warps_per_cta - 1) / warps_per_cta, warps_per_cta * 32, 0, ctx->stream>>>(
+        d_out_train, d_frame_offset, d_pairs, nq_single, n_pairs, max_rows, d_offset, d_query_list, d_train_list);
+    ctx->launches++;
+    SG_CUDA(cudaGetLastError());
+    return SLAMGPU_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// POPC-pipe microbenchmark: long chains of independent POPCs, nothing else on the critical pipe.
+// ---------------------------------------------------------------------------------------------
+namespace {
+__global__ void __launch_bounds__(256) popc_bench_kernel(uint32_t seed, int iters, uint32_t* sink, long long* cycles)
+{
+    uint32_t x[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) x[i] = seed * (threadIdx.x + 1) + i * 0x9E3779B9u + blockIdx.x;
+    uint32_t acc = 0;
+    const long long c0 = clock64();
+    for (int it = 0; it < iters; ++it) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            x[i] = __popc(x[i]) + seed;   // dependent per chain, 8 independent chains per thread
+        }
+    }
+    const long long c1 = clock64();
+#pragma unroll
+    for (int i = 0; i < 8; ++i) acc ^= x[i];
+    if (acc == 0xDEADBEEFu) sink[0] = acc;
+    if (threadIdx.x == 0 && blockIdx.x == 0) cycles[0] = c1 - c0;
+}
+} // namespace
+
+int popc_microbench(slamgpu_ctx* ctx, double* popc_per_s, int* n_sm, double* sm_mhz_est)
+{
+    SG_TRY(ensure_device_ws(ctx, 4096));
+    uint32_t* sink = static_cast<uint32_t*>(ctx->d_ws.ptr);
+    long long* cyc = reinterpret_cast<long long*>(sink + 16);
+    const int iters = 20000, ctas = ctx->n_sm * 8;
+    cudaEvent_t e0, e1;
+    SG_CUDA(cudaEventCreate(&e0));
+    SG_CUDA(cudaEventCreate(&e1));
+    popc_bench_kernel<<<ctas, 256, 0, ctx->stream>>>(12345u, 2000, sink, cyc);   // warm-up
+    SG_CUDA(cudaEventRecord(e0, ctx->stream));
+    popc_bench_kernel<<<ctas, 256, 0, ctx->stream>>>(12345u, iters, sink, cyc);
+    SG_CUDA(cudaEventRecord(e1, ctx->stream));
+    ctx->launches += 2;
+    SG_CUDA(cudaEventSynchronize(e1));
+    float ms = 0.f;
+    SG_CUDA(cudaEventElapsedTime(&ms, e0, e1));
+    long long h_cyc = 0;
+    SG_CUDA(cudaMemcpy(&h_cyc, cyc, sizeof(h_cyc), cudaMemcpyDeviceToHost));
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    const double ops = static_cast<double>(ctas) * 256.0 * 8.0 * iters;
+    if (popc_per_s) *popc_per_s = ops / (ms * 1e-3);
+    if (n_sm) *n_sm = ctx->n_sm;
+    // cycles measured by CTA 0 cover (about) the whole launch: SM clock estimate in MHz
+    if (sm_mhz_est) *sm_mhz_est = static_cast<double>(h_cyc) / (ms * 1e-3) / 1e6;
+    return SLAMGPU_OK;
+}
+
+} // namespace slamgpu

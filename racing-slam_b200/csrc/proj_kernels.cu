@@ -1,0 +1,289 @@
+// proj_kernels.cu -- projection-guided map-point search for sm_100a.
+//
+// Replaces match_via_reproject (src/MapMatcher.cpp:45-98) and its drivers (:107-127,165-175):
+//   K4  proj_match_kernel   one thread per visited map point: Camera::project (src/Camera.cpp:25-32),
+//                           is_in_image (:34-37), viewing-angle and distance gates
+//                           (src/MapMatcher.cpp:62-73), KDTree2D::radius_search in the reference's
+//                           visit order (src/KDTree.cpp:52-82), candidates x observations Hamming
+//                           (src/MapMatcher.cpp:80-93), then a 64-bit atomicMin of
+//                           (distance << 32 | visit rank) on the chosen keypoint (:95-97)
+//   K5  proj_emit_kernel    per keypoint: decode the winning proposal (accepted_matches, :34-43)
+//   N2  point_stats_kernel  avg_viewing_normal / observed_distance_range (src/MapPoint.cpp:24-45)
+//
+// Float parity: every float operation is an explicit round-to-nearest intrinsic in the oracle's
+// order, so nvcc can never contract a multiply-add into an FMA (the reference builds without
+// FMA: CMakeLists.txt:1-7).  Roofline: HBM/L2 bytes, in practice latency.
+#include "slamgpu_internal.cuh"
+
+namespace slamgpu {
+
+namespace {
+
+constexpr int kProjThreads = 128;
+constexpr int kStackDepth = 40;   // KD depth <= log2(nkp) + 1; far-children pending <= depth
+
+__device__ __forceinline__ float sum3(float a0, float a1, float a2) { return __fadd_rn(a0, __fadd_rn(a1, a2)); }
+
+// Eigen normalized(): z = squaredNorm(); z > 0 ? v / sqrt(z) : v
+__device__ __forceinline__ void normalized3(const float v[3], float out[3])
+{
+    const float z = sum3(__fmul_rn(v[0], v[0]), __fmul_rn(v[1], v[1]), __fmul_rn(v[2], v[2]));
+    if (z > 0.0f) {
+        const float n = __fsqrt_rn(z);
+        out[0] = __fdiv_rn(v[0], n);
+        out[1] = __fdiv_rn(v[1], n);
+        out[2] = __fdiv_rn(v[2], n);
+    } else {
+        out[0] = v[0]; out[1] = v[1]; out[2] = v[2];
+    }
+}
+__device__ __forceinline__ float norm3(const float v[3])
+{
+    return __fsqrt_rn(sum3(__fmul_rn(v[0], v[0]), __fmul_rn(v[1], v[1]), __fmul_rn(v[2], v[2])));
+}
+
+__device__ __forceinline__ int hamming256(const uint4& a0, const uint4& a1, const uint4& b0, const uint4& b1)
+{
+    return __popc(a0.x ^ b0.x) + __popc(a0.y ^ b0.y) + __popc(a0.z ^ b0.z) + __popc(a0.w ^ b0.w) +
+           __popc(a1.x ^ b1.x) + __popc(a1.y ^ b1.y) + __popc(a1.z ^ b1.z) + __popc(a1.w ^ b1.w);
+}
+
+struct ProjKernelArgs {
+    ProjCommonArgs c;
+    ProjFrameArgs inline_frame;       // used when frames == nullptr (single-frame call: no upload)
+    const ProjFrameArgs* frames;      // device array for the batched form
+};
+
+__global__ void __launch_bounds__(kProjThreads) proj_match_kernel(const ProjKernelArgs a)
+{
+    const ProjFrameArgs& f = a.frames ? a.frames[blockIdx.y] : a.inline_frame;
+    const ProjCommonArgs& c = a.c;
+    const int v = blockIdx.x * blockDim.x + threadIdx.x;
+    if (v >= c.n_visit) return;
+    // debug rows are per (frame, visit)
+    const size_t dbg_row = static_cast<size_t>(blockIdx.y) * c.n_visit + v;
+    if (c.dbg_uv) {
+        c.dbg_uv[2 * dbg_row] = __int_as_float(0x7FC00000);
+        c.dbg_uv[2 * dbg_row + 1] = __int_as_float(0x7FC00000);
+    }
+    if (c.dbg_kp) c.dbg_kp[dbg_row] = -1;
+    if (c.dbg_d) c.dbg_d[dbg_row] = -1;
+
+    const int pi = c.order ? c.order[v] : v;
+    if (pi < 0) return;                               // match_for_fuse nullptr, src/MapMatcher.cpp:119-121
+    if (f.skip && f.skip[pi]) return;                 // :53 is_matched(point) / :169 !is_observed_by
+
+    const float X[3] = {c.pos[3 * pi], c.pos[3 * pi + 1], c.pos[3 * pi + 2]};
+
+    // P1  Camera::project: M[:, :3] * X summed a0 + (a1 + a2), then + M[:, 3]; true division
+    float h[3];
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+        h[i] = sum3(__fmul_rn(f.M[4 * i], X[0]), __fmul_rn(f.M[4 * i + 1], X[1]), __fmul_rn(f.M[4 * i + 2], X[2]));
+        h[i] = __fadd_rn(h[i], f.M[4 * i + 3]);
+    }
+    float u, w;
+    if (h[2] < 0.0f) {
+        u = -1.0f; w = -1.0f;                          // src/Camera.cpp:28-30
+    } else {
+        u = __fdiv_rn(h[0], h[2]);
+        w = __fdiv_rn(h[1], h[2]);
+    }
+    if (c.dbg_uv) {
+        c.dbg_uv[2 * dbg_row] = u;
+        c.dbg_uv[2 * dbg_row + 1] = w;
+    }
+    // P2  is_in_image (NaN fails every comparison, as on the host)
+    if (!(u >= 0.0f && u < c.width_f && w >= 0.0f && w < c.height_f)) return;
+    if (c.stats) {
+        if (fabsf(u) < 1e-4f || fabsf(__fsub_rn(u, c.width_f)) < 1e-4f || fabsf(w) < 1e-4f ||
+            fabsf(__fsub_rn(w, c.height_f)) < 1e-4f)
+            atomicAdd(&c.stats[0], 1ull);
+    }
+
+    // P3  viewing-angle gate
+    const float ray[3] = {__fsub_rn(X[0], f.C[0]), __fsub_rn(X[1], f.C[1]), __fsub_rn(X[2], f.C[2])};
+    float rn[3];
+    normalized3(ray, rn);
+    const float nx = c.normal[3 * pi], ny = c.normal[3 * pi + 1], nz = c.normal[3 * pi + 2];
+    if (sum3(__fmul_rn(nx, rn[0]), __fmul_rn(ny, rn[1]), __fmul_rn(nz, rn[2])) < c.min_cos) return;
+    // P4  distance gate
+    const float nearest = c.range[2 * pi], furthest = c.range[2 * pi + 1];
+    const float distance = norm3(ray);
+    if (distance < __fdiv_rn(nearest, c.nearer) || distance > __fmul_rn(furthest, c.further)) return;
+
+    if (c.stats) {   // diagnostic only: keypoints within 1e-4 px of the search radius
+        unsigned long long cnt = 0;
+        for (int k = 0; k < f.nkp; ++k) {
+            const float2 p = f.xy[k];
+            const float dx = __fsub_rn(p.x, u), dy = __fsub_rn(p.y, w);
+            const float d = __fsqrt_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)));
+            if (fabsf(__fsub_rn(d, c.radius)) < 1e-4f) cnt++;
+        }
+        if (cnt) atomicAdd(&c.stats[1], cnt);
+    }
+
+    // P5 + P6  KD radius search in reference visit order, Hamming against every observation
+    const int o_begin = c.obs_offset[pi], o_end = c.obs_offset[pi + 1];
+    int best = c.thr;          // accept d < thr  <=>  (double)d < max_descriptor_distance
+    int best_kp = 0;
+
+    int st_s[kStackDepth], st_e[kStackDepth];   // st_e packs (depth << 26 | end)
+    int sp = 0;
+    int s = 0, e = f.nkp, depth = 0;
+    while (true) {
+        while (s < e) {
+            const int mid = (s + e) >> 1;                          // src/KDTree.cpp:25
+            const float2 p = f.kd_xy[mid];
+            const float dx = __fsub_rn(p.x, u);                    // :61
+            const float dy = __fsub_rn(p.y, w);                    // :62
+            const float d2 = __fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy));   // :63
+            if (d2 <= c.r2) {                                      // :65
+                const int kp = f.kd_idx[mid];
+                if (c.replace || !f.matched[kp]) {                 // src/MapMatcher.cpp:81
+                    const uint4 a0 = __ldg(&f.desc[2 * kp]), a1 = __ldg(&f.desc[2 * kp + 1]);
+                    for (int o = o_begin; o < o_end; ++o) {        // :86
+                        const uint4 b0 = __ldg(&c.obs_desc[2 * static_cast<size_t>(o)]);
+                        const uint4 b1 = __ldg(&c.obs_desc[2 * static_cast<size_t>(o) + 1]);
+                        const int d = hamming256(a0, a1, b0, b1);
+                        if (d < best) {                            // :88 strict: first in visit order wins
+                            best = d;
+                            best_kp = kp;
+                        }
+                    }
+                }
+            }
+            const float delta = (depth & 1) ? dy : dx;             // :69-70
+            const bool left_near = delta > 0.0f;                   // :73
+            const int fs = left_near ? mid + 1 : s, fe = left_near ? e : mid;
+            const int ns = left_near ? s : mid + 1, ne = left_near ? mid : e;
+            if (__fmul_rn(delta, delta) <= c.r2 && fs < fe && sp < kStackDepth) {   // :79
+                st_s[sp] = fs;
+                st_e[sp] = ((depth + 1) << 26) | fe;
+                sp++;
+            }
+            s = ns; e = ne; depth++;
+        }
+        if (sp == 0) break;
+        sp--;
+        s = st_s[sp];
+        e = st_e[sp] & ((1 << 26) - 1);
+        depth = st_e[sp] >> 26;
+    }
+
+    if (best < c.thr) {
+        // P7  proposals[kp] = min over points of (distance, visit rank): the first point in visit
+        // order attaining the minimum wins, as in the sequential loop (src/MapMatcher.cpp:95-97)
+        const unsigned long long key = (static_cast<unsigned long long>(best) << 32) | static_cast<unsigned>(v);
+        atomicMin(&f.proposals[best_kp], key);
+        if (c.dbg_kp) c.dbg_kp[dbg_row] = best_kp;
+        if (c.dbg_d) c.dbg_d[dbg_row] = best;
+    }
+}
+
+__global__ void proj_emit_kernel(const ProjKernelArgs a)
+{
+    const ProjFrameArgs& f = a.frames ? a.frames[blockIdx.y] : a.inline_frame;
+    const int kp = blockIdx.x * blockDim.x + threadIdx.x;
+    if (kp >= f.nkp) return;
+    const unsigned long long key = f.proposals[kp];
+    int point = -1, dist = -1;
+    if (key != ~0ull) {
+        const int v = static_cast<int>(key & 0xFFFFFFFFull);
+        point = a.c.order ? a.c.order[v] : v;
+        dist = static_cast<int>(key >> 32);
+    }
+    f.out_point[kp] = point;
+    f.out_dist[kp] = dist;
+}
+
+__global__ void proj_init_kernel(const ProjKernelArgs a)
+{
+    const ProjFrameArgs& f = a.frames ? a.frames[blockIdx.y] : a.inline_frame;
+    const int kp = blockIdx.x * blockDim.x + threadIdx.x;
+    if (kp < f.nkp) f.proposals[kp] = ~0ull;
+}
+
+// src/MapPoint.cpp:24-45, one thread per point, observations in the host's iteration order.
+__global__ void point_stats_kernel(const float* pos, int n, const int32_t* obs_offset, const float* obs_center,
+                                   float* normal, float* range)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float X[3] = {pos[3 * i], pos[3 * i + 1], pos[3 * i + 2]};
+    float acc[3] = {0.0f, 0.0f, 0.0f};
+    float nearest = 3.402823466e+38f, furthest = 0.0f;
+    for (int o = obs_offset[i]; o < obs_offset[i + 1]; ++o) {
+        const float* C = obs_center + 3 * static_cast<size_t>(o);
+        const float d[3] = {__fsub_rn(X[0], C[0]), __fsub_rn(X[1], C[1]), __fsub_rn(X[2], C[2])};
+        float v[3], vv[3];
+        normalized3(d, v);
+        normalized3(v, vv);
+        acc[0] = __fadd_rn(acc[0], vv[0]);
+        acc[1] = __fadd_rn(acc[1], vv[1]);
+        acc[2] = __fadd_rn(acc[2], vv[2]);
+        const float dist = norm3(d);
+        nearest = dist < nearest ? dist : nearest;     // std::min(nearest, dist)
+        furthest = furthest < dist ? dist : furthest;  // std::max(furthest, dist)
+    }
+    float nrm[3];
+    normalized3(acc, nrm);
+    normal[3 * i] = nrm[0]; normal[3 * i + 1] = nrm[1]; normal[3 * i + 2] = nrm[2];
+    range[2 * i] = nearest;
+    range[2 * i + 1] = furthest;
+}
+
+__global__ void kd_gather_kernel(const float2* xy, const int32_t* perm, int n, float2* kd_xy)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) kd_xy[i] = xy[perm[i]];
+}
+
+} // namespace
+
+int proj_launch(slamgpu_ctx* ctx, const ProjCommonArgs& common, const ProjFrameArgs* h_frames,
+                const ProjFrameArgs* d_frames, int n_frames, int max_nkp)
+{
+    if (n_frames <= 0) return SLAMGPU_OK;
+    ProjKernelArgs a;
+    a.c = common;
+    a.inline_frame = h_frames[0];
+    a.frames = n_frames == 1 ? nullptr : d_frames;
+    SG_CHECK(n_frames <= 65535, "too many frames in one projection batch");
+    if (max_nkp > 0) {
+        const dim3 gk((max_nkp + 255) / 256, n_frames);
+        proj_init_kernel<<<gk, 256, 0, ctx->stream>>>(a);
+        ctx->launches++;
+        if (common.n_visit > 0) {
+            const dim3 gp((common.n_visit + kProjThreads - 1) / kProjThreads, n_frames);
+            proj_match_kernel<<<gp, kProjThreads, 0, ctx->stream>>>(a);
+            ctx->launches++;
+        }
+        proj_emit_kernel<<<gk, 256, 0, ctx->stream>>>(a);
+        ctx->launches++;
+    }
+    SG_CUDA(cudaGetLastError());
+    return SLAMGPU_OK;
+}
+
+int proj_launch_point_stats(slamgpu_ctx* ctx, const float* d_pos, int n, const int32_t* d_obs_offset,
+                            const float* d_obs_center, float* d_normal, float* d_range)
+{
+    if (n <= 0) return SLAMGPU_OK;
+    point_stats_kernel<<<(n + 127) / 128, 128, 0, ctx->stream>>>(d_pos, n, d_obs_offset, d_obs_center, d_normal,
+                                                                 d_range);
+    ctx->launches++;
+    SG_CUDA(cudaGetLastError());
+    return SLAMGPU_OK;
+}
+
+int proj_launch_kd_gather(slamgpu_ctx* ctx, const float2* d_xy, const int32_t* d_perm, int n, float2* d_kd_xy)
+{
+    if (n <= 0) return SLAMGPU_OK;
+    kd_gather_kernel<<<(n + 255) / 256, 256, 0, ctx->stream>>>(d_xy, d_perm, n, d_kd_xy);
+    ctx->launches++;
+    SG_CUDA(cudaGetLastError());
+    return SLAMGPU_OK;
+}
+
+} // namespace slamgpu

@@ -1,0 +1,240 @@
+// slamgpu.cu -- the C ABI of libslamgpu (include/slamgpu.h): contexts, resident frame / map-point
+// state, pinned staging and the stream-ordered match calls.  The kernels live in bf_kernels.cu
+// and proj_kernels.cu.  There is no CPU path in this library: every entry point that computes
+// launches CUDA kernels on the context's stream, and slamgpu_create() fails without a device.
+#include <algorithm>
+#include <cstring>
+#include <numeric>
+
+#include "slamgpu_internal.cuh"
+
+namespace slamgpu {
+
+static thread_local std::string g_error;
+
+void set_error(const std::string& msg) { g_error = msg; }
+int fail(int code, const std::string& msg)
+{
+    g_error = msg;
+    return code;
+}
+
+static int grow(slamgpu_ctx* ctx, Arena& a, size_t bytes, bool host)
+{
+    if (bytes <= a.cap) return SLAMGPU_OK;
+    // the old block may still be in use by work queued on the stream
+    SG_CUDA(cudaStreamSynchronize(ctx->stream));
+    if (a.ptr) {
+        if (host) cudaFreeHost(a.ptr); else cudaFree(a.ptr);
+        a.ptr = nullptr;
+        a.cap = 0;
+    }
+    size_t cap = std::max<size_t>(bytes + bytes / 4, size_t(1) << 20);
+    cap = (cap + 4095) & ~size_t(4095);
+    void* p = nullptr;
+    const cudaError_t e = host ? cudaMallocHost(&p, cap) : cudaMalloc(&p, cap);
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        return fail(SLAMGPU_ERR_NOMEM, std::string(host ? "pinned" : "device") + " allocation of " +
+                                           std::to_string(cap) + " bytes failed: " + cudaGetErrorString(e));
+    }
+    a.ptr = p;
+    a.cap = cap;
+    return SLAMGPU_OK;
+}
+
+int ensure_device_ws(slamgpu_ctx* ctx, size_t bytes) { return grow(ctx, ctx->d_ws, bytes, false); }
+int ensure_device_io(slamgpu_ctx* ctx, size_t bytes) { return grow(ctx, ctx->d_io, bytes, false); }
+int ensure_host_stage(slamgpu_ctx* ctx, size_t bytes) { return grow(ctx, ctx->h_stage, bytes, true); }
+
+// Host float helpers in the oracle's / Eigen's coefficient order (see proj_kernels.cu).  This
+// translation unit is compiled with -ffp-contract=off for the host, so a*b+c stays two roundings.
+static inline float hsum3(float a0, float a1, float a2)
+{
+    volatile float t = a1 + a2;
+    return a0 + t;
+}
+static inline float pose_at(const float* pose, int r, int c) { return pose[c * 4 + r]; }
+
+// src/Camera.cpp:27, first product: M = K * pose[0:3, 0:4]
+void host_projection_matrix(const float* pose, float fx, float fy, float cx, float cy, float* M)
+{
+    const float K[3][3] = {{fx, 0.0f, cx}, {0.0f, fy, cy}, {0.0f, 0.0f, 1.0f}};
+    for (int i = 0; i < 3; ++i)
+        for (int j = 0; j < 4; ++j) {
+            volatile float p0 = K[i][0] * pose_at(pose, 0, j);
+            volatile float p1 = K[i][1] * pose_at(pose, 1, j);
+            volatile float p2 = K[i][2] * pose_at(pose, 2, j);
+            M[i * 4 + j] = hsum3(p0, p1, p2);
+        }
+}
+
+// src/Frame.cpp:39-42: C = -R^T * t
+void host_camera_center(const float* pose, float* C)
+{
+    for (int i = 0; i < 3; ++i) {
+        volatile float p0 = -pose_at(pose, 0, i) * pose_at(pose, 0, 3);
+        volatile float p1 = -pose_at(pose, 1, i) * pose_at(pose, 1, 3);
+        volatile float p2 = -pose_at(pose, 2, i) * pose_at(pose, 2, 3);
+        C[i] = hsum3(p0, p1, p2);
+    }
+}
+
+// KDTree2D::build (src/KDTree.cpp:8-43) as a permutation: the node of range [s, e) is
+// perm[(s+e)/2] after std::nth_element on axis depth%2.  Ties between equal coordinates are
+// decided by libstdc++'s nth_element, so the same call, comparator and ranges are used; the
+// recursion is unrolled onto an explicit stack (left range first, like the reference).
+static void kd_build_perm(const float* xy, int n, std::vector<size_t>& idx)
+{
+    idx.resize(static_cast<size_t>(n));
+    std::iota(idx.begin(), idx.end(), size_t(0));
+    struct Range { int s, e, depth; };
+    std::vector<Range> todo;
+    todo.push_back({0, n, 0});
+    while (!todo.empty()) {
+        const Range r = todo.back();
+        todo.pop_back();
+        if (r.s >= r.e) continue;
+        const int axis = r.depth % 2;
+        const int mid = (r.s + r.e) / 2;
+        std::nth_element(idx.begin() + r.s, idx.begin() + mid, idx.begin() + r.e,
+                         [xy, axis](size_t a, size_t b) { return xy[2 * a + axis] < xy[2 * b + axis]; });
+        // sub-ranges are disjoint, so the order in which they are processed cannot change the result
+        todo.push_back({mid + 1, r.e, r.depth + 1});
+        todo.push_back({r.s, mid, r.depth + 1});
+    }
+}
+
+static bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
+
+#define SG_CTX(ctx)                                                       \
+    do {                                                                  \
+        SG_CHECK((ctx) != nullptr, "null context");                       \
+        SG_CUDA(cudaSetDevice((ctx)->device));                            \
+    } while (0)
+
+} // namespace slamgpu
+
+using namespace slamgpu;
+
+// =============================================================================================
+// context
+// =============================================================================================
+extern "C" {
+
+int slamgpu_abi_version(void) { return SLAMGPU_ABI_VERSION; }
+const char* slamgpu_last_error(void) { return g_error.c_str(); }
+
+int slamgpu_device_count(int* count)
+{
+    SG_CHECK(count != nullptr, "null count");
+    int n = 0;
+    const cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        *count = 0;
+        return fail(SLAMGPU_ERR_CUDA, std::string("cudaGetDeviceCount: ") + cudaGetErrorString(e));
+    }
+    *count = n;
+    return SLAMGPU_OK;
+}
+
+int slamgpu_create(int device, slamgpu_ctx** out)
+{
+    SG_CHECK(out != nullptr, "null out pointer");
+    *out = nullptr;
+    int n = 0;
+    SG_TRY(slamgpu_device_count(&n));
+    if (n <= 0) return fail(SLAMGPU_ERR_CUDA, "no CUDA device: libslamgpu has no CPU fallback");
+    SG_CHECK(device >= 0 && device < n, "device index out of range");
+    SG_CUDA(cudaSetDevice(device));
+    cudaDeviceProp prop;
+    SG_CUDA(cudaGetDeviceProperties(&prop, device));
+    if (prop.major != 10) {
+        return fail(SLAMGPU_ERR_CUDA, std::string("libslamgpu is built for sm_100a only; device is sm_") +
+                                          std::to_string(prop.major) + std::to_string(prop.minor));
+    }
+    slamgpu_ctx* ctx = new slamgpu_ctx();
+    ctx->device = device;
+    ctx->n_sm = prop.multiProcessorCount;
+    const cudaError_t e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking);
+    if (e != cudaSuccess) {
+        delete ctx;
+        return fail(SLAMGPU_ERR_CUDA, std::string("cudaStreamCreate: ") + cudaGetErrorString(e));
+    }
+    *out = ctx;
+    return SLAMGPU_OK;
+}
+
+static void free_frame(FrameDev& f)
+{
+    if (f.blob) cudaFree(f.blob);
+    f = FrameDev();
+}
+static void free_points(PointSetDev& p)
+{
+    if (p.blob) cudaFree(p.blob);
+    p = PointSetDev();
+}
+
+int slamgpu_destroy(slamgpu_ctx* ctx)
+{
+    if (ctx == nullptr) return SLAMGPU_OK;
+    cudaSetDevice(ctx->device);
+    cudaStreamSynchronize(ctx->stream);
+    for (auto& kv : ctx->frames) free_frame(kv.second);
+    for (auto& kv : ctx->point_sets) free_points(kv.second);
+    if (ctx->d_ws.ptr) cudaFree(ctx->d_ws.ptr);
+    if (ctx->d_io.ptr) cudaFree(ctx->d_io.ptr);
+    if (ctx->h_stage.ptr) cudaFreeHost(ctx->h_stage.ptr);
+    cudaStreamDestroy(ctx->stream);
+    delete ctx;
+    return SLAMGPU_OK;
+}
+
+int slamgpu_sync(slamgpu_ctx* ctx)
+{
+    SG_CTX(ctx);
+    SG_CUDA(cudaStreamSynchronize(ctx->stream));
+    return SLAMGPU_OK;
+}
+
+void* slamgpu_stream(slamgpu_ctx* ctx) { return ctx ? static_cast<void*>(ctx->stream) : nullptr; }
+int64_t slamgpu_launch_count(slamgpu_ctx* ctx) { return ctx ? ctx->launches : 0; }
+
+int slamgpu_host_alloc(void** ptr, size_t bytes)
+{
+    SG_CHECK(ptr != nullptr, "null ptr");
+    *ptr = nullptr;
+    if (bytes == 0) return SLAMGPU_OK;
+    const cudaError_t e = cudaMallocHost(ptr, bytes);
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        return fail(SLAMGPU_ERR_NOMEM, std::string("cudaMallocHost: ") + cudaGetErrorString(e));
+    }
+    return SLAMGPU_OK;
+}
+
+int slamgpu_host_free(void* ptr)
+{
+    if (ptr) SG_CUDA(cudaFreeHost(ptr));
+    return SLAMGPU_OK;
+}
+
+int slamgpu_kd_build_host(const float* xy, int n, uint32_t* out_perm)
+{
+    SG_CHECK(n >= 0, "negative size");
+    SG_CHECK(n == 0 || (xy != nullptr && out_perm != nullptr), "null pointer");
+    std::vector<size_t> idx;
+    kd_build_perm(xy, n, idx);
+    for (int i = 0; i < n; ++i) out_perm[i] = static_cast<uint32_t>(idx[i]);
+    return SLAMGPU_OK;
+}
+
+int slamgpu_bench_popc(slamgpu_ctx* ctx, double* popc_per_s, int* n_sm, double* sm_mhz_est)
+{
+    SG_CTX(ctx);
+    return popc_microbench(ctx, popc_per_s, n_sm, sm_mhz_est);
+}
+
+} // extern "C"

@@ -1,0 +1,187 @@
+// Internal declarations shared by the libslamgpu translation units (not installed).
+#pragma once
+
+#include <cuda_runtime.h>
+
+#include <cstdint>
+#include <cstdio>
+#include <map>
+#include <string>
+#include <vector>
+
+#include "slamgpu.h"
+
+namespace slamgpu {
+
+void set_error(const std::string& msg);
+int fail(int code, const std::string& msg);
+
+#define SG_CUDA(expr)                                                                                   \
+    do {                                                                                                \
+        cudaError_t _e = (expr);                                                                        \
+        if (_e != cudaSuccess) {                                                                        \
+            return ::slamgpu::fail(SLAMGPU_ERR_CUDA, std::string(#expr) + ": " + cudaGetErrorString(_e)); \
+        }                                                                                               \
+    } while (0)
+
+#define SG_CHECK(cond, msg)                                                        \
+    do {                                                                           \
+        if (!(cond)) return ::slamgpu::fail(SLAMGPU_ERR_INVALID, std::string(msg)); \
+    } while (0)
+
+#define SG_TRY(expr)              \
+    do {                          \
+        int _rc = (expr);         \
+        if (_rc != SLAMGPU_OK) return _rc; \
+    } while (0)
+
+// ---------------------------------------------------------------------------------------------
+// Packed (distance, index) key: a plain unsigned min gives the reference's rule "lowest distance,
+// then lowest train index" (SURVEY 8a B3).  Distance <= 256 needs 9 bits -> 22 index bits + 1 spare.
+// ---------------------------------------------------------------------------------------------
+constexpr int kIdxBits = 22;
+constexpr uint32_t kIdxMask = (1u << kIdxBits) - 1u;
+constexpr uint32_t kKeyNone = 0xFFFFFFFFu;
+
+// Device-resident frame (what match_via_reproject reads from `const Frame&`).
+struct FrameDev {
+    int nkp = 0;
+    void* blob = nullptr;         // one allocation; the pointers below are carved out of it
+    float2* kd_xy = nullptr;      // [nkp] keypoint coordinates in KD position order
+    int32_t* kd_idx = nullptr;    // [nkp] keypoint index at KD position m (= the permutation)
+    uint4* desc = nullptr;        // [nkp*2] descriptors in keypoint order
+    uint8_t* matched = nullptr;   // [nkp]
+    float2* xy = nullptr;         // [nkp] keypoint order (diagnostics)
+    unsigned long long* proposals = nullptr;  // [nkp] packed (dist << 32 | visit rank)
+    std::vector<uint32_t> perm_host;
+};
+
+// Device-resident map-point set (what match_via_reproject reads from `MapPoint&`).
+struct PointSetDev {
+    int n = 0;
+    void* blob = nullptr;         // one allocation; the pointers below are carved out of it
+    int64_t n_obs = 0;
+    float* pos = nullptr;         // [n*3]
+    float* normal = nullptr;      // [n*3]
+    float* range = nullptr;       // [n*2]
+    int32_t* obs_offset = nullptr;// [n+1]
+    uint4* obs_desc = nullptr;    // [n_obs*2]
+};
+
+struct Arena {
+    void* ptr = nullptr;
+    size_t cap = 0;
+};
+
+} // namespace slamgpu
+
+struct slamgpu_ctx {
+    int device = 0;
+    int n_sm = 0;
+    cudaStream_t stream = nullptr;
+    slamgpu::Arena d_ws;      // device scratch of the kernels (partial top-2 keys, frame argument tables)
+    slamgpu::Arena d_io;      // device copies of the host-buffer API's inputs and outputs
+    slamgpu::Arena h_stage;   // pinned staging
+    int64_t launches = 0;
+    std::map<int, slamgpu::FrameDev> frames;
+    std::map<int, slamgpu::PointSetDev> point_sets;
+};
+
+namespace slamgpu {
+
+int ensure_device_ws(slamgpu_ctx* ctx, size_t bytes);
+int ensure_device_io(slamgpu_ctx* ctx, size_t bytes);
+int ensure_host_stage(slamgpu_ctx* ctx, size_t bytes);
+
+// carve 256-byte aligned pieces out of an arena
+struct Carver {
+    uint8_t* base;
+    size_t off = 0;
+    explicit Carver(void* p) : base(static_cast<uint8_t*>(p)) {}
+    template <class T>
+    T* take(size_t count)
+    {
+        T* r = reinterpret_cast<T*>(base + off);
+        off += (count * sizeof(T) + 255) & ~size_t(255);
+        return r;
+    }
+    static size_t padded(size_t bytes) { return (bytes + 255) & ~size_t(255); }
+};
+
+// ---- brute force (bf_kernels.cu) ------------------------------------------------------------
+struct BfPlan {
+    int r = 1;          // queries per thread
+    int tile = 256;     // queries per CTA
+    int tiles = 1;      // query tiles per pair
+    int splits = 1;     // train splits per pair
+    int t_per_split = 0;
+};
+BfPlan bf_make_plan(int n_sm, int nq_max, int nt_max, int64_t n_pairs);
+size_t bf_partial_elems(const BfPlan& p, int64_t n_pairs, int max_rows);
+
+// Scan: partial top-2 keys[(pair*splits + split)*max_rows + q] for every query row.
+int bf_launch_scan(slamgpu_ctx* ctx, const BfPlan& plan, const uint8_t* d_query, int nq, const uint8_t* d_train,
+                   int nt, const int32_t* d_frame_offset, const int32_t* d_pairs, int n_pairs, int max_rows,
+                   bool swap_roles, uint2* d_keys);
+// Finish, raw: merged top-2 -> idx/dist [nq x 2].
+int bf_launch_finish_raw(slamgpu_ctx* ctx, const BfPlan& plan, const uint2* d_keys, int nq, int nt, int max_rows,
+                         int32_t* d_idx, int32_t* d_dist);
+// Finish, filtered (match_descriptors): out_train[pair][q] / count[pair].
+int bf_launch_finish_filter(slamgpu_ctx* ctx, const BfPlan& plan, const uint2* d_keys, int nq, int nt,
+                            const int32_t* d_frame_offset, const int32_t* d_pairs, int n_pairs, int max_rows,
+                            float max_dist, float ratio, int32_t* d_out_train, int32_t* d_out_count);
+// Cross-check mutuality from row partials and column partials.
+int bf_launch_mutual(slamgpu_ctx* ctx, const BfPlan& row_plan, const uint2* d_row_keys, int row_stride,
+                     const BfPlan& col_plan, const uint2* d_col_keys, int col_stride, int nq, int nt,
+                     float strict_max_dist, int32_t* d_idx, int32_t* d_dist);
+// Ordered compaction of out_train[pair][q] into (query, train) lists.
+int bf_launch_scan_counts(slamgpu_ctx* ctx, const int32_t* d_count, int n, int32_t* d_offset /* n+1 */);
+int bf_launch_compact(slamgpu_ctx* ctx, const int32_t* d_out_train, const int32_t* d_frame_offset,
+                      const int32_t* d_pairs, int nq_single, int n_pairs, int max_rows, const int32_t* d_offset,
+                      int32_t* d_query_list, int32_t* d_train_list);
+
+// ---- projection (proj_kernels.cu) -----------------------------------------------------------
+struct ProjFrameArgs {
+    int nkp;
+    const float2* kd_xy;
+    const int32_t* kd_idx;
+    const uint4* desc;
+    const uint8_t* matched;
+    const float2* xy;
+    unsigned long long* proposals;
+    const uint8_t* skip;     // [n_points] for this frame or null
+    int32_t* out_point;      // [nkp]
+    int32_t* out_dist;       // [nkp]
+    float M[12];             // K * pose[0:3,0:4], row-major
+    float C[3];              // camera centre
+};
+struct ProjCommonArgs {
+    int n_points;
+    const float* pos;
+    const float* normal;
+    const float* range;
+    const int32_t* obs_offset;
+    const uint4* obs_desc;
+    const int32_t* order;
+    int n_visit;
+    float width_f, height_f, radius, r2, min_cos, nearer, further;
+    int thr;        // accept Hamming d iff d < thr  (thr = ceil(max_dist))
+    int replace;
+    float* dbg_uv;
+    int32_t* dbg_kp;
+    int32_t* dbg_d;
+    unsigned long long* stats;
+};
+int proj_launch(slamgpu_ctx* ctx, const ProjCommonArgs& common, const ProjFrameArgs* h_frames,
+                const ProjFrameArgs* d_frames, int n_frames, int max_nkp);
+int proj_launch_point_stats(slamgpu_ctx* ctx, const float* d_pos, int n, const int32_t* d_obs_offset,
+                            const float* d_obs_center, float* d_normal, float* d_range);
+int proj_launch_kd_gather(slamgpu_ctx* ctx, const float2* d_xy, const int32_t* d_perm, int n, float2* d_kd_xy);
+
+// host-side float helpers that follow the oracle's / Eigen's operation order
+void host_projection_matrix(const float* pose_colmajor, float fx, float fy, float cx, float cy, float* M12);
+void host_camera_center(const float* pose_colmajor, float* C3);
+
+int popc_microbench(slamgpu_ctx* ctx, double* popc_per_s, int* n_sm, double* sm_mhz_est);
+
+} // namespace slamgpu
