@@ -28,6 +28,12 @@ extern "C" {
 
 #define SLAMGPU_ABI_VERSION 1
 
+#if defined(__GNUC__)
+#define SLAMGPU_API __attribute__((visibility("default")))
+#else
+#define SLAMGPU_API
+#endif
+
 enum {
     SLAMGPU_OK = 0,
     SLAMGPU_ERR_INVALID = 1,  /* bad argument (null pointer, negative size, size over the limits below) */
@@ -41,23 +47,23 @@ enum {
 
 typedef struct slamgpu_ctx slamgpu_ctx;
 
-int slamgpu_abi_version(void);
-const char* slamgpu_last_error(void);
-int slamgpu_device_count(int* count);
+SLAMGPU_API int slamgpu_abi_version(void);
+SLAMGPU_API const char* slamgpu_last_error(void);
+SLAMGPU_API int slamgpu_device_count(int* count);
 
 /* Context: replaces nothing in the reference (which is stateless, src/MapMatcher.h:16-38);
  * it is what the three MapMatcher owners (src/Tracker.cpp:42, src/Mapper.cpp:87,
  * src/LoopDetector.cpp:319) would each hold. */
-int slamgpu_create(int device, slamgpu_ctx** ctx);
-int slamgpu_destroy(slamgpu_ctx* ctx);
-int slamgpu_sync(slamgpu_ctx* ctx);
-void* slamgpu_stream(slamgpu_ctx* ctx); /* the context's cudaStream_t, for interop and timing */
+SLAMGPU_API int slamgpu_create(int device, slamgpu_ctx** ctx);
+SLAMGPU_API int slamgpu_destroy(slamgpu_ctx* ctx);
+SLAMGPU_API int slamgpu_sync(slamgpu_ctx* ctx);
+SLAMGPU_API void* slamgpu_stream(slamgpu_ctx* ctx); /* the context's cudaStream_t, for interop and timing */
 /* Kernels launched on this context since creation (bench.py's gpu_launches). */
-int64_t slamgpu_launch_count(slamgpu_ctx* ctx);
+SLAMGPU_API int64_t slamgpu_launch_count(slamgpu_ctx* ctx);
 
 /* Page-locked host memory for callers that want zero-staging uploads (optional). */
-int slamgpu_host_alloc(void** ptr, size_t bytes);
-int slamgpu_host_free(void* ptr);
+SLAMGPU_API int slamgpu_host_alloc(void** ptr, size_t bytes);
+SLAMGPU_API int slamgpu_host_free(void* ptr);
 
 /* ------------------------------------------------------------------------------------------
  * Brute force
@@ -66,13 +72,13 @@ int slamgpu_host_free(void* ptr);
 /* cv::BFMatcher(NORM_HAMMING).knnMatch(query, train, knn, k=2)  -- src/MapMatcher.cpp:145-148.
  * out_idx / out_dist are nq x 2: the first two of a stable sort by (distance, trainIdx).
  * With nt == 1 the second column is -1 (the reference asks for k = 1 then, :145). */
-int slamgpu_knn2(slamgpu_ctx* ctx, const uint8_t* query, int nq, const uint8_t* train, int nt,
+SLAMGPU_API int slamgpu_knn2(slamgpu_ctx* ctx, const uint8_t* query, int nq, const uint8_t* train, int nt,
                  int32_t* out_idx, int32_t* out_dist);
 
 /* cv::BFMatcher::create(NORM_HAMMING, crossCheck=true)->knnMatch(query, train, m, 1)
  * -- src/features/FeatureExtractor.cpp:20-21.  out_idx[q] = t iff t is q's nearest train row and
  * q is t's nearest query row (lowest index wins ties both ways), else -1. */
-int slamgpu_crosscheck(slamgpu_ctx* ctx, const uint8_t* query, int nq, const uint8_t* train, int nt,
+SLAMGPU_API int slamgpu_crosscheck(slamgpu_ctx* ctx, const uint8_t* query, int nq, const uint8_t* train, int nt,
                        int32_t* out_idx, int32_t* out_dist);
 
 /* MapMatcher::match_descriptors  -- src/MapMatcher.cpp:129-163.
@@ -80,23 +86,23 @@ int slamgpu_crosscheck(slamgpu_ctx* ctx, const uint8_t* query, int nq, const uin
  * ascending keypoint order (:135-138).  Keeps a row unless d0 > max_dist (:152) or, when nt >= 2,
  * d0 > ratio * d1 in float (:156).  Emits (queryIdx, trainIdx) in ascending query order; the
  * adapter turns trainIdx into points[trainIdx].  Buffers hold nq entries. */
-int slamgpu_match_descriptors(slamgpu_ctx* ctx, const uint8_t* query, int nq, const uint8_t* train, int nt,
+SLAMGPU_API int slamgpu_match_descriptors(slamgpu_ctx* ctx, const uint8_t* query, int nq, const uint8_t* train, int nt,
                               float max_dist, float ratio, int32_t* out_query, int32_t* out_train,
                               int* out_count);
 
 /* BaseFeatureExtractor::match_features(prev, cur)  -- src/features/FeatureExtractor.cpp:15-30.
  * Cross-check with query = cur, train = prev; keeps distance < max_dist (strict, :25); emits
  * FeatureMatch(train_index, query_index) in ascending query order.  Buffers hold ncur entries. */
-int slamgpu_match_features(slamgpu_ctx* ctx, const uint8_t* prev, int nprev, const uint8_t* cur, int ncur,
+SLAMGPU_API int slamgpu_match_features(slamgpu_ctx* ctx, const uint8_t* prev, int nprev, const uint8_t* cur, int ncur,
                            float max_dist, int32_t* out_train, int32_t* out_query, int* out_count);
 
 /* Device-resident forms of the above (inputs and outputs already in HBM). */
-int slamgpu_knn2_dev(slamgpu_ctx* ctx, const uint8_t* d_query, int nq, const uint8_t* d_train, int nt,
+SLAMGPU_API int slamgpu_knn2_dev(slamgpu_ctx* ctx, const uint8_t* d_query, int nq, const uint8_t* d_train, int nt,
                      int32_t* d_out_idx, int32_t* d_out_dist);
-int slamgpu_crosscheck_dev(slamgpu_ctx* ctx, const uint8_t* d_query, int nq, const uint8_t* d_train, int nt,
+SLAMGPU_API int slamgpu_crosscheck_dev(slamgpu_ctx* ctx, const uint8_t* d_query, int nq, const uint8_t* d_train, int nt,
                            int32_t* d_out_idx, int32_t* d_out_dist);
 /* d_out_train[q] = trainIdx of the surviving match or -1; *d_out_count (device int) = survivors. */
-int slamgpu_match_descriptors_dev(slamgpu_ctx* ctx, const uint8_t* d_query, int nq, const uint8_t* d_train, int nt,
+SLAMGPU_API int slamgpu_match_descriptors_dev(slamgpu_ctx* ctx, const uint8_t* d_query, int nq, const uint8_t* d_train, int nt,
                                   float max_dist, float ratio, int32_t* d_out_train, int32_t* d_out_count);
 
 /* Batched match_descriptors over a key-frame database -- the LoopDetector all-pairs verification
@@ -108,14 +114,14 @@ int slamgpu_match_descriptors_dev(slamgpu_ctx* ctx, const uint8_t* d_query, int 
  *   d_out_train     [n_pairs x max_rows] trainIdx per query row or -1
  *   d_out_count     [n_pairs] surviving matches per pair
  * Pairs are independent: shard them across GPUs by giving each context its own slice. */
-int slamgpu_match_descriptors_batch_dev(slamgpu_ctx* ctx, const uint8_t* d_desc, const int32_t* d_frame_offset,
+SLAMGPU_API int slamgpu_match_descriptors_batch_dev(slamgpu_ctx* ctx, const uint8_t* d_desc, const int32_t* d_frame_offset,
                                         int n_frames, const int32_t* d_pairs, int n_pairs, int max_rows,
                                         float max_dist, float ratio, int32_t* d_out_train, int32_t* d_out_count);
 /* Host-buffer form: uploads desc / offsets / pairs, returns per-pair counts and a compacted
  * (pair-major, ascending query) list of (queryIdx, trainIdx); out_offset is [n_pairs + 1].
  * out_query / out_train hold `capacity` entries; *out_total is the number produced (if it exceeds
  * capacity the call fails with SLAMGPU_ERR_NOMEM and *out_total tells the size needed). */
-int slamgpu_match_descriptors_batch(slamgpu_ctx* ctx, const uint8_t* desc, const int32_t* frame_offset,
+SLAMGPU_API int slamgpu_match_descriptors_batch(slamgpu_ctx* ctx, const uint8_t* desc, const int32_t* frame_offset,
                                     int n_frames, const int32_t* pairs, int n_pairs, float max_dist, float ratio,
                                     int32_t* out_offset, int32_t* out_query, int32_t* out_train, int64_t capacity,
                                     int64_t* out_total);
@@ -143,14 +149,14 @@ typedef struct slamgpu_proj_params {
  *            (src/KDTree.cpp:18-43).  Pass NULL to have the library build it with the same
  *            std::nth_element call; pass your own when the host's libstdc++ must decide ties.
  *   matched  [nkp] bytes, non-zero = keypoint already has a map point; NULL = none matched. */
-int slamgpu_frame_upload(slamgpu_ctx* ctx, int frame_id, int nkp, const float* xy, const uint8_t* desc,
+SLAMGPU_API int slamgpu_frame_upload(slamgpu_ctx* ctx, int frame_id, int nkp, const float* xy, const uint8_t* desc,
                          const uint32_t* kd_perm, const uint8_t* matched);
-int slamgpu_frame_set_matched(slamgpu_ctx* ctx, int frame_id, const uint8_t* matched);
-int slamgpu_frame_release(slamgpu_ctx* ctx, int frame_id);
+SLAMGPU_API int slamgpu_frame_set_matched(slamgpu_ctx* ctx, int frame_id, const uint8_t* matched);
+SLAMGPU_API int slamgpu_frame_release(slamgpu_ctx* ctx, int frame_id);
 /* The permutation the library built / was given (for tests and for hosts that want to reuse it). */
-int slamgpu_frame_get_kd_perm(slamgpu_ctx* ctx, int frame_id, uint32_t* out_perm);
+SLAMGPU_API int slamgpu_frame_get_kd_perm(slamgpu_ctx* ctx, int frame_id, uint32_t* out_perm);
 /* Build the permutation on the host exactly as KDTree2D::build does (src/KDTree.cpp:8-43). */
-int slamgpu_kd_build_host(const float* xy, int n, uint32_t* out_perm);
+SLAMGPU_API int slamgpu_kd_build_host(const float* xy, int n, uint32_t* out_perm);
 
 /* Map-point state kept resident: what match_via_reproject reads from `MapPoint&`:
  * position() (src/MapPoint.h:16), avg_viewing_normal() (src/MapPoint.cpp:24-33),
@@ -158,12 +164,12 @@ int slamgpu_kd_build_host(const float* xy, int n, uint32_t* out_perm);
  * observations() iteration order (src/MapPoint.h:38, src/MapMatcher.cpp:86-87).
  *   normal / range may be NULL when obs_center is given: the library then derives them on the
  *   device from the observers' camera centres (src/Frame.cpp:39-42) in the same order. */
-int slamgpu_points_upload(slamgpu_ctx* ctx, int set_id, int n, const float* pos, const float* normal,
+SLAMGPU_API int slamgpu_points_upload(slamgpu_ctx* ctx, int set_id, int n, const float* pos, const float* normal,
                           const float* range, const int32_t* obs_offset, const uint8_t* obs_desc,
                           const float* obs_center);
-int slamgpu_points_release(slamgpu_ctx* ctx, int set_id);
+SLAMGPU_API int slamgpu_points_release(slamgpu_ctx* ctx, int set_id);
 /* Read back the per-point normal [n x 3] and range [n x 2] held on the device. */
-int slamgpu_points_get_stats(slamgpu_ctx* ctx, int set_id, float* out_normal, float* out_range);
+SLAMGPU_API int slamgpu_points_get_stats(slamgpu_ctx* ctx, int set_id, float* out_normal, float* out_range);
 
 /* MapMatcher::match_map / match_key_frame / match_for_fuse -- src/MapMatcher.cpp:107-127,165-175.
  *   skip     [n] bytes or NULL: non-zero drops the point up front -- frame.is_matched(point)
@@ -173,7 +179,7 @@ int slamgpu_points_get_stats(slamgpu_ctx* ctx, int set_id, float* out_normal, fl
  *            match_for_fuse's nullptr (:119-121)
  *   out_point[kp] = point-set index matched to keypoint kp or -1; out_dist[kp] = Hamming distance.
  *   accepted_matches (:34-43) is the list of kp with out_point[kp] >= 0, ascending. */
-int slamgpu_match_projection(slamgpu_ctx* ctx, int frame_id, int set_id, const float* pose_colmajor16,
+SLAMGPU_API int slamgpu_match_projection(slamgpu_ctx* ctx, int frame_id, int set_id, const float* pose_colmajor16,
                              const slamgpu_proj_params* params, const uint8_t* skip, const int32_t* order,
                              int n_order, int32_t* out_point, int32_t* out_dist);
 
@@ -182,7 +188,7 @@ int slamgpu_match_projection(slamgpu_ctx* ctx, int frame_id, int set_id, const f
  * within 1e-4 px of an image border, stats[1] = (point, keypoint) pairs within 1e-4 px of the
  * search radius -- the candidates the north-star tolerance exempts from bit-exactness.  Any of
  * the four may be NULL. */
-int slamgpu_match_projection_ex(slamgpu_ctx* ctx, int frame_id, int set_id, const float* pose_colmajor16,
+SLAMGPU_API int slamgpu_match_projection_ex(slamgpu_ctx* ctx, int frame_id, int set_id, const float* pose_colmajor16,
                                 const slamgpu_proj_params* params, const uint8_t* skip, const int32_t* order,
                                 int n_order, int32_t* out_point, int32_t* out_dist, float* dbg_uv,
                                 int32_t* dbg_kp, int32_t* dbg_d, int64_t* stats);
@@ -192,7 +198,7 @@ int slamgpu_match_projection_ex(slamgpu_ctx* ctx, int frame_id, int set_id, cons
  * point set / order / params; skip is [n_frames x n] or NULL.  Outputs are concatenated per
  * frame in the order given (sum of the frames' nkp entries).  Key frames are independent:
  * shard them across GPUs by giving each context its own slice. */
-int slamgpu_match_projection_batch(slamgpu_ctx* ctx, const int* frame_ids, int n_frames, int set_id,
+SLAMGPU_API int slamgpu_match_projection_batch(slamgpu_ctx* ctx, const int* frame_ids, int n_frames, int set_id,
                                    const float* poses_colmajor16, const slamgpu_proj_params* params,
                                    const uint8_t* skip, const int32_t* order, int n_order, int32_t* out_point,
                                    int32_t* out_dist);
@@ -202,7 +208,7 @@ int slamgpu_match_projection_batch(slamgpu_ctx* ctx, const int* frame_ids, int n
  * ---------------------------------------------------------------------------------------- */
 /* POPC-pipe microbenchmark ("confirm with a POPC microbenchmark on the box"):
  * returns 32-bit POPC results per second over the whole device and the SM count. */
-int slamgpu_bench_popc(slamgpu_ctx* ctx, double* popc_per_s, int* n_sm, double* sm_mhz_est);
+SLAMGPU_API int slamgpu_bench_popc(slamgpu_ctx* ctx, double* popc_per_s, int* n_sm, double* sm_mhz_est);
 
 #ifdef __cplusplus
 }

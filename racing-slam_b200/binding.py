@@ -1,0 +1,344 @@
+"""ctypes binding of libslamgpu.so (include/slamgpu.h) -- the only way this package computes.
+
+There is NO CPU path here: if the CUDA library is missing or no sm_100 device is present the
+calls raise.  Host arrays are numpy; the *_dev forms take raw device pointers (e.g. torch
+`tensor.data_ptr()`), enqueue on the context's stream and do not synchronise.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libslamgpu.so")
+
+OK, ERR_INVALID, ERR_CUDA, ERR_NOMEM, ERR_NOTFOUND = 0, 1, 2, 3, 4
+MAX_TRAIN = 1 << 22
+
+_u8p, _i32p, _u32p, _f32p = (C.POINTER(C.c_uint8), C.POINTER(C.c_int32), C.POINTER(C.c_uint32), C.POINTER(C.c_float))
+_i64p = C.POINTER(C.c_int64)
+_ctx = C.c_void_p
+
+
+class SlamGpuError(RuntimeError):
+    def __init__(self, code: int, text: str):
+        super().__init__(f"libslamgpu error {code}: {text}")
+        self.code = code
+
+
+class ProjParams(C.Structure):
+    """slamgpu_proj_params: constants of src/MapMatcher.cpp:12-18 and the camera, as runtime values."""
+    _fields_ = [("fx", C.c_float), ("fy", C.c_float), ("cx", C.c_float), ("cy", C.c_float),
+                ("width", C.c_int32), ("height", C.c_int32), ("radius", C.c_float), ("max_dist", C.c_float),
+                ("min_cos", C.c_float), ("nearer", C.c_float), ("further", C.c_float), ("replace", C.c_int32)]
+
+
+# name -> (restype, argtypes); every symbol include/slamgpu.h declares
+SIGNATURES = {
+    "slamgpu_abi_version": (C.c_int, []),
+    "slamgpu_last_error": (C.c_char_p, []),
+    "slamgpu_device_count": (C.c_int, [C.POINTER(C.c_int)]),
+    "slamgpu_create": (C.c_int, [C.c_int, C.POINTER(_ctx)]),
+    "slamgpu_destroy": (C.c_int, [_ctx]),
+    "slamgpu_sync": (C.c_int, [_ctx]),
+    "slamgpu_stream": (C.c_void_p, [_ctx]),
+    "slamgpu_launch_count": (C.c_int64, [_ctx]),
+    "slamgpu_host_alloc": (C.c_int, [C.POINTER(C.c_void_p), C.c_size_t]),
+    "slamgpu_host_free": (C.c_int, [C.c_void_p]),
+    "slamgpu_knn2": (C.c_int, [_ctx, _u8p, C.c_int, _u8p, C.c_int, _i32p, _i32p]),
+    "slamgpu_crosscheck": (C.c_int, [_ctx, _u8p, C.c_int, _u8p, C.c_int, _i32p, _i32p]),
+    "slamgpu_match_descriptors": (C.c_int, [_ctx, _u8p, C.c_int, _u8p, C.c_int, C.c_float, C.c_float, _i32p, _i32p,
+                                            C.POINTER(C.c_int)]),
+    "slamgpu_match_features": (C.c_int, [_ctx, _u8p, C.c_int, _u8p, C.c_int, C.c_float, _i32p, _i32p,
+                                         C.POINTER(C.c_int)]),
+    "slamgpu_knn2_dev": (C.c_int, [_ctx, C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]),
+    "slamgpu_crosscheck_dev": (C.c_int, [_ctx, C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]),
+    "slamgpu_match_descriptors_dev": (C.c_int, [_ctx, C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_float, C.c_float,
+                                                C.c_void_p, C.c_void_p]),
+    "slamgpu_match_descriptors_batch_dev": (C.c_int, [_ctx, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_int,
+                                                      C.c_int, C.c_float, C.c_float, C.c_void_p, C.c_void_p]),
+    "slamgpu_match_descriptors_batch": (C.c_int, [_ctx, _u8p, _i32p, C.c_int, _i32p, C.c_int, C.c_float, C.c_float,
+                                                  _i32p, _i32p, _i32p, C.c_int64, _i64p]),
+    "slamgpu_frame_upload": (C.c_int, [_ctx, C.c_int, C.c_int, _f32p, _u8p, _u32p, _u8p]),
+    "slamgpu_frame_set_matched": (C.c_int, [_ctx, C.c_int, _u8p]),
+    "slamgpu_frame_release": (C.c_int, [_ctx, C.c_int]),
+    "slamgpu_frame_get_kd_perm": (C.c_int, [_ctx, C.c_int, _u32p]),
+    "slamgpu_kd_build_host": (C.c_int, [_f32p, C.c_int, _u32p]),
+    "slamgpu_points_upload": (C.c_int, [_ctx, C.c_int, C.c_int, _f32p, _f32p, _f32p, _i32p, _u8p, _f32p]),
+    "slamgpu_points_release": (C.c_int, [_ctx, C.c_int]),
+    "slamgpu_points_get_stats": (C.c_int, [_ctx, C.c_int, _f32p, _f32p]),
+    "slamgpu_match_projection": (C.c_int, [_ctx, C.c_int, C.c_int, _f32p, C.POINTER(ProjParams), _u8p, _i32p, C.c_int,
+                                           _i32p, _i32p]),
+    "slamgpu_match_projection_ex": (C.c_int, [_ctx, C.c_int, C.c_int, _f32p, C.POINTER(ProjParams), _u8p, _i32p,
+                                              C.c_int, _i32p, _i32p, _f32p, _i32p, _i32p, _i64p]),
+    "slamgpu_match_projection_batch": (C.c_int, [_ctx, C.POINTER(C.c_int), C.c_int, C.c_int, _f32p,
+                                                 C.POINTER(ProjParams), _u8p, _i32p, C.c_int, _i32p, _i32p]),
+    "slamgpu_bench_popc": (C.c_int, [_ctx, C.POINTER(C.c_double), C.POINTER(C.c_int), C.POINTER(C.c_double)]),
+}
+
+_LIB = None
+
+
+def load():
+    """dlopen the in-tree CUDA library and bind every symbol.  Raises if it has not been built."""
+    global _LIB
+    if _LIB is None:
+        if not os.path.exists(LIB_PATH):
+            raise FileNotFoundError(
+                f"{LIB_PATH} is missing: build it with `make -C racing-slam_b200/csrc` "
+                "(or __graft_entry__.build()).  This package has no CPU fallback.")
+        lib = C.CDLL(LIB_PATH)
+        for name, (res, args) in SIGNATURES.items():
+            fn = getattr(lib, name)           # AttributeError = header/library mismatch
+            fn.restype = res
+            fn.argtypes = args
+        _LIB = lib
+    return _LIB
+
+
+def _p(a, ctype):
+    return None if a is None else a.ctypes.data_as(C.POINTER(ctype))
+
+
+def _desc(a):
+    a = np.ascontiguousarray(a, dtype=np.uint8)
+    return a.reshape(-1, 32)
+
+
+def _opt(a, dtype):
+    return None if a is None else np.ascontiguousarray(a, dtype=dtype)
+
+
+def kd_build_host(xy) -> np.ndarray:
+    """KDTree2D::build as a permutation (src/KDTree.cpp:8-43); host-only, needs no device."""
+    xy = np.ascontiguousarray(xy, np.float32).reshape(-1, 2)
+    perm = np.zeros(len(xy), np.uint32)
+    lib = load()
+    rc = lib.slamgpu_kd_build_host(_p(xy, C.c_float), len(xy), _p(perm, C.c_uint32))
+    if rc != OK:
+        raise SlamGpuError(rc, lib.slamgpu_last_error().decode())
+    return perm
+
+
+def device_count() -> int:
+    lib = load()
+    n = C.c_int(0)
+    lib.slamgpu_device_count(C.byref(n))
+    return n.value
+
+
+class Context:
+    """One CUDA device + one stream + pinned staging (slamgpu_ctx)."""
+
+    def __init__(self, device: int = 0):
+        self._lib = load()
+        self._h = _ctx()
+        self._check(self._lib.slamgpu_create(device, C.byref(self._h)))
+        self.device = device
+
+    def _check(self, rc: int):
+        if rc != OK:
+            raise SlamGpuError(rc, self._lib.slamgpu_last_error().decode())
+
+    def close(self):
+        if self._h:
+            self._lib.slamgpu_destroy(self._h)
+            self._h = _ctx()
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ---- plumbing ----
+    def sync(self):
+        self._check(self._lib.slamgpu_sync(self._h))
+
+    @property
+    def stream(self) -> int:
+        return int(self._lib.slamgpu_stream(self._h) or 0)
+
+    @property
+    def launches(self) -> int:
+        return int(self._lib.slamgpu_launch_count(self._h))
+
+    def bench_popc(self):
+        rate, n_sm, mhz = C.c_double(0), C.c_int(0), C.c_double(0)
+        self._check(self._lib.slamgpu_bench_popc(self._h, C.byref(rate), C.byref(n_sm), C.byref(mhz)))
+        return rate.value, n_sm.value, mhz.value
+
+    # ---- brute force, host buffers ----
+    def knn2(self, q, t):
+        q, t = _desc(q), _desc(t)
+        idx = np.full((len(q), 2), -1, np.int32)
+        dist = np.full((len(q), 2), -1, np.int32)
+        self._check(self._lib.slamgpu_knn2(self._h, _p(q, C.c_uint8), len(q), _p(t, C.c_uint8), len(t),
+                                           _p(idx, C.c_int32), _p(dist, C.c_int32)))
+        return idx, dist
+
+    def crosscheck(self, q, t):
+        q, t = _desc(q), _desc(t)
+        idx = np.full(len(q), -1, np.int32)
+        dist = np.full(len(q), -1, np.int32)
+        self._check(self._lib.slamgpu_crosscheck(self._h, _p(q, C.c_uint8), len(q), _p(t, C.c_uint8), len(t),
+                                                 _p(idx, C.c_int32), _p(dist, C.c_int32)))
+        return idx, dist
+
+    def match_descriptors(self, q, t, max_dist=64.0, ratio=0.75):
+        """-> (query_idx, train_idx), ascending query order (src/MapMatcher.cpp:129-163)."""
+        q, t = _desc(q), _desc(t)
+        oq = np.zeros(max(len(q), 1), np.int32)
+        ot = np.zeros(max(len(q), 1), np.int32)
+        n = C.c_int(0)
+        self._check(self._lib.slamgpu_match_descriptors(self._h, _p(q, C.c_uint8), len(q), _p(t, C.c_uint8), len(t),
+                                                        max_dist, ratio, _p(oq, C.c_int32), _p(ot, C.c_int32),
+                                                        C.byref(n)))
+        return oq[:n.value].copy(), ot[:n.value].copy()
+
+    def match_features(self, prev, cur, max_dist=64.0):
+        """-> (train_idx, query_idx) (src/features/FeatureExtractor.cpp:15-30)."""
+        prev, cur = _desc(prev), _desc(cur)
+        ot = np.zeros(max(len(cur), 1), np.int32)
+        oq = np.zeros(max(len(cur), 1), np.int32)
+        n = C.c_int(0)
+        self._check(self._lib.slamgpu_match_features(self._h, _p(prev, C.c_uint8), len(prev), _p(cur, C.c_uint8),
+                                                     len(cur), max_dist, _p(ot, C.c_int32), _p(oq, C.c_int32),
+                                                     C.byref(n)))
+        return ot[:n.value].copy(), oq[:n.value].copy()
+
+    def match_descriptors_batch(self, desc, frame_offset, pairs, max_dist=64.0, ratio=0.75, capacity=None):
+        """-> (offset [n_pairs+1], query_idx, train_idx): per pair (query_frame, train_frame) the
+        compacted match_descriptors list."""
+        desc = _desc(desc)
+        frame_offset = np.ascontiguousarray(frame_offset, np.int32)
+        pairs = np.ascontiguousarray(pairs, np.int32).reshape(-1, 2)
+        n_pairs = len(pairs)
+        if capacity is None:   # every query row can match at most once per pair
+            rows = np.diff(frame_offset)
+            capacity = int(rows[pairs[:, 0]].sum()) if n_pairs else 0
+        off = np.zeros(n_pairs + 1, np.int32)
+        oq = np.zeros(max(capacity, 1), np.int32)
+        ot = np.zeros(max(capacity, 1), np.int32)
+        total = C.c_int64(0)
+        self._check(self._lib.slamgpu_match_descriptors_batch(
+            self._h, _p(desc, C.c_uint8), _p(frame_offset, C.c_int32), len(frame_offset) - 1, _p(pairs, C.c_int32),
+            n_pairs, max_dist, ratio, _p(off, C.c_int32), _p(oq, C.c_int32), _p(ot, C.c_int32), capacity,
+            C.byref(total)))
+        return off, oq[:total.value].copy(), ot[:total.value].copy()
+
+    # ---- brute force, device buffers (raw pointers; stream-ordered, no sync) ----
+    def knn2_dev(self, d_q: int, nq: int, d_t: int, nt: int, d_idx: int, d_dist: int):
+        self._check(self._lib.slamgpu_knn2_dev(self._h, d_q, nq, d_t, nt, d_idx, d_dist))
+
+    def crosscheck_dev(self, d_q: int, nq: int, d_t: int, nt: int, d_idx: int, d_dist: int):
+        self._check(self._lib.slamgpu_crosscheck_dev(self._h, d_q, nq, d_t, nt, d_idx, d_dist))
+
+    def match_descriptors_dev(self, d_q: int, nq: int, d_t: int, nt: int, max_dist: float, ratio: float,
+                              d_out_train: int, d_out_count: int):
+        self._check(self._lib.slamgpu_match_descriptors_dev(self._h, d_q, nq, d_t, nt, max_dist, ratio, d_out_train,
+                                                            d_out_count))
+
+    def match_descriptors_batch_dev(self, d_desc: int, d_frame_offset: int, n_frames: int, d_pairs: int, n_pairs: int,
+                                    max_rows: int, max_dist: float, ratio: float, d_out_train: int, d_out_count: int):
+        self._check(self._lib.slamgpu_match_descriptors_batch_dev(self._h, d_desc, d_frame_offset, n_frames, d_pairs,
+                                                                  n_pairs, max_rows, max_dist, ratio, d_out_train,
+                                                                  d_out_count))
+
+    # ---- projection-guided search ----
+    def frame_upload(self, frame_id: int, xy, desc, kd_perm=None, matched=None):
+        xy = np.ascontiguousarray(xy, np.float32).reshape(-1, 2)
+        desc = _desc(desc)
+        assert len(desc) == len(xy), "one descriptor per keypoint"
+        kd_perm = _opt(kd_perm, np.uint32)
+        matched = _opt(matched, np.uint8)
+        self._check(self._lib.slamgpu_frame_upload(self._h, frame_id, len(xy), _p(xy, C.c_float), _p(desc, C.c_uint8),
+                                                   _p(kd_perm, C.c_uint32), _p(matched, C.c_uint8)))
+
+    def frame_set_matched(self, frame_id: int, matched):
+        matched = _opt(matched, np.uint8)
+        self._check(self._lib.slamgpu_frame_set_matched(self._h, frame_id, _p(matched, C.c_uint8)))
+
+    def frame_release(self, frame_id: int):
+        self._check(self._lib.slamgpu_frame_release(self._h, frame_id))
+
+    def frame_kd_perm(self, frame_id: int, nkp: int) -> np.ndarray:
+        perm = np.zeros(nkp, np.uint32)
+        self._check(self._lib.slamgpu_frame_get_kd_perm(self._h, frame_id, _p(perm, C.c_uint32)))
+        return perm
+
+    def points_upload(self, set_id: int, pos, normal, rng, obs_offset, obs_desc, obs_center=None):
+        pos = np.ascontiguousarray(pos, np.float32).reshape(-1, 3)
+        normal = _opt(normal, np.float32)
+        rng = _opt(rng, np.float32)
+        obs_offset = np.ascontiguousarray(obs_offset, np.int32)
+        obs_desc = _desc(obs_desc)
+        obs_center = _opt(obs_center, np.float32)
+        assert len(obs_offset) == len(pos) + 1
+        self._check(self._lib.slamgpu_points_upload(self._h, set_id, len(pos), _p(pos, C.c_float),
+                                                    _p(normal, C.c_float), _p(rng, C.c_float),
+                                                    _p(obs_offset, C.c_int32), _p(obs_desc, C.c_uint8),
+                                                    _p(obs_center, C.c_float)))
+
+    def points_release(self, set_id: int):
+        self._check(self._lib.slamgpu_points_release(self._h, set_id))
+
+    def points_stats(self, set_id: int, n: int):
+        normal = np.zeros((n, 3), np.float32)
+        rng = np.zeros((n, 2), np.float32)
+        self._check(self._lib.slamgpu_points_get_stats(self._h, set_id, _p(normal, C.c_float), _p(rng, C.c_float)))
+        return normal, rng
+
+    def match_projection(self, frame_id: int, set_id: int, nkp: int, pose, params: ProjParams, skip=None, order=None,
+                         debug: bool = False, n_points: int | None = None):
+        """-> (out_point [nkp], out_dist [nkp]) and, with debug=True, a dict with uv / kp / d per
+        visited point and the two near-boundary counters."""
+        pose = np.ascontiguousarray(pose, np.float32).reshape(16)
+        skip = _opt(skip, np.uint8)
+        order = _opt(order, np.int32)
+        n_order = 0 if order is None else len(order)
+        out_point = np.full(nkp, -1, np.int32)
+        out_dist = np.full(nkp, -1, np.int32)
+        if not debug:
+            self._check(self._lib.slamgpu_match_projection(self._h, frame_id, set_id, _p(pose, C.c_float),
+                                                           C.byref(params), _p(skip, C.c_uint8), _p(order, C.c_int32),
+                                                           n_order, _p(out_point, C.c_int32), _p(out_dist, C.c_int32)))
+            return out_point, out_dist
+        n_visit = n_order if order is not None else int(n_points)
+        uv = np.zeros((n_visit, 2), np.float32)
+        kp = np.zeros(n_visit, np.int32)
+        d = np.zeros(n_visit, np.int32)
+        stats = np.zeros(2, np.int64)
+        self._check(self._lib.slamgpu_match_projection_ex(
+            self._h, frame_id, set_id, _p(pose, C.c_float), C.byref(params), _p(skip, C.c_uint8),
+            _p(order, C.c_int32), n_order, _p(out_point, C.c_int32), _p(out_dist, C.c_int32), _p(uv, C.c_float),
+            _p(kp, C.c_int32), _p(d, C.c_int32), _p(stats, C.c_int64)))
+        return out_point, out_dist, dict(uv=uv, kp=kp, d=d, near_border=int(stats[0]), near_radius=int(stats[1]))
+
+    def match_projection_batch(self, frame_ids, nkps, set_id: int, poses, params: ProjParams, skip=None, order=None):
+        """Frozen-snapshot batch over key frames -> list of (out_point, out_dist) per frame."""
+        frame_ids = [int(f) for f in frame_ids]
+        ids = (C.c_int * len(frame_ids))(*frame_ids)
+        poses = np.ascontiguousarray(poses, np.float32).reshape(len(frame_ids), 16)
+        skip = _opt(skip, np.uint8)
+        order = _opt(order, np.int32)
+        n_order = 0 if order is None else len(order)
+        total = int(sum(nkps))
+        out_point = np.full(max(total, 1), -1, np.int32)
+        out_dist = np.full(max(total, 1), -1, np.int32)
+        self._check(self._lib.slamgpu_match_projection_batch(
+            self._h, ids, len(frame_ids), set_id, _p(poses, C.c_float), C.byref(params), _p(skip, C.c_uint8),
+            _p(order, C.c_int32), n_order, _p(out_point, C.c_int32), _p(out_dist, C.c_int32)))
+        res, o = [], 0
+        for n in nkps:
+            res.append((out_point[o:o + n].copy(), out_dist[o:o + n].copy()))
+            o += n
+        return res

@@ -137,9 +137,229 @@ int slice_for(int n_sm, int max_rows)
     return static_cast<int>(std::min<size_t>(s, 1 << 20));
 }
 
+
+// ---- host-buffer plumbing -------------------------------------------------------------------
+// Stage a host array into the pinned buffer at `h_off` and queue its H2D copy to `d_dst`.
+// Pinned caller memory (slamgpu_host_alloc) skips the staging copy.
+bool is_pinned(const void* p)
+{
+    cudaPointerAttributes attr;
+    if (cudaPointerGetAttributes(&attr, p) != cudaSuccess) {
+        cudaGetLastError();
+        return false;
+    }
+    return attr.type == cudaMemoryTypeHost;
+}
+
+int upload(slamgpu_ctx* ctx, void* d_dst, const void* h_src, size_t bytes, size_t h_off)
+{
+    if (bytes == 0) return SLAMGPU_OK;
+    const void* src = h_src;
+    if (!is_pinned(h_src)) {
+        void* stage = static_cast<uint8_t*>(ctx->h_stage.ptr) + h_off;
+        std::memcpy(stage, h_src, bytes);
+        src = stage;
+    }
+    SG_CUDA(cudaMemcpyAsync(d_dst, src, bytes, cudaMemcpyHostToDevice, ctx->stream));
+    return SLAMGPU_OK;
+}
+
+struct PairIo {
+    uint8_t* d_q = nullptr;
+    uint8_t* d_t = nullptr;
+    int32_t* d_a = nullptr;   // first output array
+    int32_t* d_b = nullptr;   // second output array
+    size_t out_a_bytes = 0, out_b_bytes = 0;
+};
+
+// device + pinned buffers for one (query, train) call with two int32 outputs, inputs uploaded
+int stage_pair(slamgpu_ctx* ctx, const uint8_t* q, int nq, const uint8_t* t, int nt, size_t out_a_elems,
+               size_t out_b_elems, PairIo& io)
+{
+    const size_t qb = Carver::padded(static_cast<size_t>(nq) * 32), tb = Carver::padded(static_cast<size_t>(nt) * 32);
+    io.out_a_bytes = out_a_elems * sizeof(int32_t);
+    io.out_b_bytes = out_b_elems * sizeof(int32_t);
+    const size_t ob = Carver::padded(io.out_a_bytes) + Carver::padded(io.out_b_bytes);
+    SG_TRY(ensure_device_io(ctx, qb + tb + ob + 256));
+    SG_TRY(ensure_host_stage(ctx, std::max(qb + tb, ob) + 256));
+    Carver dio(ctx->d_io.ptr);
+    io.d_q = dio.take<uint8_t>(static_cast<size_t>(nq) * 32);
+    io.d_t = dio.take<uint8_t>(static_cast<size_t>(nt) * 32);
+    io.d_a = dio.take<int32_t>(out_a_elems);
+    io.d_b = dio.take<int32_t>(out_b_elems);
+    SG_TRY(upload(ctx, io.d_q, q, static_cast<size_t>(nq) * 32, 0));
+    SG_TRY(upload(ctx, io.d_t, t, static_cast<size_t>(nt) * 32, qb));
+    return SLAMGPU_OK;
+}
+
+// one D2H copy of both outputs into pinned memory, then wait
+int fetch_pair(slamgpu_ctx* ctx, const PairIo& io, const int32_t** h_a, const int32_t** h_b)
+{
+    const size_t ob = Carver::padded(io.out_a_bytes) + io.out_b_bytes;
+    if (ob) SG_CUDA(cudaMemcpyAsync(ctx->h_stage.ptr, io.d_a, ob, cudaMemcpyDeviceToHost, ctx->stream));
+    SG_CUDA(cudaStreamSynchronize(ctx->stream));
+    *h_a = static_cast<const int32_t*>(ctx->h_stage.ptr);
+    *h_b = reinterpret_cast<const int32_t*>(static_cast<const uint8_t*>(ctx->h_stage.ptr) + Carver::padded(io.out_a_bytes));
+    return SLAMGPU_OK;
+}
+
 } // namespace
 
 extern "C" {
+
+int slamgpu_knn2(slamgpu_ctx* ctx, const uint8_t* query, int nq, const uint8_t* train, int nt, int32_t* out_idx,
+                 int32_t* out_dist)
+{
+    SG_CTX(ctx);
+    SG_TRY(check_sets(query, nq, train, nt));
+    if (nq == 0) return SLAMGPU_OK;
+    SG_CHECK(out_idx && out_dist, "null output");
+    PairIo io;
+    SG_TRY(stage_pair(ctx, query, nq, train, nt, 2 * static_cast<size_t>(nq), 2 * static_cast<size_t>(nq), io));
+    SG_TRY(knn2_core(ctx, io.d_q, nq, io.d_t, nt, io.d_a, io.d_b));
+    const int32_t *ha, *hb;
+    SG_TRY(fetch_pair(ctx, io, &ha, &hb));
+    std::memcpy(out_idx, ha, io.out_a_bytes);
+    std::memcpy(out_dist, hb, io.out_b_bytes);
+    return SLAMGPU_OK;
+}
+
+int slamgpu_crosscheck(slamgpu_ctx* ctx, const uint8_t* query, int nq, const uint8_t* train, int nt,
+                       int32_t* out_idx, int32_t* out_dist)
+{
+    SG_CTX(ctx);
+    SG_TRY(check_sets(query, nq, train, nt));
+    if (nq == 0) return SLAMGPU_OK;
+    SG_CHECK(out_idx && out_dist, "null output");
+    PairIo io;
+    SG_TRY(stage_pair(ctx, query, nq, train, nt, nq, nq, io));
+    SG_TRY(crosscheck_core(ctx, io.d_q, nq, io.d_t, nt, -1.0f, io.d_a, io.d_b));
+    const int32_t *ha, *hb;
+    SG_TRY(fetch_pair(ctx, io, &ha, &hb));
+    std::memcpy(out_idx, ha, io.out_a_bytes);
+    std::memcpy(out_dist, hb, io.out_b_bytes);
+    return SLAMGPU_OK;
+}
+
+int slamgpu_match_descriptors(slamgpu_ctx* ctx, const uint8_t* query, int nq, const uint8_t* train, int nt,
+                              float max_dist, float ratio, int32_t* out_query, int32_t* out_train, int* out_count)
+{
+    SG_CTX(ctx);
+    SG_TRY(check_sets(query, nq, train, nt));
+    SG_CHECK(out_count != nullptr, "null out_count");
+    *out_count = 0;
+    if (nq == 0 || nt == 0) return SLAMGPU_OK;   // src/MapMatcher.cpp:139-141
+    SG_CHECK(out_query && out_train, "null output");
+    PairIo io;
+    SG_TRY(stage_pair(ctx, query, nq, train, nt, nq, 1, io));
+    SG_TRY(match_descriptors_core(ctx, io.d_q, nq, io.d_t, nt, max_dist, ratio, io.d_a, io.d_b));
+    const int32_t *h_train, *h_count;
+    SG_TRY(fetch_pair(ctx, io, &h_train, &h_count));
+    // marshal the per-row result into the reference's list form (ascending queryIdx, :151-161)
+    int n = 0;
+    for (int q = 0; q < nq; ++q) {
+        if (h_train[q] >= 0) {
+            out_query[n] = q;
+            out_train[n] = h_train[q];
+            ++n;
+        }
+    }
+    if (n != h_count[0]) return fail(SLAMGPU_ERR_CUDA, "match_descriptors: device count and row flags disagree");
+    *out_count = n;
+    return SLAMGPU_OK;
+}
+
+int slamgpu_match_features(slamgpu_ctx* ctx, const uint8_t* prev, int nprev, const uint8_t* cur, int ncur,
+                           float max_dist, int32_t* out_train, int32_t* out_query, int* out_count)
+{
+    SG_CTX(ctx);
+    SG_TRY(check_sets(cur, ncur, prev, nprev));
+    SG_CHECK(out_count != nullptr, "null out_count");
+    SG_CHECK(!(max_dist < 0.0f), "negative max_dist");
+    *out_count = 0;
+    if (ncur == 0 || nprev == 0) return SLAMGPU_OK;
+    SG_CHECK(out_query && out_train, "null output");
+    PairIo io;
+    SG_TRY(stage_pair(ctx, cur, ncur, prev, nprev, ncur, ncur, io));
+    SG_TRY(crosscheck_core(ctx, io.d_q, ncur, io.d_t, nprev, max_dist, io.d_a, io.d_b));
+    const int32_t *h_idx, *h_dist;
+    SG_TRY(fetch_pair(ctx, io, &h_idx, &h_dist));
+    int n = 0;
+    for (int q = 0; q < ncur; ++q) {   // FeatureMatch(trainIdx, queryIdx), src/features/FeatureExtractor.cpp:26
+        if (h_idx[q] >= 0) {
+            out_train[n] = h_idx[q];
+            out_query[n] = q;
+            ++n;
+        }
+    }
+    *out_count = n;
+    return SLAMGPU_OK;
+}
+
+int slamgpu_match_descriptors_batch(slamgpu_ctx* ctx, const uint8_t* desc, const int32_t* frame_offset, int n_frames,
+                                    const int32_t* pairs, int n_pairs, float max_dist, float ratio,
+                                    int32_t* out_offset, int32_t* out_query, int32_t* out_train, int64_t capacity,
+                                    int64_t* out_total)
+{
+    SG_CTX(ctx);
+    SG_CHECK(n_frames >= 0 && n_pairs >= 0 && capacity >= 0, "negative size");
+    SG_CHECK(out_total != nullptr, "null out_total");
+    *out_total = 0;
+    if (n_pairs == 0) return SLAMGPU_OK;
+    SG_CHECK(frame_offset && pairs && out_offset, "null pointer");
+    SG_CHECK(capacity == 0 || (out_query && out_train), "null output lists");
+    SG_CHECK(frame_offset[0] == 0, "frame_offset[0] must be 0");
+    int max_rows = 0;
+    for (int f = 0; f < n_frames; ++f) {
+        SG_CHECK(frame_offset[f + 1] >= frame_offset[f], "frame_offset must be non-decreasing");
+        max_rows = std::max(max_rows, frame_offset[f + 1] - frame_offset[f]);
+    }
+    SG_CHECK(max_rows <= SLAMGPU_MAX_TRAIN, "frame larger than SLAMGPU_MAX_TRAIN");
+    for (int p = 0; p < 2 * n_pairs; ++p) SG_CHECK(pairs[p] >= 0 && pairs[p] < n_frames, "pair names an unknown frame");
+    const size_t n_rows = static_cast<size_t>(frame_offset[n_frames]);
+    SG_CHECK(n_rows == 0 || desc != nullptr, "null descriptors");
+
+    const int slice = std::min(n_pairs, slice_for(ctx->n_sm, max_rows));
+    const size_t b_desc = Carver::padded(n_rows * 32), b_off = Carver::padded(sizeof(int32_t) * (n_frames + 1)),
+                 b_pairs = Carver::padded(sizeof(int32_t) * 2 * n_pairs);
+    const size_t b_rows = Carver::padded(sizeof(int32_t) * static_cast<size_t>(slice) * std::max(max_rows, 1)),
+                 b_count = Carver::padded(sizeof(int32_t) * n_pairs),
+                 b_offset = Carver::padded(sizeof(int32_t) * (static_cast<size_t>(n_pairs) + 1)),
+                 b_list = Carver::padded(sizeof(int32_t) * static_cast<size_t>(capacity));
+    SG_TRY(ensure_device_io(ctx, b_desc + b_off + b_pairs + b_rows + b_count + b_offset + 2 * b_list + 256));
+    SG_TRY(ensure_host_stage(ctx, std::max(b_desc + b_off + b_pairs, b_offset + 2 * b_list) + 256));
+    Carver dio(ctx->d_io.ptr);
+    uint8_t* d_desc = dio.take<uint8_t>(n_rows * 32);
+    int32_t* d_off = dio.take<int32_t>(n_frames + 1);
+    int32_t* d_pairs = dio.take<int32_t>(2 * static_cast<size_t>(n_pairs));
+    int32_t* d_rows = dio.take<int32_t>(static_cast<size_t>(slice) * std::max(max_rows, 1));
+    int32_t* d_count = dio.take<int32_t>(n_pairs);
+    int32_t* d_offset = dio.take<int32_t>(static_cast<size_t>(n_pairs) + 1);
+    int32_t* d_ql = dio.take<int32_t>(static_cast<size_t>(capacity));
+    int32_t* d_tl = dio.take<int32_t>(static_cast<size_t>(capacity));
+    SG_TRY(upload(ctx, d_desc, desc, n_rows * 32, 0));
+    SG_TRY(upload(ctx, d_off, frame_offset, sizeof(int32_t) * (n_frames + 1), b_desc));
+    SG_TRY(upload(ctx, d_pairs, pairs, sizeof(int32_t) * 2 * n_pairs, b_desc + b_off));
+    SG_TRY(batch_core(ctx, d_desc, d_off, d_pairs, n_pairs, max_rows, max_dist, ratio, d_rows, d_count, d_offset, d_ql,
+                      d_tl, capacity, slice));
+    // offsets first: they tell how much of the lists to bring back
+    uint8_t* hs = static_cast<uint8_t*>(ctx->h_stage.ptr);
+    SG_CUDA(cudaMemcpyAsync(hs, d_offset, sizeof(int32_t) * (static_cast<size_t>(n_pairs) + 1), cudaMemcpyDeviceToHost,
+                            ctx->stream));
+    SG_CUDA(cudaStreamSynchronize(ctx->stream));
+    std::memcpy(out_offset, hs, sizeof(int32_t) * (static_cast<size_t>(n_pairs) + 1));
+    const int64_t total = out_offset[n_pairs];
+    *out_total = total;
+    if (total > capacity) return fail(SLAMGPU_ERR_NOMEM, "match list capacity too small; *out_total holds the size needed");
+    if (total > 0) {
+        SG_CUDA(cudaMemcpyAsync(hs, d_ql, sizeof(int32_t) * total, cudaMemcpyDeviceToHost, ctx->stream));
+        SG_CUDA(cudaMemcpyAsync(hs + b_list, d_tl, sizeof(int32_t) * total, cudaMemcpyDeviceToHost, ctx->stream));
+        SG_CUDA(cudaStreamSynchronize(ctx->stream));
+        std::memcpy(out_query, hs, sizeof(int32_t) * total);
+        std::memcpy(out_train, hs + b_list, sizeof(int32_t) * total);
+    }
+    return SLAMGPU_OK;
+}
 
 int slamgpu_knn2_dev(slamgpu_ctx* ctx, const uint8_t* d_query, int nq, const uint8_t* d_train, int nt,
                      int32_t* d_out_idx, int32_t* d_out_dist)

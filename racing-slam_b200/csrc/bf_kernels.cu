@@ -288,7 +288,7 @@ __global__ void bf_scan_counts_kernel(const int32_t* count, int n, int32_t* offs
 {
     __shared__ int s_warp[32];
     __shared__ int s_carry;
-    if (threadIdx.x == 0) s_carry = 0;
+    if (threadIdx.x == 0) s_carry = offset[0];   // running total of the slices before this one
     __syncthreads();
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     for (int base = 0; base < n; base += blockDim.x) {
@@ -325,7 +325,7 @@ __global__ void bf_scan_counts_kernel(const int32_t* count, int n, int32_t* offs
 // ordered compaction: one warp per pair walks its rows 32 at a time
 __global__ void bf_compact_kernel(const int32_t* out_train, const int32_t* frame_offset, const int32_t* pairs,
                                   int nq_single, int n_pairs, int max_rows, const int32_t* offset,
-                                  int32_t* query_list, int32_t* train_list)
+                                  int32_t* query_list, int32_t* train_list, long long capacity)
 {
     const int pair = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const int lane = threadIdx.x & 31;
@@ -343,8 +343,10 @@ __global__ void bf_compact_kernel(const int32_t* out_train, const int32_t* frame
         const unsigned ballot = __ballot_sync(0xFFFFFFFFu, t >= 0);
         if (t >= 0) {
             const int p = pos + __popc(ballot & ((1u << lane) - 1u));
-            query_list[p] = q;
-            train_list[p] = t;
+            if (p < capacity) {   // an undersized list is reported by the host from offset[n_pairs]
+                query_list[p] = q;
+                train_list[p] = t;
+            }
         }
         pos += __popc(ballot);
     }
@@ -475,12 +477,13 @@ int bf_launch_scan_counts(slamgpu_ctx* ctx, const int32_t* d_count, int n, int32
 
 int bf_launch_compact(slamgpu_ctx* ctx, const int32_t* d_out_train, const int32_t* d_frame_offset,
                       const int32_t* d_pairs, int nq_single, int n_pairs, int max_rows, const int32_t* d_offset,
-                      int32_t* d_query_list, int32_t* d_train_list)
+                      int32_t* d_query_list, int32_t* d_train_list, int64_t capacity)
 {
     if (n_pairs <= 0) return SLAMGPU_OK;
     const int warps_per_cta = 8;
     bf_compact_kernel<<<(n_pairs + warps_per_cta - 1) / warps_per_cta, warps_per_cta * 32, 0, ctx->stream>>>(
-        d_out_train, d_frame_offset, d_pairs, nq_single, n_pairs, max_rows, d_offset, d_query_list, d_train_list);
+        d_out_train, d_frame_offset, d_pairs, nq_single, n_pairs, max_rows, d_offset, d_query_list, d_train_list,
+        static_cast<long long>(capacity));
     ctx->launches++;
     SG_CUDA(cudaGetLastError());
     return SLAMGPU_OK;

@@ -1,0 +1,491 @@
+// proj_api.cu -- projection-guided entry points of the C ABI (include/slamgpu.h):
+// resident frame / map-point state and the stream-ordered match_projection calls.  Kernels are
+// in proj_kernels.cu.  Uploads go through the context's pinned staging buffer in one H2D copy
+// per call; results come back in one D2H copy.
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+
+#include "slamgpu_internal.cuh"
+
+using namespace slamgpu;
+
+namespace {
+
+#define SG_CTX(ctx)                                 \
+    do {                                            \
+        SG_CHECK((ctx) != nullptr, "null context"); \
+        SG_CUDA(cudaSetDevice((ctx)->device));      \
+    } while (0)
+
+void free_frame(FrameDev& f)
+{
+    if (f.blob) cudaFree(f.blob);
+    f = FrameDev();
+}
+void free_points(PointSetDev& p)
+{
+    if (p.blob) cudaFree(p.blob);
+    p = PointSetDev();
+}
+
+int check_params(const slamgpu_proj_params* p)
+{
+    SG_CHECK(p != nullptr, "null projection params");
+    SG_CHECK(p->width >= 0 && p->height >= 0, "negative image size");
+    SG_CHECK(p->radius >= 0.0f, "negative search radius");
+    SG_CHECK(p->max_dist == p->max_dist, "max_dist is NaN");
+    return SLAMGPU_OK;
+}
+
+// accept Hamming d iff (double)d < max_dist  (src/MapMatcher.cpp:78,88)  <=>  d < ceil(max_dist)
+int dist_threshold(float max_dist)
+{
+    const double c = std::ceil(static_cast<double>(max_dist));
+    if (c <= 0.0) return 0;
+    if (c > 257.0) return 257;
+    return static_cast<int>(c);
+}
+
+void fill_common(ProjCommonArgs& c, const PointSetDev& ps, const slamgpu_proj_params& p, const int32_t* d_order,
+                 int n_visit)
+{
+    c.n_points = ps.n;
+    c.pos = ps.pos;
+    c.normal = ps.normal;
+    c.range = ps.range;
+    c.obs_offset = ps.obs_offset;
+    c.obs_desc = ps.obs_desc;
+    c.order = d_order;
+    c.n_visit = n_visit;
+    c.width_f = static_cast<float>(p.width);      // int -> float promotion of src/Camera.cpp:36
+    c.height_f = static_cast<float>(p.height);
+    c.radius = p.radius;
+    volatile float r2 = p.radius * p.radius;      // src/KDTree.cpp:48
+    c.r2 = r2;
+    c.min_cos = p.min_cos;
+    c.nearer = p.nearer;
+    c.further = p.further;
+    c.thr = dist_threshold(p.max_dist);
+    c.replace = p.replace ? 1 : 0;
+    c.dbg_uv = nullptr;
+    c.dbg_kp = nullptr;
+    c.dbg_d = nullptr;
+    c.stats = nullptr;
+}
+
+void fill_frame(ProjFrameArgs& f, const FrameDev& fd, const float* pose, const slamgpu_proj_params& p)
+{
+    f.nkp = fd.nkp;
+    f.kd_xy = fd.kd_xy;
+    f.kd_idx = fd.kd_idx;
+    f.desc = fd.desc;
+    f.matched = fd.matched;
+    f.xy = fd.xy;
+    f.proposals = fd.proposals;
+    f.skip = nullptr;
+    f.out_point = nullptr;
+    f.out_dist = nullptr;
+    host_projection_matrix(pose, p.fx, p.fy, p.cx, p.cy, f.M);
+    host_camera_center(pose, f.C);
+}
+
+// One call = any number of resident frames against one point set.
+int match_projection_impl(slamgpu_ctx* ctx, const int* frame_ids, int n_frames, int set_id, const float* poses,
+                          const slamgpu_proj_params* params, const uint8_t* skip, const int32_t* order, int n_order,
+                          int32_t* out_point, int32_t* out_dist, float* dbg_uv, int32_t* dbg_kp, int32_t* dbg_d,
+                          int64_t* stats)
+{
+    SG_CTX(ctx);
+    SG_TRY(check_params(params));
+    SG_CHECK(n_frames >= 0, "negative frame count");
+    if (n_frames == 0) return SLAMGPU_OK;
+    SG_CHECK(frame_ids != nullptr && poses != nullptr, "null frame list / poses");
+    auto ps_it = ctx->point_sets.find(set_id);
+    if (ps_it == ctx->point_sets.end()) return fail(SLAMGPU_ERR_NOTFOUND, "unknown point set id");
+    const PointSetDev& ps = ps_it->second;
+    SG_CHECK(order != nullptr || n_order == 0 || n_order == ps.n, "n_order without an order array");
+    const int n_visit = order ? n_order : ps.n;
+    SG_CHECK(n_visit >= 0, "negative visit count");
+    if (order) {
+        for (int i = 0; i < n_order; ++i)
+            SG_CHECK(order[i] < ps.n, "order entry outside the point set");
+    }
+
+    std::vector<const FrameDev*> fds(n_frames);
+    size_t total_kp = 0;
+    int max_nkp = 0;
+    for (int i = 0; i < n_frames; ++i) {
+        auto it = ctx->frames.find(frame_ids[i]);
+        if (it == ctx->frames.end()) return fail(SLAMGPU_ERR_NOTFOUND, "unknown frame id");
+        for (int j = 0; j < i; ++j)
+            SG_CHECK(frame_ids[j] != frame_ids[i], "a frame may appear only once per projection batch");
+        fds[i] = &it->second;
+        total_kp += static_cast<size_t>(it->second.nkp);
+        max_nkp = std::max(max_nkp, it->second.nkp);
+    }
+    SG_CHECK(total_kp == 0 || (out_point != nullptr && out_dist != nullptr), "null output");
+
+    const bool want_dbg = dbg_uv || dbg_kp || dbg_d || stats;
+    const size_t dbg_rows = static_cast<size_t>(n_frames) * n_visit;
+
+    // ---- device io layout: [skip][order][frame args][out_point][out_dist][dbg...] ----
+    const size_t skip_bytes = skip ? Carver::padded(static_cast<size_t>(n_frames) * ps.n) : 0;
+    const size_t order_bytes = order ? Carver::padded(sizeof(int32_t) * n_order) : 0;
+    const size_t fargs_bytes = n_frames > 1 ? Carver::padded(sizeof(ProjFrameArgs) * n_frames) : 0;
+    const size_t up_bytes = skip_bytes + order_bytes + fargs_bytes;
+    const size_t out_bytes = Carver::padded(sizeof(int32_t) * total_kp) * 2;
+    size_t dbg_bytes = 0;
+    if (want_dbg)
+        dbg_bytes = Carver::padded(sizeof(float) * 2 * dbg_rows) + 2 * Carver::padded(sizeof(int32_t) * dbg_rows) +
+                    Carver::padded(2 * sizeof(unsigned long long));
+    SG_TRY(ensure_device_io(ctx, up_bytes + out_bytes + dbg_bytes + 256));
+    SG_TRY(ensure_host_stage(ctx, std::max(up_bytes, out_bytes + dbg_bytes) + 256));
+
+    Carver dio(ctx->d_io.ptr), hio(ctx->h_stage.ptr);
+    uint8_t* d_skip = skip ? dio.take<uint8_t>(static_cast<size_t>(n_frames) * ps.n) : nullptr;
+    uint8_t* h_skip = skip ? hio.take<uint8_t>(static_cast<size_t>(n_frames) * ps.n) : nullptr;
+    int32_t* d_order = order ? dio.take<int32_t>(n_order) : nullptr;
+    int32_t* h_order = order ? hio.take<int32_t>(n_order) : nullptr;
+    ProjFrameArgs* d_fargs = n_frames > 1 ? dio.take<ProjFrameArgs>(n_frames) : nullptr;
+    ProjFrameArgs* h_fargs_stage = n_frames > 1 ? hio.take<ProjFrameArgs>(n_frames) : nullptr;
+    int32_t* d_out_point = dio.take<int32_t>(total_kp);
+    int32_t* d_out_dist = dio.take<int32_t>(total_kp);
+    float* d_dbg_uv = nullptr;
+    int32_t *d_dbg_kp = nullptr, *d_dbg_d = nullptr;
+    unsigned long long* d_stats = nullptr;
+    if (want_dbg) {
+        d_dbg_uv = dio.take<float>(2 * dbg_rows);
+        d_dbg_kp = dio.take<int32_t>(dbg_rows);
+        d_dbg_d = dio.take<int32_t>(dbg_rows);
+        d_stats = dio.take<unsigned long long>(2);
+    }
+
+    ProjCommonArgs common;
+    fill_common(common, ps, *params, d_order, n_visit);
+    if (want_dbg) {
+        common.dbg_uv = d_dbg_uv;
+        common.dbg_kp = d_dbg_kp;
+        common.dbg_d = d_dbg_d;
+        common.stats = stats ? d_stats : nullptr;
+    }
+
+    std::vector<ProjFrameArgs> fargs(n_frames);
+    size_t kp_off = 0;
+    for (int i = 0; i < n_frames; ++i) {
+        fill_frame(fargs[i], *fds[i], poses + 16 * static_cast<size_t>(i), *params);
+        fargs[i].skip = skip ? d_skip + static_cast<size_t>(i) * ps.n : nullptr;
+        fargs[i].out_point = d_out_point + kp_off;
+        fargs[i].out_dist = d_out_dist + kp_off;
+        kp_off += static_cast<size_t>(fds[i]->nkp);
+    }
+
+    // ---- upload (one copy: the three pieces are contiguous in both arenas) ----
+    if (up_bytes) {
+        if (skip) std::memcpy(h_skip, skip, static_cast<size_t>(n_frames) * ps.n);
+        if (order) std::memcpy(h_order, order, sizeof(int32_t) * n_order);
+        if (n_frames > 1) std::memcpy(h_fargs_stage, fargs.data(), sizeof(ProjFrameArgs) * n_frames);
+        SG_CUDA(cudaMemcpyAsync(ctx->d_io.ptr, ctx->h_stage.ptr, up_bytes, cudaMemcpyHostToDevice, ctx->stream));
+    }
+    if (want_dbg) {   // rows the kernel never reaches read as NaN / -1
+        SG_CUDA(cudaMemsetAsync(d_dbg_uv, 0xFF, dbg_bytes - Carver::padded(2 * sizeof(unsigned long long)), ctx->stream));
+        SG_CUDA(cudaMemsetAsync(d_stats, 0, 2 * sizeof(unsigned long long), ctx->stream));
+    }
+
+    SG_TRY(proj_launch(ctx, common, fargs.data(), d_fargs, n_frames, max_nkp));
+
+    // ---- download: results (and diagnostics) are contiguous on the device ----
+    const size_t down_bytes = out_bytes + dbg_bytes;
+    if (down_bytes) {
+        // the staging buffer's upload part has been consumed by the H2D copy queued above, and the
+        // D2H copy is ordered after it on the same stream
+        SG_CUDA(cudaMemcpyAsync(ctx->h_stage.ptr, d_out_point, down_bytes, cudaMemcpyDeviceToHost, ctx->stream));
+    }
+    SG_CUDA(cudaStreamSynchronize(ctx->stream));
+    const uint8_t* hb = static_cast<const uint8_t*>(ctx->h_stage.ptr);
+    const size_t o_pad = Carver::padded(sizeof(int32_t) * total_kp);
+    if (total_kp) {
+        std::memcpy(out_point, hb, sizeof(int32_t) * total_kp);
+        std::memcpy(out_dist, hb + o_pad, sizeof(int32_t) * total_kp);
+    }
+    if (want_dbg) {
+        const uint8_t* p = hb + 2 * o_pad;
+        if (dbg_uv) std::memcpy(dbg_uv, p, sizeof(float) * 2 * dbg_rows);
+        p += Carver::padded(sizeof(float) * 2 * dbg_rows);
+        if (dbg_kp) std::memcpy(dbg_kp, p, sizeof(int32_t) * dbg_rows);
+        p += Carver::padded(sizeof(int32_t) * dbg_rows);
+        if (dbg_d) std::memcpy(dbg_d, p, sizeof(int32_t) * dbg_rows);
+        p += Carver::padded(sizeof(int32_t) * dbg_rows);
+        if (stats) {
+            unsigned long long s[2];
+            std::memcpy(s, p, sizeof(s));
+            stats[0] = static_cast<int64_t>(s[0]);
+            stats[1] = static_cast<int64_t>(s[1]);
+        }
+    }
+    return SLAMGPU_OK;
+}
+
+} // namespace
+
+extern "C" {
+
+int slamgpu_frame_upload(slamgpu_ctx* ctx, int frame_id, int nkp, const float* xy, const uint8_t* desc,
+                         const uint32_t* kd_perm, const uint8_t* matched)
+{
+    SG_CTX(ctx);
+    SG_CHECK(nkp >= 0 && nkp < (1 << 26), "keypoint count out of range");
+    SG_CHECK(nkp == 0 || (xy != nullptr && desc != nullptr), "null keypoints / descriptors");
+
+    std::vector<uint32_t> perm(static_cast<size_t>(nkp));
+    if (kd_perm) {
+        std::vector<uint8_t> seen(static_cast<size_t>(nkp), 0);
+        for (int i = 0; i < nkp; ++i) {
+            SG_CHECK(kd_perm[i] < static_cast<uint32_t>(nkp) && !seen[kd_perm[i]], "kd_perm is not a permutation");
+            seen[kd_perm[i]] = 1;
+            perm[i] = kd_perm[i];
+        }
+    } else if (nkp > 0) {
+        SG_TRY(slamgpu_kd_build_host(xy, nkp, perm.data()));
+    }
+
+    auto it = ctx->frames.find(frame_id);
+    if (it != ctx->frames.end()) {
+        SG_CUDA(cudaStreamSynchronize(ctx->stream));
+        free_frame(it->second);
+        ctx->frames.erase(it);
+    }
+    FrameDev f;
+    f.nkp = nkp;
+    f.perm_host = perm;
+    const size_t n = static_cast<size_t>(nkp);
+    // device blob: [kd_xy][kd_idx][desc][matched][xy] (uploaded) then [proposals] (device only)
+    const size_t b_kdxy = Carver::padded(n * sizeof(float2)), b_kdidx = Carver::padded(n * sizeof(int32_t)),
+                 b_desc = Carver::padded(n * 32), b_matched = Carver::padded(n), b_xy = Carver::padded(n * sizeof(float2)),
+                 b_prop = Carver::padded(n * sizeof(unsigned long long));
+    const size_t up = b_kdxy + b_kdidx + b_desc + b_matched + b_xy;
+    const size_t total = up + b_prop + 256;
+    const cudaError_t e = cudaMalloc(&f.blob, total);
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        return fail(SLAMGPU_ERR_NOMEM, std::string("frame allocation failed: ") + cudaGetErrorString(e));
+    }
+    Carver dv(f.blob);
+    f.kd_xy = dv.take<float2>(n);
+    f.kd_idx = dv.take<int32_t>(n);
+    f.desc = dv.take<uint4>(2 * n);
+    f.matched = dv.take<uint8_t>(n);
+    f.xy = dv.take<float2>(n);
+    f.proposals = dv.take<unsigned long long>(n);
+
+    if (nkp > 0) {
+        int rc = ensure_host_stage(ctx, up + 256);
+        if (rc != SLAMGPU_OK) {
+            cudaFree(f.blob);
+            return rc;
+        }
+        // staging is free to overwrite only after earlier copies out of it have completed
+        SG_CUDA(cudaStreamSynchronize(ctx->stream));
+        Carver hv(ctx->h_stage.ptr);
+        float* h_kdxy = reinterpret_cast<float*>(hv.take<float2>(n));
+        int32_t* h_kdidx = hv.take<int32_t>(n);
+        uint8_t* h_desc = reinterpret_cast<uint8_t*>(hv.take<uint4>(2 * n));
+        uint8_t* h_matched = hv.take<uint8_t>(n);
+        float* h_xy = reinterpret_cast<float*>(hv.take<float2>(n));
+        for (size_t m = 0; m < n; ++m) {
+            const uint32_t k = perm[m];
+            h_kdxy[2 * m] = xy[2 * k];
+            h_kdxy[2 * m + 1] = xy[2 * k + 1];
+            h_kdidx[m] = static_cast<int32_t>(k);
+        }
+        std::memcpy(h_desc, desc, n * 32);
+        if (matched) {
+            for (size_t i = 0; i < n; ++i) h_matched[i] = matched[i] ? 1 : 0;
+        } else {
+            std::memset(h_matched, 0, n);
+        }
+        std::memcpy(h_xy, xy, n * sizeof(float2));
+        SG_CUDA(cudaMemcpyAsync(f.blob, ctx->h_stage.ptr, up, cudaMemcpyHostToDevice, ctx->stream));
+        SG_CUDA(cudaMemsetAsync(f.proposals, 0xFF, n * sizeof(unsigned long long), ctx->stream));
+        // the staging buffer is reused by the next call: wait for the copy out of it
+        SG_CUDA(cudaStreamSynchronize(ctx->stream));
+    }
+    ctx->frames[frame_id] = std::move(f);
+    return SLAMGPU_OK;
+}
+
+int slamgpu_frame_set_matched(slamgpu_ctx* ctx, int frame_id, const uint8_t* matched)
+{
+    SG_CTX(ctx);
+    auto it = ctx->frames.find(frame_id);
+    if (it == ctx->frames.end()) return fail(SLAMGPU_ERR_NOTFOUND, "unknown frame id");
+    FrameDev& f = it->second;
+    if (f.nkp == 0) return SLAMGPU_OK;
+    const size_t n = static_cast<size_t>(f.nkp);
+    if (matched == nullptr) {
+        SG_CUDA(cudaMemsetAsync(f.matched, 0, n, ctx->stream));
+        return SLAMGPU_OK;
+    }
+    SG_TRY(ensure_host_stage(ctx, n + 256));
+    SG_CUDA(cudaStreamSynchronize(ctx->stream));
+    uint8_t* h = static_cast<uint8_t*>(ctx->h_stage.ptr);
+    for (size_t i = 0; i < n; ++i) h[i] = matched[i] ? 1 : 0;
+    SG_CUDA(cudaMemcpyAsync(f.matched, h, n, cudaMemcpyHostToDevice, ctx->stream));
+    SG_CUDA(cudaStreamSynchronize(ctx->stream));
+    return SLAMGPU_OK;
+}
+
+int slamgpu_frame_release(slamgpu_ctx* ctx, int frame_id)
+{
+    SG_CTX(ctx);
+    auto it = ctx->frames.find(frame_id);
+    if (it == ctx->frames.end()) return fail(SLAMGPU_ERR_NOTFOUND, "unknown frame id");
+    SG_CUDA(cudaStreamSynchronize(ctx->stream));
+    free_frame(it->second);
+    ctx->frames.erase(it);
+    return SLAMGPU_OK;
+}
+
+int slamgpu_frame_get_kd_perm(slamgpu_ctx* ctx, int frame_id, uint32_t* out_perm)
+{
+    SG_CHECK(ctx != nullptr, "null context");
+    auto it = ctx->frames.find(frame_id);
+    if (it == ctx->frames.end()) return fail(SLAMGPU_ERR_NOTFOUND, "unknown frame id");
+    SG_CHECK(it->second.nkp == 0 || out_perm != nullptr, "null output");
+    std::copy(it->second.perm_host.begin(), it->second.perm_host.end(), out_perm);
+    return SLAMGPU_OK;
+}
+
+int slamgpu_points_upload(slamgpu_ctx* ctx, int set_id, int n, const float* pos, const float* normal,
+                          const float* range, const int32_t* obs_offset, const uint8_t* obs_desc,
+                          const float* obs_center)
+{
+    SG_CTX(ctx);
+    SG_CHECK(n >= 0, "negative point count");
+    SG_CHECK(n == 0 || (pos != nullptr && obs_offset != nullptr), "null positions / observation offsets");
+    const bool derive = (normal == nullptr || range == nullptr);
+    SG_CHECK(n == 0 || !derive || obs_center != nullptr, "normal/range missing and no obs_center to derive them");
+    int64_t n_obs = 0;
+    if (n > 0) {
+        SG_CHECK(obs_offset[0] == 0, "obs_offset[0] must be 0");
+        for (int i = 0; i < n; ++i) SG_CHECK(obs_offset[i + 1] >= obs_offset[i], "obs_offset must be non-decreasing");
+        n_obs = obs_offset[n];
+        SG_CHECK(n_obs == 0 || obs_desc != nullptr, "null observation descriptors");
+    }
+
+    auto it = ctx->point_sets.find(set_id);
+    if (it != ctx->point_sets.end()) {
+        SG_CUDA(cudaStreamSynchronize(ctx->stream));
+        free_points(it->second);
+        ctx->point_sets.erase(it);
+    }
+    PointSetDev p;
+    p.n = n;
+    p.n_obs = n_obs;
+    const size_t N = static_cast<size_t>(n), O = static_cast<size_t>(n_obs);
+    const size_t b_pos = Carver::padded(N * 12), b_nrm = Carver::padded(N * 12), b_rng = Carver::padded(N * 8),
+                 b_off = Carver::padded((N + 1) * 4), b_desc = Carver::padded(O * 32);
+    const size_t up = b_pos + b_nrm + b_rng + b_off + b_desc;
+    const size_t b_center = derive ? Carver::padded(O * 12) : 0;
+    const cudaError_t e = cudaMalloc(&p.blob, up + 256);
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        return fail(SLAMGPU_ERR_NOMEM, std::string("point-set allocation failed: ") + cudaGetErrorString(e));
+    }
+    Carver dv(p.blob);
+    p.pos = dv.take<float>(N * 3);
+    p.normal = dv.take<float>(N * 3);
+    p.range = dv.take<float>(N * 2);
+    p.obs_offset = dv.take<int32_t>(N + 1);
+    p.obs_desc = dv.take<uint4>(O * 2);
+
+    if (n > 0) {
+        int rc = ensure_host_stage(ctx, up + b_center + 256);
+        if (rc == SLAMGPU_OK && derive) rc = ensure_device_io(ctx, b_center + 256);
+        if (rc != SLAMGPU_OK) {
+            cudaFree(p.blob);
+            return rc;
+        }
+        SG_CUDA(cudaStreamSynchronize(ctx->stream));
+        Carver hv(ctx->h_stage.ptr);
+        float* h_pos = hv.take<float>(N * 3);
+        float* h_nrm = hv.take<float>(N * 3);
+        float* h_rng = hv.take<float>(N * 2);
+        int32_t* h_off = hv.take<int32_t>(N + 1);
+        uint8_t* h_desc = reinterpret_cast<uint8_t*>(hv.take<uint4>(O * 2));
+        std::memcpy(h_pos, pos, N * 12);
+        if (!derive) {
+            std::memcpy(h_nrm, normal, N * 12);
+            std::memcpy(h_rng, range, N * 8);
+        }
+        std::memcpy(h_off, obs_offset, (N + 1) * 4);
+        if (O) std::memcpy(h_desc, obs_desc, O * 32);
+        SG_CUDA(cudaMemcpyAsync(p.blob, ctx->h_stage.ptr, up, cudaMemcpyHostToDevice, ctx->stream));
+        if (derive) {
+            float* h_center = hv.take<float>(O * 3);
+            if (O) std::memcpy(h_center, obs_center, O * 12);
+            float* d_center = static_cast<float*>(ctx->d_io.ptr);
+            if (O) SG_CUDA(cudaMemcpyAsync(d_center, h_center, O * 12, cudaMemcpyHostToDevice, ctx->stream));
+            rc = proj_launch_point_stats(ctx, p.pos, n, p.obs_offset, d_center, p.normal, p.range);
+            if (rc != SLAMGPU_OK) {
+                cudaFree(p.blob);
+                return rc;
+            }
+        }
+        SG_CUDA(cudaStreamSynchronize(ctx->stream));
+    }
+    ctx->point_sets[set_id] = p;
+    return SLAMGPU_OK;
+}
+
+int slamgpu_points_release(slamgpu_ctx* ctx, int set_id)
+{
+    SG_CTX(ctx);
+    auto it = ctx->point_sets.find(set_id);
+    if (it == ctx->point_sets.end()) return fail(SLAMGPU_ERR_NOTFOUND, "unknown point set id");
+    SG_CUDA(cudaStreamSynchronize(ctx->stream));
+    free_points(it->second);
+    ctx->point_sets.erase(it);
+    return SLAMGPU_OK;
+}
+
+int slamgpu_points_get_stats(slamgpu_ctx* ctx, int set_id, float* out_normal, float* out_range)
+{
+    SG_CTX(ctx);
+    auto it = ctx->point_sets.find(set_id);
+    if (it == ctx->point_sets.end()) return fail(SLAMGPU_ERR_NOTFOUND, "unknown point set id");
+    const PointSetDev& p = it->second;
+    if (p.n == 0) return SLAMGPU_OK;
+    SG_CUDA(cudaStreamSynchronize(ctx->stream));
+    if (out_normal) SG_CUDA(cudaMemcpy(out_normal, p.normal, sizeof(float) * 3 * p.n, cudaMemcpyDeviceToHost));
+    if (out_range) SG_CUDA(cudaMemcpy(out_range, p.range, sizeof(float) * 2 * p.n, cudaMemcpyDeviceToHost));
+    return SLAMGPU_OK;
+}
+
+int slamgpu_match_projection(slamgpu_ctx* ctx, int frame_id, int set_id, const float* pose_colmajor16,
+                             const slamgpu_proj_params* params, const uint8_t* skip, const int32_t* order,
+                             int n_order, int32_t* out_point, int32_t* out_dist)
+{
+    return match_projection_impl(ctx, &frame_id, 1, set_id, pose_colmajor16, params, skip, order, n_order, out_point,
+                                 out_dist, nullptr, nullptr, nullptr, nullptr);
+}
+
+int slamgpu_match_projection_ex(slamgpu_ctx* ctx, int frame_id, int set_id, const float* pose_colmajor16,
+                                const slamgpu_proj_params* params, const uint8_t* skip, const int32_t* order,
+                                int n_order, int32_t* out_point, int32_t* out_dist, float* dbg_uv, int32_t* dbg_kp,
+                                int32_t* dbg_d, int64_t* stats)
+{
+    return match_projection_impl(ctx, &frame_id, 1, set_id, pose_colmajor16, params, skip, order, n_order, out_point,
+                                 out_dist, dbg_uv, dbg_kp, dbg_d, stats);
+}
+
+int slamgpu_match_projection_batch(slamgpu_ctx* ctx, const int* frame_ids, int n_frames, int set_id,
+                                   const float* poses_colmajor16, const slamgpu_proj_params* params,
+                                   const uint8_t* skip, const int32_t* order, int n_order, int32_t* out_point,
+                                   int32_t* out_dist)
+{
+    return match_projection_impl(ctx, frame_ids, n_frames, set_id, poses_colmajor16, params, skip, order, n_order,
+                                 out_point, out_dist, nullptr, nullptr, nullptr, nullptr);
+}
+
+} // extern "C"

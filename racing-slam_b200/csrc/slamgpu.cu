@@ -105,7 +105,7 @@ static void kd_build_perm(const float* xy, int n, std::vector<size_t>& idx)
     }
 }
 
-static bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
+
 
 #define SG_CTX(ctx)                                                       \
     do {                                                                  \

@@ -138,7 +138,7 @@ int bf_launch_mutual(slamgpu_ctx* ctx, const BfPlan& row_plan, const uint2* d_ro
 int bf_launch_scan_counts(slamgpu_ctx* ctx, const int32_t* d_count, int n, int32_t* d_offset /* n+1 */);
 int bf_launch_compact(slamgpu_ctx* ctx, const int32_t* d_out_train, const int32_t* d_frame_offset,
                       const int32_t* d_pairs, int nq_single, int n_pairs, int max_rows, const int32_t* d_offset,
-                      int32_t* d_query_list, int32_t* d_train_list);
+                      int32_t* d_query_list, int32_t* d_train_list, int64_t capacity);
 
 // ---- projection (proj_kernels.cu) -----------------------------------------------------------
 struct ProjFrameArgs {

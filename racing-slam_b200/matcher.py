@@ -1,0 +1,269 @@
+"""Host-side mirror of the reference's matcher interface, on top of libslamgpu.
+
+Same names, argument meaning and empty-result behaviour as the reference (paths relative to the
+reference tree):
+
+  MapMatcher                      src/MapMatcher.h:16-38
+    .match_map(frame, map)                        :21   -> [MapPointMatch]
+    .match_key_frame(frame, map, key_frame)       :24
+    .match_for_fuse(frame, points)                :27
+    .match_descriptors(frame, key_frame)          :30
+  match_features(prev, cur, max_distance)         src/features/FeatureExtractor.cpp:15-30
+  ExtractedFeatures / FeatureMatch / MapPointMatch  src/features/FeatureExtractor.h:15-38
+  Camera / Frame / KeyFrame / MapPoint / Map      read accessors only
+
+The data-model classes below hold exactly what the matcher reads; they exist so that tests read
+like the reference's call sites.  All matching arithmetic runs in the CUDA library -- this module
+only flattens objects to POD arrays (what the C++ adapter in INTEGRATION.md does) and maps
+indices back to objects.
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass, field
+
+import numpy as np
+
+from . import binding as L
+
+NORM_HAMMING = 6          # cv::NORM_HAMMING
+ORB_MAX_DISTANCE = 64.0   # src/features/OrbFeatureExtractor.h:14-17
+
+# src/MapMatcher.cpp:12-18
+SEARCH_RADIUS = 20.0
+MIN_VIEWING_ANGLE_COSINE = 0.5
+MAX_NEARER_RATIO = 2.0
+MAX_FURTHER_RATIO = 1.25
+MATCH_RATIO = 0.75
+
+
+@dataclass
+class ExtractedFeatures:
+    keypoints: np.ndarray      # [n,2] f32 (cv::KeyPoint::pt)
+    descriptors: np.ndarray    # [n,32] u8
+
+
+@dataclass
+class FeatureMatch:
+    train_index: int
+    query_index: int
+
+
+@dataclass
+class Camera:
+    fx: float
+    fy: float
+    cx: float
+    cy: float
+    width: int
+    height: int
+
+    def get_width(self):
+        return self.width
+
+    def get_height(self):
+        return self.height
+
+
+class MapPoint:
+    """position + observations (KeyFrame -> keypoint index, in insertion = iteration order)."""
+
+    def __init__(self, position):
+        self._position = np.asarray(position, np.float32).reshape(3)
+        self._observations: dict = {}
+
+    def position(self):
+        return self._position
+
+    def add_observation(self, key_frame, index: int):
+        self._observations[key_frame] = int(index)
+
+    def observations(self):
+        return self._observations
+
+    def is_observed_by(self, key_frame) -> bool:
+        return key_frame in self._observations
+
+
+@dataclass
+class MapPointMatch:
+    point: MapPoint
+    keypoint_index: int
+
+
+class Frame:
+    def __init__(self, index: int, features: ExtractedFeatures, pose=None):
+        self.index = index
+        self._features = ExtractedFeatures(np.ascontiguousarray(features.keypoints, np.float32).reshape(-1, 2),
+                                           np.ascontiguousarray(features.descriptors, np.uint8).reshape(-1, 32))
+        self._pose = np.eye(4, dtype=np.float32) if pose is None else np.asarray(pose, np.float32).reshape(4, 4)
+        self._map_matches: list = [None] * len(self._features.keypoints)
+        self._matched_points: set = set()
+
+    def features(self):
+        return self._features
+
+    def pose(self):
+        return self._pose
+
+    def set_pose(self, pose):
+        self._pose = np.asarray(pose, np.float32).reshape(4, 4)
+
+    def camera_center(self):
+        """src/Frame.cpp:39-42 in float32 (a0 + (a1 + a2) per component, like the library)."""
+        R, t = self._pose[:3, :3], self._pose[:3, 3]
+        c = np.zeros(3, np.float32)
+        for i in range(3):
+            p = [np.float32(-R[k, i]) * np.float32(t[k]) for k in range(3)]
+            c[i] = np.float32(p[0] + np.float32(p[1] + p[2]))
+        return c
+
+    def descriptor(self, index: int):
+        return self._features.descriptors[index]
+
+    def add_map_match(self, match: MapPointMatch):
+        self._map_matches[match.keypoint_index] = match.point
+        self._matched_points.add(id(match.point))
+
+    def is_matched(self, what) -> bool:
+        if isinstance(what, MapPoint):
+            return id(what) in self._matched_points
+        return self._map_matches[int(what)] is not None
+
+    def map_matches(self):
+        """Ascending keypoint order, like Frame::MapPointIterator (src/Frame.cpp:154-174)."""
+        return [MapPointMatch(p, i) for i, p in enumerate(self._map_matches) if p is not None]
+
+    def num_map_matches(self):
+        return sum(p is not None for p in self._map_matches)
+
+
+class KeyFrame(Frame):
+    def __hash__(self):
+        return id(self)
+
+    def __eq__(self, other):
+        return self is other
+
+
+class Map:
+    """Owns points; iteration order = insertion order (src/Map.cpp:164-190)."""
+
+    def __init__(self):
+        self._points: list = []
+
+    def add_point(self, point: MapPoint):
+        self._points.append(point)
+        return point
+
+    def __iter__(self):
+        return iter(self._points)
+
+    def __len__(self):
+        return len(self._points)
+
+
+def match_features(ctx: L.Context, prev_features: ExtractedFeatures, features: ExtractedFeatures,
+                   max_distance: float = ORB_MAX_DISTANCE):
+    """BaseFeatureExtractor::match_features (src/features/FeatureExtractor.cpp:15-30)."""
+    tr, qu = ctx.match_features(prev_features.descriptors, features.descriptors, max_distance)
+    return [FeatureMatch(int(t), int(q)) for t, q in zip(tr, qu)]
+
+
+@dataclass
+class _Flat:
+    points: list
+    pos: np.ndarray
+    obs_offset: np.ndarray
+    obs_desc: np.ndarray
+    obs_center: np.ndarray
+    order: np.ndarray = field(default=None)
+
+
+def _flatten_points(points) -> _Flat:
+    """What the adapter uploads per map state: position, one descriptor and one observer camera
+    centre per observation, in the host's observations() iteration order (src/MapMatcher.cpp:86)."""
+    uniq, seen, order = [], {}, []
+    for p in points:
+        if p is None:
+            order.append(-1)                      # match_for_fuse nullptr, :119-121
+            continue
+        k = seen.get(id(p))
+        if k is None:
+            k = seen[id(p)] = len(uniq)
+            uniq.append(p)
+        order.append(k)
+    n = len(uniq)
+    pos = np.zeros((n, 3), np.float32)
+    off = np.zeros(n + 1, np.int32)
+    desc, cent = [], []
+    centers = {}
+    for i, p in enumerate(uniq):
+        pos[i] = p.position()
+        for kf, idx in p.observations().items():
+            desc.append(kf.descriptor(idx))
+            c = centers.get(id(kf))
+            if c is None:
+                c = centers[id(kf)] = kf.camera_center()
+            cent.append(c)
+        off[i + 1] = len(desc)
+    obs_desc = np.asarray(desc, np.uint8).reshape(-1, 32)
+    obs_center = np.asarray(cent, np.float32).reshape(-1, 3)
+    return _Flat(uniq, pos, off, obs_desc, obs_center, np.asarray(order, np.int32))
+
+
+class MapMatcher:
+    """Drop-in for slam::MapMatcher: same four entry points, results as [MapPointMatch]."""
+
+    _FRAME_SLOT = 0
+    _SET_SLOT = 0
+
+    def __init__(self, camera: Camera, max_descriptor_distance: float = ORB_MAX_DISTANCE, norm_type=NORM_HAMMING,
+                 ctx: L.Context | None = None, search_radius: float = SEARCH_RADIUS, match_ratio: float = MATCH_RATIO):
+        if norm_type != NORM_HAMMING:
+            raise ValueError("libslamgpu implements NORM_HAMMING (ORB) matching only")
+        self.camera = camera
+        self.max_descriptor_distance = float(max_descriptor_distance)
+        self.ctx = ctx if ctx is not None else L.Context(0)
+        self.search_radius = float(search_radius)
+        self.match_ratio = float(match_ratio)
+
+    def _params(self, replace: bool) -> L.ProjParams:
+        c = self.camera
+        return L.ProjParams(c.fx, c.fy, c.cx, c.cy, c.width, c.height, self.search_radius,
+                            self.max_descriptor_distance, MIN_VIEWING_ANGLE_COSINE, MAX_NEARER_RATIO,
+                            MAX_FURTHER_RATIO, 1 if replace else 0)
+
+    def _project(self, frame: Frame, points, skip_fn, replace: bool):
+        flat = _flatten_points(points)
+        feats = frame.features()
+        nkp = len(feats.keypoints)
+        if nkp == 0:
+            return []
+        matched = np.array([frame.is_matched(i) for i in range(nkp)], np.uint8)
+        skip = np.array([1 if skip_fn(p) else 0 for p in flat.points], np.uint8)
+        self.ctx.frame_upload(self._FRAME_SLOT, feats.keypoints, feats.descriptors, None, matched)
+        self.ctx.points_upload(self._SET_SLOT, flat.pos, None, None, flat.obs_offset, flat.obs_desc, flat.obs_center)
+        pose = np.ascontiguousarray(frame.pose().flatten(order="F"))     # Eigen::Matrix4f is column-major
+        out_point, _ = self.ctx.match_projection(self._FRAME_SLOT, self._SET_SLOT, nkp, pose, self._params(replace),
+                                                 skip, flat.order)
+        # accepted_matches: ascending keypoint index (src/MapMatcher.cpp:34-43)
+        return [MapPointMatch(flat.points[int(p)], kp) for kp, p in enumerate(out_point) if p >= 0]
+
+    def match_map(self, frame: Frame, map_: Map):
+        return self._project(frame, list(map_), lambda p: frame.is_matched(p), False)
+
+    def match_key_frame(self, frame: Frame, map_: Map, key_frame: KeyFrame):
+        return self._project(frame, list(map_),
+                             lambda p: frame.is_matched(p) or not p.is_observed_by(key_frame), False)
+
+    def match_for_fuse(self, frame: Frame, points):
+        return self._project(frame, list(points), lambda p: frame.is_matched(p), True)
+
+    def match_descriptors(self, frame: Frame, key_frame: KeyFrame):
+        matches = key_frame.map_matches()                              # :135-138
+        q = frame.features().descriptors
+        if not matches or len(q) == 0:
+            return []                                                  # :139-141
+        train = np.stack([key_frame.descriptor(m.keypoint_index) for m in matches])
+        qi, ti = self.ctx.match_descriptors(q, train, self.max_descriptor_distance, self.match_ratio)
+        return [MapPointMatch(matches[int(t)].point, int(qq)) for qq, t in zip(qi, ti)]

@@ -1,0 +1,57 @@
+"""Multi-GPU sharding of the batched workloads.  One process per GPU; shards are
+independent, so there is NO data-path collective: each rank matches its own slice and the host
+gathers results.  The only optional exchange is replicating the descriptor database / point set
+(torch.distributed.broadcast over NCCL), done once before matching.
+
+  all_pairs(n)                      LoopDetector ordered pairs query > candidate (src/LoopDetector.h:33)
+  shard_pairs(pairs, rank, world)   block-cyclic split of a pair list, balanced for ragged frames
+  shard_keyframes(n, rank, world)   round-robin split of the fuse window (src/Mapper.cpp:208-219)
+"""
+from __future__ import annotations
+
+import numpy as np
+
+
+def all_pairs(n_frames: int) -> np.ndarray:
+    """Every (query, candidate) with query > candidate, query-major: [n(n-1)/2, 2] int32."""
+    q, c = np.tril_indices(n_frames, -1)
+    return np.stack([q, c], 1).astype(np.int32)
+
+
+def shard_pairs(pairs: np.ndarray, rank: int, world: int, block: int = 64) -> np.ndarray:
+    """Block-cyclic: blocks of `block` consecutive pairs go to ranks round-robin.  Consecutive
+    pairs share their query frame (L2 reuse on the owning GPU); cycling the blocks balances the
+    triangle.  The union over ranks is the input, each pair exactly once."""
+    pairs = np.asarray(pairs, np.int32).reshape(-1, 2)
+    if world <= 1:
+        return pairs
+    blk = np.arange(len(pairs)) // block
+    return np.ascontiguousarray(pairs[blk % world == rank])
+
+
+def shard_index(n: int, rank: int, world: int) -> np.ndarray:
+    """Round-robin item indices of this rank."""
+    return np.arange(rank, n, max(world, 1), dtype=np.int64)
+
+
+def shard_keyframes(n_keyframes: int, rank: int, world: int) -> np.ndarray:
+    return shard_index(n_keyframes, rank, world)
+
+
+def gather_counts(local: np.ndarray, index: np.ndarray, n_total: int, group=None) -> np.ndarray:
+    """Host-side gather of per-item integer results into item order (uses torch.distributed
+    when initialised; a single process returns its own)."""
+    out = np.zeros(n_total, np.int64)
+    out[index] = local
+    try:
+        import torch
+        import torch.distributed as dist
+    except ImportError:   # pragma: no cover
+        return out
+    if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
+        t = torch.from_numpy(out)
+        if dist.get_backend(group) == "nccl":
+            t = t.cuda()
+        dist.all_reduce(t, op=dist.ReduceOp.SUM, group=group)   # shards are disjoint: sum = gather
+        out = t.cpu().numpy()
+    return out

@@ -1,0 +1,87 @@
+"""CPU tests of the drop-in boundary: libslamgpu.so loads, exports exactly what include/slamgpu.h
+declares, has no CPU fallback, and its host-only logic (KD permutation) equals the oracle's."""
+import ctypes as C
+import os
+import re
+import subprocess
+
+import numpy as np
+import pytest
+
+from conftest import ROOT, golden, golden_names
+
+
+def header_symbols():
+    src = open(os.path.join(ROOT, "include", "slamgpu.h")).read()
+    return sorted(set(re.findall(r"^SLAMGPU_API[^;(]*?\b(slamgpu_\w+)\s*\(", src, flags=re.M)))
+
+
+def test_header_declares_the_expected_surface():
+    syms = header_symbols()
+    for must in ["slamgpu_create", "slamgpu_knn2", "slamgpu_crosscheck", "slamgpu_match_descriptors",
+                 "slamgpu_match_features", "slamgpu_match_descriptors_batch", "slamgpu_frame_upload",
+                 "slamgpu_points_upload", "slamgpu_match_projection", "slamgpu_match_projection_batch"]:
+        assert must in syms
+    assert len(syms) >= 30
+
+
+def test_library_exports_every_declared_symbol(pkg):
+    lib = pkg.binding.load()
+    for name in header_symbols():
+        assert hasattr(lib, name), f"{name} declared in include/slamgpu.h but not exported"
+    assert sorted(pkg.binding.SIGNATURES) == header_symbols()
+    assert lib.slamgpu_abi_version() == 1
+
+
+def test_dynamic_symbol_table_has_only_the_c_abi(pkg):
+    out = subprocess.run(["nm", "-D", "--defined-only", pkg.binding.LIB_PATH], capture_output=True, text=True).stdout
+    exported = sorted(l.split()[-1] for l in out.splitlines() if " T " in l)
+    assert [s for s in exported if s.startswith("slamgpu_")] == header_symbols()
+
+
+def test_library_is_built_for_sm_100a_only(pkg):
+    out = subprocess.run(["cuobjdump", "-lelf", pkg.binding.LIB_PATH], capture_output=True, text=True).stdout
+    archs = set(re.findall(r"sm_(\d+a?)", out))
+    assert archs == {"100a"}, archs
+
+
+def test_no_cpu_fallback_without_device(pkg):
+    """Without a CUDA device slamgpu_create must fail (SLAMGPU_ERR_CUDA) -- never compute on the host."""
+    if pkg.binding.device_count() > 0:
+        pytest.skip("a CUDA device is present")
+    with pytest.raises(pkg.SlamGpuError) as e:
+        pkg.Context(0)
+    assert e.value.code == pkg.binding.ERR_CUDA
+
+
+def test_product_package_never_imports_the_oracle():
+    pk = os.path.join(ROOT, "racing-slam_b200")
+    for dirpath, _, files in os.walk(pk):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".h", ".cpp")):
+                src = open(os.path.join(dirpath, f)).read()
+                assert "cpu_oracle" not in src and "liboracle" not in src and "bf_model" not in src, f
+                assert not re.search(r"^\s*(from|import)\s+oracle\b", src, flags=re.M), f
+
+
+@pytest.mark.parametrize("name", golden_names("kd_"))
+def test_kd_build_host_equals_reference_permutation(pkg, name):
+    """slamgpu_kd_build_host runs the reference's nth_element recursion (src/KDTree.cpp:18-43);
+    the golden perm came from the oracle, pinned against the reference's own KDTree2D."""
+    g = golden(name)
+    assert np.array_equal(pkg.binding.kd_build_host(g["xy"]), g["perm"])
+
+
+def test_kd_build_host_random_sizes(pkg, oracle):
+    for seed, n in enumerate([0, 1, 2, 3, 7, 64, 1000, 8000]):
+        xy = pkg.synthetic.keypoints_integer(n, 1920, 1080, seed) if n else np.zeros((0, 2), np.float32)
+        assert np.array_equal(pkg.binding.kd_build_host(xy), oracle.kd_build(xy))
+
+
+def test_last_error_and_null_checks(pkg):
+    lib = pkg.binding.load()
+    assert lib.slamgpu_create(0, None) == pkg.binding.ERR_INVALID
+    assert b"null" in lib.slamgpu_last_error()
+    assert lib.slamgpu_sync(None) == pkg.binding.ERR_INVALID
+    assert lib.slamgpu_kd_build_host(None, -1, None) == pkg.binding.ERR_INVALID
+    assert lib.slamgpu_destroy(None) == pkg.binding.OK
