@@ -1,0 +1,511 @@
+#!/usr/bin/env python
+"""bench.py -- Hamming comparisons/s of the brute-force descriptor matcher on the LoopDetector
+all-pairs workload (BASELINE.json configs[4] shape: 1000 key frames x 4000 ORB descriptors,
+ordered pairs query > candidate, kNN-2 + max-distance 64 + Lowe ratio 0.75 per pair), sharded
+by frame pair over N GPUs with no data-path collective.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+
+A step = one batch of `--pairs-per-step` frame pairs per rank (each 4000 x 4000 = 16 M
+comparisons).  `value` times the device-resident C-ABI call (inputs already in HBM) with CUDA
+events on the library's stream; `e2e` times the host-buffer C-ABI call
+(slamgpu_match_descriptors_batch: pinned host descriptors + pair list in, compacted match lists
+out, copies inside the timed region).  `--impl reference` times the reference's own CPU path for
+the same pairs: cv2.BFMatcher(NORM_HAMMING).knnMatch(k=2) + the filters of
+src/MapMatcher.cpp:151-161 (the very library call the reference makes), else the oracle port.
+Prints ONE JSON line on rank 0.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+N_FRAMES, N_DESC = 1000, 4000          # BASELINE.json configs[4]
+MAX_DIST, RATIO = 64.0, 0.75           # src/features/OrbFeatureExtractor.h:14-17, src/MapMatcher.cpp:18
+METRIC, UNIT = "hamming_comparisons_per_s", "G/s"
+POPC_PER_CLK_PER_SM = 16               # measured on the box by slamgpu_bench_popc (profiles/)
+POPC_PER_COMPARISON = 8                # 256 bits = 8 POPC32
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--pairs-per-step", type=int, default=2048, help="frame pairs per rank per step")
+    ap.add_argument("--ref-pairs-per-step", type=int, default=24, help="frame pairs per step of the CPU arm")
+    ap.add_argument("--frames", type=int, default=N_FRAMES)
+    ap.add_argument("--desc", type=int, default=N_DESC)
+    ap.add_argument("--no-also", action="store_true", help="skip the secondary C1-C4 measurements")
+    return ap.parse_args()
+
+
+def dist_env():
+    return (int(os.environ.get("RANK", 0)), int(os.environ.get("LOCAL_RANK", 0)),
+            int(os.environ.get("WORLD_SIZE", 1)))
+
+
+def load_peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        with open(path) as f:
+            p = json.load(f)
+        return dict(hbm_gbs=float(p["hbm_gbs"]), sm_max_mhz=float(p.get("sm_max_mhz", 1965.0)), source="measured")
+    return dict(hbm_gbs=6650.0, sm_max_mhz=1965.0, source="fallback")
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md)."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.rows, self.proc = [], None
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(index), f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append((time.time(), [x.strip() for x in line.split(",")]))
+
+    def stop(self, t0: float, t1: float):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(5)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+        rows = [r for t, r in self.rows if t0 - 0.05 <= t <= t1 + 0.05] or [r for _, r in self.rows]
+        sm, mx, reasons, power = [], [], set(), []
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in rows:
+            try:
+                sm.append(float(r[0])), mx.append(float(r[1])), power.append(float(r[2]))
+            except (ValueError, IndexError):
+                continue
+            for n, v in zip(names, r[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "power_w_max": max(power) if power else None, "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def make_workload(args, rank: int, world: int):
+    """The key-frame database (identical on every rank: same seed -- replication without a
+    collective) and this rank's block-cyclic shard of the ordered pair list."""
+    import racing_slam_b200 as pkg
+    db = pkg.synthetic.keyframe_db_fast(args.frames, args.desc, 5)
+    off = (np.arange(args.frames + 1, dtype=np.int64) * args.desc).astype(np.int32)
+    pairs = pkg.sharding.shard_pairs(pkg.sharding.all_pairs(args.frames), rank, world, block=64)
+    return db, off, pairs
+
+
+def workload_name(args) -> str:
+    return (f"loop-closure all-pairs verification (BASELINE configs[4] shape): {args.frames} key frames x "
+            f"{args.desc} ORB descriptors, kNN-2 + max-distance {MAX_DIST:g} + ratio {RATIO:g} per ordered pair "
+            f"(query > candidate)")
+
+
+def step_pairs(pairs: np.ndarray, step: int, n: int) -> np.ndarray:
+    """The n pairs of step `step`: a sliding window over this rank's shard (wraps around)."""
+    idx = (np.arange(n, dtype=np.int64) + step * n) % len(pairs)
+    return np.ascontiguousarray(pairs[idx])
+
+
+# ------------------------------------------------------------------------------------------------
+# CPU arm: the reference's own path for one frame pair (src/MapMatcher.cpp:145-161)
+# ------------------------------------------------------------------------------------------------
+def cpu_matcher():
+    """(kind, cores, fn, describe).  kind "reference": cv2.BFMatcher, the same OpenCV call the
+    reference makes (its C++ cannot be built here: no Eigen/OpenCV headers -- DESIGN.md).  Falls back
+    to the oracle port (OpenMP) when cv2 is missing -- the only place bench.py executes oracle/."""
+    cores = os.cpu_count() or 1
+    try:
+        import cv2
+        cv2.setNumThreads(cores)
+
+        def run(q, t):
+            knn = cv2.BFMatcher(cv2.NORM_HAMMING).knnMatch(q, t, k=2 if len(t) >= 2 else 1)
+            n = 0
+            for c in knn:                                    # the reference's filter loop, :151-161
+                if not c or c[0].distance > MAX_DIST:
+                    continue
+                if len(c) > 1 and c[0].distance > RATIO * c[1].distance:
+                    continue
+                n += 1
+            return n
+        return "reference", cores, run, f"cv2 {cv2.__version__} BFMatcher.knnMatch(k=2) + ratio filter, {cores} threads"
+    except ImportError:
+        from oracle import cpu_oracle
+
+        def run(q, t):
+            return len(cpu_oracle.match_descriptors(q, t, MAX_DIST, RATIO)[0])
+        return "port", cores, run, f"oracle/slam_oracle.cpp orc_match_descriptors, OpenMP {cores} threads"
+
+
+def time_cpu_pairs(run, db, pairs, budget_s=None):
+    """Wall time of `run` over the given pairs (stops early when budget_s is exceeded)."""
+    t0 = time.perf_counter()
+    done, matches = 0, 0
+    for fq, ft in pairs:
+        matches += run(db[fq], db[ft])
+        done += 1
+        if budget_s is not None and time.perf_counter() - t0 > budget_s:
+            break
+    return time.perf_counter() - t0, done, matches
+
+
+def run_reference(args, rank, world):
+    if rank != 0:
+        return                                       # rank 0 alone runs the CPU arm
+    import racing_slam_b200 as pkg
+    db = pkg.synthetic.keyframe_db_fast(args.frames, args.desc, 5)
+    pairs = pkg.sharding.all_pairs(args.frames)
+    kind, cores, run, what = cpu_matcher()
+    n = args.ref_pairs_per_step
+    per_pair = float(args.desc) * args.desc
+    for w in range(args.warmup):
+        time_cpu_pairs(run, db, step_pairs(pairs, w, min(n, 4)))
+    t = 0.0
+    for s in range(args.steps):
+        dt, done, _ = time_cpu_pairs(run, db, step_pairs(pairs, args.warmup + s, n))
+        assert done == n
+        t += dt
+    value = n * args.steps * per_pair / t / 1e9
+    sample = f"{n} frame pairs of {args.desc}x{args.desc} per step ({what})"
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": t / args.steps * 1e3, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+        "config": {"workload": workload_name(args), "pairs_per_step": n, "sharding": "cpu, rank 0 only"},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": kind, "sample": sample},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def cpu_baseline(args, db, budget_s=12.0):
+    """Bounded sample of the same workload on the host cores (rank 0, N=1 only)."""
+    import racing_slam_b200 as pkg
+    kind, cores, run, what = cpu_matcher()
+    pairs = pkg.sharding.all_pairs(args.frames)
+    time_cpu_pairs(run, db, pairs[:2])
+    dt, done, _ = time_cpu_pairs(run, db, pairs[2:2 + 4096], budget_s=budget_s)
+    per_pair = float(args.desc) * args.desc
+    out = {"value": done * per_pair / dt / 1e9, "unit": UNIT, "cores": cores, "kind": kind,
+           "sample": f"{done} frame pairs of {args.desc}x{args.desc} in {dt:.1f} s ({what})"}
+    if kind == "reference":                     # the oracle port beside it, for transparency
+        from oracle import cpu_oracle
+        port = lambda q, t: len(cpu_oracle.match_descriptors(q, t, MAX_DIST, RATIO)[0])  # noqa: E731
+        time_cpu_pairs(port, db, pairs[:1])
+        dt2, done2, _ = time_cpu_pairs(port, db, pairs[2:2 + 4096], budget_s=budget_s / 2)
+        out["port"] = {"value": done2 * per_pair / dt2 / 1e9, "unit": UNIT, "cores": cores,
+                       "sample": f"{done2} pairs, oracle/slam_oracle.cpp with OpenMP"}
+    return out
+
+
+# ------------------------------------------------------------------------------------------------
+# GPU arm
+# ------------------------------------------------------------------------------------------------
+def popc_peak_gcmp(n_sm: int, mhz: float) -> float:
+    return n_sm * POPC_PER_CLK_PER_SM * mhz * 1e6 / POPC_PER_COMPARISON / 1e9
+
+
+def run_ours(args, rank, local_rank, world):
+    import ctypes as C
+
+    import torch
+    import torch.distributed as dist
+
+    import racing_slam_b200 as pkg
+
+    if not torch.cuda.is_available():
+        raise RuntimeError("bench.py needs a CUDA device: libslamgpu has no CPU path")
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+
+    def max_over_ranks(x: float) -> float:
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def sum_over_ranks(x: float) -> float:
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        return float(t.item())
+
+    peaks = load_peaks()
+    ctx = pkg.Context(local_rank)
+    lib = ctx._lib
+    stream = torch.cuda.ExternalStream(ctx.stream)
+    db, off, pairs = make_workload(args, rank, world)
+    n, K, W = args.pairs_per_step, args.steps, args.warmup
+    per_pair = float(args.desc) * args.desc
+    n_sm = torch.cuda.get_device_properties(local_rank).multi_processor_count
+
+    # ---- device-resident arm: everything in HBM before the clock starts ----
+    d_desc = torch.from_numpy(db.reshape(-1, 32)).cuda()
+    d_off = torch.from_numpy(off).cuda()
+    d_pairs = torch.from_numpy(np.stack([step_pairs(pairs, s, n) for s in range(W + K)])).cuda()
+    d_out_train = torch.empty((n, args.desc), dtype=torch.int32, device="cuda")
+    d_count = torch.empty(n, dtype=torch.int32, device="cuda")
+    torch.cuda.synchronize()
+
+    def step_dev(s):
+        ctx.match_descriptors_batch_dev(d_desc.data_ptr(), d_off.data_ptr(), args.frames, d_pairs[s].data_ptr(), n,
+                                        args.desc, MAX_DIST, RATIO, d_out_train.data_ptr(), d_count.data_ptr())
+
+    for s in range(W):
+        step_dev(s)
+    ctx.sync()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    sampler = ClockSampler(local_rank) if rank == 0 else None
+    ctx.profile_enable(True)
+    ctx.profile_read(0)
+    launches0 = ctx.launches
+    barrier()
+    torch.cuda.synchronize()
+    t_wall0 = time.time()
+    e0.record(stream)
+    for s in range(K):
+        step_dev(W + s)
+    e1.record(stream)
+    torch.cuda.synchronize()
+    barrier()
+    t_wall1 = time.time()
+    ms_dev = max_over_ranks(float(e0.elapsed_time(e1)))
+    gpu_launches = ctx.launches - launches0
+    scan_ms, scan_launches = ctx.profile_read(0)
+    ctx.profile_enable(False)
+    clocks = sampler.stop(t_wall0, t_wall1) if sampler else None
+    value = world * n * K * per_pair / (ms_dev * 1e-3) / 1e9
+    dev_counts_last = d_count.cpu().numpy().astype(np.int64)
+
+    # ---- e2e arm: the host-buffer C-ABI call, host<->device copies inside the timed region ----
+    h_db = torch.from_numpy(db.reshape(-1, 32)).pin_memory()
+    h_off = torch.from_numpy(off).pin_memory()
+    h_pairs = torch.from_numpy(np.stack([step_pairs(pairs, s, n) for s in range(W + K)])).pin_memory()
+    cap = n * 1024
+    o_off = np.zeros(n + 1, np.int32)
+    o_q = np.zeros(cap, np.int32)
+    o_t = np.zeros(cap, np.int32)
+    total = C.c_int64(0)
+    u8p, i32p = C.POINTER(C.c_uint8), C.POINTER(C.c_int32)
+
+    def step_host(s):
+        rc = lib.slamgpu_match_descriptors_batch(
+            ctx._h, C.cast(h_db.data_ptr(), u8p), C.cast(h_off.data_ptr(), i32p), args.frames,
+            C.cast(h_pairs[s].data_ptr(), i32p), n, MAX_DIST, RATIO, o_off.ctypes.data_as(i32p),
+            o_q.ctypes.data_as(i32p), o_t.ctypes.data_as(i32p), cap, C.byref(total))
+        ctx._check(rc)
+        return int(total.value)
+
+    for s in range(W):
+        step_host(s)
+    barrier()
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    d2h = 0
+    for s in range(K):
+        d2h += 4 * (n + 1) + 8 * step_host(W + s)
+    torch.cuda.synchronize()
+    t_e2e = max_over_ranks(time.perf_counter() - t0)
+    barrier()
+    e2e_value = world * n * K * per_pair / t_e2e / 1e9
+    h2d_per_step = h_db.numel() + 4 * h_off.numel() + 8 * n
+    # the two API forms ran the same last step: their per-pair match counts must agree
+    assert np.array_equal(np.diff(o_off.astype(np.int64)), dev_counts_last), "host and device API forms disagree"
+    checksum = int(sum_over_ranks(float(dev_counts_last.sum())))
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    # ---- roofline of the dominant kernel (K1 brute-force scan), live CUDA-event durations ----
+    avg_ms = scan_ms / max(scan_launches, 1)
+    cmp_per_launch = n * K * per_pair / max(scan_launches, 1)
+    achieved = cmp_per_launch / (avg_ms * 1e-3) / 1e9
+    peak = popc_peak_gcmp(n_sm, peaks["sm_max_mhz"])
+    bytes_per_launch = (n * K / max(scan_launches, 1)) * (2 * args.desc * 32 + args.desc * 8)
+    hbm_achieved = bytes_per_launch / (avg_ms * 1e-3) / 1e9
+    roofline = {
+        "bound": "popc", "achieved": achieved, "peak": peak, "unit": "Gcmp/s", "frac": achieved / peak,
+        "traffic": None, "kernel": "bf_scan_kernel", "launches": scan_launches, "avg_launch_ms": avg_ms,
+        "share_of_step": scan_ms / ms_dev,
+        "peak_basis": f"{n_sm} SMs x {POPC_PER_CLK_PER_SM} POPC32/clk/SM (slamgpu_bench_popc, profiles/) x "
+                      f"{peaks['sm_max_mhz']:.0f} MHz / {POPC_PER_COMPARISON} POPC32 per 256-bit comparison",
+        "hbm": {"bound": "hbm", "achieved": hbm_achieved, "peak": peaks["hbm_gbs"], "unit": "GB/s",
+                "frac": hbm_achieved / peaks["hbm_gbs"], "peak_source": peaks["source"],
+                "algorithmic_bytes_per_launch": bytes_per_launch},
+    }
+    if clocks and clocks.get("sm_mhz"):
+        roofline["frac_at_observed_clock"] = achieved / popc_peak_gcmp(n_sm, clocks["sm_mhz"])
+
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
+        "ms_per_step": ms_dev / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8",
+        "data": "synthetic",
+        "config": {"workload": workload_name(args),
+                   "pairs_per_step_per_gpu": n, "comparisons_per_step": world * n * per_pair,
+                   "sharding": f"frame pairs block-cyclic over {world} rank(s), database replicated, no collective",
+                   "l2": f"database {db.nbytes / 2**20:.0f} MiB (>= 126 MB L2), different pairs every step"},
+        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d_per_step),
+                "d2h_bytes_per_step": int(d2h // K), "ms_per_step": t_e2e / K * 1e3,
+                "api": "slamgpu_match_descriptors_batch (host buffers; descriptors re-uploaded every step)"},
+        "gpu_launches": int(gpu_launches), "roofline": roofline, "clocks": clocks,
+        "matches_last_step_all_ranks": checksum,
+    }
+    if world == 1:
+        line["cpu_baseline"] = cpu_baseline(args, db)
+        if not args.no_also:
+            line["also"] = also_measurements(ctx, pkg, torch, stream, n_sm, peaks)
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def also_measurements(ctx, pkg, torch, stream, n_sm, peaks):
+    """Secondary numbers on the other BASELINE configs (N=1 only; not the headline):
+    C1 single 2000x2000 pair, 8k x 8k device-resident kNN-2 (the north-star roofline bar),
+    C2 projection-guided search per frame, C4 key-frame batch.  All through the C ABI."""
+    syn = pkg.synthetic
+    out = {}
+
+    def wall(fn, reps, warm=3):
+        for _ in range(warm):
+            fn()
+        ts = []
+        for _ in range(reps):
+            t = time.perf_counter()
+            fn()
+            ts.append(time.perf_counter() - t)
+        return float(np.median(ts))
+
+    # C1: host-buffer calls, H2D + D2H inside
+    q, t = syn.bf_correlated(2000, 2000, 1)
+    s = wall(lambda: ctx.match_descriptors(q, t, MAX_DIST, RATIO), 50)
+    out["c1_match_descriptors_2000x2000"] = {"us_per_call": s * 1e6, "gcmp_s": 4e6 / s / 1e9, "copies": "inside"}
+    s = wall(lambda: ctx.match_features(t, q, MAX_DIST), 50)
+    out["c1_match_features_2000x2000"] = {"us_per_call": s * 1e6, "gcmp_s": 4e6 / s / 1e9, "copies": "inside",
+                                         "note": "cross-check: both directions are needed"}
+
+    # 8k x 8k kNN-2, device-resident, CUDA events; L2 flushed between iterations
+    rng = np.random.default_rng(8)
+    dq = torch.from_numpy(rng.integers(0, 256, (8000, 32), dtype=np.uint8)).cuda()
+    dt = torch.from_numpy(rng.integers(0, 256, (8000, 32), dtype=np.uint8)).cuda()
+    idx = torch.empty((8000, 2), dtype=torch.int32, device="cuda")
+    dist_ = torch.empty((8000, 2), dtype=torch.int32, device="cuda")
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+    torch.cuda.synchronize()
+    for _ in range(3):
+        ctx.knn2_dev(dq.data_ptr(), 8000, dt.data_ptr(), 8000, idx.data_ptr(), dist_.data_ptr())
+    ctx.sync()
+    ctx.profile_enable(True)
+    ctx.profile_read(0)
+    tot = 0.0
+    for _ in range(20):
+        flush.fill_(1)
+        torch.cuda.synchronize()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record(stream)
+        ctx.knn2_dev(dq.data_ptr(), 8000, dt.data_ptr(), 8000, idx.data_ptr(), dist_.data_ptr())
+        b.record(stream)
+        torch.cuda.synchronize()
+        tot += a.elapsed_time(b)
+    scan_ms, scan_n = ctx.profile_read(0)
+    ctx.profile_enable(False)
+    g_call = 64e6 / (tot / 20 * 1e-3) / 1e9
+    g_kernel = 64e6 / (scan_ms / max(scan_n, 1) * 1e-3) / 1e9
+    peak = popc_peak_gcmp(n_sm, peaks["sm_max_mhz"])
+    out["knn2_8000x8000_device"] = {"us_per_call": tot / 20 * 1e3, "gcmp_s": g_call, "scan_kernel_gcmp_s": g_kernel,
+                                   "popc_roofline_frac_call": g_call / peak, "popc_roofline_frac_kernel": g_kernel / peak,
+                                   "l2": "flushed (256 MiB fill) before every call"}
+    del flush
+
+    # C2: resident frame + point set; per frame: pose in, proposals out
+    cam = syn.KITTI
+    sc = syn.projection_scene(10000, 2000, 2)
+    ctx.frame_upload(900, sc.kp_xy, sc.kp_desc, None, sc.kp_matched)
+    ctx.points_upload(900, sc.pos, sc.normal, sc.range, sc.obs_offset, sc.obs_desc)
+    for radius in (15.0, 20.0):
+        prm = pkg.ProjParams(cam["fx"], cam["fy"], cam["cx"], cam["cy"], cam["width"], cam["height"], radius,
+                             MAX_DIST, 0.5, 2.0, 1.25, 0)
+        s = wall(lambda: ctx.match_projection(900, 900, 2000, sc.pose, prm, sc.skip, None), 200)
+        ctx.profile_enable(True)
+        ctx.profile_read(1)
+        for _ in range(50):
+            ctx.match_projection(900, 900, 2000, sc.pose, prm, sc.skip, None)
+        k_ms, k_n = ctx.profile_read(1)
+        ctx.profile_enable(False)
+        nbytes = (len(sc.pos) * 37 + len(sc.obs_desc) * 32 + 2000 * 45 + 2000 * 8)
+        out[f"c2_projection_10k_points_2000_kp_r{radius:g}"] = {
+            "frames_per_s": 1.0 / s, "us_per_frame": s * 1e6, "match_kernel_us": k_ms / max(k_n, 1) * 1e3,
+            "algorithmic_bytes": nbytes, "kernel_gb_s": nbytes / (k_ms / max(k_n, 1) * 1e-3) / 1e9,
+            "hbm_frac": nbytes / (k_ms / max(k_n, 1) * 1e-3) / 1e9 / peaks["hbm_gbs"], "copies": "inside"}
+    ctx.frame_release(900)
+    ctx.points_release(900)
+
+    # C4: 20 key frames x 50k points, frozen snapshot, replace = true
+    sc = syn.projection_scene(50000, 2000, 4)
+    rng = np.random.default_rng(4)
+    ids, nkps, poses = [], [], []
+    for k in range(20):
+        xy = syn.keypoints_integer(2000, cam["width"], cam["height"], 700 + k)
+        ctx.frame_upload(1000 + k, xy, sc.kp_desc[rng.permutation(2000)], None, None)
+        ids.append(1000 + k), nkps.append(2000), poses.append(syn.pose_colmajor(syn.make_pose(rng)))
+    ctx.points_upload(901, sc.pos, sc.normal, sc.range, sc.obs_offset, sc.obs_desc)
+    prm = pkg.ProjParams(cam["fx"], cam["fy"], cam["cx"], cam["cy"], cam["width"], cam["height"], 20.0, MAX_DIST, 0.5,
+                         2.0, 1.25, 1)
+    poses = np.stack(poses)
+    s = wall(lambda: ctx.match_projection_batch(ids, nkps, 901, poses, prm), 30)
+    out["c4_fuse_batch_20_keyframes_x_50k_points"] = {"ms_per_batch": s * 1e3, "keyframes_per_s": 20.0 / s,
+                                                      "point_projections_per_s": 20 * 50000 / s, "copies": "inside"}
+    for k in ids:
+        ctx.frame_release(k)
+    ctx.points_release(901)
+    return out
+
+
+def main():
+    args = parse_args()
+    rank, local_rank, world = dist_env()
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+    else:
+        run_ours(args, rank, local_rank, world)
+
+
+if __name__ == "__main__":
+    main()

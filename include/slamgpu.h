@@ -206,6 +206,14 @@ SLAMGPU_API int slamgpu_match_projection_batch(slamgpu_ctx* ctx, const int* fram
 /* ------------------------------------------------------------------------------------------
  * Diagnostics
  * ---------------------------------------------------------------------------------------- */
+/* Per-kernel device timing for roofline reports: while enabled, every launch of the two dominant
+ * kernels is bracketed by a CUDA-event pair on the context's stream.  slamgpu_profile_read
+ * synchronises, returns the summed duration and launch count since the last read, and resets.
+ *   kernel  SLAMGPU_KERNEL_BF_SCAN (K1 brute-force scan) or SLAMGPU_KERNEL_PROJ_MATCH (K4). */
+#define SLAMGPU_KERNEL_BF_SCAN 0
+#define SLAMGPU_KERNEL_PROJ_MATCH 1
+SLAMGPU_API int slamgpu_profile_enable(slamgpu_ctx* ctx, int on);
+SLAMGPU_API int slamgpu_profile_read(slamgpu_ctx* ctx, int kernel, double* total_ms, int64_t* launches);
 /* POPC-pipe microbenchmark ("confirm with a POPC microbenchmark on the box"):
  * returns 32-bit POPC results per second over the whole device and the SM count. */
 SLAMGPU_API int slamgpu_bench_popc(slamgpu_ctx* ctx, double* popc_per_s, int* n_sm, double* sm_mhz_est);

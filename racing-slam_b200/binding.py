@@ -75,6 +75,8 @@ SIGNATURES = {
                                               C.c_int, _i32p, _i32p, _f32p, _i32p, _i32p, _i64p]),
     "slamgpu_match_projection_batch": (C.c_int, [_ctx, C.POINTER(C.c_int), C.c_int, C.c_int, _f32p,
                                                  C.POINTER(ProjParams), _u8p, _i32p, C.c_int, _i32p, _i32p]),
+    "slamgpu_profile_enable": (C.c_int, [_ctx, C.c_int]),
+    "slamgpu_profile_read": (C.c_int, [_ctx, C.c_int, C.POINTER(C.c_double), _i64p]),
     "slamgpu_bench_popc": (C.c_int, [_ctx, C.POINTER(C.c_double), C.POINTER(C.c_int), C.POINTER(C.c_double)]),
 }
 
@@ -170,6 +172,15 @@ class Context:
     @property
     def launches(self) -> int:
         return int(self._lib.slamgpu_launch_count(self._h))
+
+    def profile_enable(self, on: bool = True):
+        self._check(self._lib.slamgpu_profile_enable(self._h, 1 if on else 0))
+
+    def profile_read(self, kernel: int):
+        """(total_ms, launches) of kernel 0 = brute-force scan, 1 = projection match since the last read."""
+        ms, n = C.c_double(0), C.c_int64(0)
+        self._check(self._lib.slamgpu_profile_read(self._h, kernel, C.byref(ms), C.byref(n)))
+        return ms.value, n.value
 
     def bench_popc(self):
         rate, n_sm, mhz = C.c_double(0), C.c_int(0), C.c_double(0)

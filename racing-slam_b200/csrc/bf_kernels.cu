@@ -399,6 +399,7 @@ int bf_launch_scan(slamgpu_ctx* ctx, const BfPlan& plan, const uint8_t* d_query,
     if (n_ctas <= 0) return SLAMGPU_OK;
     SG_CHECK(n_ctas < (int64_t(1) << 31), "brute-force grid too large; split the pair list");
     const dim3 grid(static_cast<unsigned>(n_ctas));
+    ProfScope prof(ctx, SLAMGPU_KERNEL_BF_SCAN);
     if (plan.r == 2) {
         bf_scan_kernel<2><<<grid, kThreads, 0, ctx->stream>>>(a);
     } else {
@@ -499,18 +500,25 @@ __global__ void __launch_bounds__(256) popc_bench_kernel(uint32_t seed, int iter
 #pragma unroll
     for (int i = 0; i < 8; ++i) x[i] = seed * (threadIdx.x + 1) + i * 0x9E3779B9u + blockIdx.x;
     uint32_t acc = 0;
-    const long long c0 = clock64();
+    long long c0, c1;
+    unsigned long long t0, t1;
+    asm volatile("mov.u64 %0, %%clock64;" : "=l"(c0)::"memory");
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0)::"memory");
     for (int it = 0; it < iters; ++it) {
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
             x[i] = __popc(x[i]) + seed;   // dependent per chain, 8 independent chains per thread
         }
     }
-    const long long c1 = clock64();
 #pragma unroll
     for (int i = 0; i < 8; ++i) acc ^= x[i];
-    if (acc == 0xDEADBEEFu) sink[0] = acc;
-    if (threadIdx.x == 0 && blockIdx.x == 0) cycles[0] = c1 - c0;
+    if (acc == 0xDEADBEEFu) sink[0] = acc;   // keeps the chains alive; orders the clock reads after them
+    asm volatile("mov.u64 %0, %%clock64;" : "=l"(c1)::"memory");
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1)::"memory");
+    if (threadIdx.x == 0 && blockIdx.x == 0) {
+        cycles[0] = c1 - c0;
+        cycles[1] = static_cast<long long>(t1 - t0);   // ns
+    }
 }
 } // namespace
 
@@ -531,15 +539,15 @@ int popc_microbench(slamgpu_ctx* ctx, double* popc_per_s, int* n_sm, double* sm_
     SG_CUDA(cudaEventSynchronize(e1));
     float ms = 0.f;
     SG_CUDA(cudaEventElapsedTime(&ms, e0, e1));
-    long long h_cyc = 0;
-    SG_CUDA(cudaMemcpy(&h_cyc, cyc, sizeof(h_cyc), cudaMemcpyDeviceToHost));
+    long long h_cyc[2] = {0, 0};
+    SG_CUDA(cudaMemcpy(h_cyc, cyc, sizeof(h_cyc), cudaMemcpyDeviceToHost));
     cudaEventDestroy(e0);
     cudaEventDestroy(e1);
     const double ops = static_cast<double>(ctas) * 256.0 * 8.0 * iters;
     if (popc_per_s) *popc_per_s = ops / (ms * 1e-3);
     if (n_sm) *n_sm = ctx->n_sm;
-    // cycles measured by CTA 0 cover (about) the whole launch: SM clock estimate in MHz
-    if (sm_mhz_est) *sm_mhz_est = static_cast<double>(h_cyc) / (ms * 1e-3) / 1e6;
+    // SM cycles over wall nanoseconds seen by one thread of CTA 0: the SM clock under this load, in MHz
+    if (sm_mhz_est) *sm_mhz_est = h_cyc[1] > 0 ? static_cast<double>(h_cyc[0]) / static_cast<double>(h_cyc[1]) * 1e3 : 0.0;
     return SLAMGPU_OK;
 }
 

@@ -256,6 +256,7 @@ int proj_launch(slamgpu_ctx* ctx, const ProjCommonArgs& common, const ProjFrameA
         ctx->launches++;
         if (common.n_visit > 0) {
             const dim3 gp((common.n_visit + kProjThreads - 1) / kProjThreads, n_frames);
+            ProfScope prof(ctx, SLAMGPU_KERNEL_PROJ_MATCH);
             proj_match_kernel<<<gp, kProjThreads, 0, ctx->stream>>>(a);
             ctx->launches++;
         }

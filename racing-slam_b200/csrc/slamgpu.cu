@@ -19,6 +19,38 @@ int fail(int code, const std::string& msg)
     return code;
 }
 
+static cudaEvent_t prof_event(slamgpu_ctx* ctx)
+{
+    if (!ctx->prof_pool.empty()) {
+        cudaEvent_t e = ctx->prof_pool.back();
+        ctx->prof_pool.pop_back();
+        return e;
+    }
+    cudaEvent_t e = nullptr;
+    if (cudaEventCreate(&e) != cudaSuccess) {
+        cudaGetLastError();
+        return nullptr;
+    }
+    return e;
+}
+
+ProfScope::ProfScope(slamgpu_ctx* c, int k) : ctx(c), kernel(k)
+{
+    if (!ctx->profiling) return;
+    cudaEvent_t start = prof_event(ctx);
+    stop = prof_event(ctx);
+    if (!start || !stop) {
+        stop = nullptr;
+        return;
+    }
+    cudaEventRecord(start, ctx->stream);
+    ctx->prof_events[kernel].push_back({start, stop});
+}
+ProfScope::~ProfScope()
+{
+    if (stop) cudaEventRecord(stop, ctx->stream);
+}
+
 static int grow(slamgpu_ctx* ctx, Arena& a, size_t bytes, bool host)
 {
     if (bytes <= a.cap) return SLAMGPU_OK;
@@ -187,6 +219,12 @@ int slamgpu_destroy(slamgpu_ctx* ctx)
     if (ctx->d_ws.ptr) cudaFree(ctx->d_ws.ptr);
     if (ctx->d_io.ptr) cudaFree(ctx->d_io.ptr);
     if (ctx->h_stage.ptr) cudaFreeHost(ctx->h_stage.ptr);
+    for (auto& v : ctx->prof_events)
+        for (auto& pr : v) {
+            cudaEventDestroy(pr.first);
+            cudaEventDestroy(pr.second);
+        }
+    for (cudaEvent_t e : ctx->prof_pool) cudaEventDestroy(e);
     cudaStreamDestroy(ctx->stream);
     delete ctx;
     return SLAMGPU_OK;
@@ -228,6 +266,33 @@ int slamgpu_kd_build_host(const float* xy, int n, uint32_t* out_perm)
     std::vector<size_t> idx;
     kd_build_perm(xy, n, idx);
     for (int i = 0; i < n; ++i) out_perm[i] = static_cast<uint32_t>(idx[i]);
+    return SLAMGPU_OK;
+}
+
+int slamgpu_profile_enable(slamgpu_ctx* ctx, int on)
+{
+    SG_CHECK(ctx != nullptr, "null context");
+    ctx->profiling = on != 0;
+    return SLAMGPU_OK;
+}
+
+int slamgpu_profile_read(slamgpu_ctx* ctx, int kernel, double* total_ms, int64_t* launches)
+{
+    SG_CTX(ctx);
+    SG_CHECK(kernel == SLAMGPU_KERNEL_BF_SCAN || kernel == SLAMGPU_KERNEL_PROJ_MATCH, "unknown kernel id");
+    SG_CUDA(cudaStreamSynchronize(ctx->stream));
+    double sum = 0.0;
+    auto& v = ctx->prof_events[kernel];
+    for (auto& pr : v) {
+        float ms = 0.0f;
+        SG_CUDA(cudaEventElapsedTime(&ms, pr.first, pr.second));
+        sum += ms;
+        ctx->prof_pool.push_back(pr.first);
+        ctx->prof_pool.push_back(pr.second);
+    }
+    if (total_ms) *total_ms = sum;
+    if (launches) *launches = static_cast<int64_t>(v.size());
+    v.clear();
     return SLAMGPU_OK;
 }
 

@@ -7,6 +7,7 @@
 #include <cstdio>
 #include <map>
 #include <string>
+#include <utility>
 #include <vector>
 
 #include "slamgpu.h"
@@ -83,6 +84,9 @@ struct slamgpu_ctx {
     slamgpu::Arena d_io;      // device copies of the host-buffer API's inputs and outputs
     slamgpu::Arena h_stage;   // pinned staging
     int64_t launches = 0;
+    bool profiling = false;
+    std::vector<std::pair<cudaEvent_t, cudaEvent_t>> prof_events[2];   // per SLAMGPU_KERNEL_*
+    std::vector<cudaEvent_t> prof_pool;
     std::map<int, slamgpu::FrameDev> frames;
     std::map<int, slamgpu::PointSetDev> point_sets;
 };
@@ -181,6 +185,15 @@ int proj_launch_kd_gather(slamgpu_ctx* ctx, const float2* d_xy, const int32_t* d
 // host-side float helpers that follow the oracle's / Eigen's operation order
 void host_projection_matrix(const float* pose_colmajor, float fx, float fy, float cx, float cy, float* M12);
 void host_camera_center(const float* pose_colmajor, float* C3);
+
+// RAII bracket: records an event pair around a launch when ctx->profiling is on
+struct ProfScope {
+    slamgpu_ctx* ctx;
+    int kernel;
+    cudaEvent_t stop = nullptr;
+    ProfScope(slamgpu_ctx* c, int k);
+    ~ProfScope();
+};
 
 int popc_microbench(slamgpu_ctx* ctx, double* popc_per_s, int* n_sm, double* sm_mhz_est);
 

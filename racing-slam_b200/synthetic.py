@@ -217,3 +217,21 @@ def keyframe_db(n_frames: int, n_desc: int, seed: int, shared_frac: float = 0.3,
         src = rng.choice(len(pool), n_shared, replace=False)
         db[f, rows] = flip_bits(pool[src], rng.integers(0, max_flip + 1, n_shared), rng)
     return db
+
+
+def keyframe_db_fast(n_frames: int, n_desc: int, seed: int, shared_frac: float = 0.3) -> np.ndarray:
+    """Same shape and intent as keyframe_db, cheap enough for the full C5 size (1000 x 4000 x 32 B
+    = 128 MB): shared rows are pool rows XOR a sparse mask (each bit set with probability 1/8,
+    about 32 of 256 bits), so they pass the distance-64 and ratio gates; the rest is uniform."""
+    rng = np.random.default_rng(seed)
+    db = rng.integers(0, 256, (n_frames, n_desc, 32), dtype=np.uint8)
+    pool = rng.integers(0, 256, (max(n_desc, 1), 32), dtype=np.uint8)
+    n_shared = int(shared_frac * n_desc)
+    if n_shared == 0:
+        return db
+    for f in range(n_frames):
+        rows = rng.choice(n_desc, n_shared, replace=False)
+        src = rng.choice(len(pool), n_shared, replace=False)
+        m = rng.integers(0, 256, (3, n_shared, 32), dtype=np.uint8)
+        db[f, rows] = pool[src] ^ (m[0] & m[1] & m[2])
+    return db

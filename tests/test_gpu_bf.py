@@ -1,0 +1,151 @@
+"""GPU parity tests, brute-force family: libslamgpu through its C ABI against
+the cv2 golden vectors and the CPU oracle.  Bit-exact: indices and integer distances."""
+import numpy as np
+import pytest
+
+from conftest import golden, golden_names
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize("name", golden_names("bf_"))
+def test_golden_cv2(ctx, name):
+    g = golden(name)
+    q, t = g["q"], g["t"]
+    idx, dist = ctx.knn2(q, t)
+    assert np.array_equal(idx, g["knn_idx"]) and np.array_equal(dist, g["knn_dist"])
+    ci, cd = ctx.crosscheck(q, t)
+    assert np.array_equal(ci, g["cc_idx"]) and np.array_equal(cd, g["cc_dist"])
+    mq, mt = ctx.match_descriptors(q, t, float(g["max_dist"]), float(g["ratio"]))
+    assert np.array_equal(mq, g["md_query"]) and np.array_equal(mt, g["md_train"])
+    ft, fq = ctx.match_features(t, q, float(g["max_dist"]))
+    assert np.array_equal(ft, g["mf_train"]) and np.array_equal(fq, g["mf_query"])
+
+
+SIZES = [(1, 1), (1, 2), (2, 1), (3, 5), (31, 33), (32, 32), (255, 257), (256, 128), (257, 129), (513, 1000),
+         (1000, 513), (2000, 2000), (2049, 4097), (4000, 4000)]
+
+
+@pytest.mark.parametrize("nq,nt", SIZES)
+@pytest.mark.parametrize("kind", ["correlated", "ties"])
+def test_knn2_and_crosscheck_vs_oracle(ctx, oracle, pkg, nq, nt, kind):
+    gen = pkg.synthetic.bf_correlated if kind == "correlated" else pkg.synthetic.bf_tie_heavy
+    q, t = gen(nq, nt, nq * 7 + nt)
+    idx, dist = ctx.knn2(q, t)
+    oi, od = oracle.knn2(q, t)
+    assert np.array_equal(idx, oi) and np.array_equal(dist, od)
+    ci, cd = ctx.crosscheck(q, t)
+    oi, od = oracle.crosscheck(q, t)
+    assert np.array_equal(ci, oi) and np.array_equal(cd, od)
+
+
+@pytest.mark.parametrize("nq,nt", [(0, 0), (0, 9), (9, 0)])
+def test_empty_sets(ctx, nq, nt):
+    q = np.zeros((nq, 32), np.uint8)
+    t = np.zeros((nt, 32), np.uint8)
+    idx, dist = ctx.knn2(q, t)
+    assert idx.shape == (nq, 2) and (idx == -1).all() and (dist == -1).all()
+    ci, cd = ctx.crosscheck(q, t)
+    assert (ci == -1).all() and (cd == -1).all()
+    assert len(ctx.match_descriptors(q, t)[0]) == 0        # src/MapMatcher.cpp:139-141
+    assert len(ctx.match_features(t, q)[0]) == 0
+
+
+@pytest.mark.parametrize("max_dist,ratio", [(64.0, 0.75), (64.0, 0.8), (50.5, 0.6), (256.0, 1.0), (0.0, 0.75)])
+def test_match_descriptors_filters_vs_oracle(ctx, oracle, pkg, max_dist, ratio):
+    q, t = pkg.synthetic.bf_correlated(1500, 1100, 42, max_flip=90)
+    mq, mt = ctx.match_descriptors(q, t, max_dist, ratio)
+    oq, ot = oracle.match_descriptors(q, t, max_dist, ratio)
+    assert np.array_equal(mq, oq) and np.array_equal(mt, ot)
+    ft, fq = ctx.match_features(t, q, max_dist)
+    o_t, o_q = oracle.match_features(t, q, max_dist)
+    assert np.array_equal(ft, o_t) and np.array_equal(fq, o_q)
+
+
+def test_match_descriptors_single_train_row_uses_k1(ctx, oracle, pkg):
+    q, t = pkg.synthetic.bf_correlated(300, 1, 5, max_flip=20, frac_replaced=0.0)
+    mq, mt = ctx.match_descriptors(q, t)
+    oq, ot = oracle.match_descriptors(q, t)
+    assert np.array_equal(mq, oq) and np.array_equal(mt, ot)
+
+
+def test_full_size_8k_properties(ctx, oracle, pkg):
+    """BASELINE C3 size (8000 x 8000): bit-exact against the oracle, plus size-independent
+    properties -- match_features of a permuted copy recovers the permutation, and the result is
+    invariant under swapping roles (mutuality)."""
+    rng = np.random.default_rng(3)
+    a = rng.integers(0, 256, (8000, 32), dtype=np.uint8)
+    perm = rng.permutation(8000)
+    b = pkg.synthetic.flip_bits(a[perm], rng.integers(0, 20, 8000), rng)
+    tr, qu = ctx.match_features(a, b, 64.0)              # prev = a (train), cur = b (query)
+    assert len(qu) == 8000 and np.array_equal(qu, np.arange(8000)) and np.array_equal(tr, perm)
+    tr2, qu2 = ctx.match_features(b, a, 64.0)            # swapped roles: the same pairs
+    assert {(int(x), int(y)) for x, y in zip(tr, qu)} == {(int(y), int(x)) for x, y in zip(tr2, qu2)}
+    idx, dist = ctx.knn2(b, a)
+    oi, od = oracle.knn2(b, a)
+    assert np.array_equal(idx, oi) and np.array_equal(dist, od)
+    assert (dist[:, 0] <= dist[:, 1]).all()
+
+
+def test_batch_vs_single_and_oracle(ctx, oracle, pkg):
+    """LoopDetector all-pairs form (BASELINE C5 shape, small): ragged frames, every ordered pair."""
+    rng = np.random.default_rng(9)
+    sizes = [300, 0, 257, 1, 640, 33]
+    db = pkg.synthetic.keyframe_db(len(sizes), 640, 9, shared_frac=0.4)
+    frames = [db[i, :n] for i, n in enumerate(sizes)]
+    desc = np.concatenate(frames)
+    off = np.concatenate([[0], np.cumsum(sizes)]).astype(np.int32)
+    pairs = pkg.sharding.all_pairs(len(sizes))
+    pairs = np.concatenate([pairs, pairs[:, ::-1]])       # both directions
+    o, ql, tl = ctx.match_descriptors_batch(desc, off, pairs, 64.0, 0.75)
+    assert o[0] == 0 and o[-1] == len(ql) == len(tl)
+    for k, (fq, ft) in enumerate(pairs):
+        oq, ot = oracle.match_descriptors(frames[fq], frames[ft], 64.0, 0.75)
+        assert np.array_equal(ql[o[k]:o[k + 1]], oq), (k, fq, ft)
+        assert np.array_equal(tl[o[k]:o[k + 1]], ot), (k, fq, ft)
+    assert rng is not None
+
+
+def test_batch_capacity_error(ctx, pkg):
+    db = pkg.synthetic.keyframe_db(3, 128, 1, shared_frac=0.9, max_flip=5)
+    desc = db.reshape(-1, 32)
+    off = np.array([0, 128, 256, 384], np.int32)
+    pairs = pkg.sharding.all_pairs(3)
+    with pytest.raises(pkg.SlamGpuError) as e:
+        ctx.match_descriptors_batch(desc, off, pairs, 64.0, 0.75, capacity=3)
+    assert e.value.code == pkg.binding.ERR_NOMEM
+
+
+def test_device_pointer_forms(ctx, oracle, pkg):
+    import torch
+    q, t = pkg.synthetic.bf_correlated(3000, 2500, 77)
+    dq, dt = torch.from_numpy(q).cuda(), torch.from_numpy(t).cuda()
+    idx = torch.empty((3000, 2), dtype=torch.int32, device="cuda")
+    dist = torch.empty((3000, 2), dtype=torch.int32, device="cuda")
+    torch.cuda.synchronize()
+    ctx.knn2_dev(dq.data_ptr(), 3000, dt.data_ptr(), 2500, idx.data_ptr(), dist.data_ptr())
+    ctx.sync()
+    oi, od = oracle.knn2(q, t)
+    assert np.array_equal(idx.cpu().numpy(), oi) and np.array_equal(dist.cpu().numpy(), od)
+    out_train = torch.empty(3000, dtype=torch.int32, device="cuda")
+    count = torch.zeros(1, dtype=torch.int32, device="cuda")
+    torch.cuda.synchronize()
+    ctx.match_descriptors_dev(dq.data_ptr(), 3000, dt.data_ptr(), 2500, 64.0, 0.75, out_train.data_ptr(),
+                              count.data_ptr())
+    ctx.sync()
+    oq, ot = oracle.match_descriptors(q, t)
+    got = out_train.cpu().numpy()
+    assert int(count.item()) == len(oq)
+    assert np.array_equal(np.nonzero(got >= 0)[0], oq) and np.array_equal(got[got >= 0], ot)
+
+
+def test_errors_are_loud(ctx, pkg):
+    with pytest.raises(pkg.SlamGpuError):
+        ctx.match_projection(12345, 0, 4, np.eye(4, dtype=np.float32).flatten(), pkg.ProjParams(), None, None)
+    lib = pkg.binding.load()
+    assert lib.slamgpu_knn2(ctx._h, None, 4, None, 4, None, None) == pkg.binding.ERR_INVALID
+
+
+def test_popc_microbenchmark_runs(ctx):
+    rate, n_sm, mhz = ctx.bench_popc()
+    assert n_sm >= 100 and rate > 1e12 and 500 < mhz < 2500
