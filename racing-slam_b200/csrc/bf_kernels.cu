@@ -70,32 +70,92 @@ struct ScanArgs {
     uint2* keys;
 };
 
-// 256-bit Hamming distance: 8 x (LOP3 xor + POPC) + adds.
-__device__ __forceinline__ uint32_t hamming256(const uint32_t (&q)[8], const uint4& a, const uint4& b)
+// ---- v2 inner loop -----------------------------------------------------------------------------
+// ncu on v1 (8 POPC per comparison) showed the XU pipe, where POPC issues at 16 lanes/clk/SM, 96 %
+// busy with the ALU pipe at 45 % (profiles/r01_ncu_full_bf_scan_v1.txt).  v2 moves work off XU:
+//   * a carry-save adder tree (LOP3 xor3 / majority) compresses the 8 XOR words to 4 words of
+//     weight 1,1,2,4  ->  4 POPC instead of 8 per comparison, +8 LOP3;
+//   * two query rows share one register as packed 16-bit keys (distance << 7 | index within the
+//     128-row chunk), so the top-2 update is 3 VIMNMX.U16x2 per TWO comparisons; the chunk's
+//     top-2 is widened to the 32-bit (distance << 22 | train index) key once per chunk.
+// Ordering is unchanged: lowest distance, then lowest train index.
+__device__ __forceinline__ uint32_t lop_xor(uint32_t a, uint32_t b)
 {
-    return __popc(q[0] ^ a.x) + __popc(q[1] ^ a.y) + __popc(q[2] ^ a.z) + __popc(q[3] ^ a.w) +
-           __popc(q[4] ^ b.x) + __popc(q[5] ^ b.y) + __popc(q[6] ^ b.z) + __popc(q[7] ^ b.w);
+    uint32_t d;
+    asm("lop3.b32 %0, %1, %2, 0, 0x3c;" : "=r"(d) : "r"(a), "r"(b));
+    return d;
+}
+__device__ __forceinline__ uint32_t lop_xor3(uint32_t a, uint32_t b, uint32_t c)
+{
+    uint32_t d;
+    asm("lop3.b32 %0, %1, %2, %3, 0x96;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+    return d;
+}
+__device__ __forceinline__ uint32_t lop_maj(uint32_t a, uint32_t b, uint32_t c)
+{
+    uint32_t d;
+    asm("lop3.b32 %0, %1, %2, %3, 0xe8;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+    return d;
+}
+__device__ __forceinline__ uint32_t mad_u32(uint32_t a, uint32_t b, uint32_t c)   // IMAD: FMA pipe, not ALU
+{
+    uint32_t d;
+    asm("mad.lo.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+    return d;
 }
 
-template <int R>
-__device__ __forceinline__ void scan_one(const uint4* __restrict__ sm, int j, uint32_t tkey,
-                                         const uint32_t (&q)[R][8], uint32_t (&b0)[R], uint32_t (&b1)[R])
+// 256-bit Hamming distance with 4 POPC: CSA tree over the 8 XOR words.
+__device__ __forceinline__ uint32_t hamming256_csa(const uint32_t (&q)[8], const uint4& a, const uint4& b)
+{
+    const uint32_t x0 = lop_xor(q[0], a.x), x1 = lop_xor(q[1], a.y), x2 = lop_xor(q[2], a.z), x3 = lop_xor(q[3], a.w);
+    const uint32_t x4 = lop_xor(q[4], b.x), x5 = lop_xor(q[5], b.y), x6 = lop_xor(q[6], b.z), x7 = lop_xor(q[7], b.w);
+    const uint32_t s0 = lop_xor3(x0, x1, x2), c0 = lop_maj(x0, x1, x2);
+    const uint32_t s1 = lop_xor3(x3, x4, x5), c1 = lop_maj(x3, x4, x5);
+    const uint32_t s2 = lop_xor3(s0, s1, x6), c2 = lop_maj(s0, s1, x6);   // weight 1: s2, x7
+    const uint32_t t0 = lop_xor3(c0, c1, c2), d0 = lop_maj(c0, c1, c2);   // weight 2: t0; weight 4: d0
+    const uint32_t w1 = mad_u32(__popc(s2), 1u, __popc(x7));
+    const uint32_t w2 = mad_u32(__popc(t0), 2u, w1);
+    return mad_u32(__popc(d0), 4u, w2);
+}
+
+constexpr uint32_t kKey16None = 0xFFFFu;
+
+// one train row against RP pairs of query rows; c0/c1 = packed chunk-local top-2
+template <int RP>
+__device__ __forceinline__ void scan_one(const uint4* __restrict__ sm, int j, const uint32_t (&q)[2 * RP][8],
+                                         uint32_t (&c0)[RP], uint32_t (&c1)[RP])
 {
     const uint4 a = sm[2 * j];      // warp-uniform address -> shared-memory broadcast
     const uint4 b = sm[2 * j + 1];
+    const uint32_t jj = static_cast<uint32_t>(j) * 0x10001u;
 #pragma unroll
-    for (int r = 0; r < R; ++r) {
-        const uint32_t d = hamming256(q[r], a, b);
-        const uint32_t key = (d << kIdxBits) | tkey;
-        const uint32_t hi = max(key, b0[r]);
-        b0[r] = min(key, b0[r]);
-        b1[r] = min(b1[r], hi);
+    for (int p = 0; p < RP; ++p) {
+        const uint32_t dlo = hamming256_csa(q[2 * p], a, b);
+        const uint32_t dhi = hamming256_csa(q[2 * p + 1], a, b);
+        const uint32_t dd = mad_u32(dhi, 65536u, dlo);
+        const uint32_t key = mad_u32(dd, 128u, jj);     // (distance << 7 | j) in both halves
+        const uint32_t hi = __vmaxu2(key, c0[p]);
+        c0[p] = __vminu2(key, c0[p]);
+        c1[p] = __vminu2(c1[p], hi);
     }
 }
 
-template <int R>
+__device__ __forceinline__ uint32_t widen_key(uint32_t k16, uint32_t t0)
+{
+    return k16 == kKey16None ? kKeyNone : (((k16 >> 7) << kIdxBits) | (t0 + (k16 & 127u)));
+}
+
+__device__ __forceinline__ void merge_top2(uint32_t k0, uint32_t k1, uint32_t& b0, uint32_t& b1)
+{
+    const uint32_t hi = max(k0, b0);
+    b0 = min(k0, b0);
+    b1 = min(min(b1, hi), k1);     // k1 >= k0: it can only compete for second place
+}
+
+template <int RP>
 __global__ void __launch_bounds__(kThreads) bf_scan_kernel(const ScanArgs a)
 {
+    constexpr int R = 2 * RP;      // query rows per thread
     __shared__ __align__(128) uint4 s_train[kStages][kChunk * 2];
     __shared__ __align__(8) uint64_t s_full[kStages];
 
@@ -167,11 +227,20 @@ __global__ void __launch_bounds__(kThreads) bf_scan_kernel(const ScanArgs a)
         const int t0 = t_begin + c * kChunk;
         const int cnt = min(kChunk, t_end - t0);
         const uint4* sm = &s_train[s][0];
+        uint32_t c0[RP], c1[RP];
+#pragma unroll
+        for (int p = 0; p < RP; ++p) c0[p] = c1[p] = 0xFFFFFFFFu;
         if (cnt == kChunk) {
-#pragma unroll 4
-            for (int j = 0; j < kChunk; ++j) scan_one<R>(sm, j, static_cast<uint32_t>(t0 + j), q, b0, b1);
+#pragma unroll 2
+            for (int j = 0; j < kChunk; ++j) scan_one<RP>(sm, j, q, c0, c1);
         } else {
-            for (int j = 0; j < cnt; ++j) scan_one<R>(sm, j, static_cast<uint32_t>(t0 + j), q, b0, b1);
+            for (int j = 0; j < cnt; ++j) scan_one<RP>(sm, j, q, c0, c1);
+        }
+        // widen the chunk's packed top-2 and fold it into the running 32-bit keys
+#pragma unroll
+        for (int p = 0; p < RP; ++p) {
+            merge_top2(widen_key(c0[p] & 0xFFFFu, t0), widen_key(c1[p] & 0xFFFFu, t0), b0[2 * p], b1[2 * p]);
+            merge_top2(widen_key(c0[p] >> 16, t0), widen_key(c1[p] >> 16, t0), b0[2 * p + 1], b1[2 * p + 1]);
         }
         __syncthreads();
     }
@@ -358,8 +427,9 @@ BfPlan bf_make_plan(int n_sm, int nq_max, int nt_max, int64_t n_pairs)
 {
     BfPlan p;
     const int64_t target = static_cast<int64_t>(n_sm) * 4;   // ~32 resident warps per SM
-    const int64_t work_r2 = ((nq_max + 511) / 512) * static_cast<int64_t>((nt_max + kChunk - 1) / kChunk) * n_pairs;
-    p.r = work_r2 >= target ? 2 : 1;
+    // 4 query rows per thread when that still leaves enough CTAs to fill the machine, else 2
+    const int64_t work_r4 = ((nq_max + 1023) / 1024) * static_cast<int64_t>((nt_max + kChunk - 1) / kChunk) * n_pairs;
+    p.r = work_r4 >= target ? 4 : 2;
     p.tile = kThreads * p.r;
     p.tiles = max(1, (nq_max + p.tile - 1) / p.tile);
     const int64_t ctas_no_split = static_cast<int64_t>(p.tiles) * n_pairs;
@@ -400,7 +470,7 @@ int bf_launch_scan(slamgpu_ctx* ctx, const BfPlan& plan, const uint8_t* d_query,
     SG_CHECK(n_ctas < (int64_t(1) << 31), "brute-force grid too large; split the pair list");
     const dim3 grid(static_cast<unsigned>(n_ctas));
     ProfScope prof(ctx, SLAMGPU_KERNEL_BF_SCAN);
-    if (plan.r == 2) {
+    if (plan.r == 4) {
         bf_scan_kernel<2><<<grid, kThreads, 0, ctx->stream>>>(a);
     } else {
         bf_scan_kernel<1><<<grid, kThreads, 0, ctx->stream>>>(a);
