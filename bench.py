@@ -473,6 +473,26 @@ def also_measurements(ctx, pkg, torch, stream, n_sm, peaks):
                                    "popc8_roofline_frac_call": g_call / peak, "popc8_roofline_frac_kernel": g_kernel / peak,
                                    "int_roofline_frac_kernel": g_kernel / ipeak,
                                    "l2": "flushed (256 MiB fill) before every call"}
+    # C3 frame-to-frame: 8000 x 8000 cross-check (match_features), host buffers, copies inside
+    prev = rng.integers(0, 256, (8000, 32), dtype=np.uint8)
+    cur = syn.next_frame_descriptors(prev, 33)
+    s = wall(lambda: ctx.match_features(prev, cur, MAX_DIST), 30)
+    out["c3_match_features_8000x8000"] = {"us_per_call": s * 1e6, "frames_per_s": 1.0 / s, "gcmp_s": 64e6 / s / 1e9,
+                                          "copies": "inside", "note": "one fused scan: row top-1 + column minima"}
+    ci = torch.empty(8000, dtype=torch.int32, device="cuda")
+    cd = torch.empty(8000, dtype=torch.int32, device="cuda")
+    tot = 0.0
+    for it in range(23):
+        flush.fill_(1)
+        torch.cuda.synchronize()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record(stream)
+        ctx.crosscheck_dev(dq.data_ptr(), 8000, dt.data_ptr(), 8000, ci.data_ptr(), cd.data_ptr())
+        b.record(stream)
+        torch.cuda.synchronize()
+        if it >= 3:
+            tot += a.elapsed_time(b)
+    out["crosscheck_8000x8000_device"] = {"us_per_call": tot / 20 * 1e3, "gcmp_s": 64e6 / (tot / 20 * 1e-3) / 1e9}
     del flush
 
     # C2: resident frame + point set; per frame: pose in, proposals out
@@ -522,6 +542,8 @@ def also_measurements(ctx, pkg, torch, stream, n_sm, peaks):
 def main():
     args = parse_args()
     rank, local_rank, world = dist_env()
+    # torchrun exports OMP_NUM_THREADS=1; the CPU arm is meant to use every host core
+    os.environ["OMP_NUM_THREADS"] = str(os.cpu_count() or 1)
     if args.impl == "reference":
         run_reference(args, rank, world)
     else:

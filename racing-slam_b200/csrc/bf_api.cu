@@ -61,16 +61,16 @@ int crosscheck_core(slamgpu_ctx* ctx, const uint8_t* dq, int nq, const uint8_t* 
         SG_CUDA(cudaMemsetAsync(d_dist, 0xFF, sizeof(int32_t) * nq, ctx->stream));
         return SLAMGPU_OK;
     }
+    // one scan: per-row top-1 partials and, in the same pass, per-column minima (atomicMin)
     const BfPlan row = bf_make_plan(ctx->n_sm, nq, nt, 1);
-    const BfPlan col = bf_make_plan(ctx->n_sm, nt, nq, 1);
-    const size_t n_row = bf_partial_elems(row, 1, nq), n_col = bf_partial_elems(col, 1, nt);
-    SG_TRY(ensure_device_ws(ctx, Carver::padded(n_row * sizeof(uint2)) + Carver::padded(n_col * sizeof(uint2))));
+    const size_t n_row = bf_partial_elems(row, 1, nq);
+    SG_TRY(ensure_device_ws(ctx, Carver::padded(n_row * sizeof(uint2)) + Carver::padded(sizeof(uint32_t) * nt)));
     Carver ws(ctx->d_ws.ptr);
     uint2* row_keys = ws.take<uint2>(n_row);
-    uint2* col_keys = ws.take<uint2>(n_col);
-    SG_TRY(bf_launch_scan(ctx, row, dq, nq, dt, nt, nullptr, nullptr, 1, nq, false, row_keys));
-    SG_TRY(bf_launch_scan(ctx, col, dt, nt, dq, nq, nullptr, nullptr, 1, nt, false, col_keys));
-    return bf_launch_mutual(ctx, row, row_keys, nq, col, col_keys, nt, nq, nt, strict_max_dist, d_idx, d_dist);
+    uint32_t* col_keys = ws.take<uint32_t>(nt);
+    SG_CUDA(cudaMemsetAsync(col_keys, 0xFF, sizeof(uint32_t) * nt, ctx->stream));
+    SG_TRY(bf_launch_scan(ctx, row, dq, nq, dt, nt, nullptr, nullptr, 1, nq, false, row_keys, col_keys));
+    return bf_launch_mutual_direct(ctx, row, row_keys, nq, col_keys, nq, strict_max_dist, d_idx, d_dist);
 }
 
 int match_descriptors_core(slamgpu_ctx* ctx, const uint8_t* dq, int nq, const uint8_t* dt, int nt, float max_dist,

@@ -68,6 +68,7 @@ struct ScanArgs {
     int max_rows;                 // row stride of the key array per (pair, split)
     int swap_roles;               // batched only: scan pair as (train_frame, query_frame)
     uint2* keys;
+    uint32_t* col_keys;           // cross-check (single pair): per train row min over query rows of (distance << 22 | query)
 };
 
 // ---- v2 inner loop -----------------------------------------------------------------------------
@@ -121,22 +122,31 @@ __device__ __forceinline__ uint32_t hamming256_csa(const uint32_t (&q)[8], const
 constexpr uint32_t kKey16None = 0xFFFFu;
 
 // one train row against RP pairs of query rows; c0/c1 = packed chunk-local top-2
-template <int RP>
+template <int RP, bool COLS>
 __device__ __forceinline__ void scan_one(const uint4* __restrict__ sm, int j, const uint32_t (&q)[2 * RP][8],
-                                         uint32_t (&c0)[RP], uint32_t (&c1)[RP])
+                                         uint32_t (&c0)[RP], uint32_t (&c1)[RP], const uint32_t (&rowid)[2 * RP],
+                                         uint32_t* s_col)
 {
     const uint4 a = sm[2 * j];      // warp-uniform address -> shared-memory broadcast
     const uint4 b = sm[2 * j + 1];
     const uint32_t jj = static_cast<uint32_t>(j) * 0x10001u;
+    uint32_t ck = kKeyNone;
 #pragma unroll
     for (int p = 0; p < RP; ++p) {
         const uint32_t dlo = hamming256_csa(q[2 * p], a, b);
         const uint32_t dhi = hamming256_csa(q[2 * p + 1], a, b);
+        if constexpr (COLS) {       // column minimum for the cross-check, same pass
+            ck = min(ck, min(mad_u32(dlo, 1u << kIdxBits, rowid[2 * p]), mad_u32(dhi, 1u << kIdxBits, rowid[2 * p + 1])));
+        }
         const uint32_t dd = mad_u32(dhi, 65536u, dlo);
         const uint32_t key = mad_u32(dd, 128u, jj);     // (distance << 7 | j) in both halves
         const uint32_t hi = __vmaxu2(key, c0[p]);
         c0[p] = __vminu2(key, c0[p]);
         c1[p] = __vminu2(c1[p], hi);
+    }
+    if constexpr (COLS) {
+        ck = __reduce_min_sync(0xFFFFFFFFu, ck);            // REDUX over the warp's 32 x 2RP query rows
+        if ((threadIdx.x & 31) == 0) atomicMin(&s_col[j], ck);
     }
 }
 
@@ -152,12 +162,13 @@ __device__ __forceinline__ void merge_top2(uint32_t k0, uint32_t k1, uint32_t& b
     b1 = min(min(b1, hi), k1);     // k1 >= k0: it can only compete for second place
 }
 
-template <int RP>
+template <int RP, bool COLS>
 __global__ void __launch_bounds__(kThreads) bf_scan_kernel(const ScanArgs a)
 {
     constexpr int R = 2 * RP;      // query rows per thread
     __shared__ __align__(128) uint4 s_train[kStages][kChunk * 2];
     __shared__ __align__(8) uint64_t s_full[kStages];
+    __shared__ uint32_t s_col[COLS ? 2 : 1][kChunk];   // per-chunk column minima, double-buffered
 
     const int tid = threadIdx.x;
     int bid = blockIdx.x;
@@ -192,6 +203,9 @@ __global__ void __launch_bounds__(kThreads) bf_scan_kernel(const ScanArgs a)
         for (int s = 0; s < kStages; ++s) mbar_init(&s_full[s], 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
+    if constexpr (COLS) {
+        s_col[tid >> 7][tid & (kChunk - 1)] = kKeyNone;     // kThreads = 2 x kChunk
+    }
     __syncthreads();
 
     auto issue = [&](int c) {
@@ -208,8 +222,12 @@ __global__ void __launch_bounds__(kThreads) bf_scan_kernel(const ScanArgs a)
     // query rows live in registers: R x 8 words per thread, rows tile-strided so loads coalesce
     uint32_t q[R][8];
     uint32_t b0[R], b1[R];
+    uint32_t rowid[R];
 #pragma unroll
     for (int r = 0; r < R; ++r) {
+        // rows past the end are clamped copies of the last row: with the largest index they can
+        // never beat the real row in a column minimum
+        rowid[r] = row0 + r * kThreads + tid < nq ? static_cast<uint32_t>(row0 + r * kThreads + tid) : kIdxMask;
         const int row = min(row0 + r * kThreads + tid, nq - 1);
         const uint4* src = reinterpret_cast<const uint4*>(qp + static_cast<size_t>(row) * 32);
         const uint4 lo = __ldg(src), hi = __ldg(src + 1);
@@ -230,11 +248,12 @@ __global__ void __launch_bounds__(kThreads) bf_scan_kernel(const ScanArgs a)
         uint32_t c0[RP], c1[RP];
 #pragma unroll
         for (int p = 0; p < RP; ++p) c0[p] = c1[p] = 0xFFFFFFFFu;
+        uint32_t* col = s_col[COLS ? (c & 1) : 0];
         if (cnt == kChunk) {
 #pragma unroll 2
-            for (int j = 0; j < kChunk; ++j) scan_one<RP>(sm, j, q, c0, c1);
+            for (int j = 0; j < kChunk; ++j) scan_one<RP, COLS>(sm, j, q, c0, c1, rowid, col);
         } else {
-            for (int j = 0; j < cnt; ++j) scan_one<RP>(sm, j, q, c0, c1);
+            for (int j = 0; j < cnt; ++j) scan_one<RP, COLS>(sm, j, q, c0, c1, rowid, col);
         }
         // widen the chunk's packed top-2 and fold it into the running 32-bit keys
 #pragma unroll
@@ -243,6 +262,15 @@ __global__ void __launch_bounds__(kThreads) bf_scan_kernel(const ScanArgs a)
             merge_top2(widen_key(c0[p] >> 16, t0), widen_key(c1[p] >> 16, t0), b0[2 * p + 1], b1[2 * p + 1]);
         }
         __syncthreads();
+        if constexpr (COLS) {
+            // flush this chunk's column minima; the buffer is next written in chunk c + 2, after the
+            // __syncthreads that ends chunk c + 1
+            if (tid < cnt) {
+                const uint32_t v = col[tid];
+                col[tid] = kKeyNone;
+                if (v != kKeyNone) atomicMin(&a.col_keys[t0 + tid], v);
+            }
+        }
     }
 
     uint2* out = a.keys + (static_cast<size_t>(pair) * a.splits + split) * a.max_rows;
@@ -352,6 +380,30 @@ __global__ void bf_mutual_kernel(const uint2* row_keys, int row_splits, int row_
     dist[q] = od;
 }
 
+// same, with the column minima produced by the fused scan (one key per train row, no splits)
+__global__ void bf_mutual_direct_kernel(const uint2* row_keys, int row_splits, int row_stride,
+                                        const uint32_t* col_keys, int nq, float strict_max_dist, int32_t* idx,
+                                        int32_t* dist)
+{
+    const int q = blockIdx.x * blockDim.x + threadIdx.x;
+    if (q >= nq) return;
+    const uint2 m = merge_partials(row_keys + q, row_splits, row_stride);
+    int oi = -1, od = -1;
+    if (m.x != kKeyNone) {
+        const int t = static_cast<int>(m.x & kIdxMask);
+        const uint32_t c = col_keys[t];
+        if (c != kKeyNone && static_cast<int>(c & kIdxMask) == q) {
+            const int d = static_cast<int>(m.x >> kIdxBits);
+            if (strict_max_dist < 0.0f || static_cast<float>(d) < strict_max_dist) {
+                oi = t;
+                od = d;
+            }
+        }
+    }
+    idx[q] = oi;
+    dist[q] = od;
+}
+
 // exclusive scan of per-pair counts (single CTA; n is at most a few hundred thousand)
 __global__ void bf_scan_counts_kernel(const int32_t* count, int n, int32_t* offset)
 {
@@ -450,7 +502,7 @@ size_t bf_partial_elems(const BfPlan& p, int64_t n_pairs, int max_rows)
 
 int bf_launch_scan(slamgpu_ctx* ctx, const BfPlan& plan, const uint8_t* d_query, int nq, const uint8_t* d_train,
                    int nt, const int32_t* d_frame_offset, const int32_t* d_pairs, int n_pairs, int max_rows,
-                   bool swap_roles, uint2* d_keys)
+                   bool swap_roles, uint2* d_keys, uint32_t* d_col_keys)
 {
     ScanArgs a;
     a.q_base = d_query;
@@ -465,15 +517,23 @@ int bf_launch_scan(slamgpu_ctx* ctx, const BfPlan& plan, const uint8_t* d_query,
     a.max_rows = max_rows;
     a.swap_roles = swap_roles ? 1 : 0;
     a.keys = d_keys;
+    a.col_keys = d_col_keys;
+    SG_CHECK(d_col_keys == nullptr || d_pairs == nullptr, "fused column minima are for single-pair scans");
     const int64_t n_ctas = static_cast<int64_t>(plan.tiles) * plan.splits * n_pairs;
     if (n_ctas <= 0) return SLAMGPU_OK;
     SG_CHECK(n_ctas < (int64_t(1) << 31), "brute-force grid too large; split the pair list");
     const dim3 grid(static_cast<unsigned>(n_ctas));
     ProfScope prof(ctx, SLAMGPU_KERNEL_BF_SCAN);
-    if (plan.r == 4) {
-        bf_scan_kernel<2><<<grid, kThreads, 0, ctx->stream>>>(a);
+    if (d_col_keys != nullptr) {
+        if (plan.r == 4) {
+            bf_scan_kernel<2, true><<<grid, kThreads, 0, ctx->stream>>>(a);
+        } else {
+            bf_scan_kernel<1, true><<<grid, kThreads, 0, ctx->stream>>>(a);
+        }
+    } else if (plan.r == 4) {
+        bf_scan_kernel<2, false><<<grid, kThreads, 0, ctx->stream>>>(a);
     } else {
-        bf_scan_kernel<1><<<grid, kThreads, 0, ctx->stream>>>(a);
+        bf_scan_kernel<1, false><<<grid, kThreads, 0, ctx->stream>>>(a);
     }
     ctx->launches++;
     SG_CUDA(cudaGetLastError());
@@ -533,6 +593,17 @@ int bf_launch_mutual(slamgpu_ctx* ctx, const BfPlan& row_plan, const uint2* d_ro
     bf_mutual_kernel<<<(nq + 255) / 256, 256, 0, ctx->stream>>>(d_row_keys, row_plan.splits, row_stride, d_col_keys,
                                                                  col_plan.splits, col_stride, nq, strict_max_dist,
                                                                  d_idx, d_dist);
+    ctx->launches++;
+    SG_CUDA(cudaGetLastError());
+    return SLAMGPU_OK;
+}
+
+int bf_launch_mutual_direct(slamgpu_ctx* ctx, const BfPlan& row_plan, const uint2* d_row_keys, int row_stride,
+                            const uint32_t* d_col_keys, int nq, float strict_max_dist, int32_t* d_idx, int32_t* d_dist)
+{
+    if (nq <= 0) return SLAMGPU_OK;
+    bf_mutual_direct_kernel<<<(nq + 255) / 256, 256, 0, ctx->stream>>>(d_row_keys, row_plan.splits, row_stride,
+                                                                        d_col_keys, nq, strict_max_dist, d_idx, d_dist);
     ctx->launches++;
     SG_CUDA(cudaGetLastError());
     return SLAMGPU_OK;

@@ -126,7 +126,7 @@ size_t bf_partial_elems(const BfPlan& p, int64_t n_pairs, int max_rows);
 // Scan: partial top-2 keys[(pair*splits + split)*max_rows + q] for every query row.
 int bf_launch_scan(slamgpu_ctx* ctx, const BfPlan& plan, const uint8_t* d_query, int nq, const uint8_t* d_train,
                    int nt, const int32_t* d_frame_offset, const int32_t* d_pairs, int n_pairs, int max_rows,
-                   bool swap_roles, uint2* d_keys);
+                   bool swap_roles, uint2* d_keys, uint32_t* d_col_keys = nullptr);
 // Finish, raw: merged top-2 -> idx/dist [nq x 2].
 int bf_launch_finish_raw(slamgpu_ctx* ctx, const BfPlan& plan, const uint2* d_keys, int nq, int nt, int max_rows,
                          int32_t* d_idx, int32_t* d_dist);
@@ -138,6 +138,9 @@ int bf_launch_finish_filter(slamgpu_ctx* ctx, const BfPlan& plan, const uint2* d
 int bf_launch_mutual(slamgpu_ctx* ctx, const BfPlan& row_plan, const uint2* d_row_keys, int row_stride,
                      const BfPlan& col_plan, const uint2* d_col_keys, int col_stride, int nq, int nt,
                      float strict_max_dist, int32_t* d_idx, int32_t* d_dist);
+// Cross-check mutuality with the column minima of the fused scan (d_col_keys[nt]).
+int bf_launch_mutual_direct(slamgpu_ctx* ctx, const BfPlan& row_plan, const uint2* d_row_keys, int row_stride,
+                            const uint32_t* d_col_keys, int nq, float strict_max_dist, int32_t* d_idx, int32_t* d_dist);
 // Ordered compaction of out_train[pair][q] into (query, train) lists.
 int bf_launch_scan_counts(slamgpu_ctx* ctx, const int32_t* d_count, int n, int32_t* d_offset /* n+1 */);
 int bf_launch_compact(slamgpu_ctx* ctx, const int32_t* d_out_train, const int32_t* d_frame_offset,
