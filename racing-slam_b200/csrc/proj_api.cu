@@ -83,6 +83,13 @@ void fill_frame(ProjFrameArgs& f, const FrameDev& fd, const float* pose, const s
     f.matched = fd.matched;
     f.xy = fd.xy;
     f.proposals = fd.proposals;
+    f.cell_start = fd.cell_start;
+    f.cell_items = fd.cell_items;
+    f.gx0 = fd.gx0;
+    f.gy0 = fd.gy0;
+    f.inv_cell = fd.inv_cell;
+    f.gw = fd.gw;
+    f.gh = fd.gh;
     f.skip = nullptr;
     f.out_point = nullptr;
     f.out_dist = nullptr;
@@ -259,11 +266,36 @@ int slamgpu_frame_upload(slamgpu_ctx* ctx, int frame_id, int nkp, const float* x
     f.nkp = nkp;
     f.perm_host = perm;
     const size_t n = static_cast<size_t>(nkp);
-    // device blob: [kd_xy][kd_idx][desc][matched][xy] (uploaded) then [proposals] (device only)
+
+    // uniform grid over the keypoints' bounding box: 32 px cells (coarser when that would exceed 1 Mi cells)
+    float cell = 32.0f;
+    if (nkp > 0) {
+        float x0 = xy[0], x1 = xy[0], y0 = xy[1], y1 = xy[1];
+        for (int i = 0; i < nkp; ++i) {
+            SG_CHECK(std::isfinite(xy[2 * i]) && std::isfinite(xy[2 * i + 1]), "non-finite keypoint coordinate");
+            x0 = std::min(x0, xy[2 * i]); x1 = std::max(x1, xy[2 * i]);
+            y0 = std::min(y0, xy[2 * i + 1]); y1 = std::max(y1, xy[2 * i + 1]);
+        }
+        f.gx0 = x0;
+        f.gy0 = y0;
+        for (;;) {
+            const double gw = std::floor((double(x1) - x0) / cell) + 1.0, gh = std::floor((double(y1) - y0) / cell) + 1.0;
+            if (gw * gh <= double(1 << 20)) {
+                f.gw = static_cast<int>(gw);
+                f.gh = static_cast<int>(gh);
+                break;
+            }
+            cell *= 2.0f;
+        }
+        f.inv_cell = 1.0f / cell;
+    }
+    const size_t n_cells = static_cast<size_t>(f.gw) * f.gh;
+    // device blob: [kd_xy][kd_idx][desc][matched][xy][cell_start][cell_items] (uploaded) then [proposals] (device only)
     const size_t b_kdxy = Carver::padded(n * sizeof(float2)), b_kdidx = Carver::padded(n * sizeof(int32_t)),
                  b_desc = Carver::padded(n * 32), b_matched = Carver::padded(n), b_xy = Carver::padded(n * sizeof(float2)),
+                 b_cstart = Carver::padded((n_cells + 1) * sizeof(int32_t)), b_citems = Carver::padded(n * sizeof(int32_t)),
                  b_prop = Carver::padded(n * sizeof(unsigned long long));
-    const size_t up = b_kdxy + b_kdidx + b_desc + b_matched + b_xy;
+    const size_t up = b_kdxy + b_kdidx + b_desc + b_matched + b_xy + b_cstart + b_citems;
     const size_t total = up + b_prop + 256;
     const cudaError_t e = cudaMalloc(&f.blob, total);
     if (e != cudaSuccess) {
@@ -276,6 +308,8 @@ int slamgpu_frame_upload(slamgpu_ctx* ctx, int frame_id, int nkp, const float* x
     f.desc = dv.take<uint4>(2 * n);
     f.matched = dv.take<uint8_t>(n);
     f.xy = dv.take<float2>(n);
+    f.cell_start = dv.take<int32_t>(n_cells + 1);
+    f.cell_items = dv.take<int32_t>(n);
     f.proposals = dv.take<unsigned long long>(n);
 
     if (nkp > 0) {
@@ -305,6 +339,24 @@ int slamgpu_frame_upload(slamgpu_ctx* ctx, int frame_id, int nkp, const float* x
             std::memset(h_matched, 0, n);
         }
         std::memcpy(h_xy, xy, n * sizeof(float2));
+        // counting sort of the KD positions by cell; the device maps coordinates to cells with the
+        // same float expression (proj_kernels.cu: grid_cell), and both are monotone in the coordinate
+        int32_t* h_cstart = hv.take<int32_t>(n_cells + 1);
+        int32_t* h_citems = hv.take<int32_t>(n);
+        std::memset(h_cstart, 0, (n_cells + 1) * sizeof(int32_t));
+        auto cell_of = [&](float x, float y) {
+            int cxi = static_cast<int>(std::floor((x - f.gx0) * f.inv_cell));
+            int cyi = static_cast<int>(std::floor((y - f.gy0) * f.inv_cell));
+            cxi = std::min(std::max(cxi, 0), f.gw - 1);
+            cyi = std::min(std::max(cyi, 0), f.gh - 1);
+            return static_cast<size_t>(cyi) * f.gw + cxi;
+        };
+        for (size_t m = 0; m < n; ++m) h_cstart[cell_of(h_kdxy[2 * m], h_kdxy[2 * m + 1]) + 1]++;
+        for (size_t c = 0; c < n_cells; ++c) h_cstart[c + 1] += h_cstart[c];
+        {
+            std::vector<int32_t> cursor(h_cstart, h_cstart + n_cells);
+            for (size_t m = 0; m < n; ++m) h_citems[cursor[cell_of(h_kdxy[2 * m], h_kdxy[2 * m + 1])]++] = static_cast<int32_t>(m);
+        }
         SG_CUDA(cudaMemcpyAsync(f.blob, ctx->h_stage.ptr, up, cudaMemcpyHostToDevice, ctx->stream));
         SG_CUDA(cudaMemsetAsync(f.proposals, 0xFF, n * sizeof(unsigned long long), ctx->stream));
         // the staging buffer is reused by the next call: wait for the copy out of it

@@ -181,6 +181,169 @@ __global__ void __launch_bounds__(kProjThreads) proj_match_kernel(const ProjKern
     }
 }
 
+// ---------------------------------------------------------------------------------------------
+// K4, warp-per-point form (default).  ncu on the thread-per-point kernel above showed 5.4 of 32
+// lanes active per instruction (every lane walks its own KD path) and 2 warps per SM
+// (profiles/r01_ncu_proj_match_walk.txt).  Here one WARP owns one visited point:
+//   * projection and gates are warp-uniform;
+//   * candidates come from the frame's uniform grid (the cells the radius box touches are
+//     contiguous per cell row), one candidate per lane, tested with the reference's own float
+//     expression dx*dx + dy*dy <= r*r (src/KDTree.cpp:61-67) -- a KD radius search is exact, so
+//     the candidate SET is the same;
+//   * each lane takes the Hamming minimum of its candidate over the point's observations
+//     (observation rows are warp-uniform loads);
+//   * the winner is the minimum distance; ties are broken by the KD VISIT ORDER, recovered from
+//     the tree itself: the path root -> candidate, one symbol per level (0 = the node itself,
+//     1 = near child, 2 = far child, near/far decided by the sign of delta exactly as in
+//     src/KDTree.cpp:69-76), compared lexicographically = pre-order "node, near subtree, far
+//     subtree" = the order radius_search pushes results, so the strict '<' of
+//     src/MapMatcher.cpp:88 keeps the same candidate.  Keys are only computed on ties.
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ unsigned long long kd_visit_key(const float2* __restrict__ kd_xy, int n, int m, float u,
+                                                           float w)
+{
+    unsigned long long key = 0;
+    int s = 0, e = n, depth = 0;
+    while (s < e && depth < 31) {
+        const int mid = (s + e) >> 1;
+        if (mid == m) break;                                     // symbol 0 and all-zero tail
+        const float2 p = kd_xy[mid];
+        const float delta = (depth & 1) ? __fsub_rn(p.y, w) : __fsub_rn(p.x, u);   // src/KDTree.cpp:61-62,69-70
+        const bool left_near = delta > 0.0f;                     // :73
+        const bool go_left = m < mid;
+        key |= static_cast<unsigned long long>(go_left == left_near ? 1 : 2) << (62 - 2 * depth);
+        if (go_left) e = mid; else s = mid + 1;
+        depth++;
+    }
+    return key;
+}
+
+__device__ __forceinline__ int grid_cell(float x, float x0, float inv_cell, int n)
+{
+    const int c = static_cast<int>(floorf(__fmul_rn(__fsub_rn(x, x0), inv_cell)));
+    return min(max(c, 0), n - 1);
+}
+
+constexpr int kGroupThreads = 128;
+
+// LANES = 32: one warp per point (small calls: latency).  LANES = 8: four points per warp (large
+// batches: fewer idle lanes).  All collectives carry the group's lane mask.
+template <int LANES>
+__global__ void __launch_bounds__(kGroupThreads) proj_match_warp_kernel(const ProjKernelArgs a)
+{
+    const ProjFrameArgs& f = a.frames ? a.frames[blockIdx.y] : a.inline_frame;
+    const ProjCommonArgs& c = a.c;
+    const int lane = threadIdx.x % LANES;
+    const unsigned gmask = LANES == 32 ? 0xFFFFFFFFu : (((1u << LANES) - 1u) << ((threadIdx.x & 31) / LANES * LANES));
+    const int v = blockIdx.x * (kGroupThreads / LANES) + threadIdx.x / LANES;
+    if (v >= c.n_visit) return;
+    const size_t dbg_row = static_cast<size_t>(blockIdx.y) * c.n_visit + v;
+
+    const int pi = c.order ? c.order[v] : v;
+    if (pi < 0) return;                               // match_for_fuse nullptr, src/MapMatcher.cpp:119-121
+    if (f.skip && f.skip[pi]) return;                 // :53 is_matched(point) / :169 !is_observed_by
+
+    const float X[3] = {c.pos[3 * pi], c.pos[3 * pi + 1], c.pos[3 * pi + 2]};
+    float h[3];
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {                     // P1, same order as the kernel above
+        h[i] = sum3(__fmul_rn(f.M[4 * i], X[0]), __fmul_rn(f.M[4 * i + 1], X[1]), __fmul_rn(f.M[4 * i + 2], X[2]));
+        h[i] = __fadd_rn(h[i], f.M[4 * i + 3]);
+    }
+    float u, w;
+    if (h[2] < 0.0f) {
+        u = -1.0f; w = -1.0f;
+    } else {
+        u = __fdiv_rn(h[0], h[2]);
+        w = __fdiv_rn(h[1], h[2]);
+    }
+    if (c.dbg_uv && lane == 0) {
+        c.dbg_uv[2 * dbg_row] = u;
+        c.dbg_uv[2 * dbg_row + 1] = w;
+    }
+    if (!(u >= 0.0f && u < c.width_f && w >= 0.0f && w < c.height_f)) return;      // P2
+    if (c.stats && lane == 0) {
+        if (fabsf(u) < 1e-4f || fabsf(__fsub_rn(u, c.width_f)) < 1e-4f || fabsf(w) < 1e-4f ||
+            fabsf(__fsub_rn(w, c.height_f)) < 1e-4f)
+            atomicAdd(&c.stats[0], 1ull);
+    }
+    const float ray[3] = {__fsub_rn(X[0], f.C[0]), __fsub_rn(X[1], f.C[1]), __fsub_rn(X[2], f.C[2])};
+    float rn[3];
+    normalized3(ray, rn);
+    const float nx = c.normal[3 * pi], ny = c.normal[3 * pi + 1], nz = c.normal[3 * pi + 2];
+    if (sum3(__fmul_rn(nx, rn[0]), __fmul_rn(ny, rn[1]), __fmul_rn(nz, rn[2])) < c.min_cos) return;   // P3
+    const float nearest = c.range[2 * pi], furthest = c.range[2 * pi + 1];
+    const float distance = norm3(ray);
+    if (distance < __fdiv_rn(nearest, c.nearer) || distance > __fmul_rn(furthest, c.further)) return;  // P4
+
+    if (c.stats) {   // diagnostic only: keypoints within 1e-4 px of the search radius
+        unsigned long long cnt = 0;
+        for (int k = lane; k < f.nkp; k += LANES) {
+            const float2 p = f.xy[k];
+            const float dx = __fsub_rn(p.x, u), dy = __fsub_rn(p.y, w);
+            const float d = __fsqrt_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)));
+            if (fabsf(__fsub_rn(d, c.radius)) < 1e-4f) cnt++;
+        }
+        if (cnt) atomicAdd(&c.stats[1], cnt);
+    }
+
+    // P5 + P6: candidates from the grid, one per lane
+    const int o_begin = c.obs_offset[pi], o_end = c.obs_offset[pi + 1];
+    const float pad = c.radius + 1.0f;                           // conservative box; the exact test is d2 <= r2
+    const int cx0 = grid_cell(u - pad, f.gx0, f.inv_cell, f.gw), cx1 = grid_cell(u + pad, f.gx0, f.inv_cell, f.gw);
+    const int cy0 = grid_cell(w - pad, f.gy0, f.inv_cell, f.gh), cy1 = grid_cell(w + pad, f.gy0, f.inv_cell, f.gh);
+    int best = c.thr;                                            // lane-local best: accept d < thr
+    int best_m = -1;
+    for (int cy = cy0; cy <= cy1; ++cy) {
+        const int i_begin = f.cell_start[cy * f.gw + cx0], i_end = f.cell_start[cy * f.gw + cx1 + 1];
+        for (int i = i_begin + lane; i < i_end; i += LANES) {
+            const int m = f.cell_items[i];
+            const float2 p = f.kd_xy[m];
+            const float dx = __fsub_rn(p.x, u);                  // src/KDTree.cpp:61
+            const float dy = __fsub_rn(p.y, w);                  // :62
+            const float d2 = __fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy));   // :63
+            if (!(d2 <= c.r2)) continue;                         // :65
+            const int kp = f.kd_idx[m];
+            if (!c.replace && f.matched[kp]) continue;           // src/MapMatcher.cpp:81
+            const uint4 a0 = __ldg(&f.desc[2 * kp]), a1 = __ldg(&f.desc[2 * kp + 1]);
+            int dmin = 1 << 20;
+            for (int o = o_begin; o < o_end; ++o) {              // :86
+                const uint4 b0 = __ldg(&c.obs_desc[2 * static_cast<size_t>(o)]);
+                const uint4 b1 = __ldg(&c.obs_desc[2 * static_cast<size_t>(o) + 1]);
+                dmin = min(dmin, hamming256(a0, a1, b0, b1));
+            }
+            if (dmin < best) {
+                best = dmin;
+                best_m = m;
+            } else if (dmin == best && best_m >= 0) {            // tie inside one lane: earlier visit wins
+                if (kd_visit_key(f.kd_xy, f.nkp, m, u, w) < kd_visit_key(f.kd_xy, f.nkp, best_m, u, w)) best_m = m;
+            }
+        }
+    }
+    // warp winner: minimum distance, then earliest KD visit
+    const int wbest = __reduce_min_sync(gmask, best_m >= 0 ? best : (1 << 20));
+    if (wbest >= c.thr) return;                                  // nothing under max_descriptor_distance
+    const bool tied = best_m >= 0 && best == wbest;
+    const unsigned ballot = __ballot_sync(gmask, tied);
+    int win_lane = __ffs(ballot) - 1;                            // lane index within the warp
+    if (__popc(ballot) > 1) {
+        unsigned long long key = tied ? kd_visit_key(f.kd_xy, f.nkp, best_m, u, w) : ~0ull;
+        // 64-bit warp minimum by two 32-bit reductions
+        const unsigned hi = __reduce_min_sync(gmask, static_cast<unsigned>(key >> 32));
+        const unsigned lo = __reduce_min_sync(gmask, (key >> 32) == hi ? static_cast<unsigned>(key) : 0xFFFFFFFFu);
+        const unsigned long long wkey = (static_cast<unsigned long long>(hi) << 32) | lo;
+        win_lane = __ffs(__ballot_sync(gmask, tied && key == wkey)) - 1;
+    }
+    if (static_cast<int>(threadIdx.x & 31) == win_lane) {
+        const int best_kp = f.kd_idx[best_m];
+        // P7: first point in visit order attaining the minimum wins (src/MapMatcher.cpp:95-97)
+        const unsigned long long key = (static_cast<unsigned long long>(wbest) << 32) | static_cast<unsigned>(v);
+        atomicMin(&f.proposals[best_kp], key);
+        if (c.dbg_kp) c.dbg_kp[dbg_row] = best_kp;
+        if (c.dbg_d) c.dbg_d[dbg_row] = wbest;
+    }
+}
+
 __global__ void proj_emit_kernel(const ProjKernelArgs a)
 {
     const ProjFrameArgs& f = a.frames ? a.frames[blockIdx.y] : a.inline_frame;
@@ -255,9 +418,22 @@ int proj_launch(slamgpu_ctx* ctx, const ProjCommonArgs& common, const ProjFrameA
         proj_init_kernel<<<gk, 256, 0, ctx->stream>>>(a);
         ctx->launches++;
         if (common.n_visit > 0) {
-            const dim3 gp((common.n_visit + kProjThreads - 1) / kProjThreads, n_frames);
             ProfScope prof(ctx, SLAMGPU_KERNEL_PROJ_MATCH);
-            proj_match_kernel<<<gp, kProjThreads, 0, ctx->stream>>>(a);
+            if (ctx->proj_walk) {   // thread-per-point KD walk, kept for A/B checks (SLAMGPU_PROJ_WALK=1)
+                const dim3 gp((common.n_visit + kProjThreads - 1) / kProjThreads, n_frames);
+                proj_match_kernel<<<gp, kProjThreads, 0, ctx->stream>>>(a);
+            } else {
+                // 8 lanes per point: as fast as a full warp on C2 (19 us) and 1.8x faster on C4-sized batches
+                // (tools/time_proj.py, profiles/r01_proj_variants.txt); SLAMGPU_PROJ_LANES=32 overrides
+                const int lanes = ctx->proj_lanes ? ctx->proj_lanes : 8;
+                const int per_cta = kGroupThreads / lanes;
+                const dim3 gp((common.n_visit + per_cta - 1) / per_cta, n_frames);
+                if (lanes == 8) {
+                    proj_match_warp_kernel<8><<<gp, kGroupThreads, 0, ctx->stream>>>(a);
+                } else {
+                    proj_match_warp_kernel<32><<<gp, kGroupThreads, 0, ctx->stream>>>(a);
+                }
+            }
             ctx->launches++;
         }
         proj_emit_kernel<<<gk, 256, 0, ctx->stream>>>(a);

@@ -3,6 +3,7 @@
 // and proj_kernels.cu.  There is no CPU path in this library: every entry point that computes
 // launches CUDA kernels on the context's stream, and slamgpu_create() fails without a device.
 #include <algorithm>
+#include <cstdlib>
 #include <cstring>
 #include <numeric>
 
@@ -189,6 +190,13 @@ int slamgpu_create(int device, slamgpu_ctx** out)
     slamgpu_ctx* ctx = new slamgpu_ctx();
     ctx->device = device;
     ctx->n_sm = prop.multiProcessorCount;
+    const char* walk = std::getenv("SLAMGPU_PROJ_WALK");
+    ctx->proj_walk = walk != nullptr && walk[0] == '1';
+    const char* lanes = std::getenv("SLAMGPU_PROJ_LANES");
+    if (lanes != nullptr) {
+        const int v = std::atoi(lanes);
+        ctx->proj_lanes = (v == 8 || v == 32) ? v : 0;
+    }
     const cudaError_t e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking);
     if (e != cudaSuccess) {
         delete ctx;

@@ -54,6 +54,11 @@ struct FrameDev {
     uint8_t* matched = nullptr;   // [nkp]
     float2* xy = nullptr;         // [nkp] keypoint order (diagnostics)
     unsigned long long* proposals = nullptr;  // [nkp] packed (dist << 32 | visit rank)
+    // uniform grid over the keypoints (candidate lookup): cell c holds cell_items[cell_start[c] .. cell_start[c+1])
+    int32_t* cell_start = nullptr;            // [gw*gh + 1]
+    int32_t* cell_items = nullptr;            // [nkp] KD positions, cell-major
+    float gx0 = 0.f, gy0 = 0.f, inv_cell = 1.f;
+    int gw = 1, gh = 1;
     std::vector<uint32_t> perm_host;
 };
 
@@ -85,6 +90,8 @@ struct slamgpu_ctx {
     slamgpu::Arena h_stage;   // pinned staging
     int64_t launches = 0;
     bool profiling = false;
+    int proj_lanes = 0;       // SLAMGPU_PROJ_LANES=8|32 overrides the lanes-per-point choice (0 = by size)
+    bool proj_walk = false;   // SLAMGPU_PROJ_WALK=1: use the thread-per-point KD-walk kernel
     std::vector<std::pair<cudaEvent_t, cudaEvent_t>> prof_events[2];   // per SLAMGPU_KERNEL_*
     std::vector<cudaEvent_t> prof_pool;
     std::map<int, slamgpu::FrameDev> frames;
@@ -156,6 +163,10 @@ struct ProjFrameArgs {
     const uint8_t* matched;
     const float2* xy;
     unsigned long long* proposals;
+    const int32_t* cell_start;
+    const int32_t* cell_items;
+    float gx0, gy0, inv_cell;
+    int gw, gh;
     const uint8_t* skip;     // [n_points] for this frame or null
     int32_t* out_point;      // [nkp]
     int32_t* out_dist;       // [nkp]

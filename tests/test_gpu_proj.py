@@ -252,3 +252,32 @@ def test_mapmatcher_mirror_reads_like_the_reference(ctx, oracle, pkg):
     fm = m.match_features(ctx, kfs[0].features(), kfs[1].features())
     o_t, o_q = oracle.match_features(kfs[0].features().descriptors, kfs[1].features().descriptors, 64.0)
     assert [(f.train_index, f.query_index) for f in fm] == list(zip(o_t.tolist(), o_q.tolist()))
+
+
+def test_walk_and_warp_kernels_agree_on_tie_heavy_scene(oracle, pkg, monkeypatch):
+    """The default warp-per-point kernel (grid candidates + KD visit keys on ties) and the
+    thread-per-point KD-walk kernel (SLAMGPU_PROJ_WALK=1) must agree with each other and with the
+    oracle where equal Hamming minima make the KD visit order decide (low-entropy descriptors)."""
+    cam = dict(fx=300.0, fy=300.0, cx=160.0, cy=120.0, width=320, height=240)
+    sc = pkg.synthetic.projection_scene(6000, 1500, 91, cam=cam)
+    rng = np.random.default_rng(91)
+    sc.kp_desc[:] = rng.integers(0, 2, sc.kp_desc.shape, dtype=np.uint8) * 255
+    sc.obs_desc[:] = rng.integers(0, 2, sc.obs_desc.shape, dtype=np.uint8) * 255
+    p = _params(pkg, cam, 20.0, 200.0, 0)
+    perm = oracle.kd_build(sc.kp_xy)
+    ref = oracle.match_projection(sc.kp_xy, sc.kp_desc, perm, sc.kp_matched, sc.pos, sc.normal, sc.range,
+                                  sc.obs_offset, sc.obs_desc, sc.skip, None, sc.pose, _oparams(oracle, p))
+    results = []
+    for walk, lanes in (("0", "32"), ("0", "8"), ("1", "0")):
+        monkeypatch.setenv("SLAMGPU_PROJ_WALK", walk)
+        monkeypatch.setenv("SLAMGPU_PROJ_LANES", lanes)
+        with pkg.Context(0) as c:
+            c.frame_upload(1, sc.kp_xy, sc.kp_desc, None, sc.kp_matched)
+            c.points_upload(1, sc.pos, sc.normal, sc.range, sc.obs_offset, sc.obs_desc)
+            op, od, dbg = c.match_projection(1, 1, 1500, sc.pose, p, sc.skip, None, debug=True, n_points=6000)
+            _compare((op, od), dbg, ref)
+            results.append((op, od, dbg["kp"]))
+    for r in results[1:]:
+        assert np.array_equal(results[0][0], r[0]) and np.array_equal(results[0][2], r[2])
+    # the scene really has ties: many proposing points share their best distance with a second candidate
+    assert (ref.kp >= 0).sum() > 500
