@@ -41,6 +41,7 @@ ALU_PER_CLK_PER_SM = 64                # LOP3 / VIMNMX lanes per clock per SM (n
 # two comparisons on the ALU pipe, and 4 POPC on the XU pipe -> the ALU pipe binds
 ALU_PER_COMPARISON = 17.5
 POPC_PER_COMPARISON_CSA = 4
+NCU_SCAN_DRAM_BYTES_512_PAIRS = 7.2e6  # profiles/r01_ncu_full_prof_bf_scan_v2.txt
 
 
 def parse_args():
@@ -376,7 +377,10 @@ def run_ours(args, rank, local_rank, world):
     hbm_achieved = bytes_per_launch / (avg_ms * 1e-3) / 1e9
     roofline = {
         "bound": "int-alu", "achieved": achieved, "peak": peak, "unit": "Gcmp/s", "frac": achieved / peak,
-        "traffic": None, "kernel": "bf_scan_kernel", "launches": scan_launches, "avg_launch_ms": avg_ms,
+        "traffic": NCU_SCAN_DRAM_BYTES_512_PAIRS * (n * K / max(scan_launches, 1)) / 512.0,
+        "traffic_basis": "ncu --set full dram__bytes_read+write of one 512-pair bf_scan_kernel launch "
+                         "(profiles/r01_ncu_full_prof_bf_scan_v2.txt: 7.2 MB read, 0 written), scaled to this launch's pair count",
+        "kernel": "bf_scan_kernel", "launches": scan_launches, "avg_launch_ms": avg_ms,
         "share_of_step": scan_ms / ms_dev,
         "peak_basis": f"integer pipes, not HBM/tensor (SURVEY 8d): {n_sm} SMs x {ALU_PER_CLK_PER_SM} ALU lanes/clk/SM x "
                       f"{peaks['sm_max_mhz']:.0f} MHz / {ALU_PER_COMPARISON} ALU ops per 256-bit comparison "
