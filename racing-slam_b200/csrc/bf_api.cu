@@ -12,6 +12,8 @@ namespace {
 
 bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
 
+constexpr int64_t kTcMinComparisons = int64_t(1) << 62;   // auto choice disabled until the GPU check is in
+
 #define SG_CTX(ctx)                                 \
     do {                                            \
         SG_CHECK((ctx) != nullptr, "null context"); \
@@ -34,6 +36,49 @@ int check_dev_sets(const void* q, int nq, const void* t, int nt)
     return SLAMGPU_OK;
 }
 
+// ---- engine choice ---------------------------------------------------------------------------
+// The tensor-core scan (bf_tc_kernels.cu) pays an expansion pass and 128 x 256 tile granularity;
+// the integer scan (bf_kernels.cu) wins on small sets.  SLAMGPU_BF_ENGINE=int|tc forces one.
+bool use_tc(const slamgpu_ctx* ctx, int64_t nq, int64_t nt, int64_t n_pairs)
+{
+    if (nq <= 0 || nt <= 0 || n_pairs <= 0) return false;
+    if (ctx->bf_engine == 1) return false;
+    if (ctx->bf_engine == 2) return true;
+    return nq * nt * n_pairs >= kTcMinComparisons && nt >= 512;
+}
+
+// One (query, train) pair on the tensor cores: expand both sets, scan, leave 2 * splits partials.
+struct TcPair {
+    BfPlan plan;      // of the scan
+    BfPlan fin;       // what the finish kernels see (2 partials per split)
+    uint2* keys = nullptr;
+};
+size_t tc_pair_keys(const BfPlan& plan, int nq) { return static_cast<size_t>(plan.splits) * 2 * nq; }
+
+int tc_expand_pair(slamgpu_ctx* ctx, const uint8_t* dq, int nq, const uint8_t* dt, int nt, int* pitch_rows)
+{
+    const int pitch = bf_tc_pitch_rows(std::max(nq, nt));
+    SG_TRY(ensure_device_exp(ctx, bf_tc_expanded_bytes(2, std::max(nq, nt))));
+    uint8_t* e = static_cast<uint8_t*>(ctx->d_exp.ptr);
+    SG_TRY(bf_tc_launch_expand(ctx, dq, nullptr, 1, nq, nq, pitch, e));
+    SG_TRY(bf_tc_launch_expand(ctx, dt, nullptr, 1, nt, nt, pitch, e + bf_tc_expanded_bytes(1, std::max(nq, nt))));
+    *pitch_rows = pitch;
+    return SLAMGPU_OK;
+}
+
+// scan query-set `qi` against train-set `ti` (0 or 1: the two expanded sets of tc_expand_pair)
+int tc_scan_pair(slamgpu_ctx* ctx, int qi, int nq, int ti, int nt, int pitch_rows, uint2* keys, TcPair& out)
+{
+    out.plan = bf_tc_make_plan(ctx->n_sm, nq, nt, 1);
+    out.fin = out.plan;
+    out.fin.splits = out.plan.splits * 2;
+    out.keys = keys;
+    const uint8_t* e = static_cast<const uint8_t*>(ctx->d_exp.ptr);
+    const size_t set_bytes = static_cast<size_t>(pitch_rows) * 256;
+    return bf_tc_launch_scan(ctx, out.plan, e + qi * set_bytes, nq, e + ti * set_bytes, nt, pitch_rows, nullptr, nullptr,
+                             1, nq, keys);
+}
+
 // kNN-2 over device buffers; scratch from d_ws.
 int knn2_core(slamgpu_ctx* ctx, const uint8_t* dq, int nq, const uint8_t* dt, int nt, int32_t* d_idx, int32_t* d_dist)
 {
@@ -42,6 +87,15 @@ int knn2_core(slamgpu_ctx* ctx, const uint8_t* dq, int nq, const uint8_t* dt, in
         SG_CUDA(cudaMemsetAsync(d_idx, 0xFF, sizeof(int32_t) * 2 * nq, ctx->stream));
         SG_CUDA(cudaMemsetAsync(d_dist, 0xFF, sizeof(int32_t) * 2 * nq, ctx->stream));
         return SLAMGPU_OK;
+    }
+    if (use_tc(ctx, nq, nt, 1)) {
+        int pitch = 0;
+        SG_TRY(tc_expand_pair(ctx, dq, nq, dt, nt, &pitch));
+        const BfPlan tp = bf_tc_make_plan(ctx->n_sm, nq, nt, 1);
+        SG_TRY(ensure_device_ws(ctx, Carver::padded(tc_pair_keys(tp, nq) * sizeof(uint2))));
+        TcPair r;
+        SG_TRY(tc_scan_pair(ctx, 0, nq, 1, nt, pitch, static_cast<uint2*>(ctx->d_ws.ptr), r));
+        return bf_launch_finish_raw(ctx, r.fin, r.keys, nq, nt, nq, d_idx, d_dist);
     }
     const BfPlan plan = bf_make_plan(ctx->n_sm, nq, nt, 1);
     SG_TRY(ensure_device_ws(ctx, Carver::padded(bf_partial_elems(plan, 1, nq) * sizeof(uint2))));
@@ -60,6 +114,21 @@ int crosscheck_core(slamgpu_ctx* ctx, const uint8_t* dq, int nq, const uint8_t* 
         SG_CUDA(cudaMemsetAsync(d_idx, 0xFF, sizeof(int32_t) * nq, ctx->stream));
         SG_CUDA(cudaMemsetAsync(d_dist, 0xFF, sizeof(int32_t) * nq, ctx->stream));
         return SLAMGPU_OK;
+    }
+    if (use_tc(ctx, nq, nt, 1) && nq >= 512) {
+        // tensor cores: two scans over the same expanded sets, rows (q -> t) and columns (t -> q)
+        int pitch = 0;
+        SG_TRY(tc_expand_pair(ctx, dq, nq, dt, nt, &pitch));
+        const BfPlan rp = bf_tc_make_plan(ctx->n_sm, nq, nt, 1), cp = bf_tc_make_plan(ctx->n_sm, nt, nq, 1);
+        SG_TRY(ensure_device_ws(ctx, Carver::padded(tc_pair_keys(rp, nq) * sizeof(uint2)) +
+                                         Carver::padded(tc_pair_keys(cp, nt) * sizeof(uint2))));
+        Carver ws(ctx->d_ws.ptr);
+        uint2* row_keys = ws.take<uint2>(tc_pair_keys(rp, nq));
+        uint2* col_keys = ws.take<uint2>(tc_pair_keys(cp, nt));
+        TcPair r, c;
+        SG_TRY(tc_scan_pair(ctx, 0, nq, 1, nt, pitch, row_keys, r));
+        SG_TRY(tc_scan_pair(ctx, 1, nt, 0, nq, pitch, col_keys, c));
+        return bf_launch_mutual(ctx, r.fin, r.keys, nq, c.fin, c.keys, nt, nq, nt, strict_max_dist, d_idx, d_dist);
     }
     // one scan: per-row top-1 partials and, in the same pass, per-column minima (atomicMin)
     const BfPlan row = bf_make_plan(ctx->n_sm, nq, nt, 1);
@@ -82,6 +151,16 @@ int match_descriptors_core(slamgpu_ctx* ctx, const uint8_t* dq, int nq, const ui
         SG_CUDA(cudaMemsetAsync(d_out_train, 0xFF, sizeof(int32_t) * nq, ctx->stream));
         return SLAMGPU_OK;
     }
+    if (use_tc(ctx, nq, nt, 1)) {
+        int pitch = 0;
+        SG_TRY(tc_expand_pair(ctx, dq, nq, dt, nt, &pitch));
+        const BfPlan tp = bf_tc_make_plan(ctx->n_sm, nq, nt, 1);
+        SG_TRY(ensure_device_ws(ctx, Carver::padded(tc_pair_keys(tp, nq) * sizeof(uint2))));
+        TcPair r;
+        SG_TRY(tc_scan_pair(ctx, 0, nq, 1, nt, pitch, static_cast<uint2*>(ctx->d_ws.ptr), r));
+        return bf_launch_finish_filter(ctx, r.fin, r.keys, nq, nt, nullptr, nullptr, 1, nq, max_dist, ratio, d_out_train,
+                                       d_out_count);
+    }
     const BfPlan plan = bf_make_plan(ctx->n_sm, nq, nt, 1);
     SG_TRY(ensure_device_ws(ctx, Carver::padded(bf_partial_elems(plan, 1, nq) * sizeof(uint2))));
     Carver ws(ctx->d_ws.ptr);
@@ -94,8 +173,8 @@ int match_descriptors_core(slamgpu_ctx* ctx, const uint8_t* dq, int nq, const ui
 // Pairs are processed in slices so that the partial-key scratch stays around L2 size.
 constexpr size_t kBatchScratchBytes = size_t(64) << 20;
 
-int batch_core(slamgpu_ctx* ctx, const uint8_t* d_desc, const int32_t* d_frame_offset, const int32_t* d_pairs,
-               int n_pairs, int max_rows, float max_dist, float ratio, int32_t* d_out_train, int32_t* d_out_count,
+int batch_core(slamgpu_ctx* ctx, const uint8_t* d_desc, const int32_t* d_frame_offset, int n_frames,
+               const int32_t* d_pairs, int n_pairs, int max_rows, float max_dist, float ratio, int32_t* d_out_train, int32_t* d_out_count,
                // optional ordered compaction (host-buffer form): per-slice out_train is then a scratch
                // of slice_pairs x max_rows and the lists are filled slice by slice
                int32_t* d_offset, int32_t* d_query_list, int32_t* d_train_list, int64_t capacity, int slice_pairs)
@@ -106,8 +185,19 @@ int batch_core(slamgpu_ctx* ctx, const uint8_t* d_desc, const int32_t* d_frame_o
         if (d_offset) SG_CUDA(cudaMemsetAsync(d_offset, 0, sizeof(int32_t) * (n_pairs + 1), ctx->stream));
         return SLAMGPU_OK;
     }
-    const BfPlan plan = bf_make_plan(ctx->n_sm, max_rows, max_rows, std::min(n_pairs, slice_pairs));
-    const size_t per_pair = bf_partial_elems(plan, 1, max_rows);
+    const bool tc = use_tc(ctx, max_rows, max_rows, n_pairs);
+    BfPlan plan = tc ? bf_tc_make_plan(ctx->n_sm, max_rows, max_rows, std::min(n_pairs, slice_pairs))
+                     : bf_make_plan(ctx->n_sm, max_rows, max_rows, std::min(n_pairs, slice_pairs));
+    BfPlan fin = plan;
+    int pitch = 0;
+    if (tc) {   // every frame expanded once per call; the scans then read only the expanded copy
+        fin.splits = plan.splits * 2;
+        pitch = bf_tc_pitch_rows(max_rows);
+        SG_TRY(ensure_device_exp(ctx, bf_tc_expanded_bytes(n_frames, max_rows)));
+        SG_TRY(bf_tc_launch_expand(ctx, d_desc, d_frame_offset, n_frames, 0, max_rows, pitch,
+                                   static_cast<uint8_t*>(ctx->d_exp.ptr)));
+    }
+    const size_t per_pair = bf_partial_elems(fin, 1, max_rows);
     SG_TRY(ensure_device_ws(ctx, Carver::padded(per_pair * sizeof(uint2) * std::min(n_pairs, slice_pairs))));
     Carver ws(ctx->d_ws.ptr);
     uint2* keys = ws.take<uint2>(per_pair * std::min(n_pairs, slice_pairs));
@@ -116,8 +206,13 @@ int batch_core(slamgpu_ctx* ctx, const uint8_t* d_desc, const int32_t* d_frame_o
         const int np = std::min(slice_pairs, n_pairs - p0);
         const int32_t* pairs = d_pairs + 2 * static_cast<size_t>(p0);
         int32_t* out_train = d_offset ? d_out_train : d_out_train + static_cast<size_t>(p0) * max_rows;
-        SG_TRY(bf_launch_scan(ctx, plan, d_desc, 0, d_desc, 0, d_frame_offset, pairs, np, max_rows, false, keys));
-        SG_TRY(bf_launch_finish_filter(ctx, plan, keys, 0, 0, d_frame_offset, pairs, np, max_rows, max_dist, ratio,
+        if (tc) {
+            const uint8_t* e = static_cast<const uint8_t*>(ctx->d_exp.ptr);
+            SG_TRY(bf_tc_launch_scan(ctx, plan, e, 0, e, 0, pitch, d_frame_offset, pairs, np, max_rows, keys));
+        } else {
+            SG_TRY(bf_launch_scan(ctx, plan, d_desc, 0, d_desc, 0, d_frame_offset, pairs, np, max_rows, false, keys));
+        }
+        SG_TRY(bf_launch_finish_filter(ctx, fin, keys, 0, 0, d_frame_offset, pairs, np, max_rows, max_dist, ratio,
                                        out_train, d_out_count + p0));
         if (d_offset) {
             SG_TRY(bf_launch_scan_counts(ctx, d_out_count + p0, np, d_offset + p0));
@@ -340,7 +435,7 @@ int slamgpu_match_descriptors_batch(slamgpu_ctx* ctx, const uint8_t* desc, const
     SG_TRY(upload(ctx, d_desc, desc, n_rows * 32, 0));
     SG_TRY(upload(ctx, d_off, frame_offset, sizeof(int32_t) * (n_frames + 1), b_desc));
     SG_TRY(upload(ctx, d_pairs, pairs, sizeof(int32_t) * 2 * n_pairs, b_desc + b_off));
-    SG_TRY(batch_core(ctx, d_desc, d_off, d_pairs, n_pairs, max_rows, max_dist, ratio, d_rows, d_count, d_offset, d_ql,
+    SG_TRY(batch_core(ctx, d_desc, d_off, n_frames, d_pairs, n_pairs, max_rows, max_dist, ratio, d_rows, d_count, d_offset, d_ql,
                       d_tl, capacity, slice));
     // offsets first: they tell how much of the lists to bring back
     uint8_t* hs = static_cast<uint8_t*>(ctx->h_stage.ptr);
@@ -400,7 +495,7 @@ int slamgpu_match_descriptors_batch_dev(slamgpu_ctx* ctx, const uint8_t* d_desc,
     if (n_pairs == 0) return SLAMGPU_OK;
     SG_CHECK(d_desc && d_frame_offset && d_pairs && d_out_train && d_out_count, "null pointer");
     SG_CHECK(aligned16(d_desc), "device descriptor pointer must be 16-byte aligned");
-    return batch_core(ctx, d_desc, d_frame_offset, d_pairs, n_pairs, max_rows, max_dist, ratio, d_out_train,
+    return batch_core(ctx, d_desc, d_frame_offset, n_frames, d_pairs, n_pairs, max_rows, max_dist, ratio, d_out_train,
                       d_out_count, nullptr, nullptr, nullptr, 0, slice_for(ctx->n_sm, max_rows));
 }
 

@@ -79,6 +79,7 @@ static int grow(slamgpu_ctx* ctx, Arena& a, size_t bytes, bool host)
 int ensure_device_ws(slamgpu_ctx* ctx, size_t bytes) { return grow(ctx, ctx->d_ws, bytes, false); }
 int ensure_device_io(slamgpu_ctx* ctx, size_t bytes) { return grow(ctx, ctx->d_io, bytes, false); }
 int ensure_host_stage(slamgpu_ctx* ctx, size_t bytes) { return grow(ctx, ctx->h_stage, bytes, true); }
+int ensure_device_exp(slamgpu_ctx* ctx, size_t bytes) { return grow(ctx, ctx->d_exp, bytes, false); }
 
 // Host float helpers in the oracle's / Eigen's coefficient order (see proj_kernels.cu).  This
 // translation unit is compiled with -ffp-contract=off for the host, so a*b+c stays two roundings.
@@ -197,6 +198,10 @@ int slamgpu_create(int device, slamgpu_ctx** out)
         const int v = std::atoi(lanes);
         ctx->proj_lanes = (v == 8 || v == 32) ? v : 0;
     }
+    const char* engine = std::getenv("SLAMGPU_BF_ENGINE");
+    if (engine != nullptr) ctx->bf_engine = std::strcmp(engine, "int") == 0 ? 1 : std::strcmp(engine, "tc") == 0 ? 2 : 0;
+    const char* variant = std::getenv("SLAMGPU_TC_VARIANT");
+    if (variant != nullptr) ctx->tc_variant = std::atoi(variant);
     const cudaError_t e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking);
     if (e != cudaSuccess) {
         delete ctx;
@@ -226,6 +231,7 @@ int slamgpu_destroy(slamgpu_ctx* ctx)
     for (auto& kv : ctx->point_sets) free_points(kv.second);
     if (ctx->d_ws.ptr) cudaFree(ctx->d_ws.ptr);
     if (ctx->d_io.ptr) cudaFree(ctx->d_io.ptr);
+    if (ctx->d_exp.ptr) cudaFree(ctx->d_exp.ptr);
     if (ctx->h_stage.ptr) cudaFreeHost(ctx->h_stage.ptr);
     for (auto& v : ctx->prof_events)
         for (auto& pr : v) {

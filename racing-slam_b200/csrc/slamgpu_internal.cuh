@@ -92,6 +92,9 @@ struct slamgpu_ctx {
     bool profiling = false;
     int proj_lanes = 0;       // SLAMGPU_PROJ_LANES=8|32 overrides the lanes-per-point choice (0 = by size)
     bool proj_walk = false;   // SLAMGPU_PROJ_WALK=1: use the thread-per-point KD-walk kernel
+    int bf_engine = 0;        // SLAMGPU_BF_ENGINE=int|tc overrides the brute-force engine choice (0 = by size, 1 = int, 2 = tc)
+    int tc_variant = 0;       // SLAMGPU_TC_VARIANT: debug switches of the tensor-core scan
+    slamgpu::Arena d_exp;     // expanded (int8) descriptors of the tensor-core scan
     std::vector<std::pair<cudaEvent_t, cudaEvent_t>> prof_events[2];   // per SLAMGPU_KERNEL_*
     std::vector<cudaEvent_t> prof_pool;
     std::map<int, slamgpu::FrameDev> frames;
@@ -153,6 +156,19 @@ int bf_launch_scan_counts(slamgpu_ctx* ctx, const int32_t* d_count, int n, int32
 int bf_launch_compact(slamgpu_ctx* ctx, const int32_t* d_out_train, const int32_t* d_frame_offset,
                       const int32_t* d_pairs, int nq_single, int n_pairs, int max_rows, const int32_t* d_offset,
                       int32_t* d_query_list, int32_t* d_train_list, int64_t capacity);
+
+// ---- brute force on the tensor cores (bf_tc_kernels.cu) ---------------------------------------
+// Expanded descriptors: 256 int8 per row in the UMMA canonical layout, frames at a pitch of
+// bf_tc_pitch_rows(max_rows) rows.  The scan writes 2 * plan.splits partials per query row.
+int bf_tc_pitch_rows(int max_rows);
+size_t bf_tc_expanded_bytes(int n_frames, int max_rows);
+BfPlan bf_tc_make_plan(int n_sm, int nq_max, int nt_max, int64_t n_pairs);
+int bf_tc_launch_expand(slamgpu_ctx* ctx, const uint8_t* d_src, const int32_t* d_frame_offset, int n_frames, int n_rows,
+                        int max_rows, int pitch_rows, uint8_t* d_dst);
+int bf_tc_launch_scan(slamgpu_ctx* ctx, const BfPlan& plan, const uint8_t* d_exp_q, int nq, const uint8_t* d_exp_t,
+                      int nt, int pitch_rows, const int32_t* d_frame_offset, const int32_t* d_pairs, int n_pairs,
+                      int max_rows, uint2* d_keys);
+int ensure_device_exp(slamgpu_ctx* ctx, size_t bytes);
 
 // ---- projection (proj_kernels.cu) -----------------------------------------------------------
 struct ProjFrameArgs {
