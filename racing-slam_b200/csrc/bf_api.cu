@@ -2,6 +2,7 @@
 // Host-buffer forms stage through the context's pinned buffer, copy H2D, run the kernels of
 // bf_kernels.cu on the context's stream, copy D2H and return when the caller's buffers are filled.
 #include <algorithm>
+#include <cmath>
 #include <cstring>
 
 #include "slamgpu_internal.cuh"
@@ -12,7 +13,11 @@ namespace {
 
 bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
 
-constexpr int64_t kTcMinComparisons = int64_t(1) << 62;   // auto choice disabled until the GPU check is in
+// Measured on the B200 (tools/tc_sizes.py, profiles/r01_tc_sizes.txt): the tensor-core path has a ~22 us floor
+// (expansion + scan + finish launches) and overtakes the integer scan near 2500 x 2500 for one scan and near
+// 3500 x 3500 for the two scans of a cross-check.
+constexpr int64_t kTcMinComparisons = 6000000;
+constexpr int64_t kTcMinComparisonsCross = 12000000;
 
 #define SG_CTX(ctx)                                 \
     do {                                            \
@@ -47,13 +52,34 @@ bool use_tc(const slamgpu_ctx* ctx, int64_t nq, int64_t nt, int64_t n_pairs)
     return nq * nt * n_pairs >= kTcMinComparisons && nt >= 512;
 }
 
+// Distance cuts of the tensor-core scan's filtered mode (bf_tc_kernels.cu): train rows at a distance
+// >= cut cannot change the caller's result.
+//   match_descriptors (src/MapMatcher.cpp:151-161): a row survives only with d0 <= max_dist, and then
+//   d0 > ratio * d1 can only hold for d1 < max_dist / ratio.  Margin of 3 for the float compares.
+//   match_features (src/features/FeatureExtractor.cpp:25): only mutual nearest pairs with d < max_dist.
+constexpr int kNoCut = 257;
+int cut_for_filter(float max_dist, float ratio)
+{
+    if (!(max_dist >= 0.0f) || !(ratio > 0.0f) || !std::isfinite(max_dist) || !std::isfinite(ratio)) return kNoCut;
+    const double t = std::max(static_cast<double>(max_dist), static_cast<double>(max_dist) / ratio);
+    return t >= 254.0 ? kNoCut : static_cast<int>(std::floor(t)) + 3;
+}
+int cut_for_crosscheck(float strict_max_dist)
+{
+    if (!(strict_max_dist >= 0.0f) || !std::isfinite(strict_max_dist)) return kNoCut;   // < 0: raw cross-check
+    return strict_max_dist >= 254.0f ? kNoCut : static_cast<int>(std::ceil(strict_max_dist)) + 2;
+}
+
 // One (query, train) pair on the tensor cores: expand both sets, scan, leave 2 * splits partials.
 struct TcPair {
     BfPlan plan;      // of the scan
-    BfPlan fin;       // what the finish kernels see (2 partials per split)
+    BfPlan fin;       // what the finish kernels see (bf_tc_partials() partials per split)
     uint2* keys = nullptr;
 };
-size_t tc_pair_keys(const BfPlan& plan, int nq) { return static_cast<size_t>(plan.splits) * 2 * nq; }
+size_t tc_pair_keys(const slamgpu_ctx* ctx, const BfPlan& plan, int nq)
+{
+    return static_cast<size_t>(plan.splits) * bf_tc_partials(ctx) * nq;
+}
 
 int tc_expand_pair(slamgpu_ctx* ctx, const uint8_t* dq, int nq, const uint8_t* dt, int nt, int* pitch_rows)
 {
@@ -67,16 +93,16 @@ int tc_expand_pair(slamgpu_ctx* ctx, const uint8_t* dq, int nq, const uint8_t* d
 }
 
 // scan query-set `qi` against train-set `ti` (0 or 1: the two expanded sets of tc_expand_pair)
-int tc_scan_pair(slamgpu_ctx* ctx, int qi, int nq, int ti, int nt, int pitch_rows, uint2* keys, TcPair& out)
+int tc_scan_pair(slamgpu_ctx* ctx, int qi, int nq, int ti, int nt, int pitch_rows, int d_cut, uint2* keys, TcPair& out)
 {
-    out.plan = bf_tc_make_plan(ctx->n_sm, nq, nt, 1);
+    out.plan = bf_tc_make_plan(ctx, nq, nt, 1);
     out.fin = out.plan;
-    out.fin.splits = out.plan.splits * 2;
+    out.fin.splits = out.plan.splits * bf_tc_partials(ctx);
     out.keys = keys;
     const uint8_t* e = static_cast<const uint8_t*>(ctx->d_exp.ptr);
     const size_t set_bytes = static_cast<size_t>(pitch_rows) * 256;
     return bf_tc_launch_scan(ctx, out.plan, e + qi * set_bytes, nq, e + ti * set_bytes, nt, pitch_rows, nullptr, nullptr,
-                             1, nq, keys);
+                             1, nq, d_cut, keys);
 }
 
 // kNN-2 over device buffers; scratch from d_ws.
@@ -91,10 +117,10 @@ int knn2_core(slamgpu_ctx* ctx, const uint8_t* dq, int nq, const uint8_t* dt, in
     if (use_tc(ctx, nq, nt, 1)) {
         int pitch = 0;
         SG_TRY(tc_expand_pair(ctx, dq, nq, dt, nt, &pitch));
-        const BfPlan tp = bf_tc_make_plan(ctx->n_sm, nq, nt, 1);
-        SG_TRY(ensure_device_ws(ctx, Carver::padded(tc_pair_keys(tp, nq) * sizeof(uint2))));
+        const BfPlan tp = bf_tc_make_plan(ctx, nq, nt, 1);
+        SG_TRY(ensure_device_ws(ctx, Carver::padded(tc_pair_keys(ctx, tp, nq) * sizeof(uint2))));
         TcPair r;
-        SG_TRY(tc_scan_pair(ctx, 0, nq, 1, nt, pitch, static_cast<uint2*>(ctx->d_ws.ptr), r));
+        SG_TRY(tc_scan_pair(ctx, 0, nq, 1, nt, pitch, kNoCut, static_cast<uint2*>(ctx->d_ws.ptr), r));
         return bf_launch_finish_raw(ctx, r.fin, r.keys, nq, nt, nq, d_idx, d_dist);
     }
     const BfPlan plan = bf_make_plan(ctx->n_sm, nq, nt, 1);
@@ -115,19 +141,21 @@ int crosscheck_core(slamgpu_ctx* ctx, const uint8_t* dq, int nq, const uint8_t* 
         SG_CUDA(cudaMemsetAsync(d_dist, 0xFF, sizeof(int32_t) * nq, ctx->stream));
         return SLAMGPU_OK;
     }
-    if (use_tc(ctx, nq, nt, 1) && nq >= 512) {
+    if (nq >= 512 && use_tc(ctx, nq, nt, 1) &&
+        (ctx->bf_engine == 2 || static_cast<int64_t>(nq) * nt >= kTcMinComparisonsCross)) {
         // tensor cores: two scans over the same expanded sets, rows (q -> t) and columns (t -> q)
         int pitch = 0;
         SG_TRY(tc_expand_pair(ctx, dq, nq, dt, nt, &pitch));
-        const BfPlan rp = bf_tc_make_plan(ctx->n_sm, nq, nt, 1), cp = bf_tc_make_plan(ctx->n_sm, nt, nq, 1);
-        SG_TRY(ensure_device_ws(ctx, Carver::padded(tc_pair_keys(rp, nq) * sizeof(uint2)) +
-                                         Carver::padded(tc_pair_keys(cp, nt) * sizeof(uint2))));
+        const BfPlan rp = bf_tc_make_plan(ctx, nq, nt, 1), cp = bf_tc_make_plan(ctx, nt, nq, 1);
+        SG_TRY(ensure_device_ws(ctx, Carver::padded(tc_pair_keys(ctx, rp, nq) * sizeof(uint2)) +
+                                         Carver::padded(tc_pair_keys(ctx, cp, nt) * sizeof(uint2))));
         Carver ws(ctx->d_ws.ptr);
-        uint2* row_keys = ws.take<uint2>(tc_pair_keys(rp, nq));
-        uint2* col_keys = ws.take<uint2>(tc_pair_keys(cp, nt));
+        uint2* row_keys = ws.take<uint2>(tc_pair_keys(ctx, rp, nq));
+        uint2* col_keys = ws.take<uint2>(tc_pair_keys(ctx, cp, nt));
         TcPair r, c;
-        SG_TRY(tc_scan_pair(ctx, 0, nq, 1, nt, pitch, row_keys, r));
-        SG_TRY(tc_scan_pair(ctx, 1, nt, 0, nq, pitch, col_keys, c));
+        const int cut = cut_for_crosscheck(strict_max_dist);
+        SG_TRY(tc_scan_pair(ctx, 0, nq, 1, nt, pitch, cut, row_keys, r));
+        SG_TRY(tc_scan_pair(ctx, 1, nt, 0, nq, pitch, cut, col_keys, c));
         return bf_launch_mutual(ctx, r.fin, r.keys, nq, c.fin, c.keys, nt, nq, nt, strict_max_dist, d_idx, d_dist);
     }
     // one scan: per-row top-1 partials and, in the same pass, per-column minima (atomicMin)
@@ -154,10 +182,11 @@ int match_descriptors_core(slamgpu_ctx* ctx, const uint8_t* dq, int nq, const ui
     if (use_tc(ctx, nq, nt, 1)) {
         int pitch = 0;
         SG_TRY(tc_expand_pair(ctx, dq, nq, dt, nt, &pitch));
-        const BfPlan tp = bf_tc_make_plan(ctx->n_sm, nq, nt, 1);
-        SG_TRY(ensure_device_ws(ctx, Carver::padded(tc_pair_keys(tp, nq) * sizeof(uint2))));
+        const BfPlan tp = bf_tc_make_plan(ctx, nq, nt, 1);
+        SG_TRY(ensure_device_ws(ctx, Carver::padded(tc_pair_keys(ctx, tp, nq) * sizeof(uint2))));
         TcPair r;
-        SG_TRY(tc_scan_pair(ctx, 0, nq, 1, nt, pitch, static_cast<uint2*>(ctx->d_ws.ptr), r));
+        SG_TRY(tc_scan_pair(ctx, 0, nq, 1, nt, pitch, cut_for_filter(max_dist, ratio), static_cast<uint2*>(ctx->d_ws.ptr),
+                            r));
         return bf_launch_finish_filter(ctx, r.fin, r.keys, nq, nt, nullptr, nullptr, 1, nq, max_dist, ratio, d_out_train,
                                        d_out_count);
     }
@@ -186,12 +215,12 @@ int batch_core(slamgpu_ctx* ctx, const uint8_t* d_desc, const int32_t* d_frame_o
         return SLAMGPU_OK;
     }
     const bool tc = use_tc(ctx, max_rows, max_rows, n_pairs);
-    BfPlan plan = tc ? bf_tc_make_plan(ctx->n_sm, max_rows, max_rows, std::min(n_pairs, slice_pairs))
+    BfPlan plan = tc ? bf_tc_make_plan(ctx, max_rows, max_rows, std::min(n_pairs, slice_pairs))
                      : bf_make_plan(ctx->n_sm, max_rows, max_rows, std::min(n_pairs, slice_pairs));
     BfPlan fin = plan;
     int pitch = 0;
     if (tc) {   // every frame expanded once per call; the scans then read only the expanded copy
-        fin.splits = plan.splits * 2;
+        fin.splits = plan.splits * bf_tc_partials(ctx);
         pitch = bf_tc_pitch_rows(max_rows);
         SG_TRY(ensure_device_exp(ctx, bf_tc_expanded_bytes(n_frames, max_rows)));
         SG_TRY(bf_tc_launch_expand(ctx, d_desc, d_frame_offset, n_frames, 0, max_rows, pitch,
@@ -208,7 +237,8 @@ int batch_core(slamgpu_ctx* ctx, const uint8_t* d_desc, const int32_t* d_frame_o
         int32_t* out_train = d_offset ? d_out_train : d_out_train + static_cast<size_t>(p0) * max_rows;
         if (tc) {
             const uint8_t* e = static_cast<const uint8_t*>(ctx->d_exp.ptr);
-            SG_TRY(bf_tc_launch_scan(ctx, plan, e, 0, e, 0, pitch, d_frame_offset, pairs, np, max_rows, keys));
+            SG_TRY(bf_tc_launch_scan(ctx, plan, e, 0, e, 0, pitch, d_frame_offset, pairs, np, max_rows,
+                                     cut_for_filter(max_dist, ratio), keys));
         } else {
             SG_TRY(bf_launch_scan(ctx, plan, d_desc, 0, d_desc, 0, d_frame_offset, pairs, np, max_rows, false, keys));
         }

@@ -161,13 +161,14 @@ int bf_launch_compact(slamgpu_ctx* ctx, const int32_t* d_out_train, const int32_
 // Expanded descriptors: 256 int8 per row in the UMMA canonical layout, frames at a pitch of
 // bf_tc_pitch_rows(max_rows) rows.  The scan writes 2 * plan.splits partials per query row.
 int bf_tc_pitch_rows(int max_rows);
+int bf_tc_partials(const slamgpu_ctx* ctx);   // partial top-2 records per (pair, split, row) the scan writes
 size_t bf_tc_expanded_bytes(int n_frames, int max_rows);
-BfPlan bf_tc_make_plan(int n_sm, int nq_max, int nt_max, int64_t n_pairs);
+BfPlan bf_tc_make_plan(const slamgpu_ctx* ctx, int nq_max, int nt_max, int64_t n_pairs);
 int bf_tc_launch_expand(slamgpu_ctx* ctx, const uint8_t* d_src, const int32_t* d_frame_offset, int n_frames, int n_rows,
                         int max_rows, int pitch_rows, uint8_t* d_dst);
 int bf_tc_launch_scan(slamgpu_ctx* ctx, const BfPlan& plan, const uint8_t* d_exp_q, int nq, const uint8_t* d_exp_t,
                       int nt, int pitch_rows, const int32_t* d_frame_offset, const int32_t* d_pairs, int n_pairs,
-                      int max_rows, uint2* d_keys);
+                      int max_rows, int d_cut, uint2* d_keys);
 int ensure_device_exp(slamgpu_ctx* ctx, size_t bytes);
 
 // ---- projection (proj_kernels.cu) -----------------------------------------------------------

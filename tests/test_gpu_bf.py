@@ -8,6 +8,26 @@ from conftest import golden, golden_names
 pytestmark = pytest.mark.gpu
 
 
+@pytest.fixture(scope="module", params=["int", "tc", "auto"])
+def ctx(request, pkg):
+    """Every brute-force test runs on both engines and on the library's own choice: the integer XOR+POPC
+    scan (bf_kernels.cu), the tensor-core scan (bf_tc_kernels.cu), and `auto` (by problem size).
+    SLAMGPU_BF_ENGINE is read when the context is created."""
+    import os
+    old = os.environ.get("SLAMGPU_BF_ENGINE")
+    if request.param == "auto":
+        os.environ.pop("SLAMGPU_BF_ENGINE", None)
+    else:
+        os.environ["SLAMGPU_BF_ENGINE"] = request.param
+    c = pkg.Context(0)
+    if old is None:
+        os.environ.pop("SLAMGPU_BF_ENGINE", None)
+    else:
+        os.environ["SLAMGPU_BF_ENGINE"] = old
+    yield c
+    c.close()
+
+
 @pytest.mark.parametrize("name", golden_names("bf_"))
 def test_golden_cv2(ctx, name):
     g = golden(name)
@@ -51,7 +71,8 @@ def test_empty_sets(ctx, nq, nt):
     assert len(ctx.match_features(t, q)[0]) == 0
 
 
-@pytest.mark.parametrize("max_dist,ratio", [(64.0, 0.75), (64.0, 0.8), (50.5, 0.6), (256.0, 1.0), (0.0, 0.75)])
+@pytest.mark.parametrize("max_dist,ratio", [(64.0, 0.75), (64.0, 0.8), (50.5, 0.6), (256.0, 1.0), (0.0, 0.75), (100.0, 0.5), (30.0, 0.9),
+                                            (64.0, 1.5), (200.0, 0.8), (63.5, 0.7)])
 def test_match_descriptors_filters_vs_oracle(ctx, oracle, pkg, max_dist, ratio):
     q, t = pkg.synthetic.bf_correlated(1500, 1100, 42, max_flip=90)
     mq, mt = ctx.match_descriptors(q, t, max_dist, ratio)

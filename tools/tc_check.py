@@ -54,6 +54,21 @@ def run_variant(variant, quick):
         ok = all(np.array_equal(x, y) for x, y in zip(a, b))
         print("  match_descriptors 3000x2500 equal:", ok, flush=True)
         total_bad += 0 if ok else 1
+        for gen, gname in ((syn.bf_correlated, "correlated"), (syn.bf_tie_heavy, "ties")):
+            q2, t2 = gen(2100, 1900, 21)
+            for md, ra in ((64.0, 0.75), (30.0, 0.9), (100.0, 0.5), (200.0, 0.8), (64.0, 1.5), (0.0, 0.75), (63.5, 0.7)):
+                a, b = ci.match_descriptors(q2, t2, md, ra), ct.match_descriptors(q2, t2, md, ra)
+                ok = all(np.array_equal(x, y) for x, y in zip(a, b))
+                if not ok:
+                    print(f"  match_descriptors {gname} max_dist {md} ratio {ra}: MISMATCH ({len(a[0])} vs {len(b[0])})", flush=True)
+                    total_bad += 1
+            for md in (64.0, 20.0, 63.5, 1.0, 300.0):
+                a, b = ci.match_features(t2, q2, md), ct.match_features(t2, q2, md)
+                ok = all(np.array_equal(x, y) for x, y in zip(a, b))
+                if not ok:
+                    print(f"  match_features {gname} max_dist {md}: MISMATCH ({len(a[0])} vs {len(b[0])})", flush=True)
+                    total_bad += 1
+        print("  filter sweeps done, bad so far:", total_bad, flush=True)
         a, b = ci.crosscheck(q, t), ct.crosscheck(q, t)
         ok = all(np.array_equal(x, y) for x, y in zip(a, b))
         print("  crosscheck 3000x2500 equal:", ok, flush=True)
@@ -129,28 +144,27 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--variant", type=int, default=None)
     ap.add_argument("--quick", action="store_true")
-    ap.add_argument("--variants", default="0,1")
+    ap.add_argument("--variants", default="0,2")
     args = ap.parse_args()
     if args.variant is not None:
         sys.exit(1 if run_variant(args.variant, args.quick) else 0)
-    good = None
     for v in [int(x) for x in args.variants.split(",")]:
         print(f"=== variant {v} (quick)", flush=True)
         t0 = time.time()
         try:
             r = subprocess.run([sys.executable, __file__, "--variant", str(v), "--quick"], timeout=150)
             print(f"=== variant {v}: exit {r.returncode} in {time.time() - t0:.0f} s", flush=True)
-            if r.returncode == 0 and good is None:
-                good = v
+            if r.returncode != 0:
+                continue
         except subprocess.TimeoutExpired:
             print(f"=== variant {v}: TIMEOUT", flush=True)
-    if good is not None:
-        print(f"=== variant {good} (full)", flush=True)
+            continue
+        print(f"=== variant {v} (full)", flush=True)
         try:
-            r = subprocess.run([sys.executable, __file__, "--variant", str(good)], timeout=400)
-            print(f"=== full: exit {r.returncode}", flush=True)
+            r = subprocess.run([sys.executable, __file__, "--variant", str(v)], timeout=400)
+            print(f"=== variant {v} full: exit {r.returncode}", flush=True)
         except subprocess.TimeoutExpired:
-            print("=== full: TIMEOUT", flush=True)
+            print(f"=== variant {v} full: TIMEOUT", flush=True)
 
 
 if __name__ == "__main__":
