@@ -81,26 +81,47 @@ size_t tc_pair_keys(const slamgpu_ctx* ctx, const BfPlan& plan, int nq)
     return static_cast<size_t>(plan.splits) * bf_tc_partials(ctx) * nq;
 }
 
-int tc_expand_pair(slamgpu_ctx* ctx, const uint8_t* dq, int nq, const uint8_t* dt, int nt, int* pitch_rows)
+// Filtered calls (a distance cut exists) run on the block-scaled FP4 kernel (bf_tc4_kernels.cu), exact
+// kNN-2 on the int8 kernel (bf_tc_kernels.cu).  SLAMGPU_TC_VARIANT bit 6 keeps filtered calls on int8 (A/B).
+bool use_fp4(const slamgpu_ctx* ctx, int d_cut) { return d_cut <= 250 && !(ctx->tc_variant & 64); }
+
+BfPlan tc_plan(const slamgpu_ctx* ctx, int nq, int nt, int64_t n_pairs, bool fp4)
 {
-    const int pitch = bf_tc_pitch_rows(std::max(nq, nt));
-    SG_TRY(ensure_device_exp(ctx, bf_tc_expanded_bytes(2, std::max(nq, nt))));
+    return fp4 ? bf_tc4_make_plan(ctx, nq, nt, n_pairs) : bf_tc_make_plan(ctx, nq, nt, n_pairs);
+}
+
+int tc_expand_pair(slamgpu_ctx* ctx, const uint8_t* dq, int nq, const uint8_t* dt, int nt, bool fp4, int* pitch_rows)
+{
+    const int m = std::max(nq, nt);
+    const int pitch = fp4 ? bf_tc4_pitch_rows(m) : bf_tc_pitch_rows(m);
+    const size_t set_bytes = fp4 ? bf_tc4_expanded_bytes(1, m) : bf_tc_expanded_bytes(1, m);
+    SG_TRY(ensure_device_exp(ctx, 2 * set_bytes));
     uint8_t* e = static_cast<uint8_t*>(ctx->d_exp.ptr);
-    SG_TRY(bf_tc_launch_expand(ctx, dq, nullptr, 1, nq, nq, pitch, e));
-    SG_TRY(bf_tc_launch_expand(ctx, dt, nullptr, 1, nt, nt, pitch, e + bf_tc_expanded_bytes(1, std::max(nq, nt))));
+    if (fp4) {
+        SG_TRY(bf_tc4_launch_expand(ctx, dq, nullptr, 1, nq, pitch, e));
+        SG_TRY(bf_tc4_launch_expand(ctx, dt, nullptr, 1, nt, pitch, e + set_bytes));
+    } else {
+        SG_TRY(bf_tc_launch_expand(ctx, dq, nullptr, 1, nq, nq, pitch, e));
+        SG_TRY(bf_tc_launch_expand(ctx, dt, nullptr, 1, nt, nt, pitch, e + set_bytes));
+    }
     *pitch_rows = pitch;
     return SLAMGPU_OK;
 }
 
 // scan query-set `qi` against train-set `ti` (0 or 1: the two expanded sets of tc_expand_pair)
-int tc_scan_pair(slamgpu_ctx* ctx, int qi, int nq, int ti, int nt, int pitch_rows, int d_cut, uint2* keys, TcPair& out)
+int tc_scan_pair(slamgpu_ctx* ctx, int qi, int nq, int ti, int nt, int pitch_rows, int d_cut, bool fp4, uint2* keys,
+                 TcPair& out)
 {
-    out.plan = bf_tc_make_plan(ctx, nq, nt, 1);
+    out.plan = tc_plan(ctx, nq, nt, 1, fp4);
     out.fin = out.plan;
     out.fin.splits = out.plan.splits * bf_tc_partials(ctx);
     out.keys = keys;
     const uint8_t* e = static_cast<const uint8_t*>(ctx->d_exp.ptr);
-    const size_t set_bytes = static_cast<size_t>(pitch_rows) * 256;
+    const size_t set_bytes = static_cast<size_t>(pitch_rows) * (fp4 ? 128 : 256);
+    if (fp4) {
+        return bf_tc4_launch_scan(ctx, out.plan, e + qi * set_bytes, nq, e + ti * set_bytes, nt, pitch_rows, nullptr,
+                                  nullptr, 1, nq, d_cut, keys);
+    }
     return bf_tc_launch_scan(ctx, out.plan, e + qi * set_bytes, nq, e + ti * set_bytes, nt, pitch_rows, nullptr, nullptr,
                              1, nq, d_cut, keys);
 }
@@ -116,11 +137,11 @@ int knn2_core(slamgpu_ctx* ctx, const uint8_t* dq, int nq, const uint8_t* dt, in
     }
     if (use_tc(ctx, nq, nt, 1)) {
         int pitch = 0;
-        SG_TRY(tc_expand_pair(ctx, dq, nq, dt, nt, &pitch));
-        const BfPlan tp = bf_tc_make_plan(ctx, nq, nt, 1);
+        SG_TRY(tc_expand_pair(ctx, dq, nq, dt, nt, false, &pitch));
+        const BfPlan tp = tc_plan(ctx, nq, nt, 1, false);
         SG_TRY(ensure_device_ws(ctx, Carver::padded(tc_pair_keys(ctx, tp, nq) * sizeof(uint2))));
         TcPair r;
-        SG_TRY(tc_scan_pair(ctx, 0, nq, 1, nt, pitch, kNoCut, static_cast<uint2*>(ctx->d_ws.ptr), r));
+        SG_TRY(tc_scan_pair(ctx, 0, nq, 1, nt, pitch, kNoCut, false, static_cast<uint2*>(ctx->d_ws.ptr), r));
         return bf_launch_finish_raw(ctx, r.fin, r.keys, nq, nt, nq, d_idx, d_dist);
     }
     const BfPlan plan = bf_make_plan(ctx->n_sm, nq, nt, 1);
@@ -144,18 +165,19 @@ int crosscheck_core(slamgpu_ctx* ctx, const uint8_t* dq, int nq, const uint8_t* 
     if (nq >= 512 && use_tc(ctx, nq, nt, 1) &&
         (ctx->bf_engine == 2 || static_cast<int64_t>(nq) * nt >= kTcMinComparisonsCross)) {
         // tensor cores: two scans over the same expanded sets, rows (q -> t) and columns (t -> q)
+        const int cut = cut_for_crosscheck(strict_max_dist);
+        const bool fp4 = use_fp4(ctx, cut);
         int pitch = 0;
-        SG_TRY(tc_expand_pair(ctx, dq, nq, dt, nt, &pitch));
-        const BfPlan rp = bf_tc_make_plan(ctx, nq, nt, 1), cp = bf_tc_make_plan(ctx, nt, nq, 1);
+        SG_TRY(tc_expand_pair(ctx, dq, nq, dt, nt, fp4, &pitch));
+        const BfPlan rp = tc_plan(ctx, nq, nt, 1, fp4), cp = tc_plan(ctx, nt, nq, 1, fp4);
         SG_TRY(ensure_device_ws(ctx, Carver::padded(tc_pair_keys(ctx, rp, nq) * sizeof(uint2)) +
                                          Carver::padded(tc_pair_keys(ctx, cp, nt) * sizeof(uint2))));
         Carver ws(ctx->d_ws.ptr);
         uint2* row_keys = ws.take<uint2>(tc_pair_keys(ctx, rp, nq));
         uint2* col_keys = ws.take<uint2>(tc_pair_keys(ctx, cp, nt));
         TcPair r, c;
-        const int cut = cut_for_crosscheck(strict_max_dist);
-        SG_TRY(tc_scan_pair(ctx, 0, nq, 1, nt, pitch, cut, row_keys, r));
-        SG_TRY(tc_scan_pair(ctx, 1, nt, 0, nq, pitch, cut, col_keys, c));
+        SG_TRY(tc_scan_pair(ctx, 0, nq, 1, nt, pitch, cut, fp4, row_keys, r));
+        SG_TRY(tc_scan_pair(ctx, 1, nt, 0, nq, pitch, cut, fp4, col_keys, c));
         return bf_launch_mutual(ctx, r.fin, r.keys, nq, c.fin, c.keys, nt, nq, nt, strict_max_dist, d_idx, d_dist);
     }
     // one scan: per-row top-1 partials and, in the same pass, per-column minima (atomicMin)
@@ -180,13 +202,14 @@ int match_descriptors_core(slamgpu_ctx* ctx, const uint8_t* dq, int nq, const ui
         return SLAMGPU_OK;
     }
     if (use_tc(ctx, nq, nt, 1)) {
+        const int cut = cut_for_filter(max_dist, ratio);
+        const bool fp4 = use_fp4(ctx, cut);
         int pitch = 0;
-        SG_TRY(tc_expand_pair(ctx, dq, nq, dt, nt, &pitch));
-        const BfPlan tp = bf_tc_make_plan(ctx, nq, nt, 1);
+        SG_TRY(tc_expand_pair(ctx, dq, nq, dt, nt, fp4, &pitch));
+        const BfPlan tp = tc_plan(ctx, nq, nt, 1, fp4);
         SG_TRY(ensure_device_ws(ctx, Carver::padded(tc_pair_keys(ctx, tp, nq) * sizeof(uint2))));
         TcPair r;
-        SG_TRY(tc_scan_pair(ctx, 0, nq, 1, nt, pitch, cut_for_filter(max_dist, ratio), static_cast<uint2*>(ctx->d_ws.ptr),
-                            r));
+        SG_TRY(tc_scan_pair(ctx, 0, nq, 1, nt, pitch, cut, fp4, static_cast<uint2*>(ctx->d_ws.ptr), r));
         return bf_launch_finish_filter(ctx, r.fin, r.keys, nq, nt, nullptr, nullptr, 1, nq, max_dist, ratio, d_out_train,
                                        d_out_count);
     }
@@ -215,16 +238,26 @@ int batch_core(slamgpu_ctx* ctx, const uint8_t* d_desc, const int32_t* d_frame_o
         return SLAMGPU_OK;
     }
     const bool tc = use_tc(ctx, max_rows, max_rows, n_pairs);
-    BfPlan plan = tc ? bf_tc_make_plan(ctx, max_rows, max_rows, std::min(n_pairs, slice_pairs))
+    const int cut = cut_for_filter(max_dist, ratio);
+    const bool fp4 = tc && use_fp4(ctx, cut);
+    BfPlan plan = tc ? tc_plan(ctx, max_rows, max_rows, std::min(n_pairs, slice_pairs), fp4)
                      : bf_make_plan(ctx->n_sm, max_rows, max_rows, std::min(n_pairs, slice_pairs));
     BfPlan fin = plan;
     int pitch = 0;
     if (tc) {   // every frame expanded once per call; the scans then read only the expanded copy
         fin.splits = plan.splits * bf_tc_partials(ctx);
-        pitch = bf_tc_pitch_rows(max_rows);
-        SG_TRY(ensure_device_exp(ctx, bf_tc_expanded_bytes(n_frames, max_rows)));
-        SG_TRY(bf_tc_launch_expand(ctx, d_desc, d_frame_offset, n_frames, 0, max_rows, pitch,
-                                   static_cast<uint8_t*>(ctx->d_exp.ptr)));
+        uint8_t* e = nullptr;
+        if (fp4) {
+            pitch = bf_tc4_pitch_rows(max_rows);
+            SG_TRY(ensure_device_exp(ctx, bf_tc4_expanded_bytes(n_frames, max_rows)));
+            e = static_cast<uint8_t*>(ctx->d_exp.ptr);
+            SG_TRY(bf_tc4_launch_expand(ctx, d_desc, d_frame_offset, n_frames, 0, pitch, e));
+        } else {
+            pitch = bf_tc_pitch_rows(max_rows);
+            SG_TRY(ensure_device_exp(ctx, bf_tc_expanded_bytes(n_frames, max_rows)));
+            e = static_cast<uint8_t*>(ctx->d_exp.ptr);
+            SG_TRY(bf_tc_launch_expand(ctx, d_desc, d_frame_offset, n_frames, 0, max_rows, pitch, e));
+        }
     }
     const size_t per_pair = bf_partial_elems(fin, 1, max_rows);
     SG_TRY(ensure_device_ws(ctx, Carver::padded(per_pair * sizeof(uint2) * std::min(n_pairs, slice_pairs))));
@@ -237,8 +270,11 @@ int batch_core(slamgpu_ctx* ctx, const uint8_t* d_desc, const int32_t* d_frame_o
         int32_t* out_train = d_offset ? d_out_train : d_out_train + static_cast<size_t>(p0) * max_rows;
         if (tc) {
             const uint8_t* e = static_cast<const uint8_t*>(ctx->d_exp.ptr);
-            SG_TRY(bf_tc_launch_scan(ctx, plan, e, 0, e, 0, pitch, d_frame_offset, pairs, np, max_rows,
-                                     cut_for_filter(max_dist, ratio), keys));
+            if (fp4) {
+                SG_TRY(bf_tc4_launch_scan(ctx, plan, e, 0, e, 0, pitch, d_frame_offset, pairs, np, max_rows, cut, keys));
+            } else {
+                SG_TRY(bf_tc_launch_scan(ctx, plan, e, 0, e, 0, pitch, d_frame_offset, pairs, np, max_rows, cut, keys));
+            }
         } else {
             SG_TRY(bf_launch_scan(ctx, plan, d_desc, 0, d_desc, 0, d_frame_offset, pairs, np, max_rows, false, keys));
         }

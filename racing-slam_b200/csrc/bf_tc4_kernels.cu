@@ -1,0 +1,717 @@
+// bf_tc4_kernels.cu -- filtered brute-force Hamming scan on the block-scaled FP4 tensor cores (sm_100a).
+//
+// For match_descriptors (src/MapMatcher.cpp:129-163) and match_features
+// (src/features/FeatureExtractor.cpp:15-30) only train rows within a distance cut can change the result
+// (bf_api.cu: cut_for_filter / cut_for_crosscheck), so the scan only has to FIND those rows.  Two facts
+// measured on the int8 CTA-pair kernel (bf_tc_kernels.cu, profiles/r01_ncu_full_bf_tc_scan_v2.txt) shape
+// this kernel: the int8 MMAs already run at 95 % of the int8 peak, and reading the 32-bit accumulators
+// out of TMEM (~128 B/clk/SM) takes as long as computing them.  Hence
+//   * tcgen05.mma.cta_group::2.kind::mxf4.block_scale: every descriptor bit is one E2M1 value (+1 / -1),
+//     K = 64 per MMA at the int8 cadence -> twice the comparisons per tensor-pipe cycle;
+//   * TWO train rows per accumulator column: the K = 256 of train row cb + c runs with block scale 2^0 and
+//     is followed by the K = 256 of train row cb + 240 + c with UE8M0 block scale 2^10 into the same
+//     accumulator, acc = dot1 + 1024 * dot2 (exact in fp32, |dot| <= 256) -> half the TMEM read-out per
+//     comparison.  The scale factors are constants, so their TMEM columns are filled once with tcgen05.st;
+//   * one more K = 64 MMA per tile adds the constant 1.5 * 2^23 + 512 - 1025 * T (T = the dot threshold of the
+//     cut), so the bits of the accumulator are the integer u = 0x4B400000 + (dot1 - T + 512) + 1024 * (dot2 - T)
+//     and "dot2 >= T", "dot1 >= T" are bit 22 and bit 9 of u: the epilogue ORs 16 accumulators with 8 LOP3 and
+//     tests two bits; only on a hit are the two dots decoded and folded as (distance << 22 | train index) keys.
+// Layout, warp roles and the barrier protocol are those of the int8 CTA-pair kernel: 2 CTAs share a
+// 256-query x 240-column tile (each loads 128 query rows and 120 + 120 train rows), warp 0 = bulk-copy
+// producer, warp 1 = MMA issue (leader) / completion relay (peer), warps 2..9 = epilogue.
+#include "slamgpu_internal.cuh"
+#include "bf_tc_common.cuh"
+
+namespace slamgpu {
+
+namespace {
+
+constexpr int kQ4 = 256;                     // query rows per cluster tile (UMMA M of the pair)
+constexpr int kN4 = 240;                     // accumulator columns per tile (UMMA N of the pair)
+constexpr int kT4 = 2 * kN4;                 // train rows per tile
+constexpr int kRow4 = 128;                   // expanded descriptor: 256 x E2M1 = 128 bytes
+constexpr int kGroup4 = 8 * kRow4;           // 8 rows = 8 core matrices of 128 bytes
+constexpr int kA4Bytes = 128 * kRow4;        // this CTA's 128 query rows: 16 KB
+constexpr int kB4Half = (kN4 / 2) * kRow4;   // this CTA's 120 train rows of one K-half: 15 KB
+constexpr int kB4Bytes = 2 * kB4Half;        // both K-halves: 30 KB
+constexpr int kB4Stages = 4;
+constexpr int kTc4Threads = 64 + 8 * 32;
+constexpr int kOff4A = 0;                                  // 2 x 16 KB
+constexpr int kOff4B = 2 * kA4Bytes;                       // 4 x 30 KB
+constexpr int kOff4AX = kOff4B + kB4Stages * kB4Bytes;     // constant K = 64 slice of A: 128 rows x 32 B
+constexpr int kOff4BX = kOff4AX + 128 * 32;                // ... of B: this CTA's 120 rows x 32 B (4 KB reserved)
+constexpr int kOff4AY = kOff4BX + 128 * 32;                // second constant slice (the small part), same shapes
+constexpr int kOff4BY = kOff4AY + 128 * 32;
+constexpr int kOff4Bar = kOff4BY + 128 * 32;               // 24 mbarriers
+constexpr int kOff4TmemSlot = kOff4Bar + 32 * 8;
+constexpr int kTc4SmemBytes = kOff4TmemSlot + 16;
+// TMEM columns: accumulator stage 0 at 0, stage 1 at 256, scale factors 1.0 at 496, 2^10 at 504, and the
+// constant slice's (2^0 for block 0, 2^7 for block 1) at 240
+constexpr uint32_t kAccStride = 256, kSfOne = 496, kSfBig = 504, kSfMix = 240;
+constexpr float kMagic = 12582912.0f;        // 1.5 * 2^23: bits(x + kMagic) = 0x4B400000 + x for integer |x| < 2^22
+constexpr int kMagicBits = 0x4B400000;
+
+// cute::UMMA::InstrDescriptorBlockScaled: a/b format E2M1 (MXF4Format 1) at [7,10) / [10,13), K-major,
+// N >> 3 at [17,23), scale format UE8M0 (1) at bit 23, M >> 4 at [24,29), scale-factor ids 0, K = 64 (bit 31 = 0)
+constexpr uint32_t kIdesc4 = (1u << 7) | (1u << 10) | (static_cast<uint32_t>(kN4 >> 3) << 17) | (1u << 23) |
+                             (static_cast<uint32_t>(kQ4 >> 4) << 24);
+
+__device__ __forceinline__ void tc4_mma(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc,
+                                        uint32_t accumulate, uint32_t tmem_sfa, uint32_t tmem_sfb)
+{
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::2.kind::mxf4.block_scale.block32 [%0], %1, %2, %3, [%5], [%6], p;\n\t}" ::"r"(tmem_d),
+        "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate), "r"(tmem_sfa), "r"(tmem_sfb)
+        : "memory");
+}
+
+template <int N>
+__device__ __forceinline__ void tmem_pin(uint32_t (&v)[N])
+{
+#pragma unroll
+    for (int i = 0; i < N; i += 8)
+        asm volatile("" : "+r"(v[i]), "+r"(v[i + 1]), "+r"(v[i + 2]), "+r"(v[i + 3]), "+r"(v[i + 4]), "+r"(v[i + 5]),
+                          "+r"(v[i + 6]), "+r"(v[i + 7])::"memory");
+}
+__device__ __forceinline__ void tmem_ld8(uint32_t taddr, uint32_t (&v)[8])
+{
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+                 : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7])
+                 : "r"(taddr)
+                 : "memory");
+}
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&v)[16])
+{
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+        : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
+          "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
+        : "r"(taddr)
+        : "memory");
+}
+__device__ __forceinline__ void tmem_st8(uint32_t taddr, uint32_t x)
+{
+    asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1, %1, %1, %1, %1, %1, %1, %1};" ::"r"(taddr), "r"(x)
+                 : "memory");
+}
+
+struct Tc4Args {
+    const uint8_t* exp_q;          // expanded (E2M1) descriptors of the query side
+    const uint8_t* exp_t;          // ... of the train side
+    long long frame_pitch_bytes;   // batched: expanded bytes per frame
+    const int32_t* frame_offset;   // batched: row offsets (row counts only); null = single pair
+    const int32_t* pairs;          // batched: [n_pairs x 2]
+    int nq, nt;                    // single pair
+    int tiles, splits, t_per_split;
+    int max_rows;
+    long long n_units;
+    int variant;
+    int thr_dot;                   // a train row matters iff dot = 256 - 2 * distance >= thr_dot
+    int thr4;                      // thr_dot rounded down to a multiple of 4: what the bit tests of the hot path use
+    uint2* keys;
+};
+
+struct Unit4 {
+    bool valid;
+    int pair, split, row0, nq, t_begin, n_btiles, t_end;
+    const uint8_t* q;
+    const uint8_t* t;
+};
+
+__device__ __forceinline__ Unit4 decode_unit4(const Tc4Args& a, long long u)
+{
+    Unit4 un;
+    const int tile = static_cast<int>(u % a.tiles);
+    u /= a.tiles;
+    un.split = static_cast<int>(u % a.splits);
+    un.pair = static_cast<int>(u / a.splits);
+    int nq = a.nq, nt = a.nt;
+    un.q = a.exp_q;
+    un.t = a.exp_t;
+    if (a.pairs != nullptr) {
+        const int fq = a.pairs[2 * un.pair], ft = a.pairs[2 * un.pair + 1];
+        nq = a.frame_offset[fq + 1] - a.frame_offset[fq];
+        nt = a.frame_offset[ft + 1] - a.frame_offset[ft];
+        un.q = a.exp_q + static_cast<long long>(fq) * a.frame_pitch_bytes;
+        un.t = a.exp_t + static_cast<long long>(ft) * a.frame_pitch_bytes;
+    }
+    un.nq = nq;
+    un.row0 = tile * kQ4;
+    un.t_begin = min(un.split * a.t_per_split, nt);
+    un.t_end = min(un.t_begin + a.t_per_split, nt);
+    un.n_btiles = (un.t_end - un.t_begin + kT4 - 1) / kT4;
+    un.valid = un.row0 < nq;
+    return un;
+}
+
+__device__ __forceinline__ int max3i(int a, int b, int c) { return max(max(a, b), c); }
+
+// ---- epilogue arithmetic --------------------------------------------------------------------------
+// The constant that the extra MMA adds is  C = 1.5 * 2^23 + 512 - 1025 * T4  (T4 = the dot threshold rounded
+// down to a multiple of 4), so the accumulator bits are
+//     u = 0x4B400000 + (dot1 - T4 + 512) + 1024 * (dot2 - T4),   0 <= dot1 - T4 + 512 < 1024,
+// and the two threshold tests are single bits:  dot2 >= T4 <=> bit 22 of u,  dot1 >= T4 <=> bit 9 of u.
+// Hot path per group of 16 accumulators: 8 three-input ORs (LOP3) and one test.  (The first versions took
+// per-accumulator FADD + shift + two VIMNMX3 trees: 3 ops instead of 0.5, and the epilogue, not the MMAs,
+// set the pace.)  A group with a hit is only PARKED in local memory (4 STL.128); the decoding runs once per
+// chunk as a rolled loop over the parked groups -- with the decode unrolled inline (92 KB of SASS) ncu
+// attributed 48 % of all stall samples to instruction fetch.
+constexpr uint32_t kHitBits = (1u << 22) | (1u << 9);
+
+__device__ __forceinline__ uint32_t or3(uint32_t a, uint32_t b, uint32_t c)
+{
+    uint32_t d;
+    asm("lop3.b32 %0, %1, %2, %3, 0xfe;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+    return d;
+}
+
+// N accumulators (columns col0 .. col0 + N - 1 of the tile): scan, park the groups of 16 that hit in `park`,
+// return the mask of parked groups
+template <int N>
+__device__ __forceinline__ uint32_t scan4(const uint32_t (&v)[N], int4* park)
+{
+    uint32_t mask = 0u;
+    if constexpr (N % 16 == 0) {
+#pragma unroll
+        for (int q = 0; q < N / 16; ++q) {
+            const uint32_t* x = &v[16 * q];
+            uint32_t r = or3(x[0], x[1], x[2]);
+            r = or3(r, x[3], x[4]);
+            r = or3(r, x[5], x[6]);
+            r = or3(r, x[7], x[8]);
+            r = or3(r, x[9], x[10]);
+            r = or3(r, x[11], x[12]);
+            r = or3(r, x[13], x[14]);
+            r |= x[15];
+            if (__builtin_expect((r & kHitBits) != 0u, 0)) {
+                mask |= 1u << q;
+#pragma unroll
+                for (int k = 0; k < 4; ++k) park[4 * q + k] = make_int4(x[4 * k], x[4 * k + 1], x[4 * k + 2], x[4 * k + 3]);
+            }
+        }
+    } else {        // N = 8: half a group, the other half parked as "no hit"
+        uint32_t r = or3(v[0], v[1], v[2]);
+        r = or3(r, v[3], v[4]);
+        r = or3(r, v[5], v[6]);
+        r |= v[7];
+        if (__builtin_expect((r & kHitBits) != 0u, 0)) {
+            mask = 1u;
+            park[0] = make_int4(v[0], v[1], v[2], v[3]);
+            park[1] = make_int4(v[4], v[5], v[6], v[7]);
+            park[2] = make_int4(0, 0, 0, 0);
+            park[3] = make_int4(0, 0, 0, 0);
+        }
+    }
+    return mask;
+}
+
+// one accumulator with a hit bit: both dots decoded, those within the exact cut folded as
+// (distance << 22 | train index); t1 = the train row of dot1, dot2 belongs to t1 + 240
+__device__ __forceinline__ void decode4_one(uint32_t u, int t1, int t_end, int thr_dot, int thr4, uint32_t& b0,
+                                            uint32_t& b1)
+{
+    const int x = static_cast<int>(u) - kMagicBits;
+    const int dot2 = (x >> 10) + thr4;
+    const int dot1 = (x & 1023) - 512 + thr4;
+    const int t2 = t1 + kN4;
+    const uint32_t k1 = dot1 >= thr_dot && t1 < t_end
+                            ? (static_cast<uint32_t>(256 - dot1) >> 1 << kIdxBits) | static_cast<uint32_t>(t1)
+                            : kKeyNone;
+    const uint32_t k2 = dot2 >= thr_dot && t2 < t_end
+                            ? (static_cast<uint32_t>(256 - dot2) >> 1 << kIdxBits) | static_cast<uint32_t>(t2)
+                            : kKeyNone;
+    const uint32_t lo = min(k1, k2), hi = max(k1, k2);
+    const uint32_t top = max(lo, b0);
+    b0 = min(lo, b0);
+    b1 = min(min(b1, top), hi);
+}
+
+__device__ __forceinline__ void decode4(const int4* park, uint32_t mask, int t1_first, int t_end, int thr_dot, int thr4,
+                                        uint32_t& b0, uint32_t& b1)
+{
+#pragma unroll 1
+    while (mask != 0u) {
+        const int q = __ffs(mask) - 1;
+        mask &= mask - 1u;
+#pragma unroll 1
+        for (int k = 0; k < 4; ++k) {
+            const int4 x = park[4 * q + k];
+            const int t1 = t1_first + 16 * q + 4 * k;
+            if (static_cast<uint32_t>(x.x) & kHitBits) decode4_one(x.x, t1, t_end, thr_dot, thr4, b0, b1);
+            if (static_cast<uint32_t>(x.y) & kHitBits) decode4_one(x.y, t1 + 1, t_end, thr_dot, thr4, b0, b1);
+            if (static_cast<uint32_t>(x.z) & kHitBits) decode4_one(x.z, t1 + 2, t_end, thr_dot, thr4, b0, b1);
+            if (static_cast<uint32_t>(x.w) & kHitBits) decode4_one(x.w, t1 + 3, t_end, thr_dot, thr4, b0, b1);
+        }
+    }
+}
+
+// The constant slices.  Element i of a 32-element block holds A = a(i), B = b(i) from the E2M1 values
+// {0, 0.5, 1, 1.5, 2, 3, 4, 6} such that the block's sum of a * b is target4 / 4:
+//   block at scale 2^14: (3072 - T4 / 4) / 4 = 768 - T4 / 16   ->  1.5 * 2^23 - 1024 * T4
+//   block at scale 2^0 : 512 - T4                               (256 .. 756)
+// Greedy: n elements of 6 * 6, then 6 * q (q < 6, as 6*q or 6*2 + 6*3), 1 * s (s < 6, as s or 2 + 3) and
+// 0.5 * {0.5, 1, 1.5} for the quarters.  Values are returned doubled (0.5 -> 1 ... 6 -> 12).
+__device__ __forceinline__ void magic_pair(int target4, int i, int& a2, int& b2)
+{
+    const int n36 = target4 / 144, rem4 = target4 % 144, ip = rem4 / 4, f = rem4 % 4, q = ip / 6, sv = ip % 6;
+    a2 = 0;
+    b2 = 0;
+    if (i < n36) {
+        a2 = 12;
+        b2 = 12;
+    } else if (i == n36) {
+        a2 = 12;
+        b2 = 2 * (q == 5 ? 2 : q);
+    } else if (i == n36 + 1) {
+        a2 = 12;
+        b2 = q == 5 ? 6 : 0;
+    } else if (i == n36 + 2) {
+        a2 = 2;
+        b2 = 2 * (sv == 5 ? 2 : sv);
+    } else if (i == n36 + 3) {
+        a2 = 2;
+        b2 = sv == 5 ? 6 : 0;
+    } else if (i == n36 + 4) {
+        a2 = 1;
+        b2 = f;        // 0.5 * {0, 0.5, 1, 1.5}
+    }
+}
+__device__ __forceinline__ uint32_t e2m1_code2(int v2)      // doubled value 0, 1, 2, 3, 4, 6, 8, 12 -> E2M1 bits
+{
+    return v2 <= 4 ? static_cast<uint32_t>(v2) : v2 == 6 ? 5u : v2 == 8 ? 6u : 7u;
+}
+
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTc4Threads, 1) bf_tc4_scan_kernel(const Tc4Args a)
+{
+    extern __shared__ __align__(1024) uint8_t smem[];
+    const uint32_t sbase = smem_u32(smem);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t rank = cluster_ctarank();
+    const uint32_t bar = sbase + kOff4Bar;
+    auto A_FULL = [&](uint32_t s) { return bar + 8u * s; };                  // [2] local bulk-copy bytes
+    auto B_FULL = [&](uint32_t s) { return bar + 8u * (2 + s); };            // [4]
+    auto PEER_A_FULL = [&](uint32_t s) { return bar + 8u * (6 + s); };       // [2] leader only: the peer's relay
+    auto PEER_B_FULL = [&](uint32_t s) { return bar + 8u * (8 + s); };       // [4]
+    auto A_EMPTY = [&](uint32_t s) { return bar + 8u * (12 + s); };          // [2] multicast commit
+    auto B_EMPTY = [&](uint32_t s) { return bar + 8u * (14 + s); };          // [4]
+    auto ACC_FULL = [&](uint32_t s) { return bar + 8u * (18 + s); };         // [2] multicast commit
+    auto ACC_EMPTY = [&](uint32_t s) { return bar + 8u * (20 + s); };        // [2] leader only: 16 epilogue warps
+    volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(smem + kOff4TmemSlot);
+
+    if (threadIdx.x == 0) {
+        for (uint32_t s = 0; s < 2; ++s) {
+            mbar_init(A_FULL(s), 1);
+            mbar_init(PEER_A_FULL(s), 1);
+            mbar_init(A_EMPTY(s), 1);
+            mbar_init(ACC_FULL(s), 1);
+            mbar_init(ACC_EMPTY(s), 16);
+        }
+        for (uint32_t s = 0; s < kB4Stages; ++s) {
+            mbar_init(B_FULL(s), 1);
+            mbar_init(PEER_B_FULL(s), 1);
+            mbar_init(B_EMPTY(s), 1);
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    // The constant slice (see magic_pair): one extra K = 64 MMA per tile adds 1.5 * 2^23 + 512 - 1025 * T4, so the
+    // epilogue reads integers whose bits 22 and 9 are the two threshold tests -- no FADD, no shift, no min/max.
+    // Canonical layout: 8-row group = [k-chunk 0..1][row][16 B]; k-chunk c holds elements 32 c .. 32 c + 31 = block c.
+    // Two slices, because one MMA must not mix magnitudes: with both blocks in one MMA the small block lost its
+    // low bits (the products of one instruction are aligned to the largest before they are added).
+    //   slice X: block 1 only -> (768 - T4 / 16) * 2^14       slice Y: block 0 only -> 512 - T4
+    for (int i = threadIdx.x; i < 4 * 128 * 32 / 16; i += kTc4Threads) {
+        const int tile = i / (128 * 32 / 16);       // 0: AX  1: BX  2: AY  3: BY
+        const int e = i % (128 * 32 / 16);
+        const int chunk = (e >> 3) & 1;
+        const bool is_a = (tile & 1) == 0, is_y = tile >= 2;
+        const int target4 = is_y ? 4 * (512 - a.thr4) : 3072 - a.thr4 / 4;
+        uint32_t wds[4] = {0u, 0u, 0u, 0u};
+        if (chunk == (is_y ? 0 : 1)) {
+#pragma unroll
+            for (int n = 0; n < 32; ++n) {          // element n of the block -> nibble n of the 16 bytes
+                int av, bv;
+                magic_pair(target4, n, av, bv);
+                wds[n >> 3] |= e2m1_code2(is_a ? av : bv) << (4 * (n & 7));
+            }
+        }
+        const int off = tile == 0 ? kOff4AX : tile == 1 ? kOff4BX : tile == 2 ? kOff4AY : kOff4BY;
+        *reinterpret_cast<uint4*>(smem + off + e * 16) = make_uint4(wds[0], wds[1], wds[2], wds[3]);
+    }
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    if (warp == 1) {
+        asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(sbase + kOff4TmemSlot),
+                     "r"(512u)
+                     : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+    // constant scale factors (UE8M0): 2^0 = 0x7F, 2^10 = 0x89, in every byte of 8 columns each, all 128 lanes
+    if (warp >= 2 && warp < 6) {
+        const uint32_t lane_base = static_cast<uint32_t>((warp & 3) * 32) << 16;
+        tmem_st8(tmem_base + lane_base + kSfOne, 0x7F7F7F7Fu);
+        tmem_st8(tmem_base + lane_base + kSfBig, 0x89898989u);
+        tmem_st8(tmem_base + lane_base + kSfMix, 0x867F867Fu);     // byte b = scale of K-block b: 2^0, 2^7 (A and B: 2^14)
+        asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+    }
+    tc_fence_before();
+    __syncthreads();
+    cluster_sync_all();            // both CTAs' barriers and scale factors are in place
+    tc_fence_after();
+
+    const long long n_clusters = gridDim.x >> 1, cid = blockIdx.x >> 1;
+    if (warp == 0) {
+        // ===== producer: this CTA's 128 query rows; per tile its 120 rows of each K-half =====
+        if (lane == 0) {
+            uint32_t a_it = 0, b_it = 0;
+            for (long long u = cid; u < a.n_units; u += n_clusters) {
+                const Unit4 un = decode_unit4(a, u);
+                if (!un.valid) continue;
+                const uint32_t sa = a_it & 1u;
+                mbar_wait(A_EMPTY(sa), ((a_it >> 1) & 1u) ^ 1u);
+                mbar_expect_tx(A_FULL(sa), kA4Bytes);
+                bulk_g2s(sbase + kOff4A + sa * kA4Bytes, un.q + static_cast<long long>(un.row0 + rank * 128) * kRow4,
+                         kA4Bytes, A_FULL(sa));
+                ++a_it;
+                for (int bt = 0; bt < un.n_btiles; ++bt) {
+                    const uint32_t sb = b_it & (kB4Stages - 1);
+                    mbar_wait(B_EMPTY(sb), ((b_it / kB4Stages) & 1u) ^ 1u);
+                    mbar_expect_tx(B_FULL(sb), kB4Bytes);
+                    const uint8_t* ts = un.t + static_cast<long long>(un.t_begin + bt * kT4 + rank * (kN4 / 2)) * kRow4;
+                    const uint32_t dst = sbase + kOff4B + sb * kB4Bytes;
+                    bulk_g2s(dst, ts, kB4Half, B_FULL(sb));                                             // rows cb + c
+                    bulk_g2s(dst + kB4Half, ts + static_cast<long long>(kN4) * kRow4, kB4Half, B_FULL(sb));   // rows cb + 240 + c
+                    ++b_it;
+                }
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0 && rank == 0) {
+            // ===== MMA issuer: one thread of the leader CTA, for the pair =====
+            const uint32_t sf_one = tmem_base + kSfOne, sf_big = tmem_base + kSfBig, sf_mix = tmem_base + kSfMix;
+            const uint64_t desc_ax = umma_desc(sbase + kOff4AX, 128u, 256u), desc_bx = umma_desc(sbase + kOff4BX, 128u, 256u);
+            const uint64_t desc_ay = umma_desc(sbase + kOff4AY, 128u, 256u), desc_by = umma_desc(sbase + kOff4BY, 128u, 256u);
+            uint32_t a_it = 0, b_it = 0, c_it = 0;
+            for (long long u = cid; u < a.n_units; u += n_clusters) {
+                const Unit4 un = decode_unit4(a, u);
+                if (!un.valid) continue;
+                const uint32_t sa = a_it & 1u;
+                mbar_wait(A_FULL(sa), (a_it >> 1) & 1u);
+                mbar_wait(PEER_A_FULL(sa), (a_it >> 1) & 1u);
+                for (int bt = 0; bt < un.n_btiles; ++bt) {
+                    const uint32_t sb = b_it & (kB4Stages - 1), sc = c_it & 1u;
+                    mbar_wait(ACC_EMPTY(sc), ((c_it >> 1) & 1u) ^ 1u);
+                    mbar_wait(B_FULL(sb), (b_it / kB4Stages) & 1u);
+                    mbar_wait(PEER_B_FULL(sb), (b_it / kB4Stages) & 1u);
+                    tc_fence_after();
+                    const uint32_t d = tmem_base + sc * kAccStride;
+                    const uint32_t a0 = sbase + kOff4A + sa * kA4Bytes, b0 = sbase + kOff4B + sb * kB4Bytes;
+                    if (!(a.variant & 4)) {       // timing experiments only: bit 2 skips the MMAs
+                        tc4_mma(d, desc_ax, desc_bx, kIdesc4, 0u, sf_mix, sf_mix);      // D = 1.5 * 2^23 - 1024 * T4
+                        tc4_mma(d, desc_ay, desc_by, kIdesc4, 1u, sf_one, sf_one);      // D += 512 - T4
+#pragma unroll
+                        for (int k = 0; k < 4; ++k)     // K = 64 values = 32 bytes = two 16-byte k-chunks per MMA
+                            tc4_mma(d, umma_desc(a0 + k * 256, 128u, kGroup4), umma_desc(b0 + k * 256, 128u, kGroup4),
+                                    kIdesc4, 1u, sf_one, sf_one);
+#pragma unroll
+                        for (int k = 0; k < 4; ++k)     // second train row of every column, scaled by 2^10
+                            tc4_mma(d, umma_desc(a0 + k * 256, 128u, kGroup4),
+                                    umma_desc(b0 + kB4Half + k * 256, 128u, kGroup4), kIdesc4, 1u, sf_one, sf_big);
+                    }
+                    tc2_commit_mc(B_EMPTY(sb));
+                    tc2_commit_mc(ACC_FULL(sc));
+                    ++b_it;
+                    ++c_it;
+                }
+                tc2_commit_mc(A_EMPTY(sa));
+                ++a_it;
+            }
+        } else if (lane == 0) {
+            // ===== relay (peer CTA): forward this CTA's bulk-copy completions to the leader =====
+            uint32_t a_it = 0, b_it = 0;
+            for (long long u = cid; u < a.n_units; u += n_clusters) {
+                const Unit4 un = decode_unit4(a, u);
+                if (!un.valid) continue;
+                const uint32_t sa = a_it & 1u;
+                mbar_wait(A_FULL(sa), (a_it >> 1) & 1u);
+                mbar_arrive_remote(PEER_A_FULL(sa), 0u);
+                ++a_it;
+                for (int bt = 0; bt < un.n_btiles; ++bt) {
+                    const uint32_t sb = b_it & (kB4Stages - 1);
+                    mbar_wait(B_FULL(sb), (b_it / kB4Stages) & 1u);
+                    mbar_arrive_remote(PEER_B_FULL(sb), 0u);
+                    ++b_it;
+                }
+            }
+        }
+    } else {
+        // ===== epilogue: 8 warps = 4 TMEM lane quadrants x 2 column halves of 120 =====
+        // Software-pipelined across tiles: a warp's 120 columns are read as chunk A (64) and chunk B (56);
+        // the tcgen05.ld of the next chunk -- of the next tile after chunk B -- is in flight while the current
+        // one is folded, so the TMEM read-out (~940 cycles per tile) and the arithmetic overlap.
+        const int quad = warp & 3;
+        const int g = (warp - 2) >> 2;
+        const int row_in_tile = static_cast<int>(rank) * 128 + quad * 32 + lane;
+        const uint32_t lane_col = (static_cast<uint32_t>(quad * 32) << 16) + static_cast<uint32_t>(g * 120);
+        const int c0 = g * 120;
+        const bool skip = (a.variant & 8) != 0;     // timing experiments only: bit 3 skips the TMEM reads and the fold
+
+        // tile stream of this cluster: (unit, train tile) in the order the MMA issuer produces them
+        long long u_cur = cid - n_clusters;
+        Unit4 un_cur;
+        un_cur.valid = false;
+        un_cur.n_btiles = 0;
+        int bt_cur = 0;
+        auto next_tile = [&](long long& u, Unit4& un, int& bt) -> bool {
+            if (un.valid && bt + 1 < un.n_btiles) {
+                ++bt;
+                return true;
+            }
+            for (;;) {
+                u += n_clusters;
+                if (u >= a.n_units) return false;
+                un = decode_unit4(a, u);
+                if (!un.valid) continue;
+                if (un.n_btiles == 0) {          // no train rows: the unit still owns its (empty) key records
+                    const int row = un.row0 + row_in_tile;
+                    if (row < un.nq)
+                        a.keys[((static_cast<size_t>(un.pair) * a.splits + un.split) * 2 + g) * a.max_rows + row] =
+                            make_uint2(kKeyNone, kKeyNone);
+                    continue;
+                }
+                bt = 0;
+                return true;
+            }
+        };
+
+        uint32_t va0[32], va1[32], vb0[32], vb1[16], vb2[8];
+        int4 park[16];                  // up to 4 parked groups of 16 accumulators (local memory)
+        uint32_t c_it = 0;
+        uint32_t b0 = kKeyNone, b1 = kKeyNone;
+        bool have = next_tile(u_cur, un_cur, bt_cur);
+        if (have) {
+            mbar_wait(ACC_FULL(0), 0u);
+            tc_fence_after();
+            if (!skip) {
+                tmem_ld32(tmem_base + lane_col, va0);
+                tmem_ld32(tmem_base + lane_col + 32, va1);
+            }
+        }
+        while (have) {
+            const uint32_t sc = c_it & 1u;
+            const uint32_t taddr = tmem_base + lane_col + sc * kAccStride;
+            const int cb = un_cur.t_begin + bt_cur * kT4;
+            const int t_end = (a.variant & 32) ? -1 : un_cur.t_end;     // timing experiments only: bit 5 disables the rare path
+            if (!skip) {
+                tmem_wait_ld();                  // chunk A of this tile has landed
+                tmem_pin(va0);
+                tmem_pin(va1);
+                tmem_ld32(taddr + 64, vb0);      // chunk B in flight while A is folded
+                tmem_ld16(taddr + 96, vb1);
+                tmem_ld8(taddr + 112, vb2);
+                const uint32_t ma = (a.variant & 128) ? 0u     // timing experiments only: bit 7 skips the scan arithmetic
+                                                      : scan4(va0, park) | (scan4(va1, park + 8) << 2);
+                if (__builtin_expect(ma != 0u && t_end >= 0, 0)) decode4(park, ma, cb + c0, t_end, a.thr_dot, a.thr4, b0, b1);
+                tmem_wait_ld();                  // chunk B has landed: every TMEM read of this stage is done
+                tmem_pin(vb0);
+                tmem_pin(vb1);
+                tmem_pin(vb2);
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) {
+                if (rank == 0) mbar_arrive(ACC_EMPTY(sc));
+                else mbar_arrive_remote(ACC_EMPTY(sc), 0u);
+            }
+            // look ahead: chunk A of the next tile in flight while chunk B of this one is folded
+            long long u_nxt = u_cur;
+            Unit4 un_nxt = un_cur;
+            int bt_nxt = bt_cur;
+            const bool last_of_unit = bt_cur + 1 == un_cur.n_btiles;
+            const bool have_nxt = next_tile(u_nxt, un_nxt, bt_nxt);
+            ++c_it;
+            if (have_nxt) {
+                const uint32_t sn = c_it & 1u;
+                mbar_wait(ACC_FULL(sn), (c_it >> 1) & 1u);
+                tc_fence_after();
+                if (!skip) {
+                    tmem_ld32(tmem_base + lane_col + sn * kAccStride, va0);
+                    tmem_ld32(tmem_base + lane_col + sn * kAccStride + 32, va1);
+                }
+            }
+            if (!skip) {
+                const uint32_t mb = (a.variant & 128) ? 0u
+                                                      : scan4(vb0, park) | (scan4(vb1, park + 8) << 2) | (scan4(vb2, park + 12) << 3);
+                if (__builtin_expect(mb != 0u && t_end >= 0, 0)) decode4(park, mb, cb + c0 + 64, t_end, a.thr_dot, a.thr4, b0, b1);
+            }
+            if (last_of_unit) {
+                const int row = un_cur.row0 + row_in_tile;
+                if (row < un_cur.nq) {
+                    a.keys[((static_cast<size_t>(un_cur.pair) * a.splits + un_cur.split) * 2 + g) * a.max_rows + row] =
+                        make_uint2(b0, b1);
+                }
+                b0 = kKeyNone;
+                b1 = kKeyNone;
+            }
+            have = have_nxt;
+            u_cur = u_nxt;
+            un_cur = un_nxt;
+            bt_cur = bt_nxt;
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    __syncwarp();
+    cluster_sync_all();            // the peer's shared memory and barriers stay alive until both CTAs are done
+    if (warp == 1) {
+        asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512u) : "memory");
+    }
+}
+
+// Expansion: N x 32-byte descriptors -> 256 x E2M1 (0x2 = +1.0 for a set bit, 0xA = -1.0 for a clear one),
+// 128 bytes per row, in the UMMA no-swizzle K-major canonical layout: inside a frame, rows are grouped by 8,
+//   byte address = (row / 8) * 1024 + word * 128 + (row % 8) * 16 + byte,   word = 0..7 (32 descriptor bits)
+// One thread = one (row, word).  Every row up to the frame pitch is written (zeros = +0.0 past the frame's
+// end): tiles may read past the end and a zero row has dot 0 with everything, never NaN.
+struct Expand4Args {
+    const uint8_t* src;
+    const int32_t* frame_offset;   // null: one set of n_rows rows
+    int n_rows;
+    int pitch_rows;
+    uint8_t* dst;
+};
+
+__device__ __forceinline__ uint32_t expand8_e2m1(uint32_t x)     // 8 bits -> 8 nibbles
+{
+    uint32_t t = x & 0xFFu;
+    t = (t | (t << 12)) & 0x000F000Fu;
+    t = (t | (t << 6)) & 0x03030303u;
+    t = (t | (t << 3)) & 0x11111111u;
+    return 0xAAAAAAAAu ^ (t << 3);
+}
+
+__global__ void __launch_bounds__(256) bf_tc4_expand_kernel(const Expand4Args a)
+{
+    const int frame = blockIdx.y;
+    int n = a.n_rows;
+    const uint8_t* src = a.src;
+    if (a.frame_offset != nullptr) {
+        const int o = a.frame_offset[frame];
+        n = a.frame_offset[frame + 1] - o;
+        src += static_cast<size_t>(o) * 32;
+    }
+    const int group = blockIdx.x * 4 + (threadIdx.x >> 6);       // four 8-row groups per CTA
+    if (group * 8 >= a.pitch_rows) return;
+    const int t = threadIdx.x & 63;
+    const int row = group * 8 + (t & 7), word = t >> 3;
+    uint4 v = make_uint4(0u, 0u, 0u, 0u);
+    if (row < n) {
+        const uint32_t bits = *reinterpret_cast<const uint32_t*>(src + static_cast<size_t>(row) * 32 + word * 4);
+        v.x = expand8_e2m1(bits);
+        v.y = expand8_e2m1(bits >> 8);
+        v.z = expand8_e2m1(bits >> 16);
+        v.w = expand8_e2m1(bits >> 24);
+    }
+    uint8_t* dst = a.dst + static_cast<long long>(frame) * a.pitch_rows * kRow4 + static_cast<size_t>(group) * kGroup4;
+    *reinterpret_cast<uint4*>(dst + word * 128 + (t & 7) * 16) = v;
+}
+
+} // namespace
+
+// rows per frame in the expanded buffer: whole query tiles (256) and whole train tiles (480)
+int bf_tc4_pitch_rows(int max_rows)
+{
+    const int a = ((max_rows + kQ4 - 1) / kQ4) * kQ4, b = ((max_rows + kT4 - 1) / kT4) * kT4;
+    return max(max(a, b), 8);
+}
+size_t bf_tc4_expanded_bytes(int n_frames, int max_rows)
+{
+    return static_cast<size_t>(n_frames) * bf_tc4_pitch_rows(max_rows) * kRow4;
+}
+
+BfPlan bf_tc4_make_plan(const slamgpu_ctx* ctx, int nq_max, int nt_max, int64_t n_pairs)
+{
+    BfPlan p;
+    const int slots = ctx->n_sm / 2;
+    p.r = 0;
+    p.tile = kQ4;
+    p.tiles = max(1, (nq_max + kQ4 - 1) / kQ4);
+    const int64_t units = static_cast<int64_t>(p.tiles) * n_pairs;
+    const int n_btiles = max(1, (nt_max + kT4 - 1) / kT4);
+    int64_t splits = units >= slots ? 1 : (slots + units - 1) / units;
+    splits = min(splits, static_cast<int64_t>(n_btiles));
+    const int tiles_per_split = static_cast<int>((n_btiles + splits - 1) / splits);
+    p.t_per_split = tiles_per_split * kT4;
+    p.splits = max(1, (n_btiles + tiles_per_split - 1) / tiles_per_split);
+    return p;
+}
+
+int bf_tc4_launch_expand(slamgpu_ctx* ctx, const uint8_t* d_src, const int32_t* d_frame_offset, int n_frames, int n_rows,
+                         int pitch_rows, uint8_t* d_dst)
+{
+    if (n_frames <= 0 || pitch_rows <= 0) return SLAMGPU_OK;
+    SG_CHECK(pitch_rows % 8 == 0, "bad expanded pitch");
+    Expand4Args a;
+    a.src = d_src;
+    a.frame_offset = d_frame_offset;
+    a.n_rows = n_rows;
+    a.pitch_rows = pitch_rows;
+    a.dst = d_dst;
+    const int groups = pitch_rows / 8;
+    for (int f0 = 0; f0 < n_frames; f0 += 65535) {     // gridDim.y limit
+        const int nf = min(65535, n_frames - f0);
+        Expand4Args b = a;
+        if (d_frame_offset) b.frame_offset = d_frame_offset + f0;
+        b.dst = d_dst + static_cast<long long>(f0) * pitch_rows * kRow4;
+        bf_tc4_expand_kernel<<<dim3((groups + 3) / 4, nf), 256, 0, ctx->stream>>>(b);
+        ctx->launches++;
+    }
+    SG_CUDA(cudaGetLastError());
+    return SLAMGPU_OK;
+}
+
+// Filtered scan over E2M1-expanded descriptors; writes 2 partials per (pair, split, row) like the int8 scans.
+// d_cut in [1, 256]: train rows at Hamming distance >= d_cut may be left out of the top-2.
+int bf_tc4_launch_scan(slamgpu_ctx* ctx, const BfPlan& plan, const uint8_t* d_exp_q, int nq, const uint8_t* d_exp_t,
+                       int nt, int pitch_rows, const int32_t* d_frame_offset, const int32_t* d_pairs, int n_pairs,
+                       int max_rows, int d_cut, uint2* d_keys)
+{
+    static bool attr_set = false;
+    if (!attr_set) {
+        SG_CUDA(cudaFuncSetAttribute(bf_tc4_scan_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kTc4SmemBytes));
+        attr_set = true;
+    }
+    SG_CHECK(d_cut >= 1 && d_cut <= 250, "the fp4 scan needs a distance cut of at most 250");
+    Tc4Args a;
+    a.exp_q = d_exp_q;
+    a.exp_t = d_exp_t;
+    a.frame_pitch_bytes = static_cast<long long>(pitch_rows) * kRow4;
+    a.frame_offset = d_frame_offset;
+    a.pairs = d_pairs;
+    a.nq = nq;
+    a.nt = nt;
+    a.tiles = plan.tiles;
+    a.splits = plan.splits;
+    a.t_per_split = plan.t_per_split;
+    a.max_rows = max_rows;
+    a.n_units = static_cast<long long>(plan.tiles) * plan.splits * n_pairs;
+    a.variant = ctx->tc_variant;
+    a.thr_dot = 256 - 2 * (d_cut - 1);                      // -242 .. 256
+    a.thr4 = (a.thr_dot + 256) / 4 * 4 - 256;               // rounded DOWN to a multiple of 4: -244 .. 256
+    a.keys = d_keys;
+    if (a.n_units <= 0) return SLAMGPU_OK;
+    const unsigned grid = 2u * static_cast<unsigned>(min(a.n_units, static_cast<long long>(ctx->n_sm / 2)));
+    ProfScope prof(ctx, SLAMGPU_KERNEL_BF_SCAN);
+    bf_tc4_scan_kernel<<<grid, kTc4Threads, kTc4SmemBytes, ctx->stream>>>(a);     // __cluster_dims__(2, 1, 1)
+    ctx->launches++;
+    SG_CUDA(cudaGetLastError());
+    return SLAMGPU_OK;
+}
+
+} // namespace slamgpu

@@ -171,6 +171,17 @@ int bf_tc_launch_scan(slamgpu_ctx* ctx, const BfPlan& plan, const uint8_t* d_exp
                       int max_rows, int d_cut, uint2* d_keys);
 int ensure_device_exp(slamgpu_ctx* ctx, size_t bytes);
 
+// ---- filtered brute force on the block-scaled FP4 tensor cores (bf_tc4_kernels.cu) --------------
+// Expanded descriptors: 256 E2M1 values (128 bytes) per row, frames at bf_tc4_pitch_rows(max_rows) rows.
+int bf_tc4_pitch_rows(int max_rows);
+size_t bf_tc4_expanded_bytes(int n_frames, int max_rows);
+BfPlan bf_tc4_make_plan(const slamgpu_ctx* ctx, int nq_max, int nt_max, int64_t n_pairs);
+int bf_tc4_launch_expand(slamgpu_ctx* ctx, const uint8_t* d_src, const int32_t* d_frame_offset, int n_frames, int n_rows,
+                         int pitch_rows, uint8_t* d_dst);
+int bf_tc4_launch_scan(slamgpu_ctx* ctx, const BfPlan& plan, const uint8_t* d_exp_q, int nq, const uint8_t* d_exp_t,
+                       int nt, int pitch_rows, const int32_t* d_frame_offset, const int32_t* d_pairs, int n_pairs,
+                       int max_rows, int d_cut, uint2* d_keys);
+
 // ---- projection (proj_kernels.cu) -----------------------------------------------------------
 struct ProjFrameArgs {
     int nkp;
