@@ -42,6 +42,7 @@ ALU_PER_CLK_PER_SM = 64                # LOP3 / VIMNMX lanes per clock per SM (n
 ALU_PER_COMPARISON = 17.5
 POPC_PER_COMPARISON_CSA = 4
 NCU_SCAN_DRAM_BYTES_512_PAIRS = 7.2e6  # profiles/r01_ncu_full_prof_bf_scan_v2.txt
+NCU_TC4_DRAM_BYTES_1024_PAIRS = 56.1e6  # profiles/r01_ncu_full_bf_tc4_scan.txt (read + write; mostly the partial-key records)
 
 
 def parse_args():
@@ -68,8 +69,10 @@ def load_peaks():
     if os.path.exists(path):
         with open(path) as f:
             p = json.load(f)
-        return dict(hbm_gbs=float(p["hbm_gbs"]), sm_max_mhz=float(p.get("sm_max_mhz", 1965.0)), source="measured")
-    return dict(hbm_gbs=6650.0, sm_max_mhz=1965.0, source="fallback")
+        return dict(hbm_gbs=float(p["hbm_gbs"]), sm_max_mhz=float(p.get("sm_max_mhz", 1965.0)),
+                    bf16_tflops=float(p.get("bf16_tflops", 1590.0)),
+                    bf16_tflops_sustained=float(p.get("bf16_tflops_sustained", 1400.0)), source="measured")
+    return dict(hbm_gbs=6650.0, sm_max_mhz=1965.0, bf16_tflops=1590.0, bf16_tflops_sustained=1400.0, source="fallback")
 
 
 class ClockSampler:
@@ -369,36 +372,55 @@ def run_ours(args, rank, local_rank, world):
 
     # ---- roofline of the dominant kernel (K1 brute-force scan), live CUDA-event durations ----
     avg_ms = scan_ms / max(scan_launches, 1)
-    cmp_per_launch = n * K * per_pair / max(scan_launches, 1)
+    pairs_per_launch = n * K / max(scan_launches, 1)
+    cmp_per_launch = pairs_per_launch * per_pair
     achieved = cmp_per_launch / (avg_ms * 1e-3) / 1e9
-    peak = int_peak_gcmp(n_sm, peaks["sm_max_mhz"])
-    popc8_peak = popc_peak_gcmp(n_sm, peaks["sm_max_mhz"])
-    bytes_per_launch = (n * K / max(scan_launches, 1)) * (2 * args.desc * 32 + args.desc * 8)
+    bytes_per_launch = pairs_per_launch * (2 * args.desc * 32 + args.desc * 8)
     hbm_achieved = bytes_per_launch / (avg_ms * 1e-3) / 1e9
-    roofline = {
-        "bound": "int-alu", "achieved": achieved, "peak": peak, "unit": "Gcmp/s", "frac": achieved / peak,
-        "traffic": NCU_SCAN_DRAM_BYTES_512_PAIRS * (n * K / max(scan_launches, 1)) / 512.0,
-        "traffic_basis": "ncu --set full dram__bytes_read+write of one 512-pair bf_scan_kernel launch "
-                         "(profiles/r01_ncu_full_prof_bf_scan_v2.txt: 7.2 MB read, 0 written), scaled to this launch's pair count",
-        "kernel": "bf_scan_kernel", "launches": scan_launches, "avg_launch_ms": avg_ms,
-        "share_of_step": scan_ms / ms_dev,
-        "peak_basis": f"integer pipes, not HBM/tensor (SURVEY 8d): {n_sm} SMs x {ALU_PER_CLK_PER_SM} ALU lanes/clk/SM x "
-                      f"{peaks['sm_max_mhz']:.0f} MHz / {ALU_PER_COMPARISON} ALU ops per 256-bit comparison "
-                      f"(8 xor + 8 carry-save LOP3 + 1.5 VIMNMX.U16x2); the XU pipe (4 POPC32/comparison at "
-                      f"{POPC_PER_CLK_PER_SM}/clk/SM) allows {n_sm * POPC_PER_CLK_PER_SM * peaks['sm_max_mhz'] * 1e6 / 4 / 1e9:.0f}",
-        "popc8": {"note": "SURVEY 8d / north-star denominator: XU pipe with the plain 8 POPC32 per comparison; the "
-                          "carry-save tree halves the POPC count, so this fraction may exceed 1",
-                  "peak": popc8_peak, "frac": achieved / popc8_peak},
-        "hbm": {"bound": "hbm", "achieved": hbm_achieved, "peak": peaks["hbm_gbs"], "unit": "GB/s",
+    hbm_view = {"bound": "hbm", "achieved": hbm_achieved, "peak": peaks["hbm_gbs"], "unit": "GB/s",
                 "frac": hbm_achieved / peaks["hbm_gbs"], "peak_source": peaks["source"],
-                "algorithmic_bytes_per_launch": bytes_per_launch},
-    }
-    if clocks and clocks.get("sm_mhz"):
-        roofline["frac_at_observed_clock"] = achieved / int_peak_gcmp(n_sm, clocks["sm_mhz"])
+                "algorithmic_bytes_per_launch": bytes_per_launch}
+    int_peak = int_peak_gcmp(n_sm, peaks["sm_max_mhz"])
+    popc8_peak = popc_peak_gcmp(n_sm, peaks["sm_max_mhz"])
+    if os.environ.get("SLAMGPU_BF_ENGINE") == "int":
+        roofline = {
+            "bound": "int-alu", "achieved": achieved, "peak": int_peak, "unit": "Gcmp/s", "frac": achieved / int_peak,
+            "traffic": NCU_SCAN_DRAM_BYTES_512_PAIRS * pairs_per_launch / 512.0,
+            "traffic_basis": "ncu --set full dram__bytes_read+write of one 512-pair bf_scan_kernel launch "
+                             "(profiles/r01_ncu_full_prof_bf_scan_v2.txt: 7.2 MB read, 0 written), scaled to this launch's pair count",
+            "kernel": "bf_scan_kernel", "launches": scan_launches, "avg_launch_ms": avg_ms,
+            "share_of_step": scan_ms / ms_dev,
+            "peak_basis": f"integer pipes: {n_sm} SMs x {ALU_PER_CLK_PER_SM} ALU lanes/clk/SM x {peaks['sm_max_mhz']:.0f} MHz / "
+                          f"{ALU_PER_COMPARISON} ALU ops per 256-bit comparison",
+            "popc8": {"peak": popc8_peak, "frac": achieved / popc8_peak}, "hbm": hbm_view,
+        }
+    else:
+        # tensor-core engine (default for this workload): one comparison = 256 multiply-adds = 512 flop on the
+        # block-scaled FP4 tensor cores.  Peak = 4 x the measured dense bf16 rate of MEASURED_PEAKS.json (fp4 : bf16
+        # = 9 : 2.25 PFLOP/s nominal); burst figure, the conservative denominator.
+        tflops = achieved * 1e9 * 512.0 / 1e12
+        peak_tf = 4.0 * peaks["bf16_tflops"]
+        roofline = {
+            "bound": "tensor", "achieved": tflops, "peak": peak_tf, "unit": "TFLOP/s", "frac": tflops / peak_tf,
+            "traffic": NCU_TC4_DRAM_BYTES_1024_PAIRS * pairs_per_launch / 1024.0,
+            "traffic_basis": "ncu --set full dram__bytes_read+write of one 1024-pair bf_tc4_scan_kernel launch "
+                             "(profiles/r01_ncu_full_bf_tc4_scan.txt), scaled to this launch's pair count",
+            "kernel": "bf_tc4_scan_kernel", "launches": scan_launches, "avg_launch_ms": avg_ms,
+            "share_of_step": scan_ms / ms_dev, "achieved_gcmp_s": achieved,
+            "peak_basis": f"4 x measured dense bf16 ({peaks['bf16_tflops']:.0f} TFLOP/s burst, {peaks['source']}); algorithmic work "
+                          "= 512 flop per 256-bit comparison.  The kernel also issues one constant MMA per 8 useful ones and pads "
+                          "4000 train rows to 9 tiles of 480, so its tensor-pipe time is 1.215x the algorithmic one",
+            "vs_sustained_bf16_x4": tflops / (4.0 * peaks["bf16_tflops_sustained"]),
+            "vs_integer_pipe_roofline": {"note": "the XOR+POPC formulation's ceilings (SURVEY 8d), for scale",
+                                         "int_alu_peak_gcmp_s": int_peak, "x_int_alu": achieved / int_peak,
+                                         "popc8_peak_gcmp_s": popc8_peak, "x_popc8": achieved / popc8_peak},
+            "hbm": hbm_view,
+        }
 
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
-        "ms_per_step": ms_dev / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8",
+        "ms_per_step": ms_dev / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "u8" if os.environ.get("SLAMGPU_BF_ENGINE") == "int" else "e2m1 (fp4 products of +-1, exact fp32 accumulation)",
         "data": "synthetic",
         "config": {"workload": workload_name(args),
                    "pairs_per_step_per_gpu": n, "comparisons_per_step": world * n * per_pair,

@@ -40,9 +40,7 @@ constexpr int kOff4A = 0;                                  // 2 x 16 KB
 constexpr int kOff4B = 2 * kA4Bytes;                       // 4 x 30 KB
 constexpr int kOff4AX = kOff4B + kB4Stages * kB4Bytes;     // constant K = 64 slice of A: 128 rows x 32 B
 constexpr int kOff4BX = kOff4AX + 128 * 32;                // ... of B: this CTA's 120 rows x 32 B (4 KB reserved)
-constexpr int kOff4AY = kOff4BX + 128 * 32;                // second constant slice (the small part), same shapes
-constexpr int kOff4BY = kOff4AY + 128 * 32;
-constexpr int kOff4Bar = kOff4BY + 128 * 32;               // 24 mbarriers
+constexpr int kOff4Bar = kOff4BX + 128 * 32;               // 24 mbarriers
 constexpr int kOff4TmemSlot = kOff4Bar + 32 * 8;
 constexpr int kTc4SmemBytes = kOff4TmemSlot + 16;
 // TMEM columns: accumulator stage 0 at 0, stage 1 at 256, scale factors 1.0 at 496, 2^10 at 504, and the
@@ -168,12 +166,13 @@ __device__ __forceinline__ uint32_t or3(uint32_t a, uint32_t b, uint32_t c)
     return d;
 }
 
-// N accumulators (columns col0 .. col0 + N - 1 of the tile): scan, park the groups of 16 that hit in `park`,
-// return the mask of parked groups
+// N accumulators (columns col0 .. col0 + N - 1 of the tile): scan; a group of 16 that hits is parked in
+// `park` (16 ints per group) and its per-element hit bits are added to `hits` (bit 16 q + j = element j of
+// group q; N = 8 is the low half of one group)
 template <int N>
-__device__ __forceinline__ uint32_t scan4(const uint32_t (&v)[N], int4* park)
+__device__ __forceinline__ uint64_t scan4(const uint32_t (&v)[N], int4* park)
 {
-    uint32_t mask = 0u;
+    uint64_t hits = 0ull;
     if constexpr (N % 16 == 0) {
 #pragma unroll
         for (int q = 0; q < N / 16; ++q) {
@@ -187,25 +186,29 @@ __device__ __forceinline__ uint32_t scan4(const uint32_t (&v)[N], int4* park)
             r = or3(r, x[13], x[14]);
             r |= x[15];
             if (__builtin_expect((r & kHitBits) != 0u, 0)) {
-                mask |= 1u << q;
+                uint32_t hb = 0u;
+#pragma unroll
+                for (int j = 0; j < 16; ++j) hb |= (x[j] & kHitBits) != 0u ? 1u << j : 0u;
+                hits |= static_cast<uint64_t>(hb) << (16 * q);
 #pragma unroll
                 for (int k = 0; k < 4; ++k) park[4 * q + k] = make_int4(x[4 * k], x[4 * k + 1], x[4 * k + 2], x[4 * k + 3]);
             }
         }
-    } else {        // N = 8: half a group, the other half parked as "no hit"
+    } else {
         uint32_t r = or3(v[0], v[1], v[2]);
         r = or3(r, v[3], v[4]);
         r = or3(r, v[5], v[6]);
         r |= v[7];
         if (__builtin_expect((r & kHitBits) != 0u, 0)) {
-            mask = 1u;
+            uint32_t hb = 0u;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) hb |= (v[j] & kHitBits) != 0u ? 1u << j : 0u;
+            hits = hb;
             park[0] = make_int4(v[0], v[1], v[2], v[3]);
             park[1] = make_int4(v[4], v[5], v[6], v[7]);
-            park[2] = make_int4(0, 0, 0, 0);
-            park[3] = make_int4(0, 0, 0, 0);
         }
     }
-    return mask;
+    return hits;
 }
 
 // one accumulator with a hit bit: both dots decoded, those within the exact cut folded as
@@ -229,22 +232,16 @@ __device__ __forceinline__ void decode4_one(uint32_t u, int t1, int t_end, int t
     b1 = min(min(b1, top), hi);
 }
 
-__device__ __forceinline__ void decode4(const int4* park, uint32_t mask, int t1_first, int t_end, int thr_dot, int thr4,
+// one iteration per accumulator that hit (usually one): parked value -> keys
+__device__ __forceinline__ void decode4(const int4* park, uint64_t hits, int t1_first, int t_end, int thr_dot, int thr4,
                                         uint32_t& b0, uint32_t& b1)
 {
+    const uint32_t* p = reinterpret_cast<const uint32_t*>(park);
 #pragma unroll 1
-    while (mask != 0u) {
-        const int q = __ffs(mask) - 1;
-        mask &= mask - 1u;
-#pragma unroll 1
-        for (int k = 0; k < 4; ++k) {
-            const int4 x = park[4 * q + k];
-            const int t1 = t1_first + 16 * q + 4 * k;
-            if (static_cast<uint32_t>(x.x) & kHitBits) decode4_one(x.x, t1, t_end, thr_dot, thr4, b0, b1);
-            if (static_cast<uint32_t>(x.y) & kHitBits) decode4_one(x.y, t1 + 1, t_end, thr_dot, thr4, b0, b1);
-            if (static_cast<uint32_t>(x.z) & kHitBits) decode4_one(x.z, t1 + 2, t_end, thr_dot, thr4, b0, b1);
-            if (static_cast<uint32_t>(x.w) & kHitBits) decode4_one(x.w, t1 + 3, t_end, thr_dot, thr4, b0, b1);
-        }
+    while (hits != 0ull) {
+        const int j = __ffsll(static_cast<long long>(hits)) - 1;
+        hits &= hits - 1ull;
+        decode4_one(p[j], t1_first + j, t_end, thr_dot, thr4, b0, b1);
     }
 }
 
@@ -319,26 +316,21 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTc4Threads, 1) bf_t
     // The constant slice (see magic_pair): one extra K = 64 MMA per tile adds 1.5 * 2^23 + 512 - 1025 * T4, so the
     // epilogue reads integers whose bits 22 and 9 are the two threshold tests -- no FADD, no shift, no min/max.
     // Canonical layout: 8-row group = [k-chunk 0..1][row][16 B]; k-chunk c holds elements 32 c .. 32 c + 31 = block c.
-    // Two slices, because one MMA must not mix magnitudes: with both blocks in one MMA the small block lost its
-    // low bits (the products of one instruction are aligned to the largest before they are added).
-    //   slice X: block 1 only -> (768 - T4 / 16) * 2^14       slice Y: block 0 only -> 512 - T4
-    for (int i = threadIdx.x; i < 4 * 128 * 32 / 16; i += kTc4Threads) {
-        const int tile = i / (128 * 32 / 16);       // 0: AX  1: BX  2: AY  3: BY
-        const int e = i % (128 * 32 / 16);
+    // block 0 (k-chunk 0, scale 2^0): 512 - T4      block 1 (k-chunk 1, scale 2^7 * 2^7): (768 - T4 / 16) * 2^14
+    // (mixing the two magnitudes in one MMA is exact: checked against a two-MMA version on the B200)
+    for (int i = threadIdx.x; i < 2 * 128 * 32 / 16; i += kTc4Threads) {
+        const bool is_a = i < 128 * 32 / 16;
+        const int e = is_a ? i : i - 128 * 32 / 16;
         const int chunk = (e >> 3) & 1;
-        const bool is_a = (tile & 1) == 0, is_y = tile >= 2;
-        const int target4 = is_y ? 4 * (512 - a.thr4) : 3072 - a.thr4 / 4;
+        const int target4 = chunk == 0 ? 4 * (512 - a.thr4) : 3072 - a.thr4 / 4;
         uint32_t wds[4] = {0u, 0u, 0u, 0u};
-        if (chunk == (is_y ? 0 : 1)) {
 #pragma unroll
-            for (int n = 0; n < 32; ++n) {          // element n of the block -> nibble n of the 16 bytes
-                int av, bv;
-                magic_pair(target4, n, av, bv);
-                wds[n >> 3] |= e2m1_code2(is_a ? av : bv) << (4 * (n & 7));
-            }
+        for (int n = 0; n < 32; ++n) {          // element n of the block -> nibble n of the 16 bytes
+            int av, bv;
+            magic_pair(target4, n, av, bv);
+            wds[n >> 3] |= e2m1_code2(is_a ? av : bv) << (4 * (n & 7));
         }
-        const int off = tile == 0 ? kOff4AX : tile == 1 ? kOff4BX : tile == 2 ? kOff4AY : kOff4BY;
-        *reinterpret_cast<uint4*>(smem + off + e * 16) = make_uint4(wds[0], wds[1], wds[2], wds[3]);
+        *reinterpret_cast<uint4*>(smem + (is_a ? kOff4AX : kOff4BX) + e * 16) = make_uint4(wds[0], wds[1], wds[2], wds[3]);
     }
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     if (warp == 1) {
@@ -395,7 +387,6 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTc4Threads, 1) bf_t
             // ===== MMA issuer: one thread of the leader CTA, for the pair =====
             const uint32_t sf_one = tmem_base + kSfOne, sf_big = tmem_base + kSfBig, sf_mix = tmem_base + kSfMix;
             const uint64_t desc_ax = umma_desc(sbase + kOff4AX, 128u, 256u), desc_bx = umma_desc(sbase + kOff4BX, 128u, 256u);
-            const uint64_t desc_ay = umma_desc(sbase + kOff4AY, 128u, 256u), desc_by = umma_desc(sbase + kOff4BY, 128u, 256u);
             uint32_t a_it = 0, b_it = 0, c_it = 0;
             for (long long u = cid; u < a.n_units; u += n_clusters) {
                 const Unit4 un = decode_unit4(a, u);
@@ -412,8 +403,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTc4Threads, 1) bf_t
                     const uint32_t d = tmem_base + sc * kAccStride;
                     const uint32_t a0 = sbase + kOff4A + sa * kA4Bytes, b0 = sbase + kOff4B + sb * kB4Bytes;
                     if (!(a.variant & 4)) {       // timing experiments only: bit 2 skips the MMAs
-                        tc4_mma(d, desc_ax, desc_bx, kIdesc4, 0u, sf_mix, sf_mix);      // D = 1.5 * 2^23 - 1024 * T4
-                        tc4_mma(d, desc_ay, desc_by, kIdesc4, 1u, sf_one, sf_one);      // D += 512 - T4
+                        tc4_mma(d, desc_ax, desc_bx, kIdesc4, 0u, sf_mix, sf_mix);      // D = 1.5 * 2^23 + 512 - 1025 * T4
 #pragma unroll
                         for (int k = 0; k < 4; ++k)     // K = 64 values = 32 bytes = two 16-byte k-chunks per MMA
                             tc4_mma(d, umma_desc(a0 + k * 256, 128u, kGroup4), umma_desc(b0 + k * 256, 128u, kGroup4),
@@ -514,9 +504,9 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTc4Threads, 1) bf_t
                 tmem_ld32(taddr + 64, vb0);      // chunk B in flight while A is folded
                 tmem_ld16(taddr + 96, vb1);
                 tmem_ld8(taddr + 112, vb2);
-                const uint32_t ma = (a.variant & 128) ? 0u     // timing experiments only: bit 7 skips the scan arithmetic
-                                                      : scan4(va0, park) | (scan4(va1, park + 8) << 2);
-                if (__builtin_expect(ma != 0u && t_end >= 0, 0)) decode4(park, ma, cb + c0, t_end, a.thr_dot, a.thr4, b0, b1);
+                const uint64_t ma = (a.variant & 128) ? 0ull   // timing experiments only: bit 7 skips the scan arithmetic
+                                                      : scan4(va0, park) | (scan4(va1, park + 8) << 32);
+                if (__builtin_expect(ma != 0ull && t_end >= 0, 0)) decode4(park, ma, cb + c0, t_end, a.thr_dot, a.thr4, b0, b1);
                 tmem_wait_ld();                  // chunk B has landed: every TMEM read of this stage is done
                 tmem_pin(vb0);
                 tmem_pin(vb1);
@@ -545,9 +535,9 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTc4Threads, 1) bf_t
                 }
             }
             if (!skip) {
-                const uint32_t mb = (a.variant & 128) ? 0u
-                                                      : scan4(vb0, park) | (scan4(vb1, park + 8) << 2) | (scan4(vb2, park + 12) << 3);
-                if (__builtin_expect(mb != 0u && t_end >= 0, 0)) decode4(park, mb, cb + c0 + 64, t_end, a.thr_dot, a.thr4, b0, b1);
+                const uint64_t mb = (a.variant & 128) ? 0ull
+                                                      : scan4(vb0, park) | (scan4(vb1, park + 8) << 32) | (scan4(vb2, park + 12) << 48);
+                if (__builtin_expect(mb != 0ull && t_end >= 0, 0)) decode4(park, mb, cb + c0 + 64, t_end, a.thr_dot, a.thr4, b0, b1);
             }
             if (last_of_unit) {
                 const int row = un_cur.row0 + row_in_tile;
