@@ -51,7 +51,9 @@ def parse_args():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--pairs-per-step", type=int, default=2048, help="frame pairs per rank per step")
+    ap.add_argument("--pairs-per-step", type=int, default=32768,
+                    help="frame pairs per rank per step (32768 x 16 M comparisons = 60 ms on the tensor cores, so that "
+                         "a 5-step timed region is long enough for nvidia-smi clock samples)")
     ap.add_argument("--ref-pairs-per-step", type=int, default=24, help="frame pairs per step of the CPU arm")
     ap.add_argument("--frames", type=int, default=N_FRAMES)
     ap.add_argument("--desc", type=int, default=N_DESC)
@@ -85,7 +87,7 @@ class ClockSampler:
         self.rows, self.proc = [], None
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(index), f"--query-gpu={self.Q}",
-                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                          "--format=csv,noheader,nounits", "-lms", "20"],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.thread = threading.Thread(target=self._read, daemon=True)
             self.thread.start()

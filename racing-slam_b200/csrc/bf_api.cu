@@ -223,7 +223,7 @@ int match_descriptors_core(slamgpu_ctx* ctx, const uint8_t* dq, int nq, const ui
 }
 
 // Pairs are processed in slices so that the partial-key scratch stays around L2 size.
-constexpr size_t kBatchScratchBytes = size_t(64) << 20;
+constexpr size_t kBatchScratchBytes = size_t(256) << 20;
 
 int batch_core(slamgpu_ctx* ctx, const uint8_t* d_desc, const int32_t* d_frame_offset, int n_frames,
                const int32_t* d_pairs, int n_pairs, int max_rows, float max_dist, float ratio, int32_t* d_out_train, int32_t* d_out_count,
