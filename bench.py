@@ -264,6 +264,8 @@ def run_ours(args, rank, local_rank, world):
         raise RuntimeError("bench.py needs a CUDA device: libslamgpu has no CPU path")
     torch.cuda.set_device(local_rank)
     if world > 1:
+        # NCCL's version banner goes to stdout by default; stdout carries the one JSON line only
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
 
     def barrier():
