@@ -167,6 +167,14 @@ SLAMGPU_API int slamgpu_kd_build_host(const float* xy, int n, uint32_t* out_perm
 SLAMGPU_API int slamgpu_points_upload(slamgpu_ctx* ctx, int set_id, int n, const float* pos, const float* normal,
                           const float* range, const int32_t* obs_offset, const uint8_t* obs_desc,
                           const float* obs_center);
+/* Map growth (Mapper::insert -> Map::create_point, src/Mapper.cpp:152-174, src/Map.cpp:20-40): append
+ * n_new points at the end of the set, i.e. in Map's own vector order (src/Map.cpp:164-190).  Same
+ * arguments as slamgpu_points_upload for the appended block alone; obs_offset is relative to it
+ * (obs_offset[0] = 0).  Existing indices stay valid; storage grows geometrically on the device. */
+SLAMGPU_API int slamgpu_points_append(slamgpu_ctx* ctx, int set_id, int n_new, const float* pos, const float* normal,
+                          const float* range, const int32_t* obs_offset, const uint8_t* obs_desc,
+                          const float* obs_center);
+SLAMGPU_API int slamgpu_points_count(slamgpu_ctx* ctx, int set_id, int* n_points, int64_t* n_observations);
 SLAMGPU_API int slamgpu_points_release(slamgpu_ctx* ctx, int set_id);
 /* Read back the per-point normal [n x 3] and range [n x 2] held on the device. */
 SLAMGPU_API int slamgpu_points_get_stats(slamgpu_ctx* ctx, int set_id, float* out_normal, float* out_range);
@@ -192,6 +200,24 @@ SLAMGPU_API int slamgpu_match_projection_ex(slamgpu_ctx* ctx, int frame_id, int 
                                 const slamgpu_proj_params* params, const uint8_t* skip, const int32_t* order,
                                 int n_order, int32_t* out_point, int32_t* out_dist, float* dbg_uv,
                                 int32_t* dbg_kp, int32_t* dbg_d, int64_t* stats);
+
+/* The per-frame tracking pair, chained on the device -- Tracker::match_with_last_key_frame then
+ * Tracker::match_with_map (src/Tracker.cpp:232-248):
+ *   1. match_key_frame(frame, map, last_key_frame): visits kf_points = the indices of the points with
+ *      is_observed_by(last_key_frame) (src/MapMatcher.cpp:169), strictly ascending = map order;
+ *   2. every match is applied as Frame::add_map_match does (src/Frame.cpp:80-102): the keypoint and the
+ *      point become matched in the frame;
+ *   3. match_map(frame, map): visits every point of the set against the updated frame, and its matches
+ *      are applied too, so the resident frame ends up as the host's frame after both loops.
+ * matched_points = indices of the points with frame.is_matched(point) before the call (from
+ * track_from_last_frame, src/Tracker.cpp:197-230); the frame's keypoint flags are the resident ones
+ * (slamgpu_frame_upload / slamgpu_frame_set_matched).  replace in params is ignored (0).  One upload of
+ * the two index lists, one download of the four [nkp] result arrays; results are those of the two
+ * reference calls made one after the other. */
+SLAMGPU_API int slamgpu_track_match(slamgpu_ctx* ctx, int frame_id, int set_id, const float* pose_colmajor16,
+                        const slamgpu_proj_params* params, const int32_t* matched_points, int n_matched,
+                        const int32_t* kf_points, int n_kf, int32_t* out_kf_point, int32_t* out_kf_dist,
+                        int32_t* out_map_point, int32_t* out_map_dist);
 
 /* Batched over key frames on a frozen snapshot -- Mapper::fuse_loop's window loop
  * (src/Mapper.cpp:208-219; BASELINE C4).  n_frames resident frames, one pose each; one shared

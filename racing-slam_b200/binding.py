@@ -67,12 +67,16 @@ SIGNATURES = {
     "slamgpu_frame_get_kd_perm": (C.c_int, [_ctx, C.c_int, _u32p]),
     "slamgpu_kd_build_host": (C.c_int, [_f32p, C.c_int, _u32p]),
     "slamgpu_points_upload": (C.c_int, [_ctx, C.c_int, C.c_int, _f32p, _f32p, _f32p, _i32p, _u8p, _f32p]),
+    "slamgpu_points_append": (C.c_int, [_ctx, C.c_int, C.c_int, _f32p, _f32p, _f32p, _i32p, _u8p, _f32p]),
+    "slamgpu_points_count": (C.c_int, [_ctx, C.c_int, C.POINTER(C.c_int), _i64p]),
     "slamgpu_points_release": (C.c_int, [_ctx, C.c_int]),
     "slamgpu_points_get_stats": (C.c_int, [_ctx, C.c_int, _f32p, _f32p]),
     "slamgpu_match_projection": (C.c_int, [_ctx, C.c_int, C.c_int, _f32p, C.POINTER(ProjParams), _u8p, _i32p, C.c_int,
                                            _i32p, _i32p]),
     "slamgpu_match_projection_ex": (C.c_int, [_ctx, C.c_int, C.c_int, _f32p, C.POINTER(ProjParams), _u8p, _i32p,
                                               C.c_int, _i32p, _i32p, _f32p, _i32p, _i32p, _i64p]),
+    "slamgpu_track_match": (C.c_int, [_ctx, C.c_int, C.c_int, _f32p, C.POINTER(ProjParams), _i32p, C.c_int, _i32p,
+                                      C.c_int, _i32p, _i32p, _i32p, _i32p]),
     "slamgpu_match_projection_batch": (C.c_int, [_ctx, C.POINTER(C.c_int), C.c_int, C.c_int, _f32p,
                                                  C.POINTER(ProjParams), _u8p, _i32p, C.c_int, _i32p, _i32p]),
     "slamgpu_profile_enable": (C.c_int, [_ctx, C.c_int]),
@@ -299,6 +303,25 @@ class Context:
                                                     _p(obs_offset, C.c_int32), _p(obs_desc, C.c_uint8),
                                                     _p(obs_center, C.c_float)))
 
+    def points_append(self, set_id: int, pos, normal, rng, obs_offset, obs_desc, obs_center=None):
+        """Append points at the end of a resident set; obs_offset is relative to the appended block."""
+        pos = np.ascontiguousarray(pos, np.float32).reshape(-1, 3)
+        normal = _opt(normal, np.float32)
+        rng = _opt(rng, np.float32)
+        obs_offset = np.ascontiguousarray(obs_offset, np.int32)
+        obs_desc = _desc(obs_desc)
+        obs_center = _opt(obs_center, np.float32)
+        assert len(obs_offset) == len(pos) + 1
+        self._check(self._lib.slamgpu_points_append(self._h, set_id, len(pos), _p(pos, C.c_float),
+                                                    _p(normal, C.c_float), _p(rng, C.c_float),
+                                                    _p(obs_offset, C.c_int32), _p(obs_desc, C.c_uint8),
+                                                    _p(obs_center, C.c_float)))
+
+    def points_count(self, set_id: int):
+        n, o = C.c_int(0), C.c_int64(0)
+        self._check(self._lib.slamgpu_points_count(self._h, set_id, C.byref(n), C.byref(o)))
+        return n.value, o.value
+
     def points_release(self, set_id: int):
         self._check(self._lib.slamgpu_points_release(self._h, set_id))
 
@@ -333,6 +356,18 @@ class Context:
             _p(order, C.c_int32), n_order, _p(out_point, C.c_int32), _p(out_dist, C.c_int32), _p(uv, C.c_float),
             _p(kp, C.c_int32), _p(d, C.c_int32), _p(stats, C.c_int64)))
         return out_point, out_dist, dict(uv=uv, kp=kp, d=d, near_border=int(stats[0]), near_radius=int(stats[1]))
+
+    def track_match(self, frame_id: int, set_id: int, nkp: int, pose, params: ProjParams, matched_points, kf_points):
+        """match_key_frame -> apply -> match_map chained on the device (src/Tracker.cpp:232-248).
+        -> (kf_point, kf_dist, map_point, map_dist), each [nkp]."""
+        pose = np.ascontiguousarray(pose, np.float32).reshape(16)
+        mp = np.ascontiguousarray(matched_points, np.int32).reshape(-1)
+        kf = np.ascontiguousarray(kf_points, np.int32).reshape(-1)
+        outs = [np.full(nkp, -1, np.int32) for _ in range(4)]
+        self._check(self._lib.slamgpu_track_match(
+            self._h, frame_id, set_id, _p(pose, C.c_float), C.byref(params), _p(mp, C.c_int32), len(mp),
+            _p(kf, C.c_int32), len(kf), *[_p(o, C.c_int32) for o in outs]))
+        return tuple(outs)
 
     def match_projection_batch(self, frame_ids, nkps, set_id: int, poses, params: ProjParams, skip=None, order=None):
         """Frozen-snapshot batch over key frames -> list of (out_point, out_dist) per frame."""

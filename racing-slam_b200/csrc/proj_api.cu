@@ -29,6 +29,34 @@ void free_points(PointSetDev& p)
     p = PointSetDev();
 }
 
+// One allocation carved for cap_n points / cap_obs observations; the first five arrays are in the
+// order and padding of the staging image so that an exact-size upload is one copy.
+size_t points_image_bytes(size_t N, size_t O)
+{
+    return Carver::padded(N * 12) + Carver::padded(N * 12) + Carver::padded(N * 8) + Carver::padded((N + 1) * 4) +
+           Carver::padded(O * 32);
+}
+int alloc_points(PointSetDev& p, int cap_n, int64_t cap_obs)
+{
+    const size_t N = static_cast<size_t>(cap_n), O = static_cast<size_t>(cap_obs);
+    const cudaError_t e = cudaMalloc(&p.blob, points_image_bytes(N, O) + Carver::padded(N) + 256);
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        p.blob = nullptr;
+        return fail(SLAMGPU_ERR_NOMEM, std::string("point-set allocation failed: ") + cudaGetErrorString(e));
+    }
+    Carver dv(p.blob);
+    p.pos = dv.take<float>(N * 3);
+    p.normal = dv.take<float>(N * 3);
+    p.range = dv.take<float>(N * 2);
+    p.obs_offset = dv.take<int32_t>(N + 1);
+    p.obs_desc = dv.take<uint4>(O * 2);
+    p.pt_matched = dv.take<uint8_t>(N);
+    p.cap_n = cap_n;
+    p.cap_obs = cap_obs;
+    return SLAMGPU_OK;
+}
+
 int check_params(const slamgpu_proj_params* p)
 {
     SG_CHECK(p != nullptr, "null projection params");
@@ -435,21 +463,10 @@ int slamgpu_points_upload(slamgpu_ctx* ctx, int set_id, int n, const float* pos,
     p.n = n;
     p.n_obs = n_obs;
     const size_t N = static_cast<size_t>(n), O = static_cast<size_t>(n_obs);
-    const size_t b_pos = Carver::padded(N * 12), b_nrm = Carver::padded(N * 12), b_rng = Carver::padded(N * 8),
-                 b_off = Carver::padded((N + 1) * 4), b_desc = Carver::padded(O * 32);
-    const size_t up = b_pos + b_nrm + b_rng + b_off + b_desc;
+    const size_t up = points_image_bytes(N, O);
     const size_t b_center = derive ? Carver::padded(O * 12) : 0;
-    const cudaError_t e = cudaMalloc(&p.blob, up + 256);
-    if (e != cudaSuccess) {
-        cudaGetLastError();
-        return fail(SLAMGPU_ERR_NOMEM, std::string("point-set allocation failed: ") + cudaGetErrorString(e));
-    }
-    Carver dv(p.blob);
-    p.pos = dv.take<float>(N * 3);
-    p.normal = dv.take<float>(N * 3);
-    p.range = dv.take<float>(N * 2);
-    p.obs_offset = dv.take<int32_t>(N + 1);
-    p.obs_desc = dv.take<uint4>(O * 2);
+    SG_TRY(alloc_points(p, n, n_obs));
+    if (n == 0) cudaMemsetAsync(p.obs_offset, 0, sizeof(int32_t), ctx->stream);   // slamgpu_points_append starts here
 
     if (n > 0) {
         int rc = ensure_host_stage(ctx, up + b_center + 256);
@@ -487,6 +504,101 @@ int slamgpu_points_upload(slamgpu_ctx* ctx, int set_id, int n, const float* pos,
         SG_CUDA(cudaStreamSynchronize(ctx->stream));
     }
     ctx->point_sets[set_id] = p;
+    return SLAMGPU_OK;
+}
+
+int slamgpu_points_append(slamgpu_ctx* ctx, int set_id, int n_new, const float* pos, const float* normal,
+                          const float* range, const int32_t* obs_offset, const uint8_t* obs_desc,
+                          const float* obs_center)
+{
+    SG_CTX(ctx);
+    SG_CHECK(n_new >= 0, "negative point count");
+    auto it = ctx->point_sets.find(set_id);
+    if (it == ctx->point_sets.end()) return fail(SLAMGPU_ERR_NOTFOUND, "unknown point set id");
+    if (n_new == 0) return SLAMGPU_OK;
+    SG_CHECK(pos != nullptr && obs_offset != nullptr, "null positions / observation offsets");
+    const bool derive = (normal == nullptr || range == nullptr);
+    SG_CHECK(!derive || obs_center != nullptr, "normal/range missing and no obs_center to derive them");
+    SG_CHECK(obs_offset[0] == 0, "obs_offset[0] must be 0 (offsets are relative to the appended block)");
+    for (int i = 0; i < n_new; ++i) SG_CHECK(obs_offset[i + 1] >= obs_offset[i], "obs_offset must be non-decreasing");
+    const int64_t o_new = obs_offset[n_new];
+    SG_CHECK(o_new == 0 || obs_desc != nullptr, "null observation descriptors");
+    PointSetDev& p = it->second;
+    SG_CHECK(static_cast<int64_t>(p.n) + n_new <= (1 << 30) && p.n_obs + o_new <= 0x7FFFFFFF, "point set too large");
+
+    // grow geometrically: new allocation, device-to-device copies of the live part, old one freed
+    if (p.n + n_new > p.cap_n || p.n_obs + o_new > p.cap_obs) {
+        PointSetDev g = p;
+        const int cap_n = std::max(p.n + n_new, 2 * p.cap_n);
+        const int64_t cap_obs = std::max<int64_t>(p.n_obs + o_new, 2 * p.cap_obs);
+        SG_TRY(alloc_points(g, cap_n, cap_obs));
+        const size_t N = static_cast<size_t>(p.n), O = static_cast<size_t>(p.n_obs);
+        cudaError_t e = cudaSuccess;
+        if (p.blob) {
+            if (N) e = cudaMemcpyAsync(g.pos, p.pos, N * 12, cudaMemcpyDeviceToDevice, ctx->stream);
+            if (N && e == cudaSuccess) e = cudaMemcpyAsync(g.normal, p.normal, N * 12, cudaMemcpyDeviceToDevice, ctx->stream);
+            if (N && e == cudaSuccess) e = cudaMemcpyAsync(g.range, p.range, N * 8, cudaMemcpyDeviceToDevice, ctx->stream);
+            if (e == cudaSuccess) e = cudaMemcpyAsync(g.obs_offset, p.obs_offset, (N + 1) * 4, cudaMemcpyDeviceToDevice, ctx->stream);
+            if (O && e == cudaSuccess) e = cudaMemcpyAsync(g.obs_desc, p.obs_desc, O * 32, cudaMemcpyDeviceToDevice, ctx->stream);
+            if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+        } else {
+            e = cudaMemsetAsync(g.obs_offset, 0, 4, ctx->stream);
+        }
+        if (e != cudaSuccess) {
+            cudaFree(g.blob);
+            return fail(SLAMGPU_ERR_CUDA, std::string("point-set growth: ") + cudaGetErrorString(e));
+        }
+        if (p.blob) cudaFree(p.blob);
+        p = g;
+    }
+
+    const size_t M = static_cast<size_t>(n_new), Q = static_cast<size_t>(o_new);
+    const size_t image = points_image_bytes(M, Q);
+    const size_t b_center = derive ? Carver::padded(Q * 12) : 0;
+    SG_TRY(ensure_host_stage(ctx, image + b_center + 256));
+    if (derive) SG_TRY(ensure_device_io(ctx, b_center + 256));
+    SG_CUDA(cudaStreamSynchronize(ctx->stream));   // staging is reused
+    Carver hv(ctx->h_stage.ptr);
+    float* h_pos = hv.take<float>(M * 3);
+    float* h_nrm = hv.take<float>(M * 3);
+    float* h_rng = hv.take<float>(M * 2);
+    int32_t* h_off = hv.take<int32_t>(M + 1);
+    uint8_t* h_desc = reinterpret_cast<uint8_t*>(hv.take<uint4>(Q * 2));
+    std::memcpy(h_pos, pos, M * 12);
+    const int32_t base = static_cast<int32_t>(p.n_obs);
+    for (size_t i = 0; i < M; ++i) h_off[i] = base + obs_offset[i + 1];   // entries n+1 .. n+n_new
+    if (Q) std::memcpy(h_desc, obs_desc, Q * 32);
+    const size_t n0 = static_cast<size_t>(p.n), o0 = static_cast<size_t>(p.n_obs);
+    SG_CUDA(cudaMemcpyAsync(p.pos + 3 * n0, h_pos, M * 12, cudaMemcpyHostToDevice, ctx->stream));
+    SG_CUDA(cudaMemcpyAsync(p.obs_offset + n0 + 1, h_off, M * 4, cudaMemcpyHostToDevice, ctx->stream));
+    if (Q) SG_CUDA(cudaMemcpyAsync(p.obs_desc + 2 * o0, h_desc, Q * 32, cudaMemcpyHostToDevice, ctx->stream));
+    if (!derive) {
+        std::memcpy(h_nrm, normal, M * 12);
+        std::memcpy(h_rng, range, M * 8);
+        SG_CUDA(cudaMemcpyAsync(p.normal + 3 * n0, h_nrm, M * 12, cudaMemcpyHostToDevice, ctx->stream));
+        SG_CUDA(cudaMemcpyAsync(p.range + 2 * n0, h_rng, M * 8, cudaMemcpyHostToDevice, ctx->stream));
+    } else {
+        float* h_center = hv.take<float>(Q * 3);
+        if (Q) std::memcpy(h_center, obs_center, Q * 12);
+        float* d_center = static_cast<float*>(ctx->d_io.ptr);
+        if (Q) SG_CUDA(cudaMemcpyAsync(d_center, h_center, Q * 12, cudaMemcpyHostToDevice, ctx->stream));
+        // the kernel indexes observations by their absolute offset: bias the centre pointer by the old total
+        SG_TRY(proj_launch_point_stats(ctx, p.pos + 3 * n0, n_new, p.obs_offset + n0, d_center - 3 * o0,
+                                       p.normal + 3 * n0, p.range + 2 * n0));
+    }
+    SG_CUDA(cudaStreamSynchronize(ctx->stream));
+    p.n += n_new;
+    p.n_obs += o_new;
+    return SLAMGPU_OK;
+}
+
+int slamgpu_points_count(slamgpu_ctx* ctx, int set_id, int* n_points, int64_t* n_observations)
+{
+    SG_CHECK(ctx != nullptr, "null context");
+    auto it = ctx->point_sets.find(set_id);
+    if (it == ctx->point_sets.end()) return fail(SLAMGPU_ERR_NOTFOUND, "unknown point set id");
+    if (n_points) *n_points = it->second.n;
+    if (n_observations) *n_observations = it->second.n_obs;
     return SLAMGPU_OK;
 }
 
@@ -529,6 +641,62 @@ int slamgpu_match_projection_ex(slamgpu_ctx* ctx, int frame_id, int set_id, cons
 {
     return match_projection_impl(ctx, &frame_id, 1, set_id, pose_colmajor16, params, skip, order, n_order, out_point,
                                  out_dist, dbg_uv, dbg_kp, dbg_d, stats);
+}
+
+int slamgpu_track_match(slamgpu_ctx* ctx, int frame_id, int set_id, const float* pose_colmajor16,
+                        const slamgpu_proj_params* params, const int32_t* matched_points, int n_matched,
+                        const int32_t* kf_points, int n_kf, int32_t* out_kf_point, int32_t* out_kf_dist,
+                        int32_t* out_map_point, int32_t* out_map_dist)
+{
+    SG_CTX(ctx);
+    SG_TRY(check_params(params));
+    SG_CHECK(pose_colmajor16 != nullptr, "null pose");
+    SG_CHECK(n_matched >= 0 && n_kf >= 0, "negative list length");
+    SG_CHECK((n_matched == 0 || matched_points) && (n_kf == 0 || kf_points), "null index list");
+    auto f_it = ctx->frames.find(frame_id);
+    if (f_it == ctx->frames.end()) return fail(SLAMGPU_ERR_NOTFOUND, "unknown frame id");
+    auto ps_it = ctx->point_sets.find(set_id);
+    if (ps_it == ctx->point_sets.end()) return fail(SLAMGPU_ERR_NOTFOUND, "unknown point set id");
+    const FrameDev& fd = f_it->second;
+    const PointSetDev& ps = ps_it->second;
+    for (int i = 0; i < n_matched; ++i)
+        SG_CHECK(matched_points[i] >= 0 && matched_points[i] < ps.n, "matched_points entry outside the point set");
+    for (int i = 0; i < n_kf; ++i) {
+        SG_CHECK(kf_points[i] >= 0 && kf_points[i] < ps.n, "kf_points entry outside the point set");
+        SG_CHECK(i == 0 || kf_points[i] > kf_points[i - 1], "kf_points must be strictly ascending (map order)");
+    }
+    const size_t nkp = static_cast<size_t>(fd.nkp);
+    SG_CHECK(nkp == 0 || (out_kf_point && out_kf_dist && out_map_point && out_map_dist), "null output");
+
+    const size_t b_m = Carver::padded(sizeof(int32_t) * n_matched), b_k = Carver::padded(sizeof(int32_t) * n_kf);
+    const size_t b_out = Carver::padded(sizeof(int32_t) * 4 * nkp);
+    SG_TRY(ensure_device_io(ctx, b_m + b_k + b_out + 256));
+    SG_TRY(ensure_host_stage(ctx, std::max(b_m + b_k, b_out) + 256));
+    Carver dio(ctx->d_io.ptr), hio(ctx->h_stage.ptr);
+    int32_t* d_m = dio.take<int32_t>(n_matched);
+    int32_t* d_k = dio.take<int32_t>(n_kf);
+    int32_t* d_out = dio.take<int32_t>(4 * nkp);
+    int32_t* h_m = hio.take<int32_t>(n_matched);
+    int32_t* h_k = hio.take<int32_t>(n_kf);
+    if (n_matched) std::memcpy(h_m, matched_points, sizeof(int32_t) * n_matched);
+    if (n_kf) std::memcpy(h_k, kf_points, sizeof(int32_t) * n_kf);
+    if (b_m + b_k) SG_CUDA(cudaMemcpyAsync(ctx->d_io.ptr, ctx->h_stage.ptr, b_m + b_k, cudaMemcpyHostToDevice, ctx->stream));
+
+    ProjCommonArgs common;
+    fill_common(common, ps, *params, nullptr, ps.n);
+    ProjFrameArgs fa;
+    fill_frame(fa, fd, pose_colmajor16, *params);
+    SG_TRY(proj_launch_track(ctx, common, fa, ps.pt_matched, fd.matched, d_m, n_matched, d_k, n_kf, d_out));
+    if (nkp) SG_CUDA(cudaMemcpyAsync(ctx->h_stage.ptr, d_out, sizeof(int32_t) * 4 * nkp, cudaMemcpyDeviceToHost, ctx->stream));
+    SG_CUDA(cudaStreamSynchronize(ctx->stream));
+    if (nkp) {
+        const int32_t* h = static_cast<const int32_t*>(ctx->h_stage.ptr);
+        std::memcpy(out_kf_point, h, sizeof(int32_t) * nkp);
+        std::memcpy(out_kf_dist, h + nkp, sizeof(int32_t) * nkp);
+        std::memcpy(out_map_point, h + 2 * nkp, sizeof(int32_t) * nkp);
+        std::memcpy(out_map_dist, h + 3 * nkp, sizeof(int32_t) * nkp);
+    }
+    return SLAMGPU_OK;
 }
 
 int slamgpu_match_projection_batch(slamgpu_ctx* ctx, const int* frame_ids, int n_frames, int set_id,

@@ -360,6 +360,35 @@ __global__ void proj_emit_kernel(const ProjKernelArgs a)
     f.out_dist[kp] = dist;
 }
 
+// Emit + Frame::add_map_match (src/Frame.cpp:80-102) on the device.  A proposal comes from a point that
+// is not yet matched in the frame and lands on a keypoint that is not yet matched (replace = 0), and a
+// point proposes to one keypoint only, so `previous == nullptr` and the sweep of :90-98 finds nothing:
+// the update is two flags.  The proposal slot is reset for the next stage.
+__global__ void proj_emit_apply_kernel(const ProjKernelArgs a, uint8_t* pt_matched, uint8_t* kp_matched)
+{
+    const ProjFrameArgs& f = a.inline_frame;
+    const int kp = blockIdx.x * blockDim.x + threadIdx.x;
+    if (kp >= f.nkp) return;
+    const unsigned long long key = f.proposals[kp];
+    int point = -1, dist = -1;
+    if (key != ~0ull) {
+        const int v = static_cast<int>(key & 0xFFFFFFFFull);
+        point = a.c.order ? a.c.order[v] : v;
+        dist = static_cast<int>(key >> 32);
+        kp_matched[kp] = 1;
+        pt_matched[point] = 1;
+        f.proposals[kp] = ~0ull;
+    }
+    f.out_point[kp] = point;
+    f.out_dist[kp] = dist;
+}
+
+__global__ void proj_scatter_flags_kernel(const int32_t* idx, int n, uint8_t* flags)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) flags[idx[i]] = 1;
+}
+
 __global__ void proj_init_kernel(const ProjKernelArgs a)
 {
     const ProjFrameArgs& f = a.frames ? a.frames[blockIdx.y] : a.inline_frame;
@@ -404,6 +433,28 @@ __global__ void kd_gather_kernel(const float2* xy, const int32_t* perm, int n, f
 
 } // namespace
 
+// K4 launch: kernel variant by context switches (see the comments on the kernels).
+static void launch_match(slamgpu_ctx* ctx, const ProjKernelArgs& a, int n_visit, int n_frames)
+{
+    ProfScope prof(ctx, SLAMGPU_KERNEL_PROJ_MATCH);
+    if (ctx->proj_walk) {   // thread-per-point KD walk, kept for A/B checks (SLAMGPU_PROJ_WALK=1)
+        const dim3 gp((n_visit + kProjThreads - 1) / kProjThreads, n_frames);
+        proj_match_kernel<<<gp, kProjThreads, 0, ctx->stream>>>(a);
+    } else {
+        // 8 lanes per point: as fast as a full warp on C2 (19 us) and 1.8x faster on C4-sized batches
+        // (tools/time_proj.py, profiles/r01_proj_variants.txt); SLAMGPU_PROJ_LANES=32 overrides
+        const int lanes = ctx->proj_lanes ? ctx->proj_lanes : 8;
+        const int per_cta = kGroupThreads / lanes;
+        const dim3 gp((n_visit + per_cta - 1) / per_cta, n_frames);
+        if (lanes == 8) {
+            proj_match_warp_kernel<8><<<gp, kGroupThreads, 0, ctx->stream>>>(a);
+        } else {
+            proj_match_warp_kernel<32><<<gp, kGroupThreads, 0, ctx->stream>>>(a);
+        }
+    }
+    ctx->launches++;
+}
+
 int proj_launch(slamgpu_ctx* ctx, const ProjCommonArgs& common, const ProjFrameArgs* h_frames,
                 const ProjFrameArgs* d_frames, int n_frames, int max_nkp)
 {
@@ -417,28 +468,51 @@ int proj_launch(slamgpu_ctx* ctx, const ProjCommonArgs& common, const ProjFrameA
         const dim3 gk((max_nkp + 255) / 256, n_frames);
         proj_init_kernel<<<gk, 256, 0, ctx->stream>>>(a);
         ctx->launches++;
-        if (common.n_visit > 0) {
-            ProfScope prof(ctx, SLAMGPU_KERNEL_PROJ_MATCH);
-            if (ctx->proj_walk) {   // thread-per-point KD walk, kept for A/B checks (SLAMGPU_PROJ_WALK=1)
-                const dim3 gp((common.n_visit + kProjThreads - 1) / kProjThreads, n_frames);
-                proj_match_kernel<<<gp, kProjThreads, 0, ctx->stream>>>(a);
-            } else {
-                // 8 lanes per point: as fast as a full warp on C2 (19 us) and 1.8x faster on C4-sized batches
-                // (tools/time_proj.py, profiles/r01_proj_variants.txt); SLAMGPU_PROJ_LANES=32 overrides
-                const int lanes = ctx->proj_lanes ? ctx->proj_lanes : 8;
-                const int per_cta = kGroupThreads / lanes;
-                const dim3 gp((common.n_visit + per_cta - 1) / per_cta, n_frames);
-                if (lanes == 8) {
-                    proj_match_warp_kernel<8><<<gp, kGroupThreads, 0, ctx->stream>>>(a);
-                } else {
-                    proj_match_warp_kernel<32><<<gp, kGroupThreads, 0, ctx->stream>>>(a);
-                }
-            }
-            ctx->launches++;
-        }
+        if (common.n_visit > 0) launch_match(ctx, a, common.n_visit, n_frames);
         proj_emit_kernel<<<gk, 256, 0, ctx->stream>>>(a);
         ctx->launches++;
     }
+    SG_CUDA(cudaGetLastError());
+    return SLAMGPU_OK;
+}
+
+int proj_launch_track(slamgpu_ctx* ctx, const ProjCommonArgs& common, const ProjFrameArgs& frame, uint8_t* d_pt_matched,
+                      uint8_t* d_kp_matched, const int32_t* d_matched_points, int n_matched, const int32_t* d_kf_order,
+                      int n_kf, int32_t* d_out)
+{
+    const int nkp = frame.nkp, n = common.n_points;
+    if (n > 0) SG_CUDA(cudaMemsetAsync(d_pt_matched, 0, static_cast<size_t>(n), ctx->stream));
+    if (n_matched > 0) {
+        proj_scatter_flags_kernel<<<(n_matched + 255) / 256, 256, 0, ctx->stream>>>(d_matched_points, n_matched,
+                                                                                    d_pt_matched);
+        ctx->launches++;
+    }
+    if (nkp <= 0) return SLAMGPU_OK;
+    ProjKernelArgs a;
+    a.c = common;
+    a.c.replace = 0;                     // match(): is_matched(keypoint) candidates are skipped, src/MapMatcher.cpp:173
+    a.inline_frame = frame;
+    a.inline_frame.skip = d_pt_matched;  // frame.is_matched(point), :53
+    a.frames = nullptr;
+    const dim3 gk((nkp + 255) / 256, 1);
+    proj_init_kernel<<<gk, 256, 0, ctx->stream>>>(a);
+    ctx->launches++;
+    // stage 1: match_key_frame -- the points the last key frame observes, in map order (:169)
+    a.c.order = d_kf_order;
+    a.c.n_visit = n_kf;
+    a.inline_frame.out_point = d_out;
+    a.inline_frame.out_dist = d_out + nkp;
+    if (n_kf > 0) launch_match(ctx, a, n_kf, 1);
+    proj_emit_apply_kernel<<<gk, 256, 0, ctx->stream>>>(a, d_pt_matched, d_kp_matched);
+    ctx->launches++;
+    // stage 2: match_map -- every point (:107-110); stage 1's matches are already in the masks
+    a.c.order = nullptr;
+    a.c.n_visit = n;
+    a.inline_frame.out_point = d_out + 2 * nkp;
+    a.inline_frame.out_dist = d_out + 3 * nkp;
+    if (n > 0) launch_match(ctx, a, n, 1);
+    proj_emit_apply_kernel<<<gk, 256, 0, ctx->stream>>>(a, d_pt_matched, d_kp_matched);
+    ctx->launches++;
     SG_CUDA(cudaGetLastError());
     return SLAMGPU_OK;
 }

@@ -72,6 +72,9 @@ struct PointSetDev {
     float* range = nullptr;       // [n*2]
     int32_t* obs_offset = nullptr;// [n+1]
     uint4* obs_desc = nullptr;    // [n_obs*2]
+    uint8_t* pt_matched = nullptr;// [cap_n] scratch of slamgpu_track_match: frame.is_matched(point)
+    int cap_n = 0;                // the arrays above are carved for cap_n points / cap_obs observations,
+    int64_t cap_obs = 0;          // so that slamgpu_points_append can grow the set in place
 };
 
 struct Arena {
@@ -220,6 +223,12 @@ struct ProjCommonArgs {
 };
 int proj_launch(slamgpu_ctx* ctx, const ProjCommonArgs& common, const ProjFrameArgs* h_frames,
                 const ProjFrameArgs* d_frames, int n_frames, int max_nkp);
+// Tracker::match_with_last_key_frame + match_with_map chained on the stream (src/Tracker.cpp:232-248):
+// stage 1 visits kf_order (points observed by the last key frame), its matches are applied on the
+// device (Frame::add_map_match, src/Frame.cpp:80-102), stage 2 visits the whole set.
+int proj_launch_track(slamgpu_ctx* ctx, const ProjCommonArgs& common, const ProjFrameArgs& frame, uint8_t* d_pt_matched,
+                      uint8_t* d_kp_matched, const int32_t* d_matched_points, int n_matched, const int32_t* d_kf_order,
+                      int n_kf, int32_t* d_out /* [4 x nkp]: kf point, kf dist, map point, map dist */);
 int proj_launch_point_stats(slamgpu_ctx* ctx, const float* d_pos, int n, const int32_t* d_obs_offset,
                             const float* d_obs_center, float* d_normal, float* d_range);
 int proj_launch_kd_gather(slamgpu_ctx* ctx, const float2* d_xy, const int32_t* d_perm, int n, float2* d_kd_xy);

@@ -256,6 +256,33 @@ class MapMatcher:
         return self._project(frame, list(map_),
                              lambda p: frame.is_matched(p) or not p.is_observed_by(key_frame), False)
 
+    def track(self, frame: Frame, map_: Map, last_key_frame: KeyFrame):
+        """Tracker::match_with_last_key_frame followed by Tracker::match_with_map
+        (src/Tracker.cpp:232-248) as one chained device call (slamgpu_track_match): both match lists
+        are applied to `frame` with add_map_match, exactly as the two reference loops do.
+        -> (key-frame matches, map matches)."""
+        points = list(map_)
+        flat = _flatten_points(points)
+        feats = frame.features()
+        nkp = len(feats.keypoints)
+        if nkp == 0:
+            return [], []
+        matched = np.array([frame.is_matched(i) for i in range(nkp)], np.uint8)
+        self.ctx.frame_upload(self._FRAME_SLOT, feats.keypoints, feats.descriptors, None, matched)
+        self.ctx.points_upload(self._SET_SLOT, flat.pos, None, None, flat.obs_offset, flat.obs_desc, flat.obs_center)
+        matched_points = [i for i, p in enumerate(flat.points) if frame.is_matched(p)]
+        kf_points = [i for i, p in enumerate(flat.points) if p.is_observed_by(last_key_frame)]   # :169, map order
+        pose = np.ascontiguousarray(frame.pose().flatten(order="F"))
+        kf_pt, _, map_pt, _ = self.ctx.track_match(self._FRAME_SLOT, self._SET_SLOT, nkp, pose, self._params(False),
+                                                   matched_points, kf_points)
+        kf_matches = [MapPointMatch(flat.points[int(p)], kp) for kp, p in enumerate(kf_pt) if p >= 0]
+        map_matches = [MapPointMatch(flat.points[int(p)], kp) for kp, p in enumerate(map_pt) if p >= 0]
+        for m in kf_matches:
+            frame.add_map_match(m)
+        for m in map_matches:
+            frame.add_map_match(m)
+        return kf_matches, map_matches
+
     def match_for_fuse(self, frame: Frame, points):
         return self._project(frame, list(points), lambda p: frame.is_matched(p), True)
 

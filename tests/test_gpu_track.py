@@ -1,0 +1,165 @@
+"""GPU parity tests of the per-frame tracking pair and of map growth through the C ABI.
+
+slamgpu_track_match chains Tracker::match_with_last_key_frame and Tracker::match_with_map
+(src/Tracker.cpp:232-248) on the device; the bar is the same as for the single calls: the results
+must be bit-identical to the two reference calls made one after the other with Frame::add_map_match
+(src/Frame.cpp:80-102) applied in between -- here the oracle called twice with the masks updated on
+the host.  slamgpu_points_append must leave the resident set exactly as one full upload would."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+def _params(pkg, cam, radius=20.0, max_dist=64.0, replace=0):
+    return pkg.ProjParams(cam["fx"], cam["fy"], cam["cx"], cam["cy"], cam["width"], cam["height"], radius, max_dist,
+                          0.5, 2.0, 1.25, replace)
+
+
+def _oparams(oracle, p):
+    return oracle.ProjParams(p.fx, p.fy, p.cx, p.cy, p.width, p.height, p.radius, p.max_dist, p.min_cos, p.nearer,
+                             p.further, p.replace)
+
+
+def _oracle_track(oracle, sc, perm, kp_matched, matched_points, kf_points, op):
+    """The two reference calls in sequence, with add_map_match between and after them."""
+    n = len(sc.pos)
+    pt_matched = np.zeros(n, np.uint8)
+    pt_matched[matched_points] = 1
+    kp_matched = kp_matched.copy()
+    in_kf = np.zeros(n, np.uint8)
+    in_kf[kf_points] = 1
+    skip1 = (pt_matched | (1 - in_kf)).astype(np.uint8)          # :53 and :169
+    r1 = oracle.match_projection(sc.kp_xy, sc.kp_desc, perm, kp_matched, sc.pos, sc.normal, sc.range, sc.obs_offset,
+                                 sc.obs_desc, skip1, None, sc.pose, op, want_stats=False)
+    for kp, pi in enumerate(r1.point):
+        if pi >= 0:
+            assert not kp_matched[kp] and not pt_matched[pi]
+            kp_matched[kp] = 1
+            pt_matched[pi] = 1
+    r2 = oracle.match_projection(sc.kp_xy, sc.kp_desc, perm, kp_matched, sc.pos, sc.normal, sc.range, sc.obs_offset,
+                                 sc.obs_desc, pt_matched, None, sc.pose, op, want_stats=False)
+    for kp, pi in enumerate(r2.point):
+        if pi >= 0:
+            kp_matched[kp] = 1
+            pt_matched[pi] = 1
+    return r1, r2, kp_matched, pt_matched
+
+
+TRACK_SCENES = [
+    # n_points, nkp, seed, cam, n_kf, n_matched
+    (10000, 2000, 2, "KITTI", 3000, 300),      # BASELINE C2 sizes
+    (30000, 8000, 3, "HD1080", 3000, 1500),    # BASELINE C3 frame size, ~3k points seen by the key frame
+    (2000, 500, 7, "KITTI", 0, 0),             # no key-frame points: stage 1 is empty
+    (2000, 500, 8, "KITTI", 2000, 0),          # the key frame sees every point: stage 2 finds what is left
+    (500, 300, 9, "KITTI", 100, 500),          # every point already matched in the frame: nothing at all
+]
+
+
+@pytest.mark.parametrize("n_points,nkp,seed,cam,n_kf,n_matched", TRACK_SCENES)
+def test_track_match_equals_the_two_reference_calls(ctx, oracle, pkg, n_points, nkp, seed, cam, n_kf, n_matched):
+    camd = getattr(pkg.synthetic, cam)
+    sc = pkg.synthetic.projection_scene(n_points, nkp, seed, cam=camd)
+    rng = np.random.default_rng(seed + 100)
+    kf_points = np.sort(rng.choice(n_points, n_kf, replace=False)).astype(np.int32)
+    matched_points = rng.choice(n_points, n_matched, replace=False).astype(np.int32)
+    p = _params(pkg, camd)
+    perm = oracle.kd_build(sc.kp_xy)
+    r1, r2, kp_after, pt_after = _oracle_track(oracle, sc, perm, sc.kp_matched, matched_points, kf_points,
+                                               _oparams(oracle, p))
+    ctx.frame_upload(7, sc.kp_xy, sc.kp_desc, None, sc.kp_matched)
+    ctx.points_upload(7, sc.pos, sc.normal, sc.range, sc.obs_offset, sc.obs_desc)
+    kf_pt, kf_d, map_pt, map_d = ctx.track_match(7, 7, nkp, sc.pose, p, matched_points, kf_points)
+    assert np.array_equal(kf_pt, r1.point) and np.array_equal(kf_d, r1.dist)
+    assert np.array_equal(map_pt, r2.point) and np.array_equal(map_d, r2.dist)
+    if n_matched < n_points and n_kf > 0:
+        assert (kf_pt >= 0).sum() > 0
+    # no keypoint and no point is handed out twice across the two stages
+    both = np.concatenate([kf_pt[kf_pt >= 0], map_pt[map_pt >= 0]])
+    assert len(np.unique(both)) == len(both) and not np.any((kf_pt >= 0) & (map_pt >= 0))
+    # the resident frame now carries the host frame's flags after both add_map_match loops: a fuse-style
+    # call that skips the matched points must agree with the oracle run on the updated masks
+    ref3 = oracle.match_projection(sc.kp_xy, sc.kp_desc, perm, kp_after, sc.pos, sc.normal, sc.range, sc.obs_offset,
+                                   sc.obs_desc, pt_after, None, sc.pose, _oparams(oracle, p), want_stats=False)
+    op3, od3 = ctx.match_projection(7, 7, nkp, sc.pose, p, pt_after, None)
+    assert np.array_equal(op3, ref3.point) and np.array_equal(od3, ref3.dist)
+    # a second track call on the same frame starts from the flags the first one left behind
+    mp2 = np.nonzero(pt_after)[0].astype(np.int32)
+    q1, q2, _, _ = _oracle_track(oracle, sc, perm, kp_after, mp2, kf_points, _oparams(oracle, p))
+    again = ctx.track_match(7, 7, nkp, sc.pose, p, mp2, kf_points)
+    assert np.array_equal(again[0], q1.point) and np.array_equal(again[2], q2.point)
+    ctx.frame_release(7), ctx.points_release(7)
+
+
+def test_track_match_argument_errors(ctx, pkg):
+    sc = pkg.synthetic.projection_scene(100, 50, 1)
+    p = _params(pkg, pkg.synthetic.KITTI)
+    ctx.frame_upload(8, sc.kp_xy, sc.kp_desc, None, None)
+    ctx.points_upload(8, sc.pos, sc.normal, sc.range, sc.obs_offset, sc.obs_desc)
+    with pytest.raises(pkg.SlamGpuError):
+        ctx.track_match(8, 8, 50, sc.pose, p, [], [5, 3])            # not ascending
+    with pytest.raises(pkg.SlamGpuError):
+        ctx.track_match(8, 8, 50, sc.pose, p, [100], [])             # outside the set
+    with pytest.raises(pkg.SlamGpuError):
+        ctx.track_match(8, 99, 50, sc.pose, p, [], [])               # unknown set
+    ctx.frame_release(8), ctx.points_release(8)
+
+
+@pytest.mark.parametrize("derive", [False, True])
+def test_points_append_equals_one_full_upload(ctx, oracle, pkg, derive):
+    """Map growth in blocks of uneven size (including growth past the doubled capacity and an empty
+    initial set) leaves normals, ranges and match results bit-identical to one upload."""
+    n, nkp = 9000, 1500
+    sc = pkg.synthetic.projection_scene(n, nkp, 41)
+    p = _params(pkg, pkg.synthetic.KITTI)
+    nrm, rng_ = (None, None) if derive else (sc.normal, sc.range)
+    cen = sc.obs_center if derive else None
+    ctx.points_upload(20, sc.pos, nrm, rng_, sc.obs_offset, sc.obs_desc, cen)
+    cuts = [0, 0, 1, 2, 700, 701, 5000, 5003, n]      # first block empty
+    off = sc.obs_offset
+
+    def block(a, b):
+        o0, o1 = off[a], off[b]
+        return (sc.pos[a:b], None if derive else sc.normal[a:b], None if derive else sc.range[a:b],
+                (off[a:b + 1] - o0).astype(np.int32), sc.obs_desc[o0:o1], sc.obs_center[o0:o1] if derive else None)
+
+    ctx.points_upload(21, *block(0, 0))
+    for a, b in zip(cuts[:-1], cuts[1:]):
+        ctx.points_append(21, *block(a, b))
+    assert ctx.points_count(21) == (n, int(off[n])) == ctx.points_count(20)
+    n_full, r_full = ctx.points_stats(20, n)
+    n_app, r_app = ctx.points_stats(21, n)
+    assert np.array_equal(n_full, n_app) and np.array_equal(r_full, r_app)
+    if derive:
+        on, orng = oracle.point_stats(sc.pos, sc.obs_offset, sc.obs_center)
+        assert np.array_equal(n_app, on) and np.array_equal(r_app, orng)
+    ctx.frame_upload(20, sc.kp_xy, sc.kp_desc, None, sc.kp_matched)
+    a = ctx.match_projection(20, 20, nkp, sc.pose, p, sc.skip, None)
+    b = ctx.match_projection(20, 21, nkp, sc.pose, p, sc.skip, None)
+    assert np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1]) and (a[0] >= 0).sum() > 100
+    ctx.frame_release(20), ctx.points_release(20), ctx.points_release(21)
+
+
+def test_mirror_track_equals_the_reference_call_sequence(ctx, oracle, pkg):
+    """MapMatcher.track() through the mirror classes == match_key_frame, add_map_match loop,
+    match_map, add_map_match loop (src/Tracker.cpp:232-248) on an identical second world."""
+    from test_gpu_proj import _build_world
+    m = pkg.matcher
+    cam, world_a, kfs_a, frame_a = _build_world(pkg, 77)
+    _, world_b, kfs_b, frame_b = _build_world(pkg, 77)
+    matcher = m.MapMatcher(cam, m.ORB_MAX_DISTANCE, m.NORM_HAMMING, ctx=ctx)
+    idx_a = {id(p): i for i, p in enumerate(world_a)}
+    idx_b = {id(p): i for i, p in enumerate(world_b)}
+    kf_m, map_m = matcher.track(frame_a, world_a, kfs_a[2])
+    want_kf = matcher.match_key_frame(frame_b, world_b, kfs_b[2])
+    for x in want_kf:
+        frame_b.add_map_match(x)
+    want_map = matcher.match_map(frame_b, world_b)
+    for x in want_map:
+        frame_b.add_map_match(x)
+    assert [(idx_a[id(x.point)], x.keypoint_index) for x in kf_m] == \
+           [(idx_b[id(x.point)], x.keypoint_index) for x in want_kf]
+    assert [(idx_a[id(x.point)], x.keypoint_index) for x in map_m] == \
+           [(idx_b[id(x.point)], x.keypoint_index) for x in want_map]
+    assert len(kf_m) > 5 and len(map_m) > 20
+    assert frame_a.num_map_matches() == frame_b.num_map_matches()
