@@ -566,7 +566,72 @@ def also_measurements(ctx, pkg, torch, stream, n_sm, peaks):
     for k in ids:
         ctx.frame_release(k)
     ctx.points_release(901)
+
+    # C3: the tracking sequence, shortened 10x in frames with 10x the points per frame so that the map
+    # still grows 0 -> 200k (tools/bench_c3.py runs the full 2000 frames; profiles/ holds its output)
+    sys.path.insert(0, os.path.join(ROOT, "tools"))
+    import bench_c3
+    bench_c3.run_sequence(ctx, pkg, 10, 8000, 1000, 3, 0)
+    out["c3_tracking_sequence_200_frames"] = bench_c3.run_sequence(ctx, pkg, 200, 8000, 1000, 3, 3, c3_cpu_arm)
     return out
+
+
+def c3_cpu_arm(pkg, seq, kept, prm):
+    """The same four steps on the host for the sampled frames; also the parity check of those frames."""
+    from oracle import cpu_oracle
+    try:
+        import cv2
+        cv2.setNumThreads(os.cpu_count() or 1)
+    except Exception:           # the GPU box may not have cv2: the oracle port stands in
+        cv2 = None
+    oprm = cpu_oracle.ProjParams(prm.fx, prm.fy, prm.cx, prm.cy, prm.width, prm.height, prm.radius, prm.max_dist,
+                                 prm.min_cos, prm.nearer, prm.further, 0)
+    p = seq.pool
+    t_bf = t_kd = t_proj = 0.0
+    parity_ok = True
+    for f, (prev, cur, (ft, fq), res) in sorted(kept.items()):
+        n = seq.map_size(f)
+        t0 = time.perf_counter()
+        if cv2 is not None:
+            ms = cv2.BFMatcher(cv2.NORM_HAMMING, True).knnMatch(cur["kp_desc"], prev["kp_desc"], 1)   # FeatureExtractor.cpp:20-21
+            pairs = [(m[0].trainIdx, m[0].queryIdx) for m in ms if m and m[0].distance < MAX_DIST]
+            o_t = np.array([a for a, _ in pairs], np.int32)
+            o_q = np.array([b for _, b in pairs], np.int32)
+        else:
+            o_t, o_q = cpu_oracle.match_features(prev["kp_desc"], cur["kp_desc"], MAX_DIST)
+        t1 = time.perf_counter()
+        perm = cpu_oracle.kd_build(cur["kp_xy"])
+        t2 = time.perf_counter()
+        pt = np.zeros(n, np.uint8)
+        pt[cur["matched_points"]] = 1
+        in_kf = np.zeros(n, np.uint8)
+        in_kf[cur["kf_points"]] = 1
+        kpm = cur["kp_matched"].copy()
+        off = p.obs_offset[:n + 1]
+        args = (p.pos[:n], p.normal[:n], p.range[:n], off, p.obs_desc[:int(off[-1])])
+        r1 = cpu_oracle.match_projection(cur["kp_xy"], cur["kp_desc"], perm, kpm, *args, (pt | (1 - in_kf)).astype(np.uint8),
+                                         None, cur["pose"], oprm, want_stats=False)
+        hit = r1.point >= 0
+        kpm[hit] = 1
+        pt[r1.point[hit]] = 1
+        r2 = cpu_oracle.match_projection(cur["kp_xy"], cur["kp_desc"], perm, kpm, *args, pt, None, cur["pose"], oprm,
+                                         want_stats=False)
+        t3 = time.perf_counter()
+        t_bf += t1 - t0
+        t_kd += t2 - t1
+        t_proj += t3 - t2
+        parity_ok &= bool(np.array_equal(ft, o_t) and np.array_equal(fq, o_q) and np.array_equal(res[0], r1.point)
+                          and np.array_equal(res[1], r1.dist) and np.array_equal(res[2], r2.point)
+                          and np.array_equal(res[3], r2.dist))
+    k = len(kept)
+    tot = t_bf + t_kd + t_proj
+    return {"frames_per_s": k / tot, "ms_per_frame": tot / k * 1e3,
+            "ms_per_frame_parts": {"match_features": t_bf / k * 1e3, "kd_build": t_kd / k * 1e3, "projection_pair": t_proj / k * 1e3},
+            "sample": f"{k} frames spread over the run (map sizes {[seq.map_size(f) for f in sorted(kept)]})",
+            "kind": ("cv2 BFMatcher cross-check (all cores)" if cv2 is not None else "oracle cross-check") +
+                    " + oracle/slam_oracle.cpp KD build and projection search (1 core, like the reference)",
+            "cores": os.cpu_count(), "gpu_results_identical_on_sample": parity_ok}
+
 
 
 def main():

@@ -113,6 +113,7 @@ void fill_frame(ProjFrameArgs& f, const FrameDev& fd, const float* pose, const s
     f.proposals = fd.proposals;
     f.cell_start = fd.cell_start;
     f.cell_items = fd.cell_items;
+    f.cell_rec = fd.cell_rec;
     f.gx0 = fd.gx0;
     f.gy0 = fd.gy0;
     f.inv_cell = fd.inv_cell;
@@ -284,10 +285,20 @@ int slamgpu_frame_upload(slamgpu_ctx* ctx, int frame_id, int nkp, const float* x
         SG_TRY(slamgpu_kd_build_host(xy, nkp, perm.data()));
     }
 
+    // a slot that is uploaded again (the tracker's current frame, every frame) keeps its allocation
+    // when it is large enough: cudaFree + cudaMalloc cost more than the upload itself
+    struct Held {   // freed on every early return unless the new frame adopts it
+        void* p = nullptr;
+        ~Held() { if (p) cudaFree(p); }
+    } held;
+    void*& old_blob = held.p;
+    size_t old_bytes = 0;
     auto it = ctx->frames.find(frame_id);
     if (it != ctx->frames.end()) {
         SG_CUDA(cudaStreamSynchronize(ctx->stream));
-        free_frame(it->second);
+        old_blob = it->second.blob;
+        old_bytes = it->second.blob_bytes;
+        it->second.blob = nullptr;
         ctx->frames.erase(it);
     }
     FrameDev f;
@@ -296,7 +307,7 @@ int slamgpu_frame_upload(slamgpu_ctx* ctx, int frame_id, int nkp, const float* x
     const size_t n = static_cast<size_t>(nkp);
 
     // uniform grid over the keypoints' bounding box: 32 px cells (coarser when that would exceed 1 Mi cells)
-    float cell = 32.0f;
+    float cell = ctx->grid_cell;
     if (nkp > 0) {
         float x0 = xy[0], x1 = xy[0], y0 = xy[1], y1 = xy[1];
         for (int i = 0; i < nkp; ++i) {
@@ -318,17 +329,26 @@ int slamgpu_frame_upload(slamgpu_ctx* ctx, int frame_id, int nkp, const float* x
         f.inv_cell = 1.0f / cell;
     }
     const size_t n_cells = static_cast<size_t>(f.gw) * f.gh;
-    // device blob: [kd_xy][kd_idx][desc][matched][xy][cell_start][cell_items] (uploaded) then [proposals] (device only)
+    // device blob: [kd_xy][kd_idx][desc][matched][xy][cell_start][cell_items][cell_rec] (uploaded) then [proposals] (device only)
     const size_t b_kdxy = Carver::padded(n * sizeof(float2)), b_kdidx = Carver::padded(n * sizeof(int32_t)),
                  b_desc = Carver::padded(n * 32), b_matched = Carver::padded(n), b_xy = Carver::padded(n * sizeof(float2)),
                  b_cstart = Carver::padded((n_cells + 1) * sizeof(int32_t)), b_citems = Carver::padded(n * sizeof(int32_t)),
-                 b_prop = Carver::padded(n * sizeof(unsigned long long));
-    const size_t up = b_kdxy + b_kdidx + b_desc + b_matched + b_xy + b_cstart + b_citems;
+                 b_crec = Carver::padded(n * sizeof(int4)), b_prop = Carver::padded(n * sizeof(unsigned long long));
+    const size_t up = b_kdxy + b_kdidx + b_desc + b_matched + b_xy + b_cstart + b_citems + b_crec;
     const size_t total = up + b_prop + 256;
-    const cudaError_t e = cudaMalloc(&f.blob, total);
-    if (e != cudaSuccess) {
-        cudaGetLastError();
-        return fail(SLAMGPU_ERR_NOMEM, std::string("frame allocation failed: ") + cudaGetErrorString(e));
+    if (old_blob && old_bytes >= total) {
+        f.blob = old_blob;
+        f.blob_bytes = old_bytes;
+        old_blob = nullptr;
+    } else {
+        if (old_blob) cudaFree(old_blob);
+        old_blob = nullptr;
+        const cudaError_t e = cudaMalloc(&f.blob, total);
+        if (e != cudaSuccess) {
+            cudaGetLastError();
+            return fail(SLAMGPU_ERR_NOMEM, std::string("frame allocation failed: ") + cudaGetErrorString(e));
+        }
+        f.blob_bytes = total;
     }
     Carver dv(f.blob);
     f.kd_xy = dv.take<float2>(n);
@@ -338,6 +358,7 @@ int slamgpu_frame_upload(slamgpu_ctx* ctx, int frame_id, int nkp, const float* x
     f.xy = dv.take<float2>(n);
     f.cell_start = dv.take<int32_t>(n_cells + 1);
     f.cell_items = dv.take<int32_t>(n);
+    f.cell_rec = dv.take<int4>(n);
     f.proposals = dv.take<unsigned long long>(n);
 
     if (nkp > 0) {
@@ -384,6 +405,16 @@ int slamgpu_frame_upload(slamgpu_ctx* ctx, int frame_id, int nkp, const float* x
         {
             std::vector<int32_t> cursor(h_cstart, h_cstart + n_cells);
             for (size_t m = 0; m < n; ++m) h_citems[cursor[cell_of(h_kdxy[2 * m], h_kdxy[2 * m + 1])]++] = static_cast<int32_t>(m);
+        }
+        // one 16-byte record per grid slot: (x bits, y bits, keypoint index, KD position) -- everything the
+        // candidate test needs in a single load
+        int4* h_crec = hv.take<int4>(n);
+        for (size_t i = 0; i < n; ++i) {
+            const int32_t m = h_citems[i];
+            int32_t xb, yb;
+            std::memcpy(&xb, &h_kdxy[2 * m], 4);
+            std::memcpy(&yb, &h_kdxy[2 * m + 1], 4);
+            h_crec[i] = make_int4(xb, yb, h_kdidx[m], m);
         }
         SG_CUDA(cudaMemcpyAsync(f.blob, ctx->h_stage.ptr, up, cudaMemcpyHostToDevice, ctx->stream));
         SG_CUDA(cudaMemsetAsync(f.proposals, 0xFF, n * sizeof(unsigned long long), ctx->stream));

@@ -344,6 +344,203 @@ __global__ void __launch_bounds__(kGroupThreads) proj_match_warp_kernel(const Pr
     }
 }
 
+// ---------------------------------------------------------------------------------------------
+// K4, group-per-point form v3 (default).  ncu on the kernel above (profiles/r01_ncu_full_prof_proj_match_v2.txt):
+// 0.18 instructions issued per scheduler cycle, 66 % of the stall cycles on L1TEX scoreboards -- the time is
+// the DEPTH of the dependent-load chain (order -> point -> per cell row: cell_start -> cell_items -> kd_xy ->
+// kd_idx -> matched -> desc -> observations), about 18 round trips through L2 for a three-row search.
+// Same arithmetic, same candidates, same tie rule; the chain is cut to 5 round trips:
+//   1. order[v]
+//   2. everything indexed by the point at once (skip flag, position, normal, range, observation offsets)
+//   3. the cell-row bounds, one row per lane, and the point's first observation descriptors (kept in
+//      registers, then parked in shared memory for the group)
+//   4. one 16-byte record per grid slot (x, y, keypoint index, KD position); the rows are flattened so
+//      that the lanes share all slots evenly
+//   5. the keypoint's matched flag and descriptor together
+// ---------------------------------------------------------------------------------------------
+constexpr int kObsStaged = 8;     // observation descriptors of a point parked in shared memory (the rest: global)
+
+template <int LANES>
+__global__ void __launch_bounds__(kGroupThreads) proj_match_group_kernel(const ProjKernelArgs a)
+{
+    constexpr int GROUPS = kGroupThreads / LANES;
+    constexpr int STAGE_REGS = (2 * kObsStaged + LANES - 1) / LANES;
+    __shared__ uint4 s_obs[GROUPS][2 * kObsStaged];
+    const ProjFrameArgs& f = a.frames ? a.frames[blockIdx.y] : a.inline_frame;
+    const ProjCommonArgs& c = a.c;
+    const int lane = threadIdx.x % LANES;
+    const int grp = threadIdx.x / LANES;
+    const unsigned gmask = LANES == 32 ? 0xFFFFFFFFu : (((1u << LANES) - 1u) << ((threadIdx.x & 31) / LANES * LANES));
+    const int v = blockIdx.x * GROUPS + grp;
+    if (v >= c.n_visit) return;
+    const size_t dbg_row = static_cast<size_t>(blockIdx.y) * c.n_visit + v;
+
+    const int pi = c.order ? c.order[v] : v;
+    if (pi < 0) return;                               // match_for_fuse nullptr, src/MapMatcher.cpp:119-121
+    // round trip 2: every load indexed by the point is issued before the first test
+    const unsigned skipped = f.skip ? f.skip[pi] : 0u;
+    const float X[3] = {c.pos[3 * pi], c.pos[3 * pi + 1], c.pos[3 * pi + 2]};
+    const float nx = c.normal[3 * pi], ny = c.normal[3 * pi + 1], nz = c.normal[3 * pi + 2];
+    const float nearest = c.range[2 * pi], furthest = c.range[2 * pi + 1];
+    const int o_begin = c.obs_offset[pi], o_end = c.obs_offset[pi + 1];
+    if (skipped) return;                              // :53 is_matched(point) / :169 !is_observed_by
+
+    float h[3];
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {                     // P1, same order as the kernels above
+        h[i] = sum3(__fmul_rn(f.M[4 * i], X[0]), __fmul_rn(f.M[4 * i + 1], X[1]), __fmul_rn(f.M[4 * i + 2], X[2]));
+        h[i] = __fadd_rn(h[i], f.M[4 * i + 3]);
+    }
+    float u, w;
+    if (h[2] < 0.0f) {
+        u = -1.0f; w = -1.0f;
+    } else {
+        u = __fdiv_rn(h[0], h[2]);
+        w = __fdiv_rn(h[1], h[2]);
+    }
+    if (c.dbg_uv && lane == 0) {
+        c.dbg_uv[2 * dbg_row] = u;
+        c.dbg_uv[2 * dbg_row + 1] = w;
+    }
+    if (!(u >= 0.0f && u < c.width_f && w >= 0.0f && w < c.height_f)) return;      // P2
+
+    // round trip 3a: the first observation descriptors, one or two 16-byte halves per lane
+    const int n_obs = o_end - o_begin;
+    const int n_staged = min(n_obs, kObsStaged);
+    uint4 stage[STAGE_REGS];
+#pragma unroll
+    for (int r = 0; r < STAGE_REGS; ++r) {
+        const int k = lane + r * LANES;
+        stage[r] = k < 2 * n_staged ? __ldg(&c.obs_desc[2 * static_cast<size_t>(o_begin) + k]) : make_uint4(0, 0, 0, 0);
+    }
+    // round trip 3b: bounds of the cell rows the search box touches, one row per lane
+    const float pad = c.radius + 1.0f;                           // conservative box; the exact test is d2 <= r2
+    const int cx0 = grid_cell(u - pad, f.gx0, f.inv_cell, f.gw), cx1 = grid_cell(u + pad, f.gx0, f.inv_cell, f.gw);
+    const int cy0 = grid_cell(w - pad, f.gy0, f.inv_cell, f.gh), cy1 = grid_cell(w + pad, f.gy0, f.inv_cell, f.gh);
+    const int n_rows = cy1 - cy0 + 1;
+    int rb = 0, re = 0;
+    if (lane < n_rows) {
+        rb = f.cell_start[(cy0 + lane) * f.gw + cx0];
+        re = f.cell_start[(cy0 + lane) * f.gw + cx1 + 1];
+    }
+
+    if (c.stats && lane == 0) {
+        if (fabsf(u) < 1e-4f || fabsf(__fsub_rn(u, c.width_f)) < 1e-4f || fabsf(w) < 1e-4f ||
+            fabsf(__fsub_rn(w, c.height_f)) < 1e-4f)
+            atomicAdd(&c.stats[0], 1ull);
+    }
+    const float ray[3] = {__fsub_rn(X[0], f.C[0]), __fsub_rn(X[1], f.C[1]), __fsub_rn(X[2], f.C[2])};
+    float rn[3];
+    normalized3(ray, rn);
+    if (sum3(__fmul_rn(nx, rn[0]), __fmul_rn(ny, rn[1]), __fmul_rn(nz, rn[2])) < c.min_cos) return;   // P3
+    const float distance = norm3(ray);
+    if (distance < __fdiv_rn(nearest, c.nearer) || distance > __fmul_rn(furthest, c.further)) return;  // P4
+
+    if (c.stats) {   // diagnostic only: keypoints within 1e-4 px of the search radius
+        unsigned long long cnt = 0;
+        for (int k = lane; k < f.nkp; k += LANES) {
+            const float2 p = f.xy[k];
+            const float dx = __fsub_rn(p.x, u), dy = __fsub_rn(p.y, w);
+            const float d = __fsqrt_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)));
+            if (fabsf(__fsub_rn(d, c.radius)) < 1e-4f) cnt++;
+        }
+        if (cnt) atomicAdd(&c.stats[1], cnt);
+    }
+
+#pragma unroll
+    for (int r = 0; r < STAGE_REGS; ++r) {
+        const int k = lane + r * LANES;
+        if (k < 2 * kObsStaged) s_obs[grp][k] = stage[r];
+    }
+    __syncwarp(gmask);
+
+    // P5 + P6: candidates from the grid, the rows flattened over the lanes
+    int best = c.thr;                                            // lane-local best: accept d < thr
+    int best_m = -1;
+    for (int row0 = 0; row0 < n_rows; row0 += LANES) {
+        if (row0 > 0) {                                          // more rows than lanes (huge radius): next batch
+            rb = re = 0;
+            if (row0 + lane < n_rows) {
+                rb = f.cell_start[(cy0 + row0 + lane) * f.gw + cx0];
+                re = f.cell_start[(cy0 + row0 + lane) * f.gw + cx1 + 1];
+            }
+        }
+        const int len = re - rb;
+        int incl = len;                                          // inclusive prefix sum of the row lengths
+#pragma unroll
+        for (int d = 1; d < LANES; d <<= 1) {
+            const int t = __shfl_up_sync(gmask, incl, d, LANES);
+            if (lane >= d) incl += t;
+        }
+        const int total = __shfl_sync(gmask, incl, LANES - 1, LANES);
+        const int excl = incl - len;
+        const int rows_here = min(n_rows - row0, LANES);
+        for (int base = 0; base < total; base += LANES) {
+            const int t = base + lane;
+            int slot = -1;
+            for (int r = 0; r < rows_here; ++r) {                // which row does flat index t fall in?
+                const int e_r = __shfl_sync(gmask, excl, r, LANES);
+                const int l_r = __shfl_sync(gmask, len, r, LANES);
+                const int b_r = __shfl_sync(gmask, rb, r, LANES);
+                if (t >= e_r && t < e_r + l_r) slot = b_r + (t - e_r);
+            }
+            if (slot < 0) continue;
+            // round trip 4.  (Prefetching the next batch's records here was measured slower: 80 registers
+            // instead of 72 cost more occupancy than the overlap gained; profiles/r01_proj_variants_v3b.txt.)
+            const int4 rec = __ldg(&f.cell_rec[slot]);
+            const float dx = __fsub_rn(__int_as_float(rec.x), u);                // src/KDTree.cpp:61
+            const float dy = __fsub_rn(__int_as_float(rec.y), w);                // :62
+            const float d2 = __fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy));    // :63
+            if (!(d2 <= c.r2)) continue;                         // :65
+            const int kp = rec.z, m = rec.w;
+            const unsigned kp_matched = f.matched[kp];           // round trip 5: flag and descriptor together
+            const uint4 a0 = __ldg(&f.desc[2 * kp]), a1 = __ldg(&f.desc[2 * kp + 1]);
+            if (!c.replace && kp_matched) continue;              // src/MapMatcher.cpp:81
+            int dmin = 1 << 20;
+            for (int o = 0; o < n_staged; ++o)                   // :86
+                dmin = min(dmin, hamming256(a0, a1, s_obs[grp][2 * o], s_obs[grp][2 * o + 1]));
+            for (int o = o_begin + kObsStaged; o < o_end; ++o) {
+                const uint4 b0 = __ldg(&c.obs_desc[2 * static_cast<size_t>(o)]);
+                const uint4 b1 = __ldg(&c.obs_desc[2 * static_cast<size_t>(o) + 1]);
+                dmin = min(dmin, hamming256(a0, a1, b0, b1));
+            }
+            if (dmin < best) {
+                best = dmin;
+                best_m = m;
+            } else if (dmin == best && best_m >= 0) {            // tie inside one lane: earlier visit wins
+                if (kd_visit_key(f.kd_xy, f.nkp, m, u, w) < kd_visit_key(f.kd_xy, f.nkp, best_m, u, w)) best_m = m;
+            }
+        }
+    }
+    // group winner: minimum distance, then earliest KD visit
+    const int wbest = __reduce_min_sync(gmask, best_m >= 0 ? best : (1 << 20));
+    if (wbest >= c.thr) return;                                  // nothing under max_descriptor_distance
+    const bool tied = best_m >= 0 && best == wbest;
+    const unsigned ballot = __ballot_sync(gmask, tied);
+    int win_lane = __ffs(ballot) - 1;                            // lane index within the warp
+    if (__popc(ballot) > 1) {
+        unsigned long long key = tied ? kd_visit_key(f.kd_xy, f.nkp, best_m, u, w) : ~0ull;
+        const unsigned hi = __reduce_min_sync(gmask, static_cast<unsigned>(key >> 32));
+        const unsigned lo = __reduce_min_sync(gmask, (key >> 32) == hi ? static_cast<unsigned>(key) : 0xFFFFFFFFu);
+        const unsigned long long wkey = (static_cast<unsigned long long>(hi) << 32) | lo;
+        win_lane = __ffs(__ballot_sync(gmask, tied && key == wkey)) - 1;
+    }
+    if (static_cast<int>(threadIdx.x & 31) == win_lane) {
+        const int best_kp = f.kd_idx[best_m];
+        // P7: first point in visit order attaining the minimum wins (src/MapMatcher.cpp:95-97)
+        const unsigned long long key = (static_cast<unsigned long long>(wbest) << 32) | static_cast<unsigned>(v);
+        atomicMin(&f.proposals[best_kp], key);
+        if (c.dbg_kp) c.dbg_kp[dbg_row] = best_kp;
+        if (c.dbg_d) c.dbg_d[dbg_row] = wbest;
+    }
+}
+
+// Measured and dropped (profiles/r01_proj_variants_v4.txt): a cooperative form in which every lane first
+// projects and gates its own point and the group then walks its survivors one by one.  It removes the 8x
+// redundant projection arithmetic but was no faster on 200k points (103 vs 87 us) and 2.5x slower on 10k:
+// the kernel is bound by the latency of its dependent loads at the occupancy its registers allow, not by
+// instruction issue.
+
 __global__ void proj_emit_kernel(const ProjKernelArgs a)
 {
     const ProjFrameArgs& f = a.frames ? a.frames[blockIdx.y] : a.inline_frame;
@@ -441,15 +638,19 @@ static void launch_match(slamgpu_ctx* ctx, const ProjKernelArgs& a, int n_visit,
         const dim3 gp((n_visit + kProjThreads - 1) / kProjThreads, n_frames);
         proj_match_kernel<<<gp, kProjThreads, 0, ctx->stream>>>(a);
     } else {
-        // 8 lanes per point: as fast as a full warp on C2 (19 us) and 1.8x faster on C4-sized batches
-        // (tools/time_proj.py, profiles/r01_proj_variants.txt); SLAMGPU_PROJ_LANES=32 overrides
+        // 8 lanes per point: as fast as a full warp on C2 (16 us) and 1.8x faster on C4-sized batches; 4 lanes
+        // are no faster on large maps and slower on small ones (tools/time_proj.py,
+        // profiles/r01_proj_variants_v3*.txt); SLAMGPU_PROJ_LANES=32 overrides
         const int lanes = ctx->proj_lanes ? ctx->proj_lanes : 8;
         const int per_cta = kGroupThreads / lanes;
         const dim3 gp((n_visit + per_cta - 1) / per_cta, n_frames);
-        if (lanes == 8) {
-            proj_match_warp_kernel<8><<<gp, kGroupThreads, 0, ctx->stream>>>(a);
+        if (ctx->proj_v2) {             // previous form, kept for A/B checks (SLAMGPU_PROJ_V2=1)
+            if (lanes == 8) proj_match_warp_kernel<8><<<gp, kGroupThreads, 0, ctx->stream>>>(a);
+            else proj_match_warp_kernel<32><<<gp, kGroupThreads, 0, ctx->stream>>>(a);
+        } else if (lanes == 8) {
+            proj_match_group_kernel<8><<<gp, kGroupThreads, 0, ctx->stream>>>(a);
         } else {
-            proj_match_warp_kernel<32><<<gp, kGroupThreads, 0, ctx->stream>>>(a);
+            proj_match_group_kernel<32><<<gp, kGroupThreads, 0, ctx->stream>>>(a);
         }
     }
     ctx->launches++;

@@ -6,6 +6,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <numeric>
+#include <thread>
 
 #include "slamgpu_internal.cuh"
 
@@ -116,29 +117,65 @@ void host_camera_center(const float* pose, float* C)
 
 // KDTree2D::build (src/KDTree.cpp:8-43) as a permutation: the node of range [s, e) is
 // perm[(s+e)/2] after std::nth_element on axis depth%2.  Ties between equal coordinates are
-// decided by libstdc++'s nth_element, so the same call, comparator and ranges are used; the
-// recursion is unrolled onto an explicit stack (left range first, like the reference).
-static void kd_build_perm(const float* xy, int n, std::vector<size_t>& idx)
+// decided by libstdc++'s nth_element, so the same call, comparison results and ranges are used.
+// Two things make it faster than the reference's form without changing a single comparison outcome:
+//   * the elements are (x, y, index) records instead of indices into a point array -- nth_element
+//     only sees comparator results and moves elements, so the arrangement is the same permutation,
+//     without the indirection;
+//   * after a range is partitioned its two halves are disjoint, so the four quarter-ranges below the
+//     first two levels are built on separate threads (the order in which sub-ranges are processed
+//     cannot change the result).  This is the Frame constructor's cost (src/Frame.cpp:11-15): 1.3 ms
+//     single-threaded for 8000 keypoints, the largest item of a tracked frame
+//     (profiles/r01_c3_sequence_2000_frames_v1.json).
+// Measured and dropped: a restatement of nth_element with branch-free partition scans (no faster than
+// libstdc++'s: ~4 ns per element visit at every level, not branch misses) and a persistent worker pool
+// (condition-variable hand-offs cost more than the two thread forks they save).
+struct KdItem {
+    float x, y;
+    uint32_t idx;
+    uint32_t pad;
+};
+
+static void kd_build_range(KdItem* it, int s, int e, int depth, int fork_min)
 {
-    idx.resize(static_cast<size_t>(n));
-    std::iota(idx.begin(), idx.end(), size_t(0));
     struct Range { int s, e, depth; };
     std::vector<Range> todo;
-    todo.push_back({0, n, 0});
+    std::vector<std::thread> forks;
+    todo.push_back({s, e, depth});
     while (!todo.empty()) {
         const Range r = todo.back();
         todo.pop_back();
         if (r.s >= r.e) continue;
-        const int axis = r.depth % 2;
         const int mid = (r.s + r.e) / 2;
-        std::nth_element(idx.begin() + r.s, idx.begin() + mid, idx.begin() + r.e,
-                         [xy, axis](size_t a, size_t b) { return xy[2 * a + axis] < xy[2 * b + axis]; });
-        // sub-ranges are disjoint, so the order in which they are processed cannot change the result
-        todo.push_back({mid + 1, r.e, r.depth + 1});
+        if (r.depth % 2 == 0)
+            std::nth_element(it + r.s, it + mid, it + r.e, [](const KdItem& a, const KdItem& b) { return a.x < b.x; });
+        else
+            std::nth_element(it + r.s, it + mid, it + r.e, [](const KdItem& a, const KdItem& b) { return a.y < b.y; });
+        if (r.e - r.s >= fork_min) {
+            forks.emplace_back(kd_build_range, it, mid + 1, r.e, r.depth + 1, fork_min);
+        } else {
+            todo.push_back({mid + 1, r.e, r.depth + 1});
+        }
         todo.push_back({r.s, mid, r.depth + 1});
     }
+    for (auto& t : forks) t.join();
 }
 
+static void kd_build_perm(const float* xy, int n, uint32_t* out_perm)
+{
+    std::vector<KdItem> items(static_cast<size_t>(n));
+    for (int i = 0; i < n; ++i) items[i] = {xy[2 * i], xy[2 * i + 1], static_cast<uint32_t>(i), 0u};
+    // SLAMGPU_KD_THREADS = 1, 2, 4 (default), 8 ...: ranges of at least 2n / threads elements fork
+    static const int max_threads = [] {
+        const char* e = std::getenv("SLAMGPU_KD_THREADS");
+        const int hw = static_cast<int>(std::max(1u, std::thread::hardware_concurrency()));
+        return std::max(1, std::min(e ? std::atoi(e) : 4, hw));
+    }();
+    int fork_min = n + 1;
+    if (max_threads > 1 && n >= 2048) fork_min = std::max(512, 2 * n / max_threads - 16);
+    kd_build_range(items.data(), 0, n, 0, fork_min);
+    for (int i = 0; i < n; ++i) out_perm[i] = items[i].idx;
+}
 
 
 #define SG_CTX(ctx)                                                       \
@@ -193,6 +230,10 @@ int slamgpu_create(int device, slamgpu_ctx** out)
     ctx->n_sm = prop.multiProcessorCount;
     const char* walk = std::getenv("SLAMGPU_PROJ_WALK");
     ctx->proj_walk = walk != nullptr && walk[0] == '1';
+    const char* v2 = std::getenv("SLAMGPU_PROJ_V2");
+    ctx->proj_v2 = v2 != nullptr && v2[0] == '1';
+    const char* gcell = std::getenv("SLAMGPU_GRID_CELL");
+    if (gcell != nullptr && std::atof(gcell) >= 1.0) ctx->grid_cell = static_cast<float>(std::atof(gcell));
     const char* lanes = std::getenv("SLAMGPU_PROJ_LANES");
     if (lanes != nullptr) {
         const int v = std::atoi(lanes);
@@ -277,9 +318,7 @@ int slamgpu_kd_build_host(const float* xy, int n, uint32_t* out_perm)
 {
     SG_CHECK(n >= 0, "negative size");
     SG_CHECK(n == 0 || (xy != nullptr && out_perm != nullptr), "null pointer");
-    std::vector<size_t> idx;
-    kd_build_perm(xy, n, idx);
-    for (int i = 0; i < n; ++i) out_perm[i] = static_cast<uint32_t>(idx[i]);
+    kd_build_perm(xy, n, out_perm);
     return SLAMGPU_OK;
 }
 

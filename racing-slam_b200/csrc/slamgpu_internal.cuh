@@ -48,6 +48,7 @@ constexpr uint32_t kKeyNone = 0xFFFFFFFFu;
 struct FrameDev {
     int nkp = 0;
     void* blob = nullptr;         // one allocation; the pointers below are carved out of it
+    size_t blob_bytes = 0;
     float2* kd_xy = nullptr;      // [nkp] keypoint coordinates in KD position order
     int32_t* kd_idx = nullptr;    // [nkp] keypoint index at KD position m (= the permutation)
     uint4* desc = nullptr;        // [nkp*2] descriptors in keypoint order
@@ -57,6 +58,7 @@ struct FrameDev {
     // uniform grid over the keypoints (candidate lookup): cell c holds cell_items[cell_start[c] .. cell_start[c+1])
     int32_t* cell_start = nullptr;            // [gw*gh + 1]
     int32_t* cell_items = nullptr;            // [nkp] KD positions, cell-major
+    int4* cell_rec = nullptr;                 // [nkp] cell-major (x bits, y bits, keypoint index, KD position)
     float gx0 = 0.f, gy0 = 0.f, inv_cell = 1.f;
     int gw = 1, gh = 1;
     std::vector<uint32_t> perm_host;
@@ -94,6 +96,8 @@ struct slamgpu_ctx {
     int64_t launches = 0;
     bool profiling = false;
     int proj_lanes = 0;       // SLAMGPU_PROJ_LANES=8|32 overrides the lanes-per-point choice (0 = by size)
+    bool proj_v2 = false;     // SLAMGPU_PROJ_V2=1: the previous group kernel (row-by-row candidate loop)
+    float grid_cell = 16.0f;  // SLAMGPU_GRID_CELL: keypoint grid cell size in pixels (16: fewest slots per search at radius 15-20)
     bool proj_walk = false;   // SLAMGPU_PROJ_WALK=1: use the thread-per-point KD-walk kernel
     int bf_engine = 0;        // SLAMGPU_BF_ENGINE=int|tc overrides the brute-force engine choice (0 = by size, 1 = int, 2 = tc)
     int tc_variant = 0;       // SLAMGPU_TC_VARIANT: debug switches of the tensor-core scan
@@ -196,6 +200,7 @@ struct ProjFrameArgs {
     unsigned long long* proposals;
     const int32_t* cell_start;
     const int32_t* cell_items;
+    const int4* cell_rec;
     float gx0, gy0, inv_cell;
     int gw, gh;
     const uint8_t* skip;     // [n_points] for this frame or null

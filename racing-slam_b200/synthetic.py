@@ -235,3 +235,50 @@ def keyframe_db_fast(n_frames: int, n_desc: int, seed: int, shared_frac: float =
         m = rng.integers(0, 256, (3, n_shared, 32), dtype=np.uint8)
         db[f, rows] = pool[src] ^ (m[0] & m[1] & m[2])
     return db
+
+
+class TrackingSequence:
+    """a synthetic tracking run.  One pool of map points laid out for a base camera
+    pose; the map at frame f is the pool's first f * points_per_frame points (Map's vector order,
+    src/Map.cpp:164-190), so it grows 0 -> n_frames * points_per_frame.  Every frame has the base
+    frame's keypoints jittered by <= 1 px (integer pixels) and descriptors that are a fresh <= 30-bit
+    perturbation of the base descriptors with 10 % replaced, so consecutive frames differ by <= 60
+    bits on the surviving rows and the link to the map descriptors does not drift over the run."""
+
+    def __init__(self, n_frames: int, nkp: int, points_per_frame: int, seed: int, cam: dict = HD1080,
+                 kf_window: int = 3000, frac_tracked: float = 0.05):
+        self.n_frames, self.nkp, self.ppf, self.seed, self.cam = n_frames, nkp, points_per_frame, seed, dict(cam)
+        self.kf_window, self.frac_tracked = kf_window, frac_tracked
+        self.pool = projection_scene(n_frames * points_per_frame, nkp, seed, cam=cam)
+        self.base_T = np.asarray(self.pool.pose, np.float32).reshape(4, 4, order="F").copy()
+
+    def map_size(self, f: int) -> int:
+        """Points in the map when frame f is tracked (the frame's own new points come after it)."""
+        return f * self.ppf
+
+    def frame(self, f: int):
+        """-> dict(kp_xy, kp_desc, kp_matched, pose, matched_points, kf_points) for frame f."""
+        rng = np.random.default_rng(self.seed * 1000003 + f)
+        W, H = self.cam["width"], self.cam["height"]
+        xy = self.pool.kp_xy + rng.integers(-1, 2, self.pool.kp_xy.shape).astype(np.float32)
+        xy[:, 0] = np.clip(xy[:, 0], 0, W - 1)
+        xy[:, 1] = np.clip(xy[:, 1], 0, H - 1)
+        desc = flip_bits(self.pool.kp_desc, rng.integers(0, 31, self.nkp), rng)
+        repl = rng.random(self.nkp) < 0.1
+        desc[repl] = rng.integers(0, 256, (int(repl.sum()), 32), dtype=np.uint8)
+        T = self.base_T.copy()
+        T[:3, 3] += rng.uniform(-0.02, 0.02, 3).astype(np.float32)
+        n = self.map_size(f)
+        kf_points = np.arange(max(0, n - self.kf_window), n, dtype=np.int32)    # seen by the last key frame
+        tracked = kf_points[rng.random(len(kf_points)) < self.frac_tracked]      # track_from_last_frame
+        return dict(kp_xy=np.ascontiguousarray(xy, np.float32), kp_desc=np.ascontiguousarray(desc),
+                    kp_matched=self.pool.kp_matched, pose=pose_colmajor(T), matched_points=tracked.astype(np.int32),
+                    kf_points=kf_points)
+
+    def new_points(self, f: int):
+        """The block Mapper::insert adds after frame f: (pos, normal, range, obs_offset (relative), obs_desc)."""
+        a, b = f * self.ppf, (f + 1) * self.ppf
+        p = self.pool
+        o0, o1 = int(p.obs_offset[a]), int(p.obs_offset[b])
+        return (p.pos[a:b], p.normal[a:b], p.range[a:b], (p.obs_offset[a:b + 1] - o0).astype(np.int32),
+                p.obs_desc[o0:o1])

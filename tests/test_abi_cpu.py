@@ -78,6 +78,18 @@ def test_kd_build_host_random_sizes(pkg, oracle):
         assert np.array_equal(pkg.binding.kd_build_host(xy), oracle.kd_build(xy))
 
 
+def test_kd_build_host_threaded_ranges_keep_the_reference_arrangement(pkg, oracle):
+    """From 2048 keypoints up the quarter-ranges are built on separate threads: tie-heavy, sorted,
+    constant and organ-pipe inputs must still give the single-threaded std::nth_element arrangement."""
+    rng = np.random.default_rng(5)
+    for n in (2048, 2049, 4097, 8000, 20000):
+        k = np.concatenate([np.arange(n // 2), np.arange(n - n // 2)[::-1]]).astype(np.float32)
+        for xy in (rng.integers(0, 8, (n, 2)), rng.integers(0, 1920, (n, 2)), rng.random((n, 2)),
+                   np.stack([np.arange(n), np.arange(n)[::-1]], 1), np.zeros((n, 2)), np.stack([k, k], 1)):
+            xy = np.ascontiguousarray(xy, np.float32)
+            assert np.array_equal(pkg.binding.kd_build_host(xy), oracle.kd_build(xy))
+
+
 def test_last_error_and_null_checks(pkg):
     lib = pkg.binding.load()
     assert lib.slamgpu_create(0, None) == pkg.binding.ERR_INVALID

@@ -67,6 +67,7 @@ SCENES = [
     (20000, 8000, 3, "HD1080", 20.0, 64.0, 0),     # BASELINE C3 frame size
     (3000, 1, 5, "KITTI", 2000.0, 300.0, 0),       # one keypoint, radius covering the image
     (500, 64, 6, "KITTI", 0.0, 64.0, 0),           # zero radius: only exact integer hits
+    (2000, 300, 13, "KITTI", 300.0, 80.0, 0),      # search box of ~19 cell rows: more rows than lanes in a group
 ]
 
 
@@ -255,8 +256,9 @@ def test_mapmatcher_mirror_reads_like_the_reference(ctx, oracle, pkg):
 
 
 def test_walk_and_warp_kernels_agree_on_tie_heavy_scene(oracle, pkg, monkeypatch):
-    """The default warp-per-point kernel (grid candidates + KD visit keys on ties) and the
-    thread-per-point KD-walk kernel (SLAMGPU_PROJ_WALK=1) must agree with each other and with the
+    """The default group-per-point kernel (flattened grid rows + KD visit keys on ties; 8 or 32 lanes,
+    several grid cell sizes), its predecessor (SLAMGPU_PROJ_V2=1) and the thread-per-point KD-walk
+    kernel (SLAMGPU_PROJ_WALK=1) must agree with each other and with the
     oracle where equal Hamming minima make the KD visit order decide (low-entropy descriptors)."""
     cam = dict(fx=300.0, fy=300.0, cx=160.0, cy=120.0, width=320, height=240)
     sc = pkg.synthetic.projection_scene(6000, 1500, 91, cam=cam)
@@ -268,9 +270,13 @@ def test_walk_and_warp_kernels_agree_on_tie_heavy_scene(oracle, pkg, monkeypatch
     ref = oracle.match_projection(sc.kp_xy, sc.kp_desc, perm, sc.kp_matched, sc.pos, sc.normal, sc.range,
                                   sc.obs_offset, sc.obs_desc, sc.skip, None, sc.pose, _oparams(oracle, p))
     results = []
-    for walk, lanes in (("0", "32"), ("0", "8"), ("1", "0")):
+    for walk, lanes, v2, cell in (("0", "32", "0", "32"), ("0", "8", "0", "32"), ("0", "8", "0", "16"),
+                                  ("0", "8", "0", "12"), ("0", "32", "0", "7"), ("0", "8", "1", "32"),
+                                  ("0", "32", "1", "32"), ("1", "0", "0", "32")):
         monkeypatch.setenv("SLAMGPU_PROJ_WALK", walk)
         monkeypatch.setenv("SLAMGPU_PROJ_LANES", lanes)
+        monkeypatch.setenv("SLAMGPU_PROJ_V2", v2)
+        monkeypatch.setenv("SLAMGPU_GRID_CELL", cell)
         with pkg.Context(0) as c:
             c.frame_upload(1, sc.kp_xy, sc.kp_desc, None, sc.kp_matched)
             c.points_upload(1, sc.pos, sc.normal, sc.range, sc.obs_offset, sc.obs_desc)

@@ -1,36 +1,94 @@
 #!/usr/bin/env python
-"""Kernel time of the projection match kernel variants (walk / 8 / 32 lanes per point) on C2 and C4 shapes."""
+"""A/B timing of the projection match kernel (K4) variants on a B200: CUDA-event time per launch through the
+library's profile hooks, plus a checksum of the results so that the variants can be compared for equality.
+
+  python tools/time_proj.py            # runs every variant in a subprocess (env switches are read at context creation)
+  python tools/time_proj.py --one NAME # one variant in this process (env already set)
+"""
+import hashlib
 import os
+import subprocess
 import sys
 
 import numpy as np
 
-sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
-import racing_slam_b200 as pkg  # noqa: E402
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
 
-syn = pkg.synthetic
-cam = syn.KITTI
-for name, walk, lanes in (("walk", "1", "0"), ("lanes32", "0", "32"), ("lanes8", "0", "8"), ("auto", "0", "0")):
-    os.environ["SLAMGPU_PROJ_WALK"] = walk
-    os.environ["SLAMGPU_PROJ_LANES"] = lanes
+VARIANTS = {
+    "v2_lanes8_cell32": {"SLAMGPU_PROJ_V2": "1", "SLAMGPU_PROJ_LANES": "8", "SLAMGPU_GRID_CELL": "32"},
+    "v3_lanes8_cell32": {"SLAMGPU_PROJ_LANES": "8", "SLAMGPU_GRID_CELL": "32"},
+    "v3_lanes8_cell16": {"SLAMGPU_PROJ_LANES": "8", "SLAMGPU_GRID_CELL": "16"},
+    "v3_lanes8_cell12": {"SLAMGPU_PROJ_LANES": "8", "SLAMGPU_GRID_CELL": "12"},
+    "v3_lanes32_cell16": {"SLAMGPU_PROJ_LANES": "32", "SLAMGPU_GRID_CELL": "16"},
+    "default": {},
+}
+
+
+def one(name):
+    import racing_slam_b200 as pkg
+    syn = pkg.synthetic
+    kitti, hd = syn.KITTI, syn.HD1080
+
+    def prm(cam, replace):
+        return pkg.ProjParams(cam["fx"], cam["fy"], cam["cx"], cam["cy"], cam["width"], cam["height"], 20.0, 64.0, 0.5,
+                              2.0, 1.25, replace)
+
     with pkg.Context(0) as ctx:
-        for label, npts, nkf in (("c2", 10000, 1), ("c4", 50000, 20), ("200k", 200000, 1)):
-            sc = syn.projection_scene(npts, 2000, 4)
-            rng = np.random.default_rng(4)
-            ids, nkps, poses = [], [], []
-            for k in range(nkf):
-                ctx.frame_upload(k, sc.kp_xy, sc.kp_desc, None, sc.kp_matched)
-                ids.append(k), nkps.append(2000)
-                poses.append(sc.pose if k == 0 else syn.pose_colmajor(syn.make_pose(rng)))
-            ctx.points_upload(0, sc.pos, sc.normal, sc.range, sc.obs_offset, sc.obs_desc)
-            prm = pkg.ProjParams(cam["fx"], cam["fy"], cam["cx"], cam["cy"], cam["width"], cam["height"], 20.0, 64.0,
-                                 0.5, 2.0, 1.25, 1 if nkf > 1 else 0)
+        def timed(fn, reps=30):
             for _ in range(3):
-                ctx.match_projection_batch(ids, nkps, 0, np.stack(poses), prm)
+                r = fn()
             ctx.profile_enable(True)
             ctx.profile_read(1)
-            for _ in range(10):
-                res = ctx.match_projection_batch(ids, nkps, 0, np.stack(poses), prm)
+            for _ in range(reps):
+                r = fn()
             ms, n = ctx.profile_read(1)
             ctx.profile_enable(False)
-            print(f"{name:8s} {label:5s} kernel_us {ms / n * 1e3:9.1f}  matches {sum(int((r[0] >= 0).sum()) for r in res)}")
+            return ms / max(n, 1) * 1e3, r
+
+        def digest(arrs):
+            h = hashlib.sha1()
+            for a in arrs:
+                h.update(np.ascontiguousarray(a).tobytes())
+            return h.hexdigest()[:10]
+
+        sc = syn.projection_scene(10000, 2000, 2)
+        ctx.frame_upload(0, sc.kp_xy, sc.kp_desc, None, sc.kp_matched)
+        ctx.points_upload(0, sc.pos, sc.normal, sc.range, sc.obs_offset, sc.obs_desc)
+        us, r = timed(lambda: ctx.match_projection(0, 0, 2000, sc.pose, prm(kitti, 0), sc.skip, None))
+        print(f"{name:20s} c2    kernel_us {us:9.1f}  matches {int((r[0] >= 0).sum())}  sha {digest(r)}")
+
+        sc4 = syn.projection_scene(50000, 2000, 4)
+        rng = np.random.default_rng(4)
+        ids, poses = [], []
+        for k in range(20):
+            xy = syn.keypoints_integer(2000, kitti["width"], kitti["height"], 700 + k)
+            ctx.frame_upload(100 + k, xy, sc4.kp_desc[rng.permutation(2000)], None, None)
+            ids.append(100 + k)
+            poses.append(syn.pose_colmajor(syn.make_pose(rng)))
+        ctx.points_upload(1, sc4.pos, sc4.normal, sc4.range, sc4.obs_offset, sc4.obs_desc)
+        poses = np.stack(poses)
+        us, r = timed(lambda: ctx.match_projection_batch(ids, [2000] * 20, 1, poses, prm(kitti, 1)), 10)
+        print(f"{name:20s} c4    kernel_us {us:9.1f}  matches {sum(int((a >= 0).sum()) for a, _ in r)}  "
+              f"sha {digest([x for pr in r for x in pr])}")
+
+        sc3 = syn.projection_scene(200000, 8000, 3, cam=hd)
+        ctx.frame_upload(2, sc3.kp_xy, sc3.kp_desc, None, sc3.kp_matched)
+        ctx.points_upload(2, sc3.pos, sc3.normal, sc3.range, sc3.obs_offset, sc3.obs_desc)
+        us, r = timed(lambda: ctx.match_projection(2, 2, 8000, sc3.pose, prm(hd, 0), sc3.skip, None), 10)
+        print(f"{name:20s} 200k  kernel_us {us:9.1f}  matches {int((r[0] >= 0).sum())}  sha {digest(r)}")
+
+
+if __name__ == "__main__":
+    if len(sys.argv) > 2 and sys.argv[1] == "--one":
+        one(sys.argv[2])
+    else:
+        print("# tools/time_proj.py on B200: proj match kernel, CUDA-event time per launch; c2 = 10k points x 1 frame "
+              "(KITTI, 2000 kp), c4 = 50k points x 20 key frames, 200k = 200k points x 1 frame (1080p, 8000 kp)")
+        for name, env in VARIANTS.items():
+            e = dict(os.environ)
+            for k in ("SLAMGPU_PROJ_V2", "SLAMGPU_PROJ_LANES", "SLAMGPU_GRID_CELL", "SLAMGPU_PROJ_WALK", "SLAMGPU_PROJ_COOP"):
+                e.pop(k, None)
+            e.update(env)
+            sys.stdout.flush()
+            subprocess.run([sys.executable, os.path.abspath(__file__), "--one", name], env=e, check=False)
