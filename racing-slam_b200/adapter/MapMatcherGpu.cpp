@@ -73,16 +73,14 @@ std::vector<MapPointMatch> MapMatcherGpu::match_for_fuse(const Frame& frame, con
     return project(frame, points, nullptr, true);               // nullptr entries are kept: :119-121
 }
 
-std::vector<MapPointMatch> MapMatcherGpu::project(const Frame& frame, const std::vector<MapPoint*>& visit,
-                                                  KeyFrame* required_observer, bool replace) const
+// Frame state: keypoints, descriptors, is_matched(size_t) (src/Frame.cpp:143-146) -> resident frame slot.
+int MapMatcherGpu::upload_frame(const Frame& frame) const
 {
     const auto& features = frame.features();
     const int nkp = static_cast<int>(features.keypoints.size());
     if (nkp == 0) {
-        return {};
+        return 0;
     }
-
-    // ---- frame state: keypoints, descriptors, is_matched(size_t) (src/Frame.cpp:143-146) ----
     std::vector<float> xy(2 * static_cast<size_t>(nkp));
     std::vector<uint8_t> matched(static_cast<size_t>(nkp));
     for (int i = 0; i < nkp; i++) {
@@ -97,15 +95,19 @@ std::vector<MapPointMatch> MapMatcherGpu::project(const Frame& frame, const std:
     // (Frame::m_kd_tree is private, src/Frame.h:69)
     check(slamgpu_frame_upload(m_ctx, FRAME_SLOT, nkp, xy.data(), desc.data(), nullptr, matched.data()),
           "slamgpu_frame_upload");
+    return nkp;
+}
 
-    // ---- point state: unique points in first-visit order, observations in the host's iteration order ----
+// Point state: unique points in first-visit order, observations in the host's iteration order -> resident set.
+void MapMatcherGpu::upload_points(const std::vector<MapPoint*>& visit, std::vector<MapPoint*>& uniq,
+                                  std::vector<int32_t>& order) const
+{
     std::unordered_map<const MapPoint*, int> slot;
-    std::vector<MapPoint*> uniq;
-    std::vector<int32_t> order(visit.size());
+    uniq.clear();
+    order.assign(visit.size(), -1);
     for (size_t v = 0; v < visit.size(); v++) {
         if (visit[v] == nullptr) {
-            order[v] = -1;
-            continue;
+            continue;                                           // match_for_fuse nullptr entry
         }
         auto it = slot.find(visit[v]);
         if (it == slot.end()) {
@@ -117,7 +119,7 @@ std::vector<MapPointMatch> MapMatcherGpu::project(const Frame& frame, const std:
     const int n = static_cast<int>(uniq.size());
     std::vector<float> pos(3 * static_cast<size_t>(n));
     std::vector<int32_t> obs_offset(static_cast<size_t>(n) + 1, 0);
-    std::vector<uint8_t> obs_desc, skip(static_cast<size_t>(n));
+    std::vector<uint8_t> obs_desc;
     std::vector<float> obs_center;
     std::unordered_map<const KeyFrame*, Eigen::Vector3f> centers;
     for (int i = 0; i < n; i++) {
@@ -125,9 +127,7 @@ std::vector<MapPointMatch> MapMatcherGpu::project(const Frame& frame, const std:
         pos[3 * i] = p.position().x();
         pos[3 * i + 1] = p.position().y();
         pos[3 * i + 2] = p.position().z();
-        // P0 is_matched(point) (src/MapMatcher.cpp:53) and P9 !is_observed_by(kf) (:169)
-        skip[i] = (frame.is_matched(p) || (required_observer != nullptr && !p.is_observed_by(required_observer))) ? 1 : 0;
-        for (const auto& [obs_keyframe, obs_index] : p.observations()) {        // :86, same iteration order
+        for (const auto& [obs_keyframe, obs_index] : p.observations()) {        // src/MapMatcher.cpp:86, same iteration order
             const cv::Mat d = obs_keyframe->descriptor(obs_index);
             const uint8_t* dp = d.ptr<uint8_t>(0);
             obs_desc.insert(obs_desc.end(), dp, dp + 32);
@@ -146,7 +146,10 @@ std::vector<MapPointMatch> MapMatcherGpu::project(const Frame& frame, const std:
     check(slamgpu_points_upload(m_ctx, POINT_SLOT, n, pos.data(), nullptr, nullptr, obs_offset.data(), obs_desc.data(),
                                 obs_center.data()),
           "slamgpu_points_upload");
+}
 
+slamgpu_proj_params MapMatcherGpu::params(bool replace) const
+{
     slamgpu_proj_params prm;
     const Eigen::Matrix3f& K = m_camera.get_intrinsic_matrix();
     prm.fx = K(0, 0);
@@ -161,7 +164,26 @@ std::vector<MapPointMatch> MapMatcherGpu::project(const Frame& frame, const std:
     prm.nearer = max_nearer_ratio;
     prm.further = max_further_ratio;
     prm.replace = replace ? 1 : 0;
+    return prm;
+}
 
+std::vector<MapPointMatch> MapMatcherGpu::project(const Frame& frame, const std::vector<MapPoint*>& visit,
+                                                  KeyFrame* required_observer, bool replace) const
+{
+    const int nkp = upload_frame(frame);
+    if (nkp == 0) {
+        return {};
+    }
+    std::vector<MapPoint*> uniq;
+    std::vector<int32_t> order;
+    upload_points(visit, uniq, order);
+    std::vector<uint8_t> skip(uniq.size());
+    for (size_t i = 0; i < uniq.size(); i++) {
+        const MapPoint& p = *uniq[i];
+        // P0 is_matched(point) (src/MapMatcher.cpp:53) and P9 !is_observed_by(kf) (:169)
+        skip[i] = (frame.is_matched(p) || (required_observer != nullptr && !p.is_observed_by(required_observer))) ? 1 : 0;
+    }
+    const slamgpu_proj_params prm = params(replace);
     std::vector<int32_t> out_point(static_cast<size_t>(nkp)), out_dist(static_cast<size_t>(nkp));
     const Eigen::Matrix4f& pose = frame.pose();                 // column-major, as the ABI expects
     check(slamgpu_match_projection(m_ctx, FRAME_SLOT, POINT_SLOT, pose.data(), &prm, skip.data(), order.data(),
@@ -175,6 +197,55 @@ std::vector<MapPointMatch> MapMatcherGpu::project(const Frame& frame, const std:
         }
     }
     return matches;
+}
+
+std::pair<std::vector<MapPointMatch>, std::vector<MapPointMatch>>
+MapMatcherGpu::track(Frame& frame, Map& map, KeyFrame& last_key_frame) const
+{
+    std::pair<std::vector<MapPointMatch>, std::vector<MapPointMatch>> result;
+    const int nkp = upload_frame(frame);
+    if (nkp == 0) {
+        return result;
+    }
+    std::vector<MapPoint*> visit, uniq;
+    for (auto& point : map) {                                   // map order, src/MapMatcher.cpp:168
+        visit.push_back(&point);
+    }
+    std::vector<int32_t> order;
+    upload_points(visit, uniq, order);                          // a Map holds every point once: uniq == visit
+    std::vector<int32_t> matched_points, kf_points;
+    for (size_t i = 0; i < uniq.size(); i++) {
+        if (frame.is_matched(*uniq[i])) {
+            matched_points.push_back(static_cast<int32_t>(i));  // :53
+        }
+        if (uniq[i]->is_observed_by(&last_key_frame)) {
+            kf_points.push_back(static_cast<int32_t>(i));       // :169, ascending = map order
+        }
+    }
+    const slamgpu_proj_params prm = params(false);
+    const size_t n = static_cast<size_t>(nkp);
+    std::vector<int32_t> kf_point(n), kf_dist(n), map_point(n), map_dist(n);
+    const Eigen::Matrix4f& pose = frame.pose();
+    check(slamgpu_track_match(m_ctx, FRAME_SLOT, POINT_SLOT, pose.data(), &prm, matched_points.data(),
+                              static_cast<int>(matched_points.size()), kf_points.data(),
+                              static_cast<int>(kf_points.size()), kf_point.data(), kf_dist.data(), map_point.data(),
+                              map_dist.data()),
+          "slamgpu_track_match");
+    for (int i = 0; i < nkp; i++) {
+        if (kf_point[i] >= 0) {
+            result.first.push_back(MapPointMatch{*uniq[static_cast<size_t>(kf_point[i])], static_cast<size_t>(i)});
+        }
+        if (map_point[i] >= 0) {
+            result.second.push_back(MapPointMatch{*uniq[static_cast<size_t>(map_point[i])], static_cast<size_t>(i)});
+        }
+    }
+    for (const auto& match : result.first) {                    // src/Tracker.cpp:235-237
+        frame.add_map_match(match);
+    }
+    for (const auto& match : result.second) {                   // :244-246
+        frame.add_map_match(match);
+    }
+    return result;
 }
 
 std::vector<MapPointMatch> MapMatcherGpu::match_descriptors(const Frame& frame, const KeyFrame& key_frame) const

@@ -7,6 +7,8 @@
 // (include/slamgpu.h); this class flattens the object graph to POD arrays and maps indices back.
 #pragma once
 
+#include <cstdint>
+#include <utility>
 #include <vector>
 
 #include "features/FeatureExtractor.h"   // slam::MapPointMatch, slam::FeatureMatch, slam::ExtractedFeatures
@@ -43,6 +45,13 @@ class MapMatcherGpu {
     std::vector<FeatureMatch> match_features(const ExtractedFeatures& prev_features, const ExtractedFeatures& features,
                                              float max_distance) const;
 
+    /** Tracker::match_with_last_key_frame followed by Tracker::match_with_map (src/Tracker.cpp:232-248) as ONE
+     *  chained device call (slamgpu_track_match): both match lists are applied to `frame` with add_map_match
+     *  exactly as the two loops do.  Returns {key-frame matches, map matches}; the Tracker replaces its two
+     *  calls by this one. */
+    std::pair<std::vector<MapPointMatch>, std::vector<MapPointMatch>> track(Frame& frame, Map& map,
+                                                                            KeyFrame& last_key_frame) const;
+
     // Matching constants of src/MapMatcher.cpp:12-18, runtime-settable (defaults = the reference's)
     float search_radius = 20.0F;
     float min_viewing_angle_cosine = 0.5F;
@@ -53,6 +62,10 @@ class MapMatcherGpu {
   private:
     std::vector<MapPointMatch> project(const Frame& frame, const std::vector<MapPoint*>& visit,
                                        KeyFrame* required_observer, bool replace) const;
+    int upload_frame(const Frame& frame) const;
+    void upload_points(const std::vector<MapPoint*>& visit, std::vector<MapPoint*>& uniq,
+                       std::vector<int32_t>& order) const;
+    slamgpu_proj_params params(bool replace) const;
 
     const Camera& m_camera;
     float m_max_descriptor_distance;

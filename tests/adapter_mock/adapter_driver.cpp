@@ -128,6 +128,11 @@ int main(int argc, char** argv)
         auto fm = matcher.match_features(kfs[0]->features(), frame.features(), 64.0F);
         out << "match_features " << fm.size() << "\n";
         for (const auto& m : fm) out << m.train_index << " " << m.query_index << "\n";
+        // last: it applies its matches to the frame (Tracker::match_with_last_key_frame + match_with_map)
+        auto tr = matcher.track(frame, map, *kfs[required]);
+        dump("track_key_frame", tr.first);
+        dump("track_map", tr.second);
+        out << "frame_matches_after_track " << frame.num_map_matches() << "\n";
     } catch (const std::exception& e) {
         std::cerr << e.what() << "\n";
         return 1;

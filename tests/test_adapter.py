@@ -100,6 +100,10 @@ def parse_output(path):
     while i < len(lines) and lines[i].strip():
         name, n = lines[i].split()
         n = int(n)
+        if name == "frame_matches_after_track":
+            res[name] = n
+            i += 1
+            continue
         rows = [tuple(int(x) for x in lines[i + 1 + r].split()) for r in range(n)]
         res[name] = rows
         i += 1 + n
@@ -173,3 +177,13 @@ def test_adapter_end_to_end_vs_oracle(pkg, oracle, tmp_path):
     assert got["match_descriptors"] == [(kfm[int(t)][1], int(q)) for q, t in zip(oq, ot)]
     o_t, o_q = oracle.match_features(kfs[0]["desc"], fr["desc"], 64.0)
     assert got["match_features"] == list(zip(o_t.tolist(), o_q.tolist()))
+
+    # MapMatcherGpu::track = match_key_frame, add_map_match loop, match_map, add_map_match loop
+    # (src/Tracker.cpp:232-248): the first stage equals the stand-alone call, the second sees its matches
+    assert got["track_key_frame"] == got["match_key_frame"]
+    skip_after = skip_m.copy()
+    for pi, kp in got["track_key_frame"]:
+        matched[kp] = 1
+        skip_after[pi] = 1
+    assert got["track_map"] == run(skip_after, None, 0) and len(got["track_map"]) > 10
+    assert got["frame_matches_after_track"] == len(w["frame_matches"]) + len(got["track_key_frame"]) + len(got["track_map"])
