@@ -230,14 +230,71 @@ SLAMGPU_API int slamgpu_match_projection_batch(slamgpu_ctx* ctx, const int* fram
                                    int32_t* out_dist);
 
 /* ------------------------------------------------------------------------------------------
+ * Bag of words: the step before the brute-force verification in LoopDetector --
+ * bow_of (src/LoopDetector.cpp:85-92) -> DBoW2 TemplatedVocabulary::transform
+ * (thirdparty/DBoW2/DBoW2/TemplatedVocabulary.h:1064-1120,1218-1257, FORB::distance FORB.cpp:81-101)
+ * and vocabulary->score (src/LoopDetector.cpp:369) -> L1Scoring::score (ScoringObject.cpp:23-68).
+ * ---------------------------------------------------------------------------------------- */
+
+/* DBoW2 enums, same values: WeightingType (BowVector.h:36-42) and the norm the scoring object asks for
+ * (ScoringObject mustNormalize: L1_NORM scoring -> SLAMGPU_BOW_NORM_L1). */
+#define SLAMGPU_BOW_TF_IDF 0
+#define SLAMGPU_BOW_TF 1
+#define SLAMGPU_BOW_IDF 2
+#define SLAMGPU_BOW_BINARY 3
+#define SLAMGPU_BOW_NORM_NONE 0
+#define SLAMGPU_BOW_NORM_L1 1
+#define SLAMGPU_BOW_NORM_L2 2
+#define SLAMGPU_BOW_MAX_FEATURES 16384 /* features per image in slamgpu_vocab_bow */
+
+/* Vocabulary tree kept resident (TemplatedVocabulary::m_nodes): node 0 is the root;
+ *   child_offset [n_nodes + 1], child_ids [child_offset[n_nodes]]  children of node i in DBoW2's own order
+ *                (Node::children; transform() takes the FIRST child with the strictly smallest distance)
+ *   desc [n_nodes x 32]   Node::descriptor (the root's is ignored)
+ *   weight [n_nodes]      Node::weight (the word weight, e.g. idf; read at the leaves)
+ *   word_id [n_nodes]     Node::word_id at the leaves, ignored for inner nodes */
+SLAMGPU_API int slamgpu_vocab_upload(slamgpu_ctx* ctx, int vocab_id, int n_nodes, const int32_t* child_offset,
+                         const int32_t* child_ids, const uint8_t* desc, const double* weight, const int32_t* word_id);
+SLAMGPU_API int slamgpu_vocab_release(slamgpu_ctx* ctx, int vocab_id);
+
+/* transform(feature, word_id, weight) for n descriptors (TemplatedVocabulary.h:1218-1257): out_word [n],
+ * out_weight [n] (may be NULL). */
+SLAMGPU_API int slamgpu_vocab_transform(slamgpu_ctx* ctx, int vocab_id, const uint8_t* desc, int n, int32_t* out_word,
+                            double* out_weight);
+/* Device-pointer form: enqueues on the context's stream, no synchronisation. */
+SLAMGPU_API int slamgpu_vocab_transform_dev(slamgpu_ctx* ctx, int vocab_id, const uint8_t* d_desc, int n,
+                                int32_t* d_out_word, double* d_out_weight);
+
+/* transform(features, bow) for a batch of images (TemplatedVocabulary.h:1064-1120, BowVector.cpp:33-84):
+ * image i owns descriptors [image_offset[i], image_offset[i+1]) (at most SLAMGPU_BOW_MAX_FEATURES each).
+ * Its bag-of-words vector comes back as out_ids / out_vals [out_offset[i], out_offset[i+1]) ascending by
+ * word id, exactly the std::map DBoW2 builds; out_ids / out_vals need image_offset[n_images] entries.
+ * Words are found, sorted and counted on the device; the per-word value fold and the normalisation are
+ * double-precision sums whose order DBoW2 fixes (feature order, ascending word id) and are done in that
+ * order on the host from the counts. */
+SLAMGPU_API int slamgpu_vocab_bow(slamgpu_ctx* ctx, int vocab_id, const uint8_t* desc, const int32_t* image_offset,
+                      int n_images, int weighting, int norm, int32_t* out_ids, double* out_vals,
+                      int32_t* out_offset);
+
+/* L1Scoring::score(query, db[i]) for every vector of a database (LoopDetector::Impl::score_candidates,
+ * src/LoopDetector.cpp:346-373): vectors are (ids ascending, values); the database is concatenated with
+ * db_offset [n_db + 1].  out_score [n_db].  The terms of a score are summed in ascending word order as
+ * DBoW2 does, so the doubles are bit-identical. */
+SLAMGPU_API int slamgpu_vocab_score_l1(slamgpu_ctx* ctx, const int32_t* q_ids, const double* q_vals, int nq,
+                           const int32_t* db_ids, const double* db_vals, const int32_t* db_offset, int n_db,
+                           double* out_score);
+
+/* ------------------------------------------------------------------------------------------
  * Diagnostics
  * ---------------------------------------------------------------------------------------- */
 /* Per-kernel device timing for roofline reports: while enabled, every launch of the two dominant
  * kernels is bracketed by a CUDA-event pair on the context's stream.  slamgpu_profile_read
  * synchronises, returns the summed duration and launch count since the last read, and resets.
- *   kernel  SLAMGPU_KERNEL_BF_SCAN (K1 brute-force scan) or SLAMGPU_KERNEL_PROJ_MATCH (K4). */
+ *   kernel  SLAMGPU_KERNEL_BF_SCAN (K1 brute-force scan), SLAMGPU_KERNEL_PROJ_MATCH (K4) or
+ *           SLAMGPU_KERNEL_VOC_TRANSFORM (vocabulary descent). */
 #define SLAMGPU_KERNEL_BF_SCAN 0
 #define SLAMGPU_KERNEL_PROJ_MATCH 1
+#define SLAMGPU_KERNEL_VOC_TRANSFORM 2
 SLAMGPU_API int slamgpu_profile_enable(slamgpu_ctx* ctx, int on);
 SLAMGPU_API int slamgpu_profile_read(slamgpu_ctx* ctx, int kernel, double* total_ms, int64_t* launches);
 /* POPC-pipe microbenchmark ("confirm with a POPC microbenchmark on the box"):

@@ -69,6 +69,12 @@ def lib():
         L.orc_match_projection.argtypes = [C.c_int, f32p, u8p, u32p, u8p, C.c_int, f32p, f32p, f32p, i32p, u8p, u8p,
                                            i32p, C.c_int, f32p, C.POINTER(ProjParams), i32p, i32p, f32p, i32p, i32p,
                                            C.POINTER(C.c_int64)]
+        f64p = C.POINTER(C.c_double)
+        L.orc_voc_transform_each.argtypes = [i32p, i32p, u8p, f64p, i32p, u8p, C.c_int, i32p, f64p]
+        L.orc_voc_bow.argtypes = [i32p, f64p, C.c_int, C.c_int, C.c_int, i32p, f64p]
+        L.orc_voc_bow.restype = C.c_int
+        L.orc_voc_score_l1.argtypes = [i32p, f64p, C.c_int, i32p, f64p, C.c_int]
+        L.orc_voc_score_l1.restype = C.c_double
         _LIB = L
     return _LIB
 
@@ -250,3 +256,130 @@ def match_projection(kp_xy, kp_desc, kd_perm, kp_matched, pos, normal, rng, obs_
                                _ptr(uv, C.c_float), _ptr(kp, C.c_int32), _ptr(d, C.c_int32),
                                stats if want_stats else None)
     return ProjResult(out_point, out_dist, uv, kp, d, int(stats[0]), int(stats[1]))
+
+
+# ---------------------------------------------------------------------------------------------
+# Bag of words: DBoW2 transform / L1 score, restated in slam_oracle.cpp and pinned
+# against the reference's vendored DBoW2 compiled into oracle/_ref/libref_dbow2.so.
+# ---------------------------------------------------------------------------------------------
+TF_IDF, TF, IDF, BINARY = 0, 1, 2, 3          # DBoW2::WeightingType (BowVector.h:36-42)
+NORM_NONE, NORM_L1, NORM_L2 = 0, 1, 2
+
+
+@dataclass
+class Vocabulary:
+    """A DBoW2 vocabulary tree as plain arrays (children in DBoW2's own scan order; node 0 = root)."""
+    child_offset: np.ndarray    # [n_nodes + 1] i32
+    child_ids: np.ndarray       # [n_nodes - 1] i32
+    desc: np.ndarray            # [n_nodes, 32] u8
+    weight: np.ndarray          # [n_nodes] f64  word weight (idf) at the leaves
+    word_id: np.ndarray         # [n_nodes] i32  -1 for inner nodes
+    k: int = 0
+    L: int = 0
+
+
+def voc_transform_each(voc: Vocabulary, desc):
+    """-> (word [n] i32, weight [n] f64): TemplatedVocabulary::transform(feature, id, weight)."""
+    desc = _u8(desc)
+    n = len(desc)
+    word = np.zeros(n, np.int32)
+    w = np.zeros(n, np.float64)
+    lib().orc_voc_transform_each(_ptr(voc.child_offset, C.c_int32), _ptr(voc.child_ids, C.c_int32),
+                                 _ptr(voc.desc, C.c_uint8), _ptr(voc.weight, C.c_double),
+                                 _ptr(voc.word_id, C.c_int32), _ptr(desc, C.c_uint8), n, _ptr(word, C.c_int32),
+                                 _ptr(w, C.c_double))
+    return word, w
+
+
+def voc_bow(word, weight, weighting=TF_IDF, norm=NORM_L1):
+    """-> (ids [m] i32 ascending, values [m] f64): TemplatedVocabulary::transform(features, bow)."""
+    word = np.ascontiguousarray(word, np.int32)
+    weight = np.ascontiguousarray(weight, np.float64)
+    ids = np.zeros(max(len(word), 1), np.int32)
+    vals = np.zeros(max(len(word), 1), np.float64)
+    m = lib().orc_voc_bow(_ptr(word, C.c_int32), _ptr(weight, C.c_double), len(word), weighting, norm,
+                          _ptr(ids, C.c_int32), _ptr(vals, C.c_double))
+    return ids[:m].copy(), vals[:m].copy()
+
+
+def voc_score_l1(ids_a, vals_a, ids_b, vals_b) -> float:
+    ids_a, ids_b = np.ascontiguousarray(ids_a, np.int32), np.ascontiguousarray(ids_b, np.int32)
+    vals_a, vals_b = np.ascontiguousarray(vals_a, np.float64), np.ascontiguousarray(vals_b, np.float64)
+    return float(lib().orc_voc_score_l1(_ptr(ids_a, C.c_int32), _ptr(vals_a, C.c_double), len(ids_a),
+                                        _ptr(ids_b, C.c_int32), _ptr(vals_b, C.c_double), len(ids_b)))
+
+
+_REF_DBOW = None
+
+
+def ref_dbow2():
+    """The reference's own DBoW2 (oracle/_ref/libref_dbow2.so) or None when not built."""
+    global _REF_DBOW
+    if _REF_DBOW is None:
+        path = os.path.join(_HERE, "_ref", "libref_dbow2.so")
+        if not os.path.exists(path):
+            return None
+        R = C.CDLL(path)
+        u8p, i32p, f64p = C.POINTER(C.c_uint8), C.POINTER(C.c_int32), C.POINTER(C.c_double)
+        R.ref_voc_create.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, u8p, i32p, C.c_int]
+        R.ref_voc_create.restype = C.c_void_p
+        R.ref_voc_destroy.argtypes = [C.c_void_p]
+        R.ref_voc_num_nodes.argtypes = [C.c_void_p]
+        R.ref_voc_num_words.argtypes = [C.c_void_p]
+        R.ref_voc_export.argtypes = [C.c_void_p, i32p, i32p, u8p, f64p, i32p]
+        R.ref_voc_transform_each.argtypes = [C.c_void_p, u8p, C.c_int, i32p, f64p]
+        R.ref_voc_transform_bow.argtypes = [C.c_void_p, u8p, C.c_int, i32p, f64p, C.c_int]
+        R.ref_voc_transform_bow.restype = C.c_int
+        R.ref_voc_score.argtypes = [C.c_void_p, i32p, f64p, C.c_int, i32p, f64p, C.c_int]
+        R.ref_voc_score.restype = C.c_double
+        _REF_DBOW = R
+    return _REF_DBOW
+
+
+class RefVocabulary:
+    """DBoW2's own TemplatedVocabulary<FORB>: create() from training images, then its transform / score."""
+
+    def __init__(self, k, L, training_desc, image_offset, weighting=TF_IDF, scoring=0):
+        self.R = ref_dbow2()
+        if self.R is None:
+            raise RuntimeError("oracle/_ref/libref_dbow2.so is not built (needs /root/reference)")
+        d = _u8(training_desc)
+        off = np.ascontiguousarray(image_offset, np.int32)
+        self.k, self.L = k, L
+        self.h = self.R.ref_voc_create(k, L, weighting, scoring, _ptr(d, C.c_uint8), _ptr(off, C.c_int32), len(off) - 1)
+
+    def export(self) -> Vocabulary:
+        n = self.R.ref_voc_num_nodes(self.h)
+        v = Vocabulary(np.zeros(n + 1, np.int32), np.zeros(max(n - 1, 1), np.int32), np.zeros((n, 32), np.uint8),
+                       np.zeros(n, np.float64), np.zeros(n, np.int32), self.k, self.L)
+        self.R.ref_voc_export(self.h, _ptr(v.child_offset, C.c_int32), _ptr(v.child_ids, C.c_int32),
+                              _ptr(v.desc, C.c_uint8), _ptr(v.weight, C.c_double), _ptr(v.word_id, C.c_int32))
+        v.child_ids = v.child_ids[:n - 1].copy()
+        return v
+
+    def transform_each(self, desc):
+        desc = _u8(desc)
+        word = np.zeros(len(desc), np.int32)
+        w = np.zeros(len(desc), np.float64)
+        self.R.ref_voc_transform_each(self.h, _ptr(desc, C.c_uint8), len(desc), _ptr(word, C.c_int32),
+                                      _ptr(w, C.c_double))
+        return word, w
+
+    def transform_bow(self, desc):
+        desc = _u8(desc)
+        ids = np.zeros(max(len(desc), 1), np.int32)
+        vals = np.zeros(max(len(desc), 1), np.float64)
+        m = self.R.ref_voc_transform_bow(self.h, _ptr(desc, C.c_uint8), len(desc), _ptr(ids, C.c_int32),
+                                         _ptr(vals, C.c_double), len(ids))
+        return ids[:m].copy(), vals[:m].copy()
+
+    def score(self, a, b) -> float:
+        ia, va = np.ascontiguousarray(a[0], np.int32), np.ascontiguousarray(a[1], np.float64)
+        ib, vb = np.ascontiguousarray(b[0], np.int32), np.ascontiguousarray(b[1], np.float64)
+        return float(self.R.ref_voc_score(self.h, _ptr(ia, C.c_int32), _ptr(va, C.c_double), len(ia),
+                                          _ptr(ib, C.c_int32), _ptr(vb, C.c_double), len(ib)))
+
+    def close(self):
+        if self.h:
+            self.R.ref_voc_destroy(self.h)
+            self.h = None

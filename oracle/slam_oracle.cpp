@@ -428,3 +428,108 @@ ORC_API void orc_match_projection(int nkp, const float* kp_xy, const uint8_t* kp
 }
 
 ORC_API int orc_abi_version(void) { return 1; }
+
+// =============================================================================================
+// Bag-of-words transform and scoring: what LoopDetector does before the brute-force
+// verification -- bow_of (src/LoopDetector.cpp:85-92) -> DBoW2 TemplatedVocabulary::transform, and
+// vocabulary->score (:369) -> L1Scoring::score.  DBoW2 is vendored in the reference
+// (thirdparty/DBoW2); this restatement is PINNED against that code compiled unmodified into
+// oracle/_ref/libref_dbow2.so (oracle/ref_dbow2_wrap.cpp), fixtures under tests/golden/voc_*.npz.
+//
+// The vocabulary is a tree given as arrays: child_offset [n_nodes + 1] / child_ids in DBoW2's own
+// child order, desc [n_nodes x 32], weight [n_nodes] (word weight, e.g. idf), word_id [n_nodes]
+// (-1 for inner nodes).  Node 0 is the root.
+// =============================================================================================
+
+// thirdparty/DBoW2/DBoW2/TemplatedVocabulary.h:1218-1257: descend from the root, at each level take the
+// FIRST child with the strictly smallest FORB::distance (FORB.cpp:81-101 = 256-bit Hamming).
+ORC_API void orc_voc_transform_each(const int32_t* child_offset, const int32_t* child_ids, const uint8_t* node_desc,
+                                    const double* weight, const int32_t* word_id, const uint8_t* desc, int n,
+                                    int32_t* out_word, double* out_weight)
+{
+#pragma omp parallel for schedule(static)
+    for (int i = 0; i < n; i++) {
+        const uint8_t* f = desc + 32 * (size_t)i;
+        int node = 0;
+        do {
+            const int b = child_offset[node], e = child_offset[node + 1];
+            int best = child_ids[b];
+            int best_d = hamming256(f, node_desc + 32 * (size_t)best);
+            for (int c = b + 1; c < e; c++) {
+                const int id = child_ids[c];
+                const int d = hamming256(f, node_desc + 32 * (size_t)id);
+                if (d < best_d) {
+                    best_d = d;
+                    best = id;
+                }
+            }
+            node = best;
+        } while (child_offset[node + 1] > child_offset[node]);
+        out_word[i] = word_id[node];
+        out_weight[i] = weight[node];
+    }
+}
+
+// TemplatedVocabulary.h:1064-1120 + BowVector.cpp:33-84.  weighting: 0 TF_IDF, 1 TF, 2 IDF, 3 BINARY;
+// norm: 0 = none (scoring without normalisation), 1 = L1, 2 = L2 (ScoringObject mustNormalize).
+// Words arrive per feature in feature order; values accumulate in that order; the map is ascending by
+// word id; the norm is summed in ascending order.  Returns the number of entries.
+ORC_API int orc_voc_bow(const int32_t* word, const double* w, int n, int weighting, int norm, int32_t* out_ids,
+                        double* out_vals)
+{
+    std::vector<std::pair<int32_t, int>> order(n);        // (word, feature index): stable order by word
+    int m = 0;
+    for (int i = 0; i < n; i++)
+        if (w[i] > 0) order[m++] = {word[i], i};          // "not stopped"
+    order.resize(m);
+    std::stable_sort(order.begin(), order.end(), [](const auto& a, const auto& b) { return a.first < b.first; });
+    int cnt = 0;
+    for (int i = 0; i < m;) {
+        int j = i;
+        double v = w[order[i].second];                    // insert(id, w)
+        for (j = i + 1; j < m && order[j].first == order[i].first; j++)
+            if (weighting == 0 || weighting == 1) v += w[order[j].second];   // addWeight; addIfNotExist keeps the first
+        out_ids[cnt] = order[i].first;
+        out_vals[cnt] = v;
+        cnt++;
+        i = j;
+    }
+    const bool must = norm != 0;
+    if ((weighting == 0 || weighting == 1) && cnt > 0 && !must) {
+        const double nd = cnt;
+        for (int i = 0; i < cnt; i++) out_vals[i] /= nd;
+    }
+    if (must) {
+        double s = 0.0;
+        if (norm == 1) {
+            for (int i = 0; i < cnt; i++) s += std::fabs(out_vals[i]);
+        } else {
+            for (int i = 0; i < cnt; i++) s += out_vals[i] * out_vals[i];
+            s = std::sqrt(s);
+        }
+        if (s > 0.0)
+            for (int i = 0; i < cnt; i++) out_vals[i] /= s;
+    }
+    return cnt;
+}
+
+// ScoringObject.cpp:23-68 (L1Scoring::score): merge of two ascending bow vectors.
+ORC_API double orc_voc_score_l1(const int32_t* ids_a, const double* vals_a, int na, const int32_t* ids_b,
+                                const double* vals_b, int nb)
+{
+    int i = 0, j = 0;
+    double score = 0;
+    while (i < na && j < nb) {
+        if (ids_a[i] == ids_b[j]) {
+            const double vi = vals_a[i], wi = vals_b[j];
+            score += std::fabs(vi - wi) - std::fabs(vi) - std::fabs(wi);
+            i++;
+            j++;
+        } else if (ids_a[i] < ids_b[j]) {
+            i = (int)(std::lower_bound(ids_a + i, ids_a + na, ids_b[j]) - ids_a);
+        } else {
+            j = (int)(std::lower_bound(ids_b + j, ids_b + nb, ids_a[i]) - ids_b);
+        }
+    }
+    return -score / 2.0;
+}

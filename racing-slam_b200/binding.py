@@ -19,6 +19,10 @@ MAX_TRAIN = 1 << 22
 
 _u8p, _i32p, _u32p, _f32p = (C.POINTER(C.c_uint8), C.POINTER(C.c_int32), C.POINTER(C.c_uint32), C.POINTER(C.c_float))
 _i64p = C.POINTER(C.c_int64)
+_f64p = C.POINTER(C.c_double)
+BOW_TF_IDF, BOW_TF, BOW_IDF, BOW_BINARY = 0, 1, 2, 3          # DBoW2::WeightingType
+BOW_NORM_NONE, BOW_NORM_L1, BOW_NORM_L2 = 0, 1, 2
+BOW_MAX_FEATURES = 16384
 _ctx = C.c_void_p
 
 
@@ -79,6 +83,12 @@ SIGNATURES = {
                                       C.c_int, _i32p, _i32p, _i32p, _i32p]),
     "slamgpu_match_projection_batch": (C.c_int, [_ctx, C.POINTER(C.c_int), C.c_int, C.c_int, _f32p,
                                                  C.POINTER(ProjParams), _u8p, _i32p, C.c_int, _i32p, _i32p]),
+    "slamgpu_vocab_upload": (C.c_int, [_ctx, C.c_int, C.c_int, _i32p, _i32p, _u8p, _f64p, _i32p]),
+    "slamgpu_vocab_release": (C.c_int, [_ctx, C.c_int]),
+    "slamgpu_vocab_transform": (C.c_int, [_ctx, C.c_int, _u8p, C.c_int, _i32p, _f64p]),
+    "slamgpu_vocab_transform_dev": (C.c_int, [_ctx, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]),
+    "slamgpu_vocab_bow": (C.c_int, [_ctx, C.c_int, _u8p, _i32p, C.c_int, C.c_int, C.c_int, _i32p, _f64p, _i32p]),
+    "slamgpu_vocab_score_l1": (C.c_int, [_ctx, _i32p, _f64p, C.c_int, _i32p, _f64p, _i32p, C.c_int, _f64p]),
     "slamgpu_profile_enable": (C.c_int, [_ctx, C.c_int]),
     "slamgpu_profile_read": (C.c_int, [_ctx, C.c_int, C.POINTER(C.c_double), _i64p]),
     "slamgpu_bench_popc": (C.c_int, [_ctx, C.POINTER(C.c_double), C.POINTER(C.c_int), C.POINTER(C.c_double)]),
@@ -368,6 +378,66 @@ class Context:
             self._h, frame_id, set_id, _p(pose, C.c_float), C.byref(params), _p(mp, C.c_int32), len(mp),
             _p(kf, C.c_int32), len(kf), *[_p(o, C.c_int32) for o in outs]))
         return tuple(outs)
+
+    # ---- bag of words ----
+    def vocab_upload(self, vocab_id: int, child_offset, child_ids, desc, weight, word_id):
+        """DBoW2 vocabulary tree as arrays (TemplatedVocabulary::m_nodes; node 0 = root)."""
+        child_offset = np.ascontiguousarray(child_offset, np.int32)
+        child_ids = np.ascontiguousarray(child_ids, np.int32)
+        desc = _desc(desc)
+        weight = np.ascontiguousarray(weight, np.float64)
+        word_id = np.ascontiguousarray(word_id, np.int32)
+        n_nodes = len(child_offset) - 1
+        assert len(desc) == n_nodes and len(weight) == n_nodes and len(word_id) == n_nodes
+        self._check(self._lib.slamgpu_vocab_upload(self._h, vocab_id, n_nodes, _p(child_offset, C.c_int32),
+                                                   _p(child_ids, C.c_int32), _p(desc, C.c_uint8),
+                                                   _p(weight, C.c_double), _p(word_id, C.c_int32)))
+
+    def vocab_release(self, vocab_id: int):
+        self._check(self._lib.slamgpu_vocab_release(self._h, vocab_id))
+
+    def vocab_transform(self, vocab_id: int, desc):
+        """-> (word [n] i32, weight [n] f64): TemplatedVocabulary::transform(feature, id, weight)."""
+        desc = _desc(desc)
+        word = np.full(len(desc), -1, np.int32)
+        weight = np.zeros(len(desc), np.float64)
+        self._check(self._lib.slamgpu_vocab_transform(self._h, vocab_id, _p(desc, C.c_uint8), len(desc),
+                                                      _p(word, C.c_int32), _p(weight, C.c_double)))
+        return word, weight
+
+    def vocab_transform_dev(self, vocab_id: int, d_desc: int, n: int, d_word: int, d_weight: int = 0):
+        self._check(self._lib.slamgpu_vocab_transform_dev(self._h, vocab_id, d_desc, n, d_word, d_weight or None))
+
+    def vocab_bow(self, vocab_id: int, desc, image_offset=None, weighting=BOW_TF_IDF, norm=BOW_NORM_L1):
+        """transform(features, bow) for a batch of images -> list of (ids ascending, values) per image."""
+        desc = _desc(desc)
+        if image_offset is None:
+            image_offset = [0, len(desc)]
+        off = np.ascontiguousarray(image_offset, np.int32)
+        n_img = len(off) - 1
+        ids = np.zeros(max(len(desc), 1), np.int32)
+        vals = np.zeros(max(len(desc), 1), np.float64)
+        out_off = np.zeros(n_img + 1, np.int32)
+        self._check(self._lib.slamgpu_vocab_bow(self._h, vocab_id, _p(desc, C.c_uint8), _p(off, C.c_int32), n_img,
+                                                weighting, norm, _p(ids, C.c_int32), _p(vals, C.c_double),
+                                                _p(out_off, C.c_int32)))
+        return [(ids[out_off[i]:out_off[i + 1]].copy(), vals[out_off[i]:out_off[i + 1]].copy()) for i in range(n_img)]
+
+    def vocab_score_l1(self, query, database):
+        """L1Scoring::score(query, v) for every (ids, values) vector v of `database` -> scores [n_db] f64."""
+        q_ids = np.ascontiguousarray(query[0], np.int32)
+        q_vals = np.ascontiguousarray(query[1], np.float64)
+        off = np.zeros(len(database) + 1, np.int32)
+        for i, (a, _) in enumerate(database):
+            off[i + 1] = off[i] + len(a)
+        db_ids = np.concatenate([np.asarray(a, np.int32) for a, _ in database]) if len(database) else np.zeros(0, np.int32)
+        db_vals = np.concatenate([np.asarray(b, np.float64) for _, b in database]) if len(database) else np.zeros(0)
+        db_ids, db_vals = np.ascontiguousarray(db_ids, np.int32), np.ascontiguousarray(db_vals, np.float64)
+        out = np.zeros(len(database), np.float64)
+        self._check(self._lib.slamgpu_vocab_score_l1(self._h, _p(q_ids, C.c_int32), _p(q_vals, C.c_double), len(q_ids),
+                                                     _p(db_ids, C.c_int32), _p(db_vals, C.c_double),
+                                                     _p(off, C.c_int32), len(database), _p(out, C.c_double)))
+        return out
 
     def match_projection_batch(self, frame_ids, nkps, set_id: int, poses, params: ProjParams, skip=None, order=None):
         """Frozen-snapshot batch over key frames -> list of (out_point, out_dist) per frame."""

@@ -270,6 +270,7 @@ int slamgpu_destroy(slamgpu_ctx* ctx)
     cudaStreamSynchronize(ctx->stream);
     for (auto& kv : ctx->frames) free_frame(kv.second);
     for (auto& kv : ctx->point_sets) free_points(kv.second);
+    free_all_vocabs(ctx);
     if (ctx->d_ws.ptr) cudaFree(ctx->d_ws.ptr);
     if (ctx->d_io.ptr) cudaFree(ctx->d_io.ptr);
     if (ctx->d_exp.ptr) cudaFree(ctx->d_exp.ptr);
@@ -332,7 +333,7 @@ int slamgpu_profile_enable(slamgpu_ctx* ctx, int on)
 int slamgpu_profile_read(slamgpu_ctx* ctx, int kernel, double* total_ms, int64_t* launches)
 {
     SG_CTX(ctx);
-    SG_CHECK(kernel == SLAMGPU_KERNEL_BF_SCAN || kernel == SLAMGPU_KERNEL_PROJ_MATCH, "unknown kernel id");
+    SG_CHECK(kernel >= SLAMGPU_KERNEL_BF_SCAN && kernel <= SLAMGPU_KERNEL_VOC_TRANSFORM, "unknown kernel id");
     SG_CUDA(cudaStreamSynchronize(ctx->stream));
     double sum = 0.0;
     auto& v = ctx->prof_events[kernel];

@@ -79,6 +79,20 @@ struct PointSetDev {
     int64_t cap_obs = 0;          // so that slamgpu_points_append can grow the set in place
 };
 
+// Device-resident DBoW2 vocabulary, re-laid out by CHILD POSITION: position c of the child array is one
+// node, its descriptor sits at cdesc[c] (the children of a node are contiguous, so one level of the
+// descent is one contiguous read), rec[c] = (first child position, child count, word id) of that node.
+struct VocabDev {
+    int n_nodes = 0, n_children = 0, n_words = 0;
+    int root_begin = 0, root_count = 0;
+    void* blob = nullptr;
+    int4* rec = nullptr;          // [n_children] (child_begin, n_children, word_id, 0)
+    uint4* cdesc = nullptr;       // [n_children * 2]
+    double* cweight = nullptr;    // [n_children]
+    double* word_weight = nullptr;// [n_words] weight by word id
+    std::vector<double> word_weight_host;   // the same on the host: the bag-of-words value fold runs there
+};
+
 struct Arena {
     void* ptr = nullptr;
     size_t cap = 0;
@@ -102,10 +116,11 @@ struct slamgpu_ctx {
     int bf_engine = 0;        // SLAMGPU_BF_ENGINE=int|tc overrides the brute-force engine choice (0 = by size, 1 = int, 2 = tc)
     int tc_variant = 0;       // SLAMGPU_TC_VARIANT: debug switches of the tensor-core scan
     slamgpu::Arena d_exp;     // expanded (int8) descriptors of the tensor-core scan
-    std::vector<std::pair<cudaEvent_t, cudaEvent_t>> prof_events[2];   // per SLAMGPU_KERNEL_*
+    std::vector<std::pair<cudaEvent_t, cudaEvent_t>> prof_events[3];   // per SLAMGPU_KERNEL_*
     std::vector<cudaEvent_t> prof_pool;
     std::map<int, slamgpu::FrameDev> frames;
     std::map<int, slamgpu::PointSetDev> point_sets;
+    std::map<int, slamgpu::VocabDev> vocabs;
 };
 
 namespace slamgpu {
@@ -250,6 +265,17 @@ struct ProfScope {
     ProfScope(slamgpu_ctx* c, int k);
     ~ProfScope();
 };
+
+void free_all_vocabs(slamgpu_ctx* ctx);   // voc_api.cu
+// ---- bag of words (voc_kernels.cu) -----------------------------------------------------------
+int voc_launch_transform(slamgpu_ctx* ctx, const VocabDev& v, const uint8_t* d_desc, int n, int32_t* d_word,
+                         double* d_weight);
+// one CTA per image: sort the image's words, run-length encode -> (id, count) per distinct word, ascending
+int voc_launch_bow_count(slamgpu_ctx* ctx, const int32_t* d_word, const int32_t* d_image_offset, int n_images,
+                         int32_t* d_ids, int32_t* d_counts, int32_t* d_n_distinct);
+int voc_launch_score_l1(slamgpu_ctx* ctx, const int32_t* d_q_ids, const double* d_q_vals, int nq,
+                        const int32_t* d_db_ids, const double* d_db_vals, const int32_t* d_db_offset, int n_db,
+                        double* d_score);
 
 int popc_microbench(slamgpu_ctx* ctx, double* popc_per_s, int* n_sm, double* sm_mhz_est);
 

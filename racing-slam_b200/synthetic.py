@@ -282,3 +282,41 @@ class TrackingSequence:
         o0, o1 = int(p.obs_offset[a]), int(p.obs_offset[b])
         return (p.pos[a:b], p.normal[a:b], p.range[a:b], (p.obs_offset[a:b + 1] - o0).astype(np.int32),
                 p.obs_desc[o0:o1])
+
+
+def random_vocabulary(k: int, L: int, seed: int, flip: int = 48):
+    """A synthetic DBoW2-shaped vocabulary tree for sizes DBoW2's own k-means is too slow to
+    build here: complete k-ary tree of depth L, node ids in breadth-first order (children of a node are
+    contiguous, as DBoW2's HKmeansStep creates them), every child descriptor = its parent's with <= flip
+    bits flipped, leaf weights = a plausible idf in (0, 10].  -> dict of the arrays the C ABI takes
+    (child_offset, child_ids, desc, weight, word_id).  The ORB vocabulary the reference loads has k = 10,
+    L = 6 (about 1.1 M nodes)."""
+    rng = np.random.default_rng(seed)
+    level_sizes = [k ** l for l in range(L + 1)]
+    n = int(sum(level_sizes))
+    desc = np.zeros((n, 32), np.uint8)
+    child_offset = np.zeros(n + 1, np.int32)
+    first = np.cumsum([0] + level_sizes)              # first node id of every level
+    for l in range(L):
+        parents = np.arange(first[l], first[l + 1])
+        kids = np.arange(first[l + 1], first[l + 2])
+        base = desc[np.repeat(parents, k)] if l > 0 else rng.integers(0, 256, (len(kids), 32), dtype=np.uint8)
+        desc[kids] = flip_bits(base, rng.integers(flip // 2, flip + 1, len(kids)), rng) if l > 0 else base
+        child_offset[parents + 1] = k
+    child_offset = np.cumsum(child_offset).astype(np.int32)
+    child_ids = np.arange(1, n, dtype=np.int32)
+    word_id = np.full(n, -1, np.int32)
+    leaves = np.arange(first[L], n)
+    word_id[leaves] = np.arange(len(leaves), dtype=np.int32)
+    weight = np.zeros(n, np.float64)
+    weight[leaves] = rng.uniform(0.05, 10.0, len(leaves))
+    return dict(child_offset=child_offset, child_ids=child_ids, desc=desc, weight=weight, word_id=word_id, k=k, L=L)
+
+
+def vocabulary_queries(voc: dict, n: int, seed: int, flip: int = 40) -> np.ndarray:
+    """n query descriptors: perturbed copies of random leaf descriptors, so the descent is decisive at most
+    levels but not all."""
+    rng = np.random.default_rng(seed)
+    leaves = np.nonzero(voc["word_id"] >= 0)[0]
+    src = voc["desc"][rng.choice(leaves, n)]
+    return flip_bits(src, rng.integers(0, flip + 1, n), rng)

@@ -123,3 +123,75 @@ def test_bf_model_vs_oracle_random(oracle):
         a, b = oracle.crosscheck(q, t)
         c, d = bf_model.crosscheck(q, t)
         assert np.array_equal(a, c) and np.array_equal(b, d)
+
+
+# ---- bag of words: the restatement against the reference's own DBoW2 -------------------
+def _voc_of(oracle, g):
+    return oracle.Vocabulary(g["child_offset"], g["child_ids"], g["desc"], g["weight"], g["word_id"], int(g["k"]),
+                             int(g["L"]))
+
+
+@pytest.mark.parametrize("name", golden_names("voc_"))
+def test_voc_oracle_matches_dbow2_golden(oracle, name):
+    """Fixtures come from thirdparty/DBoW2 compiled unmodified (oracle/gen_golden_voc.py): trees built by
+    DBoW2's create(), words / bag-of-words vectors / L1 score from DBoW2's transform() and score()."""
+    g = golden(name)
+    v = _voc_of(oracle, g)
+    word, w = oracle.voc_transform_each(v, g["query"])
+    assert np.array_equal(word, g["word"]) and np.array_equal(w, g["word_weight"])
+    ids, vals = oracle.voc_bow(word, w)
+    assert np.array_equal(ids, g["bow_ids"]) and np.array_equal(vals, g["bow_vals"])     # doubles bit-identical
+    w2, ww2 = oracle.voc_transform_each(v, g["query2"])
+    ids2, vals2 = oracle.voc_bow(w2, ww2)
+    assert np.array_equal(ids2, g["bow2_ids"]) and np.array_equal(vals2, g["bow2_vals"])
+    assert oracle.voc_score_l1(ids, vals, ids2, vals2) == float(g["score"])
+
+
+def test_voc_golden_has_ties_between_children(oracle):
+    """The tie fixture really exercises 'first child with the strictly smallest distance'."""
+    g = golden("voc_k3_L4_ties.npz")
+    off, ids, desc = g["child_offset"], g["child_ids"], g["desc"]
+    ties = 0
+    for q in g["query"][:200]:
+        node = 0
+        while off[node + 1] > off[node]:
+            kids = ids[off[node]:off[node + 1]]
+            d = [oracle.hamming(q, desc[c]) for c in kids]
+            ties += sorted(d)[0] == sorted(d)[1] if len(d) > 1 else 0
+            node = int(kids[int(np.argmin(d))])
+    assert ties > 20
+
+
+def test_voc_oracle_matches_live_dbow2_when_built(oracle, pkg):
+    """Fresh vocabulary from the real DBoW2 (k-means seeded from the clock) when oracle/_ref is present."""
+    if oracle.ref_dbow2() is None:
+        pytest.skip("oracle/_ref/libref_dbow2.so not built (no /root/reference on this machine)")
+    syn = pkg.synthetic
+    rng = np.random.default_rng(17)
+    pool = rng.integers(0, 256, (1200, 32), dtype=np.uint8)
+    imgs = [syn.flip_bits(pool[rng.choice(1200, 250, replace=False)], rng.integers(0, 40, 250), rng) for _ in range(16)]
+    rv = oracle.RefVocabulary(6, 4, np.concatenate(imgs), np.arange(17) * 250)
+    v = rv.export()
+    q = syn.flip_bits(pool[rng.choice(1200, 900)], rng.integers(0, 70, 900), rng)
+    word, w = oracle.voc_transform_each(v, q)
+    rw, rww = rv.transform_each(q)
+    assert np.array_equal(word, rw) and np.array_equal(w, rww)
+    bow, rbow = oracle.voc_bow(word, w), rv.transform_bow(q)
+    assert np.array_equal(bow[0], rbow[0]) and np.array_equal(bow[1], rbow[1])
+    b2 = rv.transform_bow(q[::3])
+    assert oracle.voc_score_l1(*bow, *b2) == rv.score(rbow, b2)
+    rv.close()
+
+
+def test_voc_bow_weightings_and_norms(oracle):
+    """TF / IDF / BINARY and the un-normalised / L2 paths of transform() (TemplatedVocabulary.h:1081-1119)."""
+    word = np.array([5, 2, 5, 9, 2, 5, 7], np.int32)
+    w = np.array([0.5, 2.0, 0.5, 0.0, 2.0, 0.5, 1.5])           # word 9 is stopped (weight 0)
+    ids, v = oracle.voc_bow(word, w, oracle.TF_IDF, oracle.NORM_L1)
+    assert ids.tolist() == [2, 5, 7] and np.allclose(v, np.array([4.0, 1.5, 1.5]) / 7.0) and abs(v.sum() - 1) < 1e-15
+    ids, v = oracle.voc_bow(word, w, oracle.IDF, oracle.NORM_NONE)
+    assert ids.tolist() == [2, 5, 7] and v.tolist() == [2.0, 0.5, 1.5]
+    ids, v = oracle.voc_bow(word, w, oracle.TF, oracle.NORM_NONE)
+    assert v.tolist() == [4.0 / 3, 1.5 / 3, 1.5 / 3]
+    ids, v = oracle.voc_bow(word, w, oracle.BINARY, oracle.NORM_L2)
+    assert np.allclose((v * v).sum(), 1.0)
