@@ -573,6 +573,117 @@ def also_measurements(ctx, pkg, torch, stream, n_sm, peaks):
     import bench_c3
     bench_c3.run_sequence(ctx, pkg, 10, 8000, 1000, 3, 0)
     out["c3_tracking_sequence_200_frames"] = bench_c3.run_sequence(ctx, pkg, 200, 8000, 1000, 3, 3, c3_cpu_arm)
+    out["n4_bag_of_words"] = bow_measurements(ctx, pkg, torch, stream, peaks)
+    return out
+
+
+def bow_measurements(ctx, pkg, torch, stream, peaks):
+    """LoopDetector's retrieval step on an ORB-vocabulary-sized tree (k = 10, L = 6, 1.1 M nodes,
+    synthetic): bow_of for one 8000-feature key frame through the host-buffer call, the word lookup for a
+    1000 x 4000 batch device-resident, and score_candidates against 1000 key frames; CPU legs beside them."""
+    from oracle import cpu_oracle
+    syn = pkg.synthetic
+    out = {}
+    voc = syn.random_vocabulary(10, 6, 6)
+    n_nodes = len(voc["desc"])
+    ctx.vocab_upload(50, voc["child_offset"], voc["child_ids"], voc["desc"], voc["weight"], voc["word_id"])
+    ov = cpu_oracle.Vocabulary(voc["child_offset"], voc["child_ids"], voc["desc"], voc["weight"], voc["word_id"])
+    bytes_per_desc = 32 + 6 * (16 + 32 * 10)            # descriptor + per level: one node record + ten child descriptors
+
+    def wall(fn, reps, warm=3):
+        for _ in range(warm):
+            fn()
+        ts = []
+        for _ in range(reps):
+            t = time.perf_counter()
+            fn()
+            ts.append(time.perf_counter() - t)
+        return float(np.median(ts))
+
+    # one key frame, host buffers, copies inside
+    q = syn.vocabulary_queries(voc, 8000, 7)
+    s = wall(lambda: ctx.vocab_bow(50, q), 50)
+    ctx.profile_enable(True)
+    ctx.profile_read(2)
+    for _ in range(20):
+        ctx.vocab_bow(50, q)
+    k_ms, k_n = ctx.profile_read(2)
+    ctx.profile_enable(False)
+    got = ctx.vocab_bow(50, q)[0]
+    t = time.perf_counter()
+    word, w = cpu_oracle.voc_transform_each(ov, q)
+    ob = cpu_oracle.voc_bow(word, w)
+    t_port = time.perf_counter() - t
+    out["bow_of_8000_features"] = {
+        "us_per_call": s * 1e6, "transform_kernel_us": k_ms / max(k_n, 1) * 1e3, "copies": "inside",
+        "vocabulary": f"k=10 L=6 synthetic, {n_nodes} nodes ({n_nodes * 32 / 1e6:.0f} MB of node descriptors)",
+        "cpu_port_us": t_port * 1e6, "cpu_port_cores": os.cpu_count(),
+        "identical_to_oracle": bool(np.array_equal(got[0], ob[0]) and np.array_equal(got[1], ob[1]))}
+    if cpu_oracle.ref_dbow2() is not None:
+        # the reference's own DBoW2 on a tree of its own (single-threaded, like bow_of in the reference)
+        rng = np.random.default_rng(3)
+        pool = rng.integers(0, 256, (4000, 32), dtype=np.uint8)
+        imgs = [syn.flip_bits(pool[rng.choice(4000, 500, replace=False)], rng.integers(0, 40, 500), rng) for _ in range(40)]
+        rv = cpu_oracle.RefVocabulary(10, 4, np.concatenate(imgs), np.arange(41) * 500)
+        qq = syn.flip_bits(pool[rng.choice(4000, 8000)], rng.integers(0, 60, 8000), rng)
+        t = time.perf_counter()
+        rv.transform_bow(qq)
+        out["bow_of_8000_features"]["reference_dbow2_us_k10_L4"] = (time.perf_counter() - t) * 1e6
+        rv.close()
+
+    # the word lookup for a C5-sized batch, device-resident (1000 key frames x 4000 descriptors)
+    n_big = 4_000_000
+    rng = np.random.default_rng(8)
+    leaves = np.nonzero(voc["word_id"] >= 0)[0]
+    base = voc["desc"][rng.choice(leaves, 200_000)]
+    qbig = np.repeat(base, n_big // len(base), axis=0) ^ rng.integers(0, 256, (n_big, 32), dtype=np.uint8) & \
+        rng.integers(0, 256, (n_big, 32), dtype=np.uint8) & rng.integers(0, 256, (n_big, 32), dtype=np.uint8)
+    dq = torch.from_numpy(np.ascontiguousarray(qbig)).cuda()
+    dword = torch.empty(n_big, dtype=torch.int32, device="cuda")
+    torch.cuda.synchronize()
+    for _ in range(2):
+        ctx.vocab_transform_dev(50, dq.data_ptr(), n_big, dword.data_ptr())
+    ctx.sync()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record(stream)
+    for _ in range(5):
+        ctx.vocab_transform_dev(50, dq.data_ptr(), n_big, dword.data_ptr())
+    b.record(stream)
+    torch.cuda.synchronize()
+    ms = a.elapsed_time(b) / 5
+    sample = 200_000
+    t = time.perf_counter()
+    ow, _ = cpu_oracle.voc_transform_each(ov, qbig[:sample])
+    t_cpu = time.perf_counter() - t
+    out["transform_4M_descriptors_device"] = {
+        "ms": ms, "descriptors_per_s": n_big / (ms * 1e-3), "algorithmic_bytes_per_descriptor": bytes_per_desc,
+        "gb_s_algorithmic": n_big * bytes_per_desc / (ms * 1e-3) / 1e9,
+        "hbm_frac": n_big * bytes_per_desc / (ms * 1e-3) / 1e9 / peaks["hbm_gbs"],
+        "note": "the tree (49 MB with its node records) stays in the 126 MB L2; the bound is L2 -> SM gathers of 32-byte rows",
+        "cpu_port_descriptors_per_s": sample / t_cpu, "cpu_port_cores": os.cpu_count(),
+        "identical_to_oracle_on_sample": bool(np.array_equal(dword[:sample].cpu().numpy(), ow))}
+    del dq, dword
+
+    # score_candidates: one key frame against 1000 earlier ones
+    per = 4000
+    qdb = qbig[:1000 * per]
+    off = (np.arange(1001) * per).astype(np.int32)
+    db = ctx.vocab_bow(50, qdb, off)
+    query = ctx.vocab_bow(50, np.concatenate([qdb[:per // 2], qdb[7 * per:7 * per + per // 2]]))[0]
+    s = wall(lambda: ctx.vocab_score_l1(query, db), 10)
+    t = time.perf_counter()
+    want = np.array([cpu_oracle.voc_score_l1(*query, *d) for d in db])
+    t_cpu = time.perf_counter() - t
+    for vec in db:
+        ctx.bowdb_append(51, vec)
+    s_res = wall(lambda: ctx.bowdb_score_l1(51, query), 50)
+    out["score_l1_1000_keyframes"] = {"us_per_call_resident_database": s_res * 1e6,
+                                      "us_per_call_database_uploaded_per_call": s * 1e6,
+                                      "copies": "inside (query up, 1000 scores down)",
+                                      "cpu_port_us": t_cpu * 1e6, "cpu_port_note": "one core, called per vector from Python",
+                                      "identical_to_oracle": bool(np.array_equal(ctx.bowdb_score_l1(51, query), want))}
+    ctx.bowdb_release(51)
+    ctx.vocab_release(50)
     return out
 
 

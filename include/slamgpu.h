@@ -284,6 +284,16 @@ SLAMGPU_API int slamgpu_vocab_score_l1(slamgpu_ctx* ctx, const int32_t* q_ids, c
                            const int32_t* db_ids, const double* db_vals, const int32_t* db_offset, int n_db,
                            double* out_score);
 
+/* Resident database of bag-of-words vectors -- LoopDetector::Impl::bows, one vector per key frame
+ * (src/LoopDetector.cpp:346-373): append a key frame's vector when it is inserted, score a query against
+ * every resident vector with one small upload and one download of n_vectors doubles.  Vector indices are
+ * the append order.  db_id is created by the first append. */
+SLAMGPU_API int slamgpu_bowdb_append(slamgpu_ctx* ctx, int db_id, const int32_t* ids, const double* vals, int n);
+SLAMGPU_API int slamgpu_bowdb_count(slamgpu_ctx* ctx, int db_id, int* n_vectors);
+SLAMGPU_API int slamgpu_bowdb_score_l1(slamgpu_ctx* ctx, int db_id, const int32_t* q_ids, const double* q_vals, int nq,
+                           double* out_score);
+SLAMGPU_API int slamgpu_bowdb_release(slamgpu_ctx* ctx, int db_id);
+
 /* ------------------------------------------------------------------------------------------
  * Diagnostics
  * ---------------------------------------------------------------------------------------- */

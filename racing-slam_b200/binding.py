@@ -89,6 +89,10 @@ SIGNATURES = {
     "slamgpu_vocab_transform_dev": (C.c_int, [_ctx, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]),
     "slamgpu_vocab_bow": (C.c_int, [_ctx, C.c_int, _u8p, _i32p, C.c_int, C.c_int, C.c_int, _i32p, _f64p, _i32p]),
     "slamgpu_vocab_score_l1": (C.c_int, [_ctx, _i32p, _f64p, C.c_int, _i32p, _f64p, _i32p, C.c_int, _f64p]),
+    "slamgpu_bowdb_append": (C.c_int, [_ctx, C.c_int, _i32p, _f64p, C.c_int]),
+    "slamgpu_bowdb_count": (C.c_int, [_ctx, C.c_int, C.POINTER(C.c_int)]),
+    "slamgpu_bowdb_score_l1": (C.c_int, [_ctx, C.c_int, _i32p, _f64p, C.c_int, _f64p]),
+    "slamgpu_bowdb_release": (C.c_int, [_ctx, C.c_int]),
     "slamgpu_profile_enable": (C.c_int, [_ctx, C.c_int]),
     "slamgpu_profile_read": (C.c_int, [_ctx, C.c_int, C.POINTER(C.c_double), _i64p]),
     "slamgpu_bench_popc": (C.c_int, [_ctx, C.POINTER(C.c_double), C.POINTER(C.c_int), C.POINTER(C.c_double)]),
@@ -438,6 +442,28 @@ class Context:
                                                      _p(db_ids, C.c_int32), _p(db_vals, C.c_double),
                                                      _p(off, C.c_int32), len(database), _p(out, C.c_double)))
         return out
+
+    def bowdb_append(self, db_id: int, vector):
+        """Append one (ids ascending, values) vector to a resident database (created by the first append)."""
+        ids = np.ascontiguousarray(vector[0], np.int32)
+        vals = np.ascontiguousarray(vector[1], np.float64)
+        self._check(self._lib.slamgpu_bowdb_append(self._h, db_id, _p(ids, C.c_int32), _p(vals, C.c_double), len(ids)))
+
+    def bowdb_count(self, db_id: int) -> int:
+        n = C.c_int(0)
+        self._check(self._lib.slamgpu_bowdb_count(self._h, db_id, C.byref(n)))
+        return n.value
+
+    def bowdb_score_l1(self, db_id: int, query):
+        q_ids = np.ascontiguousarray(query[0], np.int32)
+        q_vals = np.ascontiguousarray(query[1], np.float64)
+        out = np.zeros(self.bowdb_count(db_id), np.float64)
+        self._check(self._lib.slamgpu_bowdb_score_l1(self._h, db_id, _p(q_ids, C.c_int32), _p(q_vals, C.c_double),
+                                                     len(q_ids), _p(out, C.c_double)))
+        return out
+
+    def bowdb_release(self, db_id: int):
+        self._check(self._lib.slamgpu_bowdb_release(self._h, db_id))
 
     def match_projection_batch(self, frame_ids, nkps, set_id: int, poses, params: ProjParams, skip=None, order=None):
         """Frozen-snapshot batch over key frames -> list of (out_point, out_dist) per frame."""

@@ -93,6 +93,15 @@ struct VocabDev {
     std::vector<double> word_weight_host;   // the same on the host: the bag-of-words value fold runs there
 };
 
+// Resident bag-of-words database: concatenated (ids, values) with offsets, grown geometrically.
+struct BowDbDev {
+    int n_vectors = 0, cap_vectors = 0;
+    int64_t n_entries = 0, cap_entries = 0;
+    int32_t* ids = nullptr;
+    double* vals = nullptr;
+    int32_t* offset = nullptr;    // [cap_vectors + 1]
+};
+
 struct Arena {
     void* ptr = nullptr;
     size_t cap = 0;
@@ -121,6 +130,8 @@ struct slamgpu_ctx {
     std::map<int, slamgpu::FrameDev> frames;
     std::map<int, slamgpu::PointSetDev> point_sets;
     std::map<int, slamgpu::VocabDev> vocabs;
+    std::map<int, slamgpu::BowDbDev> bow_dbs;
+    bool bow_smem_set = false;
 };
 
 namespace slamgpu {

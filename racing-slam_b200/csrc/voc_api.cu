@@ -17,6 +17,14 @@ namespace {
         SG_CUDA(cudaSetDevice((ctx)->device));      \
     } while (0)
 
+void free_bowdb(BowDbDev& d)
+{
+    if (d.ids) cudaFree(d.ids);
+    if (d.vals) cudaFree(d.vals);
+    if (d.offset) cudaFree(d.offset);
+    d = BowDbDev();
+}
+
 void free_vocab(VocabDev& v)
 {
     if (v.blob) cudaFree(v.blob);
@@ -30,6 +38,8 @@ void free_all_vocabs(slamgpu_ctx* ctx)
 {
     for (auto& kv : ctx->vocabs) free_vocab(kv.second);
     ctx->vocabs.clear();
+    for (auto& kv : ctx->bow_dbs) free_bowdb(kv.second);
+    ctx->bow_dbs.clear();
 }
 } // namespace slamgpu
 
@@ -305,6 +315,125 @@ int slamgpu_vocab_score_l1(slamgpu_ctx* ctx, const int32_t* q_ids, const double*
     SG_CUDA(cudaMemcpyAsync(ctx->h_stage.ptr, d_s, D * 8, cudaMemcpyDeviceToHost, ctx->stream));
     SG_CUDA(cudaStreamSynchronize(ctx->stream));
     std::memcpy(out_score, ctx->h_stage.ptr, D * 8);
+    return SLAMGPU_OK;
+}
+
+int slamgpu_bowdb_append(slamgpu_ctx* ctx, int db_id, const int32_t* ids, const double* vals, int n)
+{
+    SG_CTX(ctx);
+    SG_CHECK(n >= 0, "negative vector length");
+    SG_CHECK(n == 0 || (ids != nullptr && vals != nullptr), "null vector arrays");
+    for (int i = 1; i < n; ++i) SG_CHECK(ids[i] > ids[i - 1], "vector ids must be strictly ascending");
+    BowDbDev& d = ctx->bow_dbs[db_id];
+    SG_CHECK(d.n_entries + n <= 0x7FFFFFFF, "bag-of-words database too large");
+    // grow geometrically; the live part moves device-to-device
+    if (d.n_vectors + 1 > d.cap_vectors) {
+        const int cap = std::max(1024, 2 * d.cap_vectors);
+        int32_t* p = nullptr;
+        SG_CUDA(cudaMalloc(&p, (static_cast<size_t>(cap) + 1) * sizeof(int32_t)));
+        if (d.offset) {
+            SG_CUDA(cudaMemcpyAsync(p, d.offset, (static_cast<size_t>(d.n_vectors) + 1) * 4, cudaMemcpyDeviceToDevice, ctx->stream));
+            SG_CUDA(cudaStreamSynchronize(ctx->stream));
+            cudaFree(d.offset);
+        } else {
+            SG_CUDA(cudaMemsetAsync(p, 0, 4, ctx->stream));
+        }
+        d.offset = p;
+        d.cap_vectors = cap;
+    }
+    if (d.n_entries + n > d.cap_entries) {
+        const int64_t cap = std::max<int64_t>(std::max<int64_t>(1 << 20, d.n_entries + n), 2 * d.cap_entries);
+        int32_t* pi = nullptr;
+        double* pv = nullptr;
+        SG_CUDA(cudaMalloc(&pi, static_cast<size_t>(cap) * 4));
+        const cudaError_t e = cudaMalloc(&pv, static_cast<size_t>(cap) * 8);
+        if (e != cudaSuccess) {
+            cudaFree(pi);
+            cudaGetLastError();
+            return fail(SLAMGPU_ERR_NOMEM, std::string("bag-of-words database growth failed: ") + cudaGetErrorString(e));
+        }
+        if (d.n_entries) {
+            SG_CUDA(cudaMemcpyAsync(pi, d.ids, static_cast<size_t>(d.n_entries) * 4, cudaMemcpyDeviceToDevice, ctx->stream));
+            SG_CUDA(cudaMemcpyAsync(pv, d.vals, static_cast<size_t>(d.n_entries) * 8, cudaMemcpyDeviceToDevice, ctx->stream));
+            SG_CUDA(cudaStreamSynchronize(ctx->stream));
+        }
+        if (d.ids) cudaFree(d.ids);
+        if (d.vals) cudaFree(d.vals);
+        d.ids = pi;
+        d.vals = pv;
+        d.cap_entries = cap;
+    }
+    const size_t N = static_cast<size_t>(n);
+    const size_t b_i = Carver::padded(N * 4), b_v = Carver::padded(N * 8);
+    SG_TRY(ensure_host_stage(ctx, b_i + b_v + 256));
+    SG_CUDA(cudaStreamSynchronize(ctx->stream));
+    Carver hio(ctx->h_stage.ptr);
+    int32_t* h_i = hio.take<int32_t>(N);
+    double* h_v = hio.take<double>(N);
+    int32_t* h_end = hio.take<int32_t>(1);
+    if (n) {
+        std::memcpy(h_i, ids, N * 4);
+        std::memcpy(h_v, vals, N * 8);
+        SG_CUDA(cudaMemcpyAsync(d.ids + d.n_entries, h_i, N * 4, cudaMemcpyHostToDevice, ctx->stream));
+        SG_CUDA(cudaMemcpyAsync(d.vals + d.n_entries, h_v, N * 8, cudaMemcpyHostToDevice, ctx->stream));
+    }
+    *h_end = static_cast<int32_t>(d.n_entries + n);
+    SG_CUDA(cudaMemcpyAsync(d.offset + d.n_vectors + 1, h_end, 4, cudaMemcpyHostToDevice, ctx->stream));
+    SG_CUDA(cudaStreamSynchronize(ctx->stream));
+    d.n_vectors++;
+    d.n_entries += n;
+    return SLAMGPU_OK;
+}
+
+int slamgpu_bowdb_count(slamgpu_ctx* ctx, int db_id, int* n_vectors)
+{
+    SG_CHECK(ctx != nullptr && n_vectors != nullptr, "null pointer");
+    auto it = ctx->bow_dbs.find(db_id);
+    *n_vectors = it == ctx->bow_dbs.end() ? 0 : it->second.n_vectors;
+    return SLAMGPU_OK;
+}
+
+int slamgpu_bowdb_score_l1(slamgpu_ctx* ctx, int db_id, const int32_t* q_ids, const double* q_vals, int nq,
+                           double* out_score)
+{
+    SG_CTX(ctx);
+    SG_CHECK(nq >= 0, "negative vector length");
+    auto it = ctx->bow_dbs.find(db_id);
+    if (it == ctx->bow_dbs.end()) return fail(SLAMGPU_ERR_NOTFOUND, "unknown bag-of-words database id");
+    const BowDbDev& d = it->second;
+    if (d.n_vectors == 0) return SLAMGPU_OK;
+    SG_CHECK(out_score != nullptr && (nq == 0 || (q_ids && q_vals)), "null pointer");
+    for (int i = 1; i < nq; ++i) SG_CHECK(q_ids[i] > q_ids[i - 1], "query ids must be strictly ascending");
+    const size_t Q = static_cast<size_t>(nq), D = static_cast<size_t>(d.n_vectors);
+    const size_t b_qi = Carver::padded(Q * 4), b_qv = Carver::padded(Q * 8), b_s = Carver::padded(D * 8);
+    SG_TRY(ensure_device_io(ctx, b_qi + b_qv + b_s + 256));
+    SG_TRY(ensure_host_stage(ctx, std::max(b_qi + b_qv, b_s) + 256));
+    Carver dio(ctx->d_io.ptr), hio(ctx->h_stage.ptr);
+    int32_t* d_qi = dio.take<int32_t>(Q);
+    double* d_qv = dio.take<double>(Q);
+    double* d_s = dio.take<double>(D);
+    int32_t* h_qi = hio.take<int32_t>(Q);
+    double* h_qv = hio.take<double>(Q);
+    if (Q) {
+        std::memcpy(h_qi, q_ids, Q * 4);
+        std::memcpy(h_qv, q_vals, Q * 8);
+        SG_CUDA(cudaMemcpyAsync(ctx->d_io.ptr, ctx->h_stage.ptr, b_qi + b_qv, cudaMemcpyHostToDevice, ctx->stream));
+    }
+    SG_TRY(voc_launch_score_l1(ctx, d_qi, d_qv, nq, d.ids, d.vals, d.offset, d.n_vectors, d_s));
+    SG_CUDA(cudaMemcpyAsync(ctx->h_stage.ptr, d_s, D * 8, cudaMemcpyDeviceToHost, ctx->stream));
+    SG_CUDA(cudaStreamSynchronize(ctx->stream));
+    std::memcpy(out_score, ctx->h_stage.ptr, D * 8);
+    return SLAMGPU_OK;
+}
+
+int slamgpu_bowdb_release(slamgpu_ctx* ctx, int db_id)
+{
+    SG_CTX(ctx);
+    auto it = ctx->bow_dbs.find(db_id);
+    if (it == ctx->bow_dbs.end()) return fail(SLAMGPU_ERR_NOTFOUND, "unknown bag-of-words database id");
+    SG_CUDA(cudaStreamSynchronize(ctx->stream));
+    free_bowdb(it->second);
+    ctx->bow_dbs.erase(it);
     return SLAMGPU_OK;
 }
 

@@ -70,7 +70,7 @@ __global__ void __launch_bounds__(kVocThreads) voc_transform_kernel(const int4* 
 
 // One CTA per image: bitonic sort of the image's words in shared memory (padded with INT_MAX to a power of
 // two), then run-length encoding with a block-wide exclusive scan of the run heads.
-constexpr int kBowThreads = 512;
+constexpr int kBowThreads = 1024;
 
 __global__ void __launch_bounds__(kBowThreads) voc_bow_count_kernel(const int32_t* __restrict__ word,
                                                                     const int32_t* __restrict__ image_offset,
@@ -88,15 +88,14 @@ __global__ void __launch_bounds__(kBowThreads) voc_bow_count_kernel(const int32_
     __syncthreads();
     for (int k = 2; k <= cap; k <<= 1) {
         for (int j = k >> 1; j > 0; j >>= 1) {
-            for (int t = threadIdx.x; t < cap; t += kBowThreads) {
-                const int p = t ^ j;
-                if (p > t) {
-                    const int32_t x = s_w[t], y = s_w[p];
-                    const bool up = (t & k) == 0;
-                    if ((x > y) == up) {
-                        s_w[t] = y;
-                        s_w[p] = x;
-                    }
+            for (int i = threadIdx.x; i < (cap >> 1); i += kBowThreads) {    // one compare-exchange pair per iteration
+                const int t = ((i & ~(j - 1)) << 1) | (i & (j - 1));
+                const int p = t | j;
+                const int32_t x = s_w[t], y = s_w[p];
+                const bool up = (t & k) == 0;
+                if ((x > y) == up) {
+                    s_w[t] = y;
+                    s_w[p] = x;
                 }
             }
             __syncthreads();
@@ -196,7 +195,10 @@ int voc_launch_bow_count(slamgpu_ctx* ctx, const int32_t* d_word, const int32_t*
 {
     if (n_images <= 0) return SLAMGPU_OK;
     const size_t smem = (SLAMGPU_BOW_MAX_FEATURES + kBowThreads) * sizeof(int32_t);
-    SG_CUDA(cudaFuncSetAttribute(voc_bow_count_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+    if (!ctx->bow_smem_set) {     // per context = per device
+        SG_CUDA(cudaFuncSetAttribute(voc_bow_count_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+        ctx->bow_smem_set = true;
+    }
     voc_bow_count_kernel<<<n_images, kBowThreads, smem, ctx->stream>>>(d_word, d_image_offset, d_ids, d_counts, d_n_distinct);
     ctx->launches++;
     SG_CUDA(cudaGetLastError());

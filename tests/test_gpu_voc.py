@@ -124,6 +124,34 @@ def test_score_l1_against_a_database_vs_oracle(ctx, oracle, pkg):
     ctx.vocab_release(5)
 
 
+def test_resident_database_equals_the_one_shot_call(ctx, oracle, pkg):
+    """slamgpu_bowdb_*: key-frame vectors appended one by one (growth past the first capacity included),
+    scored in place; same doubles as the host-buffer call and the oracle."""
+    syn = pkg.synthetic
+    v = syn.random_vocabulary(10, 3, 51)
+    _upload(ctx, 8, v)
+    n_db = 1300                                                           # > 1024: the offset table grows once
+    sizes = np.random.default_rng(52).integers(0, 900, n_db)
+    sizes[3] = 0
+    off = np.concatenate([[0], np.cumsum(sizes)]).astype(np.int32)
+    q_all = syn.vocabulary_queries(v, int(off[-1]), 53)
+    db = ctx.vocab_bow(8, q_all, off)
+    assert ctx.bowdb_count(30) == 0
+    for vec in db:
+        ctx.bowdb_append(30, vec)
+    assert ctx.bowdb_count(30) == n_db
+    query = ctx.vocab_bow(8, q_all[off[10]:off[12]])[0]
+    got = ctx.bowdb_score_l1(30, query)
+    assert np.array_equal(got, ctx.vocab_score_l1(query, db))
+    assert np.array_equal(got, np.array([oracle.voc_score_l1(*query, *d) for d in db]))
+    assert got[3] == 0.0 and got[10] > 0.3 and got[11] > 0.3
+    with pytest.raises(pkg.SlamGpuError):
+        ctx.bowdb_append(30, (np.array([5, 5], np.int32), np.array([0.5, 0.5])))
+    ctx.bowdb_release(30), ctx.vocab_release(8)
+    with pytest.raises(pkg.SlamGpuError):
+        ctx.bowdb_score_l1(30, query)
+
+
 def test_argument_errors(ctx, pkg):
     syn = pkg.synthetic
     v = syn.random_vocabulary(4, 2, 41)
