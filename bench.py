@@ -368,6 +368,8 @@ def run_ours(args, rank, local_rank, world):
     # the two API forms ran the same last step: their per-pair match counts must agree
     assert np.array_equal(np.diff(o_off.astype(np.int64)), dev_counts_last), "host and device API forms disagree"
     checksum = int(sum_over_ranks(float(dev_counts_last.sum())))
+    # every rank takes part in the sharded C4 batch (collectives inside): before the non-zero ranks leave
+    c4_line = c4_sharded(ctx, pkg, rank, world, barrier, max_over_ranks, sum_over_ranks)
 
     if rank != 0:
         if world > 1:
@@ -436,6 +438,7 @@ def run_ours(args, rank, local_rank, world):
         "gpu_launches": int(gpu_launches), "roofline": roofline, "clocks": clocks,
         "matches_last_step_all_ranks": checksum,
     }
+    line["c4_local_window_batch"] = c4_line
     if world == 1:
         line["cpu_baseline"] = cpu_baseline(args, db)
         if not args.no_also:
@@ -443,6 +446,51 @@ def run_ours(args, rank, local_rank, world):
     print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
+
+
+def c4_sharded(ctx, pkg, rank, world, barrier, max_over_ranks, sum_over_ranks):
+    """BASELINE configs[3]: the fuse window -- 20 key frames x 50k map points on a frozen
+    snapshot, replace = true -- sharded by key frame (round-robin, sharding.shard_keyframes), point set
+    replicated (same seed on every rank), no collective on the data path.  'strong' = the 20 key frames of the
+    config split over the ranks; 'weak' = 20 key frames per rank.  Host-buffer call (poses up, matches down),
+    host clock between barriers, max over ranks, median of the repetitions."""
+    syn = pkg.synthetic
+    cam = syn.KITTI
+    sc = syn.projection_scene(50000, 2000, 4)
+    prm = pkg.ProjParams(cam["fx"], cam["fy"], cam["cx"], cam["cy"], cam["width"], cam["height"], 20.0, MAX_DIST, 0.5,
+                         2.0, 1.25, 1)
+    ctx.points_upload(940, sc.pos, sc.normal, sc.range, sc.obs_offset, sc.obs_desc)
+    out = {}
+    for mode, n_kf in (("strong", 20), ("weak", 20 * world)):
+        rng = np.random.default_rng(4)
+        xys = [syn.keypoints_integer(2000, cam["width"], cam["height"], 700 + k) for k in range(n_kf)]
+        descs = [sc.kp_desc[rng.permutation(2000)] for _ in range(n_kf)]
+        poses_all = np.stack([syn.pose_colmajor(syn.make_pose(rng)) for _ in range(n_kf)])
+        mine = pkg.sharding.shard_keyframes(n_kf, rank, world)
+        ids = []
+        for j, k in enumerate(mine):
+            ctx.frame_upload(2000 + j, xys[k], descs[k], None, None)
+            ids.append(2000 + j)
+        poses = poses_all[mine]
+        nk = [2000] * len(ids)
+        ts, matches = [], 0
+        for rep in range(13):
+            barrier()
+            t0 = time.perf_counter()
+            res = ctx.match_projection_batch(ids, nk, 940, poses, prm) if ids else []
+            dt = max_over_ranks(time.perf_counter() - t0)
+            if rep >= 3:
+                ts.append(dt)
+            matches = sum(int((p >= 0).sum()) for p, _ in res)
+        s = float(np.median(ts))
+        out[mode] = {"key_frames_total": n_kf, "key_frames_this_rank": len(ids), "ms_per_batch": s * 1e3,
+                     "keyframes_per_s": n_kf / s, "point_projections_per_s": n_kf * 50000 / s,
+                     "matches_all_ranks": int(sum_over_ranks(float(matches)))}
+        for i in ids:
+            ctx.frame_release(i)
+    ctx.points_release(940)
+    out["sharding"] = f"key frames round-robin over {world} rank(s), 50k-point set replicated, no collective; copies inside"
+    return out
 
 
 def also_measurements(ctx, pkg, torch, stream, n_sm, peaks):

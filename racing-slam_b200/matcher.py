@@ -294,3 +294,59 @@ class MapMatcher:
         train = np.stack([key_frame.descriptor(m.keypoint_index) for m in matches])
         qi, ti = self.ctx.match_descriptors(q, train, self.max_descriptor_distance, self.match_ratio)
         return [MapPointMatch(matches[int(t)].point, int(qq)) for qq, t in zip(qi, ti)]
+
+
+class OrbVocabulary:
+    """Host-side mirror of what LoopDetector uses of DBoW2's OrbVocabulary (src/LoopDetector.cpp:26,85-92,369):
+    transform(features) -> bag-of-words vector and score(a, b), on a vocabulary tree resident on the device.
+    A vector is (ids ascending, values) -- the contents of DBoW2::BowVector's std::map in order."""
+
+    _next_id = 100
+
+    def __init__(self, ctx: L.Context, child_offset, child_ids, desc, weight, word_id,
+                 weighting: int = L.BOW_TF_IDF, norm: int = L.BOW_NORM_L1):
+        self.ctx, self.weighting, self.norm = ctx, weighting, norm
+        self.vocab_id = OrbVocabulary._next_id
+        OrbVocabulary._next_id += 1
+        ctx.vocab_upload(self.vocab_id, child_offset, child_ids, desc, weight, word_id)
+
+    def transform(self, descriptors):
+        """bow_of (src/LoopDetector.cpp:85-92): empty features give an empty vector."""
+        d = np.ascontiguousarray(descriptors, np.uint8).reshape(-1, 32)
+        if len(d) == 0:
+            return np.zeros(0, np.int32), np.zeros(0, np.float64)
+        return self.ctx.vocab_bow(self.vocab_id, d, None, self.weighting, self.norm)[0]
+
+    def score(self, a, b) -> float:
+        return float(self.ctx.vocab_score_l1(a, [b])[0])
+
+    def close(self):
+        self.ctx.vocab_release(self.vocab_id)
+
+
+class BowDatabase:
+    """LoopDetector::Impl::bows kept on the device: add() per key frame, scores() of a query against all."""
+
+    _next_id = 100
+
+    def __init__(self, ctx: L.Context):
+        self.ctx = ctx
+        self.db_id = BowDatabase._next_id
+        BowDatabase._next_id += 1
+        self._n = 0
+
+    def add(self, vector) -> int:
+        self.ctx.bowdb_append(self.db_id, vector)
+        self._n += 1
+        return self._n - 1
+
+    def scores(self, query) -> np.ndarray:
+        """score_candidates' inner loop (src/LoopDetector.cpp:369) for every stored key frame."""
+        if self._n == 0:
+            return np.zeros(0, np.float64)
+        return self.ctx.bowdb_score_l1(self.db_id, query)
+
+    def close(self):
+        if self._n:
+            self.ctx.bowdb_release(self.db_id)
+            self._n = 0

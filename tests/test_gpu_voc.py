@@ -175,3 +175,21 @@ def test_argument_errors(ctx, pkg):
     assert word.tolist() == [-1, -1, -1]
     assert len(ctx.vocab_bow(7, np.zeros((3, 32), np.uint8))[0][0]) == 0
     ctx.vocab_release(7)
+
+
+def test_mirror_vocabulary_and_database_read_like_the_reference(ctx, pkg):
+    """bow_of + score_candidates through the mirror classes, on a DBoW2-built tree (golden fixture)."""
+    m = pkg.matcher
+    g = golden("voc_k10_L3.npz")
+    voc = m.OrbVocabulary(ctx, g["child_offset"], g["child_ids"], g["desc"], g["weight"], g["word_id"])
+    bow = voc.transform(g["query"])
+    bow2 = voc.transform(g["query2"])
+    assert np.array_equal(bow[0], g["bow_ids"]) and np.array_equal(bow[1], g["bow_vals"])
+    assert voc.score(bow, bow2) == float(g["score"])
+    assert len(voc.transform(np.zeros((0, 32), np.uint8))[0]) == 0
+    db = m.BowDatabase(ctx)
+    assert len(db.scores(bow)) == 0
+    assert db.add(bow2) == 0 and db.add(bow) == 1
+    s = db.scores(bow)
+    assert s[0] == float(g["score"]) and abs(s[1] - 1.0) < 1e-12
+    db.close(), voc.close()
