@@ -266,7 +266,10 @@ def run_ours(args, rank, local_rank, world):
     if world > 1:
         # NCCL's version banner goes to stdout by default; stdout carries the one JSON line only
         os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+        import datetime
+        # a rank that dies must not leave the others waiting for the default 10 minutes
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank),
+                                timeout=datetime.timedelta(seconds=180))
 
     def barrier():
         if world > 1:

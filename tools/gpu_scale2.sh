@@ -1,10 +1,10 @@
 # N = 1, 2 (and 4, 8 when the box has them) with the sharded C4 batch in the line
 cd $GRAFT_REPO_ROOT
 NG=$(nvidia-smi -L | wc -l)
-timeout 1200 python bench.py > gpurun_out/bench_n1.json 2> gpurun_out/bench_n1.err; echo "n1 exit $?"
+[ "$SKIP_N1" = 1 ] || (timeout 1200 python bench.py > gpurun_out/bench_n1.json 2> gpurun_out/bench_n1.err; echo "n1 exit $?")
 for n in 2 4 8; do
   if [ $n -le $NG ]; then
-    timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $n --master-addr 127.0.0.1 --master-port $((29540+n)) bench.py --gpus $n --steps 5 --warmup 3 > gpurun_out/bench_n$n.json 2> gpurun_out/bench_n$n.err; echo "n$n exit $?"
+    timeout 400 python -m torch.distributed.run --nnodes=1 --nproc-per-node $n --master-addr 127.0.0.1 --master-port $((29540+n)) bench.py --gpus $n --steps 5 --warmup 3 > gpurun_out/bench_n$n.json 2> gpurun_out/bench_n$n.err; echo "n$n exit $?"
   fi
 done
 python - <<'P'
