@@ -20,9 +20,15 @@ namespace {
 
 void free_frame(FrameDev& f)
 {
+    if (f.pending && f.pending->worker.joinable()) f.pending->worker.join();   // a KD build still running
     if (f.blob) cudaFree(f.blob);
     f = FrameDev();
 }
+int finalize_frame(slamgpu_ctx* ctx, FrameDev& f);
+void join_frame(FrameDev& f);
+size_t kd_image_bytes(size_t n, size_t n_cells);
+void build_kd_image(FrameKdPending& k);
+
 void free_points(PointSetDev& p)
 {
     if (p.blob) cudaFree(p.blob);
@@ -156,6 +162,7 @@ int match_projection_impl(slamgpu_ctx* ctx, const int* frame_ids, int n_frames, 
         if (it == ctx->frames.end()) return fail(SLAMGPU_ERR_NOTFOUND, "unknown frame id");
         for (int j = 0; j < i; ++j)
             SG_CHECK(frame_ids[j] != frame_ids[i], "a frame may appear only once per projection batch");
+        SG_TRY(finalize_frame(ctx, it->second));      // the KD-tree may still be building on its host thread
         fds[i] = &it->second;
         total_kp += static_cast<size_t>(it->second.nkp);
         max_nkp = std::max(max_nkp, it->second.nkp);
@@ -262,6 +269,86 @@ int match_projection_impl(slamgpu_ctx* ctx, const int* frame_ids, int n_frames, 
     return SLAMGPU_OK;
 }
 
+// Bytes of the KD image: [kd_xy][kd_idx][cell_start][cell_items][cell_rec], each padded like the device blob.
+size_t kd_image_bytes(size_t n, size_t n_cells)
+{
+    return Carver::padded(n * sizeof(float2)) + Carver::padded(n * sizeof(int32_t)) +
+           Carver::padded((n_cells + 1) * sizeof(int32_t)) + Carver::padded(n * sizeof(int32_t)) +
+           Carver::padded(n * sizeof(int4));
+}
+
+// Everything the device keeps in KD order, from the permutation (host side; may run on the frame's worker thread).
+void build_kd_image(FrameKdPending& k)
+{
+    const size_t n = k.xy.size() / 2;
+    const size_t n_cells = static_cast<size_t>(k.gw) * k.gh;
+    Carver hv(k.image.data());
+    float* h_kdxy = reinterpret_cast<float*>(hv.take<float2>(n));
+    int32_t* h_kdidx = hv.take<int32_t>(n);
+    int32_t* h_cstart = hv.take<int32_t>(n_cells + 1);
+    int32_t* h_citems = hv.take<int32_t>(n);
+    int4* h_crec = hv.take<int4>(n);
+    const float* xy = k.xy.data();
+    for (size_t m = 0; m < n; ++m) {
+        const uint32_t p = k.perm[m];
+        h_kdxy[2 * m] = xy[2 * p];
+        h_kdxy[2 * m + 1] = xy[2 * p + 1];
+        h_kdidx[m] = static_cast<int32_t>(p);
+    }
+    // counting sort of the KD positions by cell; the device maps coordinates to cells with the
+    // same float expression (proj_kernels.cu: grid_cell), and both are monotone in the coordinate
+    std::memset(h_cstart, 0, (n_cells + 1) * sizeof(int32_t));
+    auto cell_of = [&](float x, float y) {
+        int cxi = static_cast<int>(std::floor((x - k.gx0) * k.inv_cell));
+        int cyi = static_cast<int>(std::floor((y - k.gy0) * k.inv_cell));
+        cxi = std::min(std::max(cxi, 0), k.gw - 1);
+        cyi = std::min(std::max(cyi, 0), k.gh - 1);
+        return static_cast<size_t>(cyi) * k.gw + cxi;
+    };
+    std::vector<int32_t> cell(n);
+    for (size_t m = 0; m < n; ++m) {
+        cell[m] = static_cast<int32_t>(cell_of(h_kdxy[2 * m], h_kdxy[2 * m + 1]));
+        h_cstart[cell[m] + 1]++;
+    }
+    for (size_t c = 0; c < n_cells; ++c) h_cstart[c + 1] += h_cstart[c];
+    {
+        std::vector<int32_t> cursor(h_cstart, h_cstart + n_cells);
+        for (size_t m = 0; m < n; ++m) h_citems[cursor[cell[m]]++] = static_cast<int32_t>(m);
+    }
+    // one 16-byte record per grid slot: (x bits, y bits, keypoint index, KD position) -- everything the
+    // candidate test needs in a single load
+    for (size_t i = 0; i < n; ++i) {
+        const int32_t m = h_citems[i];
+        int32_t xb, yb;
+        std::memcpy(&xb, &h_kdxy[2 * m], 4);
+        std::memcpy(&yb, &h_kdxy[2 * m + 1], 4);
+        h_crec[i] = make_int4(xb, yb, h_kdidx[m], m);
+    }
+}
+
+void join_frame(FrameDev& f)
+{
+    if (f.pending && f.pending->worker.joinable()) f.pending->worker.join();
+}
+
+// Make the frame's KD image resident: wait for the builder, one H2D copy.  Every entry point that reads the
+// tree calls this first; it is a no-op once done.
+int finalize_frame(slamgpu_ctx* ctx, FrameDev& f)
+{
+    if (!f.pending) return SLAMGPU_OK;
+    join_frame(f);
+    f.perm_host = f.pending->perm;
+    if (f.kd_image_bytes) {
+        SG_TRY(ensure_host_stage(ctx, f.kd_image_bytes + 256));
+        SG_CUDA(cudaStreamSynchronize(ctx->stream));            // staging is reused
+        std::memcpy(ctx->h_stage.ptr, f.pending->image.data(), f.kd_image_bytes);
+        SG_CUDA(cudaMemcpyAsync(f.kd_image, ctx->h_stage.ptr, f.kd_image_bytes, cudaMemcpyHostToDevice, ctx->stream));
+        SG_CUDA(cudaStreamSynchronize(ctx->stream));
+    }
+    f.pending.reset();
+    return SLAMGPU_OK;
+}
+
 } // namespace
 
 extern "C" {
@@ -272,41 +359,22 @@ int slamgpu_frame_upload(slamgpu_ctx* ctx, int frame_id, int nkp, const float* x
     SG_CTX(ctx);
     SG_CHECK(nkp >= 0 && nkp < (1 << 26), "keypoint count out of range");
     SG_CHECK(nkp == 0 || (xy != nullptr && desc != nullptr), "null keypoints / descriptors");
+    const size_t n = static_cast<size_t>(nkp);
 
-    std::vector<uint32_t> perm(static_cast<size_t>(nkp));
+    std::vector<uint32_t> perm;
     if (kd_perm) {
-        std::vector<uint8_t> seen(static_cast<size_t>(nkp), 0);
+        perm.resize(n);
+        std::vector<uint8_t> seen(n, 0);
         for (int i = 0; i < nkp; ++i) {
             SG_CHECK(kd_perm[i] < static_cast<uint32_t>(nkp) && !seen[kd_perm[i]], "kd_perm is not a permutation");
             seen[kd_perm[i]] = 1;
             perm[i] = kd_perm[i];
         }
-    } else if (nkp > 0) {
-        SG_TRY(slamgpu_kd_build_host(xy, nkp, perm.data()));
     }
 
-    // a slot that is uploaded again (the tracker's current frame, every frame) keeps its allocation
-    // when it is large enough: cudaFree + cudaMalloc cost more than the upload itself
-    struct Held {   // freed on every early return unless the new frame adopts it
-        void* p = nullptr;
-        ~Held() { if (p) cudaFree(p); }
-    } held;
-    void*& old_blob = held.p;
-    size_t old_bytes = 0;
-    auto it = ctx->frames.find(frame_id);
-    if (it != ctx->frames.end()) {
-        SG_CUDA(cudaStreamSynchronize(ctx->stream));
-        old_blob = it->second.blob;
-        old_bytes = it->second.blob_bytes;
-        it->second.blob = nullptr;
-        ctx->frames.erase(it);
-    }
     FrameDev f;
     f.nkp = nkp;
-    f.perm_host = perm;
-    const size_t n = static_cast<size_t>(nkp);
-
-    // uniform grid over the keypoints' bounding box: 32 px cells (coarser when that would exceed 1 Mi cells)
+    // uniform grid over the keypoints' bounding box: 16 px cells (coarser when that would exceed 1 Mi cells)
     float cell = ctx->grid_cell;
     if (nkp > 0) {
         float x0 = xy[0], x1 = xy[0], y0 = xy[1], y1 = xy[1];
@@ -328,14 +396,32 @@ int slamgpu_frame_upload(slamgpu_ctx* ctx, int frame_id, int nkp, const float* x
         }
         f.inv_cell = 1.0f / cell;
     }
+
+    // a slot that is uploaded again (the tracker's current frame, every frame) keeps its allocation
+    // when it is large enough: cudaFree + cudaMalloc cost more than the upload itself
+    struct Held {   // freed on every early return unless the new frame adopts it
+        void* p = nullptr;
+        ~Held() { if (p) cudaFree(p); }
+    } held;
+    void*& old_blob = held.p;
+    size_t old_bytes = 0;
+    auto it = ctx->frames.find(frame_id);
+    if (it != ctx->frames.end()) {
+        SG_CUDA(cudaStreamSynchronize(ctx->stream));
+        join_frame(it->second);                       // a KD build still running on the old contents
+        old_blob = it->second.blob;
+        old_bytes = it->second.blob_bytes;
+        it->second.blob = nullptr;
+        ctx->frames.erase(it);
+    }
+
+    // device blob: [desc][matched][xy] (uploaded now) [kd_xy][kd_idx][cell_start][cell_items][cell_rec] (the KD
+    // image, uploaded when the tree is built) [proposals] (device only)
     const size_t n_cells = static_cast<size_t>(f.gw) * f.gh;
-    // device blob: [kd_xy][kd_idx][desc][matched][xy][cell_start][cell_items][cell_rec] (uploaded) then [proposals] (device only)
-    const size_t b_kdxy = Carver::padded(n * sizeof(float2)), b_kdidx = Carver::padded(n * sizeof(int32_t)),
-                 b_desc = Carver::padded(n * 32), b_matched = Carver::padded(n), b_xy = Carver::padded(n * sizeof(float2)),
-                 b_cstart = Carver::padded((n_cells + 1) * sizeof(int32_t)), b_citems = Carver::padded(n * sizeof(int32_t)),
-                 b_crec = Carver::padded(n * sizeof(int4)), b_prop = Carver::padded(n * sizeof(unsigned long long));
-    const size_t up = b_kdxy + b_kdidx + b_desc + b_matched + b_xy + b_cstart + b_citems + b_crec;
-    const size_t total = up + b_prop + 256;
+    const size_t b_desc = Carver::padded(n * 32), b_matched = Carver::padded(n), b_xy = Carver::padded(n * sizeof(float2));
+    const size_t now_bytes = b_desc + b_matched + b_xy;
+    const size_t kd_bytes = kd_image_bytes(n, n_cells);
+    const size_t total = now_bytes + kd_bytes + Carver::padded(n * sizeof(unsigned long long)) + 256;
     if (old_blob && old_bytes >= total) {
         f.blob = old_blob;
         f.blob_bytes = old_bytes;
@@ -351,18 +437,20 @@ int slamgpu_frame_upload(slamgpu_ctx* ctx, int frame_id, int nkp, const float* x
         f.blob_bytes = total;
     }
     Carver dv(f.blob);
-    f.kd_xy = dv.take<float2>(n);
-    f.kd_idx = dv.take<int32_t>(n);
     f.desc = dv.take<uint4>(2 * n);
     f.matched = dv.take<uint8_t>(n);
     f.xy = dv.take<float2>(n);
+    f.kd_image = dv.base + dv.off;
+    f.kd_xy = dv.take<float2>(n);
+    f.kd_idx = dv.take<int32_t>(n);
     f.cell_start = dv.take<int32_t>(n_cells + 1);
     f.cell_items = dv.take<int32_t>(n);
     f.cell_rec = dv.take<int4>(n);
     f.proposals = dv.take<unsigned long long>(n);
+    f.kd_image_bytes = kd_bytes;
 
     if (nkp > 0) {
-        int rc = ensure_host_stage(ctx, up + 256);
+        int rc = ensure_host_stage(ctx, std::max(now_bytes, kd_bytes) + 256);
         if (rc != SLAMGPU_OK) {
             cudaFree(f.blob);
             return rc;
@@ -370,17 +458,9 @@ int slamgpu_frame_upload(slamgpu_ctx* ctx, int frame_id, int nkp, const float* x
         // staging is free to overwrite only after earlier copies out of it have completed
         SG_CUDA(cudaStreamSynchronize(ctx->stream));
         Carver hv(ctx->h_stage.ptr);
-        float* h_kdxy = reinterpret_cast<float*>(hv.take<float2>(n));
-        int32_t* h_kdidx = hv.take<int32_t>(n);
         uint8_t* h_desc = reinterpret_cast<uint8_t*>(hv.take<uint4>(2 * n));
         uint8_t* h_matched = hv.take<uint8_t>(n);
         float* h_xy = reinterpret_cast<float*>(hv.take<float2>(n));
-        for (size_t m = 0; m < n; ++m) {
-            const uint32_t k = perm[m];
-            h_kdxy[2 * m] = xy[2 * k];
-            h_kdxy[2 * m + 1] = xy[2 * k + 1];
-            h_kdidx[m] = static_cast<int32_t>(k);
-        }
         std::memcpy(h_desc, desc, n * 32);
         if (matched) {
             for (size_t i = 0; i < n; ++i) h_matched[i] = matched[i] ? 1 : 0;
@@ -388,38 +468,35 @@ int slamgpu_frame_upload(slamgpu_ctx* ctx, int frame_id, int nkp, const float* x
             std::memset(h_matched, 0, n);
         }
         std::memcpy(h_xy, xy, n * sizeof(float2));
-        // counting sort of the KD positions by cell; the device maps coordinates to cells with the
-        // same float expression (proj_kernels.cu: grid_cell), and both are monotone in the coordinate
-        int32_t* h_cstart = hv.take<int32_t>(n_cells + 1);
-        int32_t* h_citems = hv.take<int32_t>(n);
-        std::memset(h_cstart, 0, (n_cells + 1) * sizeof(int32_t));
-        auto cell_of = [&](float x, float y) {
-            int cxi = static_cast<int>(std::floor((x - f.gx0) * f.inv_cell));
-            int cyi = static_cast<int>(std::floor((y - f.gy0) * f.inv_cell));
-            cxi = std::min(std::max(cxi, 0), f.gw - 1);
-            cyi = std::min(std::max(cyi, 0), f.gh - 1);
-            return static_cast<size_t>(cyi) * f.gw + cxi;
-        };
-        for (size_t m = 0; m < n; ++m) h_cstart[cell_of(h_kdxy[2 * m], h_kdxy[2 * m + 1]) + 1]++;
-        for (size_t c = 0; c < n_cells; ++c) h_cstart[c + 1] += h_cstart[c];
-        {
-            std::vector<int32_t> cursor(h_cstart, h_cstart + n_cells);
-            for (size_t m = 0; m < n; ++m) h_citems[cursor[cell_of(h_kdxy[2 * m], h_kdxy[2 * m + 1])]++] = static_cast<int32_t>(m);
-        }
-        // one 16-byte record per grid slot: (x bits, y bits, keypoint index, KD position) -- everything the
-        // candidate test needs in a single load
-        int4* h_crec = hv.take<int4>(n);
-        for (size_t i = 0; i < n; ++i) {
-            const int32_t m = h_citems[i];
-            int32_t xb, yb;
-            std::memcpy(&xb, &h_kdxy[2 * m], 4);
-            std::memcpy(&yb, &h_kdxy[2 * m + 1], 4);
-            h_crec[i] = make_int4(xb, yb, h_kdidx[m], m);
-        }
-        SG_CUDA(cudaMemcpyAsync(f.blob, ctx->h_stage.ptr, up, cudaMemcpyHostToDevice, ctx->stream));
+        SG_CUDA(cudaMemcpyAsync(f.blob, ctx->h_stage.ptr, now_bytes, cudaMemcpyHostToDevice, ctx->stream));
         SG_CUDA(cudaMemsetAsync(f.proposals, 0xFF, n * sizeof(unsigned long long), ctx->stream));
         // the staging buffer is reused by the next call: wait for the copy out of it
         SG_CUDA(cudaStreamSynchronize(ctx->stream));
+
+        // The KD-tree and everything ordered by it.  With the caller's permutation (or SLAMGPU_KD_ASYNC=0) it is
+        // built here; otherwise on a host thread that the first call needing the tree joins, so that the build
+        // (the largest item of a tracked frame) overlaps whatever the caller does in between -- in the reference
+        // KLT tracking and pose seeding sit between Frame construction and matching (src/Tracker.cpp:66-88).
+        auto pending = std::make_shared<FrameKdPending>();
+        pending->xy.assign(xy, xy + 2 * n);
+        pending->image.resize(kd_bytes);
+        pending->gx0 = f.gx0; pending->gy0 = f.gy0; pending->inv_cell = f.inv_cell; pending->gw = f.gw; pending->gh = f.gh;
+        if (kd_perm) pending->perm = perm;
+        auto work = [](FrameKdPending* k, bool have_perm) {
+            const int nk = static_cast<int>(k->xy.size() / 2);
+            if (!have_perm) {
+                k->perm.resize(static_cast<size_t>(nk));
+                slamgpu_kd_build_host(k->xy.data(), nk, k->perm.data());
+            }
+            build_kd_image(*k);
+        };
+        f.pending = pending;
+        if (kd_perm || !ctx->kd_async) {
+            work(pending.get(), kd_perm != nullptr);
+            SG_TRY(finalize_frame(ctx, f));
+        } else {
+            pending->worker = std::thread(work, pending.get(), false);
+        }
     }
     ctx->frames[frame_id] = std::move(f);
     return SLAMGPU_OK;
@@ -463,6 +540,8 @@ int slamgpu_frame_get_kd_perm(slamgpu_ctx* ctx, int frame_id, uint32_t* out_perm
     auto it = ctx->frames.find(frame_id);
     if (it == ctx->frames.end()) return fail(SLAMGPU_ERR_NOTFOUND, "unknown frame id");
     SG_CHECK(it->second.nkp == 0 || out_perm != nullptr, "null output");
+    SG_CUDA(cudaSetDevice(ctx->device));
+    SG_TRY(finalize_frame(ctx, it->second));
     std::copy(it->second.perm_host.begin(), it->second.perm_host.end(), out_perm);
     return SLAMGPU_OK;
 }
@@ -688,6 +767,7 @@ int slamgpu_track_match(slamgpu_ctx* ctx, int frame_id, int set_id, const float*
     if (f_it == ctx->frames.end()) return fail(SLAMGPU_ERR_NOTFOUND, "unknown frame id");
     auto ps_it = ctx->point_sets.find(set_id);
     if (ps_it == ctx->point_sets.end()) return fail(SLAMGPU_ERR_NOTFOUND, "unknown point set id");
+    SG_TRY(finalize_frame(ctx, f_it->second));        // the KD-tree may still be building on its host thread
     const FrameDev& fd = f_it->second;
     const PointSetDev& ps = ps_it->second;
     for (int i = 0; i < n_matched; ++i)

@@ -230,6 +230,8 @@ int slamgpu_create(int device, slamgpu_ctx** out)
     ctx->n_sm = prop.multiProcessorCount;
     const char* walk = std::getenv("SLAMGPU_PROJ_WALK");
     ctx->proj_walk = walk != nullptr && walk[0] == '1';
+    const char* kda = std::getenv("SLAMGPU_KD_ASYNC");
+    if (kda != nullptr) ctx->kd_async = kda[0] != '0';
     const char* v2 = std::getenv("SLAMGPU_PROJ_V2");
     ctx->proj_v2 = v2 != nullptr && v2[0] == '1';
     const char* gcell = std::getenv("SLAMGPU_GRID_CELL");
@@ -254,6 +256,7 @@ int slamgpu_create(int device, slamgpu_ctx** out)
 
 static void free_frame(FrameDev& f)
 {
+    if (f.pending && f.pending->worker.joinable()) f.pending->worker.join();   // a KD build still running
     if (f.blob) cudaFree(f.blob);
     f = FrameDev();
 }

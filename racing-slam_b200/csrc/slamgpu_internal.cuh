@@ -6,7 +6,9 @@
 #include <cstdint>
 #include <cstdio>
 #include <map>
+#include <memory>
 #include <string>
+#include <thread>
 #include <utility>
 #include <vector>
 
@@ -44,6 +46,16 @@ constexpr int kIdxBits = 22;
 constexpr uint32_t kIdxMask = (1u << kIdxBits) - 1u;
 constexpr uint32_t kKeyNone = 0xFFFFFFFFu;
 
+// The KD-tree of a frame being built on a host thread (slamgpu_frame_upload) until a call needs it.
+struct FrameKdPending {
+    std::thread worker;
+    std::vector<float> xy;            // private copy of the keypoints
+    std::vector<uint32_t> perm;       // the tree as its permutation
+    std::vector<uint8_t> image;       // host image of the KD-ordered device arrays
+    float gx0 = 0.f, gy0 = 0.f, inv_cell = 1.f;
+    int gw = 1, gh = 1;
+};
+
 // Device-resident frame (what match_via_reproject reads from `const Frame&`).
 struct FrameDev {
     int nkp = 0;
@@ -62,6 +74,9 @@ struct FrameDev {
     float gx0 = 0.f, gy0 = 0.f, inv_cell = 1.f;
     int gw = 1, gh = 1;
     std::vector<uint32_t> perm_host;
+    uint8_t* kd_image = nullptr;              // first byte of [kd_xy][kd_idx][cell_start][cell_items][cell_rec]
+    size_t kd_image_bytes = 0;
+    std::shared_ptr<FrameKdPending> pending;  // set while the KD image is not yet resident
 };
 
 // Device-resident map-point set (what match_via_reproject reads from `MapPoint&`).
@@ -121,6 +136,7 @@ struct slamgpu_ctx {
     int proj_lanes = 0;       // SLAMGPU_PROJ_LANES=8|32 overrides the lanes-per-point choice (0 = by size)
     bool proj_v2 = false;     // SLAMGPU_PROJ_V2=1: the previous group kernel (row-by-row candidate loop)
     float grid_cell = 16.0f;  // SLAMGPU_GRID_CELL: keypoint grid cell size in pixels (16: fewest slots per search at radius 15-20)
+    bool kd_async = true;     // SLAMGPU_KD_ASYNC=0: build the KD-tree inside slamgpu_frame_upload instead of on a thread
     bool proj_walk = false;   // SLAMGPU_PROJ_WALK=1: use the thread-per-point KD-walk kernel
     int bf_engine = 0;        // SLAMGPU_BF_ENGINE=int|tc overrides the brute-force engine choice (0 = by size, 1 = int, 2 = tc)
     int tc_variant = 0;       // SLAMGPU_TC_VARIANT: debug switches of the tensor-core scan
