@@ -148,7 +148,13 @@ typedef struct slamgpu_proj_params {
  *   kd_perm  the KD-tree as its permutation: perm[(s+e)/2] is the node of range [s,e)
  *            (src/KDTree.cpp:18-43).  Pass NULL to have the library build it with the same
  *            std::nth_element call; pass your own when the host's libstdc++ must decide ties.
- *   matched  [nkp] bytes, non-zero = keypoint already has a map point; NULL = none matched. */
+ *   matched  [nkp] bytes, non-zero = keypoint already has a map point; NULL = none matched.
+ * The call returns once keypoints, descriptors and flags are resident (the arrays may be reused).  When the
+ * library builds the tree itself it does so on a host thread of its own and the first call that reads the tree
+ * (any match_projection / track_match / get_kd_perm on this frame) waits for it: upload a frame as soon as its
+ * keypoints exist and the build overlaps whatever comes before matching.  SLAMGPU_KD_ASYNC=0 builds it inside
+ * the call; SLAMGPU_KD_THREADS (default 4) is the number of host threads one build forks.
+ * Uploading to a frame_id that is in use replaces it (and reuses its device allocation when large enough). */
 SLAMGPU_API int slamgpu_frame_upload(slamgpu_ctx* ctx, int frame_id, int nkp, const float* xy, const uint8_t* desc,
                          const uint32_t* kd_perm, const uint8_t* matched);
 SLAMGPU_API int slamgpu_frame_set_matched(slamgpu_ctx* ctx, int frame_id, const uint8_t* matched);

@@ -163,3 +163,31 @@ def test_mirror_track_equals_the_reference_call_sequence(ctx, oracle, pkg):
            [(idx_b[id(x.point)], x.keypoint_index) for x in want_map]
     assert len(kf_m) > 5 and len(map_m) > 20
     assert frame_a.num_map_matches() == frame_b.num_map_matches()
+
+
+def test_kd_build_on_the_library_thread_equals_the_inline_build(oracle, pkg, monkeypatch):
+    """slamgpu_frame_upload hands the KD build to a host thread (default) or does it inline
+    (SLAMGPU_KD_ASYNC=0): same permutation as the oracle, same matches, also when the frame is replaced
+    or released while its build is still running."""
+    sc = pkg.synthetic.projection_scene(8000, 8000, 61, cam=pkg.synthetic.HD1080)
+    p = _params(pkg, pkg.synthetic.HD1080)
+    perm = oracle.kd_build(sc.kp_xy)
+    results = []
+    for mode in ("1", "0"):
+        monkeypatch.setenv("SLAMGPU_KD_ASYNC", mode)
+        with pkg.Context(0) as c:
+            c.points_upload(1, sc.pos, sc.normal, sc.range, sc.obs_offset, sc.obs_desc)
+            for _ in range(3):                                    # replace the slot while a build may be in flight
+                c.frame_upload(1, sc.kp_xy[::-1].copy(), sc.kp_desc, None, None)
+            c.frame_upload(1, sc.kp_xy, sc.kp_desc, None, sc.kp_matched)
+            c.frame_set_matched(1, sc.kp_matched)                  # does not need the tree
+            results.append(c.match_projection(1, 1, 8000, sc.pose, p, sc.skip, None))
+            assert np.array_equal(c.frame_kd_perm(1, 8000), perm)
+            c.frame_upload(2, sc.kp_xy, sc.kp_desc, None, None)
+            c.frame_release(2)                                     # released before anything joined the build
+            c.frame_upload(3, sc.kp_xy, sc.kp_desc, None, None)    # left for the context's destructor to join
+    ref = oracle.match_projection(sc.kp_xy, sc.kp_desc, perm, sc.kp_matched, sc.pos, sc.normal, sc.range,
+                                  sc.obs_offset, sc.obs_desc, sc.skip, None, sc.pose, _oparams(oracle, p),
+                                  want_stats=False)
+    for op, od in results:
+        assert np.array_equal(op, ref.point) and np.array_equal(od, ref.dist)
