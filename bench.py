@@ -709,8 +709,9 @@ def bow_measurements(ctx, pkg, torch, stream, peaks):
     out["transform_4M_descriptors_device"] = {
         "ms": ms, "descriptors_per_s": n_big / (ms * 1e-3), "algorithmic_bytes_per_descriptor": bytes_per_desc,
         "gb_s_algorithmic": n_big * bytes_per_desc / (ms * 1e-3) / 1e9,
-        "hbm_frac": n_big * bytes_per_desc / (ms * 1e-3) / 1e9 / peaks["hbm_gbs"],
-        "note": "the tree (49 MB with its node records) stays in the 126 MB L2; the bound is L2 -> SM gathers of 32-byte rows",
+        "x_hbm_peak": n_big * bytes_per_desc / (ms * 1e-3) / 1e9 / peaks["hbm_gbs"],
+        "note": "the tree (49 MB with its node records) stays in the 126 MB L2, so the algorithmic bytes are served by L2 "
+                "and may exceed the HBM figure; ncu: issue slots 56 %, L1/TEX 51 % busy (profiles/r01_ncu_full_voc_transform_1M.txt)",
         "cpu_port_descriptors_per_s": sample / t_cpu, "cpu_port_cores": os.cpu_count(),
         "identical_to_oracle_on_sample": bool(np.array_equal(dword[:sample].cpu().numpy(), ow))}
     del dq, dword

@@ -99,7 +99,7 @@ struct PointSetDev {
 // descent is one contiguous read), rec[c] = (first child position, child count, word id) of that node.
 struct VocabDev {
     int n_nodes = 0, n_children = 0, n_words = 0;
-    int root_begin = 0, root_count = 0;
+    int root_begin = 0, root_count = 0, max_children = 0;
     void* blob = nullptr;
     int4* rec = nullptr;          // [n_children] (child_begin, n_children, word_id, 0)
     uint4* cdesc = nullptr;       // [n_children * 2]

@@ -58,7 +58,7 @@ int slamgpu_vocab_upload(slamgpu_ctx* ctx, int vocab_id, int n_nodes, const int3
     SG_CHECK(nc < (1 << 30), "vocabulary too large");
     // every node except the root is the child of exactly one node (a tree)
     std::vector<uint8_t> seen(static_cast<size_t>(n_nodes), 0);
-    int n_words = 0;
+    int n_words = 0, max_children = 0;
     for (int c = 0; c < nc; ++c) {
         const int id = child_ids[c];
         SG_CHECK(id > 0 && id < n_nodes && !seen[id], "child_ids is not a tree over the nodes");
@@ -66,6 +66,7 @@ int slamgpu_vocab_upload(slamgpu_ctx* ctx, int vocab_id, int n_nodes, const int3
     }
     for (int i = 0; i < n_nodes; ++i) {
         SG_CHECK(child_offset[i + 1] - child_offset[i] < (1 << 20), "too many children in one node");
+        max_children = std::max(max_children, child_offset[i + 1] - child_offset[i]);
         if (child_offset[i + 1] == child_offset[i] && i != 0) {
             SG_CHECK(word_id[i] >= 0, "negative word id at a leaf");
             n_words = std::max(n_words, word_id[i] + 1);
@@ -84,6 +85,7 @@ int slamgpu_vocab_upload(slamgpu_ctx* ctx, int vocab_id, int n_nodes, const int3
     v.n_words = n_words;
     v.root_begin = 0;
     v.root_count = child_offset[1] - child_offset[0];
+    v.max_children = max_children;
     const size_t C = static_cast<size_t>(nc), W = static_cast<size_t>(n_words);
     const size_t b_rec = Carver::padded(C * sizeof(int4)), b_desc = Carver::padded(C * 32),
                  b_w = Carver::padded(C * sizeof(double)), b_ww = Carver::padded(W * sizeof(double));

@@ -30,10 +30,12 @@ __device__ __forceinline__ int hamming256(const uint4& a0, const uint4& a1, cons
            __popc(a1.x ^ b1.x) + __popc(a1.y ^ b1.y) + __popc(a1.z ^ b1.z) + __popc(a1.w ^ b1.w);
 }
 
-// One group of LANES lanes per descriptor.  State = the child-array position of the current node; one
-// level = rec[position] -> the node's children, contiguous in cdesc, one child per lane -> packed key
-// (distance << 20 | child order) minimum over the group = the reference's "first strictly smaller".
-template <int LANES>
+// One group of W lanes per descriptor, 32 / W groups per warp (W = 10 for the usual k = 10: three
+// descriptors per warp, 30 of 32 lanes busy; a power-of-two group of 16 would leave 6 of every 16 idle).
+// State = the child-array position of the current node; one level = rec[position] -> the node's children,
+// contiguous in cdesc, one child per lane -> packed key (distance << 20 | child order), minimum over the
+// group = the reference's "first strictly smaller".
+template <int W>
 __global__ void __launch_bounds__(kVocThreads) voc_transform_kernel(const int4* __restrict__ rec,
                                                                     const uint4* __restrict__ cdesc,
                                                                     const double* __restrict__ cweight, int root_begin,
@@ -41,21 +43,33 @@ __global__ void __launch_bounds__(kVocThreads) voc_transform_kernel(const int4* 
                                                                     int32_t* __restrict__ out_word,
                                                                     double* __restrict__ out_weight)
 {
-    const int lane = threadIdx.x % LANES;
-    const unsigned gmask = LANES == 32 ? 0xFFFFFFFFu : (((1u << LANES) - 1u) << ((threadIdx.x & 31) / LANES * LANES));
-    const int i = blockIdx.x * (kVocThreads / LANES) + threadIdx.x / LANES;
+    constexpr int G = 32 / W;                                    // groups per warp
+    const int wl = threadIdx.x & 31;
+    const int g = wl / W;
+    if (g >= G) return;                                          // the warp's spare lanes (32 - G * W)
+    const int lane = wl - g * W;
+    const unsigned gmask = (W == 32 ? 0xFFFFFFFFu : ((1u << W) - 1u)) << (g * W);
+    const int warp = blockIdx.x * (kVocThreads / 32) + (threadIdx.x >> 5);
+    const int i = warp * G + g;
     if (i >= n) return;
     const uint4 q0 = __ldg(&desc[2 * static_cast<size_t>(i)]), q1 = __ldg(&desc[2 * static_cast<size_t>(i) + 1]);
     int begin = root_begin, count = root_count, pos = -1, word = -1;
     while (count > 0) {
         unsigned best = 0xFFFFFFFFu;
-        for (int c = lane; c < count; c += LANES) {                 // TemplatedVocabulary.h:1237-1247
+        for (int c = lane; c < count; c += W) {                  // TemplatedVocabulary.h:1237-1247
             const uint4 b0 = __ldg(&cdesc[2 * static_cast<size_t>(begin + c)]);
             const uint4 b1 = __ldg(&cdesc[2 * static_cast<size_t>(begin + c) + 1]);
             const unsigned key = (static_cast<unsigned>(hamming256(q0, q1, b0, b1)) << 20) | static_cast<unsigned>(c);
             best = min(best, key);
         }
-        best = __reduce_min_sync(gmask, best);
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) {                 // minimum into the group's first lane
+            if (off < W) {
+                const unsigned o = __shfl_down_sync(gmask, best, off);
+                if (lane + off < W) best = min(best, o);
+            }
+        }
+        best = __shfl_sync(gmask, best, g * W);
         pos = begin + static_cast<int>(best & 0xFFFFFu);
         const int4 r = __ldg(&rec[pos]);
         begin = r.x;
@@ -176,14 +190,18 @@ int voc_launch_transform(slamgpu_ctx* ctx, const VocabDev& v, const uint8_t* d_d
 {
     if (n <= 0) return SLAMGPU_OK;
     ProfScope prof(ctx, SLAMGPU_KERNEL_VOC_TRANSFORM);
-    // 16 lanes cover the usual k = 10 in one pass; narrow trees take 4 lanes so that more descriptors are in flight
-    const int widest = v.root_count;   // proxy: DBoW2 trees use one branching factor
-    if (widest <= 4) {
-        voc_transform_kernel<4><<<(n + kVocThreads / 4 - 1) / (kVocThreads / 4), kVocThreads, 0, ctx->stream>>>(
-            v.rec, v.cdesc, v.cweight, v.root_begin, v.root_count, reinterpret_cast<const uint4*>(d_desc), n, d_word, d_weight);
+    // group width by the widest node: 4 / 8 / 10 lanes when one pass covers every child, else 16 lanes looping
+    const int k = v.max_children;
+    const uint4* d4 = reinterpret_cast<const uint4*>(d_desc);
+    auto grid = [&](int w) { const int per_cta = (kVocThreads / 32) * (32 / w); return (n + per_cta - 1) / per_cta; };
+    if (k <= 4) {
+        voc_transform_kernel<4><<<grid(4), kVocThreads, 0, ctx->stream>>>(v.rec, v.cdesc, v.cweight, v.root_begin, v.root_count, d4, n, d_word, d_weight);
+    } else if (k <= 8) {
+        voc_transform_kernel<8><<<grid(8), kVocThreads, 0, ctx->stream>>>(v.rec, v.cdesc, v.cweight, v.root_begin, v.root_count, d4, n, d_word, d_weight);
+    } else if (k <= 10) {
+        voc_transform_kernel<10><<<grid(10), kVocThreads, 0, ctx->stream>>>(v.rec, v.cdesc, v.cweight, v.root_begin, v.root_count, d4, n, d_word, d_weight);
     } else {
-        voc_transform_kernel<16><<<(n + kVocThreads / 16 - 1) / (kVocThreads / 16), kVocThreads, 0, ctx->stream>>>(
-            v.rec, v.cdesc, v.cweight, v.root_begin, v.root_count, reinterpret_cast<const uint4*>(d_desc), n, d_word, d_weight);
+        voc_transform_kernel<16><<<grid(16), kVocThreads, 0, ctx->stream>>>(v.rec, v.cdesc, v.cweight, v.root_begin, v.root_count, d4, n, d_word, d_weight);
     }
     ctx->launches++;
     SG_CUDA(cudaGetLastError());
