@@ -636,11 +636,14 @@ int slamgpu_points_append(slamgpu_ctx* ctx, int set_id, int n_new, const float* 
     PointSetDev& p = it->second;
     SG_CHECK(static_cast<int64_t>(p.n) + n_new <= (1 << 30) && p.n_obs + o_new <= 0x7FFFFFFF, "point set too large");
 
-    // grow geometrically: new allocation, device-to-device copies of the live part, old one freed
+    // grow geometrically: new allocation, device-to-device copies of the live part, old one freed.  A set that
+    // is appended to is a map: its first growth reserves room for 256k points / 1M observations (45 MB of the
+    // 180 GB; SLAMGPU_MAP_RESERVE = points), so a tracking run of BASELINE C3's size never reallocates (each cudaMalloc + cudaFree pair
+    // stalls the frame for milliseconds).
     if (p.n + n_new > p.cap_n || p.n_obs + o_new > p.cap_obs) {
         PointSetDev g = p;
-        const int cap_n = std::max(p.n + n_new, 2 * p.cap_n);
-        const int64_t cap_obs = std::max<int64_t>(p.n_obs + o_new, 2 * p.cap_obs);
+        const int cap_n = std::max({p.n + n_new, 2 * p.cap_n, ctx->map_reserve});
+        const int64_t cap_obs = std::max<int64_t>({p.n_obs + o_new, 2 * p.cap_obs, int64_t(4) * ctx->map_reserve});
         SG_TRY(alloc_points(g, cap_n, cap_obs));
         const size_t N = static_cast<size_t>(p.n), O = static_cast<size_t>(p.n_obs);
         cudaError_t e = cudaSuccess;

@@ -48,10 +48,21 @@ __device__ __forceinline__ int hamming256(const uint4& a0, const uint4& a1, cons
            __popc(a1.x ^ b1.x) + __popc(a1.y ^ b1.y) + __popc(a1.z ^ b1.z) + __popc(a1.w ^ b1.w);
 }
 
+// A point that passed P0-P4, as the gate pass of the two-pass form hands it to the search pass.
+struct ProjSurvivor {
+    float u, w;
+    int v, o_begin;
+    int o_end, cx0, cx1, cy0;
+    int n_rows, pad0, pad1, pad2;
+};
+static_assert(sizeof(ProjSurvivor) == 48, "three 16-byte loads");
+
 struct ProjKernelArgs {
     ProjCommonArgs c;
     ProjFrameArgs inline_frame;       // used when frames == nullptr (single-frame call: no upload)
     const ProjFrameArgs* frames;      // device array for the batched form
+    ProjSurvivor* surv = nullptr;     // two-pass form: [n_frames][n_visit] survivors and their count per frame
+    int* surv_count = nullptr;
 };
 
 __global__ void __launch_bounds__(kProjThreads) proj_match_kernel(const ProjKernelArgs a)
@@ -360,12 +371,159 @@ __global__ void __launch_bounds__(kGroupThreads) proj_match_warp_kernel(const Pr
 // ---------------------------------------------------------------------------------------------
 constexpr int kObsStaged = 8;     // observation descriptors of a point parked in shared memory (the rest: global)
 
-template <int LANES>
+// The search half of K4 for one point and its group of LANES lanes (P5-P7): the point's staged observation
+// descriptors go to shared memory, the cell rows [rb, re) (one row per lane) are flattened over the lanes, every
+// slot is tested, the group's best candidate proposes.  Shared by the fused kernel below and by the two-pass
+// form (proj_search_kernel).
+template <int LANES, bool QUEUE>
+__device__ __forceinline__ void group_search(const ProjFrameArgs& f, const ProjCommonArgs& c, const int lane, const int grp,
+                                             const unsigned gmask, const float u, const float w, const int v,
+                                             const size_t dbg_row, const int o_begin, const int o_end, const int n_staged,
+                                             const int cx0, const int cx1, const int cy0, const int n_rows, int rb, int re,
+                                             const uint4* stage, uint4 (*s_obs)[2 * kObsStaged], int2 (*s_queue)[2 * LANES])
+{
+    constexpr int STAGE_REGS = (2 * kObsStaged + LANES - 1) / LANES;
+    if (c.stats) {   // diagnostic only: keypoints within 1e-4 px of the search radius
+        unsigned long long cnt = 0;
+        for (int k = lane; k < f.nkp; k += LANES) {
+            const float2 p = f.xy[k];
+            const float dx = __fsub_rn(p.x, u), dy = __fsub_rn(p.y, w);
+            const float d = __fsqrt_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)));
+            if (fabsf(__fsub_rn(d, c.radius)) < 1e-4f) cnt++;
+        }
+        if (cnt) atomicAdd(&c.stats[1], cnt);
+    }
+
+#pragma unroll
+    for (int r = 0; r < STAGE_REGS; ++r) {
+        const int k = lane + r * LANES;
+        if (k < 2 * kObsStaged) s_obs[grp][k] = stage[r];
+    }
+    __syncwarp(gmask);
+
+    // P5 + P6: candidates from the grid, the rows flattened over the lanes
+    int best = c.thr;                                            // lane-local best: accept d < thr
+    int best_m = -1;
+    // P6 for one candidate: every observation descriptor of the point against the keypoint's
+    auto score = [&](const int kp, const int m) {
+        const unsigned kp_matched = f.matched[kp];               // round trip 5: flag and descriptor together
+        const uint4 a0 = __ldg(&f.desc[2 * kp]), a1 = __ldg(&f.desc[2 * kp + 1]);
+        if (!c.replace && kp_matched) return;                    // src/MapMatcher.cpp:81
+        int dmin = 1 << 20;
+        for (int o = 0; o < n_staged; ++o)                       // :86
+            dmin = min(dmin, hamming256(a0, a1, s_obs[grp][2 * o], s_obs[grp][2 * o + 1]));
+        for (int o = o_begin + kObsStaged; o < o_end; ++o) {
+            const uint4 b0 = __ldg(&c.obs_desc[2 * static_cast<size_t>(o)]);
+            const uint4 b1 = __ldg(&c.obs_desc[2 * static_cast<size_t>(o) + 1]);
+            dmin = min(dmin, hamming256(a0, a1, b0, b1));
+        }
+        if (dmin < best) {
+            best = dmin;
+            best_m = m;
+        } else if (dmin == best && best_m >= 0) {                // tie inside one lane: earlier visit wins
+            if (kd_visit_key(f.kd_xy, f.nkp, m, u, w) < kd_visit_key(f.kd_xy, f.nkp, best_m, u, w)) best_m = m;
+        }
+    };
+    // QUEUE: the slots that pass the radius test (about 4 in 10 of the box) are packed into a per-group queue
+    // and scored LANES at a time, so that the Hamming loop runs with full groups instead of 3 lanes in 8.
+    // The order candidates are scored in does not matter: ties are settled by the KD visit key.
+    const int gshift = (threadIdx.x & 31) / LANES * LANES;
+    int qn = 0;                                                  // queue fill, the same in every lane of the group
+    for (int row0 = 0; row0 < n_rows; row0 += LANES) {
+        if (row0 > 0) {                                          // more rows than lanes (huge radius): next batch
+            rb = re = 0;
+            if (row0 + lane < n_rows) {
+                rb = f.cell_start[(cy0 + row0 + lane) * f.gw + cx0];
+                re = f.cell_start[(cy0 + row0 + lane) * f.gw + cx1 + 1];
+            }
+        }
+        const int len = re - rb;
+        int incl = len;                                          // inclusive prefix sum of the row lengths
+#pragma unroll
+        for (int d = 1; d < LANES; d <<= 1) {
+            const int t = __shfl_up_sync(gmask, incl, d, LANES);
+            if (lane >= d) incl += t;
+        }
+        const int total = __shfl_sync(gmask, incl, LANES - 1, LANES);
+        const int excl = incl - len;                             // lanes past the last row hold `total`
+        const int delta = rb - excl;
+        for (int base = 0; base < total; base += LANES) {
+            const int t = base + lane;
+            // which row does flat index t fall in?  The last row whose exclusive prefix is <= t (an empty row
+            // shares its prefix with the next one, which then wins): binary search over the lanes' prefixes
+            int r = 0;
+#pragma unroll
+            for (int step = LANES / 2; step > 0; step >>= 1) {
+                const int e = __shfl_sync(gmask, excl, r + step, LANES);
+                if (t >= e) r += step;
+            }
+            const int slot = t + __shfl_sync(gmask, delta, r, LANES);
+            bool pass = false;
+            int kp = 0, m = 0;
+            if (t < total) {
+                // round trip 4.  (Prefetching the next batch's records here was measured slower: 80 registers
+                // instead of 72 cost more occupancy than the overlap gained; profiles/r01_proj_variants_v3b.txt.)
+                const int4 rec = __ldg(&f.cell_rec[slot]);
+                const float dx = __fsub_rn(__int_as_float(rec.x), u);                // src/KDTree.cpp:61
+                const float dy = __fsub_rn(__int_as_float(rec.y), w);                // :62
+                const float d2 = __fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy));    // :63
+                pass = d2 <= c.r2;                               // :65
+                kp = rec.z;
+                m = rec.w;
+            }
+            if (!QUEUE) {
+                if (pass) score(kp, m);
+                continue;
+            }
+            const unsigned hits = (__ballot_sync(gmask, pass) >> gshift) & (LANES == 32 ? 0xFFFFFFFFu : ((1u << LANES) - 1u));
+            if (pass) s_queue[grp][qn + __popc(hits & ((1u << lane) - 1u))] = make_int2(kp, m);
+            qn += __popc(hits);
+            __syncwarp(gmask);
+            if (qn >= LANES) {                                   // a full group of candidates: score them
+                const int2 cand = s_queue[grp][lane];
+                const int2 left = s_queue[grp][LANES + lane];    // read before anyone overwrites
+                __syncwarp(gmask);
+                qn -= LANES;
+                if (lane < qn) s_queue[grp][lane] = left;
+                score(cand.x, cand.y);
+                __syncwarp(gmask);
+            }
+        }
+    }
+    if (QUEUE && lane < qn) {
+        const int2 cand = s_queue[grp][lane];
+        score(cand.x, cand.y);
+    }
+    // group winner: minimum distance, then earliest KD visit
+    const int wbest = __reduce_min_sync(gmask, best_m >= 0 ? best : (1 << 20));
+    if (wbest >= c.thr) return;                                  // nothing under max_descriptor_distance
+    const bool tied = best_m >= 0 && best == wbest;
+    const unsigned ballot = __ballot_sync(gmask, tied);
+    int win_lane = __ffs(ballot) - 1;                            // lane index within the warp
+    if (__popc(ballot) > 1) {
+        unsigned long long key = tied ? kd_visit_key(f.kd_xy, f.nkp, best_m, u, w) : ~0ull;
+        const unsigned hi = __reduce_min_sync(gmask, static_cast<unsigned>(key >> 32));
+        const unsigned lo = __reduce_min_sync(gmask, (key >> 32) == hi ? static_cast<unsigned>(key) : 0xFFFFFFFFu);
+        const unsigned long long wkey = (static_cast<unsigned long long>(hi) << 32) | lo;
+        win_lane = __ffs(__ballot_sync(gmask, tied && key == wkey)) - 1;
+    }
+    if (static_cast<int>(threadIdx.x & 31) == win_lane) {
+        const int best_kp = f.kd_idx[best_m];
+        // P7: first point in visit order attaining the minimum wins (src/MapMatcher.cpp:95-97)
+        const unsigned long long key = (static_cast<unsigned long long>(wbest) << 32) | static_cast<unsigned>(v);
+        atomicMin(&f.proposals[best_kp], key);
+        if (c.dbg_kp) c.dbg_kp[dbg_row] = best_kp;
+        if (c.dbg_d) c.dbg_d[dbg_row] = wbest;
+    }
+}
+
+template <int LANES, bool QUEUE>
 __global__ void __launch_bounds__(kGroupThreads) proj_match_group_kernel(const ProjKernelArgs a)
 {
     constexpr int GROUPS = kGroupThreads / LANES;
     constexpr int STAGE_REGS = (2 * kObsStaged + LANES - 1) / LANES;
     __shared__ uint4 s_obs[GROUPS][2 * kObsStaged];
+    __shared__ int2 s_queue[QUEUE ? GROUPS : 1][2 * LANES];
     const ProjFrameArgs& f = a.frames ? a.frames[blockIdx.y] : a.inline_frame;
     const ProjCommonArgs& c = a.c;
     const int lane = threadIdx.x % LANES;
@@ -436,103 +594,138 @@ __global__ void __launch_bounds__(kGroupThreads) proj_match_group_kernel(const P
     const float distance = norm3(ray);
     if (distance < __fdiv_rn(nearest, c.nearer) || distance > __fmul_rn(furthest, c.further)) return;  // P4
 
-    if (c.stats) {   // diagnostic only: keypoints within 1e-4 px of the search radius
-        unsigned long long cnt = 0;
-        for (int k = lane; k < f.nkp; k += LANES) {
-            const float2 p = f.xy[k];
-            const float dx = __fsub_rn(p.x, u), dy = __fsub_rn(p.y, w);
-            const float d = __fsqrt_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)));
-            if (fabsf(__fsub_rn(d, c.radius)) < 1e-4f) cnt++;
-        }
-        if (cnt) atomicAdd(&c.stats[1], cnt);
-    }
+    group_search<LANES, QUEUE>(f, c, lane, grp, gmask, u, w, v, dbg_row, o_begin, o_end, n_staged, cx0, cx1, cy0, n_rows,
+                               rb, re, stage, s_obs, s_queue);
+}
 
+// ---------------------------------------------------------------------------------------------
+// K4, two-pass form (large visit lists).  In the fused kernel every lane of a group repeats the point's
+// projection and gates (IEEE divisions and square roots are long instruction sequences): one warp
+// instruction serves 4 points, and on a 200k-point map the kernel issues on 56 % of the cycles
+// (profiles/r01_ncu_full_proj_match_group_200k.txt).  Here the gate pass runs one THREAD per point (one warp
+// instruction serves 32 points, the point arrays are read coalesced) and compacts the survivors; the search
+// pass gives every survivor a group of lanes and runs the same group_search.  Same arithmetic, same
+// candidates, same tie rule; the visit rank travels with the survivor, so the order of the compaction cannot
+// change a result.  Small visit lists stay on the fused kernel (one launch less, shorter dependent chain).
+// ---------------------------------------------------------------------------------------------
+constexpr int kGateThreads = 256;
+
+__global__ void __launch_bounds__(kGateThreads) proj_gate_kernel(const ProjKernelArgs a)
+{
+    const ProjFrameArgs& f = a.frames ? a.frames[blockIdx.y] : a.inline_frame;
+    const ProjCommonArgs& c = a.c;
+    const int v = blockIdx.x * kGateThreads + threadIdx.x;
+    bool alive = v < c.n_visit;
+    int pi = -1;
+    if (alive) {
+        pi = c.order ? c.order[v] : v;
+        alive = pi >= 0;                                         // match_for_fuse nullptr, src/MapMatcher.cpp:119-121
+    }
+    ProjSurvivor s;
+    s.u = s.w = 0.0f;
+    s.v = v;
+    s.o_begin = s.o_end = s.cx0 = s.cx1 = s.cy0 = s.n_rows = s.pad0 = s.pad1 = s.pad2 = 0;
+    if (alive) {
+        const unsigned skipped = f.skip ? f.skip[pi] : 0u;
+        const float X[3] = {c.pos[3 * pi], c.pos[3 * pi + 1], c.pos[3 * pi + 2]};
+        const float nx = c.normal[3 * pi], ny = c.normal[3 * pi + 1], nz = c.normal[3 * pi + 2];
+        const float nearest = c.range[2 * pi], furthest = c.range[2 * pi + 1];
+        s.o_begin = c.obs_offset[pi];
+        s.o_end = c.obs_offset[pi + 1];
+        alive = !skipped;                                        // :53 is_matched(point) / :169 !is_observed_by
+        float h[3];
+#pragma unroll
+        for (int i = 0; i < 3; ++i) {                            // P1, same order as the kernels above
+            h[i] = sum3(__fmul_rn(f.M[4 * i], X[0]), __fmul_rn(f.M[4 * i + 1], X[1]), __fmul_rn(f.M[4 * i + 2], X[2]));
+            h[i] = __fadd_rn(h[i], f.M[4 * i + 3]);
+        }
+        float u, w;
+        if (h[2] < 0.0f) {
+            u = -1.0f; w = -1.0f;
+        } else {
+            u = __fdiv_rn(h[0], h[2]);
+            w = __fdiv_rn(h[1], h[2]);
+        }
+        s.u = u;
+        s.w = w;
+        if (alive && c.dbg_uv) {
+            const size_t dbg_row = static_cast<size_t>(blockIdx.y) * c.n_visit + v;
+            c.dbg_uv[2 * dbg_row] = u;
+            c.dbg_uv[2 * dbg_row + 1] = w;
+        }
+        alive = alive && (u >= 0.0f && u < c.width_f && w >= 0.0f && w < c.height_f);      // P2
+        if (alive) {
+            if (c.stats) {
+                if (fabsf(u) < 1e-4f || fabsf(__fsub_rn(u, c.width_f)) < 1e-4f || fabsf(w) < 1e-4f ||
+                    fabsf(__fsub_rn(w, c.height_f)) < 1e-4f)
+                    atomicAdd(&c.stats[0], 1ull);
+            }
+            const float ray[3] = {__fsub_rn(X[0], f.C[0]), __fsub_rn(X[1], f.C[1]), __fsub_rn(X[2], f.C[2])};
+            float rn[3];
+            normalized3(ray, rn);
+            if (sum3(__fmul_rn(nx, rn[0]), __fmul_rn(ny, rn[1]), __fmul_rn(nz, rn[2])) < c.min_cos) alive = false;   // P3
+            const float distance = norm3(ray);
+            if (distance < __fdiv_rn(nearest, c.nearer) || distance > __fmul_rn(furthest, c.further)) alive = false;  // P4
+            const float pad = c.radius + 1.0f;                   // conservative box; the exact test is d2 <= r2
+            s.cx0 = grid_cell(u - pad, f.gx0, f.inv_cell, f.gw);
+            s.cx1 = grid_cell(u + pad, f.gx0, f.inv_cell, f.gw);
+            s.cy0 = grid_cell(w - pad, f.gy0, f.inv_cell, f.gh);
+            s.n_rows = grid_cell(w + pad, f.gy0, f.inv_cell, f.gh) - s.cy0 + 1;
+        }
+    }
+    // warp-aggregated append to this frame's survivor list
+    const unsigned live = __ballot_sync(0xFFFFFFFFu, alive);
+    if (live == 0u) return;
+    const int lane = threadIdx.x & 31;
+    const int leader = __ffs(live) - 1;
+    int base = 0;
+    if (lane == leader) base = atomicAdd(&a.surv_count[blockIdx.y], __popc(live));
+    base = __shfl_sync(0xFFFFFFFFu, base, leader);
+    if (alive) {
+        ProjSurvivor* dst = a.surv + static_cast<size_t>(blockIdx.y) * c.n_visit + base + __popc(live & ((1u << lane) - 1u));
+        uint4* d4 = reinterpret_cast<uint4*>(dst);
+        const uint4* s4 = reinterpret_cast<const uint4*>(&s);
+        d4[0] = s4[0];
+        d4[1] = s4[1];
+        d4[2] = s4[2];
+    }
+}
+
+template <int LANES, bool QUEUE>
+__global__ void __launch_bounds__(kGroupThreads) proj_search_kernel(const ProjKernelArgs a)
+{
+    constexpr int GROUPS = kGroupThreads / LANES;
+    constexpr int STAGE_REGS = (2 * kObsStaged + LANES - 1) / LANES;
+    __shared__ uint4 s_obs[GROUPS][2 * kObsStaged];
+    __shared__ int2 s_queue[QUEUE ? GROUPS : 1][2 * LANES];
+    const ProjFrameArgs& f = a.frames ? a.frames[blockIdx.y] : a.inline_frame;
+    const ProjCommonArgs& c = a.c;
+    const int lane = threadIdx.x % LANES;
+    const int grp = threadIdx.x / LANES;
+    const unsigned gmask = LANES == 32 ? 0xFFFFFFFFu : (((1u << LANES) - 1u) << ((threadIdx.x & 31) / LANES * LANES));
+    const int idx = blockIdx.x * GROUPS + grp;
+    if (idx >= a.surv_count[blockIdx.y]) return;
+    const uint4* s4 = reinterpret_cast<const uint4*>(a.surv + static_cast<size_t>(blockIdx.y) * c.n_visit + idx);
+    const uint4 r0 = __ldcg(s4), r1 = __ldcg(s4 + 1), r2 = __ldcg(s4 + 2);
+    const float u = __uint_as_float(r0.x), w = __uint_as_float(r0.y);
+    const int v = static_cast<int>(r0.z), o_begin = static_cast<int>(r0.w), o_end = static_cast<int>(r1.x);
+    const int cx0 = static_cast<int>(r1.y), cx1 = static_cast<int>(r1.z), cy0 = static_cast<int>(r1.w);
+    const int n_rows = static_cast<int>(r2.x);
+    const size_t dbg_row = static_cast<size_t>(blockIdx.y) * c.n_visit + v;
+    const int n_staged = min(o_end - o_begin, kObsStaged);
+    uint4 stage[STAGE_REGS];
 #pragma unroll
     for (int r = 0; r < STAGE_REGS; ++r) {
         const int k = lane + r * LANES;
-        if (k < 2 * kObsStaged) s_obs[grp][k] = stage[r];
+        stage[r] = k < 2 * n_staged ? __ldg(&c.obs_desc[2 * static_cast<size_t>(o_begin) + k]) : make_uint4(0, 0, 0, 0);
     }
-    __syncwarp(gmask);
-
-    // P5 + P6: candidates from the grid, the rows flattened over the lanes
-    int best = c.thr;                                            // lane-local best: accept d < thr
-    int best_m = -1;
-    for (int row0 = 0; row0 < n_rows; row0 += LANES) {
-        if (row0 > 0) {                                          // more rows than lanes (huge radius): next batch
-            rb = re = 0;
-            if (row0 + lane < n_rows) {
-                rb = f.cell_start[(cy0 + row0 + lane) * f.gw + cx0];
-                re = f.cell_start[(cy0 + row0 + lane) * f.gw + cx1 + 1];
-            }
-        }
-        const int len = re - rb;
-        int incl = len;                                          // inclusive prefix sum of the row lengths
-#pragma unroll
-        for (int d = 1; d < LANES; d <<= 1) {
-            const int t = __shfl_up_sync(gmask, incl, d, LANES);
-            if (lane >= d) incl += t;
-        }
-        const int total = __shfl_sync(gmask, incl, LANES - 1, LANES);
-        const int excl = incl - len;
-        const int rows_here = min(n_rows - row0, LANES);
-        for (int base = 0; base < total; base += LANES) {
-            const int t = base + lane;
-            int slot = -1;
-            for (int r = 0; r < rows_here; ++r) {                // which row does flat index t fall in?
-                const int e_r = __shfl_sync(gmask, excl, r, LANES);
-                const int l_r = __shfl_sync(gmask, len, r, LANES);
-                const int b_r = __shfl_sync(gmask, rb, r, LANES);
-                if (t >= e_r && t < e_r + l_r) slot = b_r + (t - e_r);
-            }
-            if (slot < 0) continue;
-            // round trip 4.  (Prefetching the next batch's records here was measured slower: 80 registers
-            // instead of 72 cost more occupancy than the overlap gained; profiles/r01_proj_variants_v3b.txt.)
-            const int4 rec = __ldg(&f.cell_rec[slot]);
-            const float dx = __fsub_rn(__int_as_float(rec.x), u);                // src/KDTree.cpp:61
-            const float dy = __fsub_rn(__int_as_float(rec.y), w);                // :62
-            const float d2 = __fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy));    // :63
-            if (!(d2 <= c.r2)) continue;                         // :65
-            const int kp = rec.z, m = rec.w;
-            const unsigned kp_matched = f.matched[kp];           // round trip 5: flag and descriptor together
-            const uint4 a0 = __ldg(&f.desc[2 * kp]), a1 = __ldg(&f.desc[2 * kp + 1]);
-            if (!c.replace && kp_matched) continue;              // src/MapMatcher.cpp:81
-            int dmin = 1 << 20;
-            for (int o = 0; o < n_staged; ++o)                   // :86
-                dmin = min(dmin, hamming256(a0, a1, s_obs[grp][2 * o], s_obs[grp][2 * o + 1]));
-            for (int o = o_begin + kObsStaged; o < o_end; ++o) {
-                const uint4 b0 = __ldg(&c.obs_desc[2 * static_cast<size_t>(o)]);
-                const uint4 b1 = __ldg(&c.obs_desc[2 * static_cast<size_t>(o) + 1]);
-                dmin = min(dmin, hamming256(a0, a1, b0, b1));
-            }
-            if (dmin < best) {
-                best = dmin;
-                best_m = m;
-            } else if (dmin == best && best_m >= 0) {            // tie inside one lane: earlier visit wins
-                if (kd_visit_key(f.kd_xy, f.nkp, m, u, w) < kd_visit_key(f.kd_xy, f.nkp, best_m, u, w)) best_m = m;
-            }
-        }
+    int rb = 0, re = 0;
+    if (lane < n_rows) {
+        rb = f.cell_start[(cy0 + lane) * f.gw + cx0];
+        re = f.cell_start[(cy0 + lane) * f.gw + cx1 + 1];
     }
-    // group winner: minimum distance, then earliest KD visit
-    const int wbest = __reduce_min_sync(gmask, best_m >= 0 ? best : (1 << 20));
-    if (wbest >= c.thr) return;                                  // nothing under max_descriptor_distance
-    const bool tied = best_m >= 0 && best == wbest;
-    const unsigned ballot = __ballot_sync(gmask, tied);
-    int win_lane = __ffs(ballot) - 1;                            // lane index within the warp
-    if (__popc(ballot) > 1) {
-        unsigned long long key = tied ? kd_visit_key(f.kd_xy, f.nkp, best_m, u, w) : ~0ull;
-        const unsigned hi = __reduce_min_sync(gmask, static_cast<unsigned>(key >> 32));
-        const unsigned lo = __reduce_min_sync(gmask, (key >> 32) == hi ? static_cast<unsigned>(key) : 0xFFFFFFFFu);
-        const unsigned long long wkey = (static_cast<unsigned long long>(hi) << 32) | lo;
-        win_lane = __ffs(__ballot_sync(gmask, tied && key == wkey)) - 1;
-    }
-    if (static_cast<int>(threadIdx.x & 31) == win_lane) {
-        const int best_kp = f.kd_idx[best_m];
-        // P7: first point in visit order attaining the minimum wins (src/MapMatcher.cpp:95-97)
-        const unsigned long long key = (static_cast<unsigned long long>(wbest) << 32) | static_cast<unsigned>(v);
-        atomicMin(&f.proposals[best_kp], key);
-        if (c.dbg_kp) c.dbg_kp[dbg_row] = best_kp;
-        if (c.dbg_d) c.dbg_d[dbg_row] = wbest;
-    }
+    group_search<LANES, QUEUE>(f, c, lane, grp, gmask, u, w, v, dbg_row, o_begin, o_end, n_staged, cx0, cx1, cy0, n_rows,
+                               rb, re, stage, s_obs, s_queue);
 }
 
 // Measured and dropped (profiles/r01_proj_variants_v4.txt): a cooperative form in which every lane first
@@ -631,29 +824,52 @@ __global__ void kd_gather_kernel(const float2* xy, const int32_t* perm, int n, f
 } // namespace
 
 // K4 launch: kernel variant by context switches (see the comments on the kernels).
-static void launch_match(slamgpu_ctx* ctx, const ProjKernelArgs& a, int n_visit, int n_frames)
+static int launch_match(slamgpu_ctx* ctx, const ProjKernelArgs& a, int n_visit, int n_frames)
 {
     ProfScope prof(ctx, SLAMGPU_KERNEL_PROJ_MATCH);
     if (ctx->proj_walk) {   // thread-per-point KD walk, kept for A/B checks (SLAMGPU_PROJ_WALK=1)
         const dim3 gp((n_visit + kProjThreads - 1) / kProjThreads, n_frames);
         proj_match_kernel<<<gp, kProjThreads, 0, ctx->stream>>>(a);
+        ctx->launches++;
+        return SLAMGPU_OK;
+    }
+    // 8 lanes per point: as fast as a full warp on C2 (16 us) and 1.8x faster on C4-sized batches; 4 lanes
+    // are no faster on large maps and slower on small ones (tools/time_proj.py,
+    // profiles/r01_proj_variants_v3*.txt); SLAMGPU_PROJ_LANES=32 overrides
+    const int lanes = ctx->proj_lanes ? ctx->proj_lanes : 8;
+    const int per_cta = kGroupThreads / lanes;
+    const dim3 gp((n_visit + per_cta - 1) / per_cta, n_frames);
+    const long long visits = static_cast<long long>(n_visit) * n_frames;
+    const bool two_pass = !ctx->proj_v2 && (ctx->proj_two_pass == 1 || (ctx->proj_two_pass == 0 && visits >= 32768));
+    if (two_pass) {
+        const size_t b_surv = Carver::padded(static_cast<size_t>(visits) * sizeof(ProjSurvivor));
+        SG_TRY(ensure_device_ws(ctx, b_surv + Carver::padded(sizeof(int) * n_frames) + 256));
+        ProjKernelArgs b = a;
+        Carver ws(ctx->d_ws.ptr);
+        b.surv = ws.take<ProjSurvivor>(static_cast<size_t>(visits));
+        b.surv_count = ws.take<int>(n_frames);
+        SG_CUDA(cudaMemsetAsync(b.surv_count, 0, sizeof(int) * n_frames, ctx->stream));
+        const dim3 gg((n_visit + kGateThreads - 1) / kGateThreads, n_frames);
+        proj_gate_kernel<<<gg, kGateThreads, 0, ctx->stream>>>(b);
+        if (lanes == 8 && ctx->proj_queue) proj_search_kernel<8, true><<<gp, kGroupThreads, 0, ctx->stream>>>(b);
+        else if (lanes == 8) proj_search_kernel<8, false><<<gp, kGroupThreads, 0, ctx->stream>>>(b);
+        else if (ctx->proj_queue) proj_search_kernel<32, true><<<gp, kGroupThreads, 0, ctx->stream>>>(b);
+        else proj_search_kernel<32, false><<<gp, kGroupThreads, 0, ctx->stream>>>(b);
+        ctx->launches += 2;
+        return SLAMGPU_OK;
+    }
+    if (ctx->proj_v2) {             // previous form, kept for A/B checks (SLAMGPU_PROJ_V2=1)
+        if (lanes == 8) proj_match_warp_kernel<8><<<gp, kGroupThreads, 0, ctx->stream>>>(a);
+        else proj_match_warp_kernel<32><<<gp, kGroupThreads, 0, ctx->stream>>>(a);
+    } else if (lanes == 8) {
+        if (ctx->proj_queue) proj_match_group_kernel<8, true><<<gp, kGroupThreads, 0, ctx->stream>>>(a);
+        else proj_match_group_kernel<8, false><<<gp, kGroupThreads, 0, ctx->stream>>>(a);
     } else {
-        // 8 lanes per point: as fast as a full warp on C2 (16 us) and 1.8x faster on C4-sized batches; 4 lanes
-        // are no faster on large maps and slower on small ones (tools/time_proj.py,
-        // profiles/r01_proj_variants_v3*.txt); SLAMGPU_PROJ_LANES=32 overrides
-        const int lanes = ctx->proj_lanes ? ctx->proj_lanes : 8;
-        const int per_cta = kGroupThreads / lanes;
-        const dim3 gp((n_visit + per_cta - 1) / per_cta, n_frames);
-        if (ctx->proj_v2) {             // previous form, kept for A/B checks (SLAMGPU_PROJ_V2=1)
-            if (lanes == 8) proj_match_warp_kernel<8><<<gp, kGroupThreads, 0, ctx->stream>>>(a);
-            else proj_match_warp_kernel<32><<<gp, kGroupThreads, 0, ctx->stream>>>(a);
-        } else if (lanes == 8) {
-            proj_match_group_kernel<8><<<gp, kGroupThreads, 0, ctx->stream>>>(a);
-        } else {
-            proj_match_group_kernel<32><<<gp, kGroupThreads, 0, ctx->stream>>>(a);
-        }
+        if (ctx->proj_queue) proj_match_group_kernel<32, true><<<gp, kGroupThreads, 0, ctx->stream>>>(a);
+        else proj_match_group_kernel<32, false><<<gp, kGroupThreads, 0, ctx->stream>>>(a);
     }
     ctx->launches++;
+    return SLAMGPU_OK;
 }
 
 int proj_launch(slamgpu_ctx* ctx, const ProjCommonArgs& common, const ProjFrameArgs* h_frames,
@@ -669,7 +885,7 @@ int proj_launch(slamgpu_ctx* ctx, const ProjCommonArgs& common, const ProjFrameA
         const dim3 gk((max_nkp + 255) / 256, n_frames);
         proj_init_kernel<<<gk, 256, 0, ctx->stream>>>(a);
         ctx->launches++;
-        if (common.n_visit > 0) launch_match(ctx, a, common.n_visit, n_frames);
+        if (common.n_visit > 0) SG_TRY(launch_match(ctx, a, common.n_visit, n_frames));
         proj_emit_kernel<<<gk, 256, 0, ctx->stream>>>(a);
         ctx->launches++;
     }
@@ -703,7 +919,7 @@ int proj_launch_track(slamgpu_ctx* ctx, const ProjCommonArgs& common, const Proj
     a.c.n_visit = n_kf;
     a.inline_frame.out_point = d_out;
     a.inline_frame.out_dist = d_out + nkp;
-    if (n_kf > 0) launch_match(ctx, a, n_kf, 1);
+    if (n_kf > 0) SG_TRY(launch_match(ctx, a, n_kf, 1));
     proj_emit_apply_kernel<<<gk, 256, 0, ctx->stream>>>(a, d_pt_matched, d_kp_matched);
     ctx->launches++;
     // stage 2: match_map -- every point (:107-110); stage 1's matches are already in the masks
@@ -711,7 +927,7 @@ int proj_launch_track(slamgpu_ctx* ctx, const ProjCommonArgs& common, const Proj
     a.c.n_visit = n;
     a.inline_frame.out_point = d_out + 2 * nkp;
     a.inline_frame.out_dist = d_out + 3 * nkp;
-    if (n > 0) launch_match(ctx, a, n, 1);
+    if (n > 0) SG_TRY(launch_match(ctx, a, n, 1));
     proj_emit_apply_kernel<<<gk, 256, 0, ctx->stream>>>(a, d_pt_matched, d_kp_matched);
     ctx->launches++;
     SG_CUDA(cudaGetLastError());

@@ -63,7 +63,9 @@ static int grow(slamgpu_ctx* ctx, Arena& a, size_t bytes, bool host)
         a.ptr = nullptr;
         a.cap = 0;
     }
-    size_t cap = std::max<size_t>(bytes + bytes / 4, size_t(1) << 20);
+    // small arenas double (a growing map asks for a little more on every frame, and cudaMalloc / cudaMallocHost
+    // cost milliseconds); large ones add a quarter
+    size_t cap = std::max<size_t>(bytes < (size_t(64) << 20) ? 2 * bytes : bytes + bytes / 4, size_t(1) << 20);
     cap = (cap + 4095) & ~size_t(4095);
     void* p = nullptr;
     const cudaError_t e = host ? cudaMallocHost(&p, cap) : cudaMalloc(&p, cap);
@@ -230,6 +232,12 @@ int slamgpu_create(int device, slamgpu_ctx** out)
     ctx->n_sm = prop.multiProcessorCount;
     const char* walk = std::getenv("SLAMGPU_PROJ_WALK");
     ctx->proj_walk = walk != nullptr && walk[0] == '1';
+    const char* pq = std::getenv("SLAMGPU_PROJ_QUEUE");
+    if (pq != nullptr) ctx->proj_queue = std::atoi(pq) != 0;
+    const char* tp = std::getenv("SLAMGPU_PROJ_TWOPASS");
+    if (tp != nullptr) ctx->proj_two_pass = std::atoi(tp);
+    const char* mr = std::getenv("SLAMGPU_MAP_RESERVE");
+    if (mr != nullptr) ctx->map_reserve = std::min(std::max(std::atoi(mr), 0), 1 << 28);
     const char* kda = std::getenv("SLAMGPU_KD_ASYNC");
     if (kda != nullptr) ctx->kd_async = kda[0] != '0';
     const char* v2 = std::getenv("SLAMGPU_PROJ_V2");

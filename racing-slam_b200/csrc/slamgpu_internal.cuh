@@ -136,6 +136,9 @@ struct slamgpu_ctx {
     int proj_lanes = 0;       // SLAMGPU_PROJ_LANES=8|32 overrides the lanes-per-point choice (0 = by size)
     bool proj_v2 = false;     // SLAMGPU_PROJ_V2=1: the previous group kernel (row-by-row candidate loop)
     float grid_cell = 16.0f;  // SLAMGPU_GRID_CELL: keypoint grid cell size in pixels (16: fewest slots per search at radius 15-20)
+    bool proj_queue = true;   // SLAMGPU_PROJ_QUEUE=0: score candidates batch by batch instead of through the per-group queue
+    int proj_two_pass = 0;    // SLAMGPU_PROJ_TWOPASS=1|2: force / forbid the gate + search form of K4 (0 = by visit count)
+    int map_reserve = 1 << 18; // SLAMGPU_MAP_RESERVE: points reserved by a point set's first growth (4 observations each)
     bool kd_async = true;     // SLAMGPU_KD_ASYNC=0: build the KD-tree inside slamgpu_frame_upload instead of on a thread
     bool proj_walk = false;   // SLAMGPU_PROJ_WALK=1: use the thread-per-point KD-walk kernel
     int bf_engine = 0;        // SLAMGPU_BF_ENGINE=int|tc overrides the brute-force engine choice (0 = by size, 1 = int, 2 = tc)

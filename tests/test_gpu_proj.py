@@ -257,7 +257,7 @@ def test_mapmatcher_mirror_reads_like_the_reference(ctx, oracle, pkg):
 
 def test_walk_and_warp_kernels_agree_on_tie_heavy_scene(oracle, pkg, monkeypatch):
     """The default group-per-point kernel (flattened grid rows + KD visit keys on ties; 8 or 32 lanes,
-    several grid cell sizes), its predecessor (SLAMGPU_PROJ_V2=1) and the thread-per-point KD-walk
+    several grid cell sizes; fused or as gate + search passes), its predecessor (SLAMGPU_PROJ_V2=1) and the thread-per-point KD-walk
     kernel (SLAMGPU_PROJ_WALK=1) must agree with each other and with the
     oracle where equal Hamming minima make the KD visit order decide (low-entropy descriptors)."""
     cam = dict(fx=300.0, fy=300.0, cx=160.0, cy=120.0, width=320, height=240)
@@ -270,9 +270,13 @@ def test_walk_and_warp_kernels_agree_on_tie_heavy_scene(oracle, pkg, monkeypatch
     ref = oracle.match_projection(sc.kp_xy, sc.kp_desc, perm, sc.kp_matched, sc.pos, sc.normal, sc.range,
                                   sc.obs_offset, sc.obs_desc, sc.skip, None, sc.pose, _oparams(oracle, p))
     results = []
-    for walk, lanes, v2, cell in (("0", "32", "0", "32"), ("0", "8", "0", "32"), ("0", "8", "0", "16"),
-                                  ("0", "8", "0", "12"), ("0", "32", "0", "7"), ("0", "8", "1", "32"),
-                                  ("0", "32", "1", "32"), ("1", "0", "0", "32")):
+    for walk, lanes, v2, cell, two, queue in (
+            ("0", "32", "0", "32", "2", "1"), ("0", "8", "0", "32", "2", "1"), ("0", "8", "0", "16", "2", "1"),
+            ("0", "8", "0", "12", "2", "0"), ("0", "32", "0", "7", "2", "0"), ("0", "8", "1", "32", "2", "1"),
+            ("0", "32", "1", "32", "2", "1"), ("1", "0", "0", "32", "2", "1"), ("0", "8", "0", "16", "1", "1"),
+            ("0", "32", "0", "7", "1", "1"), ("0", "8", "0", "16", "1", "0"), ("0", "8", "0", "16", "0", "1")):
+        monkeypatch.setenv("SLAMGPU_PROJ_TWOPASS", two)      # 1: gate + search passes, 2: fused kernel, 0: by size
+        monkeypatch.setenv("SLAMGPU_PROJ_QUEUE", queue)      # 1: radius survivors packed before scoring
         monkeypatch.setenv("SLAMGPU_PROJ_WALK", walk)
         monkeypatch.setenv("SLAMGPU_PROJ_LANES", lanes)
         monkeypatch.setenv("SLAMGPU_PROJ_V2", v2)

@@ -105,10 +105,19 @@ def test_track_match_argument_errors(ctx, pkg):
     ctx.frame_release(8), ctx.points_release(8)
 
 
-@pytest.mark.parametrize("derive", [False, True])
-def test_points_append_equals_one_full_upload(ctx, oracle, pkg, derive):
+@pytest.mark.parametrize("derive,reserve", [(False, "0"), (True, "0"), (False, None)])
+def test_points_append_equals_one_full_upload(oracle, pkg, monkeypatch, derive, reserve):
     """Map growth in blocks of uneven size (including growth past the doubled capacity and an empty
-    initial set) leaves normals, ranges and match results bit-identical to one upload."""
+    initial set) leaves normals, ranges and match results bit-identical to one upload.  With
+    SLAMGPU_MAP_RESERVE=0 every growth step is a reallocation with live data; by default the first growth
+    reserves the whole run."""
+    if reserve is not None:
+        monkeypatch.setenv("SLAMGPU_MAP_RESERVE", reserve)
+    with pkg.Context(0) as ctx:
+        _append_equals_upload(ctx, oracle, pkg, derive)
+
+
+def _append_equals_upload(ctx, oracle, pkg, derive):
     n, nkp = 9000, 1500
     sc = pkg.synthetic.projection_scene(n, nkp, 41)
     p = _params(pkg, pkg.synthetic.KITTI)

@@ -50,6 +50,7 @@ def run_sequence(ctx, pkg, n_frames=2000, nkp=8000, ppf=100, seed=3, cpu_frames=
     if cpu_frames and cpu_arm is not None:
         sample = set(np.linspace(n_frames // 10, n_frames - 1, cpu_frames).astype(int).tolist())
     t_parts = np.zeros(4)
+    t_worst = np.zeros(4)
     kept = {}
     prev = seq.frame(0)
     n_kf = n_map = 0
@@ -71,6 +72,7 @@ def run_sequence(ctx, pkg, n_frames=2000, nkp=8000, ppf=100, seed=3, cpu_frames=
         ctx.points_append(set_slot, *new)
         t4 = time.perf_counter()
         t_parts += (t1 - t0, t2 - t1, t3 - t2, t4 - t3)
+        t_worst = np.maximum(t_worst, (t1 - t0, t2 - t1, t3 - t2, t4 - t3))
         n_kf += int((res[0] >= 0).sum())
         n_map += int((res[2] >= 0).sum())
         if f in sample:
@@ -87,6 +89,8 @@ def run_sequence(ctx, pkg, n_frames=2000, nkp=8000, ppf=100, seed=3, cpu_frames=
         "ms_per_frame_parts": {"frame_upload": t_parts[0] / n_frames * 1e3, "match_features": t_parts[1] / n_frames * 1e3,
                                "track_match_incl_kd_wait": t_parts[2] / n_frames * 1e3,
                                "points_append": t_parts[3] / n_frames * 1e3},
+        "ms_worst_frame_parts": {"frame_upload": t_worst[0] * 1e3, "match_features": t_worst[1] * 1e3,
+                                 "track_match_incl_kd_wait": t_worst[2] * 1e3, "points_append": t_worst[3] * 1e3},
         "gcmp_s_bruteforce_part": nkp * nkp / (t_parts[1] / n_frames) / 1e9,
         "proj_match_kernel_us_avg": k_ms / max(k_n, 1) * 1e3, "proj_match_kernel_launches": int(k_n),
         "keyframe_matches": n_kf, "map_matches": n_map, "copies": "inside", "clock": "host",

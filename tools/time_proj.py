@@ -21,6 +21,10 @@ VARIANTS = {
     "v3_lanes8_cell16": {"SLAMGPU_PROJ_LANES": "8", "SLAMGPU_GRID_CELL": "16"},
     "v3_lanes8_cell12": {"SLAMGPU_PROJ_LANES": "8", "SLAMGPU_GRID_CELL": "12"},
     "v3_lanes32_cell16": {"SLAMGPU_PROJ_LANES": "32", "SLAMGPU_GRID_CELL": "16"},
+    "fused_only": {"SLAMGPU_PROJ_TWOPASS": "2"},
+    "fused_only_noqueue": {"SLAMGPU_PROJ_TWOPASS": "2", "SLAMGPU_PROJ_QUEUE": "0"},
+    "two_pass_noqueue": {"SLAMGPU_PROJ_TWOPASS": "1", "SLAMGPU_PROJ_QUEUE": "0"},
+    "two_pass_always": {"SLAMGPU_PROJ_TWOPASS": "1"},
     "default": {},
 }
 
@@ -87,7 +91,7 @@ if __name__ == "__main__":
               "(KITTI, 2000 kp), c4 = 50k points x 20 key frames, 200k = 200k points x 1 frame (1080p, 8000 kp)")
         for name, env in VARIANTS.items():
             e = dict(os.environ)
-            for k in ("SLAMGPU_PROJ_V2", "SLAMGPU_PROJ_LANES", "SLAMGPU_GRID_CELL", "SLAMGPU_PROJ_WALK", "SLAMGPU_PROJ_COOP"):
+            for k in ("SLAMGPU_PROJ_V2", "SLAMGPU_PROJ_LANES", "SLAMGPU_GRID_CELL", "SLAMGPU_PROJ_WALK", "SLAMGPU_PROJ_TWOPASS", "SLAMGPU_PROJ_QUEUE"):
                 e.pop(k, None)
             e.update(env)
             sys.stdout.flush()
