@@ -342,8 +342,9 @@ def run_ours(args, rank, local_rank, world):
     h_pairs = torch.from_numpy(np.stack([step_pairs(pairs, s, n) for s in range(W + K)])).pin_memory()
     cap = n * 1024
     o_off = np.zeros(n + 1, np.int32)
-    o_q = np.zeros(cap, np.int32)
-    o_t = np.zeros(cap, np.int32)
+    # result lists in pinned memory (what slamgpu_host_alloc hands out): the slices' copies land in them directly
+    o_q = torch.zeros(cap, dtype=torch.int32).pin_memory().numpy()
+    o_t = torch.zeros(cap, dtype=torch.int32).pin_memory().numpy()
     total = C.c_int64(0)
     u8p, i32p = C.POINTER(C.c_uint8), C.POINTER(C.c_int32)
 

@@ -244,9 +244,10 @@ class Context:
                                                      C.byref(n)))
         return ot[:n.value].copy(), oq[:n.value].copy()
 
-    def match_descriptors_batch(self, desc, frame_offset, pairs, max_dist=64.0, ratio=0.75, capacity=None):
+    def match_descriptors_batch(self, desc, frame_offset, pairs, max_dist=64.0, ratio=0.75, capacity=None, out=None):
         """-> (offset [n_pairs+1], query_idx, train_idx): per pair (query_frame, train_frame) the
-        compacted match_descriptors list."""
+        compacted match_descriptors list.  out = (query_idx, train_idx) int32 arrays to fill (pinned ones receive
+        the device copies directly); their length is then the capacity."""
         desc = _desc(desc)
         frame_offset = np.ascontiguousarray(frame_offset, np.int32)
         pairs = np.ascontiguousarray(pairs, np.int32).reshape(-1, 2)
@@ -255,8 +256,13 @@ class Context:
             rows = np.diff(frame_offset)
             capacity = int(rows[pairs[:, 0]].sum()) if n_pairs else 0
         off = np.zeros(n_pairs + 1, np.int32)
-        oq = np.zeros(max(capacity, 1), np.int32)
-        ot = np.zeros(max(capacity, 1), np.int32)
+        if out is not None:
+            oq, ot = out
+            assert oq.dtype == np.int32 and ot.dtype == np.int32 and oq.flags.c_contiguous and ot.flags.c_contiguous
+            capacity = min(len(oq), len(ot))
+        else:
+            oq = np.zeros(max(capacity, 1), np.int32)
+            ot = np.zeros(max(capacity, 1), np.int32)
         total = C.c_int64(0)
         self._check(self._lib.slamgpu_match_descriptors_batch(
             self._h, _p(desc, C.c_uint8), _p(frame_offset, C.c_int32), len(frame_offset) - 1, _p(pairs, C.c_int32),

@@ -2,6 +2,7 @@
 // Host-buffer forms stage through the context's pinned buffer, copy H2D, run the kernels of
 // bf_kernels.cu on the context's stream, copy D2H and return when the caller's buffers are filled.
 #include <algorithm>
+#include <functional>
 #include <cmath>
 #include <cstring>
 
@@ -229,7 +230,9 @@ int batch_core(slamgpu_ctx* ctx, const uint8_t* d_desc, const int32_t* d_frame_o
                const int32_t* d_pairs, int n_pairs, int max_rows, float max_dist, float ratio, int32_t* d_out_train, int32_t* d_out_count,
                // optional ordered compaction (host-buffer form): per-slice out_train is then a scratch
                // of slice_pairs x max_rows and the lists are filled slice by slice
-               int32_t* d_offset, int32_t* d_query_list, int32_t* d_train_list, int64_t capacity, int slice_pairs)
+               int32_t* d_offset, int32_t* d_query_list, int32_t* d_train_list, int64_t capacity, int slice_pairs,
+               // called after the work of slice [p0, p0 + np) has been queued on the stream
+               const std::function<int(int, int)>* after_slice = nullptr)
 {
     if (n_pairs == 0) return SLAMGPU_OK;
     if (max_rows == 0) {
@@ -285,12 +288,15 @@ int batch_core(slamgpu_ctx* ctx, const uint8_t* d_desc, const int32_t* d_frame_o
             SG_TRY(bf_launch_compact(ctx, out_train, d_frame_offset, pairs, 0, np, max_rows, d_offset + p0,
                                      d_query_list, d_train_list, capacity));
         }
+        if (after_slice) SG_TRY((*after_slice)(p0, np));
     }
     return SLAMGPU_OK;
 }
 
-int slice_for(int n_sm, int max_rows)
+int slice_for(const slamgpu_ctx* ctx, int max_rows)
 {
+    if (ctx->batch_slice > 0) return ctx->batch_slice;
+    const int n_sm = ctx->n_sm;
     // one slice = enough pairs to fill the GPU a few times over, bounded by the scratch budget
     const size_t per_pair = static_cast<size_t>(max_rows) * sizeof(uint2);
     size_t s = per_pair ? kBatchScratchBytes / per_pair : 1;
@@ -480,7 +486,11 @@ int slamgpu_match_descriptors_batch(slamgpu_ctx* ctx, const uint8_t* desc, const
     const size_t n_rows = static_cast<size_t>(frame_offset[n_frames]);
     SG_CHECK(n_rows == 0 || desc != nullptr, "null descriptors");
 
-    const int slice = std::min(n_pairs, slice_for(ctx->n_sm, max_rows));
+    if (max_rows == 0) {   // every frame is empty: no matches (src/MapMatcher.cpp:139-141)
+        std::memset(out_offset, 0, sizeof(int32_t) * (static_cast<size_t>(n_pairs) + 1));
+        return SLAMGPU_OK;
+    }
+    const int slice = std::min(n_pairs, slice_for(ctx, max_rows));
     const size_t b_desc = Carver::padded(n_rows * 32), b_off = Carver::padded(sizeof(int32_t) * (n_frames + 1)),
                  b_pairs = Carver::padded(sizeof(int32_t) * 2 * n_pairs);
     const size_t b_rows = Carver::padded(sizeof(int32_t) * static_cast<size_t>(slice) * std::max(max_rows, 1)),
@@ -501,24 +511,79 @@ int slamgpu_match_descriptors_batch(slamgpu_ctx* ctx, const uint8_t* desc, const
     SG_TRY(upload(ctx, d_desc, desc, n_rows * 32, 0));
     SG_TRY(upload(ctx, d_off, frame_offset, sizeof(int32_t) * (n_frames + 1), b_desc));
     SG_TRY(upload(ctx, d_pairs, pairs, sizeof(int32_t) * 2 * n_pairs, b_desc + b_off));
-    SG_TRY(batch_core(ctx, d_desc, d_off, n_frames, d_pairs, n_pairs, max_rows, max_dist, ratio, d_rows, d_count, d_offset, d_ql,
-                      d_tl, capacity, slice));
-    // offsets first: they tell how much of the lists to bring back
-    uint8_t* hs = static_cast<uint8_t*>(ctx->h_stage.ptr);
-    SG_CUDA(cudaMemcpyAsync(hs, d_offset, sizeof(int32_t) * (static_cast<size_t>(n_pairs) + 1), cudaMemcpyDeviceToHost,
-                            ctx->stream));
-    SG_CUDA(cudaStreamSynchronize(ctx->stream));
-    std::memcpy(out_offset, hs, sizeof(int32_t) * (static_cast<size_t>(n_pairs) + 1));
-    const int64_t total = out_offset[n_pairs];
-    *out_total = total;
-    if (total > capacity) return fail(SLAMGPU_ERR_NOMEM, "match list capacity too small; *out_total holds the size needed");
-    if (total > 0) {
-        SG_CUDA(cudaMemcpyAsync(hs, d_ql, sizeof(int32_t) * total, cudaMemcpyDeviceToHost, ctx->stream));
-        SG_CUDA(cudaMemcpyAsync(hs + b_list, d_tl, sizeof(int32_t) * total, cudaMemcpyDeviceToHost, ctx->stream));
-        SG_CUDA(cudaStreamSynchronize(ctx->stream));
-        std::memcpy(out_query, hs, sizeof(int32_t) * total);
-        std::memcpy(out_train, hs + b_list, sizeof(int32_t) * total);
+    // The lists come back slice by slice: once a slice's kernels are done its offsets are copied out on a second
+    // stream, the host reads them, queues the copy of that slice's piece of the two lists and moves the previous
+    // piece into the caller's arrays -- all while the GPU scans the later slices.  Pinned caller arrays
+    // (slamgpu_host_alloc) receive the copies directly.
+    if (ctx->copy_stream == nullptr) SG_CUDA(cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking));
+    const int n_slices = (n_pairs + slice - 1) / slice;
+    while (ctx->slice_events.size() < 3 * static_cast<size_t>(n_slices)) {
+        cudaEvent_t e = nullptr;
+        SG_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+        ctx->slice_events.push_back(e);
     }
+    uint8_t* hs = static_cast<uint8_t*>(ctx->h_stage.ptr);
+    int32_t* h_offset = reinterpret_cast<int32_t*>(hs);
+    const bool direct = capacity > 0 && is_pinned(out_query) && is_pinned(out_train);
+    int32_t* h_ql = direct ? out_query : reinterpret_cast<int32_t*>(hs + b_offset);
+    int32_t* h_tl = direct ? out_train : reinterpret_cast<int32_t*>(hs + b_offset + b_list);
+    // the uploads above may have been staged through the same pinned block: the downloads must not start
+    // before they have been consumed (stream order covers it: slice 0 runs after the uploads)
+    int slice_no = 0;
+    const std::function<int(int, int)> after_slice = [&](int p0, int np) -> int {
+        cudaEvent_t done = ctx->slice_events[3 * slice_no], off_ready = ctx->slice_events[3 * slice_no + 1];
+        ++slice_no;
+        SG_CUDA(cudaEventRecord(done, ctx->stream));
+        SG_CUDA(cudaStreamWaitEvent(ctx->copy_stream, done, 0));
+        SG_CUDA(cudaMemcpyAsync(h_offset + p0 + 1, d_offset + p0 + 1, sizeof(int32_t) * np, cudaMemcpyDeviceToHost,
+                                ctx->copy_stream));
+        SG_CUDA(cudaEventRecord(off_ready, ctx->copy_stream));
+        return SLAMGPU_OK;
+    };
+    const int rc = batch_core(ctx, d_desc, d_off, n_frames, d_pairs, n_pairs, max_rows, max_dist, ratio, d_rows, d_count,
+                              d_offset, d_ql, d_tl, capacity, slice, &after_slice);
+    if (rc != SLAMGPU_OK) {
+        cudaStreamSynchronize(ctx->copy_stream);
+        return rc;
+    }
+    h_offset[0] = 0;
+    bool overflow = false;
+    int64_t begin = 0, prev_begin = 0, prev_end = 0;
+    int prev = -1;
+    auto unstage = [&](int s, int64_t b, int64_t e) -> int {      // piece [b, e) of slice s into the caller's arrays
+        SG_CUDA(cudaEventSynchronize(ctx->slice_events[3 * s + 2]));
+        if (!direct && e > b) {
+            std::memcpy(out_query + b, h_ql + b, sizeof(int32_t) * (e - b));
+            std::memcpy(out_train + b, h_tl + b, sizeof(int32_t) * (e - b));
+        }
+        return SLAMGPU_OK;
+    };
+    for (int s = 0; s < slice_no; ++s) {
+        const int p0 = s * slice, np = std::min(slice, n_pairs - p0);
+        SG_CUDA(cudaEventSynchronize(ctx->slice_events[3 * s + 1]));
+        const int64_t end = h_offset[p0 + np];
+        overflow = overflow || end > capacity;
+        if (!overflow) {
+            if (end > begin) {
+                SG_CUDA(cudaMemcpyAsync(h_ql + begin, d_ql + begin, sizeof(int32_t) * (end - begin), cudaMemcpyDeviceToHost,
+                                        ctx->copy_stream));
+                SG_CUDA(cudaMemcpyAsync(h_tl + begin, d_tl + begin, sizeof(int32_t) * (end - begin), cudaMemcpyDeviceToHost,
+                                        ctx->copy_stream));
+            }
+            SG_CUDA(cudaEventRecord(ctx->slice_events[3 * s + 2], ctx->copy_stream));
+            if (prev >= 0) SG_TRY(unstage(prev, prev_begin, prev_end));
+            prev = s;
+            prev_begin = begin;
+            prev_end = end;
+        }
+        begin = end;
+    }
+    if (prev >= 0) SG_TRY(unstage(prev, prev_begin, prev_end));
+    SG_CUDA(cudaStreamSynchronize(ctx->copy_stream));
+    SG_CUDA(cudaStreamSynchronize(ctx->stream));
+    std::memcpy(out_offset, h_offset, sizeof(int32_t) * (static_cast<size_t>(n_pairs) + 1));
+    *out_total = out_offset[n_pairs];
+    if (overflow) return fail(SLAMGPU_ERR_NOMEM, "match list capacity too small; *out_total holds the size needed");
     return SLAMGPU_OK;
 }
 
@@ -562,7 +627,7 @@ int slamgpu_match_descriptors_batch_dev(slamgpu_ctx* ctx, const uint8_t* d_desc,
     SG_CHECK(d_desc && d_frame_offset && d_pairs && d_out_train && d_out_count, "null pointer");
     SG_CHECK(aligned16(d_desc), "device descriptor pointer must be 16-byte aligned");
     return batch_core(ctx, d_desc, d_frame_offset, n_frames, d_pairs, n_pairs, max_rows, max_dist, ratio, d_out_train,
-                      d_out_count, nullptr, nullptr, nullptr, 0, slice_for(ctx->n_sm, max_rows));
+                      d_out_count, nullptr, nullptr, nullptr, 0, slice_for(ctx, max_rows));
 }
 
 } // extern "C"

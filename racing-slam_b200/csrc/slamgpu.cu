@@ -232,6 +232,8 @@ int slamgpu_create(int device, slamgpu_ctx** out)
     ctx->n_sm = prop.multiProcessorCount;
     const char* walk = std::getenv("SLAMGPU_PROJ_WALK");
     ctx->proj_walk = walk != nullptr && walk[0] == '1';
+    const char* bs = std::getenv("SLAMGPU_BATCH_SLICE");
+    if (bs != nullptr) ctx->batch_slice = std::max(std::atoi(bs), 0);
     const char* pq = std::getenv("SLAMGPU_PROJ_QUEUE");
     if (pq != nullptr) ctx->proj_queue = std::atoi(pq) != 0;
     const char* tp = std::getenv("SLAMGPU_PROJ_TWOPASS");
@@ -292,6 +294,8 @@ int slamgpu_destroy(slamgpu_ctx* ctx)
             cudaEventDestroy(pr.second);
         }
     for (cudaEvent_t e : ctx->prof_pool) cudaEventDestroy(e);
+    for (cudaEvent_t e : ctx->slice_events) cudaEventDestroy(e);
+    if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);
     cudaStreamDestroy(ctx->stream);
     delete ctx;
     return SLAMGPU_OK;

@@ -151,6 +151,9 @@ struct slamgpu_ctx {
     std::map<int, slamgpu::VocabDev> vocabs;
     std::map<int, slamgpu::BowDbDev> bow_dbs;
     bool bow_smem_set = false;
+    int batch_slice = 0;                       // SLAMGPU_BATCH_SLICE: pairs per slice of the batch calls (0 = by scratch size)
+    cudaStream_t copy_stream = nullptr;        // result copies of the batch call, overlapped with later slices
+    std::vector<cudaEvent_t> slice_events;     // 3 per slice of slamgpu_match_descriptors_batch (created on demand)
 };
 
 namespace slamgpu {

@@ -127,6 +127,43 @@ def test_batch_vs_single_and_oracle(ctx, oracle, pkg):
     assert rng is not None
 
 
+@pytest.mark.parametrize("slice_pairs,pinned", [("7", False), ("1", False), ("4", True), ("0", True)])
+def test_batch_in_slices_returns_the_same_lists(oracle, pkg, monkeypatch, slice_pairs, pinned):
+    """The host-buffer batch call brings its lists back slice by slice while later slices are scanned
+    (SLAMGPU_BATCH_SLICE forces small slices; 0 = the library's choice, one slice here); pinned output arrays
+    receive the device copies directly.  Same lists either way, and an overflow in a middle slice is reported
+    with the size needed."""
+    import torch
+    monkeypatch.setenv("SLAMGPU_BATCH_SLICE", slice_pairs)
+    sizes = [300, 0, 257, 1, 640, 33]
+    db = pkg.synthetic.keyframe_db(len(sizes), 640, 9, shared_frac=0.4)
+    frames = [db[i, :n] for i, n in enumerate(sizes)]
+    desc = np.concatenate(frames)
+    off = np.concatenate([[0], np.cumsum(sizes)]).astype(np.int32)
+    pairs = pkg.sharding.all_pairs(len(sizes))
+    pairs = np.concatenate([pairs, pairs[:, ::-1]])
+    want_q, want_t, want_o = [], [], [0]
+    for fq, ft in pairs:
+        oq, ot = oracle.match_descriptors(frames[fq], frames[ft], 64.0, 0.75)
+        want_q.append(oq), want_t.append(ot), want_o.append(want_o[-1] + len(oq))
+    want_q, want_t = np.concatenate(want_q), np.concatenate(want_t)
+    assert want_o[-1] > 200
+    with pkg.Context(0) as c:
+        out = None
+        if pinned:
+            out = (torch.zeros(4096, dtype=torch.int32).pin_memory().numpy(),
+                   torch.zeros(4096, dtype=torch.int32).pin_memory().numpy())
+        o, ql, tl = c.match_descriptors_batch(desc, off, pairs, 64.0, 0.75, out=out)
+        assert np.array_equal(o, want_o) and np.array_equal(ql, want_q) and np.array_equal(tl, want_t)
+        o2, ql2, tl2 = c.match_descriptors_batch(desc, off, pairs, 64.0, 0.75, capacity=want_o[-1])    # exact fit
+        assert np.array_equal(o2, want_o) and np.array_equal(ql2, want_q) and np.array_equal(tl2, want_t)
+        with pytest.raises(pkg.SlamGpuError) as e:
+            c.match_descriptors_batch(desc, off, pairs, 64.0, 0.75, capacity=want_o[len(pairs) // 2])
+        assert e.value.code == pkg.binding.ERR_NOMEM
+        o3, ql3, _ = c.match_descriptors_batch(desc, off, pairs[:3], 64.0, 0.75)                        # still usable
+        assert np.array_equal(o3, want_o[:4]) and np.array_equal(ql3, want_q[:want_o[3]])
+
+
 def test_batch_capacity_error(ctx, pkg):
     db = pkg.synthetic.keyframe_db(3, 128, 1, shared_frac=0.9, max_flip=5)
     desc = db.reshape(-1, 32)

@@ -291,3 +291,26 @@ def test_walk_and_warp_kernels_agree_on_tie_heavy_scene(oracle, pkg, monkeypatch
         assert np.array_equal(results[0][0], r[0]) and np.array_equal(results[0][2], r[2])
     # the scene really has ties: many proposing points share their best distance with a second candidate
     assert (ref.kp >= 0).sum() > 500
+
+
+FORMS = [
+    {"SLAMGPU_PROJ_TWOPASS": "1"},                                  # gate + search passes at every size
+    {"SLAMGPU_PROJ_TWOPASS": "1", "SLAMGPU_PROJ_QUEUE": "0"},
+    {"SLAMGPU_PROJ_TWOPASS": "2"},                                  # the fused kernel at every size
+    {"SLAMGPU_PROJ_TWOPASS": "1", "SLAMGPU_PROJ_LANES": "32"},
+]
+
+
+@pytest.mark.parametrize("env", FORMS, ids=lambda e: ",".join(f"{k[13:]}={v}" for k, v in e.items()))
+def test_every_form_of_the_match_kernel_passes_the_parity_cases(oracle, pkg, monkeypatch, env):
+    """The library picks the form of K4 by visit count; here each form is forced and run through the parity cases
+    above that exercise order lists with null entries, degenerate geometry, key-frame batches with per-frame
+    skip masks, replace = true and search boxes taller than a group."""
+    for k, v in env.items():
+        monkeypatch.setenv(k, v)
+    with pkg.Context(0) as c:
+        test_order_subset_and_null_entries(c, oracle, pkg)
+        test_degenerate_inputs(c, oracle, pkg)
+        test_batch_over_keyframes_equals_single_calls(c, oracle, pkg)
+        for scene in (SCENES[2], SCENES[5], SCENES[6], SCENES[7]):
+            test_scene_vs_oracle(c, oracle, pkg, *scene)

@@ -200,3 +200,13 @@ def test_kd_build_on_the_library_thread_equals_the_inline_build(oracle, pkg, mon
                                   want_stats=False)
     for op, od in results:
         assert np.array_equal(op, ref.point) and np.array_equal(od, ref.dist)
+
+
+@pytest.mark.parametrize("two_pass", ["1", "2"])
+def test_track_match_with_either_form_of_the_match_kernel(oracle, pkg, monkeypatch, two_pass):
+    """The tracking pair with K4 forced to its gate + search form (1) and to the fused kernel (2): by default
+    the key-frame subset takes the fused kernel and a large map the two passes."""
+    monkeypatch.setenv("SLAMGPU_PROJ_TWOPASS", two_pass)
+    with pkg.Context(0) as c:
+        for scene in TRACK_SCENES[:2]:
+            test_track_match_equals_the_two_reference_calls(c, oracle, pkg, *scene)
