@@ -294,6 +294,19 @@ def run_ours(args, rank, local_rank, world):
     lib = ctx._lib
     stream = torch.cuda.ExternalStream(ctx.stream)
     db, off, pairs = make_workload(args, rank, world)
+    replicate_ms = None
+    if world > 1:
+        # the one exchange of the path: rank 0's key-frame database to every GPU, one NCCL broadcast
+        # of the device tensor over NVLink / NVSwitch, before the clock starts.  The other ranks drop their own
+        # copy and match against what arrived.
+        pkg.sharding.replicate(db[:1] if rank == 0 else None, 0)          # warm the communicator
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        _, d_db = pkg.sharding.replicate(db if rank == 0 else None, 0)
+        torch.cuda.synchronize()
+        replicate_ms = max_over_ranks(time.perf_counter() - t0) * 1e3
+        if rank != 0:
+            db = d_db.cpu().numpy()
     n, K, W = args.pairs_per_step, args.steps, args.warmup
     per_pair = float(args.desc) * args.desc
     n_sm = torch.cuda.get_device_properties(local_rank).multi_processor_count
@@ -443,6 +456,10 @@ def run_ours(args, rank, local_rank, world):
         "matches_last_step_all_ranks": checksum,
     }
     line["c4_local_window_batch"] = c4_line
+    if replicate_ms is not None:
+        line["replicate"] = {"what": "key-frame database, rank 0 -> all ranks, one NCCL broadcast of the device tensor "
+                                     "(outside the timed region)", "bytes": int(db.nbytes), "ms": replicate_ms,
+                             "gb_s": db.nbytes / (replicate_ms * 1e-3) / 1e9}
     if world == 1:
         line["cpu_baseline"] = cpu_baseline(args, db)
         if not args.no_also:

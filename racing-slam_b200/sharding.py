@@ -6,6 +6,7 @@ gathers results.  The only optional exchange is replicating the descriptor datab
   all_pairs(n)                      LoopDetector ordered pairs query > candidate (src/LoopDetector.h:33)
   shard_pairs(pairs, rank, world)   block-cyclic split of a pair list, balanced for ragged frames
   shard_keyframes(n, rank, world)   round-robin split of the fuse window (src/Mapper.cpp:208-219)
+  replicate(array, src)             the one exchange: the database / point set from one rank to all
 """
 from __future__ import annotations
 
@@ -55,3 +56,41 @@ def gather_counts(local: np.ndarray, index: np.ndarray, n_total: int, group=None
         dist.all_reduce(t, op=dist.ReduceOp.SUM, group=group)   # shards are disjoint: sum = gather
         out = t.cpu().numpy()
     return out
+
+
+def replicate(array, src: int = 0, group=None, device=None):
+    """Replicate `array` (numpy, read on the source rank only) from rank `src` to
+    every rank: shape and dtype travel first, then ONE broadcast of the payload -- over NCCL the payload is a
+    device tensor, so the copy runs GPU to GPU through NVLink / NVSwitch and arrives already resident.
+    -> (numpy array or None, device tensor or None): NCCL returns the device tensor (host copy left to the caller),
+    gloo / single process the numpy array."""
+    import torch
+    import torch.distributed as dist
+    if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) == 1:
+        a = np.ascontiguousarray(array)
+        return a, (torch.from_numpy(a).to(device) if device is not None else None)
+    rank = dist.get_rank(group)
+    nccl = dist.get_backend(group) == "nccl"
+    dev = torch.device(device) if device is not None else (torch.device("cuda", torch.cuda.current_device()) if nccl
+                                                           else torch.device("cpu"))
+    meta = [None]
+    if rank == src:
+        a = np.ascontiguousarray(array)
+        meta = [(a.shape, a.dtype.str)]
+    dist.broadcast_object_list(meta, src=src, group=group)
+    shape, dtype = meta[0]
+    nbytes = int(np.prod(shape, dtype=np.int64)) * np.dtype(dtype).itemsize
+    if rank == src:
+        t = torch.from_numpy(a.reshape(-1).view(np.uint8)).to(dev)
+    else:
+        t = torch.empty(nbytes, dtype=torch.uint8, device=dev)
+    if nbytes:
+        dist.broadcast(t, src=src, group=group)
+    if dev.type == "cuda":
+        return None, t.view(_TORCH_DTYPES(torch)[np.dtype(dtype).str]).reshape(shape)
+    return t.numpy().view(np.dtype(dtype)).reshape(shape), None
+
+
+def _TORCH_DTYPES(torch):
+    return {np.dtype(np.uint8).str: torch.uint8, np.dtype(np.int32).str: torch.int32, np.dtype(np.int64).str: torch.int64,
+            np.dtype(np.float32).str: torch.float32, np.dtype(np.float64).str: torch.float64}

@@ -314,3 +314,40 @@ def test_every_form_of_the_match_kernel_passes_the_parity_cases(oracle, pkg, mon
         test_batch_over_keyframes_equals_single_calls(c, oracle, pkg)
         for scene in (SCENES[2], SCENES[5], SCENES[6], SCENES[7]):
             test_scene_vs_oracle(c, oracle, pkg, *scene)
+
+
+@pytest.mark.parametrize("two_pass", ["0", "1"])
+def test_many_random_small_scenes_vs_oracle(oracle, pkg, monkeypatch, two_pass):
+    """60 seeded scenes with everything varied at once: image size (dense to sparse cells), keypoint count (1 to
+    800), radius (0 to 70 px), acceptance threshold, replace, observation counts past the staged 8, low-entropy
+    descriptors (ties decided by the KD visit order), visit lists with null entries.  Strict comparison."""
+    monkeypatch.setenv("SLAMGPU_PROJ_TWOPASS", two_pass)
+    rng = np.random.default_rng(20260 + int(two_pass))
+    ties = 0
+    with pkg.Context(0) as c:
+        for it in range(60):
+            w, h = int(rng.integers(40, 900)), int(rng.integers(30, 500))
+            cam = dict(fx=float(rng.uniform(100, 800)), fy=float(rng.uniform(100, 800)), cx=w / 2.0, cy=h / 2.0,
+                       width=w, height=h)
+            n_points, nkp = int(rng.integers(1, 3000)), int(rng.integers(1, 800))
+            sc = pkg.synthetic.projection_scene(n_points, nkp, 7000 + it, cam=cam, max_obs=int(rng.integers(1, 14)),
+                                                frac_matched_kp=float(rng.uniform(0, 0.5)),
+                                                frac_skip=float(rng.uniform(0, 0.3)))
+            if it % 2:
+                sc.kp_desc[:] = rng.integers(0, 2, sc.kp_desc.shape, dtype=np.uint8) * 255
+                sc.obs_desc[:] = rng.integers(0, 2, sc.obs_desc.shape, dtype=np.uint8) * 255
+            radius = float(rng.choice([0.0, 1.0, 5.5, 15.0, 20.0, 33.0, 70.0]))
+            p = _params(pkg, cam, radius, float(rng.choice([40.0, 64.0, 150.0, 257.0])), int(rng.integers(0, 2)))
+            order = None
+            if it % 3 == 0:
+                order = rng.integers(0, n_points, int(rng.integers(1, 2 * n_points + 2))).astype(np.int32)
+                order[rng.random(len(order)) < 0.15] = -1
+            perm = oracle.kd_build(sc.kp_xy)
+            ref = oracle.match_projection(sc.kp_xy, sc.kp_desc, perm, sc.kp_matched, sc.pos, sc.normal, sc.range,
+                                          sc.obs_offset, sc.obs_desc, sc.skip, order, sc.pose, _oparams(oracle, p))
+            c.frame_upload(1, sc.kp_xy, sc.kp_desc, None, sc.kp_matched)
+            c.points_upload(1, sc.pos, sc.normal, sc.range, sc.obs_offset, sc.obs_desc)
+            op, od, dbg = c.match_projection(1, 1, nkp, sc.pose, p, sc.skip, order, debug=True, n_points=n_points)
+            _compare((op, od), dbg, ref)
+            ties += int((ref.kp >= 0).sum())
+    assert ties > 2000

@@ -48,6 +48,13 @@ def _gloo_worker(rank, world, port, q):
         # stand-in per-pair result (the GPU would produce match counts): a function of the pair
         local = mine[:, 0] * 100 + mine[:, 1]
         full = pkg.sharding.gather_counts(local, idx, len(pairs))
+        # the one exchange of the batched workloads: the database from rank 0 to everyone
+        db = pkg.synthetic.keyframe_db(3, 16, 5) if rank == 0 else None
+        got, _ = pkg.sharding.replicate(db, src=0)
+        assert got.shape == (3, 16, 32) and got.dtype == np.uint8
+        assert np.array_equal(got, pkg.synthetic.keyframe_db(3, 16, 5))
+        empty, _ = pkg.sharding.replicate(np.zeros((0, 32), np.uint8) if rank == 0 else None, src=0)
+        assert empty.shape == (0, 32)
         q.put((rank, full.tolist()))
     finally:
         dist.destroy_process_group()
