@@ -408,10 +408,15 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTc4Threads, 1) bf_t
                         for (int k = 0; k < 4; ++k)     // K = 64 values = 32 bytes = two 16-byte k-chunks per MMA
                             tc4_mma(d, umma_desc(a0 + k * 256, 128u, kGroup4), umma_desc(b0 + k * 256, 128u, kGroup4),
                                     kIdesc4, 1u, sf_one, sf_one);
+                        // second train row of every column, scaled by 2^10.  A last tile with at most 240 rows
+                        // left has none: its columns keep dot2 = 0, what the zero padding rows would have given
+                        // (4000 rows = 8 tiles + 160 rows: 4 of 81 MMAs less per unit)
+                        if (un.t_begin + bt * kT4 + kN4 < un.t_end || (a.variant & 256)) {
 #pragma unroll
-                        for (int k = 0; k < 4; ++k)     // second train row of every column, scaled by 2^10
-                            tc4_mma(d, umma_desc(a0 + k * 256, 128u, kGroup4),
-                                    umma_desc(b0 + kB4Half + k * 256, 128u, kGroup4), kIdesc4, 1u, sf_one, sf_big);
+                            for (int k = 0; k < 4; ++k)
+                                tc4_mma(d, umma_desc(a0 + k * 256, 128u, kGroup4),
+                                        umma_desc(b0 + kB4Half + k * 256, 128u, kGroup4), kIdesc4, 1u, sf_one, sf_big);
+                        }
                     }
                     tc2_commit_mc(B_EMPTY(sb));
                     tc2_commit_mc(ACC_FULL(sc));

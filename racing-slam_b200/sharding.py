@@ -59,7 +59,7 @@ def gather_counts(local: np.ndarray, index: np.ndarray, n_total: int, group=None
 
 
 def replicate(array, src: int = 0, group=None, device=None):
-    """Replicate `array` (numpy, read on the source rank only) from rank `src` to
+    """Replicate `array` (numpy or a device tensor, read on the source rank only) from rank `src` to
     every rank: shape and dtype travel first, then ONE broadcast of the payload -- over NCCL the payload is a
     device tensor, so the copy runs GPU to GPU through NVLink / NVSwitch and arrives already resident.
     -> (numpy array or None, device tensor or None): NCCL returns the device tensor (host copy left to the caller),
@@ -75,13 +75,19 @@ def replicate(array, src: int = 0, group=None, device=None):
                                                            else torch.device("cpu"))
     meta = [None]
     if rank == src:
-        a = np.ascontiguousarray(array)
-        meta = [(a.shape, a.dtype.str)]
+        if isinstance(array, torch.Tensor):          # already resident on the source GPU: no staging at all
+            resident = array.contiguous()
+            meta = [(tuple(resident.shape), np.dtype(str(resident.dtype).replace("torch.", "")).str)]
+        else:
+            resident = None
+            a = np.ascontiguousarray(array)
+            meta = [(a.shape, a.dtype.str)]
     dist.broadcast_object_list(meta, src=src, group=group)
     shape, dtype = meta[0]
     nbytes = int(np.prod(shape, dtype=np.int64)) * np.dtype(dtype).itemsize
     if rank == src:
-        t = torch.from_numpy(a.reshape(-1).view(np.uint8)).to(dev)
+        t = resident.reshape(-1).view(torch.uint8).to(dev) if resident is not None else \
+            torch.from_numpy(a.reshape(-1).view(np.uint8)).to(dev)
     else:
         t = torch.empty(nbytes, dtype=torch.uint8, device=dev)
     if nbytes:
