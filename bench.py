@@ -645,6 +645,80 @@ def also_measurements(ctx, pkg, torch, stream, n_sm, peaks):
     bench_c3.run_sequence(ctx, pkg, 10, 8000, 1000, 3, 0)
     out["c3_tracking_sequence_200_frames"] = bench_c3.run_sequence(ctx, pkg, 200, 8000, 1000, 3, 3, c3_cpu_arm)
     out["n4_bag_of_words"] = bow_measurements(ctx, pkg, torch, stream, peaks)
+    out["n3_pnp_scoring"] = pnp_measurements(ctx, pkg, torch, stream)
+    return out
+
+
+def pnp_measurements(ctx, pkg, torch, stream):
+    """the scoring step of verify_pnp (src/LoopDetector.cpp:203-214: 200 RANSAC models, reprojection
+    error 4.0).  One problem through the host-buffer call (copies inside) and a 4000-problem batch device-resident;
+    the CPU port (oracle, all cores over models) beside them.  An evaluation = one correspondence under one model:
+    23 FP64 multiplies / adds, one FP64 division, five conversions, five FP32 operations."""
+    from oracle import cpu_oracle
+    syn = pkg.synthetic
+    K4 = syn.PNP_K4
+    out = {}
+    cores = os.cpu_count()
+
+    def wall(fn, reps, warm=3):
+        for _ in range(warm):
+            fn()
+        ts = []
+        for _ in range(reps):
+            t = time.perf_counter()
+            fn()
+            ts.append(time.perf_counter() - t)
+        return float(np.median(ts))
+
+    objs, imgs, models = syn.pnp_problems(1, [300], [200])
+    s = wall(lambda: ctx.pnp_ransac_score(objs, imgs, models, K4, 4.0), 50)
+    got = ctx.pnp_ransac_score(objs, imgs, models, K4, 4.0)[0]
+    hp = np.zeros(200, np.int32)
+    t_cpu = wall(lambda: cpu_oracle.pnp_score_batch(objs[0], imgs[0], [0], [300], models[0], hp, K4, 4.0, 1), 20)
+    ocnt = cpu_oracle.pnp_score_batch(objs[0], imgs[0], [0], [300], models[0], hp, K4, 4.0, 1)
+    out["one_problem_300x200"] = {"us_per_call": s * 1e6, "copies": "inside (two syncs: counts down, choice up, mask down)",
+                                  "cpu_port_us_1_core": t_cpu * 1e6,
+                                  "identical_to_oracle": bool(np.array_equal(got[0], ocnt) and
+                                                              got[1] == cpu_oracle.ransac_select(ocnt, 300)[0])}
+
+    n_prob, n_mod = 4000, 200
+    rng = np.random.default_rng(9)
+    sizes = [int(x) for x in rng.integers(40, 560, n_prob)]
+    objs, imgs, models = syn.pnp_problems(2, sizes, [n_mod] * n_prob)
+    obj, img, rt = np.concatenate(objs), np.concatenate(imgs), np.concatenate(models)
+    cnt = np.array(sizes, np.int32)
+    begin = (np.cumsum(cnt) - cnt).astype(np.int32)
+    hp = np.repeat(np.arange(n_prob, dtype=np.int32), n_mod)
+    evals = int(cnt.astype(np.int64).sum()) * n_mod
+    d = lambda a: torch.from_numpy(np.ascontiguousarray(a)).cuda()
+    d_obj, d_img, d_rt, d_begin, d_cnt, d_hp = d(obj), d(img), d(rt), d(begin), d(cnt), d(hp)
+    d_good = torch.empty(len(hp), dtype=torch.int32, device="cuda")
+    torch.cuda.synchronize()
+    run = lambda: ctx.pnp_score_dev(d_obj.data_ptr(), d_img.data_ptr(), d_begin.data_ptr(), d_cnt.data_ptr(), n_prob,
+                                    d_rt.data_ptr(), d_hp.data_ptr(), len(hp), K4, 4.0, d_good.data_ptr())
+    for _ in range(2):
+        run()
+    ctx.sync()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record(stream)
+    for _ in range(5):
+        run()
+    b.record(stream)
+    torch.cuda.synchronize()
+    ms = a.elapsed_time(b) / 5
+    sample = 400 * n_mod                                   # the first 400 problems
+    t = time.perf_counter()
+    ocnt = cpu_oracle.pnp_score_batch(obj, img, begin, cnt, rt[:sample], hp[:sample], K4, 4.0, cores)
+    t_cpu = time.perf_counter() - t
+    sample_evals = int(cnt[:400].astype(np.int64).sum()) * n_mod
+    out["batch_4000_problems_x_200_models_device"] = {
+        "ms": ms, "evaluations": evals, "evaluations_per_s": evals / (ms * 1e-3),
+        "fp64_ops_per_s": evals * 33 / (ms * 1e-3),
+        "fp64_ops_note": "14 DMUL + 11 DADD + 8 DFMA of the IEEE division per evaluation (SASS count)",
+        "algorithmic_bytes": int(len(obj) * 20 + len(rt) * 100 + len(rt) * 4),
+        "cpu_port_evaluations_per_s": sample_evals / t_cpu, "cpu_port_cores": cores,
+        "cpu_port_sample": "first 400 problems (80000 models)",
+        "identical_to_oracle_on_sample": bool(np.array_equal(d_good[:sample].cpu().numpy(), ocnt))}
     return out
 
 

@@ -301,16 +301,77 @@ SLAMGPU_API int slamgpu_bowdb_score_l1(slamgpu_ctx* ctx, int db_id, const int32_
 SLAMGPU_API int slamgpu_bowdb_release(slamgpu_ctx* ctx, int db_id);
 
 /* ------------------------------------------------------------------------------------------
+ * PnP verification support: the data-parallel part of verify_pnp
+ * (src/LoopDetector.cpp:176-229) on either side of cv::solvePnPRansac's model solver.
+ *
+ * A PROBLEM is one (query, candidate) pair: a run of 3-D / 2-D correspondences.  A MODEL is one pose
+ * hypothesis of a problem as 12 doubles: R row-major (cv::Rodrigues of the solver's rvec), then t.
+ * K4 = fx, fy, cx, cy as doubles (the reference converts its intrinsics to CV_64F,
+ * src/LoopDetector.cpp:199-200); no distortion (cv::Mat() at :207).
+ * What stays on the host: the minimal-set sampling and the EPnP solve of each RANSAC iteration (OpenCV's
+ * RNG and solver; the sample sequence does not depend on the scores, so an adapter can draw every
+ * iteration's model first and score them in one call) and the final refinement.
+ * ---------------------------------------------------------------------------------------- */
+
+/* Input assembly, src/LoopDetector.cpp:188-197, for a batch of pairs straight from
+ * slamgpu_match_descriptors_batch_dev's output (same d_frame_offset / d_pairs / max_rows / d_match_train):
+ *   d_row_pos [rows x 3]  position of the map point behind each descriptor row (match.point.position())
+ *   d_row_xy  [rows x 2]  key point of each descriptor row (query.keypoint(i).pt)
+ * Pair p's correspondences, ascending query row, land at [p*max_rows, p*max_rows + d_out_count[p]) of
+ * d_out_object (x3) / d_out_image (x2) / d_out_query (the query row; may be NULL). */
+SLAMGPU_API int slamgpu_pnp_assemble_batch_dev(slamgpu_ctx* ctx, const int32_t* d_match_train, const int32_t* d_frame_offset,
+                                   int n_frames, const int32_t* d_pairs, int n_pairs, int max_rows,
+                                   const float* d_row_pos, const float* d_row_xy, float* d_out_object,
+                                   float* d_out_image, int32_t* d_out_query, int32_t* d_out_count);
+
+/* Inlier count of every model: PnPRansacCallback::computeError (projectPoints, float squared error) +
+ * RANSACPointSetRegistrator::findInliers (err <= (float)(reproj_error^2)) of cv::solvePnPRansac
+ * (src/LoopDetector.cpp:203-214: reproj_error 4.0).  Problem p owns correspondences
+ * [d_corr_begin[p], d_corr_begin[p] + d_corr_count[p]); model h belongs to problem d_hyp_problem[h].
+ * d_out_count [n_hyp].  Enqueues on the context's stream, no synchronisation. */
+SLAMGPU_API int slamgpu_pnp_score_dev(slamgpu_ctx* ctx, const float* d_object, const float* d_image,
+                          const int32_t* d_corr_begin, const int32_t* d_corr_count, int n_problems,
+                          const double* d_hyp_rt, const int32_t* d_hyp_problem, int n_hyp, const double* K4,
+                          double reproj_error, int32_t* d_out_count);
+/* Inlier mask of one chosen model per problem (d_sel_hyp[p] = model index or -1 for "none": zeros):
+ * d_out_mask [same indexing as d_object rows], d_out_err (float squared errors; may be NULL),
+ * d_out_inliers [n_problems] (may be NULL). */
+SLAMGPU_API int slamgpu_pnp_mask_dev(slamgpu_ctx* ctx, const float* d_object, const float* d_image,
+                         const int32_t* d_corr_begin, const int32_t* d_corr_count, int n_problems,
+                         const double* d_hyp_rt, const int32_t* d_sel_hyp, const double* K4, double reproj_error,
+                         uint8_t* d_out_mask, float* d_out_err, int32_t* d_out_inliers);
+
+/* RANSACPointSetRegistrator::run's choice over models given in iteration order with their inlier counts
+ * (host arithmetic, no device work): a model replaces the best when good > max(best, model_points - 1); the
+ * iteration bound shrinks by RANSACUpdateNumIters after every replacement.  *out_best = kept model or -1,
+ * *out_iters = models looked at (may be NULL).  cv::solvePnPRansac with SOLVEPNP_EPNP uses
+ * model_points = 5, confidence 0.99, max_iters 200 at src/LoopDetector.cpp:203-214. */
+SLAMGPU_API int slamgpu_ransac_select(const int32_t* good_count, int n_models, int n_points, int model_points,
+                          double confidence, int max_iters, int* out_best, int* out_iters);
+
+/* Host-buffer form of the whole scoring step for a batch of problems: upload, count every model, choose
+ * per problem as RANSAC would, compute the kept model's mask, download.
+ *   object [n_corr x 3], image [n_corr x 2], corr_offset [n_problems + 1]
+ *   hyp_rt [n_hyp x 12], hyp_offset [n_problems + 1] (models of a problem in iteration order)
+ *   out_count [n_hyp]; out_best [n_problems] (index within the problem, or -1); out_inliers [n_problems];
+ *   out_mask [n_corr] (the `inliers` output of cv::solvePnPRansac as a mask; may be NULL). */
+SLAMGPU_API int slamgpu_pnp_ransac_score(slamgpu_ctx* ctx, const float* object, const float* image, const int32_t* corr_offset,
+                             int n_problems, const double* hyp_rt, const int32_t* hyp_offset, const double* K4,
+                             double reproj_error, double confidence, int model_points, int max_iters,
+                             int32_t* out_count, int32_t* out_best, int32_t* out_inliers, uint8_t* out_mask);
+
+/* ------------------------------------------------------------------------------------------
  * Diagnostics
  * ---------------------------------------------------------------------------------------- */
 /* Per-kernel device timing for roofline reports: while enabled, every launch of the two dominant
  * kernels is bracketed by a CUDA-event pair on the context's stream.  slamgpu_profile_read
  * synchronises, returns the summed duration and launch count since the last read, and resets.
  *   kernel  SLAMGPU_KERNEL_BF_SCAN (K1 brute-force scan), SLAMGPU_KERNEL_PROJ_MATCH (K4) or
- *           SLAMGPU_KERNEL_VOC_TRANSFORM (vocabulary descent). */
+ *           SLAMGPU_KERNEL_VOC_TRANSFORM (vocabulary descent), SLAMGPU_KERNEL_PNP_SCORE (RANSAC inlier scoring). */
 #define SLAMGPU_KERNEL_BF_SCAN 0
 #define SLAMGPU_KERNEL_PROJ_MATCH 1
 #define SLAMGPU_KERNEL_VOC_TRANSFORM 2
+#define SLAMGPU_KERNEL_PNP_SCORE 3
 SLAMGPU_API int slamgpu_profile_enable(slamgpu_ctx* ctx, int on);
 SLAMGPU_API int slamgpu_profile_read(slamgpu_ctx* ctx, int kernel, double* total_ms, int64_t* launches);
 /* POPC-pipe microbenchmark ("confirm with a POPC microbenchmark on the box"):

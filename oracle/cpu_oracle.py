@@ -75,6 +75,16 @@ def lib():
         L.orc_voc_bow.restype = C.c_int
         L.orc_voc_score_l1.argtypes = [i32p, f64p, C.c_int, i32p, f64p, C.c_int]
         L.orc_voc_score_l1.restype = C.c_double
+        L.orc_pnp_project.argtypes = [f64p, f64p, f32p, C.c_int, f32p]
+        L.orc_pnp_score.argtypes = [f64p, f64p, f32p, f32p, C.c_int, C.c_double, f32p, u8p]
+        L.orc_pnp_score.restype = C.c_int
+        L.orc_ransac_update_num_iters.argtypes = [C.c_double, C.c_double, C.c_int, C.c_int]
+        L.orc_ransac_update_num_iters.restype = C.c_int
+        L.orc_ransac_select.argtypes = [i32p, C.c_int, C.c_int, C.c_int, C.c_double, C.c_int, C.POINTER(C.c_int)]
+        L.orc_ransac_select.restype = C.c_int
+        L.orc_pnp_assemble.argtypes = [i32p, C.c_int, f32p, f32p, f32p, f32p, i32p]
+        L.orc_pnp_assemble.restype = C.c_int
+        L.orc_pnp_score_batch.argtypes = [f32p, f32p, i32p, i32p, f64p, i32p, C.c_int, f64p, C.c_double, C.c_int, i32p]
         _LIB = L
     return _LIB
 
@@ -307,6 +317,70 @@ def voc_score_l1(ids_a, vals_a, ids_b, vals_b) -> float:
     vals_a, vals_b = np.ascontiguousarray(vals_a, np.float64), np.ascontiguousarray(vals_b, np.float64)
     return float(lib().orc_voc_score_l1(_ptr(ids_a, C.c_int32), _ptr(vals_a, C.c_double), len(ids_a),
                                         _ptr(ids_b, C.c_int32), _ptr(vals_b, C.c_double), len(ids_b)))
+
+
+# ---- verify_pnp's input assembly and RANSAC inlier scoring (src/LoopDetector.cpp:176-229) ----
+def pnp_project(rt, K4, obj):
+    """-> uv [n, 2] f32: cv::projectPoints without distortion; rt = R row-major (9) + t (3), K4 = fx, fy, cx, cy."""
+    rt = np.ascontiguousarray(rt, np.float64).reshape(12)
+    K4 = np.ascontiguousarray(K4, np.float64).reshape(4)
+    obj = np.ascontiguousarray(obj, np.float32).reshape(-1, 3)
+    uv = np.zeros((len(obj), 2), np.float32)
+    lib().orc_pnp_project(_ptr(rt, C.c_double), _ptr(K4, C.c_double), _ptr(obj, C.c_float), len(obj), _ptr(uv, C.c_float))
+    return uv
+
+
+def pnp_score(rt, K4, obj, img, reproj_error=4.0):
+    """-> (count, err [n] f32, mask [n] u8): computeError + findInliers of cv::solvePnPRansac for one model."""
+    rt = np.ascontiguousarray(rt, np.float64).reshape(12)
+    K4 = np.ascontiguousarray(K4, np.float64).reshape(4)
+    obj = np.ascontiguousarray(obj, np.float32).reshape(-1, 3)
+    img = np.ascontiguousarray(img, np.float32).reshape(-1, 2)
+    err = np.zeros(len(obj), np.float32)
+    mask = np.zeros(len(obj), np.uint8)
+    c = lib().orc_pnp_score(_ptr(rt, C.c_double), _ptr(K4, C.c_double), _ptr(obj, C.c_float), _ptr(img, C.c_float),
+                            len(obj), float(reproj_error), _ptr(err, C.c_float), _ptr(mask, C.c_uint8))
+    return int(c), err, mask
+
+
+def pnp_score_batch(obj, img, corr_begin, corr_count, hyp_rt, hyp_problem, K4, reproj_error=4.0, threads=1):
+    """-> inlier count of every model [n_hyp] i32 (ragged problems; OpenMP over models)."""
+    obj = np.ascontiguousarray(obj, np.float32)
+    img = np.ascontiguousarray(img, np.float32)
+    cb, cc = np.ascontiguousarray(corr_begin, np.int32), np.ascontiguousarray(corr_count, np.int32)
+    rt, hp = np.ascontiguousarray(hyp_rt, np.float64), np.ascontiguousarray(hyp_problem, np.int32)
+    K4 = np.ascontiguousarray(K4, np.float64).reshape(4)
+    out = np.zeros(len(hp), np.int32)
+    lib().orc_pnp_score_batch(_ptr(obj, C.c_float), _ptr(img, C.c_float), _ptr(cb, C.c_int32), _ptr(cc, C.c_int32),
+                              _ptr(rt, C.c_double), _ptr(hp, C.c_int32), len(hp), _ptr(K4, C.c_double),
+                              float(reproj_error), int(threads), _ptr(out, C.c_int32))
+    return out
+
+
+def ransac_update_num_iters(p, ep, model_points, max_iters) -> int:
+    return int(lib().orc_ransac_update_num_iters(float(p), float(ep), int(model_points), int(max_iters)))
+
+
+def ransac_select(good_count, n_points, model_points=5, confidence=0.99, max_iters=200):
+    """-> (kept model index or -1, models looked at): RANSACPointSetRegistrator::run's choice."""
+    g = np.ascontiguousarray(good_count, np.int32)
+    it = C.c_int(0)
+    b = lib().orc_ransac_select(_ptr(g, C.c_int32), len(g), int(n_points), int(model_points), float(confidence),
+                                int(max_iters), C.byref(it))
+    return int(b), int(it.value)
+
+
+def pnp_assemble(match_train, train_pos, query_xy):
+    """-> (object [n, 3], image [n, 2], query row [n]): src/LoopDetector.cpp:188-197."""
+    mt = np.ascontiguousarray(match_train, np.int32)
+    tp = np.ascontiguousarray(train_pos, np.float32).reshape(-1, 3)
+    qx = np.ascontiguousarray(query_xy, np.float32).reshape(-1, 2)
+    obj = np.zeros((len(mt), 3), np.float32)
+    img = np.zeros((len(mt), 2), np.float32)
+    qi = np.zeros(len(mt), np.int32)
+    n = lib().orc_pnp_assemble(_ptr(mt, C.c_int32), len(mt), _ptr(tp, C.c_float), _ptr(qx, C.c_float),
+                               _ptr(obj, C.c_float), _ptr(img, C.c_float), _ptr(qi, C.c_int32))
+    return obj[:n].copy(), img[:n].copy(), qi[:n].copy()
 
 
 _REF_DBOW = None

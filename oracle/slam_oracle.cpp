@@ -533,3 +533,128 @@ ORC_API double orc_voc_score_l1(const int32_t* ids_a, const double* vals_a, int 
     }
     return -score / 2.0;
 }
+
+// ---------------------------------------------------------------------------------------------
+// the data-parallel part of verify_pnp (src/LoopDetector.cpp:176-229) around
+// cv::solvePnPRansac (called at :203-214 with 200 iterations, reprojection error 4.0, confidence 0.99,
+// SOLVEPNP_EPNP; also src/Initialization.cpp:211-222).  The arithmetic lives in OpenCV (vcpkg port
+// `opencv`, baseline 4b6c50d9..., not vendored).  Restated from its published source:
+//   * projection: calib3d cvProjectPoints2Internal without distortion -- doubles, rotation applied as
+//     R[0]*X + R[1]*Y + R[2]*Z + t[0] left to right, z = z ? 1./z : 1, x *= z, u = x*fx + cx, stored as
+//     float.  PINNED: bit-identical to cv2 4.13.0 projectPoints on the fixtures of oracle/gen_golden_pnp.py
+//     (tests/golden/pnp_*.npz; R = cv2.Rodrigues(rvec), which projectPoints applies itself).
+//   * error: PnPRansacCallback::computeError (solvepnp.cpp) -- err = norm(Matx21f(ip - pp), NORM_L2SQR)
+//     = float dx*dx + dy*dy with dx, dy float differences.
+//   * inliers: RANSACPointSetRegistrator::findInliers (ptsetreg.cpp) -- float t = (float)(thr*thr);
+//     inlier iff err <= t.
+//   * model choice: RANSACPointSetRegistrator::run -- a model replaces the best when
+//     goodCount > max(maxGoodCount, modelPoints - 1); niters = RANSACUpdateNumIters(...) after each
+//     replacement; models past niters are never scored.
+// The last three are PARITY UNPINNED (cv2 exposes neither the per-model errors nor the iteration
+// count); only the projection they consume is pinned.
+// ---------------------------------------------------------------------------------------------
+namespace {
+inline void pnp_project_one(const double* rt, const double* K4, const float* X3, float* uv)
+{
+    const double X = X3[0], Y = X3[1], Z = X3[2];
+    double x = rt[0] * X + rt[1] * Y + rt[2] * Z + rt[9];
+    double y = rt[3] * X + rt[4] * Y + rt[5] * Z + rt[10];
+    double z = rt[6] * X + rt[7] * Y + rt[8] * Z + rt[11];
+    z = z ? 1. / z : 1;
+    x *= z;
+    y *= z;
+    uv[0] = (float)(x * K4[0] + K4[2]);
+    uv[1] = (float)(y * K4[1] + K4[3]);
+}
+} // namespace
+
+// rt = R row-major [9] then t [3]; K4 = fx, fy, cx, cy.
+ORC_API void orc_pnp_project(const double* rt, const double* K4, const float* object, int n, float* out_uv)
+{
+    for (int i = 0; i < n; i++) pnp_project_one(rt, K4, object + 3 * i, out_uv + 2 * i);
+}
+
+// -> inlier count; out_err [n] (may be null), out_mask [n] (may be null)
+ORC_API int orc_pnp_score(const double* rt, const double* K4, const float* object, const float* image, int n,
+                          double reproj_error, float* out_err, uint8_t* out_mask)
+{
+    const float t = (float)(reproj_error * reproj_error);
+    int nz = 0;
+    for (int i = 0; i < n; i++) {
+        float uv[2];
+        pnp_project_one(rt, K4, object + 3 * i, uv);
+        const float dx = image[2 * i] - uv[0], dy = image[2 * i + 1] - uv[1];
+        float s = 0;
+        s += dx * dx;
+        s += dy * dy;
+        const int f = s <= t;
+        if (out_err) out_err[i] = s;
+        if (out_mask) out_mask[i] = (uint8_t)f;
+        nz += f;
+    }
+    return nz;
+}
+
+// ptsetreg.cpp RANSACUpdateNumIters
+ORC_API int orc_ransac_update_num_iters(double p, double ep, int model_points, int max_iters)
+{
+    p = std::max(p, 0.);
+    p = std::min(p, 1.);
+    ep = std::max(ep, 0.);
+    ep = std::min(ep, 1.);
+    double num = std::max(1. - p, std::numeric_limits<double>::min());
+    double denom = 1. - std::pow(1. - ep, model_points);
+    if (denom < std::numeric_limits<double>::min()) return 0;
+    num = std::log(num);
+    denom = std::log(denom);
+    return denom >= 0 || -num >= max_iters * (-denom) ? max_iters : (int)std::lrint(num / denom);
+}
+
+// RANSACPointSetRegistrator::run over models given in iteration order with their inlier counts:
+// -> index of the kept model or -1; *out_iters = models the loop looked at.
+ORC_API int orc_ransac_select(const int32_t* good_count, int n_models, int n_points, int model_points,
+                              double confidence, int max_iters, int* out_iters)
+{
+    int niters = std::max(max_iters, 1), best = -1, max_good = 0, iter = 0;
+    for (; iter < niters && iter < n_models; iter++) {
+        const int good = good_count[iter];
+        if (good > std::max(max_good, model_points - 1)) {
+            best = iter;
+            max_good = good;
+            niters = orc_ransac_update_num_iters(confidence, (double)(n_points - good) / n_points, model_points, niters);
+        }
+    }
+    if (out_iters) *out_iters = iter;
+    return best;
+}
+
+// verify_pnp's input assembly, src/LoopDetector.cpp:188-197: correspondences (ascending query row, as
+// match_descriptors emits them) -> object_points / image_points.  match_train [nq] = train row or -1.
+ORC_API int orc_pnp_assemble(const int32_t* match_train, int nq, const float* train_pos, const float* query_xy,
+                             float* out_object, float* out_image, int32_t* out_query)
+{
+    int n = 0;
+    for (int q = 0; q < nq; q++) {
+        const int t = match_train[q];
+        if (t < 0) continue;
+        std::memcpy(out_object + 3 * n, train_pos + 3 * t, 12);
+        std::memcpy(out_image + 2 * n, query_xy + 2 * q, 8);
+        if (out_query) out_query[n] = q;
+        n++;
+    }
+    return n;
+}
+
+// Counts of many models over ragged problems (the CPU leg of bench.py's N3 measurement): model h belongs to
+// problem hyp_problem[h]; OpenMP over models when threads > 1.
+ORC_API void orc_pnp_score_batch(const float* object, const float* image, const int32_t* corr_begin,
+                                 const int32_t* corr_count, const double* hyp_rt, const int32_t* hyp_problem, int n_hyp,
+                                 const double* K4, double reproj_error, int threads, int32_t* out_count)
+{
+#pragma omp parallel for schedule(dynamic, 64) num_threads(threads > 0 ? threads : 1)
+    for (int h = 0; h < n_hyp; h++) {
+        const int p = hyp_problem[h];
+        out_count[h] = orc_pnp_score(hyp_rt + 12 * (size_t)h, K4, object + 3 * (size_t)corr_begin[p],
+                                     image + 2 * (size_t)corr_begin[p], corr_count[p], reproj_error, nullptr, nullptr);
+    }
+}

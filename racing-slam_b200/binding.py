@@ -93,6 +93,17 @@ SIGNATURES = {
     "slamgpu_bowdb_count": (C.c_int, [_ctx, C.c_int, C.POINTER(C.c_int)]),
     "slamgpu_bowdb_score_l1": (C.c_int, [_ctx, C.c_int, _i32p, _f64p, C.c_int, _f64p]),
     "slamgpu_bowdb_release": (C.c_int, [_ctx, C.c_int]),
+    "slamgpu_pnp_assemble_batch_dev": (C.c_int, [_ctx, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_int,
+                                                 C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                                 C.c_void_p]),
+    "slamgpu_pnp_score_dev": (C.c_int, [_ctx, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p,
+                                        C.c_void_p, C.c_int, _f64p, C.c_double, C.c_void_p]),
+    "slamgpu_pnp_mask_dev": (C.c_int, [_ctx, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p,
+                                       C.c_void_p, _f64p, C.c_double, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "slamgpu_ransac_select": (C.c_int, [_i32p, C.c_int, C.c_int, C.c_int, C.c_double, C.c_int, C.POINTER(C.c_int),
+                                        C.POINTER(C.c_int)]),
+    "slamgpu_pnp_ransac_score": (C.c_int, [_ctx, _f32p, _f32p, _i32p, C.c_int, _f64p, _i32p, _f64p, C.c_double,
+                                           C.c_double, C.c_int, C.c_int, _i32p, _i32p, _i32p, _u8p]),
     "slamgpu_profile_enable": (C.c_int, [_ctx, C.c_int]),
     "slamgpu_profile_read": (C.c_int, [_ctx, C.c_int, C.POINTER(C.c_double), _i64p]),
     "slamgpu_bench_popc": (C.c_int, [_ctx, C.POINTER(C.c_double), C.POINTER(C.c_int), C.POINTER(C.c_double)]),
@@ -140,6 +151,18 @@ def kd_build_host(xy) -> np.ndarray:
     if rc != OK:
         raise SlamGpuError(rc, lib.slamgpu_last_error().decode())
     return perm
+
+
+def ransac_select(good_count, n_points: int, model_points: int = 5, confidence: float = 0.99, max_iters: int = 200):
+    """RANSACPointSetRegistrator::run's choice over models in iteration order -> (kept model or -1, models looked at).
+    Host arithmetic inside the library; needs no device."""
+    g = np.ascontiguousarray(good_count, np.int32)
+    best, iters = C.c_int(-1), C.c_int(0)
+    rc = load().slamgpu_ransac_select(_p(g, C.c_int32), len(g), int(n_points), int(model_points), float(confidence),
+                                      int(max_iters), C.byref(best), C.byref(iters))
+    if rc != 0:
+        raise SlamGpuError(rc, load().slamgpu_last_error().decode())
+    return best.value, iters.value
 
 
 def device_count() -> int:
@@ -470,6 +493,56 @@ class Context:
 
     def bowdb_release(self, db_id: int):
         self._check(self._lib.slamgpu_bowdb_release(self._h, db_id))
+
+    # ---- PnP verification support ----
+    def pnp_assemble_batch_dev(self, d_match_train: int, d_frame_offset: int, n_frames: int, d_pairs: int, n_pairs: int,
+                               max_rows: int, d_row_pos: int, d_row_xy: int, d_out_object: int, d_out_image: int,
+                               d_out_query: int, d_out_count: int):
+        self._check(self._lib.slamgpu_pnp_assemble_batch_dev(self._h, d_match_train, d_frame_offset, n_frames, d_pairs,
+                                                             n_pairs, max_rows, d_row_pos, d_row_xy, d_out_object,
+                                                             d_out_image, d_out_query or None, d_out_count))
+
+    def pnp_score_dev(self, d_object: int, d_image: int, d_corr_begin: int, d_corr_count: int, n_problems: int,
+                      d_hyp_rt: int, d_hyp_problem: int, n_hyp: int, K4, reproj_error: float, d_out_count: int):
+        K4 = np.ascontiguousarray(K4, np.float64).reshape(4)
+        self._check(self._lib.slamgpu_pnp_score_dev(self._h, d_object, d_image, d_corr_begin, d_corr_count, n_problems,
+                                                    d_hyp_rt, d_hyp_problem, n_hyp, _p(K4, C.c_double),
+                                                    float(reproj_error), d_out_count))
+
+    def pnp_mask_dev(self, d_object: int, d_image: int, d_corr_begin: int, d_corr_count: int, n_problems: int,
+                     d_hyp_rt: int, d_sel_hyp: int, K4, reproj_error: float, d_out_mask: int, d_out_err: int = 0,
+                     d_out_inliers: int = 0):
+        K4 = np.ascontiguousarray(K4, np.float64).reshape(4)
+        self._check(self._lib.slamgpu_pnp_mask_dev(self._h, d_object, d_image, d_corr_begin, d_corr_count, n_problems,
+                                                   d_hyp_rt, d_sel_hyp, _p(K4, C.c_double), float(reproj_error),
+                                                   d_out_mask, d_out_err or None, d_out_inliers or None))
+
+    def pnp_ransac_score(self, objects, images, models, K4, reproj_error=4.0, confidence=0.99, model_points=5,
+                         max_iters=200):
+        """Score every RANSAC model of a batch of verify_pnp problems (src/LoopDetector.cpp:203-214).
+        objects[p] [n_p, 3] f32, images[p] [n_p, 2] f32, models[p] [h_p, 12] f64 (R row-major, t) in iteration order
+        -> list of (counts [h_p], kept model or -1, inliers, mask [n_p] u8) per problem."""
+        n = len(objects)
+        assert len(images) == n and len(models) == n
+        co = np.zeros(n + 1, np.int32)
+        ho = np.zeros(n + 1, np.int32)
+        for i in range(n):
+            co[i + 1] = co[i] + len(objects[i])
+            ho[i + 1] = ho[i] + len(models[i])
+        cat = lambda xs, w, dt: (np.ascontiguousarray(np.concatenate([np.asarray(x, dt).reshape(-1, w) for x in xs]), dt)
+                                 if n else np.zeros((0, w), dt))
+        obj, img, rt = cat(objects, 3, np.float32), cat(images, 2, np.float32), cat(models, 12, np.float64)
+        K4 = np.ascontiguousarray(K4, np.float64).reshape(4)
+        cnt = np.zeros(max(int(ho[-1]), 1), np.int32)
+        best = np.zeros(max(n, 1), np.int32)
+        inl = np.zeros(max(n, 1), np.int32)
+        mask = np.zeros(max(int(co[-1]), 1), np.uint8)
+        self._check(self._lib.slamgpu_pnp_ransac_score(self._h, _p(obj, C.c_float), _p(img, C.c_float), _p(co, C.c_int32),
+                                                       n, _p(rt, C.c_double), _p(ho, C.c_int32), _p(K4, C.c_double),
+                                                       float(reproj_error), float(confidence), int(model_points),
+                                                       int(max_iters), _p(cnt, C.c_int32), _p(best, C.c_int32),
+                                                       _p(inl, C.c_int32), _p(mask, C.c_uint8)))
+        return [(cnt[ho[i]:ho[i + 1]].copy(), int(best[i]), int(inl[i]), mask[co[i]:co[i + 1]].copy()) for i in range(n)]
 
     def match_projection_batch(self, frame_ids, nkps, set_id: int, poses, params: ProjParams, skip=None, order=None):
         """Frozen-snapshot batch over key frames -> list of (out_point, out_dist) per frame."""

@@ -348,7 +348,7 @@ int slamgpu_profile_enable(slamgpu_ctx* ctx, int on)
 int slamgpu_profile_read(slamgpu_ctx* ctx, int kernel, double* total_ms, int64_t* launches)
 {
     SG_CTX(ctx);
-    SG_CHECK(kernel >= SLAMGPU_KERNEL_BF_SCAN && kernel <= SLAMGPU_KERNEL_VOC_TRANSFORM, "unknown kernel id");
+    SG_CHECK(kernel >= SLAMGPU_KERNEL_BF_SCAN && kernel <= SLAMGPU_KERNEL_PNP_SCORE, "unknown kernel id");
     SG_CUDA(cudaStreamSynchronize(ctx->stream));
     double sum = 0.0;
     auto& v = ctx->prof_events[kernel];

@@ -144,7 +144,7 @@ struct slamgpu_ctx {
     int bf_engine = 0;        // SLAMGPU_BF_ENGINE=int|tc overrides the brute-force engine choice (0 = by size, 1 = int, 2 = tc)
     int tc_variant = 0;       // SLAMGPU_TC_VARIANT: debug switches of the tensor-core scan
     slamgpu::Arena d_exp;     // expanded (int8) descriptors of the tensor-core scan
-    std::vector<std::pair<cudaEvent_t, cudaEvent_t>> prof_events[3];   // per SLAMGPU_KERNEL_*
+    std::vector<std::pair<cudaEvent_t, cudaEvent_t>> prof_events[4];   // per SLAMGPU_KERNEL_*
     std::vector<cudaEvent_t> prof_pool;
     std::map<int, slamgpu::FrameDev> frames;
     std::map<int, slamgpu::PointSetDev> point_sets;
@@ -309,6 +309,19 @@ int voc_launch_bow_count(slamgpu_ctx* ctx, const int32_t* d_word, const int32_t*
 int voc_launch_score_l1(slamgpu_ctx* ctx, const int32_t* d_q_ids, const double* d_q_vals, int nq,
                         const int32_t* d_db_ids, const double* d_db_vals, const int32_t* d_db_offset, int n_db,
                         double* d_score);
+
+// ---- PnP verification support (pnp_kernels.cu) ------------------------------------------------
+int pnp_launch_score(slamgpu_ctx* ctx, const float* d_object, const float* d_image, const int32_t* d_corr_begin,
+                     const int32_t* d_corr_count, const double* d_hyp_rt, const int32_t* d_hyp_problem, int n_hyp,
+                     const double* K4, double reproj_error, int32_t* d_out_count);
+int pnp_launch_mask(slamgpu_ctx* ctx, const float* d_object, const float* d_image, const int32_t* d_corr_begin,
+                    const int32_t* d_corr_count, int n_problems, const double* d_hyp_rt, const int32_t* d_sel_hyp,
+                    const double* K4, double reproj_error, uint8_t* d_out_mask, float* d_out_err,
+                    int32_t* d_out_inliers);
+int pnp_launch_assemble(slamgpu_ctx* ctx, const int32_t* d_match_train, const int32_t* d_frame_offset,
+                        const int32_t* d_pairs, int n_pairs, int max_rows, const float* d_row_pos,
+                        const float* d_row_xy, float* d_out_object, float* d_out_image, int32_t* d_out_query,
+                        int32_t* d_out_count);
 
 int popc_microbench(slamgpu_ctx* ctx, double* popc_per_s, int* n_sm, double* sm_mhz_est);
 

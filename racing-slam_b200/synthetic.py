@@ -320,3 +320,35 @@ def vocabulary_queries(voc: dict, n: int, seed: int, flip: int = 40) -> np.ndarr
     leaves = np.nonzero(voc["word_id"] >= 0)[0]
     src = voc["desc"][rng.choice(leaves, n)]
     return flip_bits(src, rng.integers(0, flip + 1, n), rng)
+
+
+# ---- verify_pnp problems (src/LoopDetector.cpp:176-229) ----------------------------------------
+PNP_K4 = np.array([KITTI["fx"], KITTI["fy"], KITTI["cx"], KITTI["cy"]], np.float64)
+
+
+def pnp_problems(seed: int, sizes, n_models, noise: float = 1.0, outliers: float = 0.4):
+    """Synthetic verify_pnp problems: per problem n 3-D points in front of a camera with a random true pose, their
+    projections (+ Gaussian pixel noise, a fraction replaced by uniform outliers) and h pose models in iteration
+    order as [h, 12] doubles (R row-major, t): model 3, 10, 17 ... are the exact pose, the others are perturbed by
+    0 .. 4 steps (rotation entries 1.5e-3 per step, translation 2e-2 per step).
+    -> (objects [n, 3] f32 list, images [n, 2] f32 list, models [h, 12] f64 list)."""
+    rng = np.random.default_rng(seed)
+    objs, imgs, models = [], [], []
+    for n, h in zip(sizes, n_models):
+        obj = (rng.uniform(-8, 8, (n, 3)) + [0, 0, 25]).astype(np.float32)
+        R = rot_xyz(*rng.uniform(-0.2, 0.2, 3)).astype(np.float64)
+        t = rng.uniform(-0.5, 0.5, 3)
+        P = obj.astype(np.float64) @ R.T + t
+        img = np.stack([P[:, 0] / P[:, 2] * PNP_K4[0] + PNP_K4[2], P[:, 1] / P[:, 2] * PNP_K4[1] + PNP_K4[3]], 1)
+        img = (img + rng.normal(0, noise, img.shape)).astype(np.float32) if noise > 0 else img.astype(np.float32)
+        bad = rng.random(n) < outliers
+        img[bad] = rng.uniform(0, 1241, (int(bad.sum()), 2)).astype(np.float32)
+        step = (np.arange(h) + 2) % 5
+        step = np.where(np.arange(h) % 7 == 3, 0, step).astype(np.float64)[:, None]
+        rt = np.empty((h, 12), np.float64)
+        rt[:, :9] = R.reshape(1, 9) + rng.normal(0, 1.0, (h, 9)) * (1.5e-3 * step)
+        rt[:, 9:] = t[None, :] + rng.normal(0, 1.0, (h, 3)) * (2e-2 * step)
+        objs.append(obj)
+        imgs.append(img)
+        models.append(rt)
+    return objs, imgs, models

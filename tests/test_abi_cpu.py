@@ -97,3 +97,20 @@ def test_last_error_and_null_checks(pkg):
     assert lib.slamgpu_sync(None) == pkg.binding.ERR_INVALID
     assert lib.slamgpu_kd_build_host(None, -1, None) == pkg.binding.ERR_INVALID
     assert lib.slamgpu_destroy(None) == pkg.binding.OK
+
+
+def test_ransac_select_is_host_arithmetic_and_equals_the_oracle(pkg, oracle):
+    """slamgpu_ransac_select (RANSAC's model choice) is sequential host arithmetic inside the
+    library -- no device needed; 400 random count sequences against the oracle's restatement."""
+    rng = np.random.default_rng(0)
+    for i in range(400):
+        n_pts = int(rng.integers(1, 500))
+        n_models = int(rng.integers(0, 220))
+        hi = int(rng.integers(1, n_pts + 1))
+        cnt = rng.integers(0, hi + 1, n_models).astype(np.int32)
+        mp = int(rng.integers(3, 7))
+        conf = float(rng.choice([0.5, 0.9, 0.99, 0.999]))
+        iters = int(rng.choice([1, 10, 200]))
+        assert pkg.binding.ransac_select(cnt, n_pts, mp, conf, iters) == oracle.ransac_select(cnt, n_pts, mp, conf, iters), i
+    assert pkg.binding.ransac_select([], 10) == (-1, 0)
+    assert pkg.binding.ransac_select([5, 6], 0) == (-1, 0)

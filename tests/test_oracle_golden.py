@@ -195,3 +195,39 @@ def test_voc_bow_weightings_and_norms(oracle):
     assert v.tolist() == [4.0 / 3, 1.5 / 3, 1.5 / 3]
     ids, v = oracle.voc_bow(word, w, oracle.BINARY, oracle.NORM_L2)
     assert np.allclose((v * v).sum(), 1.0)
+
+
+# ---- PnP verification support -----------------------------------------------------------------
+@pytest.mark.parametrize("name", golden_names("pnp_"))
+def test_pnp_projection_and_error_vs_cv2_fixtures(oracle, name):
+    """The oracle's projectPoints / squared-error restatement against cv2 4.13.0's projections, bit for bit."""
+    g = golden(name)
+    for h in range(len(g["rt"])):
+        uv = oracle.pnp_project(g["rt"][h], g["K4"], g["object"])
+        assert np.array_equal(uv.view(np.uint32), g["uv"][h].view(np.uint32))
+        c, err, mask = oracle.pnp_score(g["rt"][h], g["K4"], g["object"], g["image"], 4.0)
+        assert np.array_equal(err.view(np.uint32), g["err_np"][h].view(np.uint32))
+        with np.errstate(all="ignore"):
+            want = g["err_np"][h] <= np.float32(16.0)
+        assert np.array_equal(mask, want.astype(np.uint8)) and c == int(want.sum())
+
+
+def test_ransac_update_num_iters_known_values(oracle):
+    # log(1 - 0.99) / log(1 - (1 - ep)^5), rounded half to even; clamped to the current bound
+    assert oracle.ransac_update_num_iters(0.99, 0.5, 5, 200) == 145
+    assert oracle.ransac_update_num_iters(0.99, 0.0, 5, 200) == 0          # all inliers: denom = 0 -> stop
+    assert oracle.ransac_update_num_iters(0.99, 1.0, 5, 200) == 200        # no inliers: keep the bound
+    assert oracle.ransac_update_num_iters(0.99, 0.9, 5, 200) == 200        # would need 460k: clamped
+    assert oracle.ransac_update_num_iters(0.99, 0.2, 5, 200) == 12
+    assert oracle.ransac_update_num_iters(0.99, 0.5, 5, 100) == 100
+
+
+def test_ransac_select_rule(oracle):
+    # first strictly better model wins; a model needs more than model_points - 1 inliers; the bound shrinks
+    assert oracle.ransac_select([3, 4, 4, 2], 100) == (-1, 4)
+    assert oracle.ransac_select([10, 10, 9], 100) == (0, 3)
+    assert oracle.ransac_select([10, 11, 11], 100) == (1, 3)
+    best, iters = oracle.ransac_select([80] + [100] * 199, 100)            # 80 % inliers -> 12 iterations
+    assert best == 1 and iters == 2                                        # model 1 is perfect: bound drops to 0
+    best, iters = oracle.ransac_select([80] + [10] * 11 + [100] * 100, 100)
+    assert (best, iters) == (0, 12)                                        # the perfect models come too late
