@@ -387,6 +387,36 @@ def run_ours(args, rank, local_rank, world):
     # the two API forms ran the same last step: their per-pair match counts must agree
     assert np.array_equal(np.diff(o_off.astype(np.int64)), dev_counts_last), "host and device API forms disagree"
     checksum = int(sum_over_ranks(float(dev_counts_last.sum())))
+    # ---- the same steps against a RESIDENT key-frame database (slamgpu_kfdb_*: every key frame uploaded once, when
+    # it is appended, as LoopDetector keeps them; a step then sends its pair list only) ----
+    KFDB = 1
+    for f in range(args.frames):
+        ctx.kfdb_append(KFDB, db.reshape(args.frames, -1, 32)[f])
+
+    def step_resident(s):
+        rc = lib.slamgpu_kfdb_match_pairs(ctx._h, KFDB, C.cast(h_pairs[s].data_ptr(), i32p), n, MAX_DIST, RATIO,
+                                          o_off.ctypes.data_as(i32p), o_q.ctypes.data_as(i32p),
+                                          o_t.ctypes.data_as(i32p), cap, C.byref(total))
+        ctx._check(rc)
+        return int(total.value)
+
+    for s in range(W):
+        step_resident(s)
+    barrier()
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    d2h_res = 0
+    for s in range(K):
+        d2h_res += 4 * (n + 1) + 8 * step_resident(W + s)
+    torch.cuda.synchronize()
+    t_res = max_over_ranks(time.perf_counter() - t0)
+    barrier()
+    assert np.array_equal(np.diff(o_off.astype(np.int64)), dev_counts_last), "resident database form disagrees"
+    ctx.kfdb_release(KFDB)
+    e2e_resident = {"value": world * n * K * per_pair / t_res / 1e9, "unit": UNIT, "h2d_bytes_per_step": 8 * n,
+                    "d2h_bytes_per_step": d2h_res // K, "ms_per_step": t_res / K * 1e3,
+                    "api": "slamgpu_kfdb_match_pairs (key frames appended once before the clock; pair list up, match "
+                           "lists down every step)"}
     # every rank takes part in the sharded C4 batch (collectives inside): before the non-zero ranks leave
     c4_line = c4_sharded(ctx, pkg, rank, world, barrier, max_over_ranks, sum_over_ranks)
 
@@ -454,6 +484,7 @@ def run_ours(args, rank, local_rank, world):
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d_per_step),
                 "d2h_bytes_per_step": int(d2h // K), "ms_per_step": t_e2e / K * 1e3,
                 "api": "slamgpu_match_descriptors_batch (host buffers; descriptors re-uploaded every step)"},
+        "e2e_resident_database": e2e_resident,
         "gpu_launches": int(gpu_launches), "roofline": roofline, "clocks": clocks,
         "matches_last_step_all_ranks": checksum,
     }

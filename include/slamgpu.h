@@ -126,6 +126,19 @@ SLAMGPU_API int slamgpu_match_descriptors_batch(slamgpu_ctx* ctx, const uint8_t*
                                     int32_t* out_offset, int32_t* out_query, int32_t* out_train, int64_t capacity,
                                     int64_t* out_total);
 
+/* Resident key-frame database: LoopDetector keeps every key frame it has seen and verifies the newest one
+ * against retrieved candidates (src/LoopDetector.cpp:314-330 the store, :176-229 verify_pnp ->
+ * match_descriptors once per (query, candidate)).  A key frame's descriptors are uploaded ONCE, when it is
+ * appended; the match call then sends only the pair list.  Frames are numbered 0, 1, ... in append order
+ * (*out_frame, may be NULL); same results, limits and errors as slamgpu_match_descriptors_batch on the
+ * concatenation of the appended frames. */
+SLAMGPU_API int slamgpu_kfdb_append(slamgpu_ctx* ctx, int db_id, const uint8_t* desc, int n_rows, int* out_frame);
+SLAMGPU_API int slamgpu_kfdb_count(slamgpu_ctx* ctx, int db_id, int* n_frames, int64_t* n_rows);
+SLAMGPU_API int slamgpu_kfdb_match_pairs(slamgpu_ctx* ctx, int db_id, const int32_t* pairs, int n_pairs, float max_dist,
+                             float ratio, int32_t* out_offset, int32_t* out_query, int32_t* out_train,
+                             int64_t capacity, int64_t* out_total);
+SLAMGPU_API int slamgpu_kfdb_release(slamgpu_ctx* ctx, int db_id);
+
 /* ------------------------------------------------------------------------------------------
  * Projection-guided search
  * ---------------------------------------------------------------------------------------- */

@@ -9,5 +9,5 @@ The directory name carries a hyphen; `import racing_slam_b200` works through the
 at the repository root (racing_slam_b200.py).
 """
 from . import binding, matcher, sharding, synthetic  # noqa: F401
-from .binding import Context, ProjParams, SlamGpuError  # noqa: F401
+from .binding import Context, ProjParams, SlamGpuError, pinned_empty  # noqa: F401
 from .matcher import MapMatcher, match_features  # noqa: F401

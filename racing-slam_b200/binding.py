@@ -65,6 +65,11 @@ SIGNATURES = {
                                                       C.c_int, C.c_float, C.c_float, C.c_void_p, C.c_void_p]),
     "slamgpu_match_descriptors_batch": (C.c_int, [_ctx, _u8p, _i32p, C.c_int, _i32p, C.c_int, C.c_float, C.c_float,
                                                   _i32p, _i32p, _i32p, C.c_int64, _i64p]),
+    "slamgpu_kfdb_append": (C.c_int, [_ctx, C.c_int, _u8p, C.c_int, C.POINTER(C.c_int)]),
+    "slamgpu_kfdb_count": (C.c_int, [_ctx, C.c_int, C.POINTER(C.c_int), _i64p]),
+    "slamgpu_kfdb_match_pairs": (C.c_int, [_ctx, C.c_int, _i32p, C.c_int, C.c_float, C.c_float, _i32p, _i32p, _i32p,
+                                           C.c_int64, _i64p]),
+    "slamgpu_kfdb_release": (C.c_int, [_ctx, C.c_int]),
     "slamgpu_frame_upload": (C.c_int, [_ctx, C.c_int, C.c_int, _f32p, _u8p, _u32p, _u8p]),
     "slamgpu_frame_set_matched": (C.c_int, [_ctx, C.c_int, _u8p]),
     "slamgpu_frame_release": (C.c_int, [_ctx, C.c_int]),
@@ -163,6 +168,26 @@ def ransac_select(good_count, n_points: int, model_points: int = 5, confidence: 
     if rc != 0:
         raise SlamGpuError(rc, load().slamgpu_last_error().decode())
     return best.value, iters.value
+
+
+SLAMGPU_MAX_ROWS_DEFAULT = 4096     # default per-pair capacity of kfdb_match_pairs when the caller gives none
+
+
+def pinned_empty(shape, dtype) -> np.ndarray:
+    """A numpy array over page-locked host memory from slamgpu_host_alloc (freed when the array and its views are
+    collected).  Descriptor sets and result arrays handed to the host-buffer calls from such arrays are copied by
+    DMA directly, without the driver's staging copy."""
+    import weakref
+    dtype = np.dtype(dtype)
+    n = int(np.prod(shape))
+    lib = load()
+    ptr = C.c_void_p()
+    rc = lib.slamgpu_host_alloc(C.byref(ptr), max(n * dtype.itemsize, 1))
+    if rc != OK:
+        raise SlamGpuError(rc, lib.slamgpu_last_error().decode())
+    buf = (C.c_uint8 * max(n * dtype.itemsize, 1)).from_address(ptr.value)
+    weakref.finalize(buf, lib.slamgpu_host_free, C.c_void_p(ptr.value))
+    return np.frombuffer(buf, dtype=dtype, count=n).reshape(shape)
 
 
 def device_count() -> int:
@@ -270,7 +295,7 @@ class Context:
     def match_descriptors_batch(self, desc, frame_offset, pairs, max_dist=64.0, ratio=0.75, capacity=None, out=None):
         """-> (offset [n_pairs+1], query_idx, train_idx): per pair (query_frame, train_frame) the
         compacted match_descriptors list.  out = (query_idx, train_idx) int32 arrays to fill (pinned ones receive
-        the device copies directly); their length is then the capacity."""
+        the device copies directly); their length is then the capacity and the returned lists are views of them."""
         desc = _desc(desc)
         frame_offset = np.ascontiguousarray(frame_offset, np.int32)
         pairs = np.ascontiguousarray(pairs, np.int32).reshape(-1, 2)
@@ -291,6 +316,47 @@ class Context:
             self._h, _p(desc, C.c_uint8), _p(frame_offset, C.c_int32), len(frame_offset) - 1, _p(pairs, C.c_int32),
             n_pairs, max_dist, ratio, _p(off, C.c_int32), _p(oq, C.c_int32), _p(ot, C.c_int32), capacity,
             C.byref(total)))
+        if out is not None:                      # the caller's arrays: views, no copy
+            return off, oq[:total.value], ot[:total.value]
+        return off, oq[:total.value].copy(), ot[:total.value].copy()
+
+    # ---- resident key-frame database ----
+    def kfdb_append(self, db_id: int, desc) -> int:
+        """Append one key frame's descriptors (uploaded once) -> its frame number."""
+        desc = _desc(desc)
+        f = C.c_int(-1)
+        self._check(self._lib.slamgpu_kfdb_append(self._h, db_id, _p(desc, C.c_uint8), len(desc), C.byref(f)))
+        return f.value
+
+    def kfdb_count(self, db_id: int):
+        n, rows = C.c_int(0), C.c_int64(0)
+        self._check(self._lib.slamgpu_kfdb_count(self._h, db_id, C.byref(n), C.byref(rows)))
+        return n.value, rows.value
+
+    def kfdb_release(self, db_id: int):
+        self._check(self._lib.slamgpu_kfdb_release(self._h, db_id))
+
+    def kfdb_match_pairs(self, db_id: int, pairs, max_dist=64.0, ratio=0.75, capacity=None, out=None):
+        """match_descriptors for (query_frame, train_frame) pairs of a resident database; same return as
+        match_descriptors_batch.  Only the pair list goes up."""
+        pairs = np.ascontiguousarray(pairs, np.int32).reshape(-1, 2)
+        n_pairs = len(pairs)
+        off = np.zeros(n_pairs + 1, np.int32)
+        if out is not None:
+            oq, ot = out
+            assert oq.dtype == np.int32 and ot.dtype == np.int32 and oq.flags.c_contiguous and ot.flags.c_contiguous
+            capacity = min(len(oq), len(ot))
+        else:
+            if capacity is None:
+                capacity = n_pairs * SLAMGPU_MAX_ROWS_DEFAULT
+            oq = np.zeros(max(capacity, 1), np.int32)
+            ot = np.zeros(max(capacity, 1), np.int32)
+        total = C.c_int64(0)
+        self._check(self._lib.slamgpu_kfdb_match_pairs(
+            self._h, db_id, _p(pairs, C.c_int32), n_pairs, max_dist, ratio, _p(off, C.c_int32), _p(oq, C.c_int32),
+            _p(ot, C.c_int32), capacity, C.byref(total)))
+        if out is not None:                      # the caller's arrays: views, no copy
+            return off, oq[:total.value], ot[:total.value]
         return off, oq[:total.value].copy(), ot[:total.value].copy()
 
     # ---- brute force, device buffers (raw pointers; stream-ordered, no sync) ----

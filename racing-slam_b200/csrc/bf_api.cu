@@ -370,6 +370,129 @@ int fetch_pair(slamgpu_ctx* ctx, const PairIo& io, const int32_t** h_a, const in
     return SLAMGPU_OK;
 }
 
+// The host-buffer batch call behind slamgpu_match_descriptors_batch (descriptors uploaded per call) and
+// slamgpu_kfdb_match_pairs (d_desc_res / d_off_res: the resident database; nothing but the pair list goes up).
+int batch_host(slamgpu_ctx* ctx, const uint8_t* desc, const uint8_t* d_desc_res, const int32_t* d_off_res,
+               const int32_t* frame_offset, int n_frames, int max_rows, const int32_t* pairs, int n_pairs, float max_dist,
+               float ratio, int32_t* out_offset, int32_t* out_query, int32_t* out_train, int64_t capacity,
+               int64_t* out_total)
+{
+    const size_t n_rows = static_cast<size_t>(frame_offset[n_frames]);
+    if (max_rows == 0) {   // every frame is empty: no matches (src/MapMatcher.cpp:139-141)
+        std::memset(out_offset, 0, sizeof(int32_t) * (static_cast<size_t>(n_pairs) + 1));
+        return SLAMGPU_OK;
+    }
+    const int slice = std::min(n_pairs, slice_for(ctx, max_rows));
+    const bool resident = d_desc_res != nullptr;
+    const size_t b_desc = resident ? 0 : Carver::padded(n_rows * 32),
+                 b_off = resident ? 0 : Carver::padded(sizeof(int32_t) * (n_frames + 1)), b_pairs = Carver::padded(sizeof(int32_t) * 2 * n_pairs);
+    const size_t b_rows = Carver::padded(sizeof(int32_t) * static_cast<size_t>(slice) * std::max(max_rows, 1)),
+                 b_count = Carver::padded(sizeof(int32_t) * n_pairs),
+                 b_offset = Carver::padded(sizeof(int32_t) * (static_cast<size_t>(n_pairs) + 1)),
+                 b_list = Carver::padded(sizeof(int32_t) * static_cast<size_t>(capacity));
+    SG_TRY(ensure_device_io(ctx, b_desc + b_off + b_pairs + b_rows + b_count + b_offset + 2 * b_list + 256));
+    SG_TRY(ensure_host_stage(ctx, std::max(b_desc + b_off + b_pairs, b_offset + 2 * b_list) + 256));
+    Carver dio(ctx->d_io.ptr);
+    const uint8_t* d_desc = d_desc_res;
+    const int32_t* d_off = d_off_res;
+    if (!resident) {
+        uint8_t* dd = dio.take<uint8_t>(n_rows * 32);
+        int32_t* doff = dio.take<int32_t>(n_frames + 1);
+        SG_TRY(upload(ctx, dd, desc, n_rows * 32, 0));
+        SG_TRY(upload(ctx, doff, frame_offset, sizeof(int32_t) * (n_frames + 1), b_desc));
+        d_desc = dd;
+        d_off = doff;
+    }
+    int32_t* d_pairs = dio.take<int32_t>(2 * static_cast<size_t>(n_pairs));
+    int32_t* d_rows = dio.take<int32_t>(static_cast<size_t>(slice) * std::max(max_rows, 1));
+    int32_t* d_count = dio.take<int32_t>(n_pairs);
+    int32_t* d_offset = dio.take<int32_t>(static_cast<size_t>(n_pairs) + 1);
+    int32_t* d_ql = dio.take<int32_t>(static_cast<size_t>(capacity));
+    int32_t* d_tl = dio.take<int32_t>(static_cast<size_t>(capacity));
+    SG_TRY(upload(ctx, d_pairs, pairs, sizeof(int32_t) * 2 * n_pairs, b_desc + b_off));
+    // The lists come back slice by slice: once a slice's kernels are done its offsets are copied out on a second
+    // stream, the host reads them, queues the copy of that slice's piece of the two lists and moves the previous
+    // piece into the caller's arrays -- all while the GPU scans the later slices.  Pinned caller arrays
+    // (slamgpu_host_alloc) receive the copies directly.
+    if (ctx->copy_stream == nullptr) SG_CUDA(cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking));
+    const int n_slices = (n_pairs + slice - 1) / slice;
+    while (ctx->slice_events.size() < 3 * static_cast<size_t>(n_slices)) {
+        cudaEvent_t e = nullptr;
+        SG_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+        ctx->slice_events.push_back(e);
+    }
+    uint8_t* hs = static_cast<uint8_t*>(ctx->h_stage.ptr);
+    int32_t* h_offset = reinterpret_cast<int32_t*>(hs);
+    const bool direct = capacity > 0 && is_pinned(out_query) && is_pinned(out_train);
+    int32_t* h_ql = direct ? out_query : reinterpret_cast<int32_t*>(hs + b_offset);
+    int32_t* h_tl = direct ? out_train : reinterpret_cast<int32_t*>(hs + b_offset + b_list);
+    // the uploads above may have been staged through the same pinned block: the downloads must not start
+    // before they have been consumed (stream order covers it: slice 0 runs after the uploads)
+    int slice_no = 0;
+    const std::function<int(int, int)> after_slice = [&](int p0, int np) -> int {
+        cudaEvent_t done = ctx->slice_events[3 * slice_no], off_ready = ctx->slice_events[3 * slice_no + 1];
+        ++slice_no;
+        SG_CUDA(cudaEventRecord(done, ctx->stream));
+        SG_CUDA(cudaStreamWaitEvent(ctx->copy_stream, done, 0));
+        SG_CUDA(cudaMemcpyAsync(h_offset + p0 + 1, d_offset + p0 + 1, sizeof(int32_t) * np, cudaMemcpyDeviceToHost,
+                                ctx->copy_stream));
+        SG_CUDA(cudaEventRecord(off_ready, ctx->copy_stream));
+        return SLAMGPU_OK;
+    };
+    const int rc = batch_core(ctx, d_desc, d_off, n_frames, d_pairs, n_pairs, max_rows, max_dist, ratio, d_rows, d_count,
+                              d_offset, d_ql, d_tl, capacity, slice, &after_slice);
+    if (rc != SLAMGPU_OK) {
+        cudaStreamSynchronize(ctx->copy_stream);
+        return rc;
+    }
+    h_offset[0] = 0;
+    bool overflow = false;
+    int64_t begin = 0, prev_begin = 0, prev_end = 0;
+    int prev = -1;
+    auto unstage = [&](int s, int64_t b, int64_t e) -> int {      // piece [b, e) of slice s into the caller's arrays
+        SG_CUDA(cudaEventSynchronize(ctx->slice_events[3 * s + 2]));
+        if (!direct && e > b) {
+            std::memcpy(out_query + b, h_ql + b, sizeof(int32_t) * (e - b));
+            std::memcpy(out_train + b, h_tl + b, sizeof(int32_t) * (e - b));
+        }
+        return SLAMGPU_OK;
+    };
+    for (int s = 0; s < slice_no; ++s) {
+        const int p0 = s * slice, np = std::min(slice, n_pairs - p0);
+        SG_CUDA(cudaEventSynchronize(ctx->slice_events[3 * s + 1]));
+        const int64_t end = h_offset[p0 + np];
+        overflow = overflow || end > capacity;
+        if (!overflow) {
+            if (end > begin) {
+                SG_CUDA(cudaMemcpyAsync(h_ql + begin, d_ql + begin, sizeof(int32_t) * (end - begin), cudaMemcpyDeviceToHost,
+                                        ctx->copy_stream));
+                SG_CUDA(cudaMemcpyAsync(h_tl + begin, d_tl + begin, sizeof(int32_t) * (end - begin), cudaMemcpyDeviceToHost,
+                                        ctx->copy_stream));
+            }
+            SG_CUDA(cudaEventRecord(ctx->slice_events[3 * s + 2], ctx->copy_stream));
+            if (prev >= 0) SG_TRY(unstage(prev, prev_begin, prev_end));
+            prev = s;
+            prev_begin = begin;
+            prev_end = end;
+        }
+        begin = end;
+    }
+    if (prev >= 0) SG_TRY(unstage(prev, prev_begin, prev_end));
+    SG_CUDA(cudaStreamSynchronize(ctx->copy_stream));
+    SG_CUDA(cudaStreamSynchronize(ctx->stream));
+    std::memcpy(out_offset, h_offset, sizeof(int32_t) * (static_cast<size_t>(n_pairs) + 1));
+    *out_total = out_offset[n_pairs];
+    if (overflow) return fail(SLAMGPU_ERR_NOMEM, "match list capacity too small; *out_total holds the size needed");
+    return SLAMGPU_OK;
+}
+
+void free_kfdb(KfDbDev& d)
+{
+    if (d.desc) cudaFree(d.desc);
+    if (d.offset) cudaFree(d.offset);
+    d = KfDbDev();
+}
+
 } // namespace
 
 extern "C" {
@@ -483,108 +606,107 @@ int slamgpu_match_descriptors_batch(slamgpu_ctx* ctx, const uint8_t* desc, const
     }
     SG_CHECK(max_rows <= SLAMGPU_MAX_TRAIN, "frame larger than SLAMGPU_MAX_TRAIN");
     for (int p = 0; p < 2 * n_pairs; ++p) SG_CHECK(pairs[p] >= 0 && pairs[p] < n_frames, "pair names an unknown frame");
-    const size_t n_rows = static_cast<size_t>(frame_offset[n_frames]);
-    SG_CHECK(n_rows == 0 || desc != nullptr, "null descriptors");
+    SG_CHECK(frame_offset[n_frames] == 0 || desc != nullptr, "null descriptors");
+    return batch_host(ctx, desc, nullptr, nullptr, frame_offset, n_frames, max_rows, pairs, n_pairs, max_dist, ratio,
+                      out_offset, out_query, out_train, capacity, out_total);
+}
 
-    if (max_rows == 0) {   // every frame is empty: no matches (src/MapMatcher.cpp:139-141)
-        std::memset(out_offset, 0, sizeof(int32_t) * (static_cast<size_t>(n_pairs) + 1));
-        return SLAMGPU_OK;
-    }
-    const int slice = std::min(n_pairs, slice_for(ctx, max_rows));
-    const size_t b_desc = Carver::padded(n_rows * 32), b_off = Carver::padded(sizeof(int32_t) * (n_frames + 1)),
-                 b_pairs = Carver::padded(sizeof(int32_t) * 2 * n_pairs);
-    const size_t b_rows = Carver::padded(sizeof(int32_t) * static_cast<size_t>(slice) * std::max(max_rows, 1)),
-                 b_count = Carver::padded(sizeof(int32_t) * n_pairs),
-                 b_offset = Carver::padded(sizeof(int32_t) * (static_cast<size_t>(n_pairs) + 1)),
-                 b_list = Carver::padded(sizeof(int32_t) * static_cast<size_t>(capacity));
-    SG_TRY(ensure_device_io(ctx, b_desc + b_off + b_pairs + b_rows + b_count + b_offset + 2 * b_list + 256));
-    SG_TRY(ensure_host_stage(ctx, std::max(b_desc + b_off + b_pairs, b_offset + 2 * b_list) + 256));
-    Carver dio(ctx->d_io.ptr);
-    uint8_t* d_desc = dio.take<uint8_t>(n_rows * 32);
-    int32_t* d_off = dio.take<int32_t>(n_frames + 1);
-    int32_t* d_pairs = dio.take<int32_t>(2 * static_cast<size_t>(n_pairs));
-    int32_t* d_rows = dio.take<int32_t>(static_cast<size_t>(slice) * std::max(max_rows, 1));
-    int32_t* d_count = dio.take<int32_t>(n_pairs);
-    int32_t* d_offset = dio.take<int32_t>(static_cast<size_t>(n_pairs) + 1);
-    int32_t* d_ql = dio.take<int32_t>(static_cast<size_t>(capacity));
-    int32_t* d_tl = dio.take<int32_t>(static_cast<size_t>(capacity));
-    SG_TRY(upload(ctx, d_desc, desc, n_rows * 32, 0));
-    SG_TRY(upload(ctx, d_off, frame_offset, sizeof(int32_t) * (n_frames + 1), b_desc));
-    SG_TRY(upload(ctx, d_pairs, pairs, sizeof(int32_t) * 2 * n_pairs, b_desc + b_off));
-    // The lists come back slice by slice: once a slice's kernels are done its offsets are copied out on a second
-    // stream, the host reads them, queues the copy of that slice's piece of the two lists and moves the previous
-    // piece into the caller's arrays -- all while the GPU scans the later slices.  Pinned caller arrays
-    // (slamgpu_host_alloc) receive the copies directly.
-    if (ctx->copy_stream == nullptr) SG_CUDA(cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking));
-    const int n_slices = (n_pairs + slice - 1) / slice;
-    while (ctx->slice_events.size() < 3 * static_cast<size_t>(n_slices)) {
-        cudaEvent_t e = nullptr;
-        SG_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
-        ctx->slice_events.push_back(e);
-    }
-    uint8_t* hs = static_cast<uint8_t*>(ctx->h_stage.ptr);
-    int32_t* h_offset = reinterpret_cast<int32_t*>(hs);
-    const bool direct = capacity > 0 && is_pinned(out_query) && is_pinned(out_train);
-    int32_t* h_ql = direct ? out_query : reinterpret_cast<int32_t*>(hs + b_offset);
-    int32_t* h_tl = direct ? out_train : reinterpret_cast<int32_t*>(hs + b_offset + b_list);
-    // the uploads above may have been staged through the same pinned block: the downloads must not start
-    // before they have been consumed (stream order covers it: slice 0 runs after the uploads)
-    int slice_no = 0;
-    const std::function<int(int, int)> after_slice = [&](int p0, int np) -> int {
-        cudaEvent_t done = ctx->slice_events[3 * slice_no], off_ready = ctx->slice_events[3 * slice_no + 1];
-        ++slice_no;
-        SG_CUDA(cudaEventRecord(done, ctx->stream));
-        SG_CUDA(cudaStreamWaitEvent(ctx->copy_stream, done, 0));
-        SG_CUDA(cudaMemcpyAsync(h_offset + p0 + 1, d_offset + p0 + 1, sizeof(int32_t) * np, cudaMemcpyDeviceToHost,
-                                ctx->copy_stream));
-        SG_CUDA(cudaEventRecord(off_ready, ctx->copy_stream));
-        return SLAMGPU_OK;
-    };
-    const int rc = batch_core(ctx, d_desc, d_off, n_frames, d_pairs, n_pairs, max_rows, max_dist, ratio, d_rows, d_count,
-                              d_offset, d_ql, d_tl, capacity, slice, &after_slice);
-    if (rc != SLAMGPU_OK) {
-        cudaStreamSynchronize(ctx->copy_stream);
-        return rc;
-    }
-    h_offset[0] = 0;
-    bool overflow = false;
-    int64_t begin = 0, prev_begin = 0, prev_end = 0;
-    int prev = -1;
-    auto unstage = [&](int s, int64_t b, int64_t e) -> int {      // piece [b, e) of slice s into the caller's arrays
-        SG_CUDA(cudaEventSynchronize(ctx->slice_events[3 * s + 2]));
-        if (!direct && e > b) {
-            std::memcpy(out_query + b, h_ql + b, sizeof(int32_t) * (e - b));
-            std::memcpy(out_train + b, h_tl + b, sizeof(int32_t) * (e - b));
+// ---- resident key-frame database ---------------------------------------------------------------
+
+int slamgpu_kfdb_append(slamgpu_ctx* ctx, int db_id, const uint8_t* desc, int n_rows, int* out_frame)
+{
+    SG_CTX(ctx);
+    SG_CHECK(n_rows >= 0, "negative row count");
+    SG_CHECK(n_rows == 0 || desc != nullptr, "null descriptors");
+    SG_CHECK(n_rows <= SLAMGPU_MAX_TRAIN, "frame larger than SLAMGPU_MAX_TRAIN");
+    KfDbDev& d = ctx->kf_dbs[db_id];
+    if (d.h_offset.empty()) d.h_offset.push_back(0);
+    const int n_frames = static_cast<int>(d.h_offset.size()) - 1;
+    const int64_t rows = d.h_offset.back();
+    SG_CHECK(rows + n_rows <= 0x7FFFFFFF, "key-frame database too large");
+    if (n_frames + 1 > d.cap_frames) {      // grow geometrically; the live part moves device-to-device
+        const int cap = std::max(1024, 2 * d.cap_frames);
+        int32_t* p = nullptr;
+        SG_CUDA(cudaMalloc(&p, (static_cast<size_t>(cap) + 1) * sizeof(int32_t)));
+        if (d.offset) {
+            SG_CUDA(cudaMemcpyAsync(p, d.offset, (static_cast<size_t>(n_frames) + 1) * 4, cudaMemcpyDeviceToDevice, ctx->stream));
+            SG_CUDA(cudaStreamSynchronize(ctx->stream));
+            cudaFree(d.offset);
+        } else {
+            SG_CUDA(cudaMemsetAsync(p, 0, 4, ctx->stream));
         }
-        return SLAMGPU_OK;
-    };
-    for (int s = 0; s < slice_no; ++s) {
-        const int p0 = s * slice, np = std::min(slice, n_pairs - p0);
-        SG_CUDA(cudaEventSynchronize(ctx->slice_events[3 * s + 1]));
-        const int64_t end = h_offset[p0 + np];
-        overflow = overflow || end > capacity;
-        if (!overflow) {
-            if (end > begin) {
-                SG_CUDA(cudaMemcpyAsync(h_ql + begin, d_ql + begin, sizeof(int32_t) * (end - begin), cudaMemcpyDeviceToHost,
-                                        ctx->copy_stream));
-                SG_CUDA(cudaMemcpyAsync(h_tl + begin, d_tl + begin, sizeof(int32_t) * (end - begin), cudaMemcpyDeviceToHost,
-                                        ctx->copy_stream));
-            }
-            SG_CUDA(cudaEventRecord(ctx->slice_events[3 * s + 2], ctx->copy_stream));
-            if (prev >= 0) SG_TRY(unstage(prev, prev_begin, prev_end));
-            prev = s;
-            prev_begin = begin;
-            prev_end = end;
-        }
-        begin = end;
+        d.offset = p;
+        d.cap_frames = cap;
     }
-    if (prev >= 0) SG_TRY(unstage(prev, prev_begin, prev_end));
-    SG_CUDA(cudaStreamSynchronize(ctx->copy_stream));
-    SG_CUDA(cudaStreamSynchronize(ctx->stream));
-    std::memcpy(out_offset, h_offset, sizeof(int32_t) * (static_cast<size_t>(n_pairs) + 1));
-    *out_total = out_offset[n_pairs];
-    if (overflow) return fail(SLAMGPU_ERR_NOMEM, "match list capacity too small; *out_total holds the size needed");
+    if (rows + n_rows > d.cap_rows) {
+        const int64_t cap = std::max<int64_t>(std::max<int64_t>(1 << 20, rows + n_rows), 2 * d.cap_rows);
+        uint8_t* p = nullptr;
+        const cudaError_t e = cudaMalloc(&p, static_cast<size_t>(cap) * 32);
+        if (e != cudaSuccess) {
+            cudaGetLastError();
+            return fail(SLAMGPU_ERR_NOMEM, std::string("key-frame database growth failed: ") + cudaGetErrorString(e));
+        }
+        if (rows) {
+            SG_CUDA(cudaMemcpyAsync(p, d.desc, static_cast<size_t>(rows) * 32, cudaMemcpyDeviceToDevice, ctx->stream));
+            SG_CUDA(cudaStreamSynchronize(ctx->stream));
+        }
+        if (d.desc) cudaFree(d.desc);
+        d.desc = p;
+        d.cap_rows = cap;
+    }
+    const int32_t end = static_cast<int32_t>(rows + n_rows);
+    if (n_rows) {
+        SG_TRY(ensure_host_stage(ctx, static_cast<size_t>(n_rows) * 32 + 256));
+        SG_TRY(upload(ctx, d.desc + static_cast<size_t>(rows) * 32, desc, static_cast<size_t>(n_rows) * 32, 0));
+    }
+    SG_CUDA(cudaMemcpyAsync(d.offset + n_frames + 1, &end, sizeof(int32_t), cudaMemcpyHostToDevice, ctx->stream));
+    SG_CUDA(cudaStreamSynchronize(ctx->stream));       // the caller's rows and `end` have been consumed
+    d.h_offset.push_back(end);
+    d.max_rows = std::max(d.max_rows, n_rows);
+    if (out_frame) *out_frame = n_frames;
     return SLAMGPU_OK;
+}
+
+int slamgpu_kfdb_count(slamgpu_ctx* ctx, int db_id, int* n_frames, int64_t* n_rows)
+{
+    SG_CHECK(ctx != nullptr, "null context");
+    auto it = ctx->kf_dbs.find(db_id);
+    const bool have = it != ctx->kf_dbs.end() && !it->second.h_offset.empty();
+    if (n_frames) *n_frames = have ? static_cast<int>(it->second.h_offset.size()) - 1 : 0;
+    if (n_rows) *n_rows = have ? it->second.h_offset.back() : 0;
+    return SLAMGPU_OK;
+}
+
+int slamgpu_kfdb_release(slamgpu_ctx* ctx, int db_id)
+{
+    SG_CTX(ctx);
+    auto it = ctx->kf_dbs.find(db_id);
+    if (it == ctx->kf_dbs.end()) return fail(SLAMGPU_ERR_NOTFOUND, "unknown key-frame database id");
+    SG_CUDA(cudaStreamSynchronize(ctx->stream));
+    free_kfdb(it->second);
+    ctx->kf_dbs.erase(it);
+    return SLAMGPU_OK;
+}
+
+int slamgpu_kfdb_match_pairs(slamgpu_ctx* ctx, int db_id, const int32_t* pairs, int n_pairs, float max_dist, float ratio,
+                             int32_t* out_offset, int32_t* out_query, int32_t* out_train, int64_t capacity,
+                             int64_t* out_total)
+{
+    SG_CTX(ctx);
+    SG_CHECK(n_pairs >= 0 && capacity >= 0, "negative size");
+    SG_CHECK(out_total != nullptr, "null out_total");
+    *out_total = 0;
+    if (n_pairs == 0) return SLAMGPU_OK;
+    SG_CHECK(pairs && out_offset, "null pointer");
+    SG_CHECK(capacity == 0 || (out_query && out_train), "null output lists");
+    auto it = ctx->kf_dbs.find(db_id);
+    if (it == ctx->kf_dbs.end() || it->second.h_offset.size() < 2)
+        return fail(SLAMGPU_ERR_NOTFOUND, "unknown or empty key-frame database id");
+    const KfDbDev& d = it->second;
+    const int n_frames = static_cast<int>(d.h_offset.size()) - 1;
+    for (int p = 0; p < 2 * n_pairs; ++p) SG_CHECK(pairs[p] >= 0 && pairs[p] < n_frames, "pair names an unknown frame");
+    return batch_host(ctx, nullptr, d.desc, d.offset, d.h_offset.data(), n_frames, d.max_rows, pairs, n_pairs, max_dist,
+                      ratio, out_offset, out_query, out_train, capacity, out_total);
 }
 
 int slamgpu_knn2_dev(slamgpu_ctx* ctx, const uint8_t* d_query, int nq, const uint8_t* d_train, int nt,
@@ -631,3 +753,11 @@ int slamgpu_match_descriptors_batch_dev(slamgpu_ctx* ctx, const uint8_t* d_desc,
 }
 
 } // extern "C"
+
+namespace slamgpu {
+void free_all_kfdbs(slamgpu_ctx* ctx)
+{
+    for (auto& kv : ctx->kf_dbs) free_kfdb(kv.second);
+    ctx->kf_dbs.clear();
+}
+} // namespace slamgpu

@@ -284,6 +284,7 @@ int slamgpu_destroy(slamgpu_ctx* ctx)
     for (auto& kv : ctx->frames) free_frame(kv.second);
     for (auto& kv : ctx->point_sets) free_points(kv.second);
     free_all_vocabs(ctx);
+    free_all_kfdbs(ctx);
     if (ctx->d_ws.ptr) cudaFree(ctx->d_ws.ptr);
     if (ctx->d_io.ptr) cudaFree(ctx->d_io.ptr);
     if (ctx->d_exp.ptr) cudaFree(ctx->d_exp.ptr);

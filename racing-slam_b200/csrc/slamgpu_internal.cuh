@@ -117,6 +117,17 @@ struct BowDbDev {
     int32_t* offset = nullptr;    // [cap_vectors + 1]
 };
 
+// Resident key-frame descriptor database of the loop detector (LoopDetector::Impl keeps every key frame,
+// src/LoopDetector.cpp:314-330): concatenated rows + frame offsets, grown geometrically.
+struct KfDbDev {
+    uint8_t* desc = nullptr;            // [cap_rows x 32]
+    int32_t* offset = nullptr;          // device copy of h_offset, [cap_frames + 1]
+    int64_t cap_rows = 0;
+    int cap_frames = 0;
+    int max_rows = 0;                   // largest frame
+    std::vector<int32_t> h_offset;      // [n_frames + 1], h_offset[0] = 0
+};
+
 struct Arena {
     void* ptr = nullptr;
     size_t cap = 0;
@@ -150,6 +161,7 @@ struct slamgpu_ctx {
     std::map<int, slamgpu::PointSetDev> point_sets;
     std::map<int, slamgpu::VocabDev> vocabs;
     std::map<int, slamgpu::BowDbDev> bow_dbs;
+    std::map<int, slamgpu::KfDbDev> kf_dbs;
     bool bow_smem_set = false;
     int batch_slice = 0;                       // SLAMGPU_BATCH_SLICE: pairs per slice of the batch calls (0 = by scratch size)
     cudaStream_t copy_stream = nullptr;        // result copies of the batch call, overlapped with later slices
@@ -311,6 +323,7 @@ int voc_launch_score_l1(slamgpu_ctx* ctx, const int32_t* d_q_ids, const double* 
                         double* d_score);
 
 // ---- PnP verification support (pnp_kernels.cu) ------------------------------------------------
+void free_all_kfdbs(slamgpu_ctx* ctx);
 int pnp_launch_score(slamgpu_ctx* ctx, const float* d_object, const float* d_image, const int32_t* d_corr_begin,
                      const int32_t* d_corr_count, const double* d_hyp_rt, const int32_t* d_hyp_problem, int n_hyp,
                      const double* K4, double reproj_error, int32_t* d_out_count);

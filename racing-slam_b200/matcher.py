@@ -324,6 +324,40 @@ class OrbVocabulary:
         self.ctx.vocab_release(self.vocab_id)
 
 
+class KeyFrameDatabase:
+    """The key frames LoopDetector keeps (src/LoopDetector.cpp:314-330) resident on the device: add() uploads a key
+    frame's descriptors once; match_pairs() is match_descriptors (src/MapMatcher.cpp:129-163) for a list of
+    (query key frame, candidate key frame) numbers -- verify_pnp's first step for every retrieved candidate."""
+
+    _next_id = 100
+
+    def __init__(self, ctx: L.Context):
+        self.ctx = ctx
+        self.db_id = KeyFrameDatabase._next_id
+        KeyFrameDatabase._next_id += 1
+        self._n = 0
+        self._max_rows = 0
+
+    def add(self, descriptors) -> int:
+        f = self.ctx.kfdb_append(self.db_id, descriptors)
+        self._n += 1
+        self._max_rows = max(self._max_rows, len(descriptors))
+        return f
+
+    def __len__(self):
+        return self._n
+
+    def match_pairs(self, pairs, max_dist=64.0, ratio=0.75, out=None):
+        pairs = np.asarray(pairs, np.int32).reshape(-1, 2)
+        return self.ctx.kfdb_match_pairs(self.db_id, pairs, max_dist, ratio,
+                                         capacity=len(pairs) * max(self._max_rows, 1), out=out)
+
+    def close(self):
+        if self._n:
+            self.ctx.kfdb_release(self.db_id)
+            self._n = 0
+
+
 class BowDatabase:
     """LoopDetector::Impl::bows kept on the device: add() per key frame, scores() of a query against all."""
 

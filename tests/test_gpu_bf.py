@@ -108,6 +108,99 @@ def test_full_size_8k_properties(ctx, oracle, pkg):
     assert (dist[:, 0] <= dist[:, 1]).all()
 
 
+def test_c5_full_size_database_properties(ctx, oracle, pkg):
+    """BASELINE C5 size (1000 key frames x 4000 descriptors, the 128 MB database bench.py uses): 2048 ordered
+    pairs drawn over the whole triangle through the host-buffer batch call.  Size-independent properties: list
+    structure, every reported match within the distance gate (popcount recomputed here), the two shards of a
+    world of 2 reproduce the unsharded lists pair for pair, and a sample of pairs is bit-exact against the oracle."""
+    db = pkg.synthetic.keyframe_db_fast(1000, 4000, 5)
+    desc = db.reshape(-1, 32)
+    off = (np.arange(1001, dtype=np.int64) * 4000).astype(np.int32)
+    every = pkg.sharding.all_pairs(1000)
+    assert len(every) == 499500
+    rng = np.random.default_rng(55)
+    pairs = every[np.sort(rng.choice(len(every), 2048, replace=False))]
+    o, ql, tl = ctx.match_descriptors_batch(desc, off, pairs, 64.0, 0.75)
+    cnt = np.diff(o)
+    assert o[0] == 0 and o[-1] == len(ql) == len(tl) and (cnt >= 0).all() and (cnt <= 4000).all()
+    assert cnt.sum() > 2048 * 100                       # the shared rows do match
+    pair_of = np.repeat(np.arange(len(pairs)), cnt)
+    inner = np.ones(len(ql), bool)
+    inner[o[:-1][cnt > 0]] = False                      # first entry of every non-empty list
+    assert (np.diff(ql)[inner[1:]] > 0).all()           # query rows strictly ascending within a pair
+    assert ((ql >= 0) & (ql < 4000) & (tl >= 0) & (tl < 4000)).all()
+    qa = db[pairs[pair_of, 0], ql].view(np.uint64)
+    ta = db[pairs[pair_of, 1], tl].view(np.uint64)
+    d = np.bitwise_count(qa ^ ta).sum(axis=1)
+    assert d.max() <= 64
+    # sharding: block-cyclic halves, concatenated back in pair order
+    got = {}
+    for r in range(2):
+        mine = pkg.sharding.shard_pairs(pairs, r, 2, block=64)
+        so, sq, st = ctx.match_descriptors_batch(desc, off, mine, 64.0, 0.75)
+        for k, (fq, ft) in enumerate(mine):
+            got[(int(fq), int(ft))] = (sq[so[k]:so[k + 1]], st[so[k]:so[k + 1]])
+    assert len(got) == len(pairs)
+    for k, (fq, ft) in enumerate(pairs):
+        sq, st = got[(int(fq), int(ft))]
+        assert np.array_equal(sq, ql[o[k]:o[k + 1]]) and np.array_equal(st, tl[o[k]:o[k + 1]]), k
+    for k in rng.choice(len(pairs), 6, replace=False):
+        oq, ot = oracle.match_descriptors(db[pairs[k, 0]], db[pairs[k, 1]], 64.0, 0.75)
+        assert np.array_equal(ql[o[k]:o[k + 1]], oq) and np.array_equal(tl[o[k]:o[k + 1]], ot), k
+
+
+def test_pinned_arrays_from_host_alloc_as_inputs_and_outputs(ctx, oracle, pkg):
+    """slamgpu_host_alloc through the binding: a page-locked descriptor set and result arrays give the same lists."""
+    db = pkg.synthetic.keyframe_db(4, 500, 21, shared_frac=0.4)
+    desc = pkg.pinned_empty((4 * 500, 32), np.uint8)
+    desc[...] = db.reshape(-1, 32)
+    off = (np.arange(5) * 500).astype(np.int32)
+    pairs = pkg.sharding.all_pairs(4)
+    out = (pkg.pinned_empty(len(pairs) * 500, np.int32), pkg.pinned_empty(len(pairs) * 500, np.int32))
+    o, ql, tl = ctx.match_descriptors_batch(desc, off, pairs, 64.0, 0.75, out=out)
+    for k, (fq, ft) in enumerate(pairs):
+        oq, ot = oracle.match_descriptors(db[fq], db[ft], 64.0, 0.75)
+        assert np.array_equal(ql[o[k]:o[k + 1]], oq) and np.array_equal(tl[o[k]:o[k + 1]], ot), k
+    del out, desc
+
+
+def test_resident_keyframe_database_equals_the_batch_call(ctx, oracle, pkg):
+    """slamgpu_kfdb_*: key frames appended one by one (ragged, one empty, growth across the first reservation of
+    2^20 rows), then pair lists matched against the resident copy -- the same lists as the upload-per-call form and
+    the oracle; new frames appended between calls are visible to the next call."""
+    sizes = [300, 0, 257, 1, 640, 33, 512]
+    db = pkg.synthetic.keyframe_db(len(sizes), 640, 9, shared_frac=0.4)
+    frames = [db[i, :n] for i, n in enumerate(sizes)]
+    kf = pkg.matcher.KeyFrameDatabase(ctx)
+    for i, f in enumerate(frames[:5]):
+        assert kf.add(f) == i
+    assert ctx.kfdb_count(kf.db_id) == (5, sum(sizes[:5]))
+    pairs = pkg.sharding.all_pairs(5)
+    pairs = np.concatenate([pairs, pairs[:, ::-1]])
+    o, ql, tl = kf.match_pairs(pairs)
+    desc = np.concatenate(frames[:5])
+    off = np.concatenate([[0], np.cumsum(sizes[:5])]).astype(np.int32)
+    bo, bq, bt = ctx.match_descriptors_batch(desc, off, pairs, 64.0, 0.75)
+    assert np.array_equal(o, bo) and np.array_equal(ql, bq) and np.array_equal(tl, bt)
+    for f in frames[5:]:
+        kf.add(f)
+    big = pkg.synthetic.keyframe_db_fast(270, 4000, 31)          # 1.08 M rows: the row store grows and moves
+    for f in big:
+        kf.add(f)
+    assert len(kf) == 7 + 270 and ctx.kfdb_count(kf.db_id)[1] == sum(sizes) + 270 * 4000
+    pairs = np.array([[6, 4], [4, 6], [5, 0], [276, 7], [7, 276], [100, 99], [3, 6], [1, 2]], np.int32)
+    o, ql, tl = kf.match_pairs(pairs, 64.0, 0.75)
+    every = frames + list(big)
+    for k, (fq, ft) in enumerate(pairs):
+        oq, ot = oracle.match_descriptors(every[fq], every[ft], 64.0, 0.75)
+        assert np.array_equal(ql[o[k]:o[k + 1]], oq) and np.array_equal(tl[o[k]:o[k + 1]], ot), (k, fq, ft)
+    with pytest.raises(pkg.SlamGpuError):
+        kf.match_pairs([[0, 277]])                                # unknown frame
+    kf.close()
+    with pytest.raises(pkg.SlamGpuError):
+        ctx.kfdb_match_pairs(kf.db_id, [[0, 1]])                  # released
+
+
 def test_batch_vs_single_and_oracle(ctx, oracle, pkg):
     """LoopDetector all-pairs form (BASELINE C5 shape, small): ragged frames, every ordered pair."""
     rng = np.random.default_rng(9)
