@@ -278,6 +278,52 @@ std::vector<MapPointMatch> MapMatcherGpu::match_descriptors(const Frame& frame, 
     return matches;
 }
 
+std::vector<std::vector<MapPointMatch>>
+MapMatcherGpu::match_descriptors_batch(const Frame& frame, const std::vector<const KeyFrame*>& candidates) const
+{
+    std::vector<std::vector<MapPointMatch>> result(candidates.size());
+    const cv::Mat& query_mat = frame.features().descriptors;
+    if (candidates.empty() || query_mat.empty()) {
+        return result;                                          // :139-141 for every candidate
+    }
+    // descriptor frame 0 = the query's rows; frame i + 1 = candidate i's matched rows, ascending keypoint index
+    std::vector<uint8_t> desc;
+    append_rows(query_mat, desc);
+    const int nq = query_mat.rows;
+    std::vector<int32_t> frame_offset{0, nq};
+    std::vector<std::vector<MapPoint*>> points(candidates.size());
+    std::vector<int32_t> pairs;
+    for (size_t c = 0; c < candidates.size(); c++) {
+        const KeyFrame& key_frame = *candidates[c];
+        points[c].reserve(key_frame.num_map_matches());
+        for (const auto& match : key_frame.map_matches()) {     // :135-138
+            points[c].push_back(&match.point);
+            const cv::Mat d = key_frame.descriptor(match.keypoint_index);
+            const uint8_t* dp = d.ptr<uint8_t>(0);
+            desc.insert(desc.end(), dp, dp + 32);
+        }
+        frame_offset.push_back(frame_offset.back() + static_cast<int32_t>(points[c].size()));
+        pairs.push_back(0);
+        pairs.push_back(static_cast<int32_t>(c) + 1);
+    }
+    const int n_pairs = static_cast<int>(candidates.size());
+    const int64_t capacity = static_cast<int64_t>(nq) * n_pairs;   // a query row matches at most once per candidate
+    std::vector<int32_t> out_offset(static_cast<size_t>(n_pairs) + 1), out_query(static_cast<size_t>(capacity)),
+        out_train(static_cast<size_t>(capacity));
+    int64_t total = 0;
+    check(slamgpu_match_descriptors_batch(m_ctx, desc.data(), frame_offset.data(), n_pairs + 1, pairs.data(), n_pairs,
+                                          m_max_descriptor_distance, match_ratio, out_offset.data(), out_query.data(),
+                                          out_train.data(), capacity, &total),
+          "slamgpu_match_descriptors_batch");
+    for (int c = 0; c < n_pairs; c++) {
+        for (int32_t i = out_offset[c]; i < out_offset[c + 1]; i++) {          // :159-160
+            result[static_cast<size_t>(c)].push_back(
+                {*points[static_cast<size_t>(c)][static_cast<size_t>(out_train[i])], static_cast<size_t>(out_query[i])});
+        }
+    }
+    return result;
+}
+
 std::vector<FeatureMatch> MapMatcherGpu::match_features(const ExtractedFeatures& prev_features,
                                                         const ExtractedFeatures& features, float max_distance) const
 {

@@ -41,6 +41,12 @@ class MapMatcherGpu {
     /** Descriptor match to a key frame's points via knn (:129-163) */
     std::vector<MapPointMatch> match_descriptors(const Frame& frame, const KeyFrame& key_frame) const;
 
+    /** verify_pnp's first step for every retrieved loop candidate at once (src/LoopDetector.cpp:181 runs
+     *  match_descriptors once per candidate): result[i] == match_descriptors(frame, *candidates[i]), from ONE batched
+     *  device call (slamgpu_match_descriptors_batch: the query rows go up once, every candidate's matched rows once). */
+    std::vector<std::vector<MapPointMatch>> match_descriptors_batch(const Frame& frame,
+                                                                    const std::vector<const KeyFrame*>& candidates) const;
+
     /** BaseFeatureExtractor::match_features (src/features/FeatureExtractor.cpp:15-30) on the same context */
     std::vector<FeatureMatch> match_features(const ExtractedFeatures& prev_features, const ExtractedFeatures& features,
                                              float max_distance) const;

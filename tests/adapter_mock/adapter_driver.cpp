@@ -6,6 +6,7 @@
 #include <fstream>
 #include <iostream>
 #include <memory>
+#include <string>
 #include <vector>
 
 #include "Camera.h"
@@ -125,6 +126,12 @@ int main(int argc, char** argv)
         dump("match_key_frame", matcher.match_key_frame(frame, map, kfs[required].get()));
         dump("match_for_fuse", matcher.match_for_fuse(frame, fuse));
         dump("match_descriptors", matcher.match_descriptors(frame, *kfs[required]));
+        {   // every key frame as a loop candidate, one batched call
+            std::vector<const KeyFrame*> candidates;
+            for (auto& kf : kfs) candidates.push_back(kf.get());
+            const auto lists = matcher.match_descriptors_batch(frame, candidates);
+            for (size_t c = 0; c < lists.size(); c++) dump(("mdb" + std::to_string(c)).c_str(), lists[c]);
+        }
         auto fm = matcher.match_features(kfs[0]->features(), frame.features(), 64.0F);
         out << "match_features " << fm.size() << "\n";
         for (const auto& m : fm) out << m.train_index << " " << m.query_index << "\n";

@@ -175,6 +175,19 @@ def test_adapter_end_to_end_vs_oracle(pkg, oracle, tmp_path):
     train = np.stack([kfs[req]["desc"][idx] for idx, _ in kfm])
     oq, ot = oracle.match_descriptors(fr["desc"], train, 64.0, 0.75)
     assert got["match_descriptors"] == [(kfm[int(t)][1], int(q)) for q, t in zip(oq, ot)]
+    # match_descriptors_batch: every key frame as a candidate, the same list as one match_descriptors each
+    assert got[f"mdb{req}"] == got["match_descriptors"]
+    n_lists = 0
+    for k in range(len(kfs)):
+        kfm_k = sorted((idx, i) for kk, idx, i in w["kf_matches"] if kk == k)
+        if not kfm_k:
+            assert got[f"mdb{k}"] == []
+            continue
+        train_k = np.stack([kfs[k]["desc"][idx] for idx, _ in kfm_k])
+        bq, bt = oracle.match_descriptors(fr["desc"], train_k, 64.0, 0.75)
+        assert got[f"mdb{k}"] == [(kfm_k[int(t)][1], int(q)) for q, t in zip(bq, bt)], k
+        n_lists += 1
+    assert n_lists >= 2
     o_t, o_q = oracle.match_features(kfs[0]["desc"], fr["desc"], 64.0)
     assert got["match_features"] == list(zip(o_t.tolist(), o_q.tolist()))
 
