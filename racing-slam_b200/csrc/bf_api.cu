@@ -223,6 +223,19 @@ int match_descriptors_core(slamgpu_ctx* ctx, const uint8_t* dq, int nq, const ui
                                    d_out_count);
 }
 
+// fn(first frame, frame count) over all frames, or over the runs of consecutive frames of a sorted list
+template <class F> int for_frame_runs(int n_frames, const std::vector<int>* used, F fn)
+{
+    if (used == nullptr) return fn(0, n_frames);
+    for (size_t i = 0; i < used->size();) {
+        size_t j = i + 1;
+        while (j < used->size() && (*used)[j] == (*used)[j - 1] + 1) ++j;
+        SG_TRY(fn((*used)[i], static_cast<int>(j - i)));
+        i = j;
+    }
+    return SLAMGPU_OK;
+}
+
 // Pairs are processed in slices so that the partial-key scratch stays around L2 size.
 constexpr size_t kBatchScratchBytes = size_t(256) << 20;
 
@@ -232,7 +245,10 @@ int batch_core(slamgpu_ctx* ctx, const uint8_t* d_desc, const int32_t* d_frame_o
                // of slice_pairs x max_rows and the lists are filled slice by slice
                int32_t* d_offset, int32_t* d_query_list, int32_t* d_train_list, int64_t capacity, int slice_pairs,
                // called after the work of slice [p0, p0 + np) has been queued on the stream
-               const std::function<int(int, int)>* after_slice = nullptr)
+               const std::function<int(int, int)>* after_slice = nullptr,
+               // sorted frames the pairs name, when they are few (host-buffer forms know them): only these get their
+               // expanded copy built (a loop-closure query against a handful of candidates of a large resident database)
+               const std::vector<int>* frames_used = nullptr)
 {
     if (n_pairs == 0) return SLAMGPU_OK;
     if (max_rows == 0) {
@@ -254,12 +270,18 @@ int batch_core(slamgpu_ctx* ctx, const uint8_t* d_desc, const int32_t* d_frame_o
             pitch = bf_tc4_pitch_rows(max_rows);
             SG_TRY(ensure_device_exp(ctx, bf_tc4_expanded_bytes(n_frames, max_rows)));
             e = static_cast<uint8_t*>(ctx->d_exp.ptr);
-            SG_TRY(bf_tc4_launch_expand(ctx, d_desc, d_frame_offset, n_frames, 0, pitch, e));
+            const size_t stride = bf_tc4_expanded_bytes(1, max_rows);
+            SG_TRY(for_frame_runs(n_frames, frames_used, [&](int f0, int nf) {
+                return bf_tc4_launch_expand(ctx, d_desc, d_frame_offset + f0, nf, 0, pitch, e + f0 * stride);
+            }));
         } else {
             pitch = bf_tc_pitch_rows(max_rows);
             SG_TRY(ensure_device_exp(ctx, bf_tc_expanded_bytes(n_frames, max_rows)));
             e = static_cast<uint8_t*>(ctx->d_exp.ptr);
-            SG_TRY(bf_tc_launch_expand(ctx, d_desc, d_frame_offset, n_frames, 0, max_rows, pitch, e));
+            const size_t stride = bf_tc_expanded_bytes(1, max_rows);
+            SG_TRY(for_frame_runs(n_frames, frames_used, [&](int f0, int nf) {
+                return bf_tc_launch_expand(ctx, d_desc, d_frame_offset + f0, nf, 0, max_rows, pitch, e + f0 * stride);
+            }));
         }
     }
     const size_t per_pair = bf_partial_elems(fin, 1, max_rows);
@@ -439,8 +461,15 @@ int batch_host(slamgpu_ctx* ctx, const uint8_t* desc, const uint8_t* d_desc_res,
         SG_CUDA(cudaEventRecord(off_ready, ctx->copy_stream));
         return SLAMGPU_OK;
     };
+    std::vector<int> used;
+    if (n_pairs <= 256) {                               // few pairs: name the frames they touch
+        used.assign(pairs, pairs + 2 * static_cast<size_t>(n_pairs));
+        std::sort(used.begin(), used.end());
+        used.erase(std::unique(used.begin(), used.end()), used.end());
+    }
+    const bool few = !used.empty() && used.size() * 2 < static_cast<size_t>(n_frames);
     const int rc = batch_core(ctx, d_desc, d_off, n_frames, d_pairs, n_pairs, max_rows, max_dist, ratio, d_rows, d_count,
-                              d_offset, d_ql, d_tl, capacity, slice, &after_slice);
+                              d_offset, d_ql, d_tl, capacity, slice, &after_slice, few ? &used : nullptr);
     if (rc != SLAMGPU_OK) {
         cudaStreamSynchronize(ctx->copy_stream);
         return rc;
