@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define SLAMGPU_ABI_VERSION 1
+#define SLAMGPU_ABI_VERSION 2
 
 #if defined(__GNUC__)
 #define SLAMGPU_API __attribute__((visibility("default")))
@@ -197,6 +197,49 @@ SLAMGPU_API int slamgpu_points_count(slamgpu_ctx* ctx, int set_id, int* n_points
 SLAMGPU_API int slamgpu_points_release(slamgpu_ctx* ctx, int set_id);
 /* Read back the per-point normal [n x 3] and range [n x 2] held on the device. */
 SLAMGPU_API int slamgpu_points_get_stats(slamgpu_ctx* ctx, int set_id, float* out_normal, float* out_range);
+
+/* ---- Mutable map (SURVEY 8f N1 / N2 "with incremental updates") ----------------------------------------
+ * The reference mutates existing points between matcher calls; a set made by slamgpu_points_create follows it
+ * with DELTAS instead of a re-upload of the whole map:
+ *   Map::associate / disassociate (src/Map.cpp:97-124, src/MapPoint.cpp:47-55)  -> slamgpu_points_set_observations
+ *   Map::fuse (src/Map.cpp:78-95; Mapper::fuse_match src/Mapper.cpp:176-196)    -> _set_observations (kept) + _remove (discarded)
+ *   Map::remove_point (src/Map.cpp:63-76; Mapper::cull_points src/Mapper.cpp:396-430) -> slamgpu_points_remove
+ *   MapPoint::set_position (src/MapPoint.cpp:19-22; src/Optimization.cpp:371,534, src/Mapper.cpp:391) -> _set_position
+ *   a key frame's pose moved by bundle adjustment / pose graph                  -> slamgpu_observer_centers_update
+ *   Map::create_point (src/Map.cpp:20-61)                                       -> slamgpu_points_append_observed
+ * SLOTS: a point's index in every match call.  Slots are handed out in append order = Map's vector order
+ * (src/Map.cpp:164-190), which is the visit rank that decides proposal ties (src/MapMatcher.cpp:95-97).  A removed
+ * point's slot becomes a tombstone that matches nothing; slamgpu_points_compact squeezes tombstones out WITHOUT
+ * reordering (exactly what vector::erase from the middle does to the indices of the later points) and reports
+ * the renumbering.  OBSERVERS: every key frame that observes a point has a small id chosen by the caller and a
+ * camera centre (Frame::camera_center(), src/Frame.cpp:39-42); normals and ranges (src/MapPoint.cpp:24-45) are
+ * re-derived on the device, in the observation order the caller gives (the host's observations() iteration
+ * order), for exactly the points an update touches.  A mutable set_id works with every match call above.
+ * slamgpu_points_upload / _append do not apply to it. */
+SLAMGPU_API int slamgpu_points_create(slamgpu_ctx* ctx, int set_id, int reserve_points, int64_t reserve_observations,
+                          int reserve_observers);
+/* New observers, or observers whose pose changed: centers [n x 3].  Every point that observes a moved key frame
+ * gets its normal and range re-derived.  Ids are distinct within a call; an id must have a centre before an
+ * observation may name it. */
+SLAMGPU_API int slamgpu_observer_centers_update(slamgpu_ctx* ctx, int set_id, const int32_t* observer_ids, int n,
+                                    const float* centers);
+/* Append n_new points (slots n .. n + n_new - 1): pos [n_new x 3], obs_offset [n_new + 1] relative to the block,
+ * obs_desc [x 32] and obs_observer [one id per observation] in the host's observations() order. */
+SLAMGPU_API int slamgpu_points_append_observed(slamgpu_ctx* ctx, int set_id, int n_new, const float* pos,
+                                   const int32_t* obs_offset, const uint8_t* obs_desc, const int32_t* obs_observer);
+/* Replace the WHOLE observation run of each listed slot (the host's current iteration order; an
+ * unordered_map may reorder on insert / erase, so the run is restated, not patched). */
+SLAMGPU_API int slamgpu_points_set_observations(slamgpu_ctx* ctx, int set_id, const int32_t* idx, int n,
+                                    const int32_t* obs_offset, const uint8_t* obs_desc, const int32_t* obs_observer);
+SLAMGPU_API int slamgpu_points_set_position(slamgpu_ctx* ctx, int set_id, const int32_t* idx, int n, const float* pos);
+/* Tombstone the listed slots (distinct, live). */
+SLAMGPU_API int slamgpu_points_remove(slamgpu_ctx* ctx, int set_id, const int32_t* idx, int n);
+/* Drop the tombstones, keep the order: out_remap [slot count before] = new slot or -1 (may be NULL), *out_n = slots
+ * after.  The caller renumbers its own point -> slot table the same way (or calls this and reads out_remap). */
+SLAMGPU_API int slamgpu_points_compact(slamgpu_ctx* ctx, int set_id, int32_t* out_remap, int* out_n);
+/* Live points, observation-arena entries in use and how many of them are garbage (superseded runs). */
+SLAMGPU_API int slamgpu_points_live(slamgpu_ctx* ctx, int set_id, int* live_points, int64_t* arena_used,
+                        int64_t* arena_garbage);
 
 /* MapMatcher::match_map / match_key_frame / match_for_fuse -- src/MapMatcher.cpp:107-127,165-175.
  *   skip     [n] bytes or NULL: non-zero drops the point up front -- frame.is_matched(point)

@@ -80,6 +80,14 @@ SIGNATURES = {
     "slamgpu_points_count": (C.c_int, [_ctx, C.c_int, C.POINTER(C.c_int), _i64p]),
     "slamgpu_points_release": (C.c_int, [_ctx, C.c_int]),
     "slamgpu_points_get_stats": (C.c_int, [_ctx, C.c_int, _f32p, _f32p]),
+    "slamgpu_points_create": (C.c_int, [_ctx, C.c_int, C.c_int, C.c_int64, C.c_int]),
+    "slamgpu_observer_centers_update": (C.c_int, [_ctx, C.c_int, _i32p, C.c_int, _f32p]),
+    "slamgpu_points_append_observed": (C.c_int, [_ctx, C.c_int, C.c_int, _f32p, _i32p, _u8p, _i32p]),
+    "slamgpu_points_set_observations": (C.c_int, [_ctx, C.c_int, _i32p, C.c_int, _i32p, _u8p, _i32p]),
+    "slamgpu_points_set_position": (C.c_int, [_ctx, C.c_int, _i32p, C.c_int, _f32p]),
+    "slamgpu_points_remove": (C.c_int, [_ctx, C.c_int, _i32p, C.c_int]),
+    "slamgpu_points_compact": (C.c_int, [_ctx, C.c_int, _i32p, C.POINTER(C.c_int)]),
+    "slamgpu_points_live": (C.c_int, [_ctx, C.c_int, C.POINTER(C.c_int), _i64p, _i64p]),
     "slamgpu_match_projection": (C.c_int, [_ctx, C.c_int, C.c_int, _f32p, C.POINTER(ProjParams), _u8p, _i32p, C.c_int,
                                            _i32p, _i32p]),
     "slamgpu_match_projection_ex": (C.c_int, [_ctx, C.c_int, C.c_int, _f32p, C.POINTER(ProjParams), _u8p, _i32p,
@@ -425,6 +433,65 @@ class Context:
                                                     _p(normal, C.c_float), _p(rng, C.c_float),
                                                     _p(obs_offset, C.c_int32), _p(obs_desc, C.c_uint8),
                                                     _p(obs_center, C.c_float)))
+
+    # ---- mutable map (slamgpu_points_create ...): deltas instead of re-uploads ----
+    def points_create(self, set_id: int, reserve_points: int = 0, reserve_observations: int = 0,
+                      reserve_observers: int = 0):
+        self._check(self._lib.slamgpu_points_create(self._h, set_id, int(reserve_points), int(reserve_observations),
+                                                    int(reserve_observers)))
+
+    def observer_centers_update(self, set_id: int, observer_ids, centers):
+        """New key frames, or key frames whose pose moved: Frame::camera_center() per observer id."""
+        ids = np.ascontiguousarray(observer_ids, np.int32).reshape(-1)
+        centers = np.ascontiguousarray(centers, np.float32).reshape(-1, 3)
+        assert len(ids) == len(centers)
+        self._check(self._lib.slamgpu_observer_centers_update(self._h, set_id, _p(ids, C.c_int32), len(ids),
+                                                              _p(centers, C.c_float)))
+
+    def points_append_observed(self, set_id: int, pos, obs_offset, obs_desc, obs_observer):
+        pos = np.ascontiguousarray(pos, np.float32).reshape(-1, 3)
+        obs_offset = np.ascontiguousarray(obs_offset, np.int32)
+        obs_desc = _desc(obs_desc)
+        obs_observer = np.ascontiguousarray(obs_observer, np.int32).reshape(-1)
+        assert len(obs_offset) == len(pos) + 1 and len(obs_desc) == len(obs_observer)
+        self._check(self._lib.slamgpu_points_append_observed(self._h, set_id, len(pos), _p(pos, C.c_float),
+                                                             _p(obs_offset, C.c_int32), _p(obs_desc, C.c_uint8),
+                                                             _p(obs_observer, C.c_int32)))
+
+    def points_set_observations(self, set_id: int, idx, obs_offset, obs_desc, obs_observer):
+        idx = np.ascontiguousarray(idx, np.int32).reshape(-1)
+        obs_offset = np.ascontiguousarray(obs_offset, np.int32)
+        obs_desc = _desc(obs_desc)
+        obs_observer = np.ascontiguousarray(obs_observer, np.int32).reshape(-1)
+        assert len(obs_offset) == len(idx) + 1 and len(obs_desc) == len(obs_observer)
+        self._check(self._lib.slamgpu_points_set_observations(self._h, set_id, _p(idx, C.c_int32), len(idx),
+                                                              _p(obs_offset, C.c_int32), _p(obs_desc, C.c_uint8),
+                                                              _p(obs_observer, C.c_int32)))
+
+    def points_set_position(self, set_id: int, idx, pos):
+        idx = np.ascontiguousarray(idx, np.int32).reshape(-1)
+        pos = np.ascontiguousarray(pos, np.float32).reshape(-1, 3)
+        assert len(idx) == len(pos)
+        self._check(self._lib.slamgpu_points_set_position(self._h, set_id, _p(idx, C.c_int32), len(idx),
+                                                          _p(pos, C.c_float)))
+
+    def points_remove(self, set_id: int, idx):
+        idx = np.ascontiguousarray(idx, np.int32).reshape(-1)
+        self._check(self._lib.slamgpu_points_remove(self._h, set_id, _p(idx, C.c_int32), len(idx)))
+
+    def points_compact(self, set_id: int):
+        """-> (remap [slots before] = new slot or -1, slots after)"""
+        n_before, _ = self.points_count(set_id)
+        remap = np.full(max(n_before, 1), -1, np.int32)
+        n = C.c_int(0)
+        self._check(self._lib.slamgpu_points_compact(self._h, set_id, _p(remap, C.c_int32), C.byref(n)))
+        return remap[:n_before], n.value
+
+    def points_live(self, set_id: int):
+        """-> (live points, observation-arena entries used, of which garbage)"""
+        n, used, garbage = C.c_int(0), C.c_int64(0), C.c_int64(0)
+        self._check(self._lib.slamgpu_points_live(self._h, set_id, C.byref(n), C.byref(used), C.byref(garbage)))
+        return n.value, used.value, garbage.value
 
     def points_count(self, set_id: int):
         n, o = C.c_int(0), C.c_int64(0)

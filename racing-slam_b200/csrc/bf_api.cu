@@ -83,8 +83,8 @@ size_t tc_pair_keys(const slamgpu_ctx* ctx, const BfPlan& plan, int nq)
 }
 
 // Filtered calls (a distance cut exists) run on the block-scaled FP4 kernel (bf_tc4_kernels.cu), exact
-// kNN-2 on the int8 kernel (bf_tc_kernels.cu).  SLAMGPU_TC_VARIANT bit 6 keeps filtered calls on int8 (A/B).
-bool use_fp4(const slamgpu_ctx* ctx, int d_cut) { return d_cut <= 250 && !(ctx->tc_variant & 64); }
+// kNN-2 on the int8 kernel (bf_tc_kernels.cu).  In -DSLAMGPU_DEBUG_VARIANTS builds SLAMGPU_TC_VARIANT bit 6 keeps filtered calls on int8 (A/B).
+bool use_fp4(const slamgpu_ctx* ctx, int d_cut) { return d_cut <= 250 && !SG_TC_VARIANT(ctx->tc_variant, 64); }
 
 BfPlan tc_plan(const slamgpu_ctx* ctx, int nq, int nt, int64_t n_pairs, bool fp4)
 {
@@ -474,8 +474,10 @@ int batch_host(slamgpu_ctx* ctx, const uint8_t* desc, const uint8_t* d_desc_res,
         cudaStreamSynchronize(ctx->copy_stream);
         return rc;
     }
-    h_offset[0] = 0;
-    bool overflow = false;
+    // h_offset[0] is never written or read on the host: the pinned block's first bytes may still be the source
+    // of an upload queued behind an unsynchronised *_dev call (the descriptors, or the pair list of the resident
+    // form), so nothing on the host may touch it before the stream has drained.  Offset 0 is the constant 0.
+    bool overflow = false, wrapped = false;
     int64_t begin = 0, prev_begin = 0, prev_end = 0;
     int prev = -1;
     auto unstage = [&](int s, int64_t b, int64_t e) -> int {      // piece [b, e) of slice s into the caller's arrays
@@ -490,7 +492,10 @@ int batch_host(slamgpu_ctx* ctx, const uint8_t* desc, const uint8_t* d_desc_res,
         const int p0 = s * slice, np = std::min(slice, n_pairs - p0);
         SG_CUDA(cudaEventSynchronize(ctx->slice_events[3 * s + 1]));
         const int64_t end = h_offset[p0 + np];
-        overflow = overflow || end > capacity;
+        // offsets are int32 on the device; one slice adds < 2^31 entries (slice_for), so a wrapped total shows up
+        // as an end below its begin
+        wrapped = wrapped || end < begin;
+        overflow = overflow || wrapped || end > capacity;
         if (!overflow) {
             if (end > begin) {
                 SG_CUDA(cudaMemcpyAsync(h_ql + begin, d_ql + begin, sizeof(int32_t) * (end - begin), cudaMemcpyDeviceToHost,
@@ -509,8 +514,10 @@ int batch_host(slamgpu_ctx* ctx, const uint8_t* desc, const uint8_t* d_desc_res,
     if (prev >= 0) SG_TRY(unstage(prev, prev_begin, prev_end));
     SG_CUDA(cudaStreamSynchronize(ctx->copy_stream));
     SG_CUDA(cudaStreamSynchronize(ctx->stream));
-    std::memcpy(out_offset, h_offset, sizeof(int32_t) * (static_cast<size_t>(n_pairs) + 1));
+    out_offset[0] = 0;
+    std::memcpy(out_offset + 1, h_offset + 1, sizeof(int32_t) * static_cast<size_t>(n_pairs));
     *out_total = out_offset[n_pairs];
+    if (wrapped) return fail(SLAMGPU_ERR_INVALID, "more than 2^31 - 1 matches in one batch call: split the pair list");
     if (overflow) return fail(SLAMGPU_ERR_NOMEM, "match list capacity too small; *out_total holds the size needed");
     return SLAMGPU_OK;
 }

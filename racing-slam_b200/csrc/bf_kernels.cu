@@ -464,7 +464,7 @@ __global__ void bf_compact_kernel(const int32_t* out_train, const int32_t* frame
         const unsigned ballot = __ballot_sync(0xFFFFFFFFu, t >= 0);
         if (t >= 0) {
             const int p = pos + __popc(ballot & ((1u << lane) - 1u));
-            if (p < capacity) {   // an undersized list is reported by the host from offset[n_pairs]
+            if (p >= 0 && p < capacity) {   // an undersized list (or a wrapped int32 total) is reported by the host from the offsets
                 query_list[p] = q;
                 train_list[p] = t;
             }

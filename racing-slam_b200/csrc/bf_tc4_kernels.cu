@@ -402,7 +402,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTc4Threads, 1) bf_t
                     tc_fence_after();
                     const uint32_t d = tmem_base + sc * kAccStride;
                     const uint32_t a0 = sbase + kOff4A + sa * kA4Bytes, b0 = sbase + kOff4B + sb * kB4Bytes;
-                    if (!(a.variant & 4)) {       // timing experiments only: bit 2 skips the MMAs
+                    if (!SG_TC_VARIANT(a.variant, 4)) {       // timing experiments only: bit 2 skips the MMAs
                         tc4_mma(d, desc_ax, desc_bx, kIdesc4, 0u, sf_mix, sf_mix);      // D = 1.5 * 2^23 + 512 - 1025 * T4
 #pragma unroll
                         for (int k = 0; k < 4; ++k)     // K = 64 values = 32 bytes = two 16-byte k-chunks per MMA
@@ -411,7 +411,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTc4Threads, 1) bf_t
                         // second train row of every column, scaled by 2^10.  A last tile with at most 240 rows
                         // left has none: its columns keep dot2 = 0, what the zero padding rows would have given
                         // (4000 rows = 8 tiles + 160 rows: 4 of 81 MMAs less per unit)
-                        if (un.t_begin + bt * kT4 + kN4 < un.t_end || (a.variant & 256)) {
+                        if (un.t_begin + bt * kT4 + kN4 < un.t_end || SG_TC_VARIANT(a.variant, 256)) {
 #pragma unroll
                             for (int k = 0; k < 4; ++k)
                                 tc4_mma(d, umma_desc(a0 + k * 256, 128u, kGroup4),
@@ -454,7 +454,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTc4Threads, 1) bf_t
         const int row_in_tile = static_cast<int>(rank) * 128 + quad * 32 + lane;
         const uint32_t lane_col = (static_cast<uint32_t>(quad * 32) << 16) + static_cast<uint32_t>(g * 120);
         const int c0 = g * 120;
-        const bool skip = (a.variant & 8) != 0;     // timing experiments only: bit 3 skips the TMEM reads and the fold
+        const bool skip = SG_TC_VARIANT(a.variant, 8);     // timing experiments only: bit 3 skips the TMEM reads and the fold
 
         // tile stream of this cluster: (unit, train tile) in the order the MMA issuer produces them
         long long u_cur = cid - n_clusters;
@@ -501,7 +501,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTc4Threads, 1) bf_t
             const uint32_t sc = c_it & 1u;
             const uint32_t taddr = tmem_base + lane_col + sc * kAccStride;
             const int cb = un_cur.t_begin + bt_cur * kT4;
-            const int t_end = (a.variant & 32) ? -1 : un_cur.t_end;     // timing experiments only: bit 5 disables the rare path
+            const int t_end = SG_TC_VARIANT(a.variant, 32) ? -1 : un_cur.t_end;     // timing experiments only: bit 5 disables the rare path
             if (!skip) {
                 tmem_wait_ld();                  // chunk A of this tile has landed
                 tmem_pin(va0);
@@ -509,7 +509,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTc4Threads, 1) bf_t
                 tmem_ld32(taddr + 64, vb0);      // chunk B in flight while A is folded
                 tmem_ld16(taddr + 96, vb1);
                 tmem_ld8(taddr + 112, vb2);
-                const uint64_t ma = (a.variant & 128) ? 0ull   // timing experiments only: bit 7 skips the scan arithmetic
+                const uint64_t ma = SG_TC_VARIANT(a.variant, 128) ? 0ull   // timing experiments only: bit 7 skips the scan arithmetic
                                                       : scan4(va0, park) | (scan4(va1, park + 8) << 32);
                 if (__builtin_expect(ma != 0ull && t_end >= 0, 0)) decode4(park, ma, cb + c0, t_end, a.thr_dot, a.thr4, b0, b1);
                 tmem_wait_ld();                  // chunk B has landed: every TMEM read of this stage is done
@@ -540,7 +540,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTc4Threads, 1) bf_t
                 }
             }
             if (!skip) {
-                const uint64_t mb = (a.variant & 128) ? 0ull
+                const uint64_t mb = SG_TC_VARIANT(a.variant, 128) ? 0ull
                                                       : scan4(vb0, park) | (scan4(vb1, park + 8) << 32) | (scan4(vb2, park + 12) << 48);
                 if (__builtin_expect(mb != 0ull && t_end >= 0, 0)) decode4(park, mb, cb + c0 + 64, t_end, a.thr_dot, a.thr4, b0, b1);
             }
@@ -677,10 +677,10 @@ int bf_tc4_launch_scan(slamgpu_ctx* ctx, const BfPlan& plan, const uint8_t* d_ex
                        int nt, int pitch_rows, const int32_t* d_frame_offset, const int32_t* d_pairs, int n_pairs,
                        int max_rows, int d_cut, uint2* d_keys)
 {
-    static bool attr_set = false;
-    if (!attr_set) {
+    // per-DEVICE function attribute: one flag per context (see bf_tc_launch_scan)
+    if (!ctx->tc4_attr_set) {
         SG_CUDA(cudaFuncSetAttribute(bf_tc4_scan_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kTc4SmemBytes));
-        attr_set = true;
+        ctx->tc4_attr_set = true;
     }
     SG_CHECK(d_cut >= 1 && d_cut <= 250, "the fp4 scan needs a distance cut of at most 250");
     Tc4Args a;

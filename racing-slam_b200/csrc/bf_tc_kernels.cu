@@ -219,7 +219,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) bf_tc_scan_kernel(const TcArgs 
     } else if (warp == 1) {
         // ===== MMA issuer: one thread =====
         if (lane == 0) {
-            const bool swap = (a.variant & 1) != 0;
+            const bool swap = SG_TC_VARIANT(a.variant, 1);
             const uint32_t lbo = swap ? kGroupBytes : 128u, sbo = swap ? 128u : kGroupBytes;
             const uint32_t lbo_x = swap ? 256u : 128u, sbo_x = swap ? 128u : 256u;
             const uint64_t desc_ax = umma_desc(sbase + kOffAX, lbo_x, sbo_x);
@@ -585,7 +585,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTc2Threads, 1) bf_t
                     tc_fence_after();
                     const uint32_t d = tmem_base + sc * TN;
                     const uint32_t a0 = sbase + kOff2A + sa * kABytes, b0 = sbase + kOff2B + sb * kB2Bytes;
-                    if (!(a.variant & 4)) {       // timing experiments only: bit 2 skips the MMAs
+                    if (!SG_TC_VARIANT(a.variant, 4)) {       // timing experiments only: bit 2 skips the MMAs
 #pragma unroll
                         for (int k = 0; k < 8; ++k)
                             tc2_mma_i8(d, umma_desc(a0 + k * 256, 128u, kGroupBytes),
@@ -640,7 +640,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTc2Threads, 1) bf_t
                         else mbar_arrive_remote(ACC_EMPTY(sc), 0u);
                     }
                 };
-                if (a.variant & 8) {          // timing experiments only: bit 3 skips the TMEM reads and the fold
+                if (SG_TC_VARIANT(a.variant, 8)) {          // timing experiments only: bit 3 skips the TMEM reads and the fold
                     tc_fence_before();
                     __syncwarp();
                     arrive();
@@ -722,7 +722,7 @@ size_t bf_tc_expanded_bytes(int n_frames, int max_rows)
 }
 
 // SLAMGPU_TC_VARIANT bit 1 selects the single-CTA kernel (v1); default is the CTA-pair kernel (v2).
-static bool tc_single_cta(const slamgpu_ctx* ctx) { return (ctx->tc_variant & 2) != 0; }
+static bool tc_single_cta(const slamgpu_ctx* ctx) { return SG_TC_VARIANT(ctx->tc_variant, 2); }
 
 BfPlan bf_tc_make_plan(const slamgpu_ctx* ctx, int nq_max, int nt_max, int64_t n_pairs)
 {
@@ -778,12 +778,13 @@ int bf_tc_launch_scan(slamgpu_ctx* ctx, const BfPlan& plan, const uint8_t* d_exp
                       int nt, int pitch_rows, const int32_t* d_frame_offset, const int32_t* d_pairs, int n_pairs,
                       int max_rows, int d_cut, uint2* d_keys)
 {
-    static bool attr_set = false;
-    if (!attr_set) {
+    // the opt-in to > 48 KB of dynamic shared memory is a per-DEVICE function attribute: one flag per context
+    // (a context is bound to one device; a process may hold contexts on several)
+    if (!ctx->tc_attr_set) {
         SG_CUDA(cudaFuncSetAttribute(bf_tc_scan_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kTcSmemBytes));
         SG_CUDA(cudaFuncSetAttribute(bf_tc2_scan_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kTc2SmemBytes));
         SG_CUDA(cudaFuncSetAttribute(bf_tc2_scan_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kTc2SmemBytes));
-        attr_set = true;
+        ctx->tc_attr_set = true;
     }
     TcArgs a;
     a.exp_q = d_exp_q;
@@ -808,7 +809,7 @@ int bf_tc_launch_scan(slamgpu_ctx* ctx, const BfPlan& plan, const uint8_t* d_exp
         bf_tc_scan_kernel<<<grid, kTcThreads, kTcSmemBytes, ctx->stream>>>(a);
     } else {
         const unsigned grid = 2u * static_cast<unsigned>(min(a.n_units, static_cast<long long>(ctx->n_sm / 2)));
-        if (d_cut <= 256 && !(ctx->tc_variant & 16)) {      // __cluster_dims__(2, 1, 1)
+        if (d_cut <= 256 && !SG_TC_VARIANT(ctx->tc_variant, 16)) {      // __cluster_dims__(2, 1, 1)
             bf_tc2_scan_kernel<true><<<grid, kTc2Threads, kTc2SmemBytes, ctx->stream>>>(a);
         } else {
             bf_tc2_scan_kernel<false><<<grid, kTc2Threads, kTc2SmemBytes, ctx->stream>>>(a);

@@ -29,12 +29,6 @@ void join_frame(FrameDev& f);
 size_t kd_image_bytes(size_t n, size_t n_cells);
 void build_kd_image(FrameKdPending& k);
 
-void free_points(PointSetDev& p)
-{
-    if (p.blob) cudaFree(p.blob);
-    p = PointSetDev();
-}
-
 // One allocation carved for cap_n points / cap_obs observations; the first five arrays are in the
 // order and padding of the staging image so that an exact-size upload is one copy.
 size_t points_image_bytes(size_t N, size_t O)
@@ -58,6 +52,7 @@ int alloc_points(PointSetDev& p, int cap_n, int64_t cap_obs)
     p.obs_offset = dv.take<int32_t>(N + 1);
     p.obs_desc = dv.take<uint4>(O * 2);
     p.pt_matched = dv.take<uint8_t>(N);
+    p.obs_end = p.obs_offset + 1;      // CSR
     p.cap_n = cap_n;
     p.cap_obs = cap_obs;
     return SLAMGPU_OK;
@@ -89,6 +84,7 @@ void fill_common(ProjCommonArgs& c, const PointSetDev& ps, const slamgpu_proj_pa
     c.normal = ps.normal;
     c.range = ps.range;
     c.obs_offset = ps.obs_offset;
+    c.obs_end = ps.obs_end;
     c.obs_desc = ps.obs_desc;
     c.order = d_order;
     c.n_visit = n_visit;
@@ -151,7 +147,7 @@ int match_projection_impl(slamgpu_ctx* ctx, const int* frame_ids, int n_frames, 
     SG_CHECK(n_visit >= 0, "negative visit count");
     if (order) {
         for (int i = 0; i < n_order; ++i)
-            SG_CHECK(order[i] < ps.n, "order entry outside the point set");
+            SG_CHECK(order[i] >= -1 && order[i] < ps.n, "order entry outside the point set (-1 = nullptr entry)");
     }
 
     std::vector<const FrameDev*> fds(n_frames);
@@ -436,6 +432,10 @@ int slamgpu_frame_upload(slamgpu_ctx* ctx, int frame_id, int nkp, const float* x
         }
         f.blob_bytes = total;
     }
+    struct NewBlob {   // freed on every error return below; disarmed when the frame is stored (on failure the
+        FrameDev* f;   // slot is left absent rather than half-built)
+        ~NewBlob() { if (f && f->blob) cudaFree(f->blob); }
+    } new_blob{&f};
     Carver dv(f.blob);
     f.desc = dv.take<uint4>(2 * n);
     f.matched = dv.take<uint8_t>(n);
@@ -450,11 +450,7 @@ int slamgpu_frame_upload(slamgpu_ctx* ctx, int frame_id, int nkp, const float* x
     f.kd_image_bytes = kd_bytes;
 
     if (nkp > 0) {
-        int rc = ensure_host_stage(ctx, std::max(now_bytes, kd_bytes) + 256);
-        if (rc != SLAMGPU_OK) {
-            cudaFree(f.blob);
-            return rc;
-        }
+        SG_TRY(ensure_host_stage(ctx, std::max(now_bytes, kd_bytes) + 256));
         // staging is free to overwrite only after earlier copies out of it have completed
         SG_CUDA(cudaStreamSynchronize(ctx->stream));
         Carver hv(ctx->h_stage.ptr);
@@ -498,6 +494,7 @@ int slamgpu_frame_upload(slamgpu_ctx* ctx, int frame_id, int nkp, const float* x
             pending->worker = std::thread(work, pending.get(), false);
         }
     }
+    new_blob.f = nullptr;
     ctx->frames[frame_id] = std::move(f);
     return SLAMGPU_OK;
 }
@@ -625,6 +622,7 @@ int slamgpu_points_append(slamgpu_ctx* ctx, int set_id, int n_new, const float* 
     SG_CHECK(n_new >= 0, "negative point count");
     auto it = ctx->point_sets.find(set_id);
     if (it == ctx->point_sets.end()) return fail(SLAMGPU_ERR_NOTFOUND, "unknown point set id");
+    SG_CHECK(!it->second.is_mutable, "a mutable point set grows through slamgpu_points_append_observed");
     if (n_new == 0) return SLAMGPU_OK;
     SG_CHECK(pos != nullptr && obs_offset != nullptr, "null positions / observation offsets");
     const bool derive = (normal == nullptr || range == nullptr);

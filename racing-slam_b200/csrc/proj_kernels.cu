@@ -135,7 +135,7 @@ __global__ void __launch_bounds__(kProjThreads) proj_match_kernel(const ProjKern
     }
 
     // P5 + P6  KD radius search in reference visit order, Hamming against every observation
-    const int o_begin = c.obs_offset[pi], o_end = c.obs_offset[pi + 1];
+    const int o_begin = c.obs_offset[pi], o_end = c.obs_end[pi];
     int best = c.thr;          // accept d < thr  <=>  (double)d < max_descriptor_distance
     int best_kp = 0;
 
@@ -299,7 +299,7 @@ __global__ void __launch_bounds__(kGroupThreads) proj_match_warp_kernel(const Pr
     }
 
     // P5 + P6: candidates from the grid, one per lane
-    const int o_begin = c.obs_offset[pi], o_end = c.obs_offset[pi + 1];
+    const int o_begin = c.obs_offset[pi], o_end = c.obs_end[pi];
     const float pad = c.radius + 1.0f;                           // conservative box; the exact test is d2 <= r2
     const int cx0 = grid_cell(u - pad, f.gx0, f.inv_cell, f.gw), cx1 = grid_cell(u + pad, f.gx0, f.inv_cell, f.gw);
     const int cy0 = grid_cell(w - pad, f.gy0, f.inv_cell, f.gh), cy1 = grid_cell(w + pad, f.gy0, f.inv_cell, f.gh);
@@ -540,7 +540,7 @@ __global__ void __launch_bounds__(kGroupThreads) proj_match_group_kernel(const P
     const float X[3] = {c.pos[3 * pi], c.pos[3 * pi + 1], c.pos[3 * pi + 2]};
     const float nx = c.normal[3 * pi], ny = c.normal[3 * pi + 1], nz = c.normal[3 * pi + 2];
     const float nearest = c.range[2 * pi], furthest = c.range[2 * pi + 1];
-    const int o_begin = c.obs_offset[pi], o_end = c.obs_offset[pi + 1];
+    const int o_begin = c.obs_offset[pi], o_end = c.obs_end[pi];
     if (skipped) return;                              // :53 is_matched(point) / :169 !is_observed_by
 
     float h[3];
@@ -631,7 +631,7 @@ __global__ void __launch_bounds__(kGateThreads) proj_gate_kernel(const ProjKerne
         const float nx = c.normal[3 * pi], ny = c.normal[3 * pi + 1], nz = c.normal[3 * pi + 2];
         const float nearest = c.range[2 * pi], furthest = c.range[2 * pi + 1];
         s.o_begin = c.obs_offset[pi];
-        s.o_end = c.obs_offset[pi + 1];
+        s.o_end = c.obs_end[pi];
         alive = !skipped;                                        // :53 is_matched(point) / :169 !is_observed_by
         float h[3];
 #pragma unroll

@@ -186,6 +186,15 @@ static void kd_build_perm(const float* xy, int n, uint32_t* out_perm)
         SG_CUDA(cudaSetDevice((ctx)->device));                            \
     } while (0)
 
+void free_points(PointSetDev& p)
+{
+    if (p.blob) cudaFree(p.blob);
+    if (p.pts_blob) cudaFree(p.pts_blob);
+    if (p.obs_blob) cudaFree(p.obs_blob);
+    if (p.kf_blob) cudaFree(p.kf_blob);
+    p = PointSetDev();
+}
+
 } // namespace slamgpu
 
 using namespace slamgpu;
@@ -253,8 +262,10 @@ int slamgpu_create(int device, slamgpu_ctx** out)
     }
     const char* engine = std::getenv("SLAMGPU_BF_ENGINE");
     if (engine != nullptr) ctx->bf_engine = std::strcmp(engine, "int") == 0 ? 1 : std::strcmp(engine, "tc") == 0 ? 2 : 0;
-    const char* variant = std::getenv("SLAMGPU_TC_VARIANT");
+#ifdef SLAMGPU_DEBUG_VARIANTS       // timing experiments that can corrupt results: never in the release library
+    const char* variant = std::getenv("SLAMGPU_TC_" "VARIANT");
     if (variant != nullptr) ctx->tc_variant = std::atoi(variant);
+#endif
     const cudaError_t e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking);
     if (e != cudaSuccess) {
         delete ctx;
@@ -269,11 +280,6 @@ static void free_frame(FrameDev& f)
     if (f.pending && f.pending->worker.joinable()) f.pending->worker.join();   // a KD build still running
     if (f.blob) cudaFree(f.blob);
     f = FrameDev();
-}
-static void free_points(PointSetDev& p)
-{
-    if (p.blob) cudaFree(p.blob);
-    p = PointSetDev();
 }
 
 int slamgpu_destroy(slamgpu_ctx* ctx)

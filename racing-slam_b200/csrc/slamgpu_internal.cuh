@@ -14,6 +14,16 @@
 
 #include "slamgpu.h"
 
+// SLAMGPU_TC_VARIANT (timing experiments: skip the MMAs, the TMEM reads, the rare path ...) exists only in builds
+// made with -DSLAMGPU_DEBUG_VARIANTS.  In the release library the switches are compiled out: the bit tests below
+// are constant-false and slamgpu_create does not read the variable, so no environment can corrupt a result.
+#ifdef SLAMGPU_DEBUG_VARIANTS
+#define SG_TC_VARIANT(value, bits) (((value) & (bits)) != 0)
+#else
+#define SG_TC_VARIANT(value, bits) false
+#endif
+
+
 namespace slamgpu {
 
 void set_error(const std::string& msg);
@@ -92,7 +102,27 @@ struct PointSetDev {
     uint8_t* pt_matched = nullptr;// [cap_n] scratch of slamgpu_track_match: frame.is_matched(point)
     int cap_n = 0;                // the arrays above are carved for cap_n points / cap_obs observations,
     int64_t cap_obs = 0;          // so that slamgpu_points_append can grow the set in place
+    // Observations of point i are obs_desc[obs_offset[i] .. obs_end[i]).  A set made by slamgpu_points_upload /
+    // _append is CSR (obs_end = obs_offset + 1, one array).  A MUTABLE set (slamgpu_points_create, map_api.cu)
+    // has two arrays and an observation arena with slack: a point whose observations change gets a new run at
+    // the arena's top, removed points are tombstones (no observations, NaN position: they fail is_in_image),
+    // and the arena / the slots are repacked in Map order when the garbage outweighs the live part.
+    const int32_t* obs_end = nullptr;
+    bool is_mutable = false;
+    void* pts_blob = nullptr;     // mutable: [pos][normal][range][obs_offset][obs_end][pt_matched] for cap_n slots
+    void* obs_blob = nullptr;     // mutable: [obs_desc][obs_kf] for cap_obs observations
+    void* kf_blob = nullptr;      // mutable: [kf_center][kf_dirty] for cap_kf observers
+    int32_t* obs_end_w = nullptr; // mutable: the writable obs_end
+    int32_t* obs_kf = nullptr;    // [cap_obs] observer (key frame) id of every observation
+    float* kf_center = nullptr;   // [cap_kf * 3] Frame::camera_center() of every observer, by id
+    uint8_t* kf_dirty = nullptr;  // [cap_kf] set while an observer's centre has moved and its points are stale
+    int n_kf = 0, cap_kf = 0;
+    int n_live = 0;
+    int64_t arena_top = 0;        // first free observation of the arena (n_obs = live observations)
+    std::vector<int32_t> h_begin, h_count;   // host mirror of the runs, by slot
+    std::vector<uint8_t> h_alive;
 };
+void free_points(PointSetDev& p);   // slamgpu.cu
 
 // Device-resident DBoW2 vocabulary, re-laid out by CHILD POSITION: position c of the child array is one
 // node, its descriptor sits at cdesc[c] (the children of a node are contiguous, so one level of the
@@ -153,7 +183,8 @@ struct slamgpu_ctx {
     bool kd_async = true;     // SLAMGPU_KD_ASYNC=0: build the KD-tree inside slamgpu_frame_upload instead of on a thread
     bool proj_walk = false;   // SLAMGPU_PROJ_WALK=1: use the thread-per-point KD-walk kernel
     int bf_engine = 0;        // SLAMGPU_BF_ENGINE=int|tc overrides the brute-force engine choice (0 = by size, 1 = int, 2 = tc)
-    int tc_variant = 0;       // SLAMGPU_TC_VARIANT: debug switches of the tensor-core scan
+    int tc_variant = 0;       // SLAMGPU_TC_VARIANT: debug switches of the tensor-core scans; read only in -DSLAMGPU_DEBUG_VARIANTS builds
+    bool tc_attr_set = false, tc4_attr_set = false;   // dynamic-smem opt-in of the tensor-core scans done on this context's device
     slamgpu::Arena d_exp;     // expanded (int8) descriptors of the tensor-core scan
     std::vector<std::pair<cudaEvent_t, cudaEvent_t>> prof_events[4];   // per SLAMGPU_KERNEL_*
     std::vector<cudaEvent_t> prof_pool;
@@ -274,7 +305,8 @@ struct ProjCommonArgs {
     const float* pos;
     const float* normal;
     const float* range;
-    const int32_t* obs_offset;
+    const int32_t* obs_offset;    // first observation of a point ...
+    const int32_t* obs_end;       // ... and one past its last (obs_offset + 1 for a CSR set)
     const uint4* obs_desc;
     const int32_t* order;
     int n_visit;

@@ -30,7 +30,7 @@ def test_library_exports_every_declared_symbol(pkg):
     for name in header_symbols():
         assert hasattr(lib, name), f"{name} declared in include/slamgpu.h but not exported"
     assert sorted(pkg.binding.SIGNATURES) == header_symbols()
-    assert lib.slamgpu_abi_version() == 1
+    assert lib.slamgpu_abi_version() == 2
 
 
 def test_dynamic_symbol_table_has_only_the_c_abi(pkg):
