@@ -253,6 +253,14 @@ SLAMGPU_API int slamgpu_match_projection(slamgpu_ctx* ctx, int frame_id, int set
                              const slamgpu_proj_params* params, const uint8_t* skip, const int32_t* order,
                              int n_order, int32_t* out_point, int32_t* out_dist);
 
+/* Same with `skip` as a LIST: matched_points = the indices of the points with frame.is_matched(point)
+ * (src/MapMatcher.cpp:53) -- at most one per keypoint, so a call against a large resident set uploads
+ * O(keypoints + n_order) instead of a mask over the whole set.  match_key_frame's !is_observed_by(kf) (:169)
+ * is expressed through `order` = the key frame's points, ascending. */
+SLAMGPU_API int slamgpu_match_projection_lists(slamgpu_ctx* ctx, int frame_id, int set_id, const float* pose_colmajor16,
+                                   const slamgpu_proj_params* params, const int32_t* matched_points, int n_matched,
+                                   const int32_t* order, int n_order, int32_t* out_point, int32_t* out_dist);
+
 /* Same, with diagnostics: per visited point its projection dbg_uv [n_visit x 2] (NaN if skipped up
  * front), chosen keypoint dbg_kp and distance dbg_d (-1 = proposes nothing); stats[0] = projections
  * within 1e-4 px of an image border, stats[1] = (point, keypoint) pairs within 1e-4 px of the
@@ -415,6 +423,22 @@ SLAMGPU_API int slamgpu_pnp_ransac_score(slamgpu_ctx* ctx, const float* object, 
                              int n_problems, const double* hyp_rt, const int32_t* hyp_offset, const double* K4,
                              double reproj_error, double confidence, int model_points, int max_iters,
                              int32_t* out_count, int32_t* out_best, int32_t* out_inliers, uint8_t* out_mask);
+
+/* ------------------------------------------------------------------------------------------
+ * Host restatements (no device): the float expressions of the projection path in the operation order the
+ * kernels use, so that a host WITH Eigen can compare them bit for bit with the reference's own code
+ * (MapMatcherGpu::self_check / audit, tools/eigen_order_check.cpp).  At u >= 1024 px one float ulp is
+ * 1.2e-4 px, more than the 1e-4 px tolerance, so the order matters.
+ *   slamgpu_host_project        Camera::project (src/Camera.cpp:25-32): out_uv [2]
+ *   slamgpu_host_camera_center  Frame::camera_center (src/Frame.cpp:39-42): out_center [3]
+ *   slamgpu_host_point_stats    MapPoint::avg_viewing_normal / observed_distance_range (src/MapPoint.cpp:24-45)
+ *                               of one point: obs_center [n_obs x 3] in observation order, out_normal [3], out_range [2]
+ * ---------------------------------------------------------------------------------------- */
+SLAMGPU_API int slamgpu_host_project(const float* pose_colmajor16, const slamgpu_proj_params* params, const float* xyz,
+                         float* out_uv);
+SLAMGPU_API int slamgpu_host_camera_center(const float* pose_colmajor16, float* out_center);
+SLAMGPU_API int slamgpu_host_point_stats(const float* xyz, int n_obs, const float* obs_center, float* out_normal,
+                             float* out_range);
 
 /* ------------------------------------------------------------------------------------------
  * Diagnostics

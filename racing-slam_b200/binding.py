@@ -90,6 +90,8 @@ SIGNATURES = {
     "slamgpu_points_live": (C.c_int, [_ctx, C.c_int, C.POINTER(C.c_int), _i64p, _i64p]),
     "slamgpu_match_projection": (C.c_int, [_ctx, C.c_int, C.c_int, _f32p, C.POINTER(ProjParams), _u8p, _i32p, C.c_int,
                                            _i32p, _i32p]),
+    "slamgpu_match_projection_lists": (C.c_int, [_ctx, C.c_int, C.c_int, _f32p, C.POINTER(ProjParams), _i32p, C.c_int,
+                                                 _i32p, C.c_int, _i32p, _i32p]),
     "slamgpu_match_projection_ex": (C.c_int, [_ctx, C.c_int, C.c_int, _f32p, C.POINTER(ProjParams), _u8p, _i32p,
                                               C.c_int, _i32p, _i32p, _f32p, _i32p, _i32p, _i64p]),
     "slamgpu_track_match": (C.c_int, [_ctx, C.c_int, C.c_int, _f32p, C.POINTER(ProjParams), _i32p, C.c_int, _i32p,
@@ -117,6 +119,9 @@ SIGNATURES = {
                                         C.POINTER(C.c_int)]),
     "slamgpu_pnp_ransac_score": (C.c_int, [_ctx, _f32p, _f32p, _i32p, C.c_int, _f64p, _i32p, _f64p, C.c_double,
                                            C.c_double, C.c_int, C.c_int, _i32p, _i32p, _i32p, _u8p]),
+    "slamgpu_host_project": (C.c_int, [_f32p, C.POINTER(ProjParams), _f32p, _f32p]),
+    "slamgpu_host_camera_center": (C.c_int, [_f32p, _f32p]),
+    "slamgpu_host_point_stats": (C.c_int, [_f32p, C.c_int, _f32p, _f32p, _f32p]),
     "slamgpu_profile_enable": (C.c_int, [_ctx, C.c_int]),
     "slamgpu_profile_read": (C.c_int, [_ctx, C.c_int, C.POINTER(C.c_double), _i64p]),
     "slamgpu_bench_popc": (C.c_int, [_ctx, C.POINTER(C.c_double), C.POINTER(C.c_int), C.POINTER(C.c_double)]),
@@ -164,6 +169,33 @@ def kd_build_host(xy) -> np.ndarray:
     if rc != OK:
         raise SlamGpuError(rc, lib.slamgpu_last_error().decode())
     return perm
+
+
+def host_project(pose, params: ProjParams, xyz) -> np.ndarray:
+    """Camera::project in the library's operation order, on the host (no device)."""
+    pose = np.ascontiguousarray(pose, np.float32).reshape(16)
+    xyz = np.ascontiguousarray(xyz, np.float32).reshape(-1, 3)
+    out = np.zeros((len(xyz), 2), np.float32)
+    lib = load()
+    for i in range(len(xyz)):
+        lib.slamgpu_host_project(_p(pose, C.c_float), C.byref(params), _p(xyz[i], C.c_float), _p(out[i], C.c_float))
+    return out
+
+
+def host_camera_center(pose) -> np.ndarray:
+    pose = np.ascontiguousarray(pose, np.float32).reshape(16)
+    out = np.zeros(3, np.float32)
+    load().slamgpu_host_camera_center(_p(pose, C.c_float), _p(out, C.c_float))
+    return out
+
+
+def host_point_stats(xyz, obs_center):
+    xyz = np.ascontiguousarray(xyz, np.float32).reshape(3)
+    obs_center = np.ascontiguousarray(obs_center, np.float32).reshape(-1, 3)
+    normal, rng = np.zeros(3, np.float32), np.zeros(2, np.float32)
+    load().slamgpu_host_point_stats(_p(xyz, C.c_float), len(obs_center), _p(obs_center, C.c_float),
+                                    _p(normal, C.c_float), _p(rng, C.c_float))
+    return normal, rng
 
 
 def ransac_select(good_count, n_points: int, model_points: int = 5, confidence: float = 0.99, max_iters: int = 200):
@@ -532,6 +564,20 @@ class Context:
             _p(order, C.c_int32), n_order, _p(out_point, C.c_int32), _p(out_dist, C.c_int32), _p(uv, C.c_float),
             _p(kp, C.c_int32), _p(d, C.c_int32), _p(stats, C.c_int64)))
         return out_point, out_dist, dict(uv=uv, kp=kp, d=d, near_border=int(stats[0]), near_radius=int(stats[1]))
+
+    def match_projection_lists(self, frame_id: int, set_id: int, nkp: int, pose, params: ProjParams, matched_points,
+                               order=None):
+        """match_projection with frame.is_matched(point) given as an index list instead of a mask."""
+        pose = np.ascontiguousarray(pose, np.float32).reshape(16)
+        matched_points = np.ascontiguousarray(matched_points, np.int32).reshape(-1)
+        order = _opt(order, np.int32)
+        out_point = np.full(nkp, -1, np.int32)
+        out_dist = np.full(nkp, -1, np.int32)
+        self._check(self._lib.slamgpu_match_projection_lists(
+            self._h, frame_id, set_id, _p(pose, C.c_float), C.byref(params), _p(matched_points, C.c_int32),
+            len(matched_points), _p(order, C.c_int32), 0 if order is None else len(order), _p(out_point, C.c_int32),
+            _p(out_dist, C.c_int32)))
+        return out_point, out_dist
 
     def track_match(self, frame_id: int, set_id: int, nkp: int, pose, params: ProjParams, matched_points, kf_points):
         """match_key_frame -> apply -> match_map chained on the device (src/Tracker.cpp:232-248).

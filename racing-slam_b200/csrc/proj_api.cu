@@ -132,7 +132,7 @@ void fill_frame(ProjFrameArgs& f, const FrameDev& fd, const float* pose, const s
 int match_projection_impl(slamgpu_ctx* ctx, const int* frame_ids, int n_frames, int set_id, const float* poses,
                           const slamgpu_proj_params* params, const uint8_t* skip, const int32_t* order, int n_order,
                           int32_t* out_point, int32_t* out_dist, float* dbg_uv, int32_t* dbg_kp, int32_t* dbg_d,
-                          int64_t* stats)
+                          int64_t* stats, const int32_t* matched_points = nullptr, int n_matched = 0)
 {
     SG_CTX(ctx);
     SG_TRY(check_params(params));
@@ -143,6 +143,11 @@ int match_projection_impl(slamgpu_ctx* ctx, const int* frame_ids, int n_frames, 
     if (ps_it == ctx->point_sets.end()) return fail(SLAMGPU_ERR_NOTFOUND, "unknown point set id");
     const PointSetDev& ps = ps_it->second;
     SG_CHECK(order != nullptr || n_order == 0 || n_order == ps.n, "n_order without an order array");
+    // the sparse form of `skip` (one frame only): the points with frame.is_matched(point), as an index list
+    SG_CHECK(n_matched >= 0 && (n_matched == 0 || matched_points != nullptr), "bad matched-point list");
+    SG_CHECK(n_matched == 0 || (skip == nullptr && n_frames == 1), "matched_points excludes skip and batches");
+    for (int i = 0; i < n_matched; ++i)
+        SG_CHECK(matched_points[i] >= 0 && matched_points[i] < ps.n, "matched_points entry outside the point set");
     const int n_visit = order ? n_order : ps.n;
     SG_CHECK(n_visit >= 0, "negative visit count");
     if (order) {
@@ -172,7 +177,8 @@ int match_projection_impl(slamgpu_ctx* ctx, const int* frame_ids, int n_frames, 
     const size_t skip_bytes = skip ? Carver::padded(static_cast<size_t>(n_frames) * ps.n) : 0;
     const size_t order_bytes = order ? Carver::padded(sizeof(int32_t) * n_order) : 0;
     const size_t fargs_bytes = n_frames > 1 ? Carver::padded(sizeof(ProjFrameArgs) * n_frames) : 0;
-    const size_t up_bytes = skip_bytes + order_bytes + fargs_bytes;
+    const size_t mlist_bytes = n_matched ? Carver::padded(sizeof(int32_t) * n_matched) : 0;
+    const size_t up_bytes = skip_bytes + order_bytes + fargs_bytes + mlist_bytes;
     const size_t out_bytes = Carver::padded(sizeof(int32_t) * total_kp) * 2;
     size_t dbg_bytes = 0;
     if (want_dbg)
@@ -188,6 +194,8 @@ int match_projection_impl(slamgpu_ctx* ctx, const int* frame_ids, int n_frames, 
     int32_t* h_order = order ? hio.take<int32_t>(n_order) : nullptr;
     ProjFrameArgs* d_fargs = n_frames > 1 ? dio.take<ProjFrameArgs>(n_frames) : nullptr;
     ProjFrameArgs* h_fargs_stage = n_frames > 1 ? hio.take<ProjFrameArgs>(n_frames) : nullptr;
+    int32_t* d_mlist = n_matched ? dio.take<int32_t>(n_matched) : nullptr;
+    int32_t* h_mlist = n_matched ? hio.take<int32_t>(n_matched) : nullptr;
     int32_t* d_out_point = dio.take<int32_t>(total_kp);
     int32_t* d_out_dist = dio.take<int32_t>(total_kp);
     float* d_dbg_uv = nullptr;
@@ -213,7 +221,7 @@ int match_projection_impl(slamgpu_ctx* ctx, const int* frame_ids, int n_frames, 
     size_t kp_off = 0;
     for (int i = 0; i < n_frames; ++i) {
         fill_frame(fargs[i], *fds[i], poses + 16 * static_cast<size_t>(i), *params);
-        fargs[i].skip = skip ? d_skip + static_cast<size_t>(i) * ps.n : nullptr;
+        fargs[i].skip = skip ? d_skip + static_cast<size_t>(i) * ps.n : (matched_points ? ps.pt_matched : nullptr);
         fargs[i].out_point = d_out_point + kp_off;
         fargs[i].out_dist = d_out_dist + kp_off;
         kp_off += static_cast<size_t>(fds[i]->nkp);
@@ -224,8 +232,10 @@ int match_projection_impl(slamgpu_ctx* ctx, const int* frame_ids, int n_frames, 
         if (skip) std::memcpy(h_skip, skip, static_cast<size_t>(n_frames) * ps.n);
         if (order) std::memcpy(h_order, order, sizeof(int32_t) * n_order);
         if (n_frames > 1) std::memcpy(h_fargs_stage, fargs.data(), sizeof(ProjFrameArgs) * n_frames);
+        if (n_matched) std::memcpy(h_mlist, matched_points, sizeof(int32_t) * n_matched);
         SG_CUDA(cudaMemcpyAsync(ctx->d_io.ptr, ctx->h_stage.ptr, up_bytes, cudaMemcpyHostToDevice, ctx->stream));
     }
+    if (matched_points) SG_TRY(proj_launch_flags(ctx, d_mlist, n_matched, ps.pt_matched, ps.n));
     if (want_dbg) {   // rows the kernel never reaches read as NaN / -1
         SG_CUDA(cudaMemsetAsync(d_dbg_uv, 0xFF, dbg_bytes - Carver::padded(2 * sizeof(unsigned long long)), ctx->stream));
         SG_CUDA(cudaMemsetAsync(d_stats, 0, 2 * sizeof(unsigned long long), ctx->stream));
@@ -752,6 +762,16 @@ int slamgpu_match_projection_ex(slamgpu_ctx* ctx, int frame_id, int set_id, cons
 {
     return match_projection_impl(ctx, &frame_id, 1, set_id, pose_colmajor16, params, skip, order, n_order, out_point,
                                  out_dist, dbg_uv, dbg_kp, dbg_d, stats);
+}
+
+int slamgpu_match_projection_lists(slamgpu_ctx* ctx, int frame_id, int set_id, const float* pose_colmajor16,
+                                   const slamgpu_proj_params* params, const int32_t* matched_points, int n_matched,
+                                   const int32_t* order, int n_order, int32_t* out_point, int32_t* out_dist)
+{
+    static const int32_t none = 0;
+    return match_projection_impl(ctx, &frame_id, 1, set_id, pose_colmajor16, params, nullptr, order, n_order, out_point,
+                                 out_dist, nullptr, nullptr, nullptr, nullptr, matched_points ? matched_points : &none,
+                                 n_matched);
 }
 
 int slamgpu_track_match(slamgpu_ctx* ctx, int frame_id, int set_id, const float* pose_colmajor16,

@@ -938,6 +938,18 @@ int proj_launch_track(slamgpu_ctx* ctx, const ProjCommonArgs& common, const Proj
     return SLAMGPU_OK;
 }
 
+// flags[0..n_flags) = 0, then flags[idx[i]] = 1: frame.is_matched(point) from a sparse list (src/MapMatcher.cpp:53)
+int proj_launch_flags(slamgpu_ctx* ctx, const int32_t* d_idx, int n, uint8_t* d_flags, int n_flags)
+{
+    if (n_flags > 0) SG_CUDA(cudaMemsetAsync(d_flags, 0, static_cast<size_t>(n_flags), ctx->stream));
+    if (n > 0) {
+        proj_scatter_flags_kernel<<<(n + 255) / 256, 256, 0, ctx->stream>>>(d_idx, n, d_flags);
+        ctx->launches++;
+        SG_CUDA(cudaGetLastError());
+    }
+    return SLAMGPU_OK;
+}
+
 int proj_launch_point_stats(slamgpu_ctx* ctx, const float* d_pos, int n, const int32_t* d_obs_offset,
                             const float* d_obs_center, float* d_normal, float* d_range)
 {

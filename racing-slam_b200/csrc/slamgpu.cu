@@ -8,6 +8,8 @@
 #include <numeric>
 #include <thread>
 
+#include <cmath>
+
 #include "slamgpu_internal.cuh"
 
 namespace slamgpu {
@@ -369,6 +371,80 @@ int slamgpu_profile_read(slamgpu_ctx* ctx, int kernel, double* total_ms, int64_t
     if (total_ms) *total_ms = sum;
     if (launches) *launches = static_cast<int64_t>(v.size());
     v.clear();
+    return SLAMGPU_OK;
+}
+
+// ---- host restatements of the float expressions of the projection path (no device needed) --------------
+// The same operation order as the kernels (proj_kernels.cu, map_api.cu) and the oracle, in plain host floats
+// (-ffp-contract=off): what MapMatcherGpu::self_check / audit and tools/eigen_order_check.cpp compare with the
+// reference's Eigen expressions, bit for bit.
+int slamgpu_host_project(const float* pose_colmajor16, const slamgpu_proj_params* params, const float* xyz, float* out_uv)
+{
+    SG_CHECK(pose_colmajor16 && params && xyz && out_uv, "null pointer");
+    float M[12];
+    host_projection_matrix(pose_colmajor16, params->fx, params->fy, params->cx, params->cy, M);
+    float h[3];
+    for (int i = 0; i < 3; ++i) {      // M[:, :3] * X summed a0 + (a1 + a2), then + M[:, 3] (src/Camera.cpp:27)
+        volatile float p0 = M[4 * i] * xyz[0], p1 = M[4 * i + 1] * xyz[1], p2 = M[4 * i + 2] * xyz[2];
+        volatile float s = hsum3(p0, p1, p2);
+        h[i] = s + M[4 * i + 3];
+    }
+    if (h[2] < 0.0f) {                 // src/Camera.cpp:28-30
+        out_uv[0] = -1.0f;
+        out_uv[1] = -1.0f;
+    } else {
+        out_uv[0] = h[0] / h[2];
+        out_uv[1] = h[1] / h[2];
+    }
+    return SLAMGPU_OK;
+}
+
+int slamgpu_host_camera_center(const float* pose_colmajor16, float* out_center)
+{
+    SG_CHECK(pose_colmajor16 && out_center, "null pointer");
+    host_camera_center(pose_colmajor16, out_center);
+    return SLAMGPU_OK;
+}
+
+static void host_normalized3(const float v[3], float out[3])      // Eigen normalized(): z > 0 ? v / sqrt(z) : v
+{
+    volatile float a = v[0] * v[0], b = v[1] * v[1], c = v[2] * v[2];
+    const float z = hsum3(a, b, c);
+    if (z > 0.0f) {
+        const float n = std::sqrt(z);
+        out[0] = v[0] / n;
+        out[1] = v[1] / n;
+        out[2] = v[2] / n;
+    } else {
+        out[0] = v[0]; out[1] = v[1]; out[2] = v[2];
+    }
+}
+
+// MapPoint::avg_viewing_normal / observed_distance_range (src/MapPoint.cpp:24-45) of one point, its observers'
+// camera centres in the host's observation order
+int slamgpu_host_point_stats(const float* xyz, int n_obs, const float* obs_center, float* out_normal, float* out_range)
+{
+    SG_CHECK(xyz && out_normal && out_range && n_obs >= 0 && (n_obs == 0 || obs_center), "bad argument");
+    float acc[3] = {0.0f, 0.0f, 0.0f};
+    float nearest = 3.402823466e+38f, furthest = 0.0f;
+    for (int o = 0; o < n_obs; ++o) {
+        const float* C = obs_center + 3 * static_cast<size_t>(o);
+        const float d[3] = {xyz[0] - C[0], xyz[1] - C[1], xyz[2] - C[2]};
+        float v[3], vv[3];
+        host_normalized3(d, v);
+        host_normalized3(v, vv);
+        for (int k = 0; k < 3; ++k) {
+            volatile float t = acc[k] + vv[k];
+            acc[k] = t;
+        }
+        volatile float a = d[0] * d[0], b = d[1] * d[1], c = d[2] * d[2];
+        const float dist = std::sqrt(hsum3(a, b, c));
+        nearest = dist < nearest ? dist : nearest;
+        furthest = furthest < dist ? dist : furthest;
+    }
+    host_normalized3(acc, out_normal);
+    out_range[0] = nearest;
+    out_range[1] = furthest;
     return SLAMGPU_OK;
 }
 

@@ -326,6 +326,7 @@ int proj_launch(slamgpu_ctx* ctx, const ProjCommonArgs& common, const ProjFrameA
 int proj_launch_track(slamgpu_ctx* ctx, const ProjCommonArgs& common, const ProjFrameArgs& frame, uint8_t* d_pt_matched,
                       uint8_t* d_kp_matched, const int32_t* d_matched_points, int n_matched, const int32_t* d_kf_order,
                       int n_kf, int32_t* d_out /* [4 x nkp]: kf point, kf dist, map point, map dist */);
+int proj_launch_flags(slamgpu_ctx* ctx, const int32_t* d_idx, int n, uint8_t* d_flags, int n_flags);
 int proj_launch_point_stats(slamgpu_ctx* ctx, const float* d_pos, int n, const int32_t* d_obs_offset,
                             const float* d_obs_center, float* d_normal, float* d_range);
 int proj_launch_kd_gather(slamgpu_ctx* ctx, const float2* d_xy, const int32_t* d_perm, int n, float2* d_kd_xy);

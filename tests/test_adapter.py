@@ -20,7 +20,10 @@ def build_driver():
     assert os.path.exists(DRIVER)
 
 
-def make_world(pkg, seed=71, n_points=1200, nkp=500, n_kf=4, kf_kp=300):
+def make_world(pkg, seed=71, n_points=1200, nkp=500, n_kf=4, kf_kp=1500):
+    """A consistent world: every observation (key frame k, keypoint idx) of a point is also the key frame's map
+    match at idx (Map::associate sets both sides, src/Map.cpp:97-113).  Initial observations use keypoints
+    [0, 1100) of each key frame; the mutation script takes free ones from [1100, kf_kp)."""
     syn = pkg.synthetic
     rng = np.random.default_rng(seed)
     cam = syn.KITTI
@@ -30,26 +33,20 @@ def make_world(pkg, seed=71, n_points=1200, nkp=500, n_kf=4, kf_kp=300):
         T = syn.make_pose(rng, 3.0, 0.8)
         w["kfs"].append(dict(xy=syn.keypoints_integer(kf_kp, cam["width"], cam["height"], seed + k),
                              desc=rng.integers(0, 256, (kf_kp, 32), dtype=np.uint8), pose=syn.pose_colmajor(T)))
+    next_kp = [0] * n_kf
     for i in range(n_points):
         obs, used = [], set()
         for o in range(sc.obs_offset[i], sc.obs_offset[i + 1]):
             k = int(rng.integers(0, n_kf))
-            if k in used:                       # observations() is keyed by key frame: one per key frame
+            if k in used or next_kp[k] >= min(1100, kf_kp):     # observations() is keyed by key frame: one per key frame
                 continue
             used.add(k)
-            idx = int(rng.integers(0, kf_kp))
+            idx = next_kp[k]
+            next_kp[k] += 1
             w["kfs"][k]["desc"][idx] = sc.obs_desc[o]
             obs.append((k, idx))
-            if rng.random() < 0.3:
-                w["kf_matches"].append((k, idx, i))
+            w["kf_matches"].append((k, idx, i))
         w["points"].append(dict(pos=sc.pos[i], obs=obs))
-    # one map point per key-frame keypoint
-    seen, km = set(), []
-    for k, idx, i in w["kf_matches"]:
-        if (k, idx) not in seen:
-            seen.add((k, idx))
-            km.append((k, idx, i))
-    w["kf_matches"] = km
     w["frame"] = dict(xy=sc.kp_xy, desc=sc.kp_desc, pose=sc.pose)
     used_p = set()
     for kp in np.nonzero(sc.kp_matched)[0][:25]:
@@ -59,6 +56,72 @@ def make_world(pkg, seed=71, n_points=1200, nkp=500, n_kf=4, kf_kp=300):
             w["frame_matches"].append((int(kp), pi))
     fuse = list(range(0, n_points, 3)) + [-1, -1] + list(range(40))
     w["fuse"] = fuse
+    return w
+
+
+def add_script(w, pkg, seed=5):
+    """The reference's mutators in a scripted order (tests/adapter_mock/adapter_driver.cpp replays them):
+    0 associate, 1 disassociate, 2 remove_point, 3 fuse, 4 set_position, 5 set_pose, 6 create_point, 7 CHECK."""
+    syn = pkg.synthetic
+    rng = np.random.default_rng(seed)
+    n_kf, kf_kp = len(w["kfs"]), len(w["kfs"][0]["xy"])
+    n0 = len(w["points"])
+    live = list(range(n0))
+    free_kp = [1100] * n_kf
+    ops = [(7,)]
+
+    def pick(n):
+        return [int(x) for x in rng.choice(live, n, replace=False)]
+
+    def take_kp(k):
+        free_kp[k] += 1
+        assert free_kp[k] <= kf_kp
+        return free_kp[k] - 1
+
+    for pid in pick(60):                                    # Map::associate at a free keypoint
+        k = int(rng.integers(0, n_kf))
+        ops.append((0, k, pid, take_kp(k)))
+    ops.append((7,))
+    for pid in pick(60):                                    # Map::disassociate
+        ops.append((1, int(rng.integers(0, n_kf)), pid))
+    ops.append((7,))
+    for pid in pick(20):                                    # associate at an OCCUPIED keypoint: the old owner loses it
+        ops.append((0, int(rng.integers(0, n_kf)), pid, int(rng.integers(0, 200))))
+    ops.append((7,))
+    pairs = pick(60)                                        # Map::fuse: kept <- discarded
+    for a, b in zip(pairs[:30], pairs[30:]):
+        ops.append((3, a, b))
+        live.remove(b)
+    ops.append((7,))
+    for pid in [int(x) for x in rng.choice(live[:len(live) // 2], 80, replace=False)]:   # erase from the middle
+        ops.append((2, pid))
+        live.remove(pid)
+    ops.append((7,))
+    for pid in pick(200):                                   # bundle adjustment: positions and two key-frame poses
+        x = w["points"][pid]["pos"] + rng.normal(0, 0.02, 3)
+        ops.append((4, pid, float(x[0]), float(x[1]), float(x[2])))
+    for k in (0, w["required"]):
+        T = np.asarray(w["kfs"][k]["pose"], np.float32).reshape(4, 4, order="F").copy()
+        T[:3, 3] += rng.normal(0, 0.05, 3).astype(np.float32)
+        ops.append((5, k, syn.pose_colmajor(T)))
+    ops.append((7,))
+    for _ in range(100):                                    # Map::create_point: new points seen by one key frame
+        src = w["points"][int(rng.integers(0, n0))]["pos"] + rng.normal(0, 0.3, 3)
+        k = int(rng.integers(0, n_kf))
+        ops.append((6, float(src[0]), float(src[1]), float(src[2]), k, take_kp(k)))
+    ops.append((7,))
+    for pid in pick(420):                                   # enough tombstones for the mirror to compact its slots
+        ops.append((2, pid))
+        live.remove(pid)
+    ops.append((7,))
+    for pid in pick(50):                                    # and life goes on after the renumbering
+        k = int(rng.integers(0, n_kf))
+        ops.append((0, k, pid, take_kp(k)))
+    for pid in pick(30):
+        ops.append((2, pid))
+        live.remove(pid)
+    ops.append((7,))
+    w["ops"] = ops
     return w
 
 
@@ -92,15 +155,70 @@ def write_world(w, path):
         f.write(struct.pack("<i", len(w["fuse"])))
         f.write(np.asarray(w["fuse"], np.int32).tobytes())
         f.write(struct.pack("<i", w["required"]))
+        ops = w.get("ops", [])
+        f.write(struct.pack("<i", len(ops)))
+        for op in ops:
+            code = op[0]
+            f.write(struct.pack("<i", code))
+            if code == 0:
+                f.write(struct.pack("<iii", *op[1:]))
+            elif code in (1, 3):
+                f.write(struct.pack("<ii", *op[1:]))
+            elif code == 2:
+                f.write(struct.pack("<i", op[1]))
+            elif code == 4:
+                f.write(struct.pack("<ifff", *op[1:]))
+            elif code == 5:
+                f.write(struct.pack("<i", op[1]))
+                f.write(np.ascontiguousarray(op[2], np.float32).tobytes())
+            elif code == 6:
+                f.write(struct.pack("<fffii", *op[1:]))
+
+
+SCALARS = ("frame_matches_after_track", "self_check", "modes_agree", "audit", "legacy_uploads", "full_uploads")
+
+
+def parse_script(lines):
+    """-> list of checks: dict(map=[(pid, pos bits[3], [(k, idx)])], poses=[16 bits], results...)"""
+    checks, i, extra = [], 0, {}
+    cur = None
+    while i < len(lines) and lines[i].strip():
+        tok = lines[i].split()
+        name, n = tok[0], int(tok[1])
+        if name == "check":
+            cur = {}
+            checks.append(cur)
+            i += 1
+        elif name == "map":
+            rows = []
+            for r in range(n):
+                t = [int(x) for x in lines[i + 1 + r].split()]
+                obs = [(t[5 + 2 * j], t[6 + 2 * j]) for j in range(t[4])]
+                rows.append((t[0], np.array(t[1:4], np.uint32).view(np.float32), obs))
+            cur["map"] = rows
+            i += 1 + n
+        elif name == "poses":
+            cur["poses"] = [np.array([int(x) for x in lines[i + 1 + r].split()], np.uint32).view(np.float32) for r in range(n)]
+            i += 1 + n
+        elif name in SCALARS:
+            (cur if name == "audit" else extra)[name] = n
+            i += 1
+        else:
+            cur[name] = [tuple(int(x) for x in lines[i + 1 + r].split()) for r in range(n)]
+            i += 1 + n
+    return checks, extra
 
 
 def parse_output(path):
     lines = open(path).read().split("\n")
     res, i = {}, 0
     while i < len(lines) and lines[i].strip():
+        if lines[i].strip() == "script":
+            res["script"], res["script_extra"] = parse_script(lines[i + 1:])
+            break
         name, n = lines[i].split()
         n = int(n)
-        if name == "frame_matches_after_track":
+        if name in SCALARS:
             res[name] = n
             i += 1
             continue
@@ -190,6 +308,9 @@ def test_adapter_end_to_end_vs_oracle(pkg, oracle, tmp_path):
     assert n_lists >= 2
     o_t, o_q = oracle.match_features(kfs[0]["desc"], fr["desc"], 64.0)
     assert got["match_features"] == list(zip(o_t.tolist(), o_q.tolist()))
+    # the library's float order against the data model's own Camera::project (the mock's here, Eigen's in the
+    # reference tree): 4096 seeded projections, bit for bit
+    assert got["self_check"] == 0
 
     # MapMatcherGpu::track = match_key_frame, add_map_match loop, match_map, add_map_match loop
     # (src/Tracker.cpp:232-248): the first stage equals the stand-alone call, the second sees its matches
@@ -200,3 +321,75 @@ def test_adapter_end_to_end_vs_oracle(pkg, oracle, tmp_path):
         skip_after[pi] = 1
     assert got["track_map"] == run(skip_after, None, 0) and len(got["track_map"]) > 10
     assert got["frame_matches_after_track"] == len(w["frame_matches"]) + len(got["track_key_frame"]) + len(got["track_map"])
+
+
+@pytest.mark.gpu
+def test_adapter_resident_map_follows_a_mutation_script(pkg, oracle, tmp_path):
+    """The scripted mutation sequence (associate, disassociate, steal a keypoint, fuse, remove from the middle, bundle
+    adjustment of positions and key-frame poses, create_point, a compaction) replayed by the C++ driver three times:
+    per-call uploads, resident mirror fed by the data model's notifications, resident mirror that scans.  All three
+    must agree, the resident ones must never fall back to a whole-map upload, their audit must be clean, and every
+    CHECK step must equal the oracle fed the map the host dumped at that step (a freshly flattened map)."""
+    build_driver()
+    w = add_script(make_world(pkg), pkg)
+    write_world(w, tmp_path / "world.bin")
+    r = subprocess.run([DRIVER, str(tmp_path / "world.bin"), str(tmp_path / "out.txt")], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    got = parse_output(tmp_path / "out.txt")
+    assert got["modes_agree"] == 1
+    extra = got["script_extra"]
+    assert extra["full_uploads"] == 1          # attach() only: everything after it went up as deltas
+    assert extra["legacy_uploads"] == 0        # no call fell back to flattening the visited points
+    assert "compactions 1" in r.stderr or "compactions 2" in r.stderr, r.stderr
+    checks = got["script"]
+    assert len(checks) == sum(1 for op in w["ops"] if op[0] == 7)
+
+    kfs, cam, fr = w["kfs"], w["cam"], w["frame"]
+    perm = oracle.kd_build(fr["xy"])
+    nkp = len(fr["xy"])
+    req = w["required"]
+    for step, c in enumerate(checks):
+        assert c["audit"] == 0, step
+        pids = [row[0] for row in c["map"]]
+        live_of = {pid: j for j, pid in enumerate(pids)}
+        n = len(pids)
+        pos = np.stack([row[1] for row in c["map"]]).astype(np.float32)
+        centers = [oracle.camera_center(p) for p in c["poses"]]
+        off = np.zeros(n + 1, np.int32)
+        od, oc, observers = [], [], []
+        for j, (_, _, obs) in enumerate(c["map"]):
+            observers.append({k for k, _ in obs})
+            for k, idx in obs:
+                od.append(kfs[k]["desc"][idx])
+                oc.append(centers[k])
+            off[j + 1] = len(od)
+        od = np.asarray(od, np.uint8).reshape(-1, 32)
+        oc = np.asarray(oc, np.float32).reshape(-1, 3)
+        normal, rng_ = oracle.point_stats(pos, off, oc)
+        matched = np.zeros(nkp, np.uint8)
+        skip_m = np.zeros(n, np.uint8)
+        for kp, pid in w["frame_matches"]:
+            if pid in live_of:
+                matched[kp] = 1
+                skip_m[live_of[pid]] = 1
+
+        def run(kpm, skip, order, replace):
+            prm = oracle.ProjParams(cam["fx"], cam["fy"], cam["cx"], cam["cy"], cam["width"], cam["height"], 20.0,
+                                    64.0, 0.5, 2.0, 1.25, replace)
+            res = oracle.match_projection(fr["xy"], fr["desc"], perm, kpm, pos, normal, rng_, off, od, skip, order,
+                                          fr["pose"], prm, want_stats=False)
+            return [(pids[int(p)], kp) for kp, p in enumerate(res.point) if p >= 0]
+
+        assert c["match_map"] == run(matched, skip_m, None, 0), step
+        assert len(c["match_map"]) > 10, step
+        skip_k = np.array([1 if (skip_m[j] or req not in observers[j]) else 0 for j in range(n)], np.uint8)
+        assert c["match_key_frame"] == run(matched, skip_k, None, 0), step
+        order = np.array([live_of.get(pid, -1) if pid >= 0 else -1 for pid in w["fuse"]], np.int32)
+        assert c["match_for_fuse"] == run(matched, skip_m, order, 1), step
+        assert c["track_key_frame"] == c["match_key_frame"], step
+        kpm, skip_after = matched.copy(), skip_m.copy()
+        for pid, kp in c["track_key_frame"]:
+            kpm[kp] = 1
+            skip_after[live_of[pid]] = 1
+        assert c["track_map"] == run(kpm, skip_after, None, 0), step
+    assert sum(len(c["match_key_frame"]) for c in checks) > 10

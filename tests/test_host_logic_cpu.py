@@ -113,3 +113,26 @@ def test_matcher_flattening_keeps_host_observation_order(pkg):
     f.add_map_match(m.MapPointMatch(p0, 2))
     assert f.is_matched(p0) and not f.is_matched(p1) and f.is_matched(2) and not f.is_matched(0)
     assert [mm.keypoint_index for mm in f.map_matches()] == [2]
+
+
+def test_host_restatements_equal_the_oracle_bit_for_bit(pkg, oracle):
+    """slamgpu_host_project / _camera_center / _point_stats (what MapMatcherGpu::self_check / audit and
+    tools/eigen_order_check.cpp compare with the reference's Eigen code) are the oracle's operation order."""
+    syn = pkg.synthetic
+    for cam, seed in ((syn.KITTI, 5), (syn.HD1080, 6)):     # HD1080: u >= 1024 px, one ulp = 1.2e-4 px
+        sc = syn.projection_scene(3000, 100, seed, cam=cam)
+        prm = pkg.ProjParams(cam["fx"], cam["fy"], cam["cx"], cam["cy"], cam["width"], cam["height"], 20.0, 64.0, 0.5,
+                             2.0, 1.25, 0)
+        uv = pkg.binding.host_project(sc.pose, prm, sc.pos)
+        ref = oracle.project(sc.pose, cam["fx"], cam["fy"], cam["cx"], cam["cy"], sc.pos)
+        assert np.array_equal(uv.view(np.uint32), ref.view(np.uint32))
+        assert (uv[:, 0] >= 1024).sum() > 100 or cam is syn.KITTI
+        c = pkg.binding.host_camera_center(sc.pose)
+        assert np.array_equal(c.view(np.uint32), oracle.camera_center(sc.pose).view(np.uint32))
+        normal, rng_ = oracle.point_stats(sc.pos, sc.obs_offset, sc.obs_center)
+        for i in range(0, 3000, 7):
+            n, r = pkg.binding.host_point_stats(sc.pos[i], sc.obs_center[sc.obs_offset[i]:sc.obs_offset[i + 1]])
+            assert np.array_equal(n.view(np.uint32), normal[i].view(np.uint32))
+            assert np.array_equal(r.view(np.uint32), rng_[i].view(np.uint32))
+    n, r = pkg.binding.host_point_stats(np.zeros(3, np.float32), np.zeros((0, 3), np.float32))   # no observation
+    assert np.array_equal(n, np.zeros(3, np.float32)) and r[0] == np.finfo(np.float32).max and r[1] == 0.0
