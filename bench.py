@@ -138,6 +138,12 @@ def workload_name(args) -> str:
             f"(query > candidate)")
 
 
+def config_of(args) -> dict:
+    """The same object in both arms: what is measured.  How much of it one step of an arm takes is under `step`."""
+    return {"workload": workload_name(args), "key_frames": args.frames, "descriptors_per_key_frame": args.desc,
+            "max_distance": MAX_DIST, "ratio": RATIO, "pairs_in_the_whole_job": args.frames * (args.frames - 1) // 2}
+
+
 def step_pairs(pairs: np.ndarray, step: int, n: int) -> np.ndarray:
     """The n pairs of step `step`: a sliding window over this rank's shard (wraps around)."""
     idx = (np.arange(n, dtype=np.int64) + step * n) % len(pairs)
@@ -209,7 +215,8 @@ def run_reference(args, rank, world):
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": t / args.steps * 1e3, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-        "config": {"workload": workload_name(args), "pairs_per_step": n, "sharding": "cpu, rank 0 only"},
+        "config": config_of(args),
+        "step": {"pairs_per_step": n, "comparisons_per_step": n * per_pair, "sharding": "cpu, rank 0 only"},
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": kind, "sample": sample},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -299,16 +306,23 @@ def run_ours(args, rank, local_rank, world):
         # the one exchange of the path: rank 0's key-frame database to every GPU, one NCCL broadcast
         # of the device tensor over NVLink / NVSwitch, before the clock starts.  The other ranks drop their own
         # copy and match against what arrived.
-        pkg.sharding.replicate(db[:1] if rank == 0 else None, 0)          # warm the communicator
-        d_src = torch.from_numpy(db).cuda() if rank == 0 else None         # resident on the source GPU first
+        # Every rank knows the database's shape (frames x descriptors x 32 bytes), so the receive buffer is pre-sized
+        # and the exchange is ONE ncclBroadcast, timed with CUDA events on the stream it runs on.
+        d_db = torch.from_numpy(db).cuda() if rank == 0 else torch.empty(db.shape, dtype=torch.uint8, device="cuda")
+        warm = torch.zeros(1 << 20, dtype=torch.uint8, device="cuda")
+        for _ in range(3):
+            dist.broadcast(warm, src=0)                                    # warm the communicator and its channels
         torch.cuda.synchronize()
         barrier()
-        t0 = time.perf_counter()
-        _, d_db = pkg.sharding.replicate(d_src, 0)
+        b0, b1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        b0.record()
+        dist.broadcast(d_db, src=0)
+        b1.record()
         torch.cuda.synchronize()
-        replicate_ms = max_over_ranks(time.perf_counter() - t0) * 1e3
+        replicate_ms = max_over_ranks(float(b0.elapsed_time(b1)))
         if rank != 0:
             db = d_db.cpu().numpy()
+        del warm
     n, K, W = args.pairs_per_step, args.steps, args.warmup
     per_pair = float(args.desc) * args.desc
     n_sm = torch.cuda.get_device_properties(local_rank).multi_processor_count
@@ -387,6 +401,22 @@ def run_ours(args, rank, local_rank, world):
     # the two API forms ran the same last step: their per-pair match counts must agree
     assert np.array_equal(np.diff(o_off.astype(np.int64)), dev_counts_last), "host and device API forms disagree"
     checksum = int(sum_over_ranks(float(dev_counts_last.sum())))
+    # ... and a random sample of the last timed step's pairs against the CPU oracle (the checker, after the clock):
+    # the full (query, train) lists, not just the counts
+    parity_sample = None
+    if rank == 0:
+        from oracle import cpu_oracle
+        last = step_pairs(pairs, W + K - 1, n)
+        pick = np.random.default_rng(1234).choice(n, min(96, n), replace=False)
+        same = True
+        frames3 = db.reshape(args.frames, -1, 32)
+        for p_ in pick:
+            oq, ot = cpu_oracle.match_descriptors(frames3[last[p_, 0]], frames3[last[p_, 1]], MAX_DIST, RATIO)
+            a, b = int(o_off[p_]), int(o_off[p_ + 1])
+            same = same and np.array_equal(o_q[a:b], oq) and np.array_equal(o_t[a:b], ot)
+        parity_sample = {"pairs": int(len(pick)), "identical": bool(same),
+                         "against": "oracle/slam_oracle.cpp orc_match_descriptors (pinned on cv2 BFMatcher goldens), the "
+                                    "(query, train) lists of randomly chosen pairs of the last timed step"}
     # ---- the same steps against a RESIDENT key-frame database (slamgpu_kfdb_*: every key frame uploaded once, when
     # it is appended, as LoopDetector keeps them; a step then sends its pair list only) ----
     KFDB = 1
@@ -426,6 +456,8 @@ def run_ours(args, rank, local_rank, world):
     for _ in range(50):
         query5()
     loop_query_us = (time.perf_counter() - t0) / 50 * 1e6
+    whole_job = c5_whole_job(args, ctx, pkg, lib, KFDB, rank, world, barrier, max_over_ranks, sum_over_ranks,
+                             o_off, o_q, o_t, cap, n)
     ctx.kfdb_release(KFDB)
     e2e_resident = {"value": world * n * K * per_pair / t_res / 1e9, "unit": UNIT, "h2d_bytes_per_step": 8 * n,
                     "d2h_bytes_per_step": d2h_res // K, "ms_per_step": t_res / K * 1e3,
@@ -492,21 +524,23 @@ def run_ours(args, rank, local_rank, world):
         "ms_per_step": ms_dev / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "u8" if os.environ.get("SLAMGPU_BF_ENGINE") == "int" else "e2m1 (fp4 products of +-1, exact fp32 accumulation)",
         "data": "synthetic",
-        "config": {"workload": workload_name(args),
-                   "pairs_per_step_per_gpu": n, "comparisons_per_step": world * n * per_pair,
-                   "sharding": f"frame pairs block-cyclic over {world} rank(s), database replicated, no collective",
-                   "l2": f"database {db.nbytes / 2**20:.0f} MiB (>= 126 MB L2), different pairs every step"},
+        "config": config_of(args),
+        "step": {"pairs_per_step": n, "pairs_per_step_per_gpu": n, "comparisons_per_step": world * n * per_pair,
+                 "sharding": f"frame pairs block-cyclic over {world} rank(s), database replicated, no collective",
+                 "l2": f"database {db.nbytes / 2**20:.0f} MiB (>= 126 MB L2), different pairs every step"},
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d_per_step),
                 "d2h_bytes_per_step": int(d2h // K), "ms_per_step": t_e2e / K * 1e3,
                 "api": "slamgpu_match_descriptors_batch (host buffers; descriptors re-uploaded every step)"},
         "e2e_resident_database": e2e_resident,
         "gpu_launches": int(gpu_launches), "roofline": roofline, "clocks": clocks,
-        "matches_last_step_all_ranks": checksum,
+        "matches_last_step_all_ranks": checksum, "parity_sample": parity_sample,
     }
     line["c4_local_window_batch"] = c4_line
+    line["c5_whole_job_strong"] = whole_job
     if replicate_ms is not None:
-        line["replicate"] = {"what": "key-frame database resident on GPU 0 -> all ranks, one NCCL broadcast of the device "
-                                     "tensor (shape exchange included; host clock, max over ranks; outside the timed region)", "bytes": int(db.nbytes), "ms": replicate_ms,
+        line["replicate"] = {"what": "key-frame database resident on GPU 0 -> all ranks, one pre-sized ncclBroadcast of the "
+                                     "device tensor (CUDA events on the collective's stream, max over ranks; outside the "
+                                     "timed region)", "bytes": int(db.nbytes), "ms": replicate_ms,
                              "gb_s": db.nbytes / (replicate_ms * 1e-3) / 1e9}
     if world == 1:
         line["cpu_baseline"] = cpu_baseline(args, db)
@@ -515,6 +549,39 @@ def run_ours(args, rank, local_rank, world):
     print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
+
+
+def c5_whole_job(args, ctx, pkg, lib, kfdb, rank, world, barrier, max_over_ranks, sum_over_ranks, o_off, o_q, o_t, cap, n):
+    """BASELINE configs[4] as ONE job, strong-scaled: every ordered pair (query > candidate) of the key-frame database
+    -- 499,500 pairs = 7.99e12 comparisons at the full size -- sharded block-cyclically over the ranks, against the
+    resident database, match lists returned to pinned host arrays.  Host clock between barriers, max over ranks; the
+    total match count is a checksum that must not depend on the number of ranks or on the slicing."""
+    import ctypes as C
+    i32p = C.POINTER(C.c_int32)
+    all_p = pkg.sharding.all_pairs(args.frames)
+    mine = pkg.sharding.shard_pairs(all_p, rank, world, block=64)
+    total = C.c_int64(0)
+    off = np.zeros(n + 1, np.int32)
+    times, matches = [], 0
+    for rep in range(2):                            # the second pass is the one reported (first: warm allocations)
+        barrier()
+        t0 = time.perf_counter()
+        matches = 0
+        for s0 in range(0, len(mine), n):
+            chunk = np.ascontiguousarray(mine[s0:s0 + n])
+            ctx._check(lib.slamgpu_kfdb_match_pairs(ctx._h, kfdb, chunk.ctypes.data_as(i32p), len(chunk), MAX_DIST, RATIO,
+                                                    off.ctypes.data_as(i32p), o_q.ctypes.data_as(i32p),
+                                                    o_t.ctypes.data_as(i32p), cap, C.byref(total)))
+            matches += int(total.value)
+        times.append(max_over_ranks(time.perf_counter() - t0))
+    secs = times[-1]
+    cmp_total = float(len(all_p)) * args.desc * args.desc
+    return {"pairs": int(len(all_p)), "pairs_this_rank": int(len(mine)), "seconds": secs, "gcmp_s": cmp_total / secs / 1e9,
+            "matches_total": int(sum_over_ranks(float(matches))), "scaling": "strong",
+            "api": "slamgpu_kfdb_match_pairs in calls of %d pairs (resident database; pair lists up, match lists down "
+                   "into pinned arrays)" % n,
+            "sharding": f"pair list block-cyclic (blocks of 64) over {world} rank(s), no collective",
+            "clock": "host wall between barriers, max over ranks"}
 
 
 def c4_sharded(ctx, pkg, rank, world, barrier, max_over_ranks, sum_over_ranks):
@@ -690,9 +757,78 @@ def also_measurements(ctx, pkg, torch, stream, n_sm, peaks):
     import bench_c3
     bench_c3.run_sequence(ctx, pkg, 10, 8000, 1000, 3, 0)
     out["c3_tracking_sequence_200_frames"] = bench_c3.run_sequence(ctx, pkg, 200, 8000, 1000, 3, 3, c3_cpu_arm)
+    out["k7b_hit_density_sweep"] = hit_density_sweep(ctx, pkg, torch, stream, peaks)
+    out["adapter_track_frame"] = adapter_track_frame(pkg)
     out["n4_bag_of_words"] = bow_measurements(ctx, pkg, torch, stream, peaks)
     out["n3_pnp_scoring"] = pnp_measurements(ctx, pkg, torch, stream)
     return out
+
+
+def hit_density_sweep(ctx, pkg, torch, stream, peaks):
+    """The FP4 filtered scan (K7b) decodes accumulators only where a threshold bit is set, so its speed depends on how
+    many (query, train) rows fall within the distance cut.  64 key frames x 4000 descriptors, all 2016 ordered pairs
+    per launch, device-resident; the share of descriptors drawn from the common landmark pool sets the hit density."""
+    out = []
+    frames, desc = 64, 4000
+    pairs = pkg.sharding.all_pairs(frames)
+    off = (np.arange(frames + 1, dtype=np.int64) * desc).astype(np.int32)
+    d_off, d_pairs = torch.from_numpy(off).cuda(), torch.from_numpy(pairs).cuda()
+    d_out = torch.empty((len(pairs), desc), dtype=torch.int32, device="cuda")
+    d_cnt = torch.empty(len(pairs), dtype=torch.int32, device="cuda")
+    for shared in (0.0, 0.03, 0.1, 0.3, 0.55, 1.0):
+        db = pkg.synthetic.keyframe_db_fast(frames, desc, 77, shared)
+        d_db = torch.from_numpy(db.reshape(-1, 32)).cuda()
+        run = lambda: ctx.match_descriptors_batch_dev(d_db.data_ptr(), d_off.data_ptr(), frames, d_pairs.data_ptr(),  # noqa: E731
+                                                      len(pairs), desc, MAX_DIST, RATIO, d_out.data_ptr(), d_cnt.data_ptr())
+        for _ in range(3):
+            run()
+        ctx.sync()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record(stream)
+        for _ in range(10):
+            run()
+        b.record(stream)
+        torch.cuda.synchronize()
+        ms = a.elapsed_time(b) / 10
+        g = len(pairs) * float(desc) * desc / (ms * 1e-3) / 1e9
+        out.append({"shared_descriptor_share": shared, "query_rows_matched_share": float(d_cnt.sum().item()) / (len(pairs) * desc),
+                    "ms_per_launch_chain": ms, "gcmp_s": g, "tensor_frac_of_4x_bf16_burst": g * 512e9 / 1e12 / (4 * peaks["bf16_tflops"])})
+    return out
+
+
+def adapter_track_frame(pkg):
+    """One tracked frame THROUGH THE C++ ADAPTER (racing-slam_b200/adapter/MapMatcherGpu, compiled against the mock of
+    the reference's data model): MapMatcherGpu::track on a 200k-point map with a mutation mix (a key-frame insertion
+    every 5th frame: new points, new observations, culled points, bundle-adjusted positions and poses), wall clock,
+    the resident mirror (deltas) against per-call uploads of the whole map; beside it the oracle's two projection calls
+    on a scene of the same size (1 core, like the reference)."""
+    from oracle import cpu_oracle
+    driver = os.path.join(ROOT, "tests", "adapter_mock", "adapter_driver")
+    out_path = os.path.join(ROOT, "gpurun_out", "adapter_bench.json")
+    os.makedirs(os.path.dirname(out_path), exist_ok=True)
+    if not os.path.exists(driver):
+        return {"unavailable": "tests/adapter_mock/adapter_driver is not built (__graft_entry__.build() makes it)"}
+    r = subprocess.run([driver, "--bench", "200000", "8000", "60", out_path], capture_output=True, text=True)
+    if r.returncode != 0:
+        return {"unavailable": f"adapter driver failed: {r.stderr[-300:]}"}
+    with open(out_path) as f:
+        res = json.load(f)
+    syn = pkg.synthetic
+    cam = syn.HD1080
+    sc = syn.projection_scene(200000, 8000, 3, cam=cam)
+    oprm = cpu_oracle.ProjParams(cam["fx"], cam["fy"], cam["cx"], cam["cy"], cam["width"], cam["height"], 20.0, MAX_DIST,
+                                 0.5, 2.0, 1.25, 0)
+    perm = cpu_oracle.kd_build(sc.kp_xy)
+    in_kf = np.zeros(200000, np.uint8)
+    in_kf[::66] = 1
+    t0 = time.perf_counter()
+    for skip in ((1 - in_kf).astype(np.uint8), np.zeros(200000, np.uint8)):
+        cpu_oracle.match_projection(sc.kp_xy, sc.kp_desc, perm, sc.kp_matched, sc.pos, sc.normal, sc.range, sc.obs_offset,
+                                    sc.obs_desc, skip, None, sc.pose, oprm, want_stats=False)
+    res["oracle_projection_pair_ms_1_core"] = (time.perf_counter() - t0) * 1e3
+    res["note"] = ("track_ms_* exclude the add_map_match loops, which are the reference's own host code "
+                   "(O(matches x keypoints), add_map_match_loops_ms) whichever matcher produced the lists")
+    return res
 
 
 def pnp_measurements(ctx, pkg, torch, stream):

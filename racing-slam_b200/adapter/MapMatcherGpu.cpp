@@ -2,6 +2,7 @@
 #include "MapMatcherGpu.h"
 
 #include <algorithm>
+#include <chrono>
 #include <cmath>
 #include <cstdint>
 #include <cstring>
@@ -389,12 +390,16 @@ MapMatcherGpu::track(Frame& frame, Map& map, KeyFrame& last_key_frame) const
             result.second.push_back(MapPointMatch{*by_index[static_cast<size_t>(map_point[i])], static_cast<size_t>(i)});
         }
     }
+    // The reference's own bookkeeping, unchanged: Frame::add_map_match sweeps all keypoints per match
+    // (src/Frame.cpp:90-98), so this is O(matches x keypoints) host work whichever matcher produced the lists.
+    const auto t0 = std::chrono::steady_clock::now();
     for (const auto& match : result.first) {                    // src/Tracker.cpp:235-237
         frame.add_map_match(match);
     }
     for (const auto& match : result.second) {                   // :244-246
         frame.add_map_match(match);
     }
+    m_stats.last_apply_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
     return result;
 }
 

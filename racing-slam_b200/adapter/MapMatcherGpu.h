@@ -91,6 +91,7 @@ class MapMatcherGpu : public MapChangeListener {
     struct MirrorStats {
         size_t syncs = 0, appended = 0, removed = 0, observation_updates = 0, position_updates = 0, observer_updates = 0,
                compactions = 0, full_uploads = 0, legacy_uploads = 0;
+        double last_apply_ms = 0.0;   // host time of the last track()'s add_map_match loops (the reference's own code)
     };
     const MirrorStats& mirror_stats() const { return m_stats; }
 

@@ -239,6 +239,19 @@ template <class F> int for_frame_runs(int n_frames, const std::vector<int>* used
 // Pairs are processed in slices so that the partial-key scratch stays around L2 size.
 constexpr size_t kBatchScratchBytes = size_t(256) << 20;
 
+// Pairs of the next slice.  The host-buffer forms bring a slice's match lists back while the later slices are
+// scanned, so only the LAST slice's copy is exposed: slices shrink geometrically toward the end of the call
+// (each takes half of what is left, down to one wave of CTA pairs), which leaves a tail copy of a few hundred
+// pairs instead of a full slice -- with eight ranks finishing a step at the same moment the full-size tail
+// copies collided on the host.
+int next_slice(const slamgpu_ctx* ctx, int remaining, int slice_pairs, bool taper)
+{
+    if (!taper || remaining > 2 * slice_pairs) return std::min(slice_pairs, remaining);
+    const int floor_pairs = std::max(ctx->n_sm * 2, 64);
+    if (remaining <= floor_pairs) return remaining;
+    return std::min(slice_pairs, std::max((remaining + 1) / 2, floor_pairs));
+}
+
 int batch_core(slamgpu_ctx* ctx, const uint8_t* d_desc, const int32_t* d_frame_offset, int n_frames,
                const int32_t* d_pairs, int n_pairs, int max_rows, float max_dist, float ratio, int32_t* d_out_train, int32_t* d_out_count,
                // optional ordered compaction (host-buffer form): per-slice out_train is then a scratch
@@ -289,8 +302,8 @@ int batch_core(slamgpu_ctx* ctx, const uint8_t* d_desc, const int32_t* d_frame_o
     Carver ws(ctx->d_ws.ptr);
     uint2* keys = ws.take<uint2>(per_pair * std::min(n_pairs, slice_pairs));
     if (d_offset) SG_CUDA(cudaMemsetAsync(d_offset, 0, sizeof(int32_t), ctx->stream));
-    for (int p0 = 0; p0 < n_pairs; p0 += slice_pairs) {
-        const int np = std::min(slice_pairs, n_pairs - p0);
+    for (int p0 = 0, np = 0; p0 < n_pairs; p0 += np) {
+        np = next_slice(ctx, n_pairs - p0, slice_pairs, d_offset != nullptr);
         const int32_t* pairs = d_pairs + 2 * static_cast<size_t>(p0);
         int32_t* out_train = d_offset ? d_out_train : d_out_train + static_cast<size_t>(p0) * max_rows;
         if (tc) {
@@ -437,7 +450,8 @@ int batch_host(slamgpu_ctx* ctx, const uint8_t* desc, const uint8_t* d_desc_res,
     // piece into the caller's arrays -- all while the GPU scans the later slices.  Pinned caller arrays
     // (slamgpu_host_alloc) receive the copies directly.
     if (ctx->copy_stream == nullptr) SG_CUDA(cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking));
-    const int n_slices = (n_pairs + slice - 1) / slice;
+    int n_slices = 0;
+    for (int left = n_pairs; left > 0; ++n_slices) left -= next_slice(ctx, left, slice, true);
     while (ctx->slice_events.size() < 3 * static_cast<size_t>(n_slices)) {
         cudaEvent_t e = nullptr;
         SG_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
@@ -451,9 +465,11 @@ int batch_host(slamgpu_ctx* ctx, const uint8_t* desc, const uint8_t* d_desc_res,
     // the uploads above may have been staged through the same pinned block: the downloads must not start
     // before they have been consumed (stream order covers it: slice 0 runs after the uploads)
     int slice_no = 0;
+    std::vector<std::pair<int, int>> slices;      // (first pair, pair count) of every slice queued
     const std::function<int(int, int)> after_slice = [&](int p0, int np) -> int {
         cudaEvent_t done = ctx->slice_events[3 * slice_no], off_ready = ctx->slice_events[3 * slice_no + 1];
         ++slice_no;
+        slices.emplace_back(p0, np);
         SG_CUDA(cudaEventRecord(done, ctx->stream));
         SG_CUDA(cudaStreamWaitEvent(ctx->copy_stream, done, 0));
         SG_CUDA(cudaMemcpyAsync(h_offset + p0 + 1, d_offset + p0 + 1, sizeof(int32_t) * np, cudaMemcpyDeviceToHost,
@@ -489,7 +505,7 @@ int batch_host(slamgpu_ctx* ctx, const uint8_t* desc, const uint8_t* d_desc_res,
         return SLAMGPU_OK;
     };
     for (int s = 0; s < slice_no; ++s) {
-        const int p0 = s * slice, np = std::min(slice, n_pairs - p0);
+        const int p0 = slices[s].first, np = slices[s].second;
         SG_CUDA(cudaEventSynchronize(ctx->slice_events[3 * s + 1]));
         const int64_t end = h_offset[p0 + np];
         // offsets are int32 on the device; one slice adds < 2^31 entries (slice_for), so a wrapped total shows up

@@ -114,3 +114,13 @@ def test_ransac_select_is_host_arithmetic_and_equals_the_oracle(pkg, oracle):
         assert pkg.binding.ransac_select(cnt, n_pts, mp, conf, iters) == oracle.ransac_select(cnt, n_pts, mp, conf, iters), i
     assert pkg.binding.ransac_select([], 10) == (-1, 0)
     assert pkg.binding.ransac_select([5, 6], 0) == (-1, 0)
+
+
+def test_release_library_has_no_debug_variant_switch(pkg):
+    """SLAMGPU_TC_VARIANT (timing experiments that skip MMAs / TMEM reads / the rare path) exists only in
+    -DSLAMGPU_DEBUG_VARIANTS builds: the release library neither reads the variable nor contains the switches."""
+    blob = open(pkg.binding.LIB_PATH, "rb").read()
+    assert b"SLAMGPU_TC_VARIANT" not in blob
+    assert b"SLAMGPU_BF_ENGINE" in blob           # the documented, result-preserving switches are still there
+    src = open(os.path.join(ROOT, "racing-slam_b200", "csrc", "Makefile")).read()
+    assert "SLAMGPU_DEBUG_VARIANTS" not in src

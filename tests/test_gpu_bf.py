@@ -144,7 +144,7 @@ def test_c5_full_size_database_properties(ctx, oracle, pkg):
     for k, (fq, ft) in enumerate(pairs):
         sq, st = got[(int(fq), int(ft))]
         assert np.array_equal(sq, ql[o[k]:o[k + 1]]) and np.array_equal(st, tl[o[k]:o[k + 1]]), k
-    for k in rng.choice(len(pairs), 6, replace=False):
+    for k in rng.choice(len(pairs), 256, replace=False):     # the OpenMP oracle does a few hundred pairs a second
         oq, ot = oracle.match_descriptors(db[pairs[k, 0]], db[pairs[k, 1]], 64.0, 0.75)
         assert np.array_equal(ql[o[k]:o[k + 1]], oq) and np.array_equal(tl[o[k]:o[k + 1]], ot), k
 
@@ -300,3 +300,121 @@ def test_errors_are_loud(ctx, pkg):
 def test_popc_microbenchmark_runs(ctx):
     rate, n_sm, mhz = ctx.bench_popc()
     assert n_sm >= 100 and rate > 1e12 and 500 < mhz < 2500
+
+
+@pytest.mark.parametrize("copies", [0.0, 0.001, 0.01, 0.08, 0.3, 1.0])
+def test_fp4_engine_tie_heavy_4000x4000_at_every_hit_density(oracle, pkg, monkeypatch, copies):
+    """The FP4 filtered scan decodes accumulators only where a threshold bit is set: a 4000 x 4000 pair forced onto
+    the tensor-core engine with the share of query rows that have EXACT copies in the train set swept from none to
+    all (every copy duplicated, so the kNN is full of ties at distance 0 and the ratio test sees d0 = d1 = 0), the
+    rest drawn from a 24-row pool (ties at every distance).  Bit-exact against the oracle at every density."""
+    monkeypatch.setenv("SLAMGPU_BF_ENGINE", "tc")
+    rng = np.random.default_rng(int(copies * 1000) + 3)
+    q, t = pkg.synthetic.bf_tie_heavy(4000, 4000, 19)
+    q, t = q.copy(), t.copy()
+    uni = rng.integers(0, 256, (4000, 32), dtype=np.uint8)         # uniform rows: no accidental matches
+    half = rng.random(4000) < 0.5
+    q[half] = uni[half]
+    n = int(copies * 4000)
+    if n:
+        rows = rng.choice(4000, n, replace=False)
+        dst = rng.choice(4000, n, replace=False)
+        t[dst] = q[rows]                                           # exact copies ...
+        t[rng.choice(4000, n // 2, replace=False)] = q[rows[:n // 2]]   # ... some of them twice: d0 = d1 = 0
+    with pkg.Context(0) as c:
+        mq, mt = c.match_descriptors(q, t, 64.0, 0.75)
+        oq, ot = oracle.match_descriptors(q, t, 64.0, 0.75)
+        assert np.array_equal(mq, oq) and np.array_equal(mt, ot)
+        ft, fq = c.match_features(t, q, 64.0)
+        o_t, o_q = oracle.match_features(t, q, 64.0)
+        assert np.array_equal(ft, o_t) and np.array_equal(fq, o_q)
+        for ratio in (0.5, 1.0):                                   # d0 > ratio * d1 with d0 = d1 = 0 keeps the row
+            mq, mt = c.match_descriptors(q, t, 64.0, ratio)
+            oq, ot = oracle.match_descriptors(q, t, 64.0, ratio)
+            assert np.array_equal(mq, oq) and np.array_equal(mt, ot)
+    if copies >= 0.08:
+        assert len(oq) > 100
+
+
+def test_two_contexts_on_two_devices_in_one_process(oracle, pkg):
+    """The opt-in to > 48 KB of dynamic shared memory is a per-device function attribute: a second context on
+    another GPU must set it for itself (round 1 kept one process-wide flag).  Skipped on a one-GPU box."""
+    if pkg.binding.device_count() < 2:
+        pytest.skip("needs two GPUs in one process")
+    q, t = pkg.synthetic.bf_correlated(4000, 4000, 5)
+    oq, ot = oracle.match_descriptors(q, t, 64.0, 0.75)
+    oi, od = oracle.knn2(q, t)
+    with pkg.Context(0) as c0, pkg.Context(1) as c1:
+        for c in (c0, c1, c0):
+            mq, mt = c.match_descriptors(q, t, 64.0, 0.75)          # FP4 tensor-core scan (164 KB of shared memory)
+            assert np.array_equal(mq, oq) and np.array_equal(mt, ot)
+            idx, dist = c.knn2(q, t)                                # int8 tensor-core scan
+            assert np.array_equal(idx, oi) and np.array_equal(dist, od)
+
+
+def test_two_contexts_on_one_device(oracle, pkg):
+    """Two contexts in one process (what the reference's three MapMatcher owners would hold), used alternately."""
+    q, t = pkg.synthetic.bf_correlated(4000, 4000, 6)
+    oq, ot = oracle.match_descriptors(q, t, 64.0, 0.75)
+    with pkg.Context(0) as c0, pkg.Context(0) as c1:
+        for c in (c0, c1, c0, c1):
+            mq, mt = c.match_descriptors(q, t, 64.0, 0.75)
+            assert np.array_equal(mq, oq) and np.array_equal(mt, ot)
+
+
+@pytest.mark.parametrize("engine", ["int", "tc"])
+def test_sizes_at_and_over_the_train_limit(pkg, monkeypatch, engine):
+    """SLAMGPU_MAX_TRAIN rows (4 Mi: the 22 index bits of the packed key) is accepted -- the last train row wins
+    when it is the only close one -- and one row more is refused."""
+    monkeypatch.setenv("SLAMGPU_BF_ENGINE", engine)
+    n = pkg.binding.MAX_TRAIN
+    rng = np.random.default_rng(4)
+    t = rng.integers(0, 256, (n, 32), dtype=np.uint8)
+    q = t[[n - 1, 0, n // 2, n - 1]].copy()
+    q[3, 0] ^= 1                                                   # distance 1 from the last row
+    with pkg.Context(0) as c:
+        idx, dist = c.knn2(q, t)
+        assert idx[:, 0].tolist() == [n - 1, 0, n // 2, n - 1] and dist[:, 0].tolist() == [0, 0, 0, 1]
+        assert (dist[:, 1] > 60).all() and (idx[:, 1] >= 0).all() and (idx[:, 1] < n).all()
+        with pytest.raises(pkg.SlamGpuError) as e:
+            c.knn2(q, np.concatenate([t, t[:1]]))
+        assert e.value.code == pkg.binding.ERR_INVALID
+
+
+@pytest.mark.parametrize("nq,nt", [(4001, 3999), (2561, 4321), (4097, 513)])
+def test_padding_rows_of_the_expanded_copy_are_never_matched(oracle, pkg, monkeypatch, nq, nt):
+    """The tensor-core scans read whole tiles from the expanded copy: rows between a set's end and its pitch must
+    behave as 'no row' whatever the scratch held before.  The scratch is poisoned with descriptors that would match
+    (a larger call with exact copies) and then reused by ragged-size calls."""
+    monkeypatch.setenv("SLAMGPU_BF_ENGINE", "tc")
+    with pkg.Context(0) as c:
+        big = np.random.default_rng(1).integers(0, 256, (9000, 32), dtype=np.uint8)
+        c.match_descriptors(big, big, 64.0, 0.75)                  # leaves exact copies of `big` all over the scratch
+        c.knn2(big, big)
+        q = big[:nq].copy()
+        t = np.random.default_rng(2).integers(0, 256, (nt, 32), dtype=np.uint8)   # unrelated to the poison
+        t[::97] = q[: len(t[::97])]                                # a few true matches
+        mq, mt = c.match_descriptors(q, t, 64.0, 0.75)
+        oq, ot = oracle.match_descriptors(q, t, 64.0, 0.75)
+        assert np.array_equal(mq, oq) and np.array_equal(mt, ot)
+        idx, dist = c.knn2(q, t)
+        oi, od = oracle.knn2(q, t)
+        assert np.array_equal(idx, oi) and np.array_equal(dist, od)
+        ft, fq = c.match_features(t, q, 64.0)
+        o_t, o_q = oracle.match_features(t, q, 64.0)
+        assert np.array_equal(ft, o_t) and np.array_equal(fq, o_q)
+
+
+def test_debug_variant_variable_is_ignored_by_the_release_library(oracle, pkg, monkeypatch):
+    """Round 1's library skipped the MMAs (bit 2), the TMEM reads (bit 3) or the rare path (bit 5) when
+    SLAMGPU_TC_VARIANT said so; the release build must compute the same matches whatever the variable holds."""
+    q, t = pkg.synthetic.bf_correlated(4000, 4000, 8)
+    oq, ot = oracle.match_descriptors(q, t, 64.0, 0.75)
+    oi, od = oracle.knn2(q, t)
+    for v in ("4", "8", "32", "128", "1"):
+        monkeypatch.setenv("SLAMGPU_TC_VARIANT", v)
+        with pkg.Context(0) as c:
+            mq, mt = c.match_descriptors(q, t, 64.0, 0.75)
+            assert np.array_equal(mq, oq) and np.array_equal(mt, ot), v
+            idx, dist = c.knn2(q, t)
+            assert np.array_equal(idx, oi) and np.array_equal(dist, od), v

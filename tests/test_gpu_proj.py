@@ -175,6 +175,50 @@ def test_batch_over_keyframes_equals_single_calls(ctx, oracle, pkg):
     ctx.points_release(9)
 
 
+@pytest.mark.parametrize("max_dist", [64.0, 257.0])
+def test_c4_full_shape_batch_vs_oracle(ctx, oracle, pkg, max_dist):
+    """BASELINE C4 at its full shape -- 20 key frames x 50,000 map points, frozen snapshot, replace = true, one
+    batched call -- every key frame compared with the oracle (and, sharded by key frame over a world of 2 or 4,
+    the same results frame for frame).  max_dist 64 is the configuration; 257 accepts every candidate, so every
+    point that passes the gates proposes and the per-keypoint arbitration is exercised 20 x 50k times."""
+    syn = pkg.synthetic
+    n_points, n_kf, nkp = 50000, 20, 2000
+    sc = syn.projection_scene(n_points, nkp, 4)
+    rng = np.random.default_rng(4)
+    p = _params(pkg, syn.KITTI, 20.0, max_dist, 1)
+    op_ = _oparams(oracle, p)
+    frames = []
+    for k in range(n_kf):
+        if k % 2 == 0:      # keypoints of their own (as bench.py's C4 leg) / the scene's keypoints under another pose
+            xy, desc = syn.keypoints_integer(nkp, 1241, 376, 700 + k), sc.kp_desc[rng.permutation(nkp)]
+        else:
+            xy, desc = sc.kp_xy, sc.kp_desc
+        pose = sc.pose if k == 1 else syn.pose_colmajor(syn.make_pose(rng))
+        matched = (rng.random(nkp) < 0.2).astype(np.uint8)
+        ctx.frame_upload(300 + k, xy, desc, None, matched)
+        frames.append((xy, desc, pose, matched))
+    ctx.points_upload(30, sc.pos, sc.normal, sc.range, sc.obs_offset, sc.obs_desc)
+    ids = [300 + k for k in range(n_kf)]
+    res = ctx.match_projection_batch(ids, [nkp] * n_kf, 30, np.stack([f[2] for f in frames]), p)
+    total = 0
+    for k, (xy, desc, pose, matched) in enumerate(frames):
+        ref = oracle.match_projection(xy, desc, oracle.kd_build(xy), matched, sc.pos, sc.normal, sc.range, sc.obs_offset,
+                                      sc.obs_desc, None, None, pose, op_, want_stats=False)
+        assert np.array_equal(res[k][0], ref.point) and np.array_equal(res[k][1], ref.dist), k
+        total += int((ref.point >= 0).sum())
+    assert total > (2000 if max_dist > 64 else 100)
+    for world in (2, 4):    # SURVEY 8e: key frames round-robin over the ranks, the point set replicated
+        for r in range(world):
+            mine = pkg.sharding.shard_keyframes(n_kf, r, world)
+            part = ctx.match_projection_batch([ids[k] for k in mine], [nkp] * len(mine), 30,
+                                              np.stack([frames[k][2] for k in mine]), p)
+            for j, k in enumerate(mine):
+                assert np.array_equal(part[j][0], res[k][0]) and np.array_equal(part[j][1], res[k][1])
+    for i in ids:
+        ctx.frame_release(i)
+    ctx.points_release(30)
+
+
 def _build_world(pkg, seed, n_points=1500, nkp=600, n_kf=4):
     """A small reference-shaped world: key frames observing map points, one current frame."""
     m, syn = pkg.matcher, pkg.synthetic
