@@ -248,7 +248,7 @@ int next_slice(const slamgpu_ctx* ctx, int remaining, int slice_pairs, bool tape
 {
     if (!taper || remaining > 2 * slice_pairs) return std::min(slice_pairs, remaining);
     const int floor_pairs = std::max(ctx->n_sm * 2, 64);
-    if (remaining <= floor_pairs) return remaining;
+    if (remaining <= floor_pairs) return std::min(remaining, slice_pairs);
     return std::min(slice_pairs, std::max((remaining + 1) / 2, floor_pairs));
 }
 

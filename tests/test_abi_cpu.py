@@ -124,3 +124,21 @@ def test_release_library_has_no_debug_variant_switch(pkg):
     assert b"SLAMGPU_BF_ENGINE" in blob           # the documented, result-preserving switches are still there
     src = open(os.path.join(ROOT, "racing-slam_b200", "csrc", "Makefile")).read()
     assert "SLAMGPU_DEBUG_VARIANTS" not in src
+
+
+def test_eigen_order_check_tool_builds_and_its_harness_detects_a_wrong_order(tmp_path, pkg):
+    """tools/eigen_order_check.cpp is the pin a maintainer WITH Eigen runs (Eigen is absent here, so the projection
+    path stays 'parity unpinned').  What can be checked here: it compiles against a stand-in of the Eigen API it uses
+    (tests/eigen_shim), reports 0 mismatches when the stand-in evaluates in the derived order, and DOES report
+    mismatches when the stand-in sums left to right -- i.e. the checker can tell the orders apart."""
+    src = os.path.join(ROOT, "tools", "eigen_order_check.cpp")
+    libdir = os.path.dirname(pkg.binding.LIB_PATH)
+    base = ["g++", "-O2", "-std=c++17", "-ffp-contract=off", "-I" + os.path.join(ROOT, "tests", "eigen_shim"),
+            "-I" + os.path.join(ROOT, "include"), src, "-L" + libdir, "-lslamgpu", "-Wl,-rpath," + libdir]
+    good, bad = str(tmp_path / "check_good"), str(tmp_path / "check_bad")
+    assert subprocess.run(base + ["-o", good], capture_output=True, text=True).returncode == 0
+    assert subprocess.run(base + ["-DEIGEN_SHIM_LEFT_TO_RIGHT", "-o", bad], capture_output=True, text=True).returncode == 0
+    r = subprocess.run([good, "20000", "2"], capture_output=True, text=True)
+    assert r.returncode == 0 and r.stdout.count(" 0 mismatches") == 5 and "at u >= 1024 px" in r.stdout, r.stdout
+    r = subprocess.run([bad, "20000", "2"], capture_output=True, text=True)
+    assert r.returncode == 1 and "MISMATCH" in r.stdout and "first project mismatch" in r.stdout, r.stdout
