@@ -13,6 +13,9 @@ import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libslamgpu.so")
+# tools/prof_tc.py only: the timing-experiment build (make -C csrc debug) in place of the product library
+if os.environ.get("SLAMGPU_DEBUG_LIBRARY"):
+    LIB_PATH = os.environ["SLAMGPU_DEBUG_LIBRARY"]
 
 OK, ERR_INVALID, ERR_CUDA, ERR_NOMEM, ERR_NOTFOUND = 0, 1, 2, 3, 4
 MAX_TRAIN = 1 << 22

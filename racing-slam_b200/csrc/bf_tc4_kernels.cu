@@ -19,6 +19,8 @@
 // Layout, warp roles and the barrier protocol are those of the int8 CTA-pair kernel: 2 CTAs share a
 // 256-query x 240-column tile (each loads 128 query rows and 120 + 120 train rows), warp 0 = bulk-copy
 // producer, warp 1 = MMA issue (leader) / completion relay (peer), warps 2..9 = epilogue.
+#include <type_traits>
+
 #include "slamgpu_internal.cuh"
 #include "bf_tc_common.cuh"
 
@@ -27,7 +29,11 @@ namespace slamgpu {
 namespace {
 
 constexpr int kQ4 = 256;                     // query rows per cluster tile (UMMA M of the pair)
+#ifdef SLAMGPU_TC4_N_EXPERIMENT                 // timing experiment (MMA cost against N): results are wrong, debug build only
+constexpr int kN4 = SLAMGPU_TC4_N_EXPERIMENT;
+#else
 constexpr int kN4 = 240;                     // accumulator columns per tile (UMMA N of the pair)
+#endif
 constexpr int kT4 = 2 * kN4;                 // train rows per tile
 constexpr int kRow4 = 128;                   // expanded descriptor: 256 x E2M1 = 128 bytes
 constexpr int kGroup4 = 8 * kRow4;           // 8 rows = 8 core matrices of 128 bytes
@@ -51,8 +57,11 @@ constexpr int kMagicBits = 0x4B400000;
 
 // cute::UMMA::InstrDescriptorBlockScaled: a/b format E2M1 (MXF4Format 1) at [7,10) / [10,13), K-major,
 // N >> 3 at [17,23), scale format UE8M0 (1) at bit 23, M >> 4 at [24,29), scale-factor ids 0, K = 64 (bit 31 = 0)
-constexpr uint32_t kIdesc4 = (1u << 7) | (1u << 10) | (static_cast<uint32_t>(kN4 >> 3) << 17) | (1u << 23) |
-                             (static_cast<uint32_t>(kQ4 >> 4) << 24);
+__host__ __device__ constexpr uint32_t idesc4(int n_cols)
+{
+    return (1u << 7) | (1u << 10) | (static_cast<uint32_t>(n_cols >> 3) << 17) | (1u << 23) |
+           (static_cast<uint32_t>(kQ4 >> 4) << 24);
+}
 
 __device__ __forceinline__ void tc4_mma(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc,
                                         uint32_t accumulate, uint32_t tmem_sfa, uint32_t tmem_sfb)
@@ -90,6 +99,45 @@ __device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&v)[16])
         : "r"(taddr)
         : "memory");
 }
+// 120 consecutive columns in one statement: five tcgen05.ld off ONE address register (as five statements ptxas
+// moved the address into five uniform registers per tile)
+__device__ __forceinline__ void tmem_ld120(uint32_t taddr, uint32_t (&a)[32], uint32_t (&b)[32], uint32_t (&c)[32],
+                                           uint32_t (&d)[16], uint32_t (&e)[8])
+{
+    asm volatile(
+        "{\n\t.reg .b32 t1, t2, t3, t4;\n\t"
+        "add.u32 t1, %120, 32;\n\tadd.u32 t2, %120, 64;\n\tadd.u32 t3, %120, 96;\n\tadd.u32 t4, %120, 112;\n\t"
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%120];\n\t"
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+        "{%32, %33, %34, %35, %36, %37, %38, %39, %40, %41, %42, %43, %44, %45, %46, %47, "
+        "%48, %49, %50, %51, %52, %53, %54, %55, %56, %57, %58, %59, %60, %61, %62, %63}, [t1];\n\t"
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+        "{%64, %65, %66, %67, %68, %69, %70, %71, %72, %73, %74, %75, %76, %77, %78, %79, "
+        "%80, %81, %82, %83, %84, %85, %86, %87, %88, %89, %90, %91, %92, %93, %94, %95}, [t2];\n\t"
+        "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+        "{%96, %97, %98, %99, %100, %101, %102, %103, %104, %105, %106, %107, %108, %109, %110, %111}, [t3];\n\t"
+        "tcgen05.ld.sync.aligned.32x32b.x8.b32 "
+        "{%112, %113, %114, %115, %116, %117, %118, %119}, [t4];\n\t}"
+        : "=r"(a[0]), "=r"(a[1]), "=r"(a[2]), "=r"(a[3]), "=r"(a[4]), "=r"(a[5]), "=r"(a[6]), "=r"(a[7]), "=r"(a[8]),
+          "=r"(a[9]), "=r"(a[10]), "=r"(a[11]), "=r"(a[12]), "=r"(a[13]), "=r"(a[14]), "=r"(a[15]), "=r"(a[16]),
+          "=r"(a[17]), "=r"(a[18]), "=r"(a[19]), "=r"(a[20]), "=r"(a[21]), "=r"(a[22]), "=r"(a[23]), "=r"(a[24]),
+          "=r"(a[25]), "=r"(a[26]), "=r"(a[27]), "=r"(a[28]), "=r"(a[29]), "=r"(a[30]), "=r"(a[31]),
+          "=r"(b[0]), "=r"(b[1]), "=r"(b[2]), "=r"(b[3]), "=r"(b[4]), "=r"(b[5]), "=r"(b[6]), "=r"(b[7]), "=r"(b[8]),
+          "=r"(b[9]), "=r"(b[10]), "=r"(b[11]), "=r"(b[12]), "=r"(b[13]), "=r"(b[14]), "=r"(b[15]), "=r"(b[16]),
+          "=r"(b[17]), "=r"(b[18]), "=r"(b[19]), "=r"(b[20]), "=r"(b[21]), "=r"(b[22]), "=r"(b[23]), "=r"(b[24]),
+          "=r"(b[25]), "=r"(b[26]), "=r"(b[27]), "=r"(b[28]), "=r"(b[29]), "=r"(b[30]), "=r"(b[31]),
+          "=r"(c[0]), "=r"(c[1]), "=r"(c[2]), "=r"(c[3]), "=r"(c[4]), "=r"(c[5]), "=r"(c[6]), "=r"(c[7]), "=r"(c[8]),
+          "=r"(c[9]), "=r"(c[10]), "=r"(c[11]), "=r"(c[12]), "=r"(c[13]), "=r"(c[14]), "=r"(c[15]), "=r"(c[16]),
+          "=r"(c[17]), "=r"(c[18]), "=r"(c[19]), "=r"(c[20]), "=r"(c[21]), "=r"(c[22]), "=r"(c[23]), "=r"(c[24]),
+          "=r"(c[25]), "=r"(c[26]), "=r"(c[27]), "=r"(c[28]), "=r"(c[29]), "=r"(c[30]), "=r"(c[31]),
+          "=r"(d[0]), "=r"(d[1]), "=r"(d[2]), "=r"(d[3]), "=r"(d[4]), "=r"(d[5]), "=r"(d[6]), "=r"(d[7]), "=r"(d[8]),
+          "=r"(d[9]), "=r"(d[10]), "=r"(d[11]), "=r"(d[12]), "=r"(d[13]), "=r"(d[14]), "=r"(d[15]),
+          "=r"(e[0]), "=r"(e[1]), "=r"(e[2]), "=r"(e[3]), "=r"(e[4]), "=r"(e[5]), "=r"(e[6]), "=r"(e[7])
+        : "r"(taddr)
+        : "memory");
+}
 __device__ __forceinline__ void tmem_st8(uint32_t taddr, uint32_t x)
 {
     asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1, %1, %1, %1, %1, %1, %1, %1};" ::"r"(taddr), "r"(x)
@@ -107,13 +155,14 @@ struct Tc4Args {
     int max_rows;
     long long n_units;
     int variant;
+    int narrow_last;               // size the last train tile of a unit to the rows that are left (SLAMGPU_TC4_NARROW=0: A/B)
     int thr_dot;                   // a train row matters iff dot = 256 - 2 * distance >= thr_dot
     int thr4;                      // thr_dot rounded down to a multiple of 4: what the bit tests of the hot path use
     uint2* keys;
 };
 
 struct Unit4 {
-    bool valid;
+    bool valid, narrow_last;
     int pair, split, row0, nq, t_begin, n_btiles, t_end;
     const uint8_t* q;
     const uint8_t* t;
@@ -142,10 +191,20 @@ __device__ __forceinline__ Unit4 decode_unit4(const Tc4Args& a, long long u)
     un.t_end = min(un.t_begin + a.t_per_split, nt);
     un.n_btiles = (un.t_end - un.t_begin + kT4 - 1) / kT4;
     un.valid = un.row0 < nq;
+    un.narrow_last = a.narrow_last != 0;
     return un;
 }
 
-__device__ __forceinline__ int max3i(int a, int b, int c) { return max(max(a, b), c); }
+// Accumulator columns of train tile bt of a unit.  Every tile but the last has kN4 columns = 2 * kN4 train rows.
+// The LAST tile is sized to what is left: rem rows -> ceil(rem / 2) columns rounded up to 16 (the N granularity of
+// cta_group::2), its second rows starting n_cols after the first ones.  The kernel is bound by the TMEM read-out
+// (about 64 B per clock per SM: 2 bytes per comparison), so reading 80 columns instead of 240 for the last 160
+// of 4000 train rows is 7 % of the whole unit's time.
+__device__ __forceinline__ int tile_cols(const Unit4& un, int bt)
+{
+    const int rem = un.t_end - (un.t_begin + bt * kT4);
+    return (rem >= kT4 || !un.narrow_last) ? kN4 : min(kN4, (((rem + 1) >> 1) + 15) & ~15);
+}
 
 // ---- epilogue arithmetic --------------------------------------------------------------------------
 // The constant that the extra MMA adds is  C = 1.5 * 2^23 + 512 - 1025 * T4  (T4 = the dot threshold rounded
@@ -211,15 +270,42 @@ __device__ __forceinline__ uint64_t scan4(const uint32_t (&v)[N], int4* park)
     return hits;
 }
 
+// OR of all N accumulators (N = 8, 16, 32): N / 2 three-input LOP3, chains of 16 independent of each other
+template <int N>
+__device__ __forceinline__ uint32_t or_all(const uint32_t (&v)[N])
+{
+    if constexpr (N == 8) {
+        uint32_t r = or3(v[0], v[1], v[2]);
+        r = or3(r, v[3], v[4]);
+        r = or3(r, v[5], v[6]);
+        return r | v[7];
+    } else {
+        uint32_t acc = 0u;
+#pragma unroll
+        for (int q = 0; q < N / 16; ++q) {
+            const uint32_t* x = &v[16 * q];
+            uint32_t r = or3(x[0], x[1], x[2]);
+            r = or3(r, x[3], x[4]);
+            r = or3(r, x[5], x[6]);
+            r = or3(r, x[7], x[8]);
+            r = or3(r, x[9], x[10]);
+            r = or3(r, x[11], x[12]);
+            r = or3(r, x[13], x[14]);
+            acc = q == 0 ? (r | x[15]) : or3(acc, r, x[15]);
+        }
+        return acc;
+    }
+}
+
 // one accumulator with a hit bit: both dots decoded, those within the exact cut folded as
-// (distance << 22 | train index); t1 = the train row of dot1, dot2 belongs to t1 + 240
-__device__ __forceinline__ void decode4_one(uint32_t u, int t1, int t_end, int thr_dot, int thr4, uint32_t& b0,
+// (distance << 22 | train index); t1 = the train row of dot1, dot2 belongs to t1 + n_cols (240 but for a last tile)
+__device__ __forceinline__ void decode4_one(uint32_t u, int t1, int t_end, int thr_dot, int thr4, int n_cols, uint32_t& b0,
                                             uint32_t& b1)
 {
     const int x = static_cast<int>(u) - kMagicBits;
     const int dot2 = (x >> 10) + thr4;
     const int dot1 = (x & 1023) - 512 + thr4;
-    const int t2 = t1 + kN4;
+    const int t2 = t1 + n_cols;
     const uint32_t k1 = dot1 >= thr_dot && t1 < t_end
                             ? (static_cast<uint32_t>(256 - dot1) >> 1 << kIdxBits) | static_cast<uint32_t>(t1)
                             : kKeyNone;
@@ -234,14 +320,14 @@ __device__ __forceinline__ void decode4_one(uint32_t u, int t1, int t_end, int t
 
 // one iteration per accumulator that hit (usually one): parked value -> keys
 __device__ __forceinline__ void decode4(const int4* park, uint64_t hits, int t1_first, int t_end, int thr_dot, int thr4,
-                                        uint32_t& b0, uint32_t& b1)
+                                        int n_cols, uint32_t& b0, uint32_t& b1)
 {
     const uint32_t* p = reinterpret_cast<const uint32_t*>(park);
 #pragma unroll 1
     while (hits != 0ull) {
         const int j = __ffsll(static_cast<long long>(hits)) - 1;
         hits &= hits - 1ull;
-        decode4_one(p[j], t1_first + j, t_end, thr_dot, thr4, b0, b1);
+        decode4_one(p[j], t1_first + j, t_end, thr_dot, thr4, n_cols, b0, b1);
     }
 }
 
@@ -281,6 +367,10 @@ __device__ __forceinline__ uint32_t e2m1_code2(int v2)      // doubled value 0, 
     return v2 <= 4 ? static_cast<uint32_t>(v2) : v2 == 6 ? 5u : v2 == 8 ? 6u : 7u;
 }
 
+// TEAMS = false: every epilogue warp reads half of the columns (120) of EVERY tile.  TEAMS = true: the eight epilogue
+// warps form two teams of four (one warp per TMEM lane quadrant); team t owns accumulator stage t, i.e. every other
+// tile, and each of its warps reads all 240 columns of its 32 lanes.
+template <bool TEAMS>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTc4Threads, 1) bf_tc4_scan_kernel(const Tc4Args a)
 {
     extern __shared__ __align__(1024) uint8_t smem[];
@@ -304,7 +394,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTc4Threads, 1) bf_t
             mbar_init(PEER_A_FULL(s), 1);
             mbar_init(A_EMPTY(s), 1);
             mbar_init(ACC_FULL(s), 1);
-            mbar_init(ACC_EMPTY(s), 16);
+            mbar_init(ACC_EMPTY(s), TEAMS ? 8 : 16);
         }
         for (uint32_t s = 0; s < kB4Stages; ++s) {
             mbar_init(B_FULL(s), 1);
@@ -373,11 +463,13 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTc4Threads, 1) bf_t
                 for (int bt = 0; bt < un.n_btiles; ++bt) {
                     const uint32_t sb = b_it & (kB4Stages - 1);
                     mbar_wait(B_EMPTY(sb), ((b_it / kB4Stages) & 1u) ^ 1u);
-                    mbar_expect_tx(B_FULL(sb), kB4Bytes);
-                    const uint8_t* ts = un.t + static_cast<long long>(un.t_begin + bt * kT4 + rank * (kN4 / 2)) * kRow4;
+                    const int n_cols = tile_cols(un, bt);
+                    const uint32_t half_bytes = static_cast<uint32_t>(n_cols >> 1) * kRow4;       // this CTA's rows of one K-half
+                    mbar_expect_tx(B_FULL(sb), 2u * half_bytes);
+                    const uint8_t* ts = un.t + static_cast<long long>(un.t_begin + bt * kT4 + rank * (n_cols >> 1)) * kRow4;
                     const uint32_t dst = sbase + kOff4B + sb * kB4Bytes;
-                    bulk_g2s(dst, ts, kB4Half, B_FULL(sb));                                             // rows cb + c
-                    bulk_g2s(dst + kB4Half, ts + static_cast<long long>(kN4) * kRow4, kB4Half, B_FULL(sb));   // rows cb + 240 + c
+                    bulk_g2s(dst, ts, half_bytes, B_FULL(sb));                                              // rows cb + c
+                    bulk_g2s(dst + kB4Half, ts + static_cast<long long>(n_cols) * kRow4, half_bytes, B_FULL(sb));   // rows cb + n_cols + c
                     ++b_it;
                 }
             }
@@ -402,20 +494,21 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTc4Threads, 1) bf_t
                     tc_fence_after();
                     const uint32_t d = tmem_base + sc * kAccStride;
                     const uint32_t a0 = sbase + kOff4A + sa * kA4Bytes, b0 = sbase + kOff4B + sb * kB4Bytes;
+                    const int n_cols = tile_cols(un, bt);
+                    const uint32_t idesc = idesc4(n_cols);
                     if (!SG_TC_VARIANT(a.variant, 4)) {       // timing experiments only: bit 2 skips the MMAs
-                        tc4_mma(d, desc_ax, desc_bx, kIdesc4, 0u, sf_mix, sf_mix);      // D = 1.5 * 2^23 + 512 - 1025 * T4
+                        tc4_mma(d, desc_ax, desc_bx, idesc, 0u, sf_mix, sf_mix);        // D = 1.5 * 2^23 + 512 - 1025 * T4
 #pragma unroll
                         for (int k = 0; k < 4; ++k)     // K = 64 values = 32 bytes = two 16-byte k-chunks per MMA
                             tc4_mma(d, umma_desc(a0 + k * 256, 128u, kGroup4), umma_desc(b0 + k * 256, 128u, kGroup4),
-                                    kIdesc4, 1u, sf_one, sf_one);
-                        // second train row of every column, scaled by 2^10.  A last tile with at most 240 rows
-                        // left has none: its columns keep dot2 = 0, what the zero padding rows would have given
-                        // (4000 rows = 8 tiles + 160 rows: 4 of 81 MMAs less per unit)
-                        if (un.t_begin + bt * kT4 + kN4 < un.t_end || SG_TC_VARIANT(a.variant, 256)) {
+                                    idesc, 1u, sf_one, sf_one);
+                        // second train row of every column, scaled by 2^10.  A last tile whose first rows already
+                        // cover what is left has none: its columns keep dot2 = 0, what zero padding rows would give
+                        if (un.t_begin + bt * kT4 + n_cols < un.t_end || SG_TC_VARIANT(a.variant, 256)) {
 #pragma unroll
                             for (int k = 0; k < 4; ++k)
                                 tc4_mma(d, umma_desc(a0 + k * 256, 128u, kGroup4),
-                                        umma_desc(b0 + kB4Half + k * 256, 128u, kGroup4), kIdesc4, 1u, sf_one, sf_big);
+                                        umma_desc(b0 + kB4Half + k * 256, 128u, kGroup4), idesc, 1u, sf_one, sf_big);
                         }
                     }
                     tc2_commit_mc(B_EMPTY(sb));
@@ -445,118 +538,197 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTc4Threads, 1) bf_t
             }
         }
     } else {
+
+        if constexpr (TEAMS) {
+        // ===== epilogue, two teams: team t = 4 warps (one per TMEM lane quadrant) owns accumulator stage t =====
+        // Measured with the timing build (8192 pairs): MMAs alone 12.2 ms, TMEM reads alone 8.9 ms, but reads +
+        // arithmetic 14.5 ms -- a warp cannot keep a tcgen05.ld in flight under its own arithmetic (ptxas schedules
+        // the OR tree of the chunk that just landed BEFORE the loads of the next one), and with every warp working
+        // on the same tile all of them compute at the same moment while the TMEM read port idles.  With two teams
+        // on alternate tiles one team computes while the other one reads.  Per tile a warp reads its 32 lanes x 240
+        // columns as chunks of 64 / 64 / 64 / 48 into two register buffers.
+        const int quad = warp & 3;
+        const int g = (warp - 2) >> 2;                      // team = accumulator stage = partial-key slot
+        const int row_in_tile = static_cast<int>(rank) * 128 + quad * 32 + lane;
+        const bool skip = SG_TC_VARIANT(a.variant, 8);     // timing experiments only: bit 3 skips the TMEM reads and the fold
+        const uint32_t tbase = tmem_base + (static_cast<uint32_t>(quad * 32) << 16) + static_cast<uint32_t>(g) * kAccStride;
+        uint32_t xa[32], xb[32], ya[32], yb[32], zc[16];
+        int4 park[16];
+        uint32_t b0 = kKeyNone, b1 = kKeyNone;
+        uint32_t c_it = 0;
+        for (long long u = cid; u < a.n_units; u += n_clusters) {
+            const Unit4 un = decode_unit4(a, u);
+            if (!un.valid) continue;
+            const int row = un.row0 + row_in_tile;
+            for (int bt = 0; bt < un.n_btiles; ++bt, ++c_it) {
+                if ((c_it & 1u) != static_cast<uint32_t>(g)) continue;       // the other team's tile
+                const int cb = un.t_begin + bt * kT4;
+                const int t_end = SG_TC_VARIANT(a.variant, 32) ? -1 : un.t_end;
+                const int n_cols = tile_cols(un, bt);
+                mbar_wait(ACC_FULL(g), (c_it >> 1) & 1u);
+                tc_fence_after();
+                if (skip) {
+                } else if (n_cols == kN4) {
+                    tmem_ld32(tbase, xa);
+                    tmem_ld32(tbase + 32, xb);
+                    tmem_wait_ld();
+                    tmem_ld32(tbase + 64, ya);
+                    tmem_ld32(tbase + 96, yb);
+                    tmem_pin(xa);
+                    tmem_pin(xb);
+                    uint64_t m = SG_TC_VARIANT(a.variant, 128) ? 0ull : scan4(xa, park) | (scan4(xb, park + 8) << 32);
+                    if (__builtin_expect(m != 0ull && t_end >= 0, 0)) decode4(park, m, cb, t_end, a.thr_dot, a.thr4, kN4, b0, b1);
+                    tmem_wait_ld();
+                    tmem_ld32(tbase + 128, xa);
+                    tmem_ld32(tbase + 160, xb);
+                    tmem_pin(ya);
+                    tmem_pin(yb);
+                    m = SG_TC_VARIANT(a.variant, 128) ? 0ull : scan4(ya, park) | (scan4(yb, park + 8) << 32);
+                    if (__builtin_expect(m != 0ull && t_end >= 0, 0)) decode4(park, m, cb + 64, t_end, a.thr_dot, a.thr4, kN4, b0, b1);
+                    tmem_wait_ld();
+                    tmem_ld32(tbase + 192, ya);
+                    tmem_ld16(tbase + 224, zc);
+                    tmem_pin(xa);
+                    tmem_pin(xb);
+                    m = SG_TC_VARIANT(a.variant, 128) ? 0ull : scan4(xa, park) | (scan4(xb, park + 8) << 32);
+                    if (__builtin_expect(m != 0ull && t_end >= 0, 0)) decode4(park, m, cb + 128, t_end, a.thr_dot, a.thr4, kN4, b0, b1);
+                    tmem_wait_ld();                 // every TMEM read of this stage is done: hand it back before the last fold
+                    tmem_pin(ya);
+                    tmem_pin(zc);
+                } else {
+                    // a last tile narrower than kN4: all of its columns, in pieces of 32 / 16 / 8
+                    int c = 0;
+                    for (; c + 32 <= n_cols; c += 32) {
+                        tmem_ld32(tbase + c, xa);
+                        tmem_wait_ld();
+                        tmem_pin(xa);
+                        const uint64_t m = scan4(xa, park);
+                        if (__builtin_expect(m != 0ull && t_end >= 0, 0)) decode4(park, m, cb + c, t_end, a.thr_dot, a.thr4, n_cols, b0, b1);
+                    }
+                    if (c + 16 <= n_cols) {
+                        tmem_ld16(tbase + c, zc);
+                        tmem_wait_ld();
+                        tmem_pin(zc);
+                        const uint64_t m = scan4(zc, park);
+                        if (__builtin_expect(m != 0ull && t_end >= 0, 0)) decode4(park, m, cb + c, t_end, a.thr_dot, a.thr4, n_cols, b0, b1);
+                    }
+                }
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) {
+                    if (rank == 0) mbar_arrive(ACC_EMPTY(g));
+                    else mbar_arrive_remote(ACC_EMPTY(g), 0u);
+                }
+                if (!skip && n_cols == kN4) {
+                    const uint64_t m = SG_TC_VARIANT(a.variant, 128) ? 0ull : scan4(ya, park) | (scan4(zc, park + 8) << 32);
+                    if (__builtin_expect(m != 0ull && t_end >= 0, 0)) decode4(park, m, cb + 192, t_end, a.thr_dot, a.thr4, kN4, b0, b1);
+                }
+            }
+            // this team's partial top-2 of the unit (all of it when the unit had no tile for this team)
+            if (row < un.nq)
+                a.keys[((static_cast<size_t>(un.pair) * a.splits + un.split) * 2 + g) * a.max_rows + row] = make_uint2(b0, b1);
+            b0 = kKeyNone;
+            b1 = kKeyNone;
+        }
+        } else {
         // ===== epilogue: 8 warps = 4 TMEM lane quadrants x 2 column halves of 120 =====
-        // Software-pipelined across tiles: a warp's 120 columns are read as chunk A (64) and chunk B (56);
-        // the tcgen05.ld of the next chunk -- of the next tile after chunk B -- is in flight while the current
-        // one is folded, so the TMEM read-out (~940 cycles per tile) and the arithmetic overlap.
+        // Read FIRST, compute AFTER.  What bounds this kernel is the turn-around of an accumulator stage: with two
+        // stages of 240 columns (all of TMEM) the MMAs of tile i + 2 cannot start before tile i has been read out, so
+        // the time from "accumulator full" to "accumulator empty" must stay under the MMA time of one tile (9 MMAs of
+        // ~158 cycles; measured with the timing build: MMAs alone 11.5 ms per 8192 pairs, this kernel 15.3 ms before).
+        // A warp therefore issues the tcgen05.ld of all its 120 columns at once, waits once, hands the stage back and
+        // only then folds the 120 accumulators -- round 1 interleaved two chunks with their arithmetic, which kept
+        // the OR tree of the first chunk (and a second wait) inside the turn-around.
         const int quad = warp & 3;
         const int g = (warp - 2) >> 2;
         const int row_in_tile = static_cast<int>(rank) * 128 + quad * 32 + lane;
         const uint32_t lane_col = (static_cast<uint32_t>(quad * 32) << 16) + static_cast<uint32_t>(g * 120);
         const int c0 = g * 120;
         const bool skip = SG_TC_VARIANT(a.variant, 8);     // timing experiments only: bit 3 skips the TMEM reads and the fold
-
-        // tile stream of this cluster: (unit, train tile) in the order the MMA issuer produces them
-        long long u_cur = cid - n_clusters;
-        Unit4 un_cur;
-        un_cur.valid = false;
-        un_cur.n_btiles = 0;
-        int bt_cur = 0;
-        auto next_tile = [&](long long& u, Unit4& un, int& bt) -> bool {
-            if (un.valid && bt + 1 < un.n_btiles) {
-                ++bt;
-                return true;
-            }
-            for (;;) {
-                u += n_clusters;
-                if (u >= a.n_units) return false;
-                un = decode_unit4(a, u);
-                if (!un.valid) continue;
-                if (un.n_btiles == 0) {          // no train rows: the unit still owns its (empty) key records
-                    const int row = un.row0 + row_in_tile;
-                    if (row < un.nq)
-                        a.keys[((static_cast<size_t>(un.pair) * a.splits + un.split) * 2 + g) * a.max_rows + row] =
-                            make_uint2(kKeyNone, kKeyNone);
-                    continue;
-                }
-                bt = 0;
-                return true;
-            }
-        };
-
         uint32_t va0[32], va1[32], vb0[32], vb1[16], vb2[8];
         int4 park[16];                  // up to 4 parked groups of 16 accumulators (local memory)
-        uint32_t c_it = 0;
         uint32_t b0 = kKeyNone, b1 = kKeyNone;
-        bool have = next_tile(u_cur, un_cur, bt_cur);
-        if (have) {
-            mbar_wait(ACC_FULL(0), 0u);
-            tc_fence_after();
-            if (!skip) {
-                tmem_ld32(tmem_base + lane_col, va0);
-                tmem_ld32(tmem_base + lane_col + 32, va1);
-            }
-        }
-        while (have) {
-            const uint32_t sc = c_it & 1u;
-            const uint32_t taddr = tmem_base + lane_col + sc * kAccStride;
-            const int cb = un_cur.t_begin + bt_cur * kT4;
-            const int t_end = SG_TC_VARIANT(a.variant, 32) ? -1 : un_cur.t_end;     // timing experiments only: bit 5 disables the rare path
-            if (!skip) {
-                tmem_wait_ld();                  // chunk A of this tile has landed
-                tmem_pin(va0);
-                tmem_pin(va1);
-                tmem_ld32(taddr + 64, vb0);      // chunk B in flight while A is folded
-                tmem_ld16(taddr + 96, vb1);
-                tmem_ld8(taddr + 112, vb2);
-                const uint64_t ma = SG_TC_VARIANT(a.variant, 128) ? 0ull   // timing experiments only: bit 7 skips the scan arithmetic
-                                                      : scan4(va0, park) | (scan4(va1, park + 8) << 32);
-                if (__builtin_expect(ma != 0ull && t_end >= 0, 0)) decode4(park, ma, cb + c0, t_end, a.thr_dot, a.thr4, b0, b1);
-                tmem_wait_ld();                  // chunk B has landed: every TMEM read of this stage is done
-                tmem_pin(vb0);
-                tmem_pin(vb1);
-                tmem_pin(vb2);
-            }
-            tc_fence_before();
-            __syncwarp();
-            if (lane == 0) {
-                if (rank == 0) mbar_arrive(ACC_EMPTY(sc));
-                else mbar_arrive_remote(ACC_EMPTY(sc), 0u);
-            }
-            // look ahead: chunk A of the next tile in flight while chunk B of this one is folded
-            long long u_nxt = u_cur;
-            Unit4 un_nxt = un_cur;
-            int bt_nxt = bt_cur;
-            const bool last_of_unit = bt_cur + 1 == un_cur.n_btiles;
-            const bool have_nxt = next_tile(u_nxt, un_nxt, bt_nxt);
-            ++c_it;
-            if (have_nxt) {
-                const uint32_t sn = c_it & 1u;
-                mbar_wait(ACC_FULL(sn), (c_it >> 1) & 1u);
+        uint32_t c_it = 0;
+        // this warp's TMEM address in either stage, kept in registers (opaque to the compiler: recomputed per tile it
+        // sat between "accumulator full" and the first load)
+        uint32_t taddr_s0 = tmem_base + lane_col, taddr_s1 = tmem_base + lane_col + kAccStride;
+        asm volatile("" : "+r"(taddr_s0), "+r"(taddr_s1));
+        for (long long u = cid; u < a.n_units; u += n_clusters) {
+            const Unit4 un = decode_unit4(a, u);
+            if (!un.valid) continue;
+            for (int bt = 0; bt < un.n_btiles; ++bt, ++c_it) {
+                const uint32_t sc = c_it & 1u;
+                const uint32_t taddr = sc ? taddr_s1 : taddr_s0;
+                const int cb = un.t_begin + bt * kT4;
+                const int t_end = SG_TC_VARIANT(a.variant, 32) ? -1 : un.t_end;     // timing experiments only: bit 5 disables the rare path
+                const int n_cols = tile_cols(un, bt);
+                const bool full = n_cols == kN4;
+                mbar_wait(ACC_FULL(sc), (c_it >> 1) & 1u);
                 tc_fence_after();
-                if (!skip) {
-                    tmem_ld32(tmem_base + lane_col + sn * kAccStride, va0);
-                    tmem_ld32(tmem_base + lane_col + sn * kAccStride + 32, va1);
+                if (!skip && full) {
+                    tmem_ld120(taddr, va0, va1, vb0, vb1, vb2);
+                    tmem_wait_ld();
+                    tmem_pin(va0);
+                    tmem_pin(va1);
+                    tmem_pin(vb0);
+                    tmem_pin(vb1);
+                    tmem_pin(vb2);
+                } else if (!skip) {
+                    // a last tile narrower than kN4 (16 .. 224 columns): this warp's half of its columns, in pieces
+                    // of 32 / 16 / 8, folded as they land
+                    const int w = n_cols >> 1;
+                    const uint32_t tcol = tmem_base + (static_cast<uint32_t>(quad * 32) << 16) + sc * kAccStride +
+                                          static_cast<uint32_t>(g * w);
+                    const int t_first = cb + g * w;
+                    int c = 0;
+                    for (; c + 32 <= w; c += 32) {
+                        tmem_ld32(tcol + c, vb0);
+                        tmem_wait_ld();
+                        tmem_pin(vb0);
+                        const uint64_t m = scan4(vb0, park);
+                        if (__builtin_expect(m != 0ull && t_end >= 0, 0)) decode4(park, m, t_first + c, t_end, a.thr_dot, a.thr4, n_cols, b0, b1);
+                    }
+                    if (c + 16 <= w) {
+                        tmem_ld16(tcol + c, vb1);
+                        tmem_wait_ld();
+                        tmem_pin(vb1);
+                        const uint64_t m = scan4(vb1, park);
+                        if (__builtin_expect(m != 0ull && t_end >= 0, 0)) decode4(park, m, t_first + c, t_end, a.thr_dot, a.thr4, n_cols, b0, b1);
+                        c += 16;
+                    }
+                    if (c + 8 <= w) {
+                        tmem_ld8(tcol + c, vb2);
+                        tmem_wait_ld();
+                        tmem_pin(vb2);
+                        const uint64_t m = scan4(vb2, park);
+                        if (__builtin_expect(m != 0ull && t_end >= 0, 0)) decode4(park, m, t_first + c, t_end, a.thr_dot, a.thr4, n_cols, b0, b1);
+                    }
+                }
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) {
+                    if (rank == 0) mbar_arrive(ACC_EMPTY(sc));
+                    else mbar_arrive_remote(ACC_EMPTY(sc), 0u);
+                }
+                if (!skip && full && !SG_TC_VARIANT(a.variant, 128)) {      // timing experiments only: bit 7 skips the scan arithmetic
+                    // hot path: ONE test for the warp's 120 accumulators (60 LOP3 + 2 to combine); the per-group scan
+                    // with its eight branches runs only when some accumulator has a hit bit
+                    const uint32_t any = or3(or3(or_all(va0), or_all(va1), or_all(vb0)), or_all(vb1), or_all(vb2));
+                    if (__builtin_expect((any & kHitBits) != 0u && t_end >= 0, 0)) {
+                        const uint64_t ma = scan4(va0, park) | (scan4(va1, park + 8) << 32);
+                        if (ma != 0ull) decode4(park, ma, cb + c0, t_end, a.thr_dot, a.thr4, kN4, b0, b1);
+                        const uint64_t mb = scan4(vb0, park) | (scan4(vb1, park + 8) << 32) | (scan4(vb2, park + 12) << 48);
+                        if (mb != 0ull) decode4(park, mb, cb + c0 + 64, t_end, a.thr_dot, a.thr4, kN4, b0, b1);
+                    }
                 }
             }
-            if (!skip) {
-                const uint64_t mb = SG_TC_VARIANT(a.variant, 128) ? 0ull
-                                                      : scan4(vb0, park) | (scan4(vb1, park + 8) << 32) | (scan4(vb2, park + 12) << 48);
-                if (__builtin_expect(mb != 0ull && t_end >= 0, 0)) decode4(park, mb, cb + c0 + 64, t_end, a.thr_dot, a.thr4, b0, b1);
-            }
-            if (last_of_unit) {
-                const int row = un_cur.row0 + row_in_tile;
-                if (row < un_cur.nq) {
-                    a.keys[((static_cast<size_t>(un_cur.pair) * a.splits + un_cur.split) * 2 + g) * a.max_rows + row] =
-                        make_uint2(b0, b1);
-                }
-                b0 = kKeyNone;
-                b1 = kKeyNone;
-            }
-            have = have_nxt;
-            u_cur = u_nxt;
-            un_cur = un_nxt;
-            bt_cur = bt_nxt;
+            // this warp's partial top-2 of the unit (no keys at all when the unit had no train rows)
+            const int row = un.row0 + row_in_tile;
+            if (row < un.nq)
+                a.keys[((static_cast<size_t>(un.pair) * a.splits + un.split) * 2 + g) * a.max_rows + row] = make_uint2(b0, b1);
+            b0 = kKeyNone;
+            b1 = kKeyNone;
+        }
         }
     }
 
@@ -679,7 +851,8 @@ int bf_tc4_launch_scan(slamgpu_ctx* ctx, const BfPlan& plan, const uint8_t* d_ex
 {
     // per-DEVICE function attribute: one flag per context (see bf_tc_launch_scan)
     if (!ctx->tc4_attr_set) {
-        SG_CUDA(cudaFuncSetAttribute(bf_tc4_scan_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kTc4SmemBytes));
+        SG_CUDA(cudaFuncSetAttribute(bf_tc4_scan_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kTc4SmemBytes));
+        SG_CUDA(cudaFuncSetAttribute(bf_tc4_scan_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kTc4SmemBytes));
         ctx->tc4_attr_set = true;
     }
     SG_CHECK(d_cut >= 1 && d_cut <= 250, "the fp4 scan needs a distance cut of at most 250");
@@ -697,13 +870,15 @@ int bf_tc4_launch_scan(slamgpu_ctx* ctx, const BfPlan& plan, const uint8_t* d_ex
     a.max_rows = max_rows;
     a.n_units = static_cast<long long>(plan.tiles) * plan.splits * n_pairs;
     a.variant = ctx->tc_variant;
+    a.narrow_last = ctx->tc4_narrow_last ? 1 : 0;
     a.thr_dot = 256 - 2 * (d_cut - 1);                      // -242 .. 256
     a.thr4 = (a.thr_dot + 256) / 4 * 4 - 256;               // rounded DOWN to a multiple of 4: -244 .. 256
     a.keys = d_keys;
     if (a.n_units <= 0) return SLAMGPU_OK;
     const unsigned grid = 2u * static_cast<unsigned>(min(a.n_units, static_cast<long long>(ctx->n_sm / 2)));
     ProfScope prof(ctx, SLAMGPU_KERNEL_BF_SCAN);
-    bf_tc4_scan_kernel<<<grid, kTc4Threads, kTc4SmemBytes, ctx->stream>>>(a);     // __cluster_dims__(2, 1, 1)
+    if (ctx->tc4_teams) bf_tc4_scan_kernel<true><<<grid, kTc4Threads, kTc4SmemBytes, ctx->stream>>>(a);     // __cluster_dims__(2, 1, 1)
+    else bf_tc4_scan_kernel<false><<<grid, kTc4Threads, kTc4SmemBytes, ctx->stream>>>(a);
     ctx->launches++;
     SG_CUDA(cudaGetLastError());
     return SLAMGPU_OK;

@@ -264,6 +264,10 @@ int slamgpu_create(int device, slamgpu_ctx** out)
     }
     const char* engine = std::getenv("SLAMGPU_BF_ENGINE");
     if (engine != nullptr) ctx->bf_engine = std::strcmp(engine, "int") == 0 ? 1 : std::strcmp(engine, "tc") == 0 ? 2 : 0;
+    const char* teams = std::getenv("SLAMGPU_TC4_TEAMS");
+    if (teams != nullptr) ctx->tc4_teams = teams[0] != '0';
+    const char* narrow = std::getenv("SLAMGPU_TC4_NARROW");
+    if (narrow != nullptr) ctx->tc4_narrow_last = narrow[0] != '0';
 #ifdef SLAMGPU_DEBUG_VARIANTS       // timing experiments that can corrupt results: never in the release library
     const char* variant = std::getenv("SLAMGPU_TC_" "VARIANT");
     if (variant != nullptr) ctx->tc_variant = std::atoi(variant);

@@ -184,6 +184,10 @@ struct slamgpu_ctx {
     bool proj_walk = false;   // SLAMGPU_PROJ_WALK=1: use the thread-per-point KD-walk kernel
     int bf_engine = 0;        // SLAMGPU_BF_ENGINE=int|tc overrides the brute-force engine choice (0 = by size, 1 = int, 2 = tc)
     int tc_variant = 0;       // SLAMGPU_TC_VARIANT: debug switches of the tensor-core scans; read only in -DSLAMGPU_DEBUG_VARIANTS builds
+    bool tc4_narrow_last = false;  // SLAMGPU_TC4_NARROW=1: size the last train tile of the FP4 scan to the rows left (same results;
+                                   // measured no faster: an MMA costs the same at N = 80 as at N = 240 and the narrow tile issues 9 instead of 5)
+    bool tc4_teams = false;        // SLAMGPU_TC4_TEAMS=1: the FP4 scan's epilogue warps as two teams on alternate tiles (measured slower than
+                                   // every warp reading its half of every tile first and folding afterwards; same results)
     bool tc_attr_set = false, tc4_attr_set = false;   // dynamic-smem opt-in of the tensor-core scans done on this context's device
     slamgpu::Arena d_exp;     // expanded (int8) descriptors of the tensor-core scan
     std::vector<std::pair<cudaEvent_t, cudaEvent_t>> prof_events[4];   // per SLAMGPU_KERNEL_*
