@@ -434,12 +434,15 @@ def run_ours(args, rank, local_rank, world):
         step_resident(s)
     barrier()
     torch.cuda.synchronize()
+    ctx.trace_read()
     t0 = time.perf_counter()
     d2h_res = 0
     for s in range(K):
         d2h_res += 4 * (n + 1) + 8 * step_resident(W + s)
     torch.cuda.synchronize()
-    t_res = max_over_ranks(time.perf_counter() - t0)
+    t_res_own = time.perf_counter() - t0
+    t_res = max_over_ranks(t_res_own)
+    trace_us, trace_calls = ctx.trace_read()
     barrier()
     assert np.array_equal(np.diff(o_off.astype(np.int64)), dev_counts_last), "resident database form disagrees"
     # one loop-closure query as LoopDetector issues it: the newest key frame against 5 retrieved candidates
@@ -464,6 +467,12 @@ def run_ours(args, rank, local_rank, world):
                     "api": "slamgpu_kfdb_match_pairs (key frames appended once before the clock; pair list up, match "
                            "lists down every step)",
                     "loop_query_5_candidates_us": loop_query_us}
+    if os.environ.get("SLAMGPU_TRACE_BATCH") == "1" and trace_calls:
+        # where the host time of a step goes (rank 0's own clock; SLAMGPU_TRACE_BATCH=1)
+        e2e_resident["host_trace_ms_per_step_rank0"] = {
+            "queueing_the_call": trace_us[0] / trace_calls / 1e3, "waiting_for_slices": trace_us[1] / trace_calls / 1e3,
+            "tail_after_last_slice": trace_us[2] / trace_calls / 1e3, "whole_call": trace_us[3] / trace_calls / 1e3,
+            "python_between_calls": (t_res_own * 1e6 - trace_us[3]) / trace_calls / 1e3}
     # every rank takes part in the sharded C4 batch (collectives inside): before the non-zero ranks leave
     c4_line = c4_sharded(ctx, pkg, rank, world, barrier, max_over_ranks, sum_over_ranks)
 

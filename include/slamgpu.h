@@ -452,6 +452,17 @@ SLAMGPU_API int slamgpu_host_point_stats(const float* xyz, int n_obs, const floa
 #define SLAMGPU_KERNEL_PROJ_MATCH 1
 #define SLAMGPU_KERNEL_VOC_TRANSFORM 2
 #define SLAMGPU_KERNEL_PNP_SCORE 3
+/* A projection call that arrives before the frame's KD-tree has been built (slamgpu_frame_upload builds it on a
+ * host thread) does not wait for it: it runs on the tree-free candidate grid and COUNTS the points whose best
+ * distance is shared by two keypoints -- the only place where the reference's KD visit order matters
+ * (src/KDTree.cpp:52-82, src/MapMatcher.cpp:88).  A zero count makes the results final; otherwise the call waits
+ * for the tree and repeats itself.  calls = speculative calls so far, repeats = how many had to be repeated.
+ * SLAMGPU_KD_SPECULATE=0 switches the speculation off. */
+SLAMGPU_API int slamgpu_speculation_count(slamgpu_ctx* ctx, int64_t* calls, int64_t* repeats);
+/* With SLAMGPU_TRACE_BATCH=1 the host-buffer batch calls (slamgpu_match_descriptors_batch, slamgpu_kfdb_match_pairs)
+ * add up host-clock microseconds per phase: out_us4 = {queueing the call's work, waiting for the slices while their
+ * lists are copied out, the tail after the last slice, the whole call}; the sums reset on read. */
+SLAMGPU_API int slamgpu_trace_read(slamgpu_ctx* ctx, double* out_us4, int64_t* out_calls);
 SLAMGPU_API int slamgpu_profile_enable(slamgpu_ctx* ctx, int on);
 SLAMGPU_API int slamgpu_profile_read(slamgpu_ctx* ctx, int kernel, double* total_ms, int64_t* launches);
 /* POPC-pipe microbenchmark ("confirm with a POPC microbenchmark on the box"):

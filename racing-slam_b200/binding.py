@@ -125,6 +125,8 @@ SIGNATURES = {
     "slamgpu_host_project": (C.c_int, [_f32p, C.POINTER(ProjParams), _f32p, _f32p]),
     "slamgpu_host_camera_center": (C.c_int, [_f32p, _f32p]),
     "slamgpu_host_point_stats": (C.c_int, [_f32p, C.c_int, _f32p, _f32p, _f32p]),
+    "slamgpu_speculation_count": (C.c_int, [_ctx, _i64p, _i64p]),
+    "slamgpu_trace_read": (C.c_int, [_ctx, _f64p, _i64p]),
     "slamgpu_profile_enable": (C.c_int, [_ctx, C.c_int]),
     "slamgpu_profile_read": (C.c_int, [_ctx, C.c_int, C.POINTER(C.c_double), _i64p]),
     "slamgpu_bench_popc": (C.c_int, [_ctx, C.POINTER(C.c_double), C.POINTER(C.c_int), C.POINTER(C.c_double)]),
@@ -281,6 +283,19 @@ class Context:
     @property
     def launches(self) -> int:
         return int(self._lib.slamgpu_launch_count(self._h))
+
+    def speculation_count(self):
+        """(speculative projection calls, of which repeated with the KD-tree because of a tie)"""
+        a, b = C.c_int64(0), C.c_int64(0)
+        self._check(self._lib.slamgpu_speculation_count(self._h, C.byref(a), C.byref(b)))
+        return a.value, b.value
+
+    def trace_read(self):
+        """SLAMGPU_TRACE_BATCH=1: (microseconds [queue, wait, tail, call] summed since the last read, calls)"""
+        us = np.zeros(4, np.float64)
+        n = C.c_int64(0)
+        self._check(self._lib.slamgpu_trace_read(self._h, _p(us, C.c_double), C.byref(n)))
+        return us, n.value
 
     def profile_enable(self, on: bool = True):
         self._check(self._lib.slamgpu_profile_enable(self._h, 1 if on else 0))

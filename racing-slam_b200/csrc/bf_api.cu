@@ -2,6 +2,7 @@
 // Host-buffer forms stage through the context's pinned buffer, copy H2D, run the kernels of
 // bf_kernels.cu on the context's stream, copy D2H and return when the caller's buffers are filled.
 #include <algorithm>
+#include <chrono>
 #include <functional>
 #include <cmath>
 #include <cstring>
@@ -457,6 +458,11 @@ int batch_host(slamgpu_ctx* ctx, const uint8_t* desc, const uint8_t* d_desc_res,
         SG_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
         ctx->slice_events.push_back(e);
     }
+    // SLAMGPU_TRACE_BATCH=1: host timestamps of this call's phases, summed per context (slamgpu_trace_read): where a
+    // step's host time goes when eight ranks share one host
+    const bool trace = ctx->trace_batch;
+    auto now = []() { return std::chrono::duration<double, std::micro>(std::chrono::steady_clock::now().time_since_epoch()).count(); };
+    const double t_call = trace ? now() : 0.0;
     uint8_t* hs = static_cast<uint8_t*>(ctx->h_stage.ptr);
     int32_t* h_offset = reinterpret_cast<int32_t*>(hs);
     const bool direct = capacity > 0 && is_pinned(out_query) && is_pinned(out_train);
@@ -490,6 +496,7 @@ int batch_host(slamgpu_ctx* ctx, const uint8_t* desc, const uint8_t* d_desc_res,
         cudaStreamSynchronize(ctx->copy_stream);
         return rc;
     }
+    const double t_queued = trace ? now() : 0.0;       // every kernel of the call is queued; the GPU is working
     // h_offset[0] is never written or read on the host: the pinned block's first bytes may still be the source
     // of an upload queued behind an unsynchronised *_dev call (the descriptors, or the pair list of the resident
     // form), so nothing on the host may touch it before the stream has drained.  Offset 0 is the constant 0.
@@ -504,9 +511,11 @@ int batch_host(slamgpu_ctx* ctx, const uint8_t* desc, const uint8_t* d_desc_res,
         }
         return SLAMGPU_OK;
     };
+    double t_last_offsets = 0.0;
     for (int s = 0; s < slice_no; ++s) {
         const int p0 = slices[s].first, np = slices[s].second;
         SG_CUDA(cudaEventSynchronize(ctx->slice_events[3 * s + 1]));
+        if (trace) t_last_offsets = now();
         const int64_t end = h_offset[p0 + np];
         // offsets are int32 on the device; one slice adds < 2^31 entries (slice_for), so a wrapped total shows up
         // as an end below its begin
@@ -530,6 +539,14 @@ int batch_host(slamgpu_ctx* ctx, const uint8_t* desc, const uint8_t* d_desc_res,
     if (prev >= 0) SG_TRY(unstage(prev, prev_begin, prev_end));
     SG_CUDA(cudaStreamSynchronize(ctx->copy_stream));
     SG_CUDA(cudaStreamSynchronize(ctx->stream));
+    if (trace) {
+        const double t_end = now();
+        ctx->trace_us[0] += t_queued - t_call;            // staging, uploads queued, every slice's kernels queued
+        ctx->trace_us[1] += t_last_offsets - t_queued;    // waiting for the GPU (slices' offsets arriving; list copies queued meanwhile)
+        ctx->trace_us[2] += t_end - t_last_offsets;       // the tail: the last slice's lists come down, final synchronisation
+        ctx->trace_us[3] += t_end - t_call;
+        ctx->trace_calls++;
+    }
     out_offset[0] = 0;
     std::memcpy(out_offset + 1, h_offset + 1, sizeof(int32_t) * static_cast<size_t>(n_pairs));
     *out_total = out_offset[n_pairs];

@@ -404,7 +404,12 @@ __device__ __forceinline__ void group_search(const ProjFrameArgs& f, const ProjC
     // P5 + P6: candidates from the grid, the rows flattened over the lanes
     int best = c.thr;                                            // lane-local best: accept d < thr
     int best_m = -1;
-    // P6 for one candidate: every observation descriptor of the point against the keypoint's
+    bool lane_tie = false;                                       // speculative call only: this lane's best is shared
+    // P6 for one candidate: every observation descriptor of the point against the keypoint's.  m = the candidate's
+    // KD position, or -- in a speculative call made before the KD-tree has been built (f.kd_ready == 0) -- its
+    // keypoint index: then ties cannot be settled, they are only COUNTED (f.ties), and the caller repeats the call
+    // with the tree if the count is not zero.  Ties at the minimum are rare (two keypoints in the search radius
+    // whose best Hamming distance to the point's observations is equal AND under the maximum distance).
     auto score = [&](const int kp, const int m) {
         const unsigned kp_matched = f.matched[kp];               // round trip 5: flag and descriptor together
         const uint4 a0 = __ldg(&f.desc[2 * kp]), a1 = __ldg(&f.desc[2 * kp + 1]);
@@ -420,8 +425,10 @@ __device__ __forceinline__ void group_search(const ProjFrameArgs& f, const ProjC
         if (dmin < best) {
             best = dmin;
             best_m = m;
+            lane_tie = false;
         } else if (dmin == best && best_m >= 0) {                // tie inside one lane: earlier visit wins
-            if (kd_visit_key(f.kd_xy, f.nkp, m, u, w) < kd_visit_key(f.kd_xy, f.nkp, best_m, u, w)) best_m = m;
+            if (!f.kd_ready) lane_tie = true;                    // speculative call: the tree is not there yet
+            else if (kd_visit_key(f.kd_xy, f.nkp, m, u, w) < kd_visit_key(f.kd_xy, f.nkp, best_m, u, w)) best_m = m;
         }
     };
     // QUEUE: the slots that pass the radius test (about 4 in 10 of the box) are packed into a per-group queue
@@ -469,7 +476,7 @@ __device__ __forceinline__ void group_search(const ProjFrameArgs& f, const ProjC
                 const float d2 = __fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy));    // :63
                 pass = d2 <= c.r2;                               // :65
                 kp = rec.z;
-                m = rec.w;
+                m = f.kd_ready ? rec.w : rec.z;
             }
             if (!QUEUE) {
                 if (pass) score(kp, m);
@@ -500,7 +507,10 @@ __device__ __forceinline__ void group_search(const ProjFrameArgs& f, const ProjC
     const bool tied = best_m >= 0 && best == wbest;
     const unsigned ballot = __ballot_sync(gmask, tied);
     int win_lane = __ffs(ballot) - 1;                            // lane index within the warp
-    if (__popc(ballot) > 1) {
+    if (!f.kd_ready) {                                           // speculative: count what the tree would have settled
+        const unsigned lt = __ballot_sync(gmask, tied && lane_tie);
+        if (static_cast<int>(threadIdx.x & 31) == win_lane && (__popc(ballot) > 1 || lt != 0u)) atomicAdd(f.ties, 1u);
+    } else if (__popc(ballot) > 1) {
         unsigned long long key = tied ? kd_visit_key(f.kd_xy, f.nkp, best_m, u, w) : ~0ull;
         const unsigned hi = __reduce_min_sync(gmask, static_cast<unsigned>(key >> 32));
         const unsigned lo = __reduce_min_sync(gmask, (key >> 32) == hi ? static_cast<unsigned>(key) : 0xFFFFFFFFu);
@@ -508,7 +518,7 @@ __device__ __forceinline__ void group_search(const ProjFrameArgs& f, const ProjC
         win_lane = __ffs(__ballot_sync(gmask, tied && key == wkey)) - 1;
     }
     if (static_cast<int>(threadIdx.x & 31) == win_lane) {
-        const int best_kp = f.kd_idx[best_m];
+        const int best_kp = f.kd_ready ? f.kd_idx[best_m] : best_m;
         // P7: first point in visit order attaining the minimum wins (src/MapMatcher.cpp:95-97)
         const unsigned long long key = (static_cast<unsigned long long>(wbest) << 32) | static_cast<unsigned>(v);
         atomicMin(&f.proposals[best_kp], key);
@@ -749,9 +759,11 @@ __global__ void proj_emit_kernel(const ProjKernelArgs a)
         const int v = static_cast<int>(key & 0xFFFFFFFFull);
         point = a.c.order ? a.c.order[v] : v;
         dist = static_cast<int>(key >> 32);
+        f.proposals[kp] = ~0ull;          // the slots are all-ones at rest (set at upload): no reset pass before a call
     }
     f.out_point[kp] = point;
     f.out_dist[kp] = dist;
+    if (kp == 0 && f.ties_out != nullptr) *f.ties_out = *f.ties;      // zero-copy call: the tie count to host memory
 }
 
 // Emit + Frame::add_map_match (src/Frame.cpp:80-102) on the device.  A proposal comes from a point that
@@ -781,13 +793,6 @@ __global__ void proj_scatter_flags_kernel(const int32_t* idx, int n, uint8_t* fl
 {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n) flags[idx[i]] = 1;
-}
-
-__global__ void proj_init_kernel(const ProjKernelArgs a)
-{
-    const ProjFrameArgs& f = a.frames ? a.frames[blockIdx.y] : a.inline_frame;
-    const int kp = blockIdx.x * blockDim.x + threadIdx.x;
-    if (kp < f.nkp) f.proposals[kp] = ~0ull;
 }
 
 // src/MapPoint.cpp:24-45, one thread per point, observations in the host's iteration order.
@@ -887,8 +892,6 @@ int proj_launch(slamgpu_ctx* ctx, const ProjCommonArgs& common, const ProjFrameA
     SG_CHECK(n_frames <= 65535, "too many frames in one projection batch");
     if (max_nkp > 0) {
         const dim3 gk((max_nkp + 255) / 256, n_frames);
-        proj_init_kernel<<<gk, 256, 0, ctx->stream>>>(a);
-        ctx->launches++;
         if (common.n_visit > 0) SG_TRY(launch_match(ctx, a, common.n_visit, n_frames));
         proj_emit_kernel<<<gk, 256, 0, ctx->stream>>>(a);
         ctx->launches++;
@@ -916,8 +919,6 @@ int proj_launch_track(slamgpu_ctx* ctx, const ProjCommonArgs& common, const Proj
     a.inline_frame.skip = d_pt_matched;  // frame.is_matched(point), :53
     a.frames = nullptr;
     const dim3 gk((nkp + 255) / 256, 1);
-    proj_init_kernel<<<gk, 256, 0, ctx->stream>>>(a);
-    ctx->launches++;
     // stage 1: match_key_frame -- the points the last key frame observes, in map order (:169)
     a.c.order = d_kf_order;
     a.c.n_visit = n_kf;

@@ -251,6 +251,16 @@ int slamgpu_create(int device, slamgpu_ctx** out)
     if (tp != nullptr) ctx->proj_two_pass = std::atoi(tp);
     const char* mr = std::getenv("SLAMGPU_MAP_RESERVE");
     if (mr != nullptr) ctx->map_reserve = std::min(std::max(std::atoi(mr), 0), 1 << 28);
+    const char* trb = std::getenv("SLAMGPU_TRACE_BATCH");
+    ctx->trace_batch = trb != nullptr && trb[0] == '1';
+    const char* pzc = std::getenv("SLAMGPU_PROJ_ZEROCOPY");
+    if (pzc != nullptr) ctx->proj_zero_copy = pzc[0] != '0';
+    const char* kdl = std::getenv("SLAMGPU_KD_LAZY");
+    if (kdl != nullptr) ctx->kd_lazy = kdl[0] != '0';
+    const char* kdd = std::getenv("SLAMGPU_KD_DELAY_MS");
+    if (kdd != nullptr) ctx->kd_delay_ms = std::min(std::max(std::atoi(kdd), 0), 10000);
+    const char* kds = std::getenv("SLAMGPU_KD_SPECULATE");
+    if (kds != nullptr) ctx->kd_speculate = kds[0] != '0';
     const char* kda = std::getenv("SLAMGPU_KD_ASYNC");
     if (kda != nullptr) ctx->kd_async = kda[0] != '0';
     const char* v2 = std::getenv("SLAMGPU_PROJ_V2");
@@ -449,6 +459,18 @@ int slamgpu_host_point_stats(const float* xyz, int n_obs, const float* obs_cente
     host_normalized3(acc, out_normal);
     out_range[0] = nearest;
     out_range[1] = furthest;
+    return SLAMGPU_OK;
+}
+
+int slamgpu_trace_read(slamgpu_ctx* ctx, double* out_us4, int64_t* out_calls)
+{
+    SG_CHECK(ctx != nullptr && out_us4 != nullptr, "null pointer");
+    for (int i = 0; i < 4; ++i) {
+        out_us4[i] = ctx->trace_us[i];
+        ctx->trace_us[i] = 0.0;
+    }
+    if (out_calls) *out_calls = ctx->trace_calls;
+    ctx->trace_calls = 0;
     return SLAMGPU_OK;
 }
 

@@ -3,6 +3,7 @@
 
 #include <cuda_runtime.h>
 
+#include <atomic>
 #include <cstdint>
 #include <cstdio>
 #include <map>
@@ -59,6 +60,8 @@ constexpr uint32_t kKeyNone = 0xFFFFFFFFu;
 // The KD-tree of a frame being built on a host thread (slamgpu_frame_upload) until a call needs it.
 struct FrameKdPending {
     std::thread worker;
+    std::atomic<int> done{0};         // set by the worker when the image is complete
+    bool lazy = false;                // no worker: the tree is built by the first call that needs it (finalize_frame)
     std::vector<float> xy;            // private copy of the keypoints
     std::vector<uint32_t> perm;       // the tree as its permutation
     std::vector<uint8_t> image;       // host image of the KD-ordered device arrays
@@ -81,6 +84,9 @@ struct FrameDev {
     int32_t* cell_start = nullptr;            // [gw*gh + 1]
     int32_t* cell_items = nullptr;            // [nkp] KD positions, cell-major
     int4* cell_rec = nullptr;                 // [nkp] cell-major (x bits, y bits, keypoint index, KD position)
+    int32_t* cell_start_spec = nullptr;       // [gw*gh + 1] uploaded with the frame (same values as cell_start)
+    int4* cell_rec_spec = nullptr;            // [nkp] the same without the tree: (x bits, y bits, keypoint index, keypoint index);
+                                              // resident with the frame itself, so a match call need not wait for the KD build
     float gx0 = 0.f, gy0 = 0.f, inv_cell = 1.f;
     int gw = 1, gh = 1;
     std::vector<uint32_t> perm_host;
@@ -181,6 +187,13 @@ struct slamgpu_ctx {
     int proj_two_pass = 0;    // SLAMGPU_PROJ_TWOPASS=1|2: force / forbid the gate + search form of K4 (0 = by visit count)
     int map_reserve = 1 << 18; // SLAMGPU_MAP_RESERVE: points reserved by a point set's first growth (4 observations each)
     bool kd_async = true;     // SLAMGPU_KD_ASYNC=0: build the KD-tree inside slamgpu_frame_upload instead of on a thread
+    bool kd_speculate = true; // SLAMGPU_KD_SPECULATE=0: a match call waits for the KD-tree instead of running on the tree-free grid
+    bool proj_zero_copy = true;   // SLAMGPU_PROJ_ZEROCOPY=0: small projection calls copy their lists / results instead of
+                                  // letting the kernels read and write the pinned staging buffer directly
+    bool kd_lazy = true;      // SLAMGPU_KD_LAZY=0: always start the KD builder thread at upload (round 1's behaviour + speculation)
+    int spec_tie_streak = 0;  // > 0 after a speculative call hit a tie: the next uploads build their tree eagerly again
+    int kd_delay_ms = 0;      // SLAMGPU_KD_DELAY_MS: the KD builder sleeps first (tests: makes match calls find the tree missing)
+    int64_t spec_calls = 0, spec_repeats = 0;   // speculative match calls, and how many had to be repeated with the tree
     bool proj_walk = false;   // SLAMGPU_PROJ_WALK=1: use the thread-per-point KD-walk kernel
     int bf_engine = 0;        // SLAMGPU_BF_ENGINE=int|tc overrides the brute-force engine choice (0 = by size, 1 = int, 2 = tc)
     int tc_variant = 0;       // SLAMGPU_TC_VARIANT: debug switches of the tensor-core scans; read only in -DSLAMGPU_DEBUG_VARIANTS builds
@@ -198,6 +211,9 @@ struct slamgpu_ctx {
     std::map<int, slamgpu::BowDbDev> bow_dbs;
     std::map<int, slamgpu::KfDbDev> kf_dbs;
     bool bow_smem_set = false;
+    bool trace_batch = false;                  // SLAMGPU_TRACE_BATCH=1
+    double trace_us[4] = {0, 0, 0, 0};
+    int64_t trace_calls = 0;
     int batch_slice = 0;                       // SLAMGPU_BATCH_SLICE: pairs per slice of the batch calls (0 = by scratch size)
     cudaStream_t copy_stream = nullptr;        // result copies of the batch call, overlapped with later slices
     std::vector<cudaEvent_t> slice_events;     // 3 per slice of slamgpu_match_descriptors_batch (created on demand)
@@ -298,6 +314,9 @@ struct ProjFrameArgs {
     const int4* cell_rec;
     float gx0, gy0, inv_cell;
     int gw, gh;
+    int kd_ready;            // 0: speculative call before the KD-tree is built -- cell_rec holds (x, y, keypoint, keypoint),
+    unsigned int* ties;      //    kd_xy / kd_idx are not read and ties at the minimum are counted here instead of settled
+    unsigned int* ties_out;  // zero-copy call: where the emit kernel leaves the tie count (mapped host memory) or null
     const uint8_t* skip;     // [n_points] for this frame or null
     int32_t* out_point;      // [nkp]
     int32_t* out_dist;       // [nkp]

@@ -210,3 +210,54 @@ def test_track_match_with_either_form_of_the_match_kernel(oracle, pkg, monkeypat
     with pkg.Context(0) as c:
         for scene in TRACK_SCENES[:2]:
             test_track_match_equals_the_two_reference_calls(c, oracle, pkg, *scene)
+
+
+@pytest.mark.parametrize("ties", [False, True])
+def test_calls_that_arrive_before_the_kd_tree_speculate_and_repeat_on_ties(oracle, pkg, monkeypatch, ties):
+    """slamgpu_frame_upload builds the KD-tree on a host thread; a projection call that finds it missing runs on the
+    tree-free grid and counts the ties only the KD visit order can settle (src/KDTree.cpp:52-82,
+    src/MapMatcher.cpp:88).  SLAMGPU_KD_DELAY_MS makes the builder late on purpose.  Without ties the speculative
+    results stand; with ties (low-entropy descriptors) the call waits for the tree, restores the frame's keypoint
+    flags and repeats itself -- either way the results are the oracle's."""
+    monkeypatch.setenv("SLAMGPU_KD_DELAY_MS", "40")
+    cam = dict(fx=300.0, fy=300.0, cx=160.0, cy=120.0, width=320, height=240)
+    sc = pkg.synthetic.projection_scene(6000, 1500, 93, cam=cam)
+    rng = np.random.default_rng(93)
+    if ties:
+        sc.kp_desc[:] = rng.integers(0, 2, sc.kp_desc.shape, dtype=np.uint8) * 255
+        sc.obs_desc[:] = rng.integers(0, 2, sc.obs_desc.shape, dtype=np.uint8) * 255
+    p = _params(pkg, cam, 20.0, 200.0 if ties else 64.0)
+    op = _oparams(oracle, p)
+    perm = oracle.kd_build(sc.kp_xy)
+    kf_points = np.sort(rng.choice(6000, 2000, replace=False)).astype(np.int32)
+    matched_points = rng.choice(6000, 300, replace=False).astype(np.int32)
+    with pkg.Context(0) as c:
+        c.points_upload(1, sc.pos, sc.normal, sc.range, sc.obs_offset, sc.obs_desc)
+        # one projection call
+        c.frame_upload(1, sc.kp_xy, sc.kp_desc, None, sc.kp_matched)
+        gp, gd = c.match_projection(1, 1, 1500, sc.pose, p, sc.skip, None)
+        ref = oracle.match_projection(sc.kp_xy, sc.kp_desc, perm, sc.kp_matched, sc.pos, sc.normal, sc.range, sc.obs_offset,
+                                      sc.obs_desc, sc.skip, None, sc.pose, op, want_stats=False)
+        assert np.array_equal(gp, ref.point) and np.array_equal(gd, ref.dist)
+        calls, repeats = c.speculation_count()
+        assert calls == 1 and repeats == (1 if ties else 0)
+        # the chained tracking pair on a freshly uploaded frame (its tree is late again)
+        c.frame_upload(1, sc.kp_xy, sc.kp_desc, None, sc.kp_matched)
+        r1, r2, kp_after, pt_after = _oracle_track(oracle, sc, perm, sc.kp_matched, matched_points, kf_points, op)
+        kf_pt, kf_d, map_pt, map_d = c.track_match(1, 1, 1500, sc.pose, p, matched_points, kf_points)
+        assert np.array_equal(kf_pt, r1.point) and np.array_equal(kf_d, r1.dist)
+        assert np.array_equal(map_pt, r2.point) and np.array_equal(map_d, r2.dist)
+        calls, repeats = c.speculation_count()
+        assert calls == 2 and repeats == (2 if ties else 0)
+        # the frame's flags are those after both add_map_match loops (restored, then rewritten by the repeat)
+        ref3 = oracle.match_projection(sc.kp_xy, sc.kp_desc, perm, kp_after, sc.pos, sc.normal, sc.range, sc.obs_offset,
+                                       sc.obs_desc, pt_after, None, sc.pose, op, want_stats=False)
+        op3, od3 = c.match_projection(1, 1, 1500, sc.pose, p, pt_after, None)
+        assert np.array_equal(op3, ref3.point) and np.array_equal(od3, ref3.dist)
+        # SLAMGPU_KD_SPECULATE=0 is the old behaviour: wait for the tree
+    monkeypatch.setenv("SLAMGPU_KD_SPECULATE", "0")
+    with pkg.Context(0) as c:
+        c.points_upload(1, sc.pos, sc.normal, sc.range, sc.obs_offset, sc.obs_desc)
+        c.frame_upload(1, sc.kp_xy, sc.kp_desc, None, sc.kp_matched)
+        gp, gd = c.match_projection(1, 1, 1500, sc.pose, p, sc.skip, None)
+        assert np.array_equal(gp, ref.point) and np.array_equal(gd, ref.dist) and c.speculation_count() == (0, 0)

@@ -80,6 +80,7 @@ def run_sequence(ctx, pkg, n_frames=2000, nkp=8000, ppf=100, seed=3, cpu_frames=
         prev = cur
     k_ms, k_n = ctx.profile_read(1)
     ctx.profile_enable(False)
+    spec_calls, spec_repeats = ctx.speculation_count()
     total = float(t_parts.sum())
     out = {
         "workload": f"{n_frames} frames x {nkp} keypoints (1920x1080), map 0 -> {n_frames * ppf} points "
@@ -94,6 +95,7 @@ def run_sequence(ctx, pkg, n_frames=2000, nkp=8000, ppf=100, seed=3, cpu_frames=
         "gcmp_s_bruteforce_part": nkp * nkp / (t_parts[1] / n_frames) / 1e9,
         "proj_match_kernel_us_avg": k_ms / max(k_n, 1) * 1e3, "proj_match_kernel_launches": int(k_n),
         "keyframe_matches": n_kf, "map_matches": n_map, "copies": "inside", "clock": "host",
+        "speculative_calls_so_far": spec_calls, "speculative_calls_repeated_with_the_tree": spec_repeats,
     }
     if kept:
         out["cpu"] = cpu_arm(pkg, seq, kept, prm)
