@@ -432,16 +432,21 @@ def run_ours(args, rank, local_rank, world):
 
     for s in range(W):
         step_resident(s)
+    sampler_res = ClockSampler(local_rank) if rank == 0 else None
     barrier()
     torch.cuda.synchronize()
     ctx.trace_read()
+    tw0 = time.time()
     t0 = time.perf_counter()
     d2h_res = 0
     for s in range(K):
         d2h_res += 4 * (n + 1) + 8 * step_resident(W + s)
     torch.cuda.synchronize()
     t_res_own = time.perf_counter() - t0
+    tw1 = time.time()
     t_res = max_over_ranks(t_res_own)
+    t_res_min = -max_over_ranks(-t_res_own)
+    clocks_res = sampler_res.stop(tw0, tw1) if sampler_res else None
     trace_us, trace_calls = ctx.trace_read()
     barrier()
     assert np.array_equal(np.diff(o_off.astype(np.int64)), dev_counts_last), "resident database form disagrees"
@@ -466,7 +471,8 @@ def run_ours(args, rank, local_rank, world):
                     "d2h_bytes_per_step": d2h_res // K, "ms_per_step": t_res / K * 1e3,
                     "api": "slamgpu_kfdb_match_pairs (key frames appended once before the clock; pair list up, match "
                            "lists down every step)",
-                    "loop_query_5_candidates_us": loop_query_us}
+                    "loop_query_5_candidates_us": loop_query_us,
+                    "ms_per_step_fastest_rank": t_res_min / K * 1e3, "clocks_rank0": clocks_res}
     if os.environ.get("SLAMGPU_TRACE_BATCH") == "1" and trace_calls:
         # where the host time of a step goes (rank 0's own clock; SLAMGPU_TRACE_BATCH=1)
         e2e_resident["host_trace_ms_per_step_rank0"] = {

@@ -74,6 +74,9 @@ class MapMatcherGpu : public MapChangeListener {
     std::pair<std::vector<MapPointMatch>, std::vector<MapPointMatch>> track(Frame& frame, Map& map,
                                                                             KeyFrame& last_key_frame) const;
 
+    /** The libslamgpu context this matcher owns (for helpers that share it, e.g. LoopDetectorGpu). */
+    slamgpu_ctx* context() const { return m_ctx; }
+
     // ---- resident map ----
     /** Keep `map` mirrored on the device from now on (full upload now, deltas afterwards). */
     void attach(Map& map, MirrorMode mode = MirrorMode::Hooks);

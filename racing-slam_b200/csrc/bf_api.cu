@@ -373,7 +373,14 @@ struct PairIo {
     int32_t* d_a = nullptr;   // first output array
     int32_t* d_b = nullptr;   // second output array
     size_t out_a_bytes = 0, out_b_bytes = 0;
+    bool zero_copy = false;   // d_a / d_b ARE the pinned host image: the kernels write the results straight into it
+    int32_t* d_b_dev = nullptr;   // the device slot of the second output whatever the mode (atomic targets stay on the device)
 };
+
+// Outputs up to this size are written by the kernels directly into the pinned staging buffer (page-locked host
+// memory is device-addressable): a single-pair call is then one upload, the kernels and one synchronisation --
+// no download to queue.  The reference makes exactly such calls, one per loop candidate (src/LoopDetector.cpp:181).
+constexpr size_t kZeroCopyOutBytes = size_t(256) << 10;
 
 // device + pinned buffers for one (query, train) call with two int32 outputs, inputs uploaded
 int stage_pair(slamgpu_ctx* ctx, const uint8_t* q, int nq, const uint8_t* t, int nt, size_t out_a_elems,
@@ -384,20 +391,40 @@ int stage_pair(slamgpu_ctx* ctx, const uint8_t* q, int nq, const uint8_t* t, int
     io.out_b_bytes = out_b_elems * sizeof(int32_t);
     const size_t ob = Carver::padded(io.out_a_bytes) + Carver::padded(io.out_b_bytes);
     SG_TRY(ensure_device_io(ctx, qb + tb + ob + 256));
-    SG_TRY(ensure_host_stage(ctx, std::max(qb + tb, ob) + 256));
+    SG_TRY(ensure_host_stage(ctx, qb + tb + ob + 256));
     Carver dio(ctx->d_io.ptr);
     io.d_q = dio.take<uint8_t>(static_cast<size_t>(nq) * 32);
     io.d_t = dio.take<uint8_t>(static_cast<size_t>(nt) * 32);
     io.d_a = dio.take<int32_t>(out_a_elems);
     io.d_b = dio.take<int32_t>(out_b_elems);
+    io.d_b_dev = io.d_b;
+    io.zero_copy = ctx->bf_zero_copy && ob <= kZeroCopyOutBytes && nq > 0 && nt > 0;    // (empty sets are answered by memsets)
+    if (io.zero_copy) {       // the results' host image sits behind the inputs in the staging buffer
+        uint8_t* h_out = static_cast<uint8_t*>(ctx->h_stage.ptr) + qb + tb;
+        io.d_a = reinterpret_cast<int32_t*>(h_out);
+        io.d_b = reinterpret_cast<int32_t*>(h_out + Carver::padded(io.out_a_bytes));
+    }
+    if (!is_pinned(q) && !is_pinned(t)) {     // both sets through the staging buffer: one copy for the two
+        uint8_t* hs = static_cast<uint8_t*>(ctx->h_stage.ptr);
+        std::memcpy(hs, q, static_cast<size_t>(nq) * 32);
+        std::memcpy(hs + qb, t, static_cast<size_t>(nt) * 32);
+        if (qb + tb) SG_CUDA(cudaMemcpyAsync(io.d_q, hs, qb + static_cast<size_t>(nt) * 32, cudaMemcpyHostToDevice, ctx->stream));
+        return SLAMGPU_OK;
+    }
     SG_TRY(upload(ctx, io.d_q, q, static_cast<size_t>(nq) * 32, 0));
     SG_TRY(upload(ctx, io.d_t, t, static_cast<size_t>(nt) * 32, qb));
     return SLAMGPU_OK;
 }
 
-// one D2H copy of both outputs into pinned memory, then wait
+// the outputs in pinned memory (one D2H copy of both unless the kernels wrote them there), then wait
 int fetch_pair(slamgpu_ctx* ctx, const PairIo& io, const int32_t** h_a, const int32_t** h_b)
 {
+    if (io.zero_copy) {
+        SG_CUDA(cudaStreamSynchronize(ctx->stream));
+        *h_a = io.d_a;
+        *h_b = io.d_b;
+        return SLAMGPU_OK;
+    }
     const size_t ob = Carver::padded(io.out_a_bytes) + io.out_b_bytes;
     if (ob) SG_CUDA(cudaMemcpyAsync(ctx->h_stage.ptr, io.d_a, ob, cudaMemcpyDeviceToHost, ctx->stream));
     SG_CUDA(cudaStreamSynchronize(ctx->stream));
@@ -611,7 +638,8 @@ int slamgpu_match_descriptors(slamgpu_ctx* ctx, const uint8_t* query, int nq, co
     SG_CHECK(out_query && out_train, "null output");
     PairIo io;
     SG_TRY(stage_pair(ctx, query, nq, train, nt, nq, 1, io));
-    SG_TRY(match_descriptors_core(ctx, io.d_q, nq, io.d_t, nt, max_dist, ratio, io.d_a, io.d_b));
+    // the per-call count is an atomicAdd target: in zero-copy mode it stays on the device (the host counts the flags)
+    SG_TRY(match_descriptors_core(ctx, io.d_q, nq, io.d_t, nt, max_dist, ratio, io.d_a, io.d_b_dev));
     const int32_t *h_train, *h_count;
     SG_TRY(fetch_pair(ctx, io, &h_train, &h_count));
     // marshal the per-row result into the reference's list form (ascending queryIdx, :151-161)
@@ -623,7 +651,7 @@ int slamgpu_match_descriptors(slamgpu_ctx* ctx, const uint8_t* query, int nq, co
             ++n;
         }
     }
-    if (n != h_count[0]) return fail(SLAMGPU_ERR_CUDA, "match_descriptors: device count and row flags disagree");
+    if (!io.zero_copy && n != h_count[0]) return fail(SLAMGPU_ERR_CUDA, "match_descriptors: device count and row flags disagree");
     *out_count = n;
     return SLAMGPU_OK;
 }

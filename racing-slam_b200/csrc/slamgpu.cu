@@ -253,6 +253,8 @@ int slamgpu_create(int device, slamgpu_ctx** out)
     if (mr != nullptr) ctx->map_reserve = std::min(std::max(std::atoi(mr), 0), 1 << 28);
     const char* trb = std::getenv("SLAMGPU_TRACE_BATCH");
     ctx->trace_batch = trb != nullptr && trb[0] == '1';
+    const char* bzc = std::getenv("SLAMGPU_BF_ZEROCOPY");
+    if (bzc != nullptr) ctx->bf_zero_copy = bzc[0] != '0';
     const char* pzc = std::getenv("SLAMGPU_PROJ_ZEROCOPY");
     if (pzc != nullptr) ctx->proj_zero_copy = pzc[0] != '0';
     const char* kdl = std::getenv("SLAMGPU_KD_LAZY");

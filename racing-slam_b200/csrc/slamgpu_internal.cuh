@@ -188,6 +188,7 @@ struct slamgpu_ctx {
     int map_reserve = 1 << 18; // SLAMGPU_MAP_RESERVE: points reserved by a point set's first growth (4 observations each)
     bool kd_async = true;     // SLAMGPU_KD_ASYNC=0: build the KD-tree inside slamgpu_frame_upload instead of on a thread
     bool kd_speculate = true; // SLAMGPU_KD_SPECULATE=0: a match call waits for the KD-tree instead of running on the tree-free grid
+    bool bf_zero_copy = true;     // SLAMGPU_BF_ZEROCOPY=0: single-pair brute-force calls download their results with a copy
     bool proj_zero_copy = true;   // SLAMGPU_PROJ_ZEROCOPY=0: small projection calls copy their lists / results instead of
                                   // letting the kernels read and write the pinned staging buffer directly
     bool kd_lazy = true;      // SLAMGPU_KD_LAZY=0: always start the KD builder thread at upload (round 1's behaviour + speculation)

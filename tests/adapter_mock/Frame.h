@@ -12,6 +12,7 @@ class Frame {   // accessors of reference src/Frame.h:36-57; add / remove_map_ma
     Frame(int index, const ExtractedFeatures& features) : m_index(index), m_features(features), m_map_matches(features.keypoints.size(), nullptr) {}
     const cv::Mat descriptor(size_t index) const { return m_features.descriptors.row(static_cast<int>(index)); }
     const ExtractedFeatures& features() const { return m_features; }
+    const cv::KeyPoint& keypoint(size_t index) const { return m_features.keypoints[index]; }
     Eigen::Vector3f camera_center() const
     {   // -R^T t with the a0 + (a1 + a2) order (src/Frame.cpp:39-42)
         Eigen::Vector3f c;

@@ -7,6 +7,7 @@
 //   adapter_driver --bench <points> <keypoints> <frames> <out.json>
 //                                             a C3-sized mock world: wall time of MapMatcherGpu::track per frame
 //                                             with a mutation mix, resident against per-call uploads
+#include <array>
 #include <chrono>
 #include <cstdio>
 #include <cstdlib>
@@ -22,6 +23,7 @@
 #include "Camera.h"
 #include "Frame.h"
 #include "Map.h"
+#include "LoopDetectorGpu.h"
 #include "MapMatcherGpu.h"
 #include "MapPoint.h"
 
@@ -312,7 +314,14 @@ static int run_world(const char* path, const char* out_path)
                         kept += line + "\n";
                 return kept;
             };
+            // The three replays run on three separately built worlds: MapPoint::observations() is an unordered_map
+            // keyed by KeyFrame POINTERS (src/MapPoint.h:38), so its iteration order -- the order of the float sum
+            // in avg_viewing_normal -- may differ between them, exactly as it may between two runs of the reference.
+            // Each replay is therefore checked against the oracle fed ITS OWN dumped map; "modes_agree" is information.
             out << "modes_agree " << (strip(hooks) == percall && strip(scan) == percall ? 1 : 0) << "\n";
+            std::ofstream(std::string(out_path) + ".hooks") << hooks;
+            std::ofstream(std::string(out_path) + ".scan") << scan;
+            std::ofstream(std::string(out_path) + ".percall") << percall;
             out << "script\n" << hooks;
         }
     } catch (const std::exception& e) {
@@ -475,8 +484,86 @@ static int run_bench(int n_points, int nkp, int n_frames, const char* out_path)
     return 0;
 }
 
+// ---- loop detector helper: vocabulary lookups, scoring, PnP model scoring ---------------------------
+
+static uint64_t bits64(double d)
+{
+    uint64_t u;
+    std::memcpy(&u, &d, 8);
+    return u;
+}
+
+static int run_loop(const char* path, const char* out_path)
+{
+    std::ifstream f(path, std::ios::binary);
+    std::ofstream out(out_path);
+    const int n_nodes = rd<int32_t>(f);
+    std::vector<int32_t> child_offset(n_nodes + 1);
+    f.read(reinterpret_cast<char*>(child_offset.data()), sizeof(int32_t) * child_offset.size());
+    std::vector<int32_t> child_ids(static_cast<size_t>(child_offset[n_nodes]));
+    f.read(reinterpret_cast<char*>(child_ids.data()), sizeof(int32_t) * child_ids.size());
+    std::vector<uint8_t> node_desc(size_t(n_nodes) * 32);
+    f.read(reinterpret_cast<char*>(node_desc.data()), node_desc.size());
+    std::vector<double> weight(n_nodes);
+    f.read(reinterpret_cast<char*>(weight.data()), sizeof(double) * weight.size());
+    std::vector<int32_t> word_id(n_nodes);
+    f.read(reinterpret_cast<char*>(word_id.data()), sizeof(int32_t) * word_id.size());
+    const int n_kf = rd<int32_t>(f);
+    std::vector<std::unique_ptr<KeyFrame>> kfs;
+    for (int k = 0; k < n_kf; k++) {
+        const int nkp = rd<int32_t>(f);
+        kfs.push_back(std::make_unique<KeyFrame>(k, read_features(f, nkp)));
+    }
+    const int n_corr = rd<int32_t>(f);
+    std::vector<cv::Point3f> object(n_corr);
+    std::vector<cv::Point2f> image(n_corr);
+    for (auto& p : object) { p.x = rd<float>(f); p.y = rd<float>(f); p.z = rd<float>(f); }
+    for (auto& p : image) { p.x = rd<float>(f); p.y = rd<float>(f); }
+    const int n_models = rd<int32_t>(f);
+    std::vector<std::array<double, 12>> models(n_models);
+    for (auto& m : models)
+        for (double& v : m) v = rd<double>(f);
+    double K4[4];
+    for (double& v : K4) v = rd<double>(f);
+    if (!f) {
+        std::cerr << "short loop file\n";
+        return 3;
+    }
+    try {
+        // shares the matcher's context, as LoopDetector::Impl holds both (src/LoopDetector.cpp:314-330)
+        Camera camera(static_cast<float>(K4[0]), static_cast<float>(K4[1]), static_cast<float>(K4[2]), static_cast<float>(K4[3]), 1241, 376);
+        MapMatcherGpu matcher(camera, 64.0F, cv::NORM_HAMMING);
+        LoopDetectorGpu loop(matcher.context());
+        loop.set_vocabulary(n_nodes, child_offset.data(), child_ids.data(), node_desc.data(), weight.data(), word_id.data());
+        std::vector<DBoW2::BowVector> bows;
+        for (int k = 0; k < n_kf; k++) {
+            bows.push_back(loop.bow_of(kfs[k]->features()));            // bow_of, src/LoopDetector.cpp:85-92
+            out << "bow " << bows.back().size() << "\n";
+            for (const auto& [word, value] : bows.back()) out << word << " " << bits64(value) << "\n";
+            if (loop.add_key_frame(bows.back()) != static_cast<size_t>(k)) return 4;
+        }
+        const std::vector<double> scores = loop.score_against_all(bows.back());   // score_candidates, :346-373
+        out << "scores " << scores.size() << "\n";
+        for (double s : scores) out << bits64(s) << "\n";
+        const auto pnp = loop.score_pnp_models(object, image, models, K4[0], K4[1], K4[2], K4[3]);   // verify_pnp, :203-214
+        out << "pnp_counts " << pnp.inlier_counts.size() << "\n";
+        for (int32_t c : pnp.inlier_counts) out << c << "\n";
+        out << "pnp_best 1\n" << pnp.best << " " << pnp.inliers << "\n";
+        out << "pnp_mask " << pnp.inlier_mask.size() << "\n";
+        for (uint8_t m : pnp.inlier_mask) out << int(m) << "\n";
+        // an empty frame gives an empty vector (:88) and scores 0 against everything
+        ExtractedFeatures none;
+        out << "empty_bow " << loop.bow_of(none).size() << "\n";
+    } catch (const std::exception& e) {
+        std::cerr << e.what() << "\n";
+        return 1;
+    }
+    return 0;
+}
+
 int main(int argc, char** argv)
 {
+    if (argc >= 4 && std::strcmp(argv[1], "--loop") == 0) return run_loop(argv[2], argv[3]);
     if (argc >= 6 && std::strcmp(argv[1], "--bench") == 0)
         return run_bench(std::atoi(argv[2]), std::atoi(argv[3]), std::atoi(argv[4]), argv[5]);
     if (argc < 3) return 2;

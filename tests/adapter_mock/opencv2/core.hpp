@@ -5,7 +5,8 @@
 #include <vector>
 namespace cv {
 enum NormTypes { NORM_L2 = 4, NORM_HAMMING = 6 };
-struct Point2f { float x = 0, y = 0; };
+struct Point2f { float x = 0, y = 0; Point2f() = default; Point2f(float a, float b) : x(a), y(b) {} };
+struct Point3f { float x = 0, y = 0, z = 0; Point3f() = default; Point3f(float a, float b, float c) : x(a), y(b), z(c) {} };
 struct KeyPoint { Point2f pt; };
 class Mat {
   public:

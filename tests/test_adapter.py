@@ -327,29 +327,34 @@ def test_adapter_end_to_end_vs_oracle(pkg, oracle, tmp_path):
 def test_adapter_resident_map_follows_a_mutation_script(pkg, oracle, tmp_path):
     """The scripted mutation sequence (associate, disassociate, steal a keypoint, fuse, remove from the middle, bundle
     adjustment of positions and key-frame poses, create_point, a compaction) replayed by the C++ driver three times:
-    per-call uploads, resident mirror fed by the data model's notifications, resident mirror that scans.  All three
-    must agree, the resident ones must never fall back to a whole-map upload, their audit must be clean, and every
-    CHECK step must equal the oracle fed the map the host dumped at that step (a freshly flattened map)."""
+    per-call uploads, resident mirror fed by the data model's notifications, resident mirror that scans -- on three
+    separately built worlds (their pointer-keyed observation maps may iterate in different orders, as two runs of the
+    reference may).  The resident ones must never fall back to a whole-map upload, their audit must be clean, and in
+    every replay every CHECK step must equal the oracle fed the map THAT host dumped at that step (a freshly
+    flattened map in its own observation order)."""
     build_driver()
     w = add_script(make_world(pkg), pkg)
     write_world(w, tmp_path / "world.bin")
     r = subprocess.run([DRIVER, str(tmp_path / "world.bin"), str(tmp_path / "out.txt")], capture_output=True, text=True)
     assert r.returncode == 0, r.stderr
-    got = parse_output(tmp_path / "out.txt")
-    assert got["modes_agree"] == 1
-    extra = got["script_extra"]
-    assert extra["full_uploads"] == 1          # attach() only: everything after it went up as deltas
-    assert extra["legacy_uploads"] == 0        # no call fell back to flattening the visited points
     assert "compactions 1" in r.stderr or "compactions 2" in r.stderr, r.stderr
-    checks = got["script"]
-    assert len(checks) == sum(1 for op in w["ops"] if op[0] == 7)
+    n_checks = sum(1 for op in w["ops"] if op[0] == 7)
+    for mode in ("hooks", "scan", "percall"):
+        checks, extra = parse_script(open(str(tmp_path / "out.txt") + "." + mode).read().split("\n"))
+        assert len(checks) == n_checks
+        if mode != "percall":
+            assert extra["full_uploads"] == 1          # attach() only: everything after it went up as deltas
+            assert extra["legacy_uploads"] == 0        # no call fell back to flattening the visited points
+        _check_script_against_oracle(w, checks, oracle, audited=mode != "percall")
 
+
+def _check_script_against_oracle(w, checks, oracle, audited):
     kfs, cam, fr = w["kfs"], w["cam"], w["frame"]
     perm = oracle.kd_build(fr["xy"])
     nkp = len(fr["xy"])
     req = w["required"]
     for step, c in enumerate(checks):
-        assert c["audit"] == 0, step
+        assert not audited or c["audit"] == 0, step
         pids = [row[0] for row in c["map"]]
         live_of = {pid: j for j, pid in enumerate(pids)}
         n = len(pids)
@@ -393,3 +398,69 @@ def test_adapter_resident_map_follows_a_mutation_script(pkg, oracle, tmp_path):
             skip_after[live_of[pid]] = 1
         assert c["track_map"] == run(kpm, skip_after, None, 0), step
     assert sum(len(c["match_key_frame"]) for c in checks) > 10
+
+
+@pytest.mark.gpu
+def test_loop_detector_helper_vs_oracle(pkg, oracle, tmp_path):
+    """racing-slam_b200/adapter/LoopDetectorGpu (compiled against the mock, sharing the matcher's context): bow_of
+    for every key frame, the L1 score of the newest key frame against all stored ones and the RANSAC model scoring
+    of verify_pnp -- word ids, doubles, counts, RANSAC's choice and the inlier mask all equal to the oracle's
+    (which is pinned on the reference's own DBoW2 and on cv2.projectPoints)."""
+    build_driver()
+    syn = pkg.synthetic
+    voc = syn.random_vocabulary(10, 3, 6)
+    n_kf, nkp = 7, 900
+    frames = [syn.vocabulary_queries(voc, nkp - 30 * k, 20 + k) for k in range(n_kf)]
+    objs, imgs, models = syn.pnp_problems(8, [300], [60])
+    path, outp = tmp_path / "loop.bin", tmp_path / "loop.txt"
+    with open(path, "wb") as f:
+        n_nodes = len(voc["desc"])
+        f.write(struct.pack("<i", n_nodes))
+        f.write(np.ascontiguousarray(voc["child_offset"], np.int32).tobytes())
+        f.write(np.ascontiguousarray(voc["child_ids"], np.int32).tobytes())
+        f.write(np.ascontiguousarray(voc["desc"], np.uint8).tobytes())
+        f.write(np.ascontiguousarray(voc["weight"], np.float64).tobytes())
+        f.write(np.ascontiguousarray(voc["word_id"], np.int32).tobytes())
+        f.write(struct.pack("<i", n_kf))
+        for d in frames:
+            f.write(struct.pack("<i", len(d)))
+            f.write(np.zeros((len(d), 2), np.float32).tobytes())
+            f.write(np.ascontiguousarray(d, np.uint8).tobytes())
+        f.write(struct.pack("<i", len(objs[0])))
+        f.write(np.ascontiguousarray(objs[0], np.float32).tobytes())
+        f.write(np.ascontiguousarray(imgs[0], np.float32).tobytes())
+        f.write(struct.pack("<i", len(models[0])))
+        f.write(np.ascontiguousarray(models[0], np.float64).tobytes())
+        f.write(np.ascontiguousarray(syn.PNP_K4, np.float64).tobytes())
+    r = subprocess.run([DRIVER, "--loop", str(path), str(outp)], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    lines = open(outp).read().split("\n")
+    i, bows, got = 0, [], {}
+    while i < len(lines) and lines[i].strip():
+        name, n = lines[i].split()
+        n = int(n)
+        if name == "empty_bow":
+            got[name] = n
+            i += 1
+            continue
+        rows = [[int(x) for x in lines[i + 1 + k].split()] for k in range(n)]
+        (bows.append(rows) if name == "bow" else got.__setitem__(name, rows))
+        i += 1 + n
+    ov = oracle.Vocabulary(voc["child_offset"], voc["child_ids"], voc["desc"], voc["weight"], voc["word_id"])
+    want = []
+    for d, b in zip(frames, bows):
+        word, w = oracle.voc_transform_each(ov, d)
+        ids, vals = oracle.voc_bow(word, w)
+        want.append((ids, vals))
+        assert [r[0] for r in b] == ids.tolist()
+        assert np.array_equal(np.array([r[1] for r in b], np.uint64), vals.view(np.uint64))     # the doubles, bit for bit
+    scores = np.array([r[0] for r in got["scores"]], np.uint64).view(np.float64)
+    assert np.array_equal(scores, np.array([oracle.voc_score_l1(*want[-1], *w) for w in want]))
+    assert scores[-1] == 1.0 and (scores[:-1] < 1.0).all()
+    ocnt = np.array([oracle.pnp_score(m, syn.PNP_K4, objs[0], imgs[0], 4.0)[0] for m in models[0]], np.int32)
+    assert [r[0] for r in got["pnp_counts"]] == ocnt.tolist()
+    best = oracle.ransac_select(ocnt, len(objs[0]))[0]
+    assert got["pnp_best"][0][0] == best and best >= 0
+    _, _, omask = oracle.pnp_score(models[0][best], syn.PNP_K4, objs[0], imgs[0], 4.0)
+    assert [r[0] for r in got["pnp_mask"]] == omask.astype(int).tolist() and got["pnp_best"][0][1] == int(omask.sum())
+    assert got["empty_bow"] == 0
