@@ -99,13 +99,8 @@ int tc_expand_pair(slamgpu_ctx* ctx, const uint8_t* dq, int nq, const uint8_t* d
     const size_t set_bytes = fp4 ? bf_tc4_expanded_bytes(1, m) : bf_tc_expanded_bytes(1, m);
     SG_TRY(ensure_device_exp(ctx, 2 * set_bytes));
     uint8_t* e = static_cast<uint8_t*>(ctx->d_exp.ptr);
-    if (fp4) {
-        SG_TRY(bf_tc4_launch_expand(ctx, dq, nullptr, 1, nq, pitch, e));
-        SG_TRY(bf_tc4_launch_expand(ctx, dt, nullptr, 1, nt, pitch, e + set_bytes));
-    } else {
-        SG_TRY(bf_tc_launch_expand(ctx, dq, nullptr, 1, nq, nq, pitch, e));
-        SG_TRY(bf_tc_launch_expand(ctx, dt, nullptr, 1, nt, nt, pitch, e + set_bytes));
-    }
+    if (fp4) SG_TRY(bf_tc4_launch_expand_pair(ctx, dq, nq, dt, nt, pitch, e));     // both sets, one launch
+    else SG_TRY(bf_tc_launch_expand_pair(ctx, dq, nq, dt, nt, pitch, e));
     *pitch_rows = pitch;
     return SLAMGPU_OK;
 }
@@ -197,7 +192,9 @@ int crosscheck_core(slamgpu_ctx* ctx, const uint8_t* dq, int nq, const uint8_t* 
 int match_descriptors_core(slamgpu_ctx* ctx, const uint8_t* dq, int nq, const uint8_t* dt, int nt, float max_dist,
                            float ratio, int32_t* d_out_train, int32_t* d_out_count)
 {
-    SG_CUDA(cudaMemsetAsync(d_out_count, 0, sizeof(int32_t), ctx->stream));
+    if (nq == 0 || nt == 0) {
+        if (d_out_count) SG_CUDA(cudaMemsetAsync(d_out_count, 0, sizeof(int32_t), ctx->stream));
+    }
     if (nq == 0) return SLAMGPU_OK;
     if (nt == 0) {   // src/MapMatcher.cpp:139-141: no matched key-frame keypoints -> no matches
         SG_CUDA(cudaMemsetAsync(d_out_train, 0xFF, sizeof(int32_t) * nq, ctx->stream));
@@ -262,7 +259,9 @@ int batch_core(slamgpu_ctx* ctx, const uint8_t* d_desc, const int32_t* d_frame_o
                const std::function<int(int, int)>* after_slice = nullptr,
                // sorted frames the pairs name, when they are few (host-buffer forms know them): only these get their
                // expanded copy built (a loop-closure query against a handful of candidates of a large resident database)
-               const std::vector<int>* frames_used = nullptr)
+               const std::vector<int>* frames_used = nullptr,
+               // a device-addressable host copy of the offsets (short calls: the kernels write results to host memory)
+               int32_t* h_offset_mirror = nullptr)
 {
     if (n_pairs == 0) return SLAMGPU_OK;
     if (max_rows == 0) {
@@ -285,17 +284,25 @@ int batch_core(slamgpu_ctx* ctx, const uint8_t* d_desc, const int32_t* d_frame_o
             SG_TRY(ensure_device_exp(ctx, bf_tc4_expanded_bytes(n_frames, max_rows)));
             e = static_cast<uint8_t*>(ctx->d_exp.ptr);
             const size_t stride = bf_tc4_expanded_bytes(1, max_rows);
-            SG_TRY(for_frame_runs(n_frames, frames_used, [&](int f0, int nf) {
-                return bf_tc4_launch_expand(ctx, d_desc, d_frame_offset + f0, nf, 0, pitch, e + f0 * stride);
-            }));
+            if (frames_used && n_pairs <= 32767) {      // few frames: one launch over the pair list itself
+                SG_TRY(bf_tc4_launch_expand_list(ctx, d_desc, d_frame_offset, d_pairs, 2 * n_pairs, pitch, e));
+            } else {
+                SG_TRY(for_frame_runs(n_frames, frames_used, [&](int f0, int nf) {
+                    return bf_tc4_launch_expand(ctx, d_desc, d_frame_offset + f0, nf, 0, pitch, e + f0 * stride);
+                }));
+            }
         } else {
             pitch = bf_tc_pitch_rows(max_rows);
             SG_TRY(ensure_device_exp(ctx, bf_tc_expanded_bytes(n_frames, max_rows)));
             e = static_cast<uint8_t*>(ctx->d_exp.ptr);
             const size_t stride = bf_tc_expanded_bytes(1, max_rows);
-            SG_TRY(for_frame_runs(n_frames, frames_used, [&](int f0, int nf) {
-                return bf_tc_launch_expand(ctx, d_desc, d_frame_offset + f0, nf, 0, max_rows, pitch, e + f0 * stride);
-            }));
+            if (frames_used && n_pairs <= 32767) {
+                SG_TRY(bf_tc_launch_expand_list(ctx, d_desc, d_frame_offset, d_pairs, 2 * n_pairs, max_rows, pitch, e));
+            } else {
+                SG_TRY(for_frame_runs(n_frames, frames_used, [&](int f0, int nf) {
+                    return bf_tc_launch_expand(ctx, d_desc, d_frame_offset + f0, nf, 0, max_rows, pitch, e + f0 * stride);
+                }));
+            }
         }
     }
     const size_t per_pair = bf_partial_elems(fin, 1, max_rows);
@@ -320,7 +327,7 @@ int batch_core(slamgpu_ctx* ctx, const uint8_t* d_desc, const int32_t* d_frame_o
         SG_TRY(bf_launch_finish_filter(ctx, fin, keys, 0, 0, d_frame_offset, pairs, np, max_rows, max_dist, ratio,
                                        out_train, d_out_count + p0));
         if (d_offset) {
-            SG_TRY(bf_launch_scan_counts(ctx, d_out_count + p0, np, d_offset + p0));
+            SG_TRY(bf_launch_scan_counts(ctx, d_out_count + p0, np, d_offset + p0, h_offset_mirror ? h_offset_mirror + p0 : nullptr));
             SG_TRY(bf_launch_compact(ctx, out_train, d_frame_offset, pairs, 0, np, max_rows, d_offset + p0,
                                      d_query_list, d_train_list, capacity));
         }
@@ -517,6 +524,21 @@ int batch_host(slamgpu_ctx* ctx, const uint8_t* desc, const uint8_t* d_desc_res,
         used.erase(std::unique(used.begin(), used.end()), used.end());
     }
     const bool few = !used.empty() && used.size() * 2 < static_cast<size_t>(n_frames);
+    if (ctx->bf_zero_copy && direct && n_pairs <= 256 && n_pairs <= slice) {
+        // A SHORT call into pinned result arrays (a loop-closure query: the newest key frame against a handful of
+        // candidates): one slice, the offsets and the two lists written by the kernels straight into host memory --
+        // no copy stream, no events, one synchronisation.
+        // (the offsets' host image shares the staging block with the pair list's upload: both are stream-ordered)
+        const int rc1 = batch_core(ctx, d_desc, d_off, n_frames, d_pairs, n_pairs, max_rows, max_dist, ratio, d_rows, d_count,
+                                   d_offset, out_query, out_train, capacity, slice, nullptr, few ? &used : nullptr, h_offset);
+        if (rc1 != SLAMGPU_OK) return rc1;
+        SG_CUDA(cudaStreamSynchronize(ctx->stream));
+        out_offset[0] = 0;
+        std::memcpy(out_offset + 1, h_offset + 1, sizeof(int32_t) * static_cast<size_t>(n_pairs));
+        *out_total = out_offset[n_pairs];
+        if (*out_total > capacity) return fail(SLAMGPU_ERR_NOMEM, "match list capacity too small; *out_total holds the size needed");
+        return SLAMGPU_OK;
+    }
     const int rc = batch_core(ctx, d_desc, d_off, n_frames, d_pairs, n_pairs, max_rows, max_dist, ratio, d_rows, d_count,
                               d_offset, d_ql, d_tl, capacity, slice, &after_slice, few ? &used : nullptr);
     if (rc != SLAMGPU_OK) {
@@ -638,8 +660,8 @@ int slamgpu_match_descriptors(slamgpu_ctx* ctx, const uint8_t* query, int nq, co
     SG_CHECK(out_query && out_train, "null output");
     PairIo io;
     SG_TRY(stage_pair(ctx, query, nq, train, nt, nq, 1, io));
-    // the per-call count is an atomicAdd target: in zero-copy mode it stays on the device (the host counts the flags)
-    SG_TRY(match_descriptors_core(ctx, io.d_q, nq, io.d_t, nt, max_dist, ratio, io.d_a, io.d_b_dev));
+    // zero-copy: the host counts the surviving rows itself, so the device count (a memset and atomics) is left out
+    SG_TRY(match_descriptors_core(ctx, io.d_q, nq, io.d_t, nt, max_dist, ratio, io.d_a, io.zero_copy ? nullptr : io.d_b_dev));
     const int32_t *h_train, *h_count;
     SG_TRY(fetch_pair(ctx, io, &h_train, &h_count));
     // marshal the per-row result into the reference's list form (ascending queryIdx, :151-161)

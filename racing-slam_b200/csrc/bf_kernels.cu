@@ -351,7 +351,7 @@ __global__ void bf_finish_filter_kernel(const FilterArgs a)
         a.out_train[static_cast<size_t>(pair) * a.max_rows + q] = -1;   // ragged batch padding
     }
     const unsigned ballot = __ballot_sync(0xFFFFFFFFu, keep);
-    if ((threadIdx.x & 31) == 0 && ballot != 0) atomicAdd(&a.out_count[pair], __popc(ballot));
+    if (a.out_count != nullptr && (threadIdx.x & 31) == 0 && ballot != 0) atomicAdd(&a.out_count[pair], __popc(ballot));
 }
 
 // cross-check: (q,t) survives iff t = argmin row q and q = argmin column t (lowest index on ties).
@@ -405,7 +405,7 @@ __global__ void bf_mutual_direct_kernel(const uint2* row_keys, int row_splits, i
 }
 
 // exclusive scan of per-pair counts (single CTA; n is at most a few hundred thousand)
-__global__ void bf_scan_counts_kernel(const int32_t* count, int n, int32_t* offset)
+__global__ void bf_scan_counts_kernel(const int32_t* count, int n, int32_t* offset, int32_t* mirror)
 {
     __shared__ int s_warp[32];
     __shared__ int s_carry;
@@ -435,12 +435,18 @@ __global__ void bf_scan_counts_kernel(const int32_t* count, int n, int32_t* offs
         __syncthreads();
         const int warp_off = warp == 0 ? 0 : s_warp[warp - 1];
         const int carry = s_carry;
-        if (i < n) offset[i] = carry + warp_off + x - v;
+        if (i < n) {
+            offset[i] = carry + warp_off + x - v;
+            if (mirror) mirror[i] = carry + warp_off + x - v;
+        }
         __syncthreads();
         if (threadIdx.x == blockDim.x - 1) s_carry = carry + warp_off + x;
         __syncthreads();
     }
-    if (threadIdx.x == 0) offset[n] = s_carry;
+    if (threadIdx.x == 0) {
+        offset[n] = s_carry;
+        if (mirror) mirror[n] = s_carry;
+    }
 }
 
 // ordered compaction: one warp per pair walks its rows 32 at a time
@@ -556,7 +562,8 @@ int bf_launch_finish_filter(slamgpu_ctx* ctx, const BfPlan& plan, const uint2* d
                             float max_dist, float ratio, int32_t* d_out_train, int32_t* d_out_count)
 {
     if (n_pairs <= 0 || max_rows <= 0) return SLAMGPU_OK;
-    SG_CUDA(cudaMemsetAsync(d_out_count, 0, sizeof(int32_t) * n_pairs, ctx->stream));
+    // d_out_count null: the caller counts the surviving rows itself (the single-pair host call does)
+    if (d_out_count) SG_CUDA(cudaMemsetAsync(d_out_count, 0, sizeof(int32_t) * n_pairs, ctx->stream));
     FilterArgs a;
     a.keys = d_keys;
     a.splits = plan.splits;
@@ -576,7 +583,7 @@ int bf_launch_finish_filter(slamgpu_ctx* ctx, const BfPlan& plan, const uint2* d
         b.keys = a.keys + static_cast<size_t>(p0) * plan.splits * max_rows;
         b.pairs = d_pairs ? d_pairs + 2 * static_cast<size_t>(p0) : nullptr;
         b.out_train = d_out_train + static_cast<size_t>(p0) * max_rows;
-        b.out_count = d_out_count + p0;
+        b.out_count = d_out_count ? d_out_count + p0 : nullptr;
         bf_finish_filter_kernel<<<dim3((rows + 255) / 256, np), 256, 0, ctx->stream>>>(b);
         ctx->launches++;
     }
@@ -609,9 +616,9 @@ int bf_launch_mutual_direct(slamgpu_ctx* ctx, const BfPlan& row_plan, const uint
     return SLAMGPU_OK;
 }
 
-int bf_launch_scan_counts(slamgpu_ctx* ctx, const int32_t* d_count, int n, int32_t* d_offset)
+int bf_launch_scan_counts(slamgpu_ctx* ctx, const int32_t* d_count, int n, int32_t* d_offset, int32_t* h_offset_mirror)
 {
-    bf_scan_counts_kernel<<<1, 1024, 0, ctx->stream>>>(d_count, n, d_offset);
+    bf_scan_counts_kernel<<<1, 1024, 0, ctx->stream>>>(d_count, n, d_offset, h_offset_mirror);
     ctx->launches++;
     SG_CUDA(cudaGetLastError());
     return SLAMGPU_OK;

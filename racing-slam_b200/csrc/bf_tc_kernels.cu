@@ -672,6 +672,9 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTc2Threads, 1) bf_t
 // contiguous bytes.  Rows past the frame's end inside its last 8-row group are zero-filled.
 struct ExpandArgs {
     const uint8_t* src;
+    const uint8_t* src2 = nullptr; // single pair: the train set, expanded as frame 1 by the same launch
+    int n_rows2 = 0;
+    const int32_t* frame_list = nullptr;   // batched: expand frame frame_list[blockIdx.y] instead of frame blockIdx.y
     const int32_t* frame_offset;   // null: one set of n_rows rows
     int n_rows;                    // single set
     int rows_per_frame_max;        // batched: upper bound of rows per frame (grid sizing)
@@ -688,13 +691,16 @@ __device__ __forceinline__ uint32_t expand4(uint32_t nibble)
 
 __global__ void __launch_bounds__(256) bf_tc_expand_kernel(const ExpandArgs a)
 {
-    const int frame = blockIdx.y;
+    const int frame = a.frame_list ? a.frame_list[blockIdx.y] : static_cast<int>(blockIdx.y);
     int n = a.n_rows;
     const uint8_t* src = a.src;
     if (a.frame_offset != nullptr) {
         const int o = a.frame_offset[frame];
         n = a.frame_offset[frame + 1] - o;
         src += static_cast<size_t>(o) * 32;
+    } else if (frame == 1) {
+        n = a.n_rows2;
+        src = a.src2;
     }
     const int group = blockIdx.x * 2 + (threadIdx.x >> 7);      // two 8-row groups per CTA
     if (group * 8 >= n) return;
@@ -733,11 +739,25 @@ BfPlan bf_tc_make_plan(const slamgpu_ctx* ctx, int nq_max, int nt_max, int64_t n
     p.tile = tm;
     p.tiles = max(1, (nq_max + tm - 1) / tm);
     // split the train range only when the query tiles alone cannot occupy every SM
-    const int64_t units = static_cast<int64_t>(p.tiles) * n_pairs;
     const int n_btiles = max(1, (nt_max + TN - 1) / TN);
-    int64_t splits = units >= slots ? 1 : (slots + units - 1) / units;
-    splits = min(splits, static_cast<int64_t>(n_btiles));
-    const int tiles_per_split = static_cast<int>((n_btiles + splits - 1) / splits);
+    // Split the train range when the query tiles alone cannot occupy every CTA pair.  A unit costs its train tiles
+    // plus about one tile's worth of fixed work (query-tile load, pipeline fill and drain), units run in waves over
+    // the resident CTA pairs: take the split count with the cheapest last wave (8000 x 8000: 2 splits = 64 units of
+    // 16 tiles in one wave, where "as many units as slots" gave 96 units of 11 tiles in two).
+    const int64_t base_units = static_cast<int64_t>(p.tiles) * n_pairs;
+    int best_tps = n_btiles;
+    int64_t best_cost = -1;
+    for (int tps = n_btiles; tps >= 1; --tps) {
+        const int s = (n_btiles + tps - 1) / tps;
+        const int64_t waves = (base_units * s + slots - 1) / slots;
+        const int64_t cost = waves * (tps + 1);
+        if (best_cost < 0 || cost < best_cost) {
+            best_cost = cost;
+            best_tps = tps;
+        }
+        if (base_units * s >= 8 * static_cast<int64_t>(slots)) break;          // many waves already: finer splits only add overhead
+    }
+    const int tiles_per_split = best_tps;
     p.t_per_split = tiles_per_split * TN;
     p.splits = max(1, (n_btiles + tiles_per_split - 1) / tiles_per_split);
     return p;
@@ -765,6 +785,48 @@ int bf_tc_launch_expand(slamgpu_ctx* ctx, const uint8_t* d_src, const int32_t* d
         bf_tc_expand_kernel<<<dim3((groups + 1) / 2, nf), 256, 0, ctx->stream>>>(b);
         ctx->launches++;
     }
+    SG_CUDA(cudaGetLastError());
+    return SLAMGPU_OK;
+}
+
+// the frames a (short) pair list names, one launch
+int bf_tc_launch_expand_list(slamgpu_ctx* ctx, const uint8_t* d_src, const int32_t* d_frame_offset, const int32_t* d_frame_list,
+                             int n_list, int max_rows, int pitch_rows, uint8_t* d_dst)
+{
+    if (n_list <= 0 || max_rows <= 0) return SLAMGPU_OK;
+    SG_CHECK(pitch_rows % TN == 0 && pitch_rows >= max_rows && n_list <= 65535, "bad expanded pitch / list too long");
+    ExpandArgs a;
+    a.src = d_src;
+    a.frame_offset = d_frame_offset;
+    a.frame_list = d_frame_list;
+    a.n_rows = 0;
+    a.rows_per_frame_max = max_rows;
+    a.frame_pitch_bytes = static_cast<long long>(pitch_rows) * kRowBytes;
+    a.dst = d_dst;
+    const int groups = (max_rows + 7) / 8;
+    bf_tc_expand_kernel<<<dim3((groups + 1) / 2, n_list), 256, 0, ctx->stream>>>(a);
+    ctx->launches++;
+    SG_CUDA(cudaGetLastError());
+    return SLAMGPU_OK;
+}
+
+// query set -> frame 0, train set -> frame 1 of d_dst, one launch
+int bf_tc_launch_expand_pair(slamgpu_ctx* ctx, const uint8_t* d_q, int nq, const uint8_t* d_t, int nt, int pitch_rows,
+                             uint8_t* d_dst)
+{
+    SG_CHECK(pitch_rows % TN == 0 && pitch_rows >= max(nq, nt), "bad expanded pitch");
+    ExpandArgs a;
+    a.src = d_q;
+    a.src2 = d_t;
+    a.n_rows2 = nt;
+    a.frame_offset = nullptr;
+    a.n_rows = nq;
+    a.rows_per_frame_max = max(nq, nt);
+    a.frame_pitch_bytes = static_cast<long long>(pitch_rows) * kRowBytes;
+    a.dst = d_dst;
+    const int groups = (max(nq, nt) + 7) / 8;
+    bf_tc_expand_kernel<<<dim3((groups + 1) / 2, 2), 256, 0, ctx->stream>>>(a);
+    ctx->launches++;
     SG_CUDA(cudaGetLastError());
     return SLAMGPU_OK;
 }

@@ -271,7 +271,8 @@ int bf_launch_mutual(slamgpu_ctx* ctx, const BfPlan& row_plan, const uint2* d_ro
 int bf_launch_mutual_direct(slamgpu_ctx* ctx, const BfPlan& row_plan, const uint2* d_row_keys, int row_stride,
                             const uint32_t* d_col_keys, int nq, float strict_max_dist, int32_t* d_idx, int32_t* d_dist);
 // Ordered compaction of out_train[pair][q] into (query, train) lists.
-int bf_launch_scan_counts(slamgpu_ctx* ctx, const int32_t* d_count, int n, int32_t* d_offset /* n+1 */);
+int bf_launch_scan_counts(slamgpu_ctx* ctx, const int32_t* d_count, int n, int32_t* d_offset /* n+1 */,
+                          int32_t* h_offset_mirror = nullptr /* n+1, device-addressable host memory */);
 int bf_launch_compact(slamgpu_ctx* ctx, const int32_t* d_out_train, const int32_t* d_frame_offset,
                       const int32_t* d_pairs, int nq_single, int n_pairs, int max_rows, const int32_t* d_offset,
                       int32_t* d_query_list, int32_t* d_train_list, int64_t capacity);
@@ -285,6 +286,10 @@ size_t bf_tc_expanded_bytes(int n_frames, int max_rows);
 BfPlan bf_tc_make_plan(const slamgpu_ctx* ctx, int nq_max, int nt_max, int64_t n_pairs);
 int bf_tc_launch_expand(slamgpu_ctx* ctx, const uint8_t* d_src, const int32_t* d_frame_offset, int n_frames, int n_rows,
                         int max_rows, int pitch_rows, uint8_t* d_dst);
+int bf_tc_launch_expand_list(slamgpu_ctx* ctx, const uint8_t* d_src, const int32_t* d_frame_offset, const int32_t* d_frame_list,
+                             int n_list, int max_rows, int pitch_rows, uint8_t* d_dst);
+int bf_tc_launch_expand_pair(slamgpu_ctx* ctx, const uint8_t* d_q, int nq, const uint8_t* d_t, int nt, int pitch_rows,
+                             uint8_t* d_dst);
 int bf_tc_launch_scan(slamgpu_ctx* ctx, const BfPlan& plan, const uint8_t* d_exp_q, int nq, const uint8_t* d_exp_t,
                       int nt, int pitch_rows, const int32_t* d_frame_offset, const int32_t* d_pairs, int n_pairs,
                       int max_rows, int d_cut, uint2* d_keys);
@@ -297,6 +302,10 @@ size_t bf_tc4_expanded_bytes(int n_frames, int max_rows);
 BfPlan bf_tc4_make_plan(const slamgpu_ctx* ctx, int nq_max, int nt_max, int64_t n_pairs);
 int bf_tc4_launch_expand(slamgpu_ctx* ctx, const uint8_t* d_src, const int32_t* d_frame_offset, int n_frames, int n_rows,
                          int pitch_rows, uint8_t* d_dst);
+int bf_tc4_launch_expand_list(slamgpu_ctx* ctx, const uint8_t* d_src, const int32_t* d_frame_offset, const int32_t* d_frame_list,
+                              int n_list, int pitch_rows, uint8_t* d_dst);
+int bf_tc4_launch_expand_pair(slamgpu_ctx* ctx, const uint8_t* d_q, int nq, const uint8_t* d_t, int nt, int pitch_rows,
+                              uint8_t* d_dst);
 int bf_tc4_launch_scan(slamgpu_ctx* ctx, const BfPlan& plan, const uint8_t* d_exp_q, int nq, const uint8_t* d_exp_t,
                        int nt, int pitch_rows, const int32_t* d_frame_offset, const int32_t* d_pairs, int n_pairs,
                        int max_rows, int d_cut, uint2* d_keys);
