@@ -42,7 +42,7 @@ ALU_PER_CLK_PER_SM = 64                # LOP3 / VIMNMX lanes per clock per SM (n
 ALU_PER_COMPARISON = 17.5
 POPC_PER_COMPARISON_CSA = 4
 NCU_SCAN_DRAM_BYTES_512_PAIRS = 7.2e6  # profiles/r01_ncu_full_prof_bf_scan_v2.txt
-NCU_TC4_DRAM_BYTES_1024_PAIRS = 56.1e6  # profiles/r01_ncu_full_bf_tc4_scan.txt (read + write; mostly the partial-key records)
+NCU_TC4_DRAM_BYTES_1024_PAIRS = 57.3e6  # profiles/r02_ncu_full_bf_tc4_scan.txt (27.9 MB read + 29.4 MB written; mostly the partial-key records)
 
 
 def parse_args():
@@ -521,12 +521,13 @@ def run_ours(args, rank, local_rank, world):
             "bound": "tensor", "achieved": tflops, "peak": peak_tf, "unit": "TFLOP/s", "frac": tflops / peak_tf,
             "traffic": NCU_TC4_DRAM_BYTES_1024_PAIRS * pairs_per_launch / 1024.0,
             "traffic_basis": "ncu --set full dram__bytes_read+write of one 1024-pair bf_tc4_scan_kernel launch "
-                             "(profiles/r01_ncu_full_bf_tc4_scan.txt), scaled to this launch's pair count",
+                             "(profiles/r02_ncu_full_bf_tc4_scan.txt: 27.9 MB read + 29.4 MB written), scaled to this launch's pair count",
             "kernel": "bf_tc4_scan_kernel", "launches": scan_launches, "avg_launch_ms": avg_ms,
             "share_of_step": scan_ms / ms_dev, "achieved_gcmp_s": achieved,
             "peak_basis": f"4 x measured dense bf16 ({peaks['bf16_tflops']:.0f} TFLOP/s burst, {peaks['source']}); algorithmic work "
                           "= 512 flop per 256-bit comparison.  The kernel also issues one constant MMA per 8 useful ones and pads "
-                          "4000 train rows to 9 tiles of 480, so its tensor-pipe time is 1.215x the algorithmic one",
+                          "4000 train rows to 9 tiles of 480, so its tensor-pipe time is 1.215x the algorithmic one (MMA-only floor of this "
+                          "instruction mix: 0.89 of the measured launch time, DESIGN.md section 4 K7b)",
             "vs_sustained_bf16_x4": tflops / (4.0 * peaks["bf16_tflops_sustained"]),
             "vs_integer_pipe_roofline": {"note": "the XOR+POPC formulation's ceilings (SURVEY 8d), for scale",
                                          "int_alu_peak_gcmp_s": int_peak, "x_int_alu": achieved / int_peak,
