@@ -775,6 +775,7 @@ def also_measurements(ctx, pkg, torch, stream, n_sm, peaks):
     out["c3_tracking_sequence_200_frames"] = bench_c3.run_sequence(ctx, pkg, 200, 8000, 1000, 3, 3, c3_cpu_arm)
     out["k7b_hit_density_sweep"] = hit_density_sweep(ctx, pkg, torch, stream, peaks)
     out["adapter_track_frame"] = adapter_track_frame(pkg)
+    out["c_abi_call_latency"] = c_abi_call_latency(pkg)
     out["n4_bag_of_words"] = bow_measurements(ctx, pkg, torch, stream, peaks)
     out["n3_pnp_scoring"] = pnp_measurements(ctx, pkg, torch, stream)
     return out
@@ -810,6 +811,49 @@ def hit_density_sweep(ctx, pkg, torch, stream, peaks):
         out.append({"shared_descriptor_share": shared, "query_rows_matched_share": float(d_cnt.sum().item()) / (len(pairs) * desc),
                     "ms_per_launch_chain": ms, "gcmp_s": g, "tensor_frac_of_4x_bf16_burst": g * 512e9 / 1e12 / (4 * peaks["bf16_tflops"])})
     return out
+
+
+def c_abi_call_latency(pkg, keep_inputs=False):
+    """The single-call paths as a C++ host sees them (tools/call_latency.cpp: plain g++ against include/slamgpu.h,
+    steady_clock around each call, copies inside, no interpreter): the same synthetic scenes as the Python legs
+    above, whose figures include numpy / ctypes marshalling."""
+    import struct
+    tool = os.path.join(ROOT, "tools", "call_latency")
+    if not os.path.exists(tool):
+        return {"unavailable": "tools/call_latency is not built (__graft_entry__.build() makes it)"}
+    syn = pkg.synthetic
+    blobs = {}
+    q, t = syn.bf_correlated(2000, 2000, 1)
+    blobs["c1_q"], blobs["c1_t"] = q, t
+    rng = np.random.default_rng(5)
+    prev = rng.integers(0, 256, (8000, 32), dtype=np.uint8)
+    blobs["c3_prev"], blobs["c3_cur"] = prev, syn.next_frame_descriptors(prev, 33)
+    cam = syn.KITTI
+    sc = syn.projection_scene(10000, 2000, 2)
+    prm = pkg.ProjParams(cam["fx"], cam["fy"], cam["cx"], cam["cy"], cam["width"], cam["height"], 20.0, MAX_DIST, 0.5,
+                         2.0, 1.25, 0)
+    blobs.update(c2_kp_xy=sc.kp_xy.astype(np.float32), c2_kp_desc=sc.kp_desc, c2_kp_matched=sc.kp_matched.astype(np.uint8),
+                 c2_pos=sc.pos.astype(np.float32), c2_normal=sc.normal.astype(np.float32), c2_range=sc.range.astype(np.float32),
+                 c2_obs_offset=sc.obs_offset.astype(np.int32), c2_obs_desc=sc.obs_desc,
+                 c2_pose=np.ascontiguousarray(sc.pose, np.float32).reshape(16), c2_skip=sc.skip.astype(np.uint8),
+                 c2_params=np.frombuffer(bytes(prm), np.uint8))
+    blobs["db_desc"] = syn.keyframe_db_fast(66, 4000, 77, 0.3)
+    blobs["db_rows"] = np.array([4000], np.int32)
+    path = os.path.join(ROOT, "gpurun_out", "call_latency_inputs.blob")
+    os.makedirs(os.path.dirname(path), exist_ok=True)
+    with open(path, "wb") as f:
+        for name, arr in blobs.items():
+            raw = np.ascontiguousarray(arr).tobytes()
+            f.write(struct.pack("<I", len(name)) + name.encode() + struct.pack("<Q", len(raw)) + raw)
+    if keep_inputs:        # for a profiler run of the tool itself (tools/run_call_latency.py --keep)
+        return {"inputs": path}
+    r = subprocess.run([tool, path, "300"], capture_output=True, text=True)
+    os.remove(path)
+    if r.returncode != 0:
+        return {"unavailable": f"call_latency failed: {r.stderr[-300:]}"}
+    res = json.loads(r.stdout)
+    res["clock"] = "std::chrono::steady_clock around each C-ABI call in a C++ host, median of 300, copies inside"
+    return res
 
 
 def adapter_track_frame(pkg):

@@ -324,6 +324,13 @@ int batch_core(slamgpu_ctx* ctx, const uint8_t* d_desc, const int32_t* d_frame_o
         } else {
             SG_TRY(bf_launch_scan(ctx, plan, d_desc, 0, d_desc, 0, d_frame_offset, pairs, np, max_rows, false, keys));
         }
+        if (h_offset_mirror) {      // short call, host-visible lists: out_train is a 2 x np x max_rows scratch here
+            SG_TRY(bf_launch_finish_compact(ctx, fin, keys, d_frame_offset, pairs, np, max_rows, max_dist, ratio, out_train,
+                                            d_out_count + p0, d_offset + p0, h_offset_mirror + p0, d_query_list,
+                                            d_train_list, capacity));
+            if (after_slice) SG_TRY((*after_slice)(p0, np));
+            continue;
+        }
         SG_TRY(bf_launch_finish_filter(ctx, fin, keys, 0, 0, d_frame_offset, pairs, np, max_rows, max_dist, ratio,
                                        out_train, d_out_count + p0));
         if (d_offset) {
@@ -427,14 +434,14 @@ int stage_pair(slamgpu_ctx* ctx, const uint8_t* q, int nq, const uint8_t* t, int
 int fetch_pair(slamgpu_ctx* ctx, const PairIo& io, const int32_t** h_a, const int32_t** h_b)
 {
     if (io.zero_copy) {
-        SG_CUDA(cudaStreamSynchronize(ctx->stream));
+        SG_TRY(wait_stream(ctx));
         *h_a = io.d_a;
         *h_b = io.d_b;
         return SLAMGPU_OK;
     }
     const size_t ob = Carver::padded(io.out_a_bytes) + io.out_b_bytes;
     if (ob) SG_CUDA(cudaMemcpyAsync(ctx->h_stage.ptr, io.d_a, ob, cudaMemcpyDeviceToHost, ctx->stream));
-    SG_CUDA(cudaStreamSynchronize(ctx->stream));
+    SG_TRY(wait_stream(ctx));
     *h_a = static_cast<const int32_t*>(ctx->h_stage.ptr);
     *h_b = reinterpret_cast<const int32_t*>(static_cast<const uint8_t*>(ctx->h_stage.ptr) + Carver::padded(io.out_a_bytes));
     return SLAMGPU_OK;
@@ -454,9 +461,12 @@ int batch_host(slamgpu_ctx* ctx, const uint8_t* desc, const uint8_t* d_desc_res,
     }
     const int slice = std::min(n_pairs, slice_for(ctx, max_rows));
     const bool resident = d_desc_res != nullptr;
+    const bool direct = capacity > 0 && is_pinned(out_query) && is_pinned(out_train);
+    // a SHORT call into pinned result arrays (a loop-closure query: the newest key frame against a handful of candidates)
+    const bool tiny = ctx->bf_zero_copy && direct && n_pairs <= 256 && n_pairs <= slice;
     const size_t b_desc = resident ? 0 : Carver::padded(n_rows * 32),
                  b_off = resident ? 0 : Carver::padded(sizeof(int32_t) * (n_frames + 1)), b_pairs = Carver::padded(sizeof(int32_t) * 2 * n_pairs);
-    const size_t b_rows = Carver::padded(sizeof(int32_t) * static_cast<size_t>(slice) * std::max(max_rows, 1)),
+    const size_t b_rows = Carver::padded(sizeof(int32_t) * static_cast<size_t>(slice) * std::max(max_rows, 1) * (tiny ? 2 : 1)),
                  b_count = Carver::padded(sizeof(int32_t) * n_pairs),
                  b_offset = Carver::padded(sizeof(int32_t) * (static_cast<size_t>(n_pairs) + 1)),
                  b_list = Carver::padded(sizeof(int32_t) * static_cast<size_t>(capacity));
@@ -474,7 +484,7 @@ int batch_host(slamgpu_ctx* ctx, const uint8_t* desc, const uint8_t* d_desc_res,
         d_off = doff;
     }
     int32_t* d_pairs = dio.take<int32_t>(2 * static_cast<size_t>(n_pairs));
-    int32_t* d_rows = dio.take<int32_t>(static_cast<size_t>(slice) * std::max(max_rows, 1));
+    int32_t* d_rows = dio.take<int32_t>(static_cast<size_t>(slice) * std::max(max_rows, 1) * (tiny ? 2 : 1));
     int32_t* d_count = dio.take<int32_t>(n_pairs);
     int32_t* d_offset = dio.take<int32_t>(static_cast<size_t>(n_pairs) + 1);
     int32_t* d_ql = dio.take<int32_t>(static_cast<size_t>(capacity));
@@ -499,7 +509,6 @@ int batch_host(slamgpu_ctx* ctx, const uint8_t* desc, const uint8_t* d_desc_res,
     const double t_call = trace ? now() : 0.0;
     uint8_t* hs = static_cast<uint8_t*>(ctx->h_stage.ptr);
     int32_t* h_offset = reinterpret_cast<int32_t*>(hs);
-    const bool direct = capacity > 0 && is_pinned(out_query) && is_pinned(out_train);
     int32_t* h_ql = direct ? out_query : reinterpret_cast<int32_t*>(hs + b_offset);
     int32_t* h_tl = direct ? out_train : reinterpret_cast<int32_t*>(hs + b_offset + b_list);
     // the uploads above may have been staged through the same pinned block: the downloads must not start
@@ -524,15 +533,14 @@ int batch_host(slamgpu_ctx* ctx, const uint8_t* desc, const uint8_t* d_desc_res,
         used.erase(std::unique(used.begin(), used.end()), used.end());
     }
     const bool few = !used.empty() && used.size() * 2 < static_cast<size_t>(n_frames);
-    if (ctx->bf_zero_copy && direct && n_pairs <= 256 && n_pairs <= slice) {
-        // A SHORT call into pinned result arrays (a loop-closure query: the newest key frame against a handful of
-        // candidates): one slice, the offsets and the two lists written by the kernels straight into host memory --
-        // no copy stream, no events, one synchronisation.
+    if (tiny) {
+        // one slice, the offsets and the two lists written by the kernels straight into host memory -- no copy
+        // stream, no events, one synchronisation.
         // (the offsets' host image shares the staging block with the pair list's upload: both are stream-ordered)
         const int rc1 = batch_core(ctx, d_desc, d_off, n_frames, d_pairs, n_pairs, max_rows, max_dist, ratio, d_rows, d_count,
                                    d_offset, out_query, out_train, capacity, slice, nullptr, few ? &used : nullptr, h_offset);
         if (rc1 != SLAMGPU_OK) return rc1;
-        SG_CUDA(cudaStreamSynchronize(ctx->stream));
+        SG_TRY(wait_stream(ctx));
         out_offset[0] = 0;
         std::memcpy(out_offset + 1, h_offset + 1, sizeof(int32_t) * static_cast<size_t>(n_pairs));
         *out_total = out_offset[n_pairs];

@@ -295,11 +295,45 @@ __device__ __forceinline__ uint2 merge_partials(const uint2* keys, int splits, s
     return make_uint2(m0, m1);
 }
 
-__global__ void bf_finish_raw_kernel(const uint2* keys, int splits, int max_rows, int nq, int32_t* idx, int32_t* dist)
+// The finish kernels run as CTAs of (kFinishThreads / G rows) x (G split groups): thread (x, y) merges the partials
+// y, y + G, ... of its row, the G results meet in shared memory and the thread with y == 0 holds the row's merged
+// top-2.  One thread per row walking all the splits is a chain of dependent L2 round trips: a single 2000 x 2000
+// pair has 63 splits, and its finish kernel took longer (11.7 us) than its scan (9.2 us).  G is chosen at launch
+// (finish_groups); every thread of the CTA must call this (it synchronises).
+constexpr int kFinishThreads = 256;
+
+__device__ __forceinline__ void merge_key(uint32_t& m0, uint32_t& m1, const uint2 p)
 {
+    const uint32_t hi = max(p.x, m0);
+    m0 = min(p.x, m0);
+    m1 = min(m1, hi);
+    m1 = min(m1, p.y);   // p.y >= p.x, so it can only compete for second place
+}
+
+__device__ __forceinline__ uint2 merge_partials_2d(const uint2* keys, int splits, size_t stride, bool active, uint2* s_part)
+{
+    uint32_t m0 = kKeyNone, m1 = kKeyNone;
+    if (active) {
+#pragma unroll 4
+        for (int s = threadIdx.y; s < splits; s += blockDim.y) merge_key(m0, m1, keys[s * stride]);
+    }
+    if (blockDim.y == 1) return make_uint2(m0, m1);
+    s_part[threadIdx.y * blockDim.x + threadIdx.x] = make_uint2(m0, m1);
+    __syncthreads();
+    if (threadIdx.y == 0) {
+        for (int g = 1; g < static_cast<int>(blockDim.y); ++g) merge_key(m0, m1, s_part[g * blockDim.x + threadIdx.x]);
+    }
+    __syncthreads();                                          // s_part may be reused by a second merge
+    return make_uint2(m0, m1);
+}
+
+__global__ void __launch_bounds__(kFinishThreads) bf_finish_raw_kernel(const uint2* keys, int splits, int max_rows, int nq,
+                                                                        int32_t* idx, int32_t* dist)
+{
+    __shared__ uint2 s_part[kFinishThreads];
     const int q = blockIdx.x * blockDim.x + threadIdx.x;
-    if (q >= nq) return;
-    const uint2 m = merge_partials(keys + q, splits, max_rows);
+    const uint2 m = merge_partials_2d(keys + q, splits, max_rows, q < nq, s_part);
+    if (q >= nq || threadIdx.y != 0) return;
     int2 i, d;
     i.x = m.x == kKeyNone ? -1 : static_cast<int>(m.x & kIdxMask);
     d.x = m.x == kKeyNone ? -1 : static_cast<int>(m.x >> kIdxBits);
@@ -322,8 +356,9 @@ struct FilterArgs {
 
 // src/MapMatcher.cpp:151-161: drop if d0 > max_dist (float, non-strict) or, with k = 2,
 // d0 > ratio * d1 (float multiply, no contraction possible: the product feeds a compare).
-__global__ void bf_finish_filter_kernel(const FilterArgs a)
+__global__ void __launch_bounds__(kFinishThreads) bf_finish_filter_kernel(const FilterArgs a)
 {
+    __shared__ uint2 s_part[kFinishThreads];
     const int pair = blockIdx.y;
     int nq = a.nq, nt = a.nt;
     if (a.pairs != nullptr) {
@@ -332,11 +367,12 @@ __global__ void bf_finish_filter_kernel(const FilterArgs a)
         nt = a.frame_offset[ft + 1] - a.frame_offset[ft];
     }
     const int q = blockIdx.x * blockDim.x + threadIdx.x;
+    const uint2 m = merge_partials_2d(a.keys + static_cast<size_t>(pair) * a.splits * a.max_rows + q, a.splits, a.max_rows,
+                                      q < nq, s_part);
+    if (threadIdx.y != 0) return;                       // whole warps: blockDim.x is a multiple of 32
     bool keep = false;
     int train = -1;
     if (q < nq) {
-        const uint2 m = merge_partials(a.keys + static_cast<size_t>(pair) * a.splits * a.max_rows + q, a.splits,
-                                       a.max_rows);
         if (m.x != kKeyNone) {
             const float d0 = static_cast<float>(m.x >> kIdxBits);
             keep = !(d0 > a.max_dist);
@@ -361,19 +397,22 @@ __global__ void bf_mutual_kernel(const uint2* row_keys, int row_splits, int row_
                                  int col_splits, int col_stride, int nq, float strict_max_dist, int32_t* idx,
                                  int32_t* dist)
 {
+    __shared__ uint2 s_part[kFinishThreads];
+    __shared__ int s_t[kFinishThreads];
     const int q = blockIdx.x * blockDim.x + threadIdx.x;
-    if (q >= nq) return;
-    const uint2 m = merge_partials(row_keys + q, row_splits, row_stride);
+    const uint2 m = merge_partials_2d(row_keys + q, row_splits, row_stride, q < nq, s_part);
+    // the row's nearest train row, handed to the row's other threads for the column merge
+    if (threadIdx.y == 0) s_t[threadIdx.x] = (q < nq && m.x != kKeyNone) ? static_cast<int>(m.x & kIdxMask) : -1;
+    __syncthreads();
+    const int t = s_t[threadIdx.x];
+    const uint2 c = merge_partials_2d(col_keys + max(t, 0), col_splits, col_stride, t >= 0, s_part);
+    if (q >= nq || threadIdx.y != 0) return;
     int oi = -1, od = -1;
-    if (m.x != kKeyNone) {
-        const int t = static_cast<int>(m.x & kIdxMask);
-        const uint2 c = merge_partials(col_keys + t, col_splits, col_stride);
-        if (c.x != kKeyNone && static_cast<int>(c.x & kIdxMask) == q) {
-            const int d = static_cast<int>(m.x >> kIdxBits);
-            if (strict_max_dist < 0.0f || static_cast<float>(d) < strict_max_dist) {
-                oi = t;
-                od = d;
-            }
+    if (t >= 0 && c.x != kKeyNone && static_cast<int>(c.x & kIdxMask) == q) {
+        const int d = static_cast<int>(m.x >> kIdxBits);
+        if (strict_max_dist < 0.0f || static_cast<float>(d) < strict_max_dist) {
+            oi = t;
+            od = d;
         }
     }
     idx[q] = oi;
@@ -385,9 +424,10 @@ __global__ void bf_mutual_direct_kernel(const uint2* row_keys, int row_splits, i
                                         const uint32_t* col_keys, int nq, float strict_max_dist, int32_t* idx,
                                         int32_t* dist)
 {
+    __shared__ uint2 s_part[kFinishThreads];
     const int q = blockIdx.x * blockDim.x + threadIdx.x;
-    if (q >= nq) return;
-    const uint2 m = merge_partials(row_keys + q, row_splits, row_stride);
+    const uint2 m = merge_partials_2d(row_keys + q, row_splits, row_stride, q < nq, s_part);
+    if (q >= nq || threadIdx.y != 0) return;
     int oi = -1, od = -1;
     if (m.x != kKeyNone) {
         const int t = static_cast<int>(m.x & kIdxMask);
@@ -479,7 +519,141 @@ __global__ void bf_compact_kernel(const int32_t* out_train, const int32_t* frame
     }
 }
 
+// ---- a short batch (a loop-closure query: at most a few hundred pairs), results to host memory ----------------
+// The general form above is finish -> exclusive scan of the counts (one CTA) -> ordered compaction (one warp per
+// pair, 125 dependent 32-row steps for a 4000-row frame): right for tens of thousands of pairs, slow for five.
+// Here one CTA owns a pair: it filters all of the pair's rows and compacts them into the pair's own block of a
+// device scratch (block-wide ballot scan, 1024 rows per step); a second launch gives every pair its offset (the
+// sum of the counts before it: n_pairs <= 1024 values) and moves the block into the caller's lists.
+constexpr int kFcThreads = 1024;
+
+__global__ void __launch_bounds__(kFcThreads) bf_finish_compact_kernel(const FilterArgs a, int32_t* loc_q, int32_t* loc_t)
+{
+    __shared__ int s_warp[32];
+    __shared__ int s_base;
+    const int pair = blockIdx.x;
+    const int fq = a.pairs[2 * pair], ft = a.pairs[2 * pair + 1];
+    const int nq = a.frame_offset[fq + 1] - a.frame_offset[fq];
+    const int nt = a.frame_offset[ft + 1] - a.frame_offset[ft];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (threadIdx.x == 0) s_base = 0;
+    __syncthreads();
+    int32_t* lq = loc_q + static_cast<size_t>(pair) * a.max_rows;
+    int32_t* lt = loc_t + static_cast<size_t>(pair) * a.max_rows;
+    const uint2* keys = a.keys + static_cast<size_t>(pair) * a.splits * a.max_rows;
+    for (int base = 0; base < nq; base += kFcThreads) {
+        const int q = base + threadIdx.x;
+        bool keep = false;
+        int train = -1;
+        if (q < nq) {                                         // the same tests as bf_finish_filter_kernel
+            const uint2 m = merge_partials(keys + q, a.splits, a.max_rows);
+            if (m.x != kKeyNone) {
+                const float d0 = static_cast<float>(m.x >> kIdxBits);
+                keep = !(d0 > a.max_dist);
+                if (keep && nt >= 2 && m.y != kKeyNone) {
+                    const float d1 = static_cast<float>(m.y >> kIdxBits);
+                    keep = !(d0 > __fmul_rn(a.ratio, d1));
+                }
+                if (keep) train = static_cast<int>(m.x & kIdxMask);
+            }
+        }
+        const unsigned ballot = __ballot_sync(0xFFFFFFFFu, keep);
+        if (lane == 0) s_warp[warp] = __popc(ballot);
+        __syncthreads();
+        if (warp == 0) {
+            int w = s_warp[lane];
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const int y = __shfl_up_sync(0xFFFFFFFFu, w, o);
+                if (lane >= o) w += y;
+            }
+            s_warp[lane] = w;                                 // inclusive scan of the warps' counts
+        }
+        __syncthreads();
+        const int at = s_base + (warp ? s_warp[warp - 1] : 0) + __popc(ballot & ((1u << lane) - 1u));
+        const int total = s_warp[31];
+        if (keep) {
+            lq[at] = q;
+            lt[at] = train;
+        }
+        __syncthreads();
+        if (threadIdx.x == 0) s_base += total;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) a.out_count[pair] = s_base;
+}
+
+__global__ void __launch_bounds__(256) bf_gather_lists_kernel(const int32_t* count, int n_pairs, int max_rows,
+                                                              const int32_t* loc_q, const int32_t* loc_t, int32_t* offset,
+                                                              int32_t* mirror, int32_t* query_list, int32_t* train_list,
+                                                              long long capacity)
+{
+    __shared__ int s_part[8];
+    __shared__ int s_off;
+    const int pair = blockIdx.x;
+    int v = 0;
+    for (int i = threadIdx.x; i < pair; i += 256) v += count[i];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xFFFFFFFFu, v, o);
+    if ((threadIdx.x & 31) == 0) s_part[threadIdx.x >> 5] = v;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        int off = 0;
+        for (int w = 0; w < 8; ++w) off += s_part[w];
+        s_off = off;
+    }
+    __syncthreads();
+    const int off = s_off, n = count[pair];
+    if (threadIdx.x == 0) {
+        offset[pair] = off;
+        if (mirror) mirror[pair] = off;
+        if (pair == n_pairs - 1) {
+            offset[n_pairs] = off + n;
+            if (mirror) mirror[n_pairs] = off + n;
+        }
+    }
+    const int32_t* lq = loc_q + static_cast<size_t>(pair) * max_rows;
+    const int32_t* lt = loc_t + static_cast<size_t>(pair) * max_rows;
+    for (int i = threadIdx.x; i < n; i += 256) {
+        const long long p = static_cast<long long>(off) + i;
+        if (p < capacity) {       // an undersized list is reported by the host from the offsets
+            query_list[p] = lq[i];
+            train_list[p] = lt[i];
+        }
+    }
+}
+
 } // namespace
+
+int bf_launch_finish_compact(slamgpu_ctx* ctx, const BfPlan& plan, const uint2* d_keys, const int32_t* d_frame_offset,
+                             const int32_t* d_pairs, int n_pairs, int max_rows, float max_dist, float ratio,
+                             int32_t* d_local /* 2 x n_pairs x max_rows */, int32_t* d_count, int32_t* d_offset,
+                             int32_t* h_offset_mirror, int32_t* query_list, int32_t* train_list, int64_t capacity)
+{
+    if (n_pairs <= 0 || max_rows <= 0) return SLAMGPU_OK;
+    SG_CHECK(n_pairs <= 65535 && d_pairs != nullptr, "finish_compact: short pair lists only");
+    FilterArgs a;
+    a.keys = d_keys;
+    a.splits = plan.splits;
+    a.max_rows = max_rows;
+    a.nq = 0;
+    a.nt = 0;
+    a.frame_offset = d_frame_offset;
+    a.pairs = d_pairs;
+    a.max_dist = max_dist;
+    a.ratio = ratio;
+    a.out_train = nullptr;
+    a.out_count = d_count;
+    int32_t* loc_q = d_local;
+    int32_t* loc_t = d_local + static_cast<size_t>(n_pairs) * max_rows;
+    bf_finish_compact_kernel<<<n_pairs, kFcThreads, 0, ctx->stream>>>(a, loc_q, loc_t);
+    bf_gather_lists_kernel<<<n_pairs, 256, 0, ctx->stream>>>(d_count, n_pairs, max_rows, loc_q, loc_t, d_offset,
+                                                             h_offset_mirror, query_list, train_list,
+                                                             static_cast<long long>(capacity));
+    ctx->launches += 2;
+    SG_CUDA(cudaGetLastError());
+    return SLAMGPU_OK;
+}
 
 BfPlan bf_make_plan(int n_sm, int nq_max, int nt_max, int64_t n_pairs)
 {
@@ -504,6 +678,13 @@ BfPlan bf_make_plan(int n_sm, int nq_max, int nt_max, int64_t n_pairs)
 size_t bf_partial_elems(const BfPlan& p, int64_t n_pairs, int max_rows)
 {
     return static_cast<size_t>(n_pairs) * p.splits * max_rows;
+}
+
+// CTA shape of the finish kernels: (rows, split groups) with about four partials per thread, at most 8 groups
+static dim3 finish_block(int splits)
+{
+    const int g = splits <= 4 ? 1 : splits <= 8 ? 2 : splits <= 16 ? 4 : 8;
+    return dim3(kFinishThreads / g, g);
 }
 
 int bf_launch_scan(slamgpu_ctx* ctx, const BfPlan& plan, const uint8_t* d_query, int nq, const uint8_t* d_train,
@@ -551,7 +732,8 @@ int bf_launch_finish_raw(slamgpu_ctx* ctx, const BfPlan& plan, const uint2* d_ke
 {
     (void)nt;
     if (nq <= 0) return SLAMGPU_OK;
-    bf_finish_raw_kernel<<<(nq + 255) / 256, 256, 0, ctx->stream>>>(d_keys, plan.splits, max_rows, nq, d_idx, d_dist);
+    const dim3 blk = finish_block(plan.splits);
+    bf_finish_raw_kernel<<<(nq + blk.x - 1) / blk.x, blk, 0, ctx->stream>>>(d_keys, plan.splits, max_rows, nq, d_idx, d_dist);
     ctx->launches++;
     SG_CUDA(cudaGetLastError());
     return SLAMGPU_OK;
@@ -584,7 +766,8 @@ int bf_launch_finish_filter(slamgpu_ctx* ctx, const BfPlan& plan, const uint2* d
         b.pairs = d_pairs ? d_pairs + 2 * static_cast<size_t>(p0) : nullptr;
         b.out_train = d_out_train + static_cast<size_t>(p0) * max_rows;
         b.out_count = d_out_count ? d_out_count + p0 : nullptr;
-        bf_finish_filter_kernel<<<dim3((rows + 255) / 256, np), 256, 0, ctx->stream>>>(b);
+        const dim3 blk = finish_block(plan.splits);
+        bf_finish_filter_kernel<<<dim3((rows + blk.x - 1) / blk.x, np), blk, 0, ctx->stream>>>(b);
         ctx->launches++;
     }
     SG_CUDA(cudaGetLastError());
@@ -597,9 +780,10 @@ int bf_launch_mutual(slamgpu_ctx* ctx, const BfPlan& row_plan, const uint2* d_ro
 {
     (void)nt;
     if (nq <= 0) return SLAMGPU_OK;
-    bf_mutual_kernel<<<(nq + 255) / 256, 256, 0, ctx->stream>>>(d_row_keys, row_plan.splits, row_stride, d_col_keys,
-                                                                 col_plan.splits, col_stride, nq, strict_max_dist,
-                                                                 d_idx, d_dist);
+    const dim3 blk = finish_block(std::max(row_plan.splits, col_plan.splits));
+    bf_mutual_kernel<<<(nq + blk.x - 1) / blk.x, blk, 0, ctx->stream>>>(d_row_keys, row_plan.splits, row_stride, d_col_keys,
+                                                                       col_plan.splits, col_stride, nq, strict_max_dist,
+                                                                       d_idx, d_dist);
     ctx->launches++;
     SG_CUDA(cudaGetLastError());
     return SLAMGPU_OK;
@@ -609,8 +793,9 @@ int bf_launch_mutual_direct(slamgpu_ctx* ctx, const BfPlan& row_plan, const uint
                             const uint32_t* d_col_keys, int nq, float strict_max_dist, int32_t* d_idx, int32_t* d_dist)
 {
     if (nq <= 0) return SLAMGPU_OK;
-    bf_mutual_direct_kernel<<<(nq + 255) / 256, 256, 0, ctx->stream>>>(d_row_keys, row_plan.splits, row_stride,
-                                                                        d_col_keys, nq, strict_max_dist, d_idx, d_dist);
+    const dim3 blk = finish_block(row_plan.splits);
+    bf_mutual_direct_kernel<<<(nq + blk.x - 1) / blk.x, blk, 0, ctx->stream>>>(d_row_keys, row_plan.splits, row_stride,
+                                                                              d_col_keys, nq, strict_max_dist, d_idx, d_dist);
     ctx->launches++;
     SG_CUDA(cudaGetLastError());
     return SLAMGPU_OK;

@@ -273,7 +273,7 @@ int match_projection_impl(slamgpu_ctx* ctx, const int* frame_ids, int n_frames, 
     const size_t down_bytes = out_bytes + dbg_bytes;
     if (down_bytes && !zero_copy)
         SG_CUDA(cudaMemcpyAsync(h_out, d_out_point, down_bytes, cudaMemcpyDeviceToHost, ctx->stream));
-    SG_CUDA(cudaStreamSynchronize(ctx->stream));
+    SG_TRY(wait_stream(ctx));
     const uint8_t* hb = h_out;
     const size_t o_pad = Carver::padded(sizeof(int32_t) * total_kp);
     if (speculative) {
@@ -328,27 +328,38 @@ size_t grid_image_bytes(size_t n, size_t n_cells)
 {
     return Carver::padded((n_cells + 1) * sizeof(int32_t)) + Carver::padded(n * sizeof(int4));
 }
-void build_grid_image(const float* xy, size_t n, float gx0, float gy0, float inv_cell, int gw, int gh, uint8_t* image)
+// floor() for the cell index: |v| is far below 2^31 here (the grid has at most 2^20 cells).  std::floor without
+// -msse4.1 is a libm call, and two of them per keypoint made this the largest item of slamgpu_frame_upload (85 us
+// for 8000 keypoints).
+static inline int floor_to_int(float v)
+{
+    const int i = static_cast<int>(v);
+    return v < static_cast<float>(i) ? i - 1 : i;
+}
+
+void build_grid_image(const float* xy, size_t n, float gx0, float gy0, float inv_cell, int gw, int gh, uint8_t* image,
+                      std::vector<int32_t>& scratch)
 {
     const size_t n_cells = static_cast<size_t>(gw) * gh;
     Carver hv(image);
     int32_t* h_cstart = hv.take<int32_t>(n_cells + 1);
     int4* h_crec = hv.take<int4>(n);
     std::memset(h_cstart, 0, (n_cells + 1) * sizeof(int32_t));
-    auto cell_of = [&](float x, float y) {        // the same expression as build_kd_image / proj_kernels.cu: grid_cell
-        int cxi = static_cast<int>(std::floor((x - gx0) * inv_cell));
-        int cyi = static_cast<int>(std::floor((y - gy0) * inv_cell));
+    scratch.resize(n + n_cells);                        // [cell of keypoint k][write cursor of cell c]
+    int32_t* cell = scratch.data();
+    int32_t* cursor = scratch.data() + n;
+    for (size_t k = 0; k < n; ++k) {                    // the same expression as build_kd_image / proj_kernels.cu: grid_cell
+        int cxi = floor_to_int((xy[2 * k] - gx0) * inv_cell);
+        int cyi = floor_to_int((xy[2 * k + 1] - gy0) * inv_cell);
         cxi = std::min(std::max(cxi, 0), gw - 1);
         cyi = std::min(std::max(cyi, 0), gh - 1);
-        return static_cast<size_t>(cyi) * gw + cxi;
-    };
-    std::vector<int32_t> cell(n);
-    for (size_t k = 0; k < n; ++k) {
-        cell[k] = static_cast<int32_t>(cell_of(xy[2 * k], xy[2 * k + 1]));
+        cell[k] = cyi * gw + cxi;
         h_cstart[cell[k] + 1]++;
     }
-    for (size_t c = 0; c < n_cells; ++c) h_cstart[c + 1] += h_cstart[c];
-    std::vector<int32_t> cursor(h_cstart, h_cstart + n_cells);
+    for (size_t c = 0; c < n_cells; ++c) {
+        cursor[c] = h_cstart[c];
+        h_cstart[c + 1] += h_cstart[c];
+    }
     for (size_t k = 0; k < n; ++k) {
         int32_t xb, yb;
         std::memcpy(&xb, &xy[2 * k], 4);
@@ -379,8 +390,8 @@ void build_kd_image(FrameKdPending& k)
     // same float expression (proj_kernels.cu: grid_cell), and both are monotone in the coordinate
     std::memset(h_cstart, 0, (n_cells + 1) * sizeof(int32_t));
     auto cell_of = [&](float x, float y) {
-        int cxi = static_cast<int>(std::floor((x - k.gx0) * k.inv_cell));
-        int cyi = static_cast<int>(std::floor((y - k.gy0) * k.inv_cell));
+        int cxi = floor_to_int((x - k.gx0) * k.inv_cell);
+        int cyi = floor_to_int((y - k.gy0) * k.inv_cell);
         cxi = std::min(std::max(cxi, 0), k.gw - 1);
         cyi = std::min(std::max(cyi, 0), k.gh - 1);
         return static_cast<size_t>(cyi) * k.gw + cxi;
@@ -433,7 +444,7 @@ int finalize_frame(slamgpu_ctx* ctx, FrameDev& f)
         SG_CUDA(cudaStreamSynchronize(ctx->stream));            // staging is reused
         std::memcpy(ctx->h_stage.ptr, f.pending->image.data(), f.kd_image_bytes);
         SG_CUDA(cudaMemcpyAsync(f.kd_image, ctx->h_stage.ptr, f.kd_image_bytes, cudaMemcpyHostToDevice, ctx->stream));
-        SG_CUDA(cudaStreamSynchronize(ctx->stream));
+        SG_TRY(wait_stream(ctx));
     }
     f.pending.reset();
     return SLAMGPU_OK;
@@ -575,11 +586,21 @@ int slamgpu_frame_upload(slamgpu_ctx* ctx, int frame_id, int nkp, const float* x
             std::memset(h_matched, 0, n);
         }
         std::memcpy(h_xy, xy, n * sizeof(float2));
-        build_grid_image(xy, n, f.gx0, f.gy0, f.inv_cell, f.gw, f.gh, static_cast<uint8_t*>(ctx->h_stage.ptr) + hv.off);
-        SG_CUDA(cudaMemcpyAsync(f.blob, ctx->h_stage.ptr, now_bytes, cudaMemcpyHostToDevice, ctx->stream));
+        // the tree-free grid: one device launch behind the upload for frames of ordinary size, else a host counting sort
+        const bool grid_on_device = ctx->grid_on_device && n <= (size_t(1) << 16) && n_cells * sizeof(int) <= (size_t(200) << 10);
+        if (!grid_on_device)
+            build_grid_image(xy, n, f.gx0, f.gy0, f.inv_cell, f.gw, f.gh, static_cast<uint8_t*>(ctx->h_stage.ptr) + hv.off, ctx->grid_scratch);
+        SG_CUDA(cudaMemcpyAsync(f.blob, ctx->h_stage.ptr, grid_on_device ? now_bytes - b_grid : now_bytes, cudaMemcpyHostToDevice,
+                                ctx->stream));
+        if (grid_on_device) {
+            bool built = false;
+            SG_TRY(proj_launch_grid_build(ctx, f.xy, nkp, f.gx0, f.gy0, f.inv_cell, f.gw, f.gh, f.cell_start_spec, f.cell_rec_spec,
+                                          &built));
+            SG_CHECK(built, "grid build refused a frame it was sized for");
+        }
         SG_CUDA(cudaMemsetAsync(f.proposals, 0xFF, n * sizeof(unsigned long long), ctx->stream));
         // the staging buffer is reused by the next call: wait for the copy out of it
-        SG_CUDA(cudaStreamSynchronize(ctx->stream));
+        SG_TRY(wait_stream(ctx));
 
         // The KD-tree and everything ordered by it.  With the caller's permutation (or SLAMGPU_KD_ASYNC=0) it is
         // built here; otherwise on a host thread that the first call needing the tree joins, so that the build
@@ -818,7 +839,7 @@ int slamgpu_points_append(slamgpu_ctx* ctx, int set_id, int n_new, const float* 
         SG_TRY(proj_launch_point_stats(ctx, p.pos + 3 * n0, n_new, p.obs_offset + n0, d_center - 3 * o0,
                                        p.normal + 3 * n0, p.range + 2 * n0));
     }
-    SG_CUDA(cudaStreamSynchronize(ctx->stream));
+    SG_TRY(wait_stream(ctx));
     p.n += n_new;
     p.n_obs += o_new;
     return SLAMGPU_OK;
@@ -923,7 +944,7 @@ int slamgpu_track_match(slamgpu_ctx* ctx, int frame_id, int set_id, const float*
     const size_t b_m = Carver::padded(sizeof(int32_t) * n_matched), b_k = Carver::padded(sizeof(int32_t) * n_kf);
     const size_t b_out = Carver::padded(sizeof(int32_t) * (4 * nkp + 1));     // + the tie counter of a speculative call
     SG_TRY(ensure_device_io(ctx, b_m + b_k + b_out + Carver::padded(nkp) + 256));
-    SG_TRY(ensure_host_stage(ctx, std::max(b_m + b_k, b_out) + 256));
+    SG_TRY(ensure_host_stage(ctx, b_m + b_k + b_out + 256));
     Carver dio(ctx->d_io.ptr), hio(ctx->h_stage.ptr);
     int32_t* d_m = dio.take<int32_t>(n_matched);
     int32_t* d_k = dio.take<int32_t>(n_kf);
@@ -932,6 +953,11 @@ int slamgpu_track_match(slamgpu_ctx* ctx, int frame_id, int set_id, const float*
     uint8_t* d_flags_backup = dio.take<uint8_t>(nkp);
     int32_t* h_m = hio.take<int32_t>(n_matched);
     int32_t* h_k = hio.take<int32_t>(n_kf);
+    int32_t* h_out = hio.take<int32_t>(4 * nkp + 1);       // the results' host image, behind the uploaded lists
+    // ZERO COPY for the results of a frame of ordinary size: the two emit kernels write the four arrays (and the
+    // tie count) straight into the pinned image -- no download to queue behind the kernels
+    const bool zero_copy = ctx->proj_zero_copy && nkp > 0 && b_out <= (size_t(1) << 20);
+    int32_t* k_out = zero_copy ? h_out : d_out;            // where the kernels write
     if (n_matched) std::memcpy(h_m, matched_points, sizeof(int32_t) * n_matched);
     if (n_kf) std::memcpy(h_k, kf_points, sizeof(int32_t) * n_kf);
     if (b_m + b_k) SG_CUDA(cudaMemcpyAsync(ctx->d_io.ptr, ctx->h_stage.ptr, b_m + b_k, cudaMemcpyHostToDevice, ctx->stream));
@@ -946,13 +972,14 @@ int slamgpu_track_match(slamgpu_ctx* ctx, int frame_id, int set_id, const float*
         // case the speculation has to be repeated with the tree
         SG_CUDA(cudaMemsetAsync(d_ties, 0, sizeof(unsigned int), ctx->stream));
         if (nkp) SG_CUDA(cudaMemcpyAsync(d_flags_backup, fd.matched, nkp, cudaMemcpyDeviceToDevice, ctx->stream));
+        if (zero_copy) fa.ties_out = reinterpret_cast<unsigned int*>(h_out + 4 * nkp);
     }
-    SG_TRY(proj_launch_track(ctx, common, fa, ps.pt_matched, fd.matched, d_m, n_matched, d_k, n_kf, d_out));
-    if (nkp) SG_CUDA(cudaMemcpyAsync(ctx->h_stage.ptr, d_out, sizeof(int32_t) * (4 * nkp + 1), cudaMemcpyDeviceToHost, ctx->stream));
-    SG_CUDA(cudaStreamSynchronize(ctx->stream));
+    SG_TRY(proj_launch_track(ctx, common, fa, ps.pt_matched, fd.matched, d_m, n_matched, d_k, n_kf, k_out));
+    if (nkp && !zero_copy) SG_CUDA(cudaMemcpyAsync(h_out, d_out, sizeof(int32_t) * (4 * nkp + 1), cudaMemcpyDeviceToHost, ctx->stream));
+    SG_TRY(wait_stream(ctx));
     if (speculative && nkp) {
         unsigned int ties = 0;
-        std::memcpy(&ties, static_cast<const int32_t*>(ctx->h_stage.ptr) + 4 * nkp, sizeof(ties));
+        std::memcpy(&ties, h_out + 4 * nkp, sizeof(ties));
         ctx->spec_calls++;
         if (ties == 0 && ctx->spec_tie_streak > 0) ctx->spec_tie_streak--;
         if (ties != 0) {      // a tie at some point's minimum: the KD visit order decides; wait for the tree, repeat
@@ -961,13 +988,13 @@ int slamgpu_track_match(slamgpu_ctx* ctx, int frame_id, int set_id, const float*
             SG_TRY(finalize_frame(ctx, f_it->second));
             SG_CUDA(cudaMemcpyAsync(fd.matched, d_flags_backup, nkp, cudaMemcpyDeviceToDevice, ctx->stream));
             fill_frame(fa, fd, pose_colmajor16, *params);
-            SG_TRY(proj_launch_track(ctx, common, fa, ps.pt_matched, fd.matched, d_m, n_matched, d_k, n_kf, d_out));
-            SG_CUDA(cudaMemcpyAsync(ctx->h_stage.ptr, d_out, sizeof(int32_t) * 4 * nkp, cudaMemcpyDeviceToHost, ctx->stream));
-            SG_CUDA(cudaStreamSynchronize(ctx->stream));
+            SG_TRY(proj_launch_track(ctx, common, fa, ps.pt_matched, fd.matched, d_m, n_matched, d_k, n_kf, k_out));
+            if (!zero_copy) SG_CUDA(cudaMemcpyAsync(h_out, d_out, sizeof(int32_t) * 4 * nkp, cudaMemcpyDeviceToHost, ctx->stream));
+            SG_TRY(wait_stream(ctx));
         }
     }
     if (nkp) {
-        const int32_t* h = static_cast<const int32_t*>(ctx->h_stage.ptr);
+        const int32_t* h = h_out;
         std::memcpy(out_kf_point, h, sizeof(int32_t) * nkp);
         std::memcpy(out_kf_dist, h + nkp, sizeof(int32_t) * nkp);
         std::memcpy(out_map_point, h + 2 * nkp, sizeof(int32_t) * nkp);

@@ -528,13 +528,11 @@ __device__ __forceinline__ void group_search(const ProjFrameArgs& f, const ProjC
 }
 
 template <int LANES, bool QUEUE>
-__global__ void __launch_bounds__(kGroupThreads) proj_match_group_kernel(const ProjKernelArgs a)
+__device__ __forceinline__ void proj_match_group_body(const ProjKernelArgs& a, const ProjFrameArgs& f,
+                                                      uint4 (*s_obs)[2 * kObsStaged], int2 (*s_queue)[2 * LANES])
 {
     constexpr int GROUPS = kGroupThreads / LANES;
     constexpr int STAGE_REGS = (2 * kObsStaged + LANES - 1) / LANES;
-    __shared__ uint4 s_obs[GROUPS][2 * kObsStaged];
-    __shared__ int2 s_queue[QUEUE ? GROUPS : 1][2 * LANES];
-    const ProjFrameArgs& f = a.frames ? a.frames[blockIdx.y] : a.inline_frame;
     const ProjCommonArgs& c = a.c;
     const int lane = threadIdx.x % LANES;
     const int grp = threadIdx.x / LANES;
@@ -607,6 +605,19 @@ __global__ void __launch_bounds__(kGroupThreads) proj_match_group_kernel(const P
     group_search<LANES, QUEUE>(f, c, lane, grp, gmask, u, w, v, dbg_row, o_begin, o_end, n_staged, cx0, cx1, cy0, n_rows,
                                rb, re, stage, s_obs, s_queue);
 }
+
+template <int LANES, bool QUEUE>
+__global__ void __launch_bounds__(kGroupThreads) proj_match_group_kernel(const ProjKernelArgs a)
+{
+    constexpr int GROUPS = kGroupThreads / LANES;
+    __shared__ uint4 s_obs[GROUPS][2 * kObsStaged];
+    __shared__ int2 s_queue[QUEUE ? GROUPS : 1][2 * LANES];
+    const ProjFrameArgs& f = a.frames ? a.frames[blockIdx.y] : a.inline_frame;
+    proj_match_group_body<LANES, QUEUE>(a, f, s_obs, s_queue);
+}
+// (Letting the last CTA of this kernel run the emit step -- one launch instead of two for a per-frame call -- was
+// tried and measured 2.5 us SLOWER on the C2 call than the separate 8-CTA emit launch: the tail is a chain of two
+// round trips on one SM behind a fence and a counter in every CTA, and a dependent launch costs only 2.3 us.)
 
 // ---------------------------------------------------------------------------------------------
 // K4, two-pass form (large visit lists).  In the fused kernel every lane of a group repeats the point's
@@ -748,12 +759,9 @@ __global__ void __launch_bounds__(kGroupThreads, 8) proj_search_kernel(const Pro
 // the kernel is bound by the latency of its dependent loads at the occupancy its registers allow, not by
 // instruction issue.
 
-__global__ void proj_emit_kernel(const ProjKernelArgs a)
+__device__ __forceinline__ void emit_keypoint(const ProjKernelArgs& a, const ProjFrameArgs& f, int kp)
 {
-    const ProjFrameArgs& f = a.frames ? a.frames[blockIdx.y] : a.inline_frame;
-    const int kp = blockIdx.x * blockDim.x + threadIdx.x;
-    if (kp >= f.nkp) return;
-    const unsigned long long key = f.proposals[kp];
+    const unsigned long long key = __ldcg(&f.proposals[kp]);          // written by atomics of other CTAs: read at L2
     int point = -1, dist = -1;
     if (key != ~0ull) {
         const int v = static_cast<int>(key & 0xFFFFFFFFull);
@@ -763,7 +771,15 @@ __global__ void proj_emit_kernel(const ProjKernelArgs a)
     }
     f.out_point[kp] = point;
     f.out_dist[kp] = dist;
-    if (kp == 0 && f.ties_out != nullptr) *f.ties_out = *f.ties;      // zero-copy call: the tie count to host memory
+    if (kp == 0 && f.ties_out != nullptr) *f.ties_out = __ldcg(f.ties);      // zero-copy call: the tie count to host memory
+}
+
+__global__ void proj_emit_kernel(const ProjKernelArgs a)
+{
+    const ProjFrameArgs& f = a.frames ? a.frames[blockIdx.y] : a.inline_frame;
+    const int kp = blockIdx.x * blockDim.x + threadIdx.x;
+    if (kp >= f.nkp) return;
+    emit_keypoint(a, f, kp);
 }
 
 // Emit + Frame::add_map_match (src/Frame.cpp:80-102) on the device.  A proposal comes from a point that
@@ -787,6 +803,7 @@ __global__ void proj_emit_apply_kernel(const ProjKernelArgs a, uint8_t* pt_match
     }
     f.out_point[kp] = point;
     f.out_dist[kp] = dist;
+    if (kp == 0 && f.ties_out != nullptr) *f.ties_out = *f.ties;      // zero-copy call: the tie count so far to host memory
 }
 
 __global__ void proj_scatter_flags_kernel(const int32_t* idx, int n, uint8_t* flags)
@@ -959,6 +976,91 @@ int proj_launch_point_stats(slamgpu_ctx* ctx, const float* d_pos, int n, const i
                                                                  d_range);
     ctx->launches++;
     SG_CUDA(cudaGetLastError());
+    return SLAMGPU_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// The candidate grid of a freshly uploaded frame, built on the device (one CTA: a frame has a few thousand
+// keypoints and a few thousand cells).  cell_start[c] .. cell_start[c + 1] are the slots of cell c, a slot holds
+// (x bits, y bits, keypoint index, keypoint index).  The slots of a cell are in NO particular order: the grid
+// without the tree serves only speculative calls, whose result does not depend on the order candidates are
+// scored in (a tie at a point's minimum is counted, whichever candidate came first, and the call is repeated with
+// the tree: group_search).  On the host the same counting sort cost 85 us per 8000-keypoint frame, the largest
+// item of slamgpu_frame_upload; here the host only queues one launch behind the upload.
+// Shared memory: one counter per cell (count, then exclusive prefix, then write cursor).
+// ---------------------------------------------------------------------------------------------
+constexpr int kGridBuildThreads = 1024;
+
+__global__ void __launch_bounds__(kGridBuildThreads) grid_build_kernel(const float2* __restrict__ xy, int n, float gx0,
+                                                                       float gy0, float inv_cell, int gw, int gh,
+                                                                       int32_t* cell_start, int4* cell_rec)
+{
+    extern __shared__ int s_cell[];                    // [n_cells]
+    __shared__ int s_warp[32];
+    const int n_cells = gw * gh;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    for (int c = tid; c < n_cells; c += kGridBuildThreads) s_cell[c] = 0;
+    __syncthreads();
+    for (int k = tid; k < n; k += kGridBuildThreads) {
+        const float2 p = xy[k];
+        atomicAdd(&s_cell[grid_cell(p.y, gy0, inv_cell, gh) * gw + grid_cell(p.x, gx0, inv_cell, gw)], 1);
+    }
+    __syncthreads();
+    // exclusive scan: every thread owns a run of consecutive cells
+    const int per = (n_cells + kGridBuildThreads - 1) / kGridBuildThreads;
+    const int c0 = min(tid * per, n_cells), c1 = min(c0 + per, n_cells);
+    int sum = 0;
+    for (int c = c0; c < c1; ++c) sum += s_cell[c];
+    int incl = sum;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const int y = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+        if (lane >= o) incl += y;
+    }
+    if (lane == 31) s_warp[warp] = incl;
+    __syncthreads();
+    if (warp == 0) {
+        int w = s_warp[lane];
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int y = __shfl_up_sync(0xFFFFFFFFu, w, o);
+            if (lane >= o) w += y;
+        }
+        s_warp[lane] = w;
+    }
+    __syncthreads();
+    int run = (warp ? s_warp[warp - 1] : 0) + incl - sum;
+    for (int c = c0; c < c1; ++c) {
+        const int cnt = s_cell[c];
+        s_cell[c] = run;                               // from here on: the cell's write cursor
+        cell_start[c] = run;
+        run += cnt;
+    }
+    if (tid == 0) cell_start[n_cells] = n;
+    __syncthreads();
+    for (int k = tid; k < n; k += kGridBuildThreads) {
+        const float2 p = xy[k];
+        const int slot = atomicAdd(&s_cell[grid_cell(p.y, gy0, inv_cell, gh) * gw + grid_cell(p.x, gx0, inv_cell, gw)], 1);
+        cell_rec[slot] = make_int4(__float_as_int(p.x), __float_as_int(p.y), k, k);
+    }
+}
+
+// true in *done when the frame is of a size the single-CTA build takes (else the caller builds the grid on the host)
+int proj_launch_grid_build(slamgpu_ctx* ctx, const float2* d_xy, int n, float gx0, float gy0, float inv_cell, int gw, int gh,
+                           int32_t* d_cell_start, int4* d_cell_rec, bool* done)
+{
+    constexpr size_t kMaxSmem = size_t(200) << 10;
+    const size_t smem = static_cast<size_t>(gw) * gh * sizeof(int);
+    *done = false;
+    if (n <= 0 || n > (1 << 16) || smem > kMaxSmem) return SLAMGPU_OK;
+    if (smem > (size_t(48) << 10) && !ctx->grid_attr_set) {
+        SG_CUDA(cudaFuncSetAttribute(grid_build_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(kMaxSmem)));
+        ctx->grid_attr_set = true;
+    }
+    grid_build_kernel<<<1, kGridBuildThreads, smem, ctx->stream>>>(d_xy, n, gx0, gy0, inv_cell, gw, gh, d_cell_start, d_cell_rec);
+    ctx->launches++;
+    SG_CUDA(cudaGetLastError());
+    *done = true;
     return SLAMGPU_OK;
 }
 

@@ -81,6 +81,13 @@ static int grow(slamgpu_ctx* ctx, Arena& a, size_t bytes, bool host)
     return SLAMGPU_OK;
 }
 
+int wait_stream(slamgpu_ctx* ctx)
+{
+    SG_CUDA(cudaEventRecord(ctx->sync_event, ctx->stream));
+    SG_CUDA(cudaEventSynchronize(ctx->sync_event));
+    return SLAMGPU_OK;
+}
+
 int ensure_device_ws(slamgpu_ctx* ctx, size_t bytes) { return grow(ctx, ctx->d_ws, bytes, false); }
 int ensure_device_io(slamgpu_ctx* ctx, size_t bytes) { return grow(ctx, ctx->d_io, bytes, false); }
 int ensure_host_stage(slamgpu_ctx* ctx, size_t bytes) { return grow(ctx, ctx->h_stage, bytes, true); }
@@ -257,6 +264,8 @@ int slamgpu_create(int device, slamgpu_ctx** out)
     if (bzc != nullptr) ctx->bf_zero_copy = bzc[0] != '0';
     const char* pzc = std::getenv("SLAMGPU_PROJ_ZEROCOPY");
     if (pzc != nullptr) ctx->proj_zero_copy = pzc[0] != '0';
+    const char* god = std::getenv("SLAMGPU_GRID_ON_DEVICE");
+    if (god != nullptr) ctx->grid_on_device = god[0] != '0';
     const char* kdl = std::getenv("SLAMGPU_KD_LAZY");
     if (kdl != nullptr) ctx->kd_lazy = kdl[0] != '0';
     const char* kdd = std::getenv("SLAMGPU_KD_DELAY_MS");
@@ -288,6 +297,11 @@ int slamgpu_create(int device, slamgpu_ctx** out)
     if (e != cudaSuccess) {
         delete ctx;
         return fail(SLAMGPU_ERR_CUDA, std::string("cudaStreamCreate: ") + cudaGetErrorString(e));
+    }
+    if (cudaEventCreateWithFlags(&ctx->sync_event, cudaEventDisableTiming) != cudaSuccess) {
+        const std::string msg = cudaGetErrorString(cudaGetLastError());
+        slamgpu_destroy(ctx);
+        return fail(SLAMGPU_ERR_CUDA, "context resources: " + msg);
     }
     *out = ctx;
     return SLAMGPU_OK;
@@ -321,6 +335,7 @@ int slamgpu_destroy(slamgpu_ctx* ctx)
     for (cudaEvent_t e : ctx->prof_pool) cudaEventDestroy(e);
     for (cudaEvent_t e : ctx->slice_events) cudaEventDestroy(e);
     if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);
+    if (ctx->sync_event) cudaEventDestroy(ctx->sync_event);
     cudaStreamDestroy(ctx->stream);
     delete ctx;
     return SLAMGPU_OK;

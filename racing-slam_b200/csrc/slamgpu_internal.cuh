@@ -202,6 +202,7 @@ struct slamgpu_ctx {
                                    // measured no faster: an MMA costs the same at N = 80 as at N = 240 and the narrow tile issues 9 instead of 5)
     bool tc4_teams = false;        // SLAMGPU_TC4_TEAMS=1: the FP4 scan's epilogue warps as two teams on alternate tiles (measured slower than
                                    // every warp reading its half of every tile first and folding afterwards; same results)
+    bool grid_attr_set = false;                       // dynamic-smem opt-in of grid_build_kernel done on this context's device
     bool tc_attr_set = false, tc4_attr_set = false;   // dynamic-smem opt-in of the tensor-core scans done on this context's device
     slamgpu::Arena d_exp;     // expanded (int8) descriptors of the tensor-core scan
     std::vector<std::pair<cudaEvent_t, cudaEvent_t>> prof_events[4];   // per SLAMGPU_KERNEL_*
@@ -217,11 +218,17 @@ struct slamgpu_ctx {
     int64_t trace_calls = 0;
     int batch_slice = 0;                       // SLAMGPU_BATCH_SLICE: pairs per slice of the batch calls (0 = by scratch size)
     cudaStream_t copy_stream = nullptr;        // result copies of the batch call, overlapped with later slices
+    bool grid_on_device = true;                // SLAMGPU_GRID_ON_DEVICE=0: slamgpu_frame_upload builds the tree-free grid on the host
+    std::vector<int32_t> grid_scratch;         // slamgpu_frame_upload's counting sort (kept: no allocation per frame)
+    cudaEvent_t sync_event = nullptr;          // wait_stream(): record + cudaEventSynchronize returns 0.5-1.3 us sooner than
+                                               // cudaStreamSynchronize on this driver (tools/lat_probe.cu)
     std::vector<cudaEvent_t> slice_events;     // 3 per slice of slamgpu_match_descriptors_batch (created on demand)
 };
 
 namespace slamgpu {
 
+// Block until everything queued on the context's stream has completed (the end of every host-buffer call).
+int wait_stream(slamgpu_ctx* ctx);
 int ensure_device_ws(slamgpu_ctx* ctx, size_t bytes);
 int ensure_device_io(slamgpu_ctx* ctx, size_t bytes);
 int ensure_host_stage(slamgpu_ctx* ctx, size_t bytes);
@@ -271,6 +278,11 @@ int bf_launch_mutual(slamgpu_ctx* ctx, const BfPlan& row_plan, const uint2* d_ro
 int bf_launch_mutual_direct(slamgpu_ctx* ctx, const BfPlan& row_plan, const uint2* d_row_keys, int row_stride,
                             const uint32_t* d_col_keys, int nq, float strict_max_dist, int32_t* d_idx, int32_t* d_dist);
 // Ordered compaction of out_train[pair][q] into (query, train) lists.
+// Short batches into host-visible lists: filter + per-pair compaction (one CTA per pair), then offsets + gather.
+int bf_launch_finish_compact(slamgpu_ctx* ctx, const BfPlan& plan, const uint2* d_keys, const int32_t* d_frame_offset,
+                             const int32_t* d_pairs, int n_pairs, int max_rows, float max_dist, float ratio,
+                             int32_t* d_local /* 2 x n_pairs x max_rows */, int32_t* d_count, int32_t* d_offset,
+                             int32_t* h_offset_mirror, int32_t* query_list, int32_t* train_list, int64_t capacity);
 int bf_launch_scan_counts(slamgpu_ctx* ctx, const int32_t* d_count, int n, int32_t* d_offset /* n+1 */,
                           int32_t* h_offset_mirror = nullptr /* n+1, device-addressable host memory */);
 int bf_launch_compact(slamgpu_ctx* ctx, const int32_t* d_out_train, const int32_t* d_frame_offset,
@@ -362,6 +374,8 @@ int proj_launch_track(slamgpu_ctx* ctx, const ProjCommonArgs& common, const Proj
 int proj_launch_flags(slamgpu_ctx* ctx, const int32_t* d_idx, int n, uint8_t* d_flags, int n_flags);
 int proj_launch_point_stats(slamgpu_ctx* ctx, const float* d_pos, int n, const int32_t* d_obs_offset,
                             const float* d_obs_center, float* d_normal, float* d_range);
+int proj_launch_grid_build(slamgpu_ctx* ctx, const float2* d_xy, int n, float gx0, float gy0, float inv_cell, int gw, int gh,
+                           int32_t* d_cell_start, int4* d_cell_rec, bool* done);
 int proj_launch_kd_gather(slamgpu_ctx* ctx, const float2* d_xy, const int32_t* d_perm, int n, float2* d_kd_xy);
 
 // host-side float helpers that follow the oracle's / Eigen's operation order

@@ -257,6 +257,41 @@ def test_batch_in_slices_returns_the_same_lists(oracle, pkg, monkeypatch, slice_
         assert np.array_equal(o3, want_o[:4]) and np.array_equal(ql3, want_q[:want_o[3]])
 
 
+@pytest.mark.parametrize("engine", ["int", "tc"])
+def test_short_batch_into_pinned_lists(oracle, pkg, monkeypatch, engine):
+    """The loop-query path (at most 256 pairs, pinned result arrays): one CTA per pair filters and compacts, a second
+    launch places the blocks -- ragged and empty frames, frames longer than one 1024-row step, 1 / 5 / 256 pairs,
+    repeated pairs, an undersized list reported with the size needed, both engines."""
+    monkeypatch.setenv("SLAMGPU_BF_ENGINE", engine)
+    sizes = [2500, 0, 1025, 1, 1024, 33, 3000, 700]
+    db = pkg.synthetic.keyframe_db(len(sizes), 3000, 19, shared_frac=0.5)
+    frames = [db[i, :n] for i, n in enumerate(sizes)]
+    desc = np.concatenate(frames)
+    off = np.concatenate([[0], np.cumsum(sizes)]).astype(np.int32)
+    rng = np.random.default_rng(4)
+    with pkg.Context(0) as c:
+        for n_pairs in (1, 5, 256):
+            pairs = rng.integers(0, len(sizes), (n_pairs, 2)).astype(np.int32)
+            if n_pairs == 5:
+                pairs = np.array([[0, 6], [6, 0], [1, 0], [0, 1], [0, 6]], np.int32)
+            want = [oracle.match_descriptors(frames[a], frames[b], 64.0, 0.75) for a, b in pairs]
+            want_o = np.concatenate([[0], np.cumsum([len(w[0]) for w in want])])
+            cap = int(want_o[-1]) + 7
+            out = (pkg.pinned_empty(cap, np.int32), pkg.pinned_empty(cap, np.int32))
+            for _ in range(2):                                    # twice: the scratch and the counters are reused
+                o, ql, tl = c.match_descriptors_batch(desc, off, pairs, 64.0, 0.75, out=out)
+                assert np.array_equal(o, want_o), n_pairs
+                assert np.array_equal(ql, np.concatenate([w[0] for w in want])), n_pairs
+                assert np.array_equal(tl, np.concatenate([w[1] for w in want])), n_pairs
+            if want_o[-1] > 8:
+                small = (pkg.pinned_empty(int(want_o[-1]) - 3, np.int32), pkg.pinned_empty(int(want_o[-1]) - 3, np.int32))
+                with pytest.raises(pkg.SlamGpuError) as e:
+                    c.match_descriptors_batch(desc, off, pairs, 64.0, 0.75, out=small)
+                assert e.value.code == pkg.binding.ERR_NOMEM
+                del small
+            del out
+
+
 def test_batch_capacity_error(ctx, pkg):
     db = pkg.synthetic.keyframe_db(3, 128, 1, shared_frac=0.9, max_flip=5)
     desc = db.reshape(-1, 32)

@@ -395,3 +395,34 @@ def test_many_random_small_scenes_vs_oracle(oracle, pkg, monkeypatch, two_pass):
             _compare((op, od), dbg, ref)
             ties += int((ref.kp >= 0).sum())
     assert ties > 2000
+
+
+def test_plain_calls_without_diagnostics_vs_oracle(oracle, pkg):
+    """The per-frame call as the adapter makes it (no diagnostics: the zero-copy path): 40 seeded scenes, each called
+    twice (the proposal slots must be back at rest), visit lists with null entries, lists in which every point is
+    skipped, one-point maps, frames of 1 and of 4096 keypoints."""
+    rng = np.random.default_rng(515)
+    matches = 0
+    with pkg.Context(0) as c:
+        for it in range(40):
+            cam = pkg.synthetic.KITTI
+            n_points = int(rng.choice([1, 7, 300, 2500, 10000]))
+            nkp = int(rng.choice([1, 50, 2000, 4096]))
+            sc = pkg.synthetic.projection_scene(n_points, nkp, 900 + it, cam=cam, max_obs=int(rng.integers(1, 12)))
+            p = _params(pkg, cam, float(rng.choice([5.0, 20.0, 40.0])), 64.0, int(rng.integers(0, 2)))
+            skip = sc.skip.copy()
+            if it % 7 == 3:
+                skip[:] = 1                                     # nothing to visit: every CTA leaves at once
+            order = None
+            if it % 4 == 1:
+                order = rng.integers(0, n_points, int(rng.integers(1, n_points + 2))).astype(np.int32)
+                order[rng.random(len(order)) < 0.2] = -1
+            ref = oracle.match_projection(sc.kp_xy, sc.kp_desc, oracle.kd_build(sc.kp_xy), sc.kp_matched, sc.pos, sc.normal,
+                                          sc.range, sc.obs_offset, sc.obs_desc, skip, order, sc.pose, _oparams(oracle, p))
+            c.frame_upload(1, sc.kp_xy, sc.kp_desc, None, sc.kp_matched)
+            c.points_upload(1, sc.pos, sc.normal, sc.range, sc.obs_offset, sc.obs_desc)
+            for _ in range(2):
+                op, od = c.match_projection(1, 1, nkp, sc.pose, p, skip, order)
+                assert np.array_equal(op, ref.point) and np.array_equal(od, ref.dist), it
+            matches += int((ref.point >= 0).sum())
+    assert matches > 3000

@@ -212,14 +212,16 @@ def test_track_match_with_either_form_of_the_match_kernel(oracle, pkg, monkeypat
             test_track_match_equals_the_two_reference_calls(c, oracle, pkg, *scene)
 
 
+@pytest.mark.parametrize("grid_on_device", ["1", "0"])
 @pytest.mark.parametrize("ties", [False, True])
-def test_calls_that_arrive_before_the_kd_tree_speculate_and_repeat_on_ties(oracle, pkg, monkeypatch, ties):
+def test_calls_that_arrive_before_the_kd_tree_speculate_and_repeat_on_ties(oracle, pkg, monkeypatch, ties, grid_on_device):
     """slamgpu_frame_upload builds the KD-tree on a host thread; a projection call that finds it missing runs on the
     tree-free grid and counts the ties only the KD visit order can settle (src/KDTree.cpp:52-82,
     src/MapMatcher.cpp:88).  SLAMGPU_KD_DELAY_MS makes the builder late on purpose.  Without ties the speculative
     results stand; with ties (low-entropy descriptors) the call waits for the tree, restores the frame's keypoint
     flags and repeats itself -- either way the results are the oracle's."""
     monkeypatch.setenv("SLAMGPU_KD_DELAY_MS", "40")
+    monkeypatch.setenv("SLAMGPU_GRID_ON_DEVICE", grid_on_device)    # the tree-free grid from the device kernel / the host sort
     cam = dict(fx=300.0, fy=300.0, cx=160.0, cy=120.0, width=320, height=240)
     sc = pkg.synthetic.projection_scene(6000, 1500, 93, cam=cam)
     rng = np.random.default_rng(93)
@@ -261,3 +263,34 @@ def test_calls_that_arrive_before_the_kd_tree_speculate_and_repeat_on_ties(oracl
         c.frame_upload(1, sc.kp_xy, sc.kp_desc, None, sc.kp_matched)
         gp, gd = c.match_projection(1, 1, 1500, sc.pose, p, sc.skip, None)
         assert np.array_equal(gp, ref.point) and np.array_equal(gd, ref.dist) and c.speculation_count() == (0, 0)
+
+
+@pytest.mark.parametrize("case", ["clustered", "one_cell", "wide", "huge_frame"])
+def test_tree_free_grid_built_on_the_device_serves_speculative_calls(oracle, pkg, monkeypatch, case):
+    """grid_build_kernel (one CTA, cells counted in shared memory) against the oracle through speculative calls:
+    keypoints piled into a few cells, all in ONE cell, a sparse grid with more than 12k cells (dynamic shared memory
+    above 48 KB), and a frame too large for the kernel (the host sort takes over).  The tree is held back so that the
+    calls really run on this grid."""
+    monkeypatch.setenv("SLAMGPU_KD_DELAY_MS", "60")
+    rng = np.random.default_rng(7)
+    cam = dict(pkg.synthetic.HD1080)
+    n_points, nkp = 4000, 3000
+    if case == "huge_frame":
+        nkp = 70000
+    sc = pkg.synthetic.projection_scene(n_points, nkp, 31, cam=cam)
+    if case == "clustered":
+        sc.kp_xy[:] = (sc.kp_xy // 160) * 160 + rng.uniform(0, 12, sc.kp_xy.shape).astype(np.float32)
+    elif case == "one_cell":
+        sc.kp_xy[:] = np.float32([900.0, 500.0]) + rng.uniform(0, 10, sc.kp_xy.shape).astype(np.float32)
+    elif case == "wide":
+        monkeypatch.setenv("SLAMGPU_GRID_CELL", "8")               # 240 x 135 = 32400 cells
+    p = _params(pkg, cam, 20.0, 64.0)
+    ref = oracle.match_projection(sc.kp_xy, sc.kp_desc, oracle.kd_build(sc.kp_xy), sc.kp_matched, sc.pos, sc.normal, sc.range,
+                                  sc.obs_offset, sc.obs_desc, sc.skip, None, sc.pose, _oparams(oracle, p), want_stats=False)
+    with pkg.Context(0) as c:
+        c.points_upload(1, sc.pos, sc.normal, sc.range, sc.obs_offset, sc.obs_desc)
+        for _ in range(2):
+            c.frame_upload(1, sc.kp_xy, sc.kp_desc, None, sc.kp_matched)
+            gp, gd = c.match_projection(1, 1, nkp, sc.pose, p, sc.skip, None)
+            assert np.array_equal(gp, ref.point) and np.array_equal(gd, ref.dist)
+        assert c.speculation_count()[0] == 2
