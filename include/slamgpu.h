@@ -101,6 +101,19 @@ SLAMGPU_API int slamgpu_knn2_dev(slamgpu_ctx* ctx, const uint8_t* d_query, int n
                      int32_t* d_out_idx, int32_t* d_out_dist);
 SLAMGPU_API int slamgpu_crosscheck_dev(slamgpu_ctx* ctx, const uint8_t* d_query, int nq, const uint8_t* d_train, int nt,
                            int32_t* d_out_idx, int32_t* d_out_dist);
+
+/* slamgpu_knn2_dev that ALLOCATES NOTHING.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid it).  Same arguments, same results as slamgpu_knn2_dev (integer XOR + POPC scan; the outputs are
+ * bit-identical to every other engine's).  The scan's partial keys live in a fixed 8 MiB device array inside the
+ * library instead of the context's growable workspace, hence the limit: nq <= 8192 and nt <= 8192, anything larger
+ * is refused with SLAMGPU_ERR_INVALID and a message (use slamgpu_knn2_dev).  Every GPU that loads the library holds
+ * the array until exit, and every call on that GPU shares it: calls on one context are stream-ordered and safe,
+ * calls that overlap on the GPU (different contexts / streams) RACE on the scratch -- serialise them.  The call
+ * queues two kernels on the context's stream (slamgpu_stream) and returns; it calls no cudaMalloc, cudaFree or any
+ * allocating routine.  The scratch address is resolved once per device inside slamgpu_create. */
+SLAMGPU_API int slamgpu_knn2_dev_noalloc(slamgpu_ctx* ctx, const uint8_t* d_query, int nq, const uint8_t* d_train, int nt,
+                             int32_t* d_out_idx, int32_t* d_out_dist);
 /* d_out_train[q] = trainIdx of the surviving match or -1; *d_out_count (device int) = survivors. */
 SLAMGPU_API int slamgpu_match_descriptors_dev(slamgpu_ctx* ctx, const uint8_t* d_query, int nq, const uint8_t* d_train, int nt,
                                   float max_dist, float ratio, int32_t* d_out_train, int32_t* d_out_count);

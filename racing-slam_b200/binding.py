@@ -62,6 +62,7 @@ SIGNATURES = {
                                          C.POINTER(C.c_int)]),
     "slamgpu_knn2_dev": (C.c_int, [_ctx, C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]),
     "slamgpu_crosscheck_dev": (C.c_int, [_ctx, C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]),
+    "slamgpu_knn2_dev_noalloc": (C.c_int, [_ctx, C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]),
     "slamgpu_match_descriptors_dev": (C.c_int, [_ctx, C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_float, C.c_float,
                                                 C.c_void_p, C.c_void_p]),
     "slamgpu_match_descriptors_batch_dev": (C.c_int, [_ctx, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_int,
@@ -420,6 +421,10 @@ class Context:
     # ---- brute force, device buffers (raw pointers; stream-ordered, no sync) ----
     def knn2_dev(self, d_q: int, nq: int, d_t: int, nt: int, d_idx: int, d_dist: int):
         self._check(self._lib.slamgpu_knn2_dev(self._h, d_q, nq, d_t, nt, d_idx, d_dist))
+
+    def knn2_dev_noalloc(self, d_q: int, nq: int, d_t: int, nt: int, d_idx: int, d_dist: int):
+        """knn2_dev without any allocation: fixed scratch inside the library, nq and nt <= 8192 (include/slamgpu.h)."""
+        self._check(self._lib.slamgpu_knn2_dev_noalloc(self._h, d_q, nq, d_t, nt, d_idx, d_dist))
 
     def crosscheck_dev(self, d_q: int, nq: int, d_t: int, nt: int, d_idx: int, d_dist: int):
         self._check(self._lib.slamgpu_crosscheck_dev(self._h, d_q, nq, d_t, nt, d_idx, d_dist))

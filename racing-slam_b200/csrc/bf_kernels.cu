@@ -9,6 +9,8 @@
 //
 // Roofline: the integer POPC pipe (8 POPC32 per 256-bit comparison), not HBM: a descriptor
 // byte is reused by every query row of the tile.
+#include <mutex>
+
 #include "slamgpu_internal.cuh"
 
 namespace slamgpu {
@@ -885,3 +887,99 @@ int popc_microbench(slamgpu_ctx* ctx, double* popc_per_s, int* n_sm, double* sm_
 }
 
 } // namespace slamgpu
+
+// ---------------------------------------------------------------------------------------------
+// slamgpu_knn2_dev_noalloc: the integer-pipe kNN-2 scan for callers that must not allocate (code under CUDA graph
+// capture, serving loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+// The scan's split partials -- the scratch slamgpu_knn2_dev takes from the context's
+// growable workspace (ensure_device_ws: cudaMalloc on growth) -- live in a file-scope device array of fixed size.
+// Every GPU that loads the library holds these 8 MiB until exit.  ALL calls on a device share the array: two calls
+// that overlap on the GPU (two contexts = two streams) race on it; calls on one context are stream-ordered and safe.
+// The array keeps the last call's contents; nothing in it has to start at zero: a call writes every (split, row)
+// entry its finish kernel reads (bf_scan_kernel stores all rows < nq of every split) before reading it.
+// ---------------------------------------------------------------------------------------------
+namespace slamgpu {
+namespace {
+
+constexpr int kNoAllocMaxRows = 8192;                         // nq and nt limit of the entry point
+constexpr size_t kNoAllocKeys = size_t(1) << 20;              // uint2 entries: 8 MiB
+static __device__ __align__(256) uint2 g_noalloc_keys[kNoAllocKeys];
+
+// In host code `g_noalloc_keys` is a host-side stand-in for the symbol, not a device address: the address a kernel
+// can use comes from cudaGetSymbolAddress, once per device, with that device current.
+constexpr int kNoAllocMaxDevices = 64;
+uint2* g_noalloc_ptr[kNoAllocMaxDevices] = {};
+std::mutex g_noalloc_mutex;
+
+int noalloc_scratch(int device, uint2** out)
+{
+    SG_CHECK(device >= 0 && device < kNoAllocMaxDevices, "device index beyond the no-alloc scratch table");
+    std::lock_guard<std::mutex> lock(g_noalloc_mutex);
+    if (g_noalloc_ptr[device] == nullptr) {
+        void* p = nullptr;
+        SG_CUDA(cudaGetSymbolAddress(&p, g_noalloc_keys));
+        SG_CHECK(p != nullptr, "cudaGetSymbolAddress returned a null scratch address");
+        g_noalloc_ptr[device] = static_cast<uint2*>(p);
+    }
+    *out = g_noalloc_ptr[device];
+    return SLAMGPU_OK;
+}
+
+} // namespace
+
+// set-up hook of slamgpu_create (device current): resolves the scratch address so that no later call has to
+int bf_noalloc_setup(int device)
+{
+    uint2* p = nullptr;
+    return noalloc_scratch(device, &p);
+}
+
+} // namespace slamgpu
+
+extern "C" int slamgpu_knn2_dev_noalloc(slamgpu_ctx* ctx, const uint8_t* d_query, int nq, const uint8_t* d_train, int nt,
+                                        int32_t* d_out_idx, int32_t* d_out_dist)
+{
+    using namespace slamgpu;
+    SG_CHECK(ctx != nullptr, "null context");
+    SG_CHECK(nq >= 0 && nt >= 0, "negative descriptor count");
+    SG_CHECK(nq <= kNoAllocMaxRows && nt <= kNoAllocMaxRows,
+             "slamgpu_knn2_dev_noalloc takes at most 8192 query and 8192 train descriptors (fixed scratch); "
+             "use slamgpu_knn2_dev for larger sets");
+    if (nq == 0) return SLAMGPU_OK;
+    SG_CHECK(d_query != nullptr && d_out_idx != nullptr && d_out_dist != nullptr && (nt == 0 || d_train != nullptr), "null pointer");
+    SG_CHECK(((reinterpret_cast<uintptr_t>(d_query) | reinterpret_cast<uintptr_t>(d_train)) & 15u) == 0,
+             "device descriptor pointers must be 16-byte aligned");
+    SG_CUDA(cudaSetDevice(ctx->device));
+    if (nt == 0) {   // every neighbour missing (as slamgpu_knn2_dev)
+        SG_CUDA(cudaMemsetAsync(d_out_idx, 0xFF, sizeof(int32_t) * 2 * nq, ctx->stream));
+        SG_CUDA(cudaMemsetAsync(d_out_dist, 0xFF, sizeof(int32_t) * 2 * nq, ctx->stream));
+        return SLAMGPU_OK;
+    }
+    uint2* keys = nullptr;
+    SG_TRY(noalloc_scratch(ctx->device, &keys));
+    const BfPlan plan = bf_make_plan(ctx->n_sm, nq, nt, 1);
+    SG_CHECK(bf_partial_elems(plan, 1, nq) <= kNoAllocKeys, "scan partials exceed the fixed scratch of slamgpu_knn2_dev_noalloc");
+    // the launches of bf_launch_scan / bf_launch_finish_raw without their profiling scope (which creates events)
+    ScanArgs a;
+    a.q_base = d_query;
+    a.t_base = d_train;
+    a.frame_offset = nullptr;
+    a.pairs = nullptr;
+    a.nq = nq;
+    a.nt = nt;
+    a.tiles = plan.tiles;
+    a.splits = plan.splits;
+    a.t_per_split = plan.t_per_split;
+    a.max_rows = nq;
+    a.swap_roles = 0;
+    a.keys = keys;
+    a.col_keys = nullptr;
+    const dim3 grid(static_cast<unsigned>(plan.tiles) * static_cast<unsigned>(plan.splits));
+    if (plan.r == 4) bf_scan_kernel<2, false><<<grid, kThreads, 0, ctx->stream>>>(a);
+    else bf_scan_kernel<1, false><<<grid, kThreads, 0, ctx->stream>>>(a);
+    const dim3 blk = finish_block(plan.splits);
+    bf_finish_raw_kernel<<<(nq + blk.x - 1) / blk.x, blk, 0, ctx->stream>>>(keys, plan.splits, nq, nq, d_out_idx, d_out_dist);
+    ctx->launches += 2;
+    SG_CUDA(cudaGetLastError());
+    return SLAMGPU_OK;
+}

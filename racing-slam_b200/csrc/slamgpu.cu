@@ -303,6 +303,9 @@ int slamgpu_create(int device, slamgpu_ctx** out)
         slamgpu_destroy(ctx);
         return fail(SLAMGPU_ERR_CUDA, "context resources: " + msg);
     }
+    // set-up for slamgpu_knn2_dev_noalloc: the address of its fixed scratch array on this device, so that the entry
+    // point itself never has to ask (a failure here is reported by that entry point, not by slamgpu_create)
+    if (bf_noalloc_setup(device) != SLAMGPU_OK) cudaGetLastError();
     *out = ctx;
     return SLAMGPU_OK;
 }

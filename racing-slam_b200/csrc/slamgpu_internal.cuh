@@ -283,6 +283,8 @@ int bf_launch_finish_compact(slamgpu_ctx* ctx, const BfPlan& plan, const uint2* 
                              const int32_t* d_pairs, int n_pairs, int max_rows, float max_dist, float ratio,
                              int32_t* d_local /* 2 x n_pairs x max_rows */, int32_t* d_count, int32_t* d_offset,
                              int32_t* h_offset_mirror, int32_t* query_list, int32_t* train_list, int64_t capacity);
+// slamgpu_knn2_dev_noalloc (bf_kernels.cu): resolve the fixed scratch array's device address (device current)
+int bf_noalloc_setup(int device);
 int bf_launch_scan_counts(slamgpu_ctx* ctx, const int32_t* d_count, int n, int32_t* d_offset /* n+1 */,
                           int32_t* h_offset_mirror = nullptr /* n+1, device-addressable host memory */);
 int bf_launch_compact(slamgpu_ctx* ctx, const int32_t* d_out_train, const int32_t* d_frame_offset,
