@@ -234,6 +234,24 @@ template <class F> int for_frame_runs(int n_frames, const std::vector<int>* used
     return SLAMGPU_OK;
 }
 
+// PUSH mode of the host-buffer batch call (pinned result lists): a slice's compaction and its way home run on a
+// second stream, driven by the device alone -- finish + offsets (main stream) -> event -> compaction of the slice's
+// rows into the device lists -> SM-store copy of that piece into the caller's pinned lists, while the main stream
+// already scans the next slice.  The host queues everything up front and waits once at the end; the offsets reach it
+// through a mapped mirror.  (Before, the host read each slice's offsets, queued two copies and waited for them: with
+// eight ranks on one host its reaction time was on every rank's critical path, and the compaction -- 3.6 % of the GPU
+// time -- sat between two scans.)  The rows scratch is double-buffered: finish of slice s + 2 waits for the compaction
+// of slice s.  Measured on one box: resident-database batches 9,558 -> 9,692 G/s.  Moving the finish kernel to the
+// second stream as well (scans back to back) was SLOWER, 9,483: its 131k CTAs get in the way of the persistent scan.
+struct BatchPush {
+    cudaStream_t stream;          // the second stream
+    int32_t* rows2;               // second rows scratch [slice_pairs x max_rows]
+    int32_t* h_query;             // the caller's pinned lists (device-addressable)
+    int32_t* h_train;
+    int32_t* h_offset_mirror;     // [n_pairs + 1] pinned
+    cudaEvent_t* events;          // 2 per slice: finish done (main stream), compaction done (second stream)
+};
+
 // Pairs are processed in slices so that the partial-key scratch stays around L2 size.
 constexpr size_t kBatchScratchBytes = size_t(256) << 20;
 
@@ -261,7 +279,8 @@ int batch_core(slamgpu_ctx* ctx, const uint8_t* d_desc, const int32_t* d_frame_o
                // expanded copy built (a loop-closure query against a handful of candidates of a large resident database)
                const std::vector<int>* frames_used = nullptr,
                // a device-addressable host copy of the offsets (short calls: the kernels write results to host memory)
-               int32_t* h_offset_mirror = nullptr)
+               int32_t* h_offset_mirror = nullptr,
+               const BatchPush* push = nullptr)
 {
     if (n_pairs == 0) return SLAMGPU_OK;
     if (max_rows == 0) {
@@ -276,6 +295,9 @@ int batch_core(slamgpu_ctx* ctx, const uint8_t* d_desc, const int32_t* d_frame_o
                      : bf_make_plan(ctx->n_sm, max_rows, max_rows, std::min(n_pairs, slice_pairs));
     BfPlan fin = plan;
     int pitch = 0;
+    // FP4 batches with one train split per pair: the scan filters and writes the rows itself (bf_tc4_kernels.cu: fused
+    // finish); the short-call path keeps its own finish + compaction kernel
+    const bool fused = fp4 && plan.splits == 1 && ctx->tc4_fuse_finish && !ctx->tc4_teams && h_offset_mirror == nullptr;
     if (tc) {   // every frame expanded once per call; the scans then read only the expanded copy
         fin.splits = plan.splits * bf_tc_partials(ctx);
         uint8_t* e = nullptr;
@@ -310,14 +332,20 @@ int batch_core(slamgpu_ctx* ctx, const uint8_t* d_desc, const int32_t* d_frame_o
     Carver ws(ctx->d_ws.ptr);
     uint2* keys = ws.take<uint2>(per_pair * std::min(n_pairs, slice_pairs));
     if (d_offset) SG_CUDA(cudaMemsetAsync(d_offset, 0, sizeof(int32_t), ctx->stream));
-    for (int p0 = 0, np = 0; p0 < n_pairs; p0 += np) {
+    int slice_no = 0;
+    for (int p0 = 0, np = 0; p0 < n_pairs; p0 += np, ++slice_no) {
         np = next_slice(ctx, n_pairs - p0, slice_pairs, d_offset != nullptr);
         const int32_t* pairs = d_pairs + 2 * static_cast<size_t>(p0);
         int32_t* out_train = d_offset ? d_out_train : d_out_train + static_cast<size_t>(p0) * max_rows;
+        if (push && (slice_no & 1)) out_train = push->rows2;
+        if (push && fused && slice_no >= 2)      // (the fused scan writes the rows itself: wait before it, not before the finish)
+            SG_CUDA(cudaStreamWaitEvent(ctx->stream, push->events[2 * (slice_no - 2) + 1], 0));
         if (tc) {
             const uint8_t* e = static_cast<const uint8_t*>(ctx->d_exp.ptr);
             if (fp4) {
-                SG_TRY(bf_tc4_launch_scan(ctx, plan, e, 0, e, 0, pitch, d_frame_offset, pairs, np, max_rows, cut, keys));
+                const Tc4Fuse fz{max_dist, ratio, out_train, d_out_count + p0};
+                SG_TRY(bf_tc4_launch_scan(ctx, plan, e, 0, e, 0, pitch, d_frame_offset, pairs, np, max_rows, cut, keys,
+                                          fused ? &fz : nullptr));
             } else {
                 SG_TRY(bf_tc_launch_scan(ctx, plan, e, 0, e, 0, pitch, d_frame_offset, pairs, np, max_rows, cut, keys));
             }
@@ -331,8 +359,27 @@ int batch_core(slamgpu_ctx* ctx, const uint8_t* d_desc, const int32_t* d_frame_o
             if (after_slice) SG_TRY((*after_slice)(p0, np));
             continue;
         }
-        SG_TRY(bf_launch_finish_filter(ctx, fin, keys, 0, 0, d_frame_offset, pairs, np, max_rows, max_dist, ratio,
-                                       out_train, d_out_count + p0));
+        if (push) {
+            cudaStream_t side = push->stream;
+            if (!fused) {
+                if (slice_no >= 2)      // the rows scratch of slice s - 2 must have been compacted
+                    SG_CUDA(cudaStreamWaitEvent(ctx->stream, push->events[2 * (slice_no - 2) + 1], 0));
+                SG_TRY(bf_launch_finish_filter(ctx, fin, keys, 0, 0, d_frame_offset, pairs, np, max_rows, max_dist, ratio,
+                                               out_train, d_out_count + p0));
+            }
+            SG_TRY(bf_launch_scan_counts(ctx, d_out_count + p0, np, d_offset + p0, push->h_offset_mirror + p0));
+            SG_CUDA(cudaEventRecord(push->events[2 * slice_no], ctx->stream));
+            SG_CUDA(cudaStreamWaitEvent(side, push->events[2 * slice_no], 0));
+            SG_TRY(bf_launch_compact(ctx, out_train, d_frame_offset, pairs, 0, np, max_rows, d_offset + p0, d_query_list,
+                                     d_train_list, capacity, side));
+            SG_TRY(bf_launch_push_lists(ctx, d_offset + p0, np, d_query_list, d_train_list, push->h_query, push->h_train,
+                                        capacity, side));
+            SG_CUDA(cudaEventRecord(push->events[2 * slice_no + 1], side));
+            continue;
+        }
+        if (!fused)
+            SG_TRY(bf_launch_finish_filter(ctx, fin, keys, 0, 0, d_frame_offset, pairs, np, max_rows, max_dist, ratio,
+                                           out_train, d_out_count + p0));
         if (d_offset) {
             SG_TRY(bf_launch_scan_counts(ctx, d_out_count + p0, np, d_offset + p0, h_offset_mirror ? h_offset_mirror + p0 : nullptr));
             SG_TRY(bf_launch_compact(ctx, out_train, d_frame_offset, pairs, 0, np, max_rows, d_offset + p0,
@@ -466,7 +513,9 @@ int batch_host(slamgpu_ctx* ctx, const uint8_t* desc, const uint8_t* d_desc_res,
     const bool tiny = ctx->bf_zero_copy && direct && n_pairs <= 256 && n_pairs <= slice;
     const size_t b_desc = resident ? 0 : Carver::padded(n_rows * 32),
                  b_off = resident ? 0 : Carver::padded(sizeof(int32_t) * (n_frames + 1)), b_pairs = Carver::padded(sizeof(int32_t) * 2 * n_pairs);
-    const size_t b_rows = Carver::padded(sizeof(int32_t) * static_cast<size_t>(slice) * std::max(max_rows, 1) * (tiny ? 2 : 1)),
+    // batches into pinned result lists: compaction and the lists' way home on a second stream (BatchPush)
+    const bool push_mode = ctx->bf_push && direct && !tiny;
+    const size_t b_rows = Carver::padded(sizeof(int32_t) * static_cast<size_t>(slice) * std::max(max_rows, 1) * ((tiny || push_mode) ? 2 : 1)),
                  b_count = Carver::padded(sizeof(int32_t) * n_pairs),
                  b_offset = Carver::padded(sizeof(int32_t) * (static_cast<size_t>(n_pairs) + 1)),
                  b_list = Carver::padded(sizeof(int32_t) * static_cast<size_t>(capacity));
@@ -484,7 +533,7 @@ int batch_host(slamgpu_ctx* ctx, const uint8_t* desc, const uint8_t* d_desc_res,
         d_off = doff;
     }
     int32_t* d_pairs = dio.take<int32_t>(2 * static_cast<size_t>(n_pairs));
-    int32_t* d_rows = dio.take<int32_t>(static_cast<size_t>(slice) * std::max(max_rows, 1) * (tiny ? 2 : 1));
+    int32_t* d_rows = dio.take<int32_t>(static_cast<size_t>(slice) * std::max(max_rows, 1) * ((tiny || push_mode) ? 2 : 1));
     int32_t* d_count = dio.take<int32_t>(n_pairs);
     int32_t* d_offset = dio.take<int32_t>(static_cast<size_t>(n_pairs) + 1);
     int32_t* d_ql = dio.take<int32_t>(static_cast<size_t>(capacity));
@@ -544,6 +593,42 @@ int batch_host(slamgpu_ctx* ctx, const uint8_t* desc, const uint8_t* d_desc_res,
         out_offset[0] = 0;
         std::memcpy(out_offset + 1, h_offset + 1, sizeof(int32_t) * static_cast<size_t>(n_pairs));
         *out_total = out_offset[n_pairs];
+        if (*out_total > capacity) return fail(SLAMGPU_ERR_NOMEM, "match list capacity too small; *out_total holds the size needed");
+        return SLAMGPU_OK;
+    }
+    if (push_mode) {
+        BatchPush pm;
+        pm.stream = ctx->copy_stream;
+        pm.rows2 = d_rows + static_cast<size_t>(slice) * std::max(max_rows, 1);
+        pm.h_query = out_query;
+        pm.h_train = out_train;
+        pm.h_offset_mirror = h_offset;           // (shares the staging block with the uploads: stream-ordered behind them)
+        pm.events = ctx->slice_events.data();    // 3 per slice exist, 2 per slice are used
+        const int rc1 = batch_core(ctx, d_desc, d_off, n_frames, d_pairs, n_pairs, max_rows, max_dist, ratio, d_rows, d_count,
+                                   d_offset, d_ql, d_tl, capacity, slice, nullptr, few ? &used : nullptr, nullptr, &pm);
+        const double t_queued = trace ? now() : 0.0;
+        const cudaError_t e1 = cudaStreamSynchronize(ctx->copy_stream), e2 = cudaStreamSynchronize(ctx->stream);
+        if (rc1 != SLAMGPU_OK) return rc1;
+        SG_CUDA(e1);
+        SG_CUDA(e2);
+        if (trace) {
+            const double t_end = now();
+            ctx->trace_us[0] += t_queued - t_call;
+            ctx->trace_us[1] += t_end - t_queued;
+            ctx->trace_us[3] += t_end - t_call;
+            ctx->trace_calls++;
+        }
+        out_offset[0] = 0;
+        std::memcpy(out_offset + 1, h_offset + 1, sizeof(int32_t) * static_cast<size_t>(n_pairs));
+        *out_total = out_offset[n_pairs];
+        bool wrapped = false;                    // one slice adds < 2^31 entries: a wrapped total shows as an end below its begin
+        for (int p0 = 0, left = n_pairs; left > 0;) {
+            const int np = next_slice(ctx, left, slice, true);
+            wrapped = wrapped || out_offset[p0 + np] < out_offset[p0];
+            p0 += np;
+            left -= np;
+        }
+        if (wrapped) return fail(SLAMGPU_ERR_INVALID, "more than 2^31 - 1 matches in one batch call: split the pair list");
         if (*out_total > capacity) return fail(SLAMGPU_ERR_NOMEM, "match list capacity too small; *out_total holds the size needed");
         return SLAMGPU_OK;
     }

@@ -743,11 +743,12 @@ int bf_launch_finish_raw(slamgpu_ctx* ctx, const BfPlan& plan, const uint2* d_ke
 
 int bf_launch_finish_filter(slamgpu_ctx* ctx, const BfPlan& plan, const uint2* d_keys, int nq, int nt,
                             const int32_t* d_frame_offset, const int32_t* d_pairs, int n_pairs, int max_rows,
-                            float max_dist, float ratio, int32_t* d_out_train, int32_t* d_out_count)
+                            float max_dist, float ratio, int32_t* d_out_train, int32_t* d_out_count, cudaStream_t stream)
 {
     if (n_pairs <= 0 || max_rows <= 0) return SLAMGPU_OK;
+    if (stream == nullptr) stream = ctx->stream;
     // d_out_count null: the caller counts the surviving rows itself (the single-pair host call does)
-    if (d_out_count) SG_CUDA(cudaMemsetAsync(d_out_count, 0, sizeof(int32_t) * n_pairs, ctx->stream));
+    if (d_out_count) SG_CUDA(cudaMemsetAsync(d_out_count, 0, sizeof(int32_t) * n_pairs, stream));
     FilterArgs a;
     a.keys = d_keys;
     a.splits = plan.splits;
@@ -769,7 +770,7 @@ int bf_launch_finish_filter(slamgpu_ctx* ctx, const BfPlan& plan, const uint2* d
         b.out_train = d_out_train + static_cast<size_t>(p0) * max_rows;
         b.out_count = d_out_count ? d_out_count + p0 : nullptr;
         const dim3 blk = finish_block(plan.splits);
-        bf_finish_filter_kernel<<<dim3((rows + blk.x - 1) / blk.x, np), blk, 0, ctx->stream>>>(b);
+        bf_finish_filter_kernel<<<dim3((rows + blk.x - 1) / blk.x, np), blk, 0, stream>>>(b);
         ctx->launches++;
     }
     SG_CUDA(cudaGetLastError());
@@ -803,9 +804,10 @@ int bf_launch_mutual_direct(slamgpu_ctx* ctx, const BfPlan& row_plan, const uint
     return SLAMGPU_OK;
 }
 
-int bf_launch_scan_counts(slamgpu_ctx* ctx, const int32_t* d_count, int n, int32_t* d_offset, int32_t* h_offset_mirror)
+int bf_launch_scan_counts(slamgpu_ctx* ctx, const int32_t* d_count, int n, int32_t* d_offset, int32_t* h_offset_mirror,
+                          cudaStream_t stream)
 {
-    bf_scan_counts_kernel<<<1, 1024, 0, ctx->stream>>>(d_count, n, d_offset, h_offset_mirror);
+    bf_scan_counts_kernel<<<1, 1024, 0, stream ? stream : ctx->stream>>>(d_count, n, d_offset, h_offset_mirror);
     ctx->launches++;
     SG_CUDA(cudaGetLastError());
     return SLAMGPU_OK;
@@ -813,13 +815,44 @@ int bf_launch_scan_counts(slamgpu_ctx* ctx, const int32_t* d_count, int n, int32
 
 int bf_launch_compact(slamgpu_ctx* ctx, const int32_t* d_out_train, const int32_t* d_frame_offset,
                       const int32_t* d_pairs, int nq_single, int n_pairs, int max_rows, const int32_t* d_offset,
-                      int32_t* d_query_list, int32_t* d_train_list, int64_t capacity)
+                      int32_t* d_query_list, int32_t* d_train_list, int64_t capacity, cudaStream_t stream)
 {
     if (n_pairs <= 0) return SLAMGPU_OK;
     const int warps_per_cta = 8;
-    bf_compact_kernel<<<(n_pairs + warps_per_cta - 1) / warps_per_cta, warps_per_cta * 32, 0, ctx->stream>>>(
+    bf_compact_kernel<<<(n_pairs + warps_per_cta - 1) / warps_per_cta, warps_per_cta * 32, 0, stream ? stream : ctx->stream>>>(
         d_out_train, d_frame_offset, d_pairs, nq_single, n_pairs, max_rows, d_offset, d_query_list, d_train_list,
         static_cast<long long>(capacity));
+    ctx->launches++;
+    SG_CUDA(cudaGetLastError());
+    return SLAMGPU_OK;
+}
+
+namespace {
+__global__ void __launch_bounds__(256) bf_push_lists_kernel(const int32_t* __restrict__ offset, int n_pairs,
+                                                            const int32_t* __restrict__ ql, const int32_t* __restrict__ tl,
+                                                            int32_t* h_ql, int32_t* h_tl, long long capacity)
+{
+    const long long begin = offset[0];
+    long long end = offset[n_pairs];
+    if (end > capacity) end = capacity;                  // an undersized list is reported by the host from the offsets
+    if (begin < 0 || end <= begin) return;               // (a wrapped int32 total as well)
+    const long long n = end - begin, stride = static_cast<long long>(gridDim.x) * blockDim.x;
+    // the two lists as one index space: warps write whole 128-byte lines towards the host
+    for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < 2 * n; i += stride) {
+        if (i < n) h_ql[begin + i] = ql[begin + i];
+        else h_tl[begin + i - n] = tl[begin + i - n];
+    }
+}
+} // namespace
+
+int bf_launch_push_lists(slamgpu_ctx* ctx, const int32_t* d_offset, int n_pairs, const int32_t* d_query_list,
+                         const int32_t* d_train_list, int32_t* h_query_list, int32_t* h_train_list, int64_t capacity,
+                         cudaStream_t stream)
+{
+    if (n_pairs <= 0) return SLAMGPU_OK;
+    // few CTAs: the copy shares the SMs with the next slice's scan and is bound by the PCIe link, not by threads
+    bf_push_lists_kernel<<<32, 256, 0, stream>>>(d_offset, n_pairs, d_query_list, d_train_list, h_query_list, h_train_list,
+                                                 static_cast<long long>(capacity));
     ctx->launches++;
     SG_CUDA(cudaGetLastError());
     return SLAMGPU_OK;

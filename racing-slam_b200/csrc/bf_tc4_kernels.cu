@@ -48,7 +48,8 @@ constexpr int kOff4AX = kOff4B + kB4Stages * kB4Bytes;     // constant K = 64 sl
 constexpr int kOff4BX = kOff4AX + 128 * 32;                // ... of B: this CTA's 120 rows x 32 B (4 KB reserved)
 constexpr int kOff4Bar = kOff4BX + 128 * 32;               // 24 mbarriers
 constexpr int kOff4TmemSlot = kOff4Bar + 32 * 8;
-constexpr int kTc4SmemBytes = kOff4TmemSlot + 16;
+constexpr int kOff4Xch = kOff4TmemSlot + 16;               // fused finish: 2 buffers x 128 rows x uint2 (2 KB)
+constexpr int kTc4SmemBytes = kOff4Xch + 2 * 128 * 8;
 // TMEM columns: accumulator stage 0 at 0, stage 1 at 256, scale factors 1.0 at 496, 2^10 at 504, and the
 // constant slice's (2^0 for block 0, 2^7 for block 1) at 240
 constexpr uint32_t kAccStride = 256, kSfOne = 496, kSfBig = 504, kSfMix = 240;
@@ -159,11 +160,19 @@ struct Tc4Args {
     int thr_dot;                   // a train row matters iff dot = 256 - 2 * distance >= thr_dot
     int thr4;                      // thr_dot rounded down to a multiple of 4: what the bit tests of the hot path use
     uint2* keys;
+    // FUSED FINISH (splits == 1: a unit sees every train row of its pair).  The two warps that hold the halves of a
+    // row's columns merge their partial top-2 through shared memory at the end of the unit and apply the caller's
+    // filter (src/MapMatcher.cpp:151-161, as bf_finish_filter_kernel) themselves: out_train[pair][row] and the
+    // pair's count are written by the scan, no key records and no finish launch (2 % of a batch step).
+    int fuse;
+    float max_dist, ratio;
+    int32_t* out_train;            // [pair][max_rows]
+    int32_t* out_count;            // [pair], zeroed by the launcher; may be null
 };
 
 struct Unit4 {
     bool valid, narrow_last;
-    int pair, split, row0, nq, t_begin, n_btiles, t_end;
+    int pair, split, row0, nq, nt, t_begin, n_btiles, t_end;
     const uint8_t* q;
     const uint8_t* t;
 };
@@ -186,6 +195,7 @@ __device__ __forceinline__ Unit4 decode_unit4(const Tc4Args& a, long long u)
         un.t = a.exp_t + static_cast<long long>(ft) * a.frame_pitch_bytes;
     }
     un.nq = nq;
+    un.nt = nt;
     un.row0 = tile * kQ4;
     un.t_begin = min(un.split * a.t_per_split, nt);
     un.t_end = min(un.t_begin + a.t_per_split, nt);
@@ -653,9 +663,16 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTc4Threads, 1) bf_t
         // sat between "accumulator full" and the first load)
         uint32_t taddr_s0 = tmem_base + lane_col, taddr_s1 = tmem_base + lane_col + kAccStride;
         asm volatile("" : "+r"(taddr_s0), "+r"(taddr_s1));
+        uint2* const xch = reinterpret_cast<uint2*>(smem + kOff4Xch);
+        uint32_t u_it = 0;              // valid units seen: parity selects the exchange buffer of the fused finish
         for (long long u = cid; u < a.n_units; u += n_clusters) {
             const Unit4 un = decode_unit4(a, u);
-            if (!un.valid) continue;
+            if (!un.valid) {
+                // a ragged batch: this pair has no query rows in this tile; its rows of the padded output read -1
+                if (a.fuse && g == 1 && un.row0 + row_in_tile < a.max_rows)
+                    a.out_train[static_cast<size_t>(un.pair) * a.max_rows + un.row0 + row_in_tile] = -1;
+                continue;
+            }
             for (int bt = 0; bt < un.n_btiles; ++bt, ++c_it) {
                 const uint32_t sc = c_it & 1u;
                 const uint32_t taddr = sc ? taddr_s1 : taddr_s0;
@@ -724,8 +741,33 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTc4Threads, 1) bf_t
             }
             // this warp's partial top-2 of the unit (no keys at all when the unit had no train rows)
             const int row = un.row0 + row_in_tile;
-            if (row < un.nq)
+            if (a.fuse) {
+                // the warp with the first 120 columns of these 32 rows hands its partial to the warp with the other 120
+                // (same quad): named barrier of the two warps, exchange buffer by unit parity (the first warp can be at
+                // most one barrier ahead)
+                uint2* const slot = xch + (u_it & 1u) * 128 + quad * 32 + lane;
+                if (g == 0) *slot = make_uint2(b0, b1);
+                asm volatile("bar.sync %0, 64;" ::"r"(1 + quad) : "memory");
+                if (g == 1) {
+                    const uint2 p = *slot;
+                    uint32_t m0 = min(b0, p.x);
+                    uint32_t m1 = min(min(max(b0, p.x), b1), p.y);         // second smallest of the four keys
+                    bool keep = false;
+                    int train = -1;
+                    if (row < un.nq && m0 != kKeyNone) {
+                        const float d0 = static_cast<float>(m0 >> kIdxBits);
+                        keep = !(d0 > a.max_dist);
+                        if (keep && un.nt >= 2 && m1 != kKeyNone) keep = !(d0 > __fmul_rn(a.ratio, static_cast<float>(m1 >> kIdxBits)));
+                        if (keep) train = static_cast<int>(m0 & kIdxMask);
+                    }
+                    if (row < a.max_rows) a.out_train[static_cast<size_t>(un.pair) * a.max_rows + row] = train;
+                    const unsigned ballot = __ballot_sync(0xFFFFFFFFu, keep);
+                    if (a.out_count != nullptr && lane == 0 && ballot != 0u) atomicAdd(&a.out_count[un.pair], __popc(ballot));
+                }
+                ++u_it;
+            } else if (row < un.nq) {
                 a.keys[((static_cast<size_t>(un.pair) * a.splits + un.split) * 2 + g) * a.max_rows + row] = make_uint2(b0, b1);
+            }
             b0 = kKeyNone;
             b1 = kKeyNone;
         }
@@ -906,7 +948,7 @@ int bf_tc4_launch_expand_pair(slamgpu_ctx* ctx, const uint8_t* d_q, int nq, cons
 // d_cut in [1, 256]: train rows at Hamming distance >= d_cut may be left out of the top-2.
 int bf_tc4_launch_scan(slamgpu_ctx* ctx, const BfPlan& plan, const uint8_t* d_exp_q, int nq, const uint8_t* d_exp_t,
                        int nt, int pitch_rows, const int32_t* d_frame_offset, const int32_t* d_pairs, int n_pairs,
-                       int max_rows, int d_cut, uint2* d_keys)
+                       int max_rows, int d_cut, uint2* d_keys, const Tc4Fuse* fuse)
 {
     // per-DEVICE function attribute: one flag per context (see bf_tc_launch_scan)
     if (!ctx->tc4_attr_set) {
@@ -933,6 +975,18 @@ int bf_tc4_launch_scan(slamgpu_ctx* ctx, const BfPlan& plan, const uint8_t* d_ex
     a.thr_dot = 256 - 2 * (d_cut - 1);                      // -242 .. 256
     a.thr4 = (a.thr_dot + 256) / 4 * 4 - 256;               // rounded DOWN to a multiple of 4: -244 .. 256
     a.keys = d_keys;
+    a.fuse = 0;
+    a.max_dist = a.ratio = 0.0f;
+    a.out_train = a.out_count = nullptr;
+    if (fuse != nullptr) {
+        SG_CHECK(plan.splits == 1 && !ctx->tc4_teams, "the fused finish needs one train split and the default epilogue");
+        a.fuse = 1;
+        a.max_dist = fuse->max_dist;
+        a.ratio = fuse->ratio;
+        a.out_train = fuse->d_out_train;
+        a.out_count = fuse->d_out_count;
+        if (fuse->d_out_count && n_pairs > 0) SG_CUDA(cudaMemsetAsync(fuse->d_out_count, 0, sizeof(int32_t) * n_pairs, ctx->stream));
+    }
     if (a.n_units <= 0) return SLAMGPU_OK;
     const unsigned grid = 2u * static_cast<unsigned>(min(a.n_units, static_cast<long long>(ctx->n_sm / 2)));
     ProfScope prof(ctx, SLAMGPU_KERNEL_BF_SCAN);

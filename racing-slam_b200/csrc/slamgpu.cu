@@ -260,6 +260,10 @@ int slamgpu_create(int device, slamgpu_ctx** out)
     if (mr != nullptr) ctx->map_reserve = std::min(std::max(std::atoi(mr), 0), 1 << 28);
     const char* trb = std::getenv("SLAMGPU_TRACE_BATCH");
     ctx->trace_batch = trb != nullptr && trb[0] == '1';
+    const char* tff = std::getenv("SLAMGPU_TC4_FUSE_FINISH");
+    if (tff != nullptr) ctx->tc4_fuse_finish = tff[0] != '0';
+    const char* bpu = std::getenv("SLAMGPU_BF_PUSH");
+    if (bpu != nullptr) ctx->bf_push = bpu[0] != '0';
     const char* bzc = std::getenv("SLAMGPU_BF_ZEROCOPY");
     if (bzc != nullptr) ctx->bf_zero_copy = bzc[0] != '0';
     const char* pzc = std::getenv("SLAMGPU_PROJ_ZEROCOPY");

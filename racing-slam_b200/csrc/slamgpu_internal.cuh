@@ -188,6 +188,8 @@ struct slamgpu_ctx {
     int map_reserve = 1 << 18; // SLAMGPU_MAP_RESERVE: points reserved by a point set's first growth (4 observations each)
     bool kd_async = true;     // SLAMGPU_KD_ASYNC=0: build the KD-tree inside slamgpu_frame_upload instead of on a thread
     bool kd_speculate = true; // SLAMGPU_KD_SPECULATE=0: a match call waits for the KD-tree instead of running on the tree-free grid
+    bool tc4_fuse_finish = true;  // SLAMGPU_TC4_FUSE_FINISH=0: batches always run the finish kernel after the FP4 scan
+    bool bf_push = true;          // SLAMGPU_BF_PUSH=0: batch calls into pinned result lists bring their lists back by host-queued copies
     bool bf_zero_copy = true;     // SLAMGPU_BF_ZEROCOPY=0: single-pair brute-force calls download their results with a copy
     bool proj_zero_copy = true;   // SLAMGPU_PROJ_ZEROCOPY=0: small projection calls copy their lists / results instead of
                                   // letting the kernels read and write the pinned staging buffer directly
@@ -269,7 +271,8 @@ int bf_launch_finish_raw(slamgpu_ctx* ctx, const BfPlan& plan, const uint2* d_ke
 // Finish, filtered (match_descriptors): out_train[pair][q] / count[pair].
 int bf_launch_finish_filter(slamgpu_ctx* ctx, const BfPlan& plan, const uint2* d_keys, int nq, int nt,
                             const int32_t* d_frame_offset, const int32_t* d_pairs, int n_pairs, int max_rows,
-                            float max_dist, float ratio, int32_t* d_out_train, int32_t* d_out_count);
+                            float max_dist, float ratio, int32_t* d_out_train, int32_t* d_out_count,
+                            cudaStream_t stream = nullptr /* default: the context's stream */);
 // Cross-check mutuality from row partials and column partials.
 int bf_launch_mutual(slamgpu_ctx* ctx, const BfPlan& row_plan, const uint2* d_row_keys, int row_stride,
                      const BfPlan& col_plan, const uint2* d_col_keys, int col_stride, int nq, int nt,
@@ -286,10 +289,17 @@ int bf_launch_finish_compact(slamgpu_ctx* ctx, const BfPlan& plan, const uint2* 
 // slamgpu_knn2_dev_noalloc (bf_kernels.cu): resolve the fixed scratch array's device address (device current)
 int bf_noalloc_setup(int device);
 int bf_launch_scan_counts(slamgpu_ctx* ctx, const int32_t* d_count, int n, int32_t* d_offset /* n+1 */,
-                          int32_t* h_offset_mirror = nullptr /* n+1, device-addressable host memory */);
+                          int32_t* h_offset_mirror = nullptr /* n+1, device-addressable host memory */,
+                          cudaStream_t stream = nullptr);
 int bf_launch_compact(slamgpu_ctx* ctx, const int32_t* d_out_train, const int32_t* d_frame_offset,
                       const int32_t* d_pairs, int nq_single, int n_pairs, int max_rows, const int32_t* d_offset,
-                      int32_t* d_query_list, int32_t* d_train_list, int64_t capacity);
+                      int32_t* d_query_list, int32_t* d_train_list, int64_t capacity, cudaStream_t stream = nullptr);
+// Entries [offset[0], offset[n_pairs]) of the two device lists -> the same positions of two device-addressable HOST
+// lists (pinned memory), copied by SM stores: the range comes from the device's own offsets, so no host round trip
+// sits between a slice's compaction and its way home.
+int bf_launch_push_lists(slamgpu_ctx* ctx, const int32_t* d_offset, int n_pairs, const int32_t* d_query_list,
+                         const int32_t* d_train_list, int32_t* h_query_list, int32_t* h_train_list, int64_t capacity,
+                         cudaStream_t stream);
 
 // ---- brute force on the tensor cores (bf_tc_kernels.cu) ---------------------------------------
 // Expanded descriptors: 256 int8 per row in the UMMA canonical layout, frames at a pitch of
@@ -320,9 +330,16 @@ int bf_tc4_launch_expand_list(slamgpu_ctx* ctx, const uint8_t* d_src, const int3
                               int n_list, int pitch_rows, uint8_t* d_dst);
 int bf_tc4_launch_expand_pair(slamgpu_ctx* ctx, const uint8_t* d_q, int nq, const uint8_t* d_t, int nt, int pitch_rows,
                               uint8_t* d_dst);
+// fuse != null (plan.splits == 1 only): the scan applies the match_descriptors filter itself and writes
+// d_out_train [pair][max_rows] / d_out_count [pair] -- no key records, no finish launch
+struct Tc4Fuse {
+    float max_dist, ratio;
+    int32_t* d_out_train;
+    int32_t* d_out_count;
+};
 int bf_tc4_launch_scan(slamgpu_ctx* ctx, const BfPlan& plan, const uint8_t* d_exp_q, int nq, const uint8_t* d_exp_t,
                        int nt, int pitch_rows, const int32_t* d_frame_offset, const int32_t* d_pairs, int n_pairs,
-                       int max_rows, int d_cut, uint2* d_keys);
+                       int max_rows, int d_cut, uint2* d_keys, const Tc4Fuse* fuse = nullptr);
 
 // ---- projection (proj_kernels.cu) -----------------------------------------------------------
 struct ProjFrameArgs {

@@ -292,6 +292,65 @@ def test_short_batch_into_pinned_lists(oracle, pkg, monkeypatch, engine):
             del out
 
 
+@pytest.mark.parametrize("fuse,push", [("1", "1"), ("0", "1"), ("1", "0"), ("0", "0")])
+def test_fp4_ragged_batches_fused_finish_and_pushed_lists(oracle, pkg, monkeypatch, fuse, push):
+    """Batches on the FP4 engine with one train split per pair: the scan's epilogue merges, filters and writes the rows
+    itself (SLAMGPU_TC4_FUSE_FINISH=0: separate finish kernel), and with pinned result lists the compaction and the
+    lists' way home run on a second stream (SLAMGPU_BF_PUSH=0: host-queued copies).  Ragged frames -- empty, one
+    row, one row over a 256-row tile, several tiles -- so that pairs have query tiles without rows (padding written as
+    -1) and single-row train sets (k = 1: no ratio test); 300 pairs in slices of 64 (several slices in flight), the
+    device-resident form (padded rows exposed to the caller), and an undersized pinned list."""
+    import torch
+    monkeypatch.setenv("SLAMGPU_BF_ENGINE", "tc")
+    monkeypatch.setenv("SLAMGPU_TC4_FUSE_FINISH", fuse)
+    monkeypatch.setenv("SLAMGPU_BF_PUSH", push)
+    monkeypatch.setenv("SLAMGPU_BATCH_SLICE", "64")
+    sizes = [900, 0, 257, 1, 256, 33, 1300, 700]
+    db = pkg.synthetic.keyframe_db(len(sizes), 1300, 23, shared_frac=0.5)
+    frames = [db[i, :n] for i, n in enumerate(sizes)]
+    desc = np.concatenate(frames)
+    off = np.concatenate([[0], np.cumsum(sizes)]).astype(np.int32)
+    rng = np.random.default_rng(8)
+    pairs = np.concatenate([pkg.sharding.all_pairs(len(sizes)), pkg.sharding.all_pairs(len(sizes))[:, ::-1],
+                            rng.integers(0, len(sizes), (244, 2)).astype(np.int32)]).astype(np.int32)
+    assert len(pairs) == 300
+    want = {}
+    for a, b in {(int(a), int(b)) for a, b in pairs}:
+        want[(a, b)] = oracle.match_descriptors(frames[a], frames[b], 64.0, 0.75)
+    want_q = np.concatenate([want[(int(a), int(b))][0] for a, b in pairs])
+    want_t = np.concatenate([want[(int(a), int(b))][1] for a, b in pairs])
+    want_o = np.concatenate([[0], np.cumsum([len(want[(int(a), int(b))][0]) for a, b in pairs])])
+    assert want_o[-1] > 5000
+    with pkg.Context(0) as c:
+        for pinned in (True, False):
+            out = None
+            if pinned:
+                out = (pkg.pinned_empty(int(want_o[-1]) + 5, np.int32), pkg.pinned_empty(int(want_o[-1]) + 5, np.int32))
+            for _ in range(2):
+                o, ql, tl = c.match_descriptors_batch(desc, off, pairs, 64.0, 0.75, out=out)
+                assert np.array_equal(o, want_o) and np.array_equal(ql, want_q) and np.array_equal(tl, want_t), pinned
+        small = (pkg.pinned_empty(int(want_o[150]), np.int32), pkg.pinned_empty(int(want_o[150]), np.int32))
+        with pytest.raises(pkg.SlamGpuError) as e:
+            c.match_descriptors_batch(desc, off, pairs, 64.0, 0.75, out=small)
+        assert e.value.code == pkg.binding.ERR_NOMEM
+        assert np.array_equal(small[0], want_q[:len(small[0])])          # what fits is in place
+        # device-resident form: [pair][max_rows] rows, -1 where a pair has no such query row
+        d_desc, d_off, d_pairs = torch.from_numpy(desc).cuda(), torch.from_numpy(off).cuda(), torch.from_numpy(pairs).cuda()
+        max_rows = max(sizes)
+        d_out = torch.full((len(pairs), max_rows), -9, dtype=torch.int32, device="cuda")
+        d_cnt = torch.full((len(pairs),), -9, dtype=torch.int32, device="cuda")
+        torch.cuda.synchronize()
+        c.match_descriptors_batch_dev(d_desc.data_ptr(), d_off.data_ptr(), len(sizes), d_pairs.data_ptr(), len(pairs), max_rows,
+                                      64.0, 0.75, d_out.data_ptr(), d_cnt.data_ptr())
+        c.sync()
+        rows, cnt = d_out.cpu().numpy(), d_cnt.cpu().numpy()
+        for k, (a, b) in enumerate(pairs):
+            wq, wt = want[(int(a), int(b))]
+            expect = np.full(max_rows, -1, np.int32)
+            expect[wq] = wt
+            assert np.array_equal(rows[k], expect) and cnt[k] == len(wq), (k, a, b)
+
+
 def test_batch_capacity_error(ctx, pkg):
     db = pkg.synthetic.keyframe_db(3, 128, 1, shared_frac=0.9, max_flip=5)
     desc = db.reshape(-1, 32)
