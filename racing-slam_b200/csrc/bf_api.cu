@@ -280,7 +280,9 @@ int batch_core(slamgpu_ctx* ctx, const uint8_t* d_desc, const int32_t* d_frame_o
                const std::vector<int>* frames_used = nullptr,
                // a device-addressable host copy of the offsets (short calls: the kernels write results to host memory)
                int32_t* h_offset_mirror = nullptr,
-               const BatchPush* push = nullptr)
+               const BatchPush* push = nullptr,
+               // the frames' FP4-expanded copy, already built (resident database): no expansion launches
+               const uint8_t* exp4_ready = nullptr, int exp4_pitch = 0)
 {
     if (n_pairs == 0) return SLAMGPU_OK;
     if (max_rows == 0) {
@@ -298,10 +300,14 @@ int batch_core(slamgpu_ctx* ctx, const uint8_t* d_desc, const int32_t* d_frame_o
     // FP4 batches with one train split per pair: the scan filters and writes the rows itself (bf_tc4_kernels.cu: fused
     // finish); the short-call path keeps its own finish + compaction kernel
     const bool fused = fp4 && plan.splits == 1 && ctx->tc4_fuse_finish && !ctx->tc4_teams && h_offset_mirror == nullptr;
+    const uint8_t* exp_base = nullptr;          // the expanded copy the scans read
     if (tc) {   // every frame expanded once per call; the scans then read only the expanded copy
         fin.splits = plan.splits * bf_tc_partials(ctx);
         uint8_t* e = nullptr;
-        if (fp4) {
+        if (fp4 && exp4_ready != nullptr) {
+            pitch = exp4_pitch;
+            exp_base = exp4_ready;
+        } else if (fp4) {
             pitch = bf_tc4_pitch_rows(max_rows);
             SG_TRY(ensure_device_exp(ctx, bf_tc4_expanded_bytes(n_frames, max_rows)));
             e = static_cast<uint8_t*>(ctx->d_exp.ptr);
@@ -341,7 +347,7 @@ int batch_core(slamgpu_ctx* ctx, const uint8_t* d_desc, const int32_t* d_frame_o
         if (push && fused && slice_no >= 2)      // (the fused scan writes the rows itself: wait before it, not before the finish)
             SG_CUDA(cudaStreamWaitEvent(ctx->stream, push->events[2 * (slice_no - 2) + 1], 0));
         if (tc) {
-            const uint8_t* e = static_cast<const uint8_t*>(ctx->d_exp.ptr);
+            const uint8_t* e = exp_base ? exp_base : static_cast<const uint8_t*>(ctx->d_exp.ptr);
             if (fp4) {
                 const Tc4Fuse fz{max_dist, ratio, out_train, d_out_count + p0};
                 SG_TRY(bf_tc4_launch_scan(ctx, plan, e, 0, e, 0, pitch, d_frame_offset, pairs, np, max_rows, cut, keys,
@@ -494,12 +500,45 @@ int fetch_pair(slamgpu_ctx* ctx, const PairIo& io, const int32_t** h_a, const in
     return SLAMGPU_OK;
 }
 
+// The resident database's FP4-expanded copy, complete for frames [0, n_frames) (see KfDbDev).
+int kfdb_expanded(slamgpu_ctx* ctx, KfDbDev& d, int n_frames, int max_rows)
+{
+    const int pitch = bf_tc4_pitch_rows(max_rows);
+    const size_t stride = bf_tc4_expanded_bytes(1, max_rows), need = stride * static_cast<size_t>(n_frames);
+    if (d.exp4 == nullptr || d.exp4_pitch != pitch || need > d.exp4_bytes) {
+        const bool keep = d.exp4 != nullptr && d.exp4_pitch == pitch;
+        const size_t bytes = stride * static_cast<size_t>(std::max(2 * n_frames, 64));
+        uint8_t* p = nullptr;
+        const cudaError_t e = cudaMalloc(&p, bytes);
+        if (e != cudaSuccess) {
+            cudaGetLastError();
+            return fail(SLAMGPU_ERR_NOMEM, std::string("expanded key-frame store allocation failed: ") + cudaGetErrorString(e));
+        }
+        if (keep && d.exp4_frames > 0)
+            SG_CUDA(cudaMemcpyAsync(p, d.exp4, stride * static_cast<size_t>(d.exp4_frames), cudaMemcpyDeviceToDevice, ctx->stream));
+        if (d.exp4) {
+            SG_CUDA(cudaStreamSynchronize(ctx->stream));
+            cudaFree(d.exp4);
+        }
+        d.exp4 = p;
+        d.exp4_bytes = bytes;
+        d.exp4_pitch = pitch;
+        if (!keep) d.exp4_frames = 0;
+    }
+    if (d.exp4_frames < n_frames) {
+        SG_TRY(bf_tc4_launch_expand(ctx, d.desc, d.offset + d.exp4_frames, n_frames - d.exp4_frames, 0, pitch,
+                                    d.exp4 + stride * static_cast<size_t>(d.exp4_frames)));
+        d.exp4_frames = n_frames;
+    }
+    return SLAMGPU_OK;
+}
+
 // The host-buffer batch call behind slamgpu_match_descriptors_batch (descriptors uploaded per call) and
 // slamgpu_kfdb_match_pairs (d_desc_res / d_off_res: the resident database; nothing but the pair list goes up).
 int batch_host(slamgpu_ctx* ctx, const uint8_t* desc, const uint8_t* d_desc_res, const int32_t* d_off_res,
                const int32_t* frame_offset, int n_frames, int max_rows, const int32_t* pairs, int n_pairs, float max_dist,
                float ratio, int32_t* out_offset, int32_t* out_query, int32_t* out_train, int64_t capacity,
-               int64_t* out_total)
+               int64_t* out_total, KfDbDev* kf = nullptr)
 {
     const size_t n_rows = static_cast<size_t>(frame_offset[n_frames]);
     if (max_rows == 0) {   // every frame is empty: no matches (src/MapMatcher.cpp:139-141)
@@ -575,6 +614,15 @@ int batch_host(slamgpu_ctx* ctx, const uint8_t* desc, const uint8_t* d_desc_res,
         SG_CUDA(cudaEventRecord(off_ready, ctx->copy_stream));
         return SLAMGPU_OK;
     };
+    // resident database on the FP4 engine: its expanded copy is kept with it (only new key frames are expanded)
+    const uint8_t* exp4_ready = nullptr;
+    int exp4_pitch = 0;
+    if (kf != nullptr && ctx->kfdb_cache_exp && use_tc(ctx, max_rows, max_rows, n_pairs) &&
+        use_fp4(ctx, cut_for_filter(max_dist, ratio))) {
+        SG_TRY(kfdb_expanded(ctx, *kf, n_frames, max_rows));
+        exp4_ready = kf->exp4;
+        exp4_pitch = kf->exp4_pitch;
+    }
     std::vector<int> used;
     if (n_pairs <= 256) {                               // few pairs: name the frames they touch
         used.assign(pairs, pairs + 2 * static_cast<size_t>(n_pairs));
@@ -587,7 +635,8 @@ int batch_host(slamgpu_ctx* ctx, const uint8_t* desc, const uint8_t* d_desc_res,
         // stream, no events, one synchronisation.
         // (the offsets' host image shares the staging block with the pair list's upload: both are stream-ordered)
         const int rc1 = batch_core(ctx, d_desc, d_off, n_frames, d_pairs, n_pairs, max_rows, max_dist, ratio, d_rows, d_count,
-                                   d_offset, out_query, out_train, capacity, slice, nullptr, few ? &used : nullptr, h_offset);
+                                   d_offset, out_query, out_train, capacity, slice, nullptr, few ? &used : nullptr, h_offset,
+                                   nullptr, exp4_ready, exp4_pitch);
         if (rc1 != SLAMGPU_OK) return rc1;
         SG_TRY(wait_stream(ctx));
         out_offset[0] = 0;
@@ -605,7 +654,8 @@ int batch_host(slamgpu_ctx* ctx, const uint8_t* desc, const uint8_t* d_desc_res,
         pm.h_offset_mirror = h_offset;           // (shares the staging block with the uploads: stream-ordered behind them)
         pm.events = ctx->slice_events.data();    // 3 per slice exist, 2 per slice are used
         const int rc1 = batch_core(ctx, d_desc, d_off, n_frames, d_pairs, n_pairs, max_rows, max_dist, ratio, d_rows, d_count,
-                                   d_offset, d_ql, d_tl, capacity, slice, nullptr, few ? &used : nullptr, nullptr, &pm);
+                                   d_offset, d_ql, d_tl, capacity, slice, nullptr, few ? &used : nullptr, nullptr, &pm,
+                                   exp4_ready, exp4_pitch);
         const double t_queued = trace ? now() : 0.0;
         const cudaError_t e1 = cudaStreamSynchronize(ctx->copy_stream), e2 = cudaStreamSynchronize(ctx->stream);
         if (rc1 != SLAMGPU_OK) return rc1;
@@ -633,7 +683,8 @@ int batch_host(slamgpu_ctx* ctx, const uint8_t* desc, const uint8_t* d_desc_res,
         return SLAMGPU_OK;
     }
     const int rc = batch_core(ctx, d_desc, d_off, n_frames, d_pairs, n_pairs, max_rows, max_dist, ratio, d_rows, d_count,
-                              d_offset, d_ql, d_tl, capacity, slice, &after_slice, few ? &used : nullptr);
+                              d_offset, d_ql, d_tl, capacity, slice, &after_slice, few ? &used : nullptr, nullptr, nullptr,
+                              exp4_ready, exp4_pitch);
     if (rc != SLAMGPU_OK) {
         cudaStreamSynchronize(ctx->copy_stream);
         return rc;
@@ -701,6 +752,7 @@ void free_kfdb(KfDbDev& d)
 {
     if (d.desc) cudaFree(d.desc);
     if (d.offset) cudaFree(d.offset);
+    if (d.exp4) cudaFree(d.exp4);
     d = KfDbDev();
 }
 
@@ -914,11 +966,11 @@ int slamgpu_kfdb_match_pairs(slamgpu_ctx* ctx, int db_id, const int32_t* pairs, 
     auto it = ctx->kf_dbs.find(db_id);
     if (it == ctx->kf_dbs.end() || it->second.h_offset.size() < 2)
         return fail(SLAMGPU_ERR_NOTFOUND, "unknown or empty key-frame database id");
-    const KfDbDev& d = it->second;
+    KfDbDev& d = it->second;
     const int n_frames = static_cast<int>(d.h_offset.size()) - 1;
     for (int p = 0; p < 2 * n_pairs; ++p) SG_CHECK(pairs[p] >= 0 && pairs[p] < n_frames, "pair names an unknown frame");
     return batch_host(ctx, nullptr, d.desc, d.offset, d.h_offset.data(), n_frames, d.max_rows, pairs, n_pairs, max_dist,
-                      ratio, out_offset, out_query, out_train, capacity, out_total);
+                      ratio, out_offset, out_query, out_train, capacity, out_total, &d);
 }
 
 int slamgpu_knn2_dev(slamgpu_ctx* ctx, const uint8_t* d_query, int nq, const uint8_t* d_train, int nt,

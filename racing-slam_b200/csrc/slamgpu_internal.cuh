@@ -162,6 +162,12 @@ struct KfDbDev {
     int cap_frames = 0;
     int max_rows = 0;                   // largest frame
     std::vector<int32_t> h_offset;      // [n_frames + 1], h_offset[0] = 0
+    // the FP4-expanded copy the tensor-core scan reads (128 B per row, `exp4_pitch` rows per frame), kept with the
+    // database: built on the first query that needs it and extended frame by frame afterwards, so a query expands
+    // only the key frames appended since the last one (a larger frame than any before changes the pitch: rebuilt)
+    uint8_t* exp4 = nullptr;
+    size_t exp4_bytes = 0;
+    int exp4_pitch = 0, exp4_frames = 0;
 };
 
 struct Arena {
@@ -188,6 +194,7 @@ struct slamgpu_ctx {
     int map_reserve = 1 << 18; // SLAMGPU_MAP_RESERVE: points reserved by a point set's first growth (4 observations each)
     bool kd_async = true;     // SLAMGPU_KD_ASYNC=0: build the KD-tree inside slamgpu_frame_upload instead of on a thread
     bool kd_speculate = true; // SLAMGPU_KD_SPECULATE=0: a match call waits for the KD-tree instead of running on the tree-free grid
+    bool kfdb_cache_exp = true;   // SLAMGPU_KFDB_CACHE=0: the resident key-frame database is expanded anew by every query
     bool tc4_fuse_finish = true;  // SLAMGPU_TC4_FUSE_FINISH=0: batches always run the finish kernel after the FP4 scan
     bool bf_push = true;          // SLAMGPU_BF_PUSH=0: batch calls into pinned result lists bring their lists back by host-queued copies
     bool bf_zero_copy = true;     // SLAMGPU_BF_ZEROCOPY=0: single-pair brute-force calls download their results with a copy
