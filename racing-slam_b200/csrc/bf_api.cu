@@ -243,6 +243,7 @@ template <class F> int for_frame_runs(int n_frames, const std::vector<int>* used
 // time -- sat between two scans.)  The rows scratch is double-buffered: finish of slice s + 2 waits for the compaction
 // of slice s.  Measured on one box: resident-database batches 9,558 -> 9,692 G/s.  Moving the finish kernel to the
 // second stream as well (scans back to back) was SLOWER, 9,483: its 131k CTAs get in the way of the persistent scan.
+constexpr int kPushTaperFloor = 2048;
 struct BatchPush {
     cudaStream_t stream;          // the second stream
     int32_t* rows2;               // second rows scratch [slice_pairs x max_rows]
@@ -260,10 +261,10 @@ constexpr size_t kBatchScratchBytes = size_t(256) << 20;
 // (each takes half of what is left, down to one wave of CTA pairs), which leaves a tail copy of a few hundred
 // pairs instead of a full slice -- with eight ranks finishing a step at the same moment the full-size tail
 // copies collided on the host.
-int next_slice(const slamgpu_ctx* ctx, int remaining, int slice_pairs, bool taper)
+int next_slice(const slamgpu_ctx* ctx, int remaining, int slice_pairs, bool taper, int floor_pairs_min = 0)
 {
     if (!taper || remaining > 2 * slice_pairs) return std::min(slice_pairs, remaining);
-    const int floor_pairs = std::max(ctx->n_sm * 2, 64);
+    const int floor_pairs = std::max(std::max(ctx->n_sm * 2, 64), floor_pairs_min);
     if (remaining <= floor_pairs) return std::min(remaining, slice_pairs);
     return std::min(slice_pairs, std::max((remaining + 1) / 2, floor_pairs));
 }
@@ -340,7 +341,8 @@ int batch_core(slamgpu_ctx* ctx, const uint8_t* d_desc, const int32_t* d_frame_o
     if (d_offset) SG_CUDA(cudaMemsetAsync(d_offset, 0, sizeof(int32_t), ctx->stream));
     int slice_no = 0;
     for (int p0 = 0, np = 0; p0 < n_pairs; p0 += np, ++slice_no) {
-        np = next_slice(ctx, n_pairs - p0, slice_pairs, d_offset != nullptr);
+        // (push mode: no host work per slice; the taper stops at 2048 pairs -- the tail is that slice's compaction and copy)
+        np = next_slice(ctx, n_pairs - p0, slice_pairs, d_offset != nullptr, push ? kPushTaperFloor : 0);
         const int32_t* pairs = d_pairs + 2 * static_cast<size_t>(p0);
         int32_t* out_train = d_offset ? d_out_train : d_out_train + static_cast<size_t>(p0) * max_rows;
         if (push && (slice_no & 1)) out_train = push->rows2;
@@ -673,7 +675,7 @@ int batch_host(slamgpu_ctx* ctx, const uint8_t* desc, const uint8_t* d_desc_res,
         *out_total = out_offset[n_pairs];
         bool wrapped = false;                    // one slice adds < 2^31 entries: a wrapped total shows as an end below its begin
         for (int p0 = 0, left = n_pairs; left > 0;) {
-            const int np = next_slice(ctx, left, slice, true);
+            const int np = next_slice(ctx, left, slice, true, kPushTaperFloor);
             wrapped = wrapped || out_offset[p0 + np] < out_offset[p0];
             p0 += np;
             left -= np;
