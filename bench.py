@@ -42,7 +42,8 @@ ALU_PER_CLK_PER_SM = 64                # LOP3 / VIMNMX lanes per clock per SM (n
 ALU_PER_COMPARISON = 17.5
 POPC_PER_COMPARISON_CSA = 4
 NCU_SCAN_DRAM_BYTES_512_PAIRS = 7.2e6  # profiles/r01_ncu_full_prof_bf_scan_v2.txt
-NCU_TC4_DRAM_BYTES_1024_PAIRS = 57.3e6  # profiles/r02_ncu_full_bf_tc4_scan.txt (27.9 MB read + 29.4 MB written; mostly the partial-key records)
+NCU_TC4_DRAM_BYTES_1024_PAIRS = 30.0e6  # profiles/r02_final_ncu_full_bf_tc4_scan.txt (27.5 MB read + 2.5 MB written: with the fused finish the scan
+                                        # writes the filtered rows, no partial-key records; r02_ncu_full_bf_tc4_scan.txt before: 57.3 MB)
 
 
 def parse_args():
@@ -521,7 +522,7 @@ def run_ours(args, rank, local_rank, world):
             "bound": "tensor", "achieved": tflops, "peak": peak_tf, "unit": "TFLOP/s", "frac": tflops / peak_tf,
             "traffic": NCU_TC4_DRAM_BYTES_1024_PAIRS * pairs_per_launch / 1024.0,
             "traffic_basis": "ncu --set full dram__bytes_read+write of one 1024-pair bf_tc4_scan_kernel launch "
-                             "(profiles/r02_ncu_full_bf_tc4_scan.txt: 27.9 MB read + 29.4 MB written), scaled to this launch's pair count",
+                             "(profiles/r02_final_ncu_full_bf_tc4_scan.txt: 27.5 MB read + 2.5 MB written), scaled to this launch's pair count",
             "kernel": "bf_tc4_scan_kernel", "launches": scan_launches, "avg_launch_ms": avg_ms,
             "share_of_step": scan_ms / ms_dev, "achieved_gcmp_s": achieved,
             "peak_basis": f"4 x measured dense bf16 ({peaks['bf16_tflops']:.0f} TFLOP/s burst, {peaks['source']}); algorithmic work "
