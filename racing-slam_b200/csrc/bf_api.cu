@@ -107,7 +107,7 @@ int tc_expand_pair(slamgpu_ctx* ctx, const uint8_t* dq, int nq, const uint8_t* d
 
 // scan query-set `qi` against train-set `ti` (0 or 1: the two expanded sets of tc_expand_pair)
 int tc_scan_pair(slamgpu_ctx* ctx, int qi, int nq, int ti, int nt, int pitch_rows, int d_cut, bool fp4, uint2* keys,
-                 TcPair& out)
+                 TcPair& out, uint32_t* col_keys = nullptr)
 {
     out.plan = tc_plan(ctx, nq, nt, 1, fp4);
     out.fin = out.plan;
@@ -117,8 +117,9 @@ int tc_scan_pair(slamgpu_ctx* ctx, int qi, int nq, int ti, int nt, int pitch_row
     const size_t set_bytes = static_cast<size_t>(pitch_rows) * (fp4 ? 128 : 256);
     if (fp4) {
         return bf_tc4_launch_scan(ctx, out.plan, e + qi * set_bytes, nq, e + ti * set_bytes, nt, pitch_rows, nullptr,
-                                  nullptr, 1, nq, d_cut, keys);
+                                  nullptr, 1, nq, d_cut, keys, nullptr, col_keys);
     }
+    SG_CHECK(col_keys == nullptr, "column minima come from the fp4 scan only");
     return bf_tc_launch_scan(ctx, out.plan, e + qi * set_bytes, nq, e + ti * set_bytes, nt, pitch_rows, nullptr, nullptr,
                              1, nq, d_cut, keys);
 }
@@ -166,6 +167,20 @@ int crosscheck_core(slamgpu_ctx* ctx, const uint8_t* dq, int nq, const uint8_t* 
         const bool fp4 = use_fp4(ctx, cut);
         int pitch = 0;
         SG_TRY(tc_expand_pair(ctx, dq, nq, dt, nt, fp4, &pitch));
+        if (fp4 && ctx->tc4_cross_one_scan) {
+            // ONE scan: only rows within the cut can be mutual nearest neighbours, and the FP4 scan decodes exactly
+            // those (its hits), so every hit also takes part in its train row's column minimum (ColOut, atomicMin);
+            // half the tensor-core work of the row scan + column scan below
+            const BfPlan rp = tc_plan(ctx, nq, nt, 1, true);
+            SG_TRY(ensure_device_ws(ctx, Carver::padded(tc_pair_keys(ctx, rp, nq) * sizeof(uint2)) + Carver::padded(sizeof(uint32_t) * nt)));
+            Carver ws(ctx->d_ws.ptr);
+            uint2* row_keys = ws.take<uint2>(tc_pair_keys(ctx, rp, nq));
+            uint32_t* col_keys = ws.take<uint32_t>(nt);
+            SG_CUDA(cudaMemsetAsync(col_keys, 0xFF, sizeof(uint32_t) * nt, ctx->stream));
+            TcPair r;
+            SG_TRY(tc_scan_pair(ctx, 0, nq, 1, nt, pitch, cut, true, row_keys, r, col_keys));
+            return bf_launch_mutual_direct(ctx, r.fin, r.keys, nq, col_keys, nq, strict_max_dist, d_idx, d_dist);
+        }
         const BfPlan rp = tc_plan(ctx, nq, nt, 1, fp4), cp = tc_plan(ctx, nt, nq, 1, fp4);
         SG_TRY(ensure_device_ws(ctx, Carver::padded(tc_pair_keys(ctx, rp, nq) * sizeof(uint2)) +
                                          Carver::padded(tc_pair_keys(ctx, cp, nt) * sizeof(uint2))));

@@ -168,6 +168,7 @@ struct Tc4Args {
     float max_dist, ratio;
     int32_t* out_train;            // [pair][max_rows]
     int32_t* out_count;            // [pair], zeroed by the launcher; may be null
+    uint32_t* col_keys;            // single pair: column minima of the cross-check (see ColOut), set to all-ones by the caller
 };
 
 struct Unit4 {
@@ -309,8 +310,16 @@ __device__ __forceinline__ uint32_t or_all(const uint32_t (&v)[N])
 
 // one accumulator with a hit bit: both dots decoded, those within the exact cut folded as
 // (distance << 22 | train index); t1 = the train row of dot1, dot2 belongs to t1 + n_cols (240 but for a last tile)
+// Cross-check in ONE scan (single pair): every hit also competes for its train row's column minimum,
+// atomicMin(col_keys[t], distance << 22 | query row) -- lowest query row on ties, as the column scan would give.  Only
+// hits can be mutual nearest neighbours under the distance cut (bf_api.cu: cut_for_crosscheck), and hits are rare.
+struct ColOut {
+    uint32_t* keys;     // [nt] or null
+    int row;            // this thread's query row, -1 when it is a padding row
+};
+
 __device__ __forceinline__ void decode4_one(uint32_t u, int t1, int t_end, int thr_dot, int thr4, int n_cols, uint32_t& b0,
-                                            uint32_t& b1)
+                                            uint32_t& b1, const ColOut& colo)
 {
     const int x = static_cast<int>(u) - kMagicBits;
     const int dot2 = (x >> 10) + thr4;
@@ -322,6 +331,10 @@ __device__ __forceinline__ void decode4_one(uint32_t u, int t1, int t_end, int t
     const uint32_t k2 = dot2 >= thr_dot && t2 < t_end
                             ? (static_cast<uint32_t>(256 - dot2) >> 1 << kIdxBits) | static_cast<uint32_t>(t2)
                             : kKeyNone;
+    if (colo.keys != nullptr && colo.row >= 0) {
+        if (k1 != kKeyNone) atomicMin(&colo.keys[t1], (k1 & ~kIdxMask) | static_cast<uint32_t>(colo.row));
+        if (k2 != kKeyNone) atomicMin(&colo.keys[t2], (k2 & ~kIdxMask) | static_cast<uint32_t>(colo.row));
+    }
     const uint32_t lo = min(k1, k2), hi = max(k1, k2);
     const uint32_t top = max(lo, b0);
     b0 = min(lo, b0);
@@ -330,14 +343,14 @@ __device__ __forceinline__ void decode4_one(uint32_t u, int t1, int t_end, int t
 
 // one iteration per accumulator that hit (usually one): parked value -> keys
 __device__ __forceinline__ void decode4(const int4* park, uint64_t hits, int t1_first, int t_end, int thr_dot, int thr4,
-                                        int n_cols, uint32_t& b0, uint32_t& b1)
+                                        int n_cols, uint32_t& b0, uint32_t& b1, const ColOut& colo)
 {
     const uint32_t* p = reinterpret_cast<const uint32_t*>(park);
 #pragma unroll 1
     while (hits != 0ull) {
         const int j = __ffsll(static_cast<long long>(hits)) - 1;
         hits &= hits - 1ull;
-        decode4_one(p[j], t1_first + j, t_end, thr_dot, thr4, n_cols, b0, b1);
+        decode4_one(p[j], t1_first + j, t_end, thr_dot, thr4, n_cols, b0, b1, colo);
     }
 }
 
@@ -566,10 +579,12 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTc4Threads, 1) bf_t
         int4 park[16];
         uint32_t b0 = kKeyNone, b1 = kKeyNone;
         uint32_t c_it = 0;
+        ColOut colo{a.col_keys, -1};
         for (long long u = cid; u < a.n_units; u += n_clusters) {
             const Unit4 un = decode_unit4(a, u);
             if (!un.valid) continue;
             const int row = un.row0 + row_in_tile;
+            colo.row = row < un.nq ? row : -1;
             for (int bt = 0; bt < un.n_btiles; ++bt, ++c_it) {
                 if ((c_it & 1u) != static_cast<uint32_t>(g)) continue;       // the other team's tile
                 const int cb = un.t_begin + bt * kT4;
@@ -587,21 +602,21 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTc4Threads, 1) bf_t
                     tmem_pin(xa);
                     tmem_pin(xb);
                     uint64_t m = SG_TC_VARIANT(a.variant, 128) ? 0ull : scan4(xa, park) | (scan4(xb, park + 8) << 32);
-                    if (__builtin_expect(m != 0ull && t_end >= 0, 0)) decode4(park, m, cb, t_end, a.thr_dot, a.thr4, kN4, b0, b1);
+                    if (__builtin_expect(m != 0ull && t_end >= 0, 0)) decode4(park, m, cb, t_end, a.thr_dot, a.thr4, kN4, b0, b1, colo);
                     tmem_wait_ld();
                     tmem_ld32(tbase + 128, xa);
                     tmem_ld32(tbase + 160, xb);
                     tmem_pin(ya);
                     tmem_pin(yb);
                     m = SG_TC_VARIANT(a.variant, 128) ? 0ull : scan4(ya, park) | (scan4(yb, park + 8) << 32);
-                    if (__builtin_expect(m != 0ull && t_end >= 0, 0)) decode4(park, m, cb + 64, t_end, a.thr_dot, a.thr4, kN4, b0, b1);
+                    if (__builtin_expect(m != 0ull && t_end >= 0, 0)) decode4(park, m, cb + 64, t_end, a.thr_dot, a.thr4, kN4, b0, b1, colo);
                     tmem_wait_ld();
                     tmem_ld32(tbase + 192, ya);
                     tmem_ld16(tbase + 224, zc);
                     tmem_pin(xa);
                     tmem_pin(xb);
                     m = SG_TC_VARIANT(a.variant, 128) ? 0ull : scan4(xa, park) | (scan4(xb, park + 8) << 32);
-                    if (__builtin_expect(m != 0ull && t_end >= 0, 0)) decode4(park, m, cb + 128, t_end, a.thr_dot, a.thr4, kN4, b0, b1);
+                    if (__builtin_expect(m != 0ull && t_end >= 0, 0)) decode4(park, m, cb + 128, t_end, a.thr_dot, a.thr4, kN4, b0, b1, colo);
                     tmem_wait_ld();                 // every TMEM read of this stage is done: hand it back before the last fold
                     tmem_pin(ya);
                     tmem_pin(zc);
@@ -613,14 +628,14 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTc4Threads, 1) bf_t
                         tmem_wait_ld();
                         tmem_pin(xa);
                         const uint64_t m = scan4(xa, park);
-                        if (__builtin_expect(m != 0ull && t_end >= 0, 0)) decode4(park, m, cb + c, t_end, a.thr_dot, a.thr4, n_cols, b0, b1);
+                        if (__builtin_expect(m != 0ull && t_end >= 0, 0)) decode4(park, m, cb + c, t_end, a.thr_dot, a.thr4, n_cols, b0, b1, colo);
                     }
                     if (c + 16 <= n_cols) {
                         tmem_ld16(tbase + c, zc);
                         tmem_wait_ld();
                         tmem_pin(zc);
                         const uint64_t m = scan4(zc, park);
-                        if (__builtin_expect(m != 0ull && t_end >= 0, 0)) decode4(park, m, cb + c, t_end, a.thr_dot, a.thr4, n_cols, b0, b1);
+                        if (__builtin_expect(m != 0ull && t_end >= 0, 0)) decode4(park, m, cb + c, t_end, a.thr_dot, a.thr4, n_cols, b0, b1, colo);
                     }
                 }
                 tc_fence_before();
@@ -631,7 +646,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTc4Threads, 1) bf_t
                 }
                 if (!skip && n_cols == kN4) {
                     const uint64_t m = SG_TC_VARIANT(a.variant, 128) ? 0ull : scan4(ya, park) | (scan4(zc, park + 8) << 32);
-                    if (__builtin_expect(m != 0ull && t_end >= 0, 0)) decode4(park, m, cb + 192, t_end, a.thr_dot, a.thr4, kN4, b0, b1);
+                    if (__builtin_expect(m != 0ull && t_end >= 0, 0)) decode4(park, m, cb + 192, t_end, a.thr_dot, a.thr4, kN4, b0, b1, colo);
                 }
             }
             // this team's partial top-2 of the unit (all of it when the unit had no tile for this team)
@@ -665,6 +680,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTc4Threads, 1) bf_t
         asm volatile("" : "+r"(taddr_s0), "+r"(taddr_s1));
         uint2* const xch = reinterpret_cast<uint2*>(smem + kOff4Xch);
         uint32_t u_it = 0;              // valid units seen: parity selects the exchange buffer of the fused finish
+        ColOut colo{a.col_keys, -1};
         for (long long u = cid; u < a.n_units; u += n_clusters) {
             const Unit4 un = decode_unit4(a, u);
             if (!un.valid) {
@@ -673,6 +689,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTc4Threads, 1) bf_t
                     a.out_train[static_cast<size_t>(un.pair) * a.max_rows + un.row0 + row_in_tile] = -1;
                 continue;
             }
+            colo.row = un.row0 + row_in_tile < un.nq ? un.row0 + row_in_tile : -1;
             for (int bt = 0; bt < un.n_btiles; ++bt, ++c_it) {
                 const uint32_t sc = c_it & 1u;
                 const uint32_t taddr = sc ? taddr_s1 : taddr_s0;
@@ -703,14 +720,14 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTc4Threads, 1) bf_t
                         tmem_wait_ld();
                         tmem_pin(vb0);
                         const uint64_t m = scan4(vb0, park);
-                        if (__builtin_expect(m != 0ull && t_end >= 0, 0)) decode4(park, m, t_first + c, t_end, a.thr_dot, a.thr4, n_cols, b0, b1);
+                        if (__builtin_expect(m != 0ull && t_end >= 0, 0)) decode4(park, m, t_first + c, t_end, a.thr_dot, a.thr4, n_cols, b0, b1, colo);
                     }
                     if (c + 16 <= w) {
                         tmem_ld16(tcol + c, vb1);
                         tmem_wait_ld();
                         tmem_pin(vb1);
                         const uint64_t m = scan4(vb1, park);
-                        if (__builtin_expect(m != 0ull && t_end >= 0, 0)) decode4(park, m, t_first + c, t_end, a.thr_dot, a.thr4, n_cols, b0, b1);
+                        if (__builtin_expect(m != 0ull && t_end >= 0, 0)) decode4(park, m, t_first + c, t_end, a.thr_dot, a.thr4, n_cols, b0, b1, colo);
                         c += 16;
                     }
                     if (c + 8 <= w) {
@@ -718,7 +735,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTc4Threads, 1) bf_t
                         tmem_wait_ld();
                         tmem_pin(vb2);
                         const uint64_t m = scan4(vb2, park);
-                        if (__builtin_expect(m != 0ull && t_end >= 0, 0)) decode4(park, m, t_first + c, t_end, a.thr_dot, a.thr4, n_cols, b0, b1);
+                        if (__builtin_expect(m != 0ull && t_end >= 0, 0)) decode4(park, m, t_first + c, t_end, a.thr_dot, a.thr4, n_cols, b0, b1, colo);
                     }
                 }
                 tc_fence_before();
@@ -733,9 +750,9 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTc4Threads, 1) bf_t
                     const uint32_t any = or3(or3(or_all(va0), or_all(va1), or_all(vb0)), or_all(vb1), or_all(vb2));
                     if (__builtin_expect((any & kHitBits) != 0u && t_end >= 0, 0)) {
                         const uint64_t ma = scan4(va0, park) | (scan4(va1, park + 8) << 32);
-                        if (ma != 0ull) decode4(park, ma, cb + c0, t_end, a.thr_dot, a.thr4, kN4, b0, b1);
+                        if (ma != 0ull) decode4(park, ma, cb + c0, t_end, a.thr_dot, a.thr4, kN4, b0, b1, colo);
                         const uint64_t mb = scan4(vb0, park) | (scan4(vb1, park + 8) << 32) | (scan4(vb2, park + 12) << 48);
-                        if (mb != 0ull) decode4(park, mb, cb + c0 + 64, t_end, a.thr_dot, a.thr4, kN4, b0, b1);
+                        if (mb != 0ull) decode4(park, mb, cb + c0 + 64, t_end, a.thr_dot, a.thr4, kN4, b0, b1, colo);
                     }
                 }
             }
@@ -948,7 +965,7 @@ int bf_tc4_launch_expand_pair(slamgpu_ctx* ctx, const uint8_t* d_q, int nq, cons
 // d_cut in [1, 256]: train rows at Hamming distance >= d_cut may be left out of the top-2.
 int bf_tc4_launch_scan(slamgpu_ctx* ctx, const BfPlan& plan, const uint8_t* d_exp_q, int nq, const uint8_t* d_exp_t,
                        int nt, int pitch_rows, const int32_t* d_frame_offset, const int32_t* d_pairs, int n_pairs,
-                       int max_rows, int d_cut, uint2* d_keys, const Tc4Fuse* fuse)
+                       int max_rows, int d_cut, uint2* d_keys, const Tc4Fuse* fuse, uint32_t* d_col_keys)
 {
     // per-DEVICE function attribute: one flag per context (see bf_tc_launch_scan)
     if (!ctx->tc4_attr_set) {
@@ -975,6 +992,8 @@ int bf_tc4_launch_scan(slamgpu_ctx* ctx, const BfPlan& plan, const uint8_t* d_ex
     a.thr_dot = 256 - 2 * (d_cut - 1);                      // -242 .. 256
     a.thr4 = (a.thr_dot + 256) / 4 * 4 - 256;               // rounded DOWN to a multiple of 4: -244 .. 256
     a.keys = d_keys;
+    SG_CHECK(d_col_keys == nullptr || d_pairs == nullptr, "column minima are for single-pair scans");
+    a.col_keys = d_col_keys;
     a.fuse = 0;
     a.max_dist = a.ratio = 0.0f;
     a.out_train = a.out_count = nullptr;

@@ -260,6 +260,8 @@ int slamgpu_create(int device, slamgpu_ctx** out)
     if (mr != nullptr) ctx->map_reserve = std::min(std::max(std::atoi(mr), 0), 1 << 28);
     const char* trb = std::getenv("SLAMGPU_TRACE_BATCH");
     ctx->trace_batch = trb != nullptr && trb[0] == '1';
+    const char* cos = std::getenv("SLAMGPU_TC4_CROSS_ONE_SCAN");
+    if (cos != nullptr) ctx->tc4_cross_one_scan = cos[0] != '0';
     const char* kce = std::getenv("SLAMGPU_KFDB_CACHE");
     if (kce != nullptr) ctx->kfdb_cache_exp = kce[0] != '0';
     const char* tff = std::getenv("SLAMGPU_TC4_FUSE_FINISH");

@@ -195,6 +195,7 @@ struct slamgpu_ctx {
     bool kd_async = true;     // SLAMGPU_KD_ASYNC=0: build the KD-tree inside slamgpu_frame_upload instead of on a thread
     bool kd_speculate = true; // SLAMGPU_KD_SPECULATE=0: a match call waits for the KD-tree instead of running on the tree-free grid
     bool kfdb_cache_exp = true;   // SLAMGPU_KFDB_CACHE=0: the resident key-frame database is expanded anew by every query
+    bool tc4_cross_one_scan = true;  // SLAMGPU_TC4_CROSS_ONE_SCAN=0: the tensor-core cross-check runs a row scan and a column scan
     bool tc4_fuse_finish = true;  // SLAMGPU_TC4_FUSE_FINISH=0: batches always run the finish kernel after the FP4 scan
     bool bf_push = true;          // SLAMGPU_BF_PUSH=0: batch calls into pinned result lists bring their lists back by host-queued copies
     bool bf_zero_copy = true;     // SLAMGPU_BF_ZEROCOPY=0: single-pair brute-force calls download their results with a copy
@@ -346,7 +347,10 @@ struct Tc4Fuse {
 };
 int bf_tc4_launch_scan(slamgpu_ctx* ctx, const BfPlan& plan, const uint8_t* d_exp_q, int nq, const uint8_t* d_exp_t,
                        int nt, int pitch_rows, const int32_t* d_frame_offset, const int32_t* d_pairs, int n_pairs,
-                       int max_rows, int d_cut, uint2* d_keys, const Tc4Fuse* fuse = nullptr);
+                       int max_rows, int d_cut, uint2* d_keys, const Tc4Fuse* fuse = nullptr,
+                       // single pair: every hit also competes for its train row's column minimum (distance << 22 | query
+                       // row) in d_col_keys [nt], which the caller has set to all-ones: the cross-check in one scan
+                       uint32_t* d_col_keys = nullptr);
 
 // ---- projection (proj_kernels.cu) -----------------------------------------------------------
 struct ProjFrameArgs {

@@ -430,6 +430,31 @@ def test_fp4_engine_tie_heavy_4000x4000_at_every_hit_density(oracle, pkg, monkey
         assert len(oq) > 100
 
 
+@pytest.mark.parametrize("one_scan", ["1", "0"])
+def test_tensor_core_cross_check_in_one_scan_or_two(oracle, pkg, monkeypatch, one_scan):
+    """match_features on the FP4 engine: by default ONE scan whose hits also compete for their train row's column
+    minimum (atomicMin of distance << 22 | query row), SLAMGPU_TC4_CROSS_ONE_SCAN=0 = a row scan and a column scan.
+    Rectangular, non-tile-sized sets full of ties (rows and columns with several partners at the same distance: the
+    lowest index must win on both sides), every distance bound the engine takes (cut <= 250)."""
+    monkeypatch.setenv("SLAMGPU_BF_ENGINE", "tc")
+    monkeypatch.setenv("SLAMGPU_TC4_CROSS_ONE_SCAN", one_scan)
+    rng = np.random.default_rng(77)
+    matched = 0
+    with pkg.Context(0) as c:
+        for nprev, ncur in ((3001, 4999), (4999, 3001), (700, 4100)):
+            prev, cur = pkg.synthetic.bf_tie_heavy(nprev, ncur, 5 + nprev)
+            prev, cur = prev.copy(), cur.copy()
+            k = min(nprev, ncur) // 3
+            cur[rng.choice(ncur, k, replace=False)] = prev[rng.choice(nprev, k, replace=False)]     # exact copies
+            cur[rng.choice(ncur, k, replace=False)] = prev[rng.choice(nprev, k, replace=True)]      # several copies of one row
+            for max_dist in (1.0, 30.0, 64.0, 100.5, 200.0):
+                ft, fq = c.match_features(prev, cur, max_dist)
+                o_t, o_q = oracle.match_features(prev, cur, max_dist)
+                assert np.array_equal(ft, o_t) and np.array_equal(fq, o_q), (nprev, ncur, max_dist)
+                matched += len(o_q)
+    assert matched > 300
+
+
 def test_two_contexts_on_two_devices_in_one_process(oracle, pkg):
     """The opt-in to > 48 KB of dynamic shared memory is a per-device function attribute: a second context on
     another GPU must set it for itself (round 1 kept one process-wide flag).  Skipped on a one-GPU box."""
